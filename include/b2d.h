@@ -1,0 +1,107 @@
+/*
+ * b2d.h -- C ABI of libb200diff.so: the sm_100a kernels behind the denoiser
+ * train step / sampler step of video-generation/diffusion (reference:
+ * wdas03/lipreading-video-generation, paths relative to /root/reference).
+ *
+ * Contract:
+ *  - every call ENQUEUES work on `stream` and returns; the library never
+ *    allocates or frees device memory, never keeps a pointer past the call and
+ *    never synchronises the stream (CUDA-graph capturable);
+ *  - all buffers are caller-owned device pointers (PyTorch caching allocator);
+ *  - return 0 on success, a B2D_ERR_* code otherwise; text via b2d_last_error();
+ *  - there is NO CPU fallback and no multi-backend dispatch: a device that is
+ *    not compute capability 10.x yields B2D_ERR_ARCH.
+ *
+ * `stream` is a cudaStream_t passed as void* so that the header is plain C.
+ */
+#ifndef B2D_H_
+#define B2D_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2D_OK 0
+#define B2D_ERR_SHAPE 1
+#define B2D_ERR_ALIGN 2
+#define B2D_ERR_ARCH 3
+#define B2D_ERR_WORKSPACE 4
+#define B2D_ERR_CUDA 5
+
+int b2d_version(void);
+const char* b2d_last_error(void);
+/* 0 when the current device is sm_100-class, B2D_ERR_ARCH otherwise. */
+int b2d_check_device(void);
+
+/* ------------------------------------------------------------------------
+ * Diffusion math (elementwise, HBM bound, fp32).
+ * ---------------------------------------------------------------------- */
+
+/* LinearNoiseScheduler.add_noise  (video-generation/diffusion/
+ * linear_noise_scheduler.py:24-46):  x_t = sqrt_acp[t[b]]*x0 + sqrt_1macp[t[b]]*eps
+ * with one timestep per sample.  x0/eps/xt: (B, per_sample) fp32 contiguous;
+ * t: (B,) int64; tables: (T,) fp32 device copies of sqrt_alpha_cum_prod and
+ * sqrt_one_minus_alpha_cum_prod.  mul, mul, add are rounded separately
+ * (no FMA contraction) so the result is bit-identical to the eager reference.
+ * An out-of-range t sets *err_flag (device int32, may be NULL) to 1 and
+ * writes NaN for that sample (the reference raises IndexError). */
+int b2d_q_sample(const float* x0, const float* eps, const int64_t* t,
+                 const float* sqrt_acp, const float* sqrt_1macp, int T,
+                 float* xt, int64_t B, int64_t per_sample, int* err_flag,
+                 void* stream);
+
+/* Sampler updates.  All three take the per-step scalar coefficients that the
+ * host gathers from the schedule tables (bit-exact fp32 table values) so the
+ * kernel does the reference's arithmetic in the reference's order.
+ * z may be NULL when use_noise == 0.  n = number of elements. */
+
+/* LinearNoiseScheduler.sample_prev_timestep (linear_noise_scheduler.py:48-76)
+ *   x0   = clamp((xt - s1m*eps) / sqrt(acp_t), -1, 1)
+ *   mean = (xt - beta*eps / s1m) / sqrt(alpha_t)
+ *   out  = mean + sigma*z   (t > 0)   |   mean   (t == 0) */
+int b2d_ddpm_step(const float* xt, const float* eps, const float* z,
+                  float s1m, float sqrt_acp, float beta, float sqrt_alpha,
+                  float sigma, int use_noise, float* x_prev, float* x0,
+                  int64_t n, void* stream);
+
+/* LinearNoiseSchedulerV2.sample_prev_timestep (linear_noise_scheduler.py:91-101)
+ *   mean = xt - (s1m*eps) / sqrt(alpha_t);  out = mean + sigma*z
+ *   x0   = clamp((xt - s1m*eps) / sqrt_acp, -1, 1) */
+int b2d_ddpm_v2_step(const float* xt, const float* eps, const float* z,
+                     float s1m, float sqrt_alpha, float sqrt_acp, float sigma,
+                     float* x_prev, float* x0, int64_t n, void* stream);
+
+/* CosineNoiseScheduler.sample_prev_timestep (noise_scheduler.py:13-29)
+ *   mean = (xt - s1m*eps) / sqrt_acp;  out = mean + sigma*z (t>0) | mean
+ *   second return value is `mean` itself. */
+int b2d_cosine_step(const float* xt, const float* eps, const float* z,
+                    float s1m, float sqrt_acp, float sigma, int use_noise,
+                    float* x_prev, float* mean_out, int64_t n, void* stream);
+
+/* DDIM eta=0 (not in the reference -- parity unpinned; Song et al. eq. 12):
+ *   x0 = clamp((xt - s1m_t*eps)/sqrt_acp_t, -1, 1)
+ *   out = sqrt_acp_prev*x0 + s1m_prev*eps */
+int b2d_ddim_step(const float* xt, const float* eps, float s1m_t,
+                  float sqrt_acp_t, float sqrt_acp_prev, float s1m_prev,
+                  float* x_prev, float* x0, int64_t n, void* stream);
+
+/* nn.MSELoss() as called at train.py:103,132: mean((pred-target)^2).
+ * partial: workspace of b2d_mse_workspace_bytes(n) bytes; loss: 1 fp32.
+ * Deterministic two-stage reduction (warp shuffle -> block -> last block). */
+size_t b2d_mse_workspace_bytes(int64_t n);
+int b2d_mse_fwd(const float* pred, const float* target, int64_t n,
+                void* workspace, size_t workspace_bytes, float* loss,
+                void* stream);
+/* grad_pred = grad_out * 2*(pred-target)/n ; grad_out is a device scalar. */
+int b2d_mse_bwd(const float* pred, const float* target, const float* grad_out,
+                int64_t n, float* grad_pred, void* stream);
+
+/* B2D_DENOISER_ABI_BEGIN -- denoiser kernels are declared below */
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2D_H_ */
