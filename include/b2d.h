@@ -99,7 +99,55 @@ int b2d_mse_fwd(const float* pred, const float* target, int64_t n,
 int b2d_mse_bwd(const float* pred, const float* target, const float* grad_out,
                 int64_t n, float* grad_pred, void* stream);
 
-/* B2D_DENOISER_ABI_BEGIN -- denoiser kernels are declared below */
+/* ------------------------------------------------------------------------
+ * Denoiser kernels.  Activation layout inside the library is PIXEL-MAJOR
+ * (N,H,W,C) bf16 -- the channels-last image of the reference's NCHW / (B,C,L)
+ * tensors -- so that one row of a tile is one K-major 128-byte line for the
+ * tcgen05 tensor cores.  Weights stay fp32 OIHW in state_dict; the host side
+ * packs bf16 copies [Cout][tap][Cin] for these calls.
+ * ---------------------------------------------------------------------- */
+
+/* Implicit-GEMM convolution on tcgen05/TMEM fed by TMA.
+ * Replaces nn.Conv2d 3x3 pad 1 (stride 1 or 2) and 1x1 convs / Conv1d k=1 of
+ * unet.py:143-152 (Downsample), :194-234 (ResBlock), :298-317 (AttentionBlock
+ * qkv / proj_out), :624-628 (head); also used for dgrad with flipped weights.
+ *   out[n,ho,wo,co] = sum_{dy,dx,ci} X[n, ho*s+dy-p, wo*s+dx-p, ci] * w[co][dy*k+dx][ci]
+ *                     + bias[co] + emb[n,co] + residual[n,ho,wo,co]
+ * X is the channel concatenation [x | x2] (torch.cat at unet.py:672) without
+ * materialising it.  C1, C2 multiples of 64; W a power of two <= 128. */
+typedef struct b2d_conv_args {
+  const void* x;   int64_t ldx;  int C1;     /* bf16 (N,H,W,ldx), channels [0,C1) used */
+  const void* x2;  int64_t ldx2; int C2;     /* optional second source, or NULL / 0 */
+  int N, H, W;                               /* input spatial size */
+  int ksize;                                 /* 1 or 3 (padding ksize/2) */
+  int stride;                                /* 1 or 2 */
+  const void* w;                             /* bf16 [CoutPad][ksize*ksize*(C1+C2)] */
+  int Cout;                                  /* logical output channels */
+  int CoutPad;                               /* rows of w: multiple of 16 */
+  const float* bias;                         /* [Cout] or NULL */
+  const float* emb;                          /* [N][Cout] per-sample add (unet.py:266) or NULL */
+  const void* residual; int64_t ldres;       /* bf16 (N,Ho,Wo,ldres) added in the epilogue, or NULL */
+  void* out; int64_t ldo;                    /* bf16 (N,Ho,Wo,ldo) or NULL */
+  float* out_nchw_f32;                       /* optional fp32 (N,Cout,Ho,Wo) output (model output) */
+} b2d_conv_args;
+
+int b2d_conv2d(const b2d_conv_args* a, void* stream);
+
+/* Weight gradient of the same convolution (fp32, ACCUMULATED into dw):
+ *   dw[co][tap][ci] += sum_{n,ho,wo} dy[n,ho,wo,co] * X[n, ho*s+dy-p, wo*s+dx-p, ci]
+ * dy: bf16 (N,Ho,Wo,lddy).  dw: fp32 [Cout][taps*(C1+C2)] (caller zeroes). */
+typedef struct b2d_wgrad_args {
+  const void* x;   int64_t ldx;  int C1;
+  const void* x2;  int64_t ldx2; int C2;
+  int N, H, W;
+  int ksize, stride;
+  const void* dy;  int64_t lddy; int Cout;   /* Cout multiple of 64 (or <= 16 via the small path) */
+  float* dw;
+} b2d_wgrad_args;
+
+int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream);
+
+/* B2D_DENOISER_ABI_BEGIN -- further denoiser kernels are declared below */
 
 #ifdef __cplusplus
 }

@@ -1,0 +1,103 @@
+"""ctypes binding of libb200diff.so (the C ABI declared in include/b2d.h).
+
+There is deliberately no fallback: if the shared library is missing or a call
+returns non-zero, a RuntimeError is raised (north_star: "no CPU fallback").
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200diff.so")
+
+_lib = None
+
+c_void_p, c_int, c_int64, c_float, c_size_t = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_size_t
+
+
+class ConvArgs(C.Structure):
+    _fields_ = [
+        ("x", c_void_p), ("ldx", c_int64), ("C1", c_int),
+        ("x2", c_void_p), ("ldx2", c_int64), ("C2", c_int),
+        ("N", c_int), ("H", c_int), ("W", c_int),
+        ("ksize", c_int), ("stride", c_int),
+        ("w", c_void_p), ("Cout", c_int), ("CoutPad", c_int),
+        ("bias", c_void_p), ("emb", c_void_p),
+        ("residual", c_void_p), ("ldres", c_int64),
+        ("out", c_void_p), ("ldo", c_int64),
+        ("out_nchw_f32", c_void_p),
+    ]
+
+
+class WgradArgs(C.Structure):
+    _fields_ = [
+        ("x", c_void_p), ("ldx", c_int64), ("C1", c_int),
+        ("x2", c_void_p), ("ldx2", c_int64), ("C2", c_int),
+        ("N", c_int), ("H", c_int), ("W", c_int),
+        ("ksize", c_int), ("stride", c_int),
+        ("dy", c_void_p), ("lddy", c_int64), ("Cout", c_int),
+        ("dw", c_void_p),
+    ]
+
+
+# name -> (restype, argtypes); every symbol include/b2d.h declares must appear here
+SIGNATURES = {
+    "b2d_version": (c_int, []),
+    "b2d_last_error": (C.c_char_p, []),
+    "b2d_check_device": (c_int, []),
+    "b2d_q_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64,
+                             c_void_p, c_void_p]),
+    "b2d_ddpm_step": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_float, c_float, c_float, c_int,
+                              c_void_p, c_void_p, c_int64, c_void_p]),
+    "b2d_ddpm_v2_step": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_float, c_float, c_void_p,
+                                 c_void_p, c_int64, c_void_p]),
+    "b2d_cosine_step": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_float, c_int, c_void_p, c_void_p,
+                                c_int64, c_void_p]),
+    "b2d_ddim_step": (c_int, [c_void_p, c_void_p, c_float, c_float, c_float, c_float, c_void_p, c_void_p, c_int64,
+                              c_void_p]),
+    "b2d_mse_workspace_bytes": (c_size_t, [c_int64]),
+    "b2d_mse_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
+    "b2d_mse_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
+    "b2d_conv2d": (c_int, [C.POINTER(ConvArgs), c_void_p]),
+    "b2d_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
+}
+
+
+def lib() -> C.CDLL:
+    """Load (once) and return the shared library; raise loudly when it is absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise RuntimeError(
+                f"{LIB_PATH} is missing: build it with `python -m lipreading_video_generation_b200.build` "
+                "(there is no CPU / PyTorch fallback for the sm_100a kernels)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)  # AttributeError if the symbol is not exported
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = lib().b2d_last_error()
+        raise RuntimeError(f"{what} failed (code {rc}): {msg.decode() if msg else ''}")
+
+
+def ptr(t: torch.Tensor | None) -> int | None:
+    return None if t is None else t.data_ptr()
+
+
+def stream_ptr() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def require_cuda(*tensors: torch.Tensor) -> None:
+    for t in tensors:
+        if t is not None and not t.is_cuda:
+            raise RuntimeError("libb200diff kernels need CUDA tensors on an sm_100a device (no CPU fallback)")

@@ -1,0 +1,235 @@
+// conv_wgrad.cu -- convolution weight gradient on tcgen05 tensor cores.
+//
+//   dw[co][tap][ci] += sum_pixels dy[pix][co] * X[pix + tap][ci]
+//
+// GEMM view per (tap, co-tile, ci-tile):  M = 128 output channels, N = 64 or 128 input channels,
+// K = pixels, walked 128 pixels per pipeline stage (8 tcgen05.mma of K=16) and split across CTAs
+// (grid.y); partial sums are reduced with fp32 atomics into dw.
+//
+// Both operands are "MN-major" for the tensor core: the TMA boxes land as [128 pixels][64 channels]
+// (pixel = K index is the slow axis, channel = M/N index is contiguous), described to tcgen05 by an
+// MN-major SWIZZLE_128B descriptor (SBO = 1024 B to the next 8 pixels, LBO = 16 KB to the next
+// 64-channel block).  The X box is shifted by the tap and zero-filled out of bounds exactly as in
+// the forward kernel, so padding and stride-2 phases are handled identically.
+#include "common.cuh"
+#include "tmap.cuh"
+#include "umma.cuh"
+
+namespace b2d {
+using namespace umma;
+
+struct WgradMaps {
+  CUtensorMap x[4];
+  CUtensorMap x2;
+  CUtensorMap dy;
+};
+
+struct WgradParams {
+  int taps, ksize, stride;
+  int C1, Ctot;          // channels of source 1, total input channels
+  int HoWo, rows, imgs;
+  int pixel_tiles;       // ceil(N*Ho*Wo / 128)
+  int Cout;
+  int co_tiles, ci_tiles, BNci;
+  int co_blocks;         // 64-channel dy blocks loaded per stage (1 when Cout == 64: loaded twice)
+  float* dw;
+};
+
+constexpr int WG_THREADS = 192;
+constexpr int WG_STAGES = 3;
+constexpr int BLK = 128 * 128;  // one [128 pixels][64 ch] block
+
+__global__ void __launch_bounds__(WG_THREADS)
+conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int nb = p.BNci / 64;
+  const uint32_t stage_bytes = (uint32_t)(2 + nb) * BLK;
+  uint64_t* full_bar = (uint64_t*)(smem + (size_t)WG_STAGES * stage_bytes);
+  uint64_t* empty_bar = full_bar + WG_STAGES;
+  uint64_t* acc_bar = empty_bar + WG_STAGES;
+  uint32_t* tmem_slot = (uint32_t*)(acc_bar + 1);
+
+  // work item decode: blockIdx.x = (tap * co_tiles + co_t) * ci_tiles + ci_t
+  int w = blockIdx.x;
+  const int ci_t = w % p.ci_tiles; w /= p.ci_tiles;
+  const int co_t = w % p.co_tiles; w /= p.co_tiles;
+  const int tap = w;
+  const int co0 = co_t * 128;
+  const int ci0 = ci_t * p.BNci;
+  const int split = blockIdx.y, nsplit = gridDim.y;
+  const int my_iters = (p.pixel_tiles - split + nsplit - 1) / nsplit;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < WG_STAGES; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  const uint32_t tmem_cols = p.BNci <= 64 ? 64 : 128;
+  if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      const int pad = p.ksize >> 1;
+      const int dy_ = tap / p.ksize, dx_ = tap - dy_ * p.ksize;
+      int hoff, wc, ph = 0;
+      if (p.stride == 1) { hoff = dy_ - pad; wc = dx_ - pad; }
+      else { ph = ((dy_ + 1) & 1) * 2 + ((dx_ + 1) & 1); hoff = (dy_ == 0 ? -1 : 0); wc = (dx_ == 0 ? -1 : 0); }
+      for (int it = 0; it < my_iters; ++it) {
+        const int tile = split + it * nsplit;
+        int img0, h0;
+        if (p.HoWo >= 128) { const int tpi = p.HoWo >> 7; img0 = tile / tpi; h0 = (tile - img0 * tpi) * p.rows; }
+        else { img0 = tile * p.imgs; h0 = 0; }
+        const int s = it % WG_STAGES;
+        const uint32_t par = (uint32_t)((it / WG_STAGES) & 1);
+        mbar_wait(&empty_bar[s], par ^ 1u);
+        uint8_t* base = smem + (size_t)s * stage_bytes;
+        mbar_expect_tx(&full_bar[s], stage_bytes);
+        // A: dy blocks (two 64-channel blocks; the same block twice when Cout == 64)
+        tma_load_4d(base, &maps.dy, &full_bar[s], co0, 0, h0, img0);
+        tma_load_4d(base + BLK, &maps.dy, &full_bar[s], p.co_blocks == 2 ? co0 + 64 : co0, 0, h0, img0);
+        // B: shifted X blocks
+        for (int j = 0; j < nb; ++j) {
+          const int c = ci0 + j * 64;
+          if (c < p.C1) tma_load_4d(base + (2 + j) * BLK, &maps.x[ph], &full_bar[s], c, wc, h0 + hoff, img0);
+          else          tma_load_4d(base + (2 + j) * BLK, &maps.x2, &full_bar[s], c - p.C1, wc, h0 + hoff, img0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = make_idesc_bf16(128, p.BNci, 1, 1);
+    for (int it = 0; it < my_iters; ++it) {
+      const int s = it % WG_STAGES;
+      const uint32_t par = (uint32_t)((it / WG_STAGES) & 1);
+      mbar_wait(&full_bar[s], par);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+        const uint32_t b_addr = a_addr + 2 * BLK;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          mma_bf16_ss(tmem_base, make_sdesc_sw128(a_addr + k * 2048, BLK, 1024),
+                      make_sdesc_sw128(b_addr + k * 2048, BLK, 1024), idesc, (uint32_t)((it | k) != 0));
+        }
+        mma_commit(&empty_bar[s]);
+        if (it == my_iters - 1) mma_commit(acc_bar);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;  // output channel within the tile
+    const int co = co0 + row;
+    const bool valid = (my_iters > 0) && (co < p.Cout) && (p.co_blocks == 2 || row < 64);
+    if (my_iters > 0) {
+      mbar_wait(acc_bar, 0);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      const long long Ktot = (long long)p.taps * p.Ctot;
+      for (int c0 = 0; c0 < p.BNci; c0 += 16) {
+        uint32_t r[16];
+        __syncwarp();
+        tmem_ld16(taddr + (uint32_t)c0, r);
+        tmem_ld_wait();
+        if (valid) {
+          float* dst = p.dw + (long long)co * Ktot + (long long)tap * p.Ctot + ci0 + c0;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) atomicAdd(dst + j, __uint_as_float(r[j]));
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
+static bool is_pow2w(int v) { return v > 0 && (v & (v - 1)) == 0; }
+
+static int make_map4(CUtensorMap* m, const void* base, int C, long long ld, int N, int H, int W, int phase_stride,
+                     int Wo, int rows, int imgs) {
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)(W / phase_stride), (uint64_t)(H / phase_stride), (uint64_t)N};
+  const uint64_t str[3] = {(uint64_t)ld * 2 * phase_stride, (uint64_t)ld * 2 * W * phase_stride,
+                           (uint64_t)ld * 2 * W * H};
+  const uint32_t box[4] = {64u, (uint32_t)Wo, (uint32_t)rows, (uint32_t)imgs};
+  return make_tmap_bf16(m, base, 4, dims, str, box);
+}
+
+}  // namespace b2d
+
+using namespace b2d;
+
+extern "C" int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream) {
+  B2D_REQUIRE(a && a->x && a->dy && a->dw, B2D_ERR_SHAPE, "wgrad: null argument");
+  B2D_REQUIRE(a->ksize == 1 || a->ksize == 3, B2D_ERR_SHAPE, "wgrad: ksize %d", a->ksize);
+  B2D_REQUIRE(a->stride == 1 || (a->stride == 2 && a->ksize == 3), B2D_ERR_SHAPE, "wgrad: stride %d", a->stride);
+  const int C2 = a->x2 ? a->C2 : 0;
+  B2D_REQUIRE(a->C1 > 0 && a->C1 % 64 == 0 && C2 % 64 == 0, B2D_ERR_SHAPE, "wgrad: channels (%d,%d) not multiples of 64",
+              a->C1, C2);
+  B2D_REQUIRE(a->stride == 1 || C2 == 0, B2D_ERR_SHAPE, "wgrad: two-source input needs stride 1");
+  B2D_REQUIRE(a->Cout > 0 && a->Cout % 64 == 0, B2D_ERR_SHAPE, "wgrad: Cout=%d must be a multiple of 64", a->Cout);
+  B2D_REQUIRE(a->H % a->stride == 0 && a->W % a->stride == 0, B2D_ERR_SHAPE, "wgrad: odd plane");
+  const int Ho = a->H / a->stride, Wo = a->W / a->stride;
+  B2D_REQUIRE(is_pow2w(Wo) && Wo <= 128, B2D_ERR_SHAPE, "wgrad: output width %d must be a power of two <= 128", Wo);
+  int rows = 128 / Wo, imgs = 1;
+  if (rows > Ho) {
+    B2D_REQUIRE((128 % (Ho * Wo)) == 0, B2D_ERR_SHAPE, "wgrad: plane %dx%d does not tile 128 pixels", Ho, Wo);
+    rows = Ho; imgs = 128 / (Ho * Wo);
+  } else {
+    B2D_REQUIRE(Ho % rows == 0, B2D_ERR_SHAPE, "wgrad: height %d not a multiple of %d", Ho, rows);
+  }
+  WgradMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  int rc;
+  if (a->stride == 1) {
+    rc = make_map4(&maps.x[0], a->x, a->C1, a->ldx, a->N, a->H, a->W, 1, Wo, rows, imgs);
+    if (rc) return rc;
+    for (int i = 1; i < 4; ++i) maps.x[i] = maps.x[0];
+  } else {
+    for (int pa = 0; pa < 2; ++pa)
+      for (int pb = 0; pb < 2; ++pb) {
+        const __nv_bfloat16* base = (const __nv_bfloat16*)a->x + ((long long)pa * a->W + pb) * a->ldx;
+        rc = make_map4(&maps.x[pa * 2 + pb], base, a->C1, a->ldx, a->N, a->H, a->W, 2, Wo, rows, imgs);
+        if (rc) return rc;
+      }
+  }
+  if (C2) { rc = make_map4(&maps.x2, a->x2, C2, a->ldx2, a->N, a->H, a->W, 1, Wo, rows, imgs); if (rc) return rc; }
+  else maps.x2 = maps.x[0];
+  rc = make_map4(&maps.dy, a->dy, a->Cout, a->lddy, a->N, Ho, Wo, 1, Wo, rows, imgs);
+  if (rc) return rc;
+
+  WgradParams p;
+  p.taps = a->ksize * a->ksize; p.ksize = a->ksize; p.stride = a->stride;
+  p.C1 = a->C1; p.Ctot = a->C1 + C2;
+  p.HoWo = Ho * Wo; p.rows = rows; p.imgs = imgs;
+  const long long total_pixels = (long long)a->N * Ho * Wo;
+  p.pixel_tiles = (int)((total_pixels + 127) / 128);
+  p.Cout = a->Cout;
+  p.co_tiles = (a->Cout + 127) / 128;
+  p.co_blocks = (a->Cout % 128 == 0) ? 2 : 1;
+  B2D_REQUIRE(p.co_blocks == 2 || a->Cout == 64, B2D_ERR_SHAPE, "wgrad: Cout=%d must be 64 or a multiple of 128", a->Cout);
+  // a 128-wide ci tile must not straddle the two sources unless both are multiples of 128
+  p.BNci = (a->C1 % 128 == 0 && C2 % 128 == 0) ? 128 : 64;
+  p.ci_tiles = p.Ctot / p.BNci;
+  p.dw = a->dw;
+  const int items = p.taps * p.co_tiles * p.ci_tiles;
+  int nsplit = (2 * num_sms() + items - 1) / items;
+  if (nsplit > p.pixel_tiles) nsplit = p.pixel_tiles;
+  if (nsplit < 1) nsplit = 1;
+  const size_t smem = (size_t)WG_STAGES * 4 * BLK + (2 * WG_STAGES + 1) * 8 + 16 + 1024;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2D_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    attr_set = true;
+  }
+  dim3 grid((unsigned)items, (unsigned)nsplit);
+  conv_wgrad_kernel<<<grid, WG_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
