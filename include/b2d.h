@@ -147,6 +147,16 @@ typedef struct b2d_wgrad_args {
 
 int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream);
 
+/* Flash-style self-attention forward (QKVAttentionLegacy.forward unet.py:349-366 when
+ * new_order == 0; QKVAttention.forward unet.py:382-401 when new_order == 1):
+ *   a = softmax_fp32((q*ch^-1/4)^T (k*ch^-1/4)) v   per (sample, head), L = H*W tokens.
+ * qkv: bf16 (N, L, ldqkv) pixel-major image of the reference's (N, 3*heads*ch, L) tensor, with the
+ * reference's channel order ([head][q|k|v][ch] legacy, [q|k|v][head][ch] new).
+ * out: bf16 (N, L, ldo), head h at channels [h*ch, (h+1)*ch).  lse: fp32 (N, heads, L) or NULL,
+ * log2-domain log-sum-exp of the scaled logits (saved for the backward).  ch in {64,128,256}. */
+int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
+                      void* out, int64_t ldo, float* lse, void* stream);
+
 /* B2D_DENOISER_ABI_BEGIN -- further denoiser kernels are declared below */
 
 #ifdef __cplusplus

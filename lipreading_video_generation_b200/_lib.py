@@ -63,6 +63,8 @@ SIGNATURES = {
     "b2d_mse_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "b2d_conv2d": (c_int, [C.POINTER(ConvArgs), c_void_p]),
     "b2d_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
+    "b2d_attention_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p,
+                                  c_void_p]),
 }
 
 
