@@ -157,6 +157,72 @@ int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream);
 int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
                       void* out, int64_t ldo, float* lse, void* stream);
 
+/* GroupNorm32(32, C) [+ SiLU] [+ dropout] on pixel-major bf16 (utils.py:54-56,130-137; call sites
+ * unet.py:194-198 in_layers, :218-225 out_layers incl. nn.Dropout, :297 attention norm, :624-628 head).
+ * Statistics in fp32/fp64 as the reference's `.float()` GroupNorm.  The input is the channel
+ * concatenation [x1 | x2] (x2 may be NULL).  act: 0 none, 1 SiLU.  drop_p > 0 applies an inverted
+ * dropout mask from a counter-based Philox stream keyed by `seed` (re-generated in the backward). */
+typedef struct b2d_gn_args {
+  const void* x1; int64_t ld1; int C1;
+  const void* x2; int64_t ld2; int C2;
+  int N, HW;
+  const float* gamma; const float* beta;     /* [C1+C2] */
+  float eps;
+  int act;
+  float drop_p;
+  uint64_t seed;
+} b2d_gn_args;
+
+size_t b2d_groupnorm_workspace_bytes(int N, int Ctot);
+/* y: bf16 (N,HW,C1+C2) contiguous; mean, rstd: fp32 [N][32] (saved for the backward). */
+int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, float* rstd, void* workspace,
+                      size_t workspace_bytes, void* stream);
+/* dy: bf16 (N,HW,C1+C2) gradient w.r.t. y.  dx1 (N,HW,lddx1) / dx2 (N,HW,lddx2) receive the input
+ * gradients; add_a / add_b (optional, bf16, channel pitch lda / ldb) are ADDED to dx1 so that the
+ * residual / skip gradient accumulation is fused.  dgamma/dbeta: fp32 [C1+C2], accumulated. */
+int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
+                      void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
+                      const void* add_b, int64_t ldb, float* dgamma, float* dbeta, void* workspace,
+                      size_t workspace_bytes, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Layout / conditioning helpers (HBM bound).
+ * ---------------------------------------------------------------------- */
+
+/* UNetAudio.forward conditioning assembly (unet_audio.py:53-61) fused with the NCHW->pixel-major
+ * conversion:  out[n,h,w,:] = [ x_t (Cin) | cond_conv_in(nearest(cond)) (Cim) | audio[n] (A) | 0 ... ]
+ * xt fp32 (N,Cin,S,S); cond fp32 (N,Cc,Hc,Wc) resized with F.interpolate's default 'nearest';
+ * wcond fp32 (Cim,Cc) = cond_conv_in.weight; audio fp32 (N,A); out bf16 (N,S,S,Cpad). */
+int b2d_assemble_input(const float* xt, const float* cond, const float* wcond, const float* audio, int N,
+                       int S, int Cin, int Cc, int Hc, int Wc, int Cim, int A, int Cpad, void* out,
+                       void* stream);
+/* Adjoint: d_wcond (Cim,Cc) and d_audio (N,A) are ACCUMULATED from dX bf16 (N,S,S,Cpad). */
+int b2d_assemble_input_bwd(const void* dX, const float* cond, int N, int S, int Cin, int Cc, int Hc, int Wc,
+                           int Cim, int A, int Cpad, float* d_wcond, float* d_audio, void* stream);
+
+/* Upsample.forward's F.interpolate(scale_factor=2, mode="nearest") (unet.py:112-122) and its adjoint. */
+int b2d_upsample2x(const void* x, void* y, int N, int H, int W, int C, void* stream);
+int b2d_upsample2x_bwd(const void* dy, void* dx, int N, int H, int W, int C, void* stream);
+/* z[n,2h,2w,:] = dy[n,h,w,:], zero elsewhere (stride-2 Downsample dgrad as a stride-1 conv). */
+int b2d_zero_insert2x(const void* dy, void* z, int N, int Ho, int Wo, int C, void* stream);
+/* fp32 (N,C,HW) -> bf16 (N,HW,Cpad) with zero-padded channels. */
+int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad, void* stream);
+/* out[n][c] += sum_pix x[n,pix,c_off+c]  (x bf16 (N,HW,ld)): emb_out / bias / audio gradients. */
+int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, void* stream);
+/* out[c] += sum_r in[r*ld + c] */
+int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream);
+/* timestep_embedding (utils.py:140-158): out[n] = [cos(t*f) | sin(t*f)], f = host-built table [dim/2]. */
+int b2d_timestep_embedding(const int64_t* t, int N, int dim, const float* freqs, float* out, void* stream);
+
+/* Small fp32 Linear layers (time_embed unet.py:483-487, emb_layers unet.py:211-217,
+ * AudioFeatureTransformer unet_audio.py:21-30):
+ *   y = act_out( f_in(x) @ w^T + bias ), f_in = SiLU if silu_in, act_out = ReLU if relu_out. */
+int b2d_linear_fwd(const float* x, const float* w, const float* bias, float* y, int M, int K, int Nout,
+                   int silu_in, int relu_out, void* stream);
+/* dx written (may be NULL); dw, db ACCUMULATED (db may be NULL). y needed only when relu_out. */
+int b2d_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx, float* dw,
+                   float* db, int M, int K, int Nout, int silu_in, int relu_out, void* stream);
+
 /* B2D_DENOISER_ABI_BEGIN -- further denoiser kernels are declared below */
 
 #ifdef __cplusplus

@@ -1,0 +1,349 @@
+// elementwise.cu -- layout / gather / reduction helpers around the tensor-core kernels:
+// conditioning assembly (unet_audio.py:53-61), nearest upsample (unet.py:112-122), stride-2 dgrad
+// zero insertion, NCHW fp32 <-> pixel-major bf16, per-sample column sums (bias / emb gradients),
+// sinusoidal timestep embedding (utils.py:140-158).  All HBM-bound, 16-byte vector accesses.
+#include "common.cuh"
+
+namespace b2d {
+
+__device__ __forceinline__ void ld8(const __nv_bfloat16* p, float* v) {
+  uint4 u = ldg_nc_u4(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ void st8(__nv_bfloat16* p, const float* v) {
+  uint4 u;
+  u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+  u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+// PyTorch 'nearest' source index: floor(dst * in / out) computed in float (F.interpolate default)
+__device__ __forceinline__ int nearest_src(int dst, int in_size, int out_size) {
+  if (in_size == out_size) return dst;
+  const float scale = (float)in_size / (float)out_size;
+  int s = (int)floorf((float)dst * scale);
+  return s < in_size - 1 ? s : in_size - 1;
+}
+
+// ------------------------------------------------------------------ conditioning assembly
+struct AssembleParams {
+  const float* xt;     // (N, Cin, S, S)
+  const float* cond;   // (N, Cc, Hc, Wc) or null
+  const float* wcond;  // (Cim, Cc)
+  const float* audio;  // (N, A)
+  int N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad;
+};
+
+__global__ void __launch_bounds__(256)
+assemble_input_kernel(AssembleParams p, __nv_bfloat16* __restrict__ out) {
+  const int V = p.Cpad >> 3;
+  const long long total = (long long)p.N * p.S * p.S * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    const long long gp = i / V;
+    const int n = (int)(gp / (p.S * p.S));
+    const int pix = (int)(gp - (long long)n * p.S * p.S);
+    const int h = pix / p.S, w = pix - h * p.S;
+    float o[8];
+    float cv[8];
+    bool have_cond = false;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = v * 8 + j;
+      float val = 0.f;
+      if (c < p.Cin) {
+        val = p.xt[((long long)n * p.Cin + c) * p.S * p.S + pix];
+      } else if (c < p.Cin + p.Cim) {
+        if (!have_cond) {
+          const int sh = nearest_src(h, p.Hc, p.S), sw = nearest_src(w, p.Wc, p.S);
+          for (int k = 0; k < p.Cc && k < 8; ++k) cv[k] = p.cond[((long long)n * p.Cc + k) * p.Hc * p.Wc + sh * p.Wc + sw];
+          have_cond = true;
+        }
+        const float* wr = p.wcond + (long long)(c - p.Cin) * p.Cc;
+        for (int k = 0; k < p.Cc && k < 8; ++k) val = fmaf(__ldg(wr + k), cv[k], val);
+      } else if (c < p.Cin + p.Cim + p.A) {
+        val = __ldg(p.audio + (long long)n * p.A + (c - p.Cin - p.Cim));
+      }
+      o[j] = val;
+    }
+    st8(out + gp * p.Cpad + v * 8, o);
+  }
+}
+
+// backward: d_wcond[c][k] += sum_{n,pix} dX[n,pix,Cin+c] * cond[n,k,src(pix)];  d_audio[n][a] += sum_pix dX[n,pix,Cin+Cim+a]
+__global__ void __launch_bounds__(256)
+assemble_input_bwd_kernel(AssembleParams p, const __nv_bfloat16* __restrict__ dX, float* __restrict__ d_wcond,
+                          float* __restrict__ d_audio) {
+  extern __shared__ float sh[];  // [Cim*Cc + A]
+  const int nsh = p.Cim * p.Cc + p.A;
+  for (int i = threadIdx.x; i < nsh; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int n = blockIdx.y;
+  const int V = (p.Cin + p.Cim + p.A + 7) >> 3;  // vectors that carry gradient
+  const int v = threadIdx.x % V;
+  const int rows = blockDim.x / V;
+  const int prow = threadIdx.x / V;
+  float acc[8][3];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = 0.f; }
+  if (prow < rows) {
+    for (int pix = blockIdx.x * rows + prow; pix < p.S * p.S; pix += gridDim.x * rows) {
+      float d[8];
+      ld8(dX + ((long long)n * p.S * p.S + pix) * p.Cpad + v * 8, d);
+      const int h = pix / p.S, w = pix - h * p.S;
+      float cv[3] = {0.f, 0.f, 0.f};
+      if (p.Cim > 0) {
+        const int shh = nearest_src(h, p.Hc, p.S), sww = nearest_src(w, p.Wc, p.S);
+        for (int k = 0; k < p.Cc && k < 3; ++k) cv[k] = p.cond[((long long)n * p.Cc + k) * p.Hc * p.Wc + shh * p.Wc + sww];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int c = v * 8 + j;
+        if (c >= p.Cin && c < p.Cin + p.Cim) {
+          acc[j][0] = fmaf(d[j], cv[0], acc[j][0]); acc[j][1] = fmaf(d[j], cv[1], acc[j][1]); acc[j][2] = fmaf(d[j], cv[2], acc[j][2]);
+        } else if (c >= p.Cin + p.Cim) {
+          acc[j][0] += d[j];
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = v * 8 + j;
+      if (c >= p.Cin && c < p.Cin + p.Cim) {
+        for (int k = 0; k < p.Cc && k < 3; ++k) atomicAdd(&sh[(c - p.Cin) * p.Cc + k], acc[j][k]);
+      } else if (c >= p.Cin + p.Cim && c < p.Cin + p.Cim + p.A) {
+        atomicAdd(&sh[p.Cim * p.Cc + (c - p.Cin - p.Cim)], acc[j][0]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < p.Cim * p.Cc; i += blockDim.x) atomicAdd(&d_wcond[i], sh[i]);
+  for (int i = threadIdx.x; i < p.A; i += blockDim.x) atomicAdd(&d_audio[(long long)n * p.A + i], sh[p.Cim * p.Cc + i]);
+}
+
+// ------------------------------------------------------------------ nearest 2x upsample and its adjoint
+__global__ void __launch_bounds__(256)
+upsample2x_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H, int W, int C) {
+  const int V = C >> 3;
+  const long long total = (long long)N * 4 * H * W * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    long long r = i / V;
+    const int wo = (int)(r % (2 * W)); r /= (2 * W);
+    const int ho = (int)(r % (2 * H));
+    const int n = (int)(r / (2 * H));
+    const uint4 u = ldg_nc_u4(x + (((long long)n * H + (ho >> 1)) * W + (wo >> 1)) * C + v * 8);
+    *reinterpret_cast<uint4*>(y + (((long long)n * 2 * H + ho) * 2 * W + wo) * C + v * 8) = u;
+  }
+}
+__global__ void __launch_bounds__(256)
+upsample2x_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C) {
+  const int V = C >> 3;
+  const long long total = (long long)N * H * W * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    long long r = i / V;
+    const int w = (int)(r % W); r /= W;
+    const int h = (int)(r % H);
+    const int n = (int)(r / H);
+    float s[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+#pragma unroll
+    for (int a = 0; a < 2; ++a)
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        float t[8];
+        ld8(dy + (((long long)n * 2 * H + 2 * h + a) * 2 * W + 2 * w + b) * C + v * 8, t);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s[j] += t[j];
+      }
+    st8(dx + (((long long)n * H + h) * W + w) * C + v * 8, s);
+  }
+}
+// z[n, 2h, 2w] = dy[n, h, w], zero elsewhere: turns the stride-2 conv dgrad into a stride-1 conv
+__global__ void __launch_bounds__(256)
+zero_insert2x_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ z, int N, int Ho, int Wo, int C) {
+  const int V = C >> 3;
+  const long long total = (long long)N * 4 * Ho * Wo * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    long long r = i / V;
+    const int w = (int)(r % (2 * Wo)); r /= (2 * Wo);
+    const int h = (int)(r % (2 * Ho));
+    const int n = (int)(r / (2 * Ho));
+    uint4 u = make_uint4(0, 0, 0, 0);
+    if (((h | w) & 1) == 0) u = ldg_nc_u4(dy + (((long long)n * Ho + (h >> 1)) * Wo + (w >> 1)) * C + v * 8);
+    *reinterpret_cast<uint4*>(z + i * 8) = u;
+  }
+}
+
+// fp32 (N, C, HW) -> bf16 (N, HW, Cpad), zero padded channels
+__global__ void __launch_bounds__(256)
+nchw_to_pixel_major_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int N, int C, int HW, int Cpad) {
+  const int V = Cpad >> 3;
+  const long long total = (long long)N * HW * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    const long long gp = i / V;
+    const int n = (int)(gp / HW);
+    const int pix = (int)(gp - (long long)n * HW);
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = v * 8 + j;
+      o[j] = c < C ? src[((long long)n * C + c) * HW + pix] : 0.f;
+    }
+    st8(dst + gp * Cpad + v * 8, o);
+  }
+}
+
+// ------------------------------------------------------------------ per-sample column sums
+// out[n][c] += sum_pix x[n, pix, c_off + c]   (emb_out gradient unet.py:266; bias grads = sum over n)
+__global__ void __launch_bounds__(256)
+colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int c_off, int C, int HW, float* __restrict__ out) {
+  extern __shared__ float sh[];  // [C]
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int n = blockIdx.y;
+  const int V = C >> 3;
+  const int v = threadIdx.x % V;
+  const int rows = blockDim.x / V;
+  const int prow = threadIdx.x / V;
+  float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
+    float t[8];
+    ld8(x + ((long long)n * HW + pix) * ld + c_off + v * 8, t);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] += t[j];
+  }
+#pragma unroll
+  for (int j = 0; j < 8; ++j) atomicAdd(&sh[v * 8 + j], a[j]);
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&out[(long long)n * C + i], sh[i]);
+}
+
+// out[c] += sum_r in[r][c]
+__global__ void reduce_rows_kernel(const float* __restrict__ in, int R, int C, long long ld, float* __restrict__ out) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= C) return;
+  float a = 0.f;
+  for (int r = 0; r < R; ++r) a += in[(long long)r * ld + c];
+  out[c] += a;
+}
+
+// ------------------------------------------------------------------ timestep embedding (utils.py:140-158)
+// freqs[k] = exp(-ln(max_period) * k / half) is built on the host with the reference's own torch ops
+// (bit-exact table); the kernel does the gather, the int->float cast, the product and cos | sin.
+__global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, int N, int dim,
+                                          const float* __restrict__ freqs, float* __restrict__ out) {
+  const int half = dim / 2;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * dim) return;
+  const int n = i / dim, j = i - n * dim;
+  float v = 0.f;
+  if (j < 2 * half) {
+    const int k = j < half ? j : j - half;
+    const float a = __fmul_rn((float)t[n], __ldg(freqs + k));
+    v = j < half ? cosf(a) : sinf(a);
+  }
+  out[i] = v;
+}
+
+static unsigned ew_blocks(long long work, int threads = 256) {
+  long long b = (work + threads - 1) / threads;
+  long long cap = (long long)num_sms() * 8;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (unsigned)b;
+}
+
+}  // namespace b2d
+
+using namespace b2d;
+
+extern "C" int b2d_assemble_input(const float* xt, const float* cond, const float* wcond, const float* audio, int N,
+                                  int S, int Cin, int Cc, int Hc, int Wc, int Cim, int A, int Cpad, void* out,
+                                  void* stream) {
+  B2D_REQUIRE(xt && out && (A == 0 || audio) && (Cim == 0 || (cond && wcond)), B2D_ERR_SHAPE, "assemble_input: null pointer");
+  B2D_REQUIRE(Cpad % 8 == 0 && Cin + Cim + A <= Cpad && Cc <= 8 && aligned16(out), B2D_ERR_SHAPE,
+              "assemble_input: channels %d+%d+%d do not fit Cpad=%d", Cin, Cim, A, Cpad);
+  AssembleParams p{xt, cond, wcond, audio, N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad};
+  const long long work = (long long)N * S * S * (Cpad / 8);
+  assemble_input_kernel<<<ew_blocks(work), 256, 0, (cudaStream_t)stream>>>(p, (__nv_bfloat16*)out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_assemble_input_bwd(const void* dX, const float* cond, int N, int S, int Cin, int Cc, int Hc, int Wc,
+                                      int Cim, int A, int Cpad, float* d_wcond, float* d_audio, void* stream) {
+  B2D_REQUIRE(dX && (Cim == 0 || (cond && d_wcond)) && (A == 0 || d_audio), B2D_ERR_SHAPE, "assemble_input_bwd: null pointer");
+  B2D_REQUIRE(Cc <= 3 && N <= 65535, B2D_ERR_SHAPE, "assemble_input_bwd: Cc=%d (max 3), N=%d", Cc, N);
+  AssembleParams p{nullptr, cond, nullptr, nullptr, N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad};
+  const int V = (Cin + Cim + A + 7) / 8;
+  B2D_REQUIRE(V <= 256, B2D_ERR_SHAPE, "assemble_input_bwd: too many channels");
+  const int rows = 256 / V;
+  long long chunks = ((long long)S * S + rows - 1) / rows;
+  long long cap = ((long long)num_sms() * 4 + N - 1) / N;
+  if (chunks > cap) chunks = cap;
+  if (chunks < 1) chunks = 1;
+  dim3 grid((unsigned)chunks, (unsigned)N);
+  assemble_input_bwd_kernel<<<grid, 256, (Cim * Cc + A) * sizeof(float), (cudaStream_t)stream>>>(
+      p, (const __nv_bfloat16*)dX, d_wcond, d_audio);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_upsample2x(const void* x, void* y, int N, int H, int W, int C, void* stream) {
+  B2D_REQUIRE(x && y && C % 8 == 0, B2D_ERR_SHAPE, "upsample2x: bad arguments");
+  upsample2x_kernel<<<ew_blocks((long long)N * 4 * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_upsample2x_bwd(const void* dy, void* dx, int N, int H, int W, int C, void* stream) {
+  B2D_REQUIRE(dy && dx && C % 8 == 0, B2D_ERR_SHAPE, "upsample2x_bwd: bad arguments");
+  upsample2x_bwd_kernel<<<ew_blocks((long long)N * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_zero_insert2x(const void* dy, void* z, int N, int Ho, int Wo, int C, void* stream) {
+  B2D_REQUIRE(dy && z && C % 8 == 0, B2D_ERR_SHAPE, "zero_insert2x: bad arguments");
+  zero_insert2x_kernel<<<ew_blocks((long long)N * 4 * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dy, (__nv_bfloat16*)z, N, Ho, Wo, C);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad, void* stream) {
+  B2D_REQUIRE(src && dst && Cpad % 8 == 0 && C <= Cpad, B2D_ERR_SHAPE, "nchw_to_pixel_major: bad arguments");
+  nchw_to_pixel_major_kernel<<<ew_blocks((long long)N * HW * (Cpad / 8)), 256, 0, (cudaStream_t)stream>>>(
+      src, (__nv_bfloat16*)dst, N, C, HW, Cpad);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, void* stream) {
+  B2D_REQUIRE(x && out && C % 8 == 0 && C <= 2048 && c_off % 8 == 0 && ld % 8 == 0 && N <= 65535, B2D_ERR_SHAPE,
+              "colsum: bad arguments C=%d c_off=%d ld=%lld", C, c_off, (long long)ld);
+  const int V = C / 8;
+  const int rows = 256 / V > 0 ? 256 / V : 1;
+  long long chunks = ((long long)HW + rows - 1) / rows;
+  long long cap = ((long long)num_sms() * 8 + N - 1) / N;
+  if (chunks > cap) chunks = cap;
+  if (chunks < 1) chunks = 1;
+  dim3 grid((unsigned)chunks, (unsigned)N);
+  colsum_kernel<<<grid, V * rows, C * sizeof(float), (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, c_off, C, HW, out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream) {
+  B2D_REQUIRE(in && out && R > 0 && C > 0, B2D_ERR_SHAPE, "reduce_rows: bad arguments");
+  reduce_rows_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(in, R, C, ld, out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_timestep_embedding(const int64_t* t, int N, int dim, const float* freqs, float* out, void* stream) {
+  B2D_REQUIRE(t && out && freqs && N > 0 && dim > 0, B2D_ERR_SHAPE, "timestep_embedding: bad arguments");
+  timestep_embedding_kernel<<<(N * dim + 255) / 256, 256, 0, (cudaStream_t)stream>>>(t, N, dim, freqs, out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}

@@ -1,0 +1,386 @@
+// groupnorm.cu -- GroupNorm32(32, C) (+ SiLU, + dropout) forward and backward on pixel-major bf16
+// activations (utils.py:54-56,130-137; used at unet.py:194-198,218-225,297,624-628).
+// Statistics are accumulated in fp32 per thread and fp64 across CTAs, as the reference computes
+// GroupNorm in fp32 regardless of activation dtype.  The input may be the channel concatenation
+// of two tensors (decoder skip connections, unet.py:672) -- it is never materialised.
+//
+// HBM-bound kernels: every thread moves 16-byte vectors (8 bf16 channels of one pixel).
+#include "common.cuh"
+
+namespace b2d {
+
+struct GnSrc {
+  const __nv_bfloat16* x1; long long ld1; int C1;
+  const __nv_bfloat16* x2; long long ld2; int C2;
+};
+
+__device__ __forceinline__ const __nv_bfloat16* src_ptr(const GnSrc& s, long long pix, int c) {
+  return (c < s.C1) ? s.x1 + pix * s.ld1 + c : s.x2 + pix * s.ld2 + (c - s.C1);
+}
+
+__device__ __forceinline__ void load8(const __nv_bfloat16* p, float* v) {
+  uint4 u = ldg_nc_u4(p);
+  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* v) {
+  uint4 u;
+  u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
+  u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
+// Philox-4x32-10 keyed by (seed, element index / 4): dropout mask reproducible in the backward.
+__device__ __forceinline__ uint4 philox4(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1) {
+  uint32_t x0 = c0, x1 = c1, x2 = 0x243F6A88u, x3 = 0x85A308D3u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, x0), lo0 = 0xD2511F53u * x0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, x2), lo1 = 0xCD9E8D57u * x2;
+    const uint32_t y0 = hi1 ^ x1 ^ k0, y2 = hi0 ^ x3 ^ k1;
+    x0 = y0; x1 = lo1; x2 = y2; x3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return make_uint4(x0, x1, x2, x3);
+}
+// keep-mask for 8 consecutive elements starting at element index e (multiple of 8)
+__device__ __forceinline__ void dropout_keep8(unsigned long long seed, unsigned long long e, float p, bool* keep) {
+  const unsigned long long blk = e >> 3;
+  uint4 a = philox4((uint32_t)seed, (uint32_t)(seed >> 32), (uint32_t)blk, (uint32_t)(blk >> 32));
+  const uint32_t w[4] = {a.x, a.y, a.z, a.w};
+  const uint32_t thr = (uint32_t)(p * 65536.0f);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    keep[2 * i] = (w[i] & 0xFFFFu) >= thr;
+    keep[2 * i + 1] = (w[i] >> 16) >= thr;
+  }
+}
+
+// ------------------------------------------------------------------ forward: statistics
+// grid (chunks, N); block = V * rows threads (V = Ctot/8 vectors per pixel).
+// sums: double [N][32][2] (sum, sum of squares), zeroed by the caller.
+__global__ void __launch_bounds__(256)
+gn_stats_kernel(GnSrc s, int HW, int Ctot, double* __restrict__ sums) {
+  extern __shared__ float sh[];  // [2*Ctot]
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V;
+  const int prow = threadIdx.x / V;
+  const int rows = blockDim.x / V;
+  const int n = blockIdx.y;
+  for (int i = threadIdx.x; i < 2 * Ctot; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  float a[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { a[i] = 0.f; q[i] = 0.f; }
+  const int c = v * 8;
+  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
+    float x[8];
+    load8(src_ptr(s, (long long)n * HW + pix, c), x);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a[i] += x[i]; q[i] = fmaf(x[i], x[i], q[i]); }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { atomicAdd(&sh[c + i], a[i]); atomicAdd(&sh[Ctot + c + i], q[i]); }
+  __syncthreads();
+  const int cpg = Ctot >> 5;
+  if (threadIdx.x < 32) {
+    float sa = 0.f, sq = 0.f;
+    for (int i = 0; i < cpg; ++i) { sa += sh[threadIdx.x * cpg + i]; sq += sh[Ctot + threadIdx.x * cpg + i]; }
+    atomicAdd(&sums[((long long)n * 32 + threadIdx.x) * 2 + 0], (double)sa);
+    atomicAdd(&sums[((long long)n * 32 + threadIdx.x) * 2 + 1], (double)sq);
+  }
+}
+
+// ------------------------------------------------------------------ forward: normalise (+SiLU, +dropout)
+// act: 0 = none, 1 = SiLU.  Writes y (N,HW,Ctot) contiguous and mean/rstd [N][32] for the backward.
+__global__ void __launch_bounds__(256)
+gn_apply_kernel(GnSrc s, int HW, int Ctot, const double* __restrict__ sums, const float* __restrict__ gamma,
+                const float* __restrict__ beta, float eps, int act, float drop_p, unsigned long long seed,
+                __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  __shared__ float s_mean[32], s_rstd[32];
+  const int n = blockIdx.y;
+  const int cpg = Ctot >> 5;
+  if (threadIdx.x < 32) {
+    const double cnt = (double)cpg * (double)HW;
+    const double m = sums[((long long)n * 32 + threadIdx.x) * 2] / cnt;
+    double var = sums[((long long)n * 32 + threadIdx.x) * 2 + 1] / cnt - m * m;
+    if (var < 0.0) var = 0.0;
+    const float r = (float)(1.0 / sqrt(var + (double)eps));
+    s_mean[threadIdx.x] = (float)m;
+    s_rstd[threadIdx.x] = r;
+    if (blockIdx.x == 0) { mean_out[n * 32 + threadIdx.x] = (float)m; rstd_out[n * 32 + threadIdx.x] = r; }
+  }
+  __syncthreads();
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V;
+  const int prow = threadIdx.x / V;
+  const int rows = blockDim.x / V;
+  const int c = v * 8;
+  float g[8], b[8], mu[8], rs[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    g[i] = __ldg(gamma + c + i); b[i] = __ldg(beta + c + i);
+    mu[i] = s_mean[(c + i) / cpg]; rs[i] = s_rstd[(c + i) / cpg];
+  }
+  const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
+  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
+    const long long gp = (long long)n * HW + pix;
+    float x[8];
+    load8(src_ptr(s, gp, c), x);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float z = fmaf((x[i] - mu[i]) * rs[i], g[i], b[i]);
+      x[i] = act ? silu_f(z) : z;
+    }
+    if (drop_p > 0.f) {
+      bool keep[8];
+      dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) x[i] = keep[i] ? x[i] * keep_scale : 0.f;
+    }
+    store8(y + gp * Ctot + c, x);
+  }
+}
+
+// ------------------------------------------------------------------ backward: per-(sample, channel) sums
+// ab: fp32 [N][Ctot][2] = (sum dyh, sum dyh * xhat) with dyh = dy * act'(z) (* dropout mask), zeroed by caller.
+__global__ void __launch_bounds__(256)
+gn_bwd_reduce_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int Ctot,
+                     const float* __restrict__ mean, const float* __restrict__ rstd,
+                     const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
+                     unsigned long long seed, float* __restrict__ ab) {
+  extern __shared__ float sh[];  // [2*Ctot]
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V;
+  const int prow = threadIdx.x / V;
+  const int rows = blockDim.x / V;
+  const int n = blockIdx.y;
+  const int cpg = Ctot >> 5;
+  for (int i = threadIdx.x; i < 2 * Ctot; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  const int c = v * 8;
+  float g[8], b[8], mu[8], rs[8], A[8], B[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    g[i] = __ldg(gamma + c + i); b[i] = __ldg(beta + c + i);
+    mu[i] = __ldg(mean + n * 32 + (c + i) / cpg); rs[i] = __ldg(rstd + n * 32 + (c + i) / cpg);
+    A[i] = 0.f; B[i] = 0.f;
+  }
+  const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
+  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
+    const long long gp = (long long)n * HW + pix;
+    float x[8], d[8];
+    load8(src_ptr(s, gp, c), x);
+    load8(dy + gp * Ctot + c, d);
+    if (drop_p > 0.f) {
+      bool keep[8];
+      dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d[i] = keep[i] ? d[i] * keep_scale : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xh = (x[i] - mu[i]) * rs[i];
+      float dh = d[i];
+      if (act) {
+        const float z = fmaf(xh, g[i], b[i]);
+        const float sg = 1.0f / (1.0f + __expf(-z));
+        dh *= sg * (1.0f + z * (1.0f - sg));
+      }
+      A[i] += dh; B[i] = fmaf(dh, xh, B[i]);
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { atomicAdd(&sh[c + i], A[i]); atomicAdd(&sh[Ctot + c + i], B[i]); }
+  __syncthreads();
+  for (int i = threadIdx.x; i < Ctot; i += blockDim.x) {
+    atomicAdd(&ab[((long long)n * Ctot + i) * 2 + 0], sh[i]);
+    atomicAdd(&ab[((long long)n * Ctot + i) * 2 + 1], sh[Ctot + i]);
+  }
+}
+
+// ------------------------------------------------------------------ backward: input gradient
+// dx = rstd * (dyh*gamma - s1/m - xhat*s2/m) (+ add_a + add_b on source 1 channels, + nothing on source 2)
+struct GnBwdOut {
+  __nv_bfloat16* dx1; long long ldd1;
+  __nv_bfloat16* dx2; long long ldd2;
+  const __nv_bfloat16* add_a; long long lda;
+  const __nv_bfloat16* add_b; long long ldb;
+};
+
+__global__ void __launch_bounds__(256)
+gn_bwd_apply_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int Ctot,
+                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
+                    unsigned long long seed, const float* __restrict__ ab, GnBwdOut o) {
+  __shared__ float s1[32], s2[32];
+  const int n = blockIdx.y;
+  const int cpg = Ctot >> 5;
+  if (threadIdx.x < 32) {
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < cpg; ++i) {
+      const int ch = threadIdx.x * cpg + i;
+      const float gm = __ldg(gamma + ch);
+      a = fmaf(gm, ab[((long long)n * Ctot + ch) * 2 + 0], a);
+      b = fmaf(gm, ab[((long long)n * Ctot + ch) * 2 + 1], b);
+    }
+    const float inv_m = 1.0f / ((float)cpg * (float)HW);
+    s1[threadIdx.x] = a * inv_m;
+    s2[threadIdx.x] = b * inv_m;
+  }
+  __syncthreads();
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V;
+  const int prow = threadIdx.x / V;
+  const int rows = blockDim.x / V;
+  const int c = v * 8;
+  float g[8], b[8], mu[8], rs[8], m1[8], m2[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int gi = (c + i) / cpg;
+    g[i] = __ldg(gamma + c + i); b[i] = __ldg(beta + c + i);
+    mu[i] = __ldg(mean + n * 32 + gi); rs[i] = __ldg(rstd + n * 32 + gi);
+    m1[i] = s1[gi]; m2[i] = s2[gi];
+  }
+  const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
+  const bool first = c < s.C1;
+  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
+    const long long gp = (long long)n * HW + pix;
+    float x[8], d[8];
+    load8(src_ptr(s, gp, c), x);
+    load8(dy + gp * Ctot + c, d);
+    if (drop_p > 0.f) {
+      bool keep[8];
+      dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) d[i] = keep[i] ? d[i] * keep_scale : 0.f;
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float xh = (x[i] - mu[i]) * rs[i];
+      float dh = d[i];
+      if (act) {
+        const float z = fmaf(xh, g[i], b[i]);
+        const float sg = 1.0f / (1.0f + __expf(-z));
+        dh *= sg * (1.0f + z * (1.0f - sg));
+      }
+      x[i] = rs[i] * (dh * g[i] - m1[i] - xh * m2[i]);
+    }
+    if (first) {
+      if (o.add_a) { float t[8]; load8(o.add_a + gp * o.lda + c, t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+      if (o.add_b) { float t[8]; load8(o.add_b + gp * o.ldb + c, t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+      store8(o.dx1 + gp * o.ldd1 + c, x);
+    } else {
+      store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+    }
+  }
+}
+
+// dgamma[c] = sum_n ab[n][c][1], dbeta[c] = sum_n ab[n][c][0]  (accumulated into fp32 grads)
+__global__ void gn_param_grad_kernel(const float* __restrict__ ab, int N, int Ctot, float* __restrict__ dgamma,
+                                     float* __restrict__ dbeta) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= Ctot) return;
+  float a = 0.f, b = 0.f;
+  for (int n = 0; n < N; ++n) { a += ab[((long long)n * Ctot + c) * 2]; b += ab[((long long)n * Ctot + c) * 2 + 1]; }
+  dbeta[c] += a;
+  dgamma[c] += b;
+}
+
+static int gn_launch_dims(int N, int HW, int Ctot, dim3* grid, int* threads) {
+  const int V = Ctot / 8;
+  int rows = 256 / V;
+  if (rows < 1) rows = 1;
+  *threads = V * rows;
+  long long chunks = (HW + rows - 1) / rows;
+  long long cap = ((long long)num_sms() * 8 + N - 1) / N;
+  if (chunks > cap) chunks = cap;
+  if (chunks < 1) chunks = 1;
+  *grid = dim3((unsigned)chunks, (unsigned)N);
+  return 0;
+}
+
+static int gn_check(const b2d_gn_args* a, const char* who) {
+  B2D_REQUIRE(a && a->x1, B2D_ERR_SHAPE, "%s: null input", who);
+  const int C2 = a->x2 ? a->C2 : 0;
+  const int Ctot = a->C1 + C2;
+  B2D_REQUIRE(a->C1 % 8 == 0 && C2 % 8 == 0 && Ctot % 32 == 0 && Ctot <= 2048, B2D_ERR_SHAPE,
+              "%s: channels (%d,%d) unsupported", who, a->C1, C2);
+  B2D_REQUIRE(a->N > 0 && a->N <= 65535 && a->HW > 0, B2D_ERR_SHAPE, "%s: bad N=%d HW=%d", who, a->N, a->HW);
+  B2D_REQUIRE(a->ld1 % 8 == 0 && (C2 == 0 || a->ld2 % 8 == 0) && aligned16(a->x1) && (C2 == 0 || aligned16(a->x2)),
+              B2D_ERR_ALIGN, "%s: inputs must be 16-byte aligned rows", who);
+  B2D_REQUIRE(a->drop_p >= 0.f && a->drop_p < 1.f, B2D_ERR_SHAPE, "%s: dropout p=%f", who, a->drop_p);
+  return B2D_OK;
+}
+
+static GnSrc make_src(const b2d_gn_args* a) {
+  GnSrc s;
+  s.x1 = (const __nv_bfloat16*)a->x1; s.ld1 = a->ld1; s.C1 = a->C1;
+  s.x2 = (const __nv_bfloat16*)a->x2; s.ld2 = a->ld2; s.C2 = a->x2 ? a->C2 : 0;
+  return s;
+}
+
+}  // namespace b2d
+
+using namespace b2d;
+
+extern "C" size_t b2d_groupnorm_workspace_bytes(int N, int Ctot) {
+  size_t a = (size_t)N * 32 * 2 * sizeof(double);
+  size_t b = (size_t)N * Ctot * 2 * sizeof(float);
+  return a > b ? a : b;
+}
+
+extern "C" int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, float* rstd, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  int rc = gn_check(a, "groupnorm_fwd");
+  if (rc) return rc;
+  B2D_REQUIRE(y && mean && rstd && workspace && a->gamma && a->beta, B2D_ERR_SHAPE, "groupnorm_fwd: null pointer");
+  const GnSrc s = make_src(a);
+  const int Ctot = s.C1 + s.C2;
+  B2D_REQUIRE(workspace_bytes >= (size_t)a->N * 64 * sizeof(double), B2D_ERR_WORKSPACE, "groupnorm_fwd: workspace");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2D_CHECK_CUDA(cudaMemsetAsync(workspace, 0, (size_t)a->N * 64 * sizeof(double), st));
+  dim3 grid; int threads;
+  gn_launch_dims(a->N, a->HW, Ctot, &grid, &threads);
+  gn_stats_kernel<<<grid, threads, 2 * Ctot * sizeof(float), st>>>(s, a->HW, Ctot, (double*)workspace);
+  B2D_CHECK_LAUNCH();
+  gn_apply_kernel<<<grid, threads, 0, st>>>(s, a->HW, Ctot, (const double*)workspace, a->gamma, a->beta, a->eps,
+                                            a->act, a->drop_p, a->seed, (__nv_bfloat16*)y, mean, rstd);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
+                                 void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
+                                 const void* add_b, int64_t ldb, float* dgamma, float* dbeta, void* workspace,
+                                 size_t workspace_bytes, void* stream) {
+  int rc = gn_check(a, "groupnorm_bwd");
+  if (rc) return rc;
+  const GnSrc s = make_src(a);
+  const int Ctot = s.C1 + s.C2;
+  B2D_REQUIRE(dy && mean && rstd && dx1 && workspace && a->gamma && a->beta && dgamma && dbeta, B2D_ERR_SHAPE,
+              "groupnorm_bwd: null pointer");
+  B2D_REQUIRE(s.C2 == 0 || dx2, B2D_ERR_SHAPE, "groupnorm_bwd: dx2 required for a two-source input");
+  B2D_REQUIRE(workspace_bytes >= (size_t)a->N * Ctot * 2 * sizeof(float), B2D_ERR_WORKSPACE, "groupnorm_bwd: workspace");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2D_CHECK_CUDA(cudaMemsetAsync(workspace, 0, (size_t)a->N * Ctot * 2 * sizeof(float), st));
+  dim3 grid; int threads;
+  gn_launch_dims(a->N, a->HW, Ctot, &grid, &threads);
+  gn_bwd_reduce_kernel<<<grid, threads, 2 * Ctot * sizeof(float), st>>>(
+      s, (const __nv_bfloat16*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
+      (float*)workspace);
+  B2D_CHECK_LAUNCH();
+  GnBwdOut o;
+  o.dx1 = (__nv_bfloat16*)dx1; o.ldd1 = lddx1; o.dx2 = (__nv_bfloat16*)dx2; o.ldd2 = lddx2;
+  o.add_a = (const __nv_bfloat16*)add_a; o.lda = lda; o.add_b = (const __nv_bfloat16*)add_b; o.ldb = ldb;
+  gn_bwd_apply_kernel<<<grid, threads, 0, st>>>(s, (const __nv_bfloat16*)dy, a->HW, Ctot, mean, rstd, a->gamma,
+                                                a->beta, a->act, a->drop_p, a->seed, (const float*)workspace, o);
+  B2D_CHECK_LAUNCH();
+  gn_param_grad_kernel<<<(Ctot + 127) / 128, 128, 0, st>>>((const float*)workspace, a->N, Ctot, dgamma, dbeta);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
