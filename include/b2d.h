@@ -223,6 +223,14 @@ int b2d_linear_fwd(const float* x, const float* w, const float* bias, float* y, 
 int b2d_linear_bwd(const float* x, const float* w, const float* y, const float* dy, float* dx, float* dw,
                    float* db, int M, int K, int Nout, int silu_in, int relu_out, void* stream);
 
+/* Backward of b2d_attention_fwd w.r.t. the packed qkv tensor (replaces autograd through
+ * unet.py:356-366 and the checkpoint recompute of utils.py:179-207).  out / lse are the forward's
+ * results; d_out: bf16 (N,L,lddo) gradient w.r.t. out; dqkv: bf16 (N,L,lddqkv) fully written;
+ * delta_ws: fp32 workspace of N*heads*L elements. */
+int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out, int64_t ldo, const void* d_out,
+                      int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
+                      void* dqkv, int64_t lddqkv, float* delta_ws, void* stream);
+
 /* B2D_DENOISER_ABI_BEGIN -- further denoiser kernels are declared below */
 
 #ifdef __cplusplus

@@ -43,6 +43,16 @@ class WgradArgs(C.Structure):
     ]
 
 
+class GnArgs(C.Structure):
+    _fields_ = [
+        ("x1", c_void_p), ("ld1", c_int64), ("C1", c_int),
+        ("x2", c_void_p), ("ld2", c_int64), ("C2", c_int),
+        ("N", c_int), ("HW", c_int),
+        ("gamma", c_void_p), ("beta", c_void_p),
+        ("eps", c_float), ("act", c_int), ("drop_p", c_float), ("seed", C.c_uint64),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b2d.h declares must appear here
 SIGNATURES = {
     "b2d_version": (c_int, []),
@@ -65,6 +75,24 @@ SIGNATURES = {
     "b2d_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
     "b2d_attention_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p,
                                   c_void_p]),
+    "b2d_attention_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int, c_int,
+                                  c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
+    "b2d_groupnorm_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "b2d_groupnorm_fwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b2d_groupnorm_bwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
+                                  c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
+                                  c_size_t, c_void_p]),
+    "b2d_assemble_input": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 9 + [c_void_p, c_void_p]),
+    "b2d_assemble_input_bwd": (c_int, [c_void_p, c_void_p] + [c_int] * 9 + [c_void_p, c_void_p, c_void_p]),
+    "b2d_upsample2x": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "b2d_upsample2x_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "b2d_zero_insert2x": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "b2d_nchw_to_pixel_major": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
+    "b2d_colsum": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b2d_reduce_rows": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
+    "b2d_timestep_embedding": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
+    "b2d_linear_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),
+    "b2d_linear_bwd": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_void_p]),
 }
 
 
