@@ -125,7 +125,7 @@ typedef struct b2d_conv_args {
   int Cout;                                  /* logical output channels */
   int CoutPad;                               /* rows of w: multiple of 16 */
   const float* bias;                         /* [Cout] or NULL */
-  const float* emb;                          /* [N][Cout] per-sample add (unet.py:266) or NULL */
+  const float* emb; int64_t ldemb;           /* [N][ldemb] per-sample add (unet.py:266) or NULL */
   const void* residual; int64_t ldres;       /* bf16 (N,Ho,Wo,ldres) added in the epilogue, or NULL */
   void* out; int64_t ldo;                    /* bf16 (N,Ho,Wo,ldo) or NULL */
   float* out_nchw_f32;                       /* optional fp32 (N,Cout,Ho,Wo) output (model output) */
@@ -179,10 +179,11 @@ int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, float* rstd, v
                       size_t workspace_bytes, void* stream);
 /* dy: bf16 (N,HW,C1+C2) gradient w.r.t. y.  dx1 (N,HW,lddx1) / dx2 (N,HW,lddx2) receive the input
  * gradients; add_a / add_b (optional, bf16, channel pitch lda / ldb) are ADDED to dx1 so that the
- * residual / skip gradient accumulation is fused.  dgamma/dbeta: fp32 [C1+C2], accumulated. */
+ * residual / skip gradient accumulation is fused; with add_a_full != 0, add_a spans all C1+C2
+ * channels and its upper C2 channels are added to dx2.  dgamma/dbeta: fp32 [C1+C2], accumulated. */
 int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
                       void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
-                      const void* add_b, int64_t ldb, float* dgamma, float* dbeta, void* workspace,
+                      const void* add_b, int64_t ldb, int add_a_full, float* dgamma, float* dbeta, void* workspace,
                       size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------
@@ -207,8 +208,8 @@ int b2d_upsample2x_bwd(const void* dy, void* dx, int N, int H, int W, int C, voi
 int b2d_zero_insert2x(const void* dy, void* z, int N, int Ho, int Wo, int C, void* stream);
 /* fp32 (N,C,HW) -> bf16 (N,HW,Cpad) with zero-padded channels. */
 int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad, void* stream);
-/* out[n][c] += sum_pix x[n,pix,c_off+c]  (x bf16 (N,HW,ld)): emb_out / bias / audio gradients. */
-int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, void* stream);
+/* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x bf16 (N,HW,ld)): emb_out / bias / audio gradients. */
+int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */
 int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream);
 /* timestep_embedding (utils.py:140-158): out[n] = [cos(t*f) | sin(t*f)], f = host-built table [dim/2]. */

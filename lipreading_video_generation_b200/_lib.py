@@ -25,7 +25,7 @@ class ConvArgs(C.Structure):
         ("N", c_int), ("H", c_int), ("W", c_int),
         ("ksize", c_int), ("stride", c_int),
         ("w", c_void_p), ("Cout", c_int), ("CoutPad", c_int),
-        ("bias", c_void_p), ("emb", c_void_p),
+        ("bias", c_void_p), ("emb", c_void_p), ("ldemb", c_int64),
         ("residual", c_void_p), ("ldres", c_int64),
         ("out", c_void_p), ("ldo", c_int64),
         ("out_nchw_f32", c_void_p),
@@ -80,7 +80,7 @@ SIGNATURES = {
     "b2d_groupnorm_workspace_bytes": (c_size_t, [c_int, c_int]),
     "b2d_groupnorm_fwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "b2d_groupnorm_bwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
-                                  c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_void_p, c_void_p,
+                                  c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p,
                                   c_size_t, c_void_p]),
     "b2d_assemble_input": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 9 + [c_void_p, c_void_p]),
     "b2d_assemble_input_bwd": (c_int, [c_void_p, c_void_p] + [c_int] * 9 + [c_void_p, c_void_p, c_void_p]),
@@ -88,7 +88,7 @@ SIGNATURES = {
     "b2d_upsample2x_bwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "b2d_zero_insert2x": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
     "b2d_nchw_to_pixel_major": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),
-    "b2d_colsum": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b2d_colsum": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "b2d_reduce_rows": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "b2d_timestep_embedding": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b2d_linear_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),

@@ -35,7 +35,7 @@ struct ConvParams {
   int stages;
   uint32_t tmem_cols;
   const float* bias;
-  const float* emb;
+  const float* emb; long long ldemb;
   const __nv_bfloat16* residual; long long ldres;
   __nv_bfloat16* out; long long ldo;
   float* out_nchw;
@@ -162,7 +162,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
         for (int j = 0; j < 16; ++j) if (j < ncol) v[j] += __ldg(p.bias + col0 + j);
       }
       if (p.emb) {
-        const float* e = p.emb + (long long)n_img * p.Cout + col0;
+        const float* e = p.emb + (long long)n_img * p.ldemb + col0;
 #pragma unroll
         for (int j = 0; j < 16; ++j) if (j < ncol) v[j] += __ldg(e + j);
       }
@@ -295,7 +295,7 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   if (stages > 6) stages = 6;
   p.stages = stages;
   p.tmem_cols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
-  p.bias = a->bias; p.emb = a->emb;
+  p.bias = a->bias; p.emb = a->emb; p.ldemb = a->ldemb;
   p.residual = (const __nv_bfloat16*)a->residual; p.ldres = a->ldres;
   p.out = (__nv_bfloat16*)a->out; p.ldo = a->ldo;
   p.out_nchw = a->out_nchw_f32;

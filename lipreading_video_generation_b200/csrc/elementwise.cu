@@ -200,7 +200,8 @@ nchw_to_pixel_major_kernel(const float* __restrict__ src, __nv_bfloat16* __restr
 // ------------------------------------------------------------------ per-sample column sums
 // out[n][c] += sum_pix x[n, pix, c_off + c]   (emb_out gradient unet.py:266; bias grads = sum over n)
 __global__ void __launch_bounds__(256)
-colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int c_off, int C, int HW, float* __restrict__ out) {
+colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int c_off, int C, int HW, float* __restrict__ out,
+              long long ldout) {
   extern __shared__ float sh[];  // [C]
   for (int i = threadIdx.x; i < C; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
@@ -219,7 +220,7 @@ colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int c_off, int 
 #pragma unroll
   for (int j = 0; j < 8; ++j) atomicAdd(&sh[v * 8 + j], a[j]);
   __syncthreads();
-  for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&out[(long long)n * C + i], sh[i]);
+  for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&out[(long long)n * ldout + i], sh[i]);
 }
 
 // out[c] += sum_r in[r][c]
@@ -321,7 +322,8 @@ extern "C" int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
-extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, void* stream) {
+extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout,
+                          void* stream) {
   B2D_REQUIRE(x && out && C % 8 == 0 && C <= 2048 && c_off % 8 == 0 && ld % 8 == 0 && N <= 65535, B2D_ERR_SHAPE,
               "colsum: bad arguments C=%d c_off=%d ld=%lld", C, c_off, (long long)ld);
   const int V = C / 8;
@@ -331,7 +333,7 @@ extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, in
   if (chunks > cap) chunks = cap;
   if (chunks < 1) chunks = 1;
   dim3 grid((unsigned)chunks, (unsigned)N);
-  colsum_kernel<<<grid, V * rows, C * sizeof(float), (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, c_off, C, HW, out);
+  colsum_kernel<<<grid, V * rows, C * sizeof(float), (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, c_off, C, HW, out, ldout);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

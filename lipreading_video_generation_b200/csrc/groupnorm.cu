@@ -206,6 +206,7 @@ struct GnBwdOut {
   __nv_bfloat16* dx2; long long ldd2;
   const __nv_bfloat16* add_a; long long lda;
   const __nv_bfloat16* add_b; long long ldb;
+  int add_a_full;  // add_a spans all C1+C2 channels (also added to dx2)
 };
 
 __global__ void __launch_bounds__(256)
@@ -275,6 +276,9 @@ gn_bwd_apply_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int C
         for (int i = 0; i < 8; ++i) x[i] += t[i]; }
       store8(o.dx1 + gp * o.ldd1 + c, x);
     } else {
+      if (o.add_a && o.add_a_full) { float t[8]; load8(o.add_a + gp * o.lda + c, t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
       store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
     }
   }
@@ -356,7 +360,7 @@ extern "C" int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, flo
 
 extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
                                  void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
-                                 const void* add_b, int64_t ldb, float* dgamma, float* dbeta, void* workspace,
+                                 const void* add_b, int64_t ldb, int add_a_full, float* dgamma, float* dbeta, void* workspace,
                                  size_t workspace_bytes, void* stream) {
   int rc = gn_check(a, "groupnorm_bwd");
   if (rc) return rc;
@@ -376,7 +380,7 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
   B2D_CHECK_LAUNCH();
   GnBwdOut o;
   o.dx1 = (__nv_bfloat16*)dx1; o.ldd1 = lddx1; o.dx2 = (__nv_bfloat16*)dx2; o.ldd2 = lddx2;
-  o.add_a = (const __nv_bfloat16*)add_a; o.lda = lda; o.add_b = (const __nv_bfloat16*)add_b; o.ldb = ldb;
+  o.add_a = (const __nv_bfloat16*)add_a; o.lda = lda; o.add_b = (const __nv_bfloat16*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
   gn_bwd_apply_kernel<<<grid, threads, 0, st>>>(s, (const __nv_bfloat16*)dy, a->HW, Ctot, mean, rstd, a->gamma,
                                                 a->beta, a->act, a->drop_p, a->seed, (const float*)workspace, o);
   B2D_CHECK_LAUNCH();

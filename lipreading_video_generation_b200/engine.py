@@ -1,0 +1,518 @@
+"""DenoiserEngine -- hand-scheduled forward / backward of the UNet torso over the C-ABI kernels.
+
+Replaces autograd through unet.py:646-675 (UNetModel.forward) and unet_audio.py:53-66 (conditioning
+assembly) with a static layer schedule: every arithmetic step is one call into libb200diff.so;
+PyTorch owns memory, streams and the parameter objects only.  The whole torso is ONE
+torch.autograd.Function (`denoiser_apply`), so the reference's training recipe
+(`loss.backward(); optimizer.step()`, train.py:131-134) works unchanged.
+
+Layout: activations pixel-major (N,H,W,C) bf16; skip concatenations (unet.py:672) are never
+materialised (two-source kernels); gradient accumulation for residual / skip fan-out is fused into the
+GroupNorm-backward and dgrad epilogues.
+"""
+from __future__ import annotations
+
+import torch
+
+from . import ops
+from .unet import AttentionBlock, Downsample, ResBlock, Upsample, timestep_freqs
+
+
+def _pad64(c: int) -> int:
+    return (c + 63) // 64 * 64
+
+
+class _Ctx:
+    """Saved tensors of one layer (forward -> backward)."""
+    __slots__ = ("kind", "mod", "t")
+
+    def __init__(self, kind, mod):
+        self.kind, self.mod, self.t = kind, mod, {}
+
+
+class DenoiserEngine:
+    def __init__(self, model):
+        self.model = model
+        self.is_audio = hasattr(model, "audio_transformer")
+        self.cin = model.in_channels                      # UNet input channels (195 for UNetAudio)
+        self.cin_pad = _pad64(self.cin)
+        self.resblocks = [m for m in model.modules() if isinstance(m, ResBlock)]
+        self.emb_off = {}
+        off = 0
+        for rb in self.resblocks:
+            self.emb_off[id(rb)] = off
+            off += rb.out_channels
+        self.emb_total = off
+        self._freqs = None
+        self._wcache = {}
+        self._step_seed = 0
+        # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
+        self._grad_layout = None
+
+    # ------------------------------------------------------------------ packed weights
+    def _packed(self, key, param, fn):
+        ver = (param._version, param.data_ptr())
+        hit = self._wcache.get(key)
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        with torch.no_grad():
+            val = fn(param.detach())
+        self._wcache[key] = (ver, val)
+        return val
+
+    def w_fwd(self, conv, cin_pad=None):
+        return self._packed((id(conv), "f"), conv.weight, lambda w: ops.pack_conv_weight(w, cin_pad))
+
+    def w_dgrad(self, conv, cin_pad=None, cout_pad=None):
+        return self._packed((id(conv), "d"), conv.weight, lambda w: ops.pack_dgrad_weight(w, cin_pad, cout_pad))
+
+    def emb_cat(self):
+        ws = [rb.emb_layers[1].weight for rb in self.resblocks]
+        bs = [rb.emb_layers[1].bias for rb in self.resblocks]
+        ver = tuple((w._version, w.data_ptr()) for w in ws) + tuple((b._version, b.data_ptr()) for b in bs)
+        hit = self._wcache.get("embcat")
+        if hit is not None and hit[0] == ver:
+            return hit[1]
+        with torch.no_grad():
+            val = (torch.cat([w.detach() for w in ws], 0).contiguous(), torch.cat([b.detach() for b in bs], 0).contiguous())
+        self._wcache["embcat"] = (ver, val)
+        return val
+
+    def freqs(self, device):
+        if self._freqs is None or self._freqs.device != device:
+            self._freqs = timestep_freqs(self.model.model_channels).to(device)
+        return self._freqs
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, xt, cond, audio_feat, timesteps, train: bool):
+        """Returns (eps_pred fp32 (N,out_ch,S,S), tape).  tape is None when train is False."""
+        m = self.model
+        dev = xt.device
+        N, _, S, _ = xt.shape
+        tape = {"N": N, "S": S} if train else None
+        drop_p = float(m.dropout) if (m.training and train) else 0.0
+        self._step_seed += 1
+        seed_base = (self._step_seed << 20)
+
+        # --- conditioning vectors: time embedding MLP + batched emb_layers
+        te = ops.timestep_embedding(timesteps.to(torch.int64).contiguous(), m.model_channels, self.freqs(dev))
+        l0, l2 = m.time_embed[0], m.time_embed[2]
+        e1 = ops.linear_fwd(te, l0.weight.detach(), l0.bias.detach())
+        emb = ops.linear_fwd(e1, l2.weight.detach(), l2.bias.detach(), silu_in=True)
+        wcat, bcat = self.emb_cat()
+        emb_all = ops.linear_fwd(emb, wcat, bcat, silu_in=True)
+        # --- input assembly (unet_audio.py:53-61) or plain NCHW -> pixel-major
+        if self.is_audio:
+            at = m.audio_transformer.transform[0]
+            avec = ops.linear_fwd(audio_feat.contiguous(), at.weight.detach(), at.bias.detach(), relu_out=True)
+            wcond = m.cond_conv_in.weight.detach().reshape(m.cond_conv_in.weight.shape[0], -1).contiguous() if m.image_cond else None
+            x0 = ops.assemble_input(xt.contiguous(), cond.contiguous() if m.image_cond else None, wcond, avec, self.cin_pad)
+        else:
+            avec = None
+            x0 = ops.nchw_to_pixel_major(xt.contiguous(), self.cin_pad)
+        if train:
+            tape.update(te=te, e1=e1, emb=emb, emb_all=emb_all, avec=avec, x0=x0, cond=cond, audio_feat=audio_feat,
+                        drop_p=drop_p)
+
+        def run_layer(layer, h, skip, idx):
+            seed = seed_base + idx
+            if isinstance(layer, ResBlock):
+                return self._res_fwd(layer, h, skip, emb_all, drop_p, seed, train)
+            if isinstance(layer, AttentionBlock):
+                return self._attn_fwd(layer, h, train)
+            if isinstance(layer, Downsample):
+                out = ops.conv2d(h, self.w_fwd(layer.op), layer.out_channels, 3, 2, bias=layer.op.bias.detach())
+                ctx = _Ctx("down", layer); ctx.t["x"] = h
+                return out, ctx
+            if isinstance(layer, Upsample):
+                u = ops.upsample2x(h)
+                out = ops.conv2d(u, self.w_fwd(layer.conv), layer.out_channels, 3, 1, bias=layer.conv.bias.detach())
+                ctx = _Ctx("up", layer); ctx.t["u"] = u
+                return out, ctx
+            raise RuntimeError(f"unexpected layer {type(layer)}")
+
+        conv_in = m.input_blocks[0][0]
+        h = ops.conv2d(x0, self.w_fwd(conv_in, self.cin_pad), conv_in.out_channels, 3, 1, bias=conv_in.bias.detach())
+        hs = [h]
+        idx = 0
+        enc, mid, dec = [], [], []
+        for block in list(m.input_blocks)[1:]:
+            ctxs = []
+            for layer in block:
+                idx += 1
+                h, ctx = run_layer(layer, h, None, idx)
+                ctxs.append(ctx)
+            enc.append(ctxs)
+            hs.append(h)
+        for layer in m.middle_block:
+            idx += 1
+            h, ctx = run_layer(layer, h, None, idx)
+            mid.append(ctx)
+        for block in m.output_blocks:
+            skip = hs.pop()
+            ctxs = []
+            for li, layer in enumerate(block):
+                idx += 1
+                h, ctx = run_layer(layer, h, skip if li == 0 else None, idx)
+                ctxs.append(ctx)
+            dec.append(ctxs)
+        if train:
+            tape.update(enc=enc, mid=mid, dec=dec)
+        gn, conv_out = m.out[0], m.out[2]
+        hh, mean, rstd = ops.groupnorm_fwd(h, gn.weight.detach(), gn.bias.detach(), act=True, eps=gn.eps)
+        out = torch.empty(N, m.out_channels, S, S, device=dev, dtype=torch.float32)
+        ops.conv2d(hh, self.w_fwd(conv_out), m.out_channels, 3, 1, bias=conv_out.bias.detach(), out_nchw_f32=out)
+        if train:
+            tape.update(head=dict(h=h, hh=hh, mean=mean, rstd=rstd))
+        return out, tape
+
+    def _res_fwd(self, rb, x, x2, emb_all, drop_p, seed, train):
+        gn1, conv1 = rb.in_layers[0], rb.in_layers[2]
+        gn2, conv2 = rb.out_layers[0], rb.out_layers[3]
+        cout = rb.out_channels
+        h1, mean1, rstd1 = ops.groupnorm_fwd(x, gn1.weight.detach(), gn1.bias.detach(), x2=x2, act=True, eps=gn1.eps)
+        off = self.emb_off[id(rb)]
+        h2 = ops.conv2d(h1, self.w_fwd(conv1), cout, 3, 1, bias=conv1.bias.detach(), emb=emb_all[:, off:off + cout])
+        h3, mean2, rstd2 = ops.groupnorm_fwd(h2, gn2.weight.detach(), gn2.bias.detach(), act=True, eps=gn2.eps,
+                                             drop_p=drop_p, seed=seed)
+        if isinstance(rb.skip_connection, torch.nn.Identity):
+            res = x
+        else:
+            sc = rb.skip_connection
+            res = ops.conv2d(x, self.w_fwd(sc), cout, 1, 1, x2=x2, bias=sc.bias.detach())
+        out = ops.conv2d(h3, self.w_fwd(conv2), cout, 3, 1, bias=conv2.bias.detach(), residual=res)
+        ctx = None
+        if train:
+            ctx = _Ctx("res", rb)
+            ctx.t.update(x=x, x2=x2, h1=h1, h2=h2, h3=h3, mean1=mean1, rstd1=rstd1, mean2=mean2, rstd2=rstd2,
+                         drop_p=drop_p, seed=seed)
+        return out, ctx
+
+    def _attn_fwd(self, ab, x, train):
+        gn = ab.norm
+        C_ = ab.channels
+        hn, mean, rstd = ops.groupnorm_fwd(x, gn.weight.detach(), gn.bias.detach(), act=False, eps=gn.eps)
+        qkv = ops.conv2d(hn, self.w_fwd(ab.qkv), 3 * C_, 1, 1, bias=ab.qkv.bias.detach())
+        a, lse = ops.attention_fwd(qkv, ab.num_heads, ab.use_new_attention_order)
+        out = ops.conv2d(a, self.w_fwd(ab.proj_out), C_, 1, 1, bias=ab.proj_out.bias.detach(), residual=x)
+        ctx = None
+        if train:
+            ctx = _Ctx("attn", ab)
+            ctx.t.update(x=x, hn=hn, qkv=qkv, a=a, lse=lse, mean=mean, rstd=rstd)
+        return out, ctx
+
+    # ------------------------------------------------------------------ gradient storage
+    def grad_layout(self):
+        """[(stage, param, packed_shape)] in backward completion order; emb_layers weights are
+        contiguous (resblock order) so that the batched emb GEMM's dW is one matrix."""
+        if self._grad_layout is not None:
+            return self._grad_layout
+        m = self.model
+        order = []
+
+        def add(stage, p, shape=None):
+            order.append((stage, p, tuple(shape) if shape is not None else tuple(p.shape)))
+
+        def conv_shape(conv, cin_pad=None):
+            w = conv.weight
+            co, ci = w.shape[0], w.shape[1]
+            taps = w.numel() // (co * ci)
+            return (max(64, _pad64(co)) if co < 64 else co, taps * (cin_pad or ci))
+
+        def add_layer(stage, layer):
+            if isinstance(layer, ResBlock):
+                for gn in (layer.in_layers[0], layer.out_layers[0]):
+                    add(stage, gn.weight); add(stage, gn.bias)
+                for conv in (layer.in_layers[2], layer.out_layers[3]):
+                    add(stage, conv.weight, conv_shape(conv)); add(stage, conv.bias)
+                if not isinstance(layer.skip_connection, torch.nn.Identity):
+                    add(stage, layer.skip_connection.weight, conv_shape(layer.skip_connection))
+                    add(stage, layer.skip_connection.bias)
+            elif isinstance(layer, AttentionBlock):
+                add(stage, layer.norm.weight); add(stage, layer.norm.bias)
+                for conv in (layer.qkv, layer.proj_out):
+                    add(stage, conv.weight, conv_shape(conv)); add(stage, conv.bias)
+            elif isinstance(layer, Downsample):
+                add(stage, layer.op.weight, conv_shape(layer.op)); add(stage, layer.op.bias)
+            elif isinstance(layer, Upsample):
+                add(stage, layer.conv.weight, conv_shape(layer.conv)); add(stage, layer.conv.bias)
+
+        stage = 0
+        add(stage, m.out[0].weight); add(stage, m.out[0].bias)
+        add(stage, m.out[2].weight, conv_shape(m.out[2])); add(stage, m.out[2].bias, (64,))
+        for block in reversed(list(m.output_blocks)):
+            for layer in reversed(list(block)):
+                stage += 1
+                add_layer(stage, layer)
+        for layer in reversed(list(m.middle_block)):
+            stage += 1
+            add_layer(stage, layer)
+        for block in reversed(list(m.input_blocks)[1:]):
+            for layer in reversed(list(block)):
+                stage += 1
+                add_layer(stage, layer)
+        stage += 1
+        conv_in = m.input_blocks[0][0]
+        add(stage, conv_in.weight, conv_shape(conv_in, self.cin_pad)); add(stage, conv_in.bias)
+        stage += 1
+        for rb in self.resblocks:
+            add(stage, rb.emb_layers[1].weight)
+        for rb in self.resblocks:
+            add(stage, rb.emb_layers[1].bias)
+        for lin in (m.time_embed[2], m.time_embed[0]):
+            add(stage, lin.weight); add(stage, lin.bias)
+        if self.is_audio:
+            at = m.audio_transformer.transform[0]
+            add(stage, at.weight); add(stage, at.bias)
+            if m.image_cond:
+                add(stage, m.cond_conv_in.weight, (m.cond_conv_in.weight.shape[0], m.cond_conv_in.weight.shape[1]))
+        self._grad_layout = order
+        self.n_stages = stage + 1
+        return order
+
+    def torso_params(self):
+        return [p for _, p, _ in self.grad_layout()]
+
+
+class _Grads:
+    """One flat fp32 buffer holding every torso gradient in packed layout (zeroed once per step)."""
+
+    def __init__(self, eng: DenoiserEngine, device):
+        layout = eng.grad_layout()
+        self.offsets = {}
+        off = 0
+        self.stage_end = [0] * eng.n_stages
+        for stage, p, shape in layout:
+            n = 1
+            for d in shape:
+                n *= d
+            self.offsets[id(p)] = (off, shape)
+            off += (n + 3) // 4 * 4
+            self.stage_end[stage] = off
+        self.flat = torch.zeros(off, device=device, dtype=torch.float32)
+        self.eng = eng
+
+    def g(self, p):
+        off, shape = self.offsets[id(p)]
+        n = 1
+        for d in shape:
+            n *= d
+        return self.flat[off:off + n].view(shape)
+
+    def unpacked(self, p):
+        """View of the packed gradient in the parameter's own shape (OIHW for convolutions)."""
+        buf = self.g(p)
+        if tuple(buf.shape) == tuple(p.shape):
+            return buf
+        if p.dim() == 1:                       # padded bias (head conv)
+            return buf[:p.shape[0]]
+        co, ci = p.shape[0], p.shape[1]
+        taps = p.numel() // (co * ci)
+        k = int(round(taps ** 0.5)) if p.dim() == 4 else 1
+        cip = buf.shape[1] // taps
+        v = buf.view(buf.shape[0], taps, cip)[:co, :, :ci]         # [co][tap][ci]
+        if p.dim() == 4:
+            return v.reshape(co, k, k, ci).permute(0, 3, 1, 2) if (cip == ci and buf.shape[0] == co) else \
+                v.contiguous().view(co, k, k, ci).permute(0, 3, 1, 2)
+        if p.dim() == 3:
+            return v.permute(0, 2, 1)                                # Conv1d (O, I, 1)
+        return v.reshape(co, ci)
+
+
+def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
+    """Hand-scheduled backward.  dout: fp32 (N,out_ch,S,S).  Returns (_Grads, d_audio_feat or None)."""
+    m = eng.model
+    N = tape["N"]
+    dev = dout.device
+    G = _Grads(eng, dev)
+    d_emb_all = torch.zeros(N, eng.emb_total, device=dev, dtype=torch.float32)
+    stage = 0
+
+    def done():
+        nonlocal stage
+        if on_stage_done is not None:
+            on_stage_done(G, stage)
+        stage += 1
+
+    def bias_grad(dy, bias_param, cout=None, also=None):
+        """bias gradient = column sums of dy over samples and pixels."""
+        cout = dy.shape[3] if cout is None else cout
+        tmp = torch.zeros(N, cout, device=dev, dtype=torch.float32)
+        ops.colsum(dy, tmp, 0, cout)
+        ops.reduce_rows(tmp, G.g(bias_param))
+        if also is not None:
+            ops.reduce_rows(tmp, G.g(also))
+
+    # ---- head: GroupNorm -> SiLU -> conv3x3 (Cout padded to 64 for the tensor-core tiles)
+    hd = tape["head"]
+    gn, conv_out = m.out[0], m.out[2]
+    dyp = ops.nchw_to_pixel_major(dout.contiguous(), 64)
+    ops.conv2d_wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
+    bias_grad(dyp, conv_out.bias, 64)
+    d_hh = ops.conv2d(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1)
+    dh, _ = ops.groupnorm_bwd(hd["h"], gn.weight.detach(), gn.bias.detach(), d_hh, hd["mean"], hd["rstd"],
+                              G.g(gn.weight), G.g(gn.bias), act=True, eps=gn.eps)
+    done()
+
+    def res_bwd(ctx, dout_, extra):
+        rb, t = ctx.mod, ctx.t
+        gn1, conv1 = rb.in_layers[0], rb.in_layers[2]
+        gn2, conv2 = rb.out_layers[0], rb.out_layers[3]
+        cout = rb.out_channels
+        x, x2 = t["x"], t["x2"]
+        has_skip_conv = not isinstance(rb.skip_connection, torch.nn.Identity)
+        # conv2 (out_layers[3]) and the skip path share dout_
+        ops.conv2d_wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
+        bias_grad(dout_, conv2.bias, also=rb.skip_connection.bias if has_skip_conv else None)
+        d_h3 = ops.conv2d(dout_, eng.w_dgrad(conv2), cout, 3, 1)
+        d_h2, _ = ops.groupnorm_bwd(t["h2"], gn2.weight.detach(), gn2.bias.detach(), d_h3, t["mean2"], t["rstd2"],
+                                    G.g(gn2.weight), G.g(gn2.bias), act=True, eps=gn2.eps, drop_p=t["drop_p"],
+                                    seed=t["seed"])
+        off = eng.emb_off[id(rb)]
+        ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)      # d emb_out (unet.py:266) and conv1 bias
+        ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
+        ops.conv2d_wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
+        cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
+        d_h1 = ops.conv2d(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1)
+        if has_skip_conv:
+            sc = rb.skip_connection
+            ops.conv2d_wgrad(x, dout_, G.g(sc.weight), 1, 1, x2=x2)
+            add_a = ops.conv2d(dout_, eng.w_dgrad(sc), cin_tot, 1, 1)
+            full = True
+        else:
+            add_a, full = dout_, False
+        dx1, dx2 = ops.groupnorm_bwd(x, gn1.weight.detach(), gn1.bias.detach(), d_h1, t["mean1"], t["rstd1"],
+                                     G.g(gn1.weight), G.g(gn1.bias), x2=x2, act=True, eps=gn1.eps,
+                                     add_a=add_a, add_b=extra, add_a_full=full)
+        return dx1, dx2
+
+    def attn_bwd(ctx, dout_, extra):
+        ab, t = ctx.mod, ctx.t
+        C_ = ab.channels
+        gn_ = ab.norm
+        ops.conv2d_wgrad(t["a"], dout_, G.g(ab.proj_out.weight), 1, 1)
+        bias_grad(dout_, ab.proj_out.bias)
+        d_a = ops.conv2d(dout_, eng.w_dgrad(ab.proj_out), C_, 1, 1)
+        dqkv = ops.attention_bwd(t["qkv"], t["a"], d_a, t["lse"], ab.num_heads, ab.use_new_attention_order)
+        ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
+        bias_grad(dqkv, ab.qkv.bias)
+        d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1)
+        dx, _ = ops.groupnorm_bwd(t["x"], gn_.weight.detach(), gn_.bias.detach(), d_hn, t["mean"], t["rstd"],
+                                  G.g(gn_.weight), G.g(gn_.bias), act=False, eps=gn_.eps, add_a=dout_, add_b=extra)
+        return dx
+
+    def down_bwd(ctx, dout_, extra):
+        layer, x = ctx.mod, ctx.t["x"]
+        ops.conv2d_wgrad(x, dout_, G.g(layer.op.weight), 3, 2)
+        bias_grad(dout_, layer.op.bias)
+        z = ops.zero_insert2x(dout_)
+        return ops.conv2d(z, eng.w_dgrad(layer.op), layer.channels, 3, 1, residual=extra)
+
+    def up_bwd(ctx, dout_):
+        layer, u = ctx.mod, ctx.t["u"]
+        ops.conv2d_wgrad(u, dout_, G.g(layer.conv.weight), 3, 1)
+        bias_grad(dout_, layer.conv.bias)
+        du = ops.conv2d(dout_, eng.w_dgrad(layer.conv), layer.channels, 3, 1)
+        return ops.upsample2x_bwd(du)
+
+    def layer_bwd(ctx, dout_, extra):
+        if ctx.kind == "res":
+            return res_bwd(ctx, dout_, extra)
+        if ctx.kind == "attn":
+            return attn_bwd(ctx, dout_, extra), None
+        if ctx.kind == "down":
+            return down_bwd(ctx, dout_, extra), None
+        assert extra is None
+        return up_bwd(ctx, dout_), None
+
+    # ---- decoder (reverse): collects the skip gradients for hs[0..]
+    skip_grads = []
+    for ctxs in reversed(tape["dec"]):
+        for li in range(len(ctxs) - 1, -1, -1):
+            dh, dskip = layer_bwd(ctxs[li], dh, None)
+            if li == 0:
+                skip_grads.append(dskip)
+            done()
+    # ---- middle: its first layer receives the last encoder output, which also fed the decoder
+    n_enc = len(tape["enc"])
+    mid = tape["mid"]
+    for li in range(len(mid) - 1, -1, -1):
+        dh, _ = layer_bwd(mid[li], dh, skip_grads[n_enc] if li == 0 else None)
+        done()
+    # ---- encoder (reverse): block i consumed hs[i] (output of block i-1 / conv_in)
+    for bi in range(n_enc - 1, -1, -1):
+        ctxs = tape["enc"][bi]
+        for li in range(len(ctxs) - 1, -1, -1):
+            dh, _ = layer_bwd(ctxs[li], dh, skip_grads[bi] if li == 0 else None)
+            done()
+    # ---- input convolution
+    conv_in = m.input_blocks[0][0]
+    x0 = tape["x0"]
+    ops.conv2d_wgrad(x0, dh, G.g(conv_in.weight), 3, 1)
+    bias_grad(dh, conv_in.bias)
+    d_feat = None
+    if eng.is_audio:
+        dx0 = ops.conv2d(dh, eng.w_dgrad(conv_in, cin_pad=eng.cin_pad), eng.cin_pad, 3, 1)
+    done()
+    # ---- conditioning vectors
+    wcat, _ = eng.emb_cat()
+    first_w, first_b = eng.resblocks[0].emb_layers[1].weight, eng.resblocks[0].emb_layers[1].bias
+    ted = wcat.shape[1]
+    off_w, _ = G.offsets[id(first_w)]
+    dwcat = G.flat[off_w:off_w + eng.emb_total * ted].view(eng.emb_total, ted)
+    off_b, _ = G.offsets[id(first_b)]
+    dbcat = G.flat[off_b:off_b + eng.emb_total]
+    l0, l2 = m.time_embed[0], m.time_embed[2]
+    d_emb = ops.linear_bwd(tape["emb"], wcat, None, d_emb_all, dwcat, dbcat, silu_in=True)
+    d_e1 = ops.linear_bwd(tape["e1"], l2.weight.detach(), None, d_emb, G.g(l2.weight), G.g(l2.bias), silu_in=True)
+    ops.linear_bwd(tape["te"], l0.weight.detach(), None, d_e1, G.g(l0.weight), G.g(l0.bias), need_dx=False)
+    if eng.is_audio:
+        at = m.audio_transformer.transform[0]
+        A = at.weight.shape[0]
+        d_avec = torch.zeros(N, A, device=dev, dtype=torch.float32)
+        cim = m.cond_conv_in.weight.shape[0] if m.image_cond else 0
+        ops.assemble_input_bwd(dx0, tape["cond"].contiguous() if m.image_cond else None, m.in_channels - A - cim, cim, A,
+                               G.g(m.cond_conv_in.weight) if m.image_cond else None, d_avec)
+        feat = tape["audio_feat"].contiguous()
+        d_feat = ops.linear_bwd(feat, at.weight.detach(), tape["avec"], d_avec, G.g(at.weight), G.g(at.bias),
+                                relu_out=True)
+    done()
+    return G, d_feat
+
+
+class _DenoiserFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, model, xt, cond, audio_feat, timesteps, *params):
+        eng = model.engine()
+        out, tape = eng.forward(xt, cond, audio_feat, timesteps, train=True)
+        ctx.model, ctx.tape = model, tape
+        ctx.has_audio = audio_feat is not None
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        model, tape = ctx.model, ctx.tape
+        if tape is None:
+            raise RuntimeError("denoiser backward called on a graph built without gradients")
+        eng = model.engine()
+        hook = getattr(model, "_grad_stage_hook", None)
+        G, d_feat = _engine_backward(eng, tape, dout, hook)
+        ctx.tape = None
+        fin = getattr(model, "_grad_final_hook", None)
+        if fin is not None:
+            fin(G)
+        grads = tuple(G.unpacked(p) if p.requires_grad else None for p in eng.torso_params())
+        return (None, None, None, d_feat if ctx.has_audio else None, None) + grads
+
+
+def denoiser_apply(model, xt, cond, audio_feat, timesteps):
+    if not xt.is_cuda:
+        raise RuntimeError("the denoiser runs on sm_100a CUDA kernels only (no CPU fallback): move the model "
+                           "and inputs to a B200 device")
+    eng = model.engine()
+    params = eng.torso_params()
+    if torch.is_grad_enabled() and (any(p.requires_grad for p in params) or
+                                    (audio_feat is not None and audio_feat.requires_grad)):
+        return _DenoiserFn.apply(model, xt.float(), cond, audio_feat, timesteps, *params)
+    out, _ = eng.forward(xt.float(), cond, audio_feat, timesteps, train=False)
+    return out

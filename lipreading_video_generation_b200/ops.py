@@ -1,0 +1,269 @@
+"""Thin tensor-level wrappers over the C ABI (include/b2d.h).
+
+Every function enqueues sm_100a kernels on torch's current CUDA stream through
+ctypes; torch only owns the memory.  Activations are pixel-major bf16 tensors
+(N, H, W, C) -- see DESIGN.md "data layout".  No function here has a CPU path.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib as L
+
+BF16 = torch.bfloat16
+
+
+def _s():
+    return L.stream_ptr()
+
+
+def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: int = 16) -> torch.Tensor:
+    """OIHW (or OI / OIK for Linear / Conv1d) fp32 -> bf16 [CoutPad][kh*kw*CinPad] (tap-major, channel-minor)."""
+    if w.dim() == 2:
+        w = w[:, :, None, None]
+    elif w.dim() == 3:
+        w = w[:, :, :, None]
+    co, ci, kh, kw = w.shape
+    cip = ci if cin_pad is None else cin_pad
+    cop = (co + cout_pad_to - 1) // cout_pad_to * cout_pad_to
+    p = torch.zeros(cop, kh * kw, cip, device=w.device, dtype=BF16)
+    p[:co, :, :ci] = w.permute(0, 2, 3, 1).reshape(co, kh * kw, ci).to(BF16)
+    return p.reshape(cop, kh * kw * cip)
+
+
+def pack_dgrad_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad: int | None = None) -> torch.Tensor:
+    """Weights of the data-gradient convolution: dX = conv(dY, flip(w)^T).
+    OIHW -> bf16 [CinPad][kh*kw*CoutPad] with the taps spatially flipped."""
+    if w.dim() == 2:
+        w = w[:, :, None, None]
+    elif w.dim() == 3:
+        w = w[:, :, :, None]
+    co, ci, kh, kw = w.shape
+    cip = ci if cin_pad is None else cin_pad
+    cop = co if cout_pad is None else cout_pad
+    wf = torch.flip(w, dims=(2, 3)).permute(1, 2, 3, 0).reshape(ci, kh * kw, co)  # [ci][tap'][co]
+    p = torch.zeros((cip + 15) // 16 * 16, kh * kw, cop, device=w.device, dtype=BF16)
+    p[:ci, :, :co] = wf.to(BF16)
+    return p.reshape(p.shape[0], kh * kw * cop)
+
+
+def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, residual=None, out=None,
+           out_nchw_f32=None, c1=None, c2=None):
+    """x: (N,H,W,ldx) bf16, optional x2 concatenated on channels.  Returns (N,Ho,Wo,cout) bf16 (or `out`)."""
+    L.require_cuda(x)
+    N, H, W, ldx = x.shape
+    a = L.ConvArgs()
+    a.x, a.ldx, a.C1 = x.data_ptr(), x.stride(2), (ldx if c1 is None else c1)
+    if x2 is not None:
+        a.x2, a.ldx2, a.C2 = x2.data_ptr(), x2.stride(2), (x2.shape[3] if c2 is None else c2)
+    else:
+        a.x2, a.ldx2, a.C2 = None, 0, 0
+    a.N, a.H, a.W, a.ksize, a.stride = N, H, W, ksize, stride
+    a.w, a.Cout, a.CoutPad = w_packed.data_ptr(), cout, w_packed.shape[0]
+    a.bias, a.emb, a.ldemb = L.ptr(bias), L.ptr(emb), (emb.stride(0) if emb is not None else 0)
+    a.residual, a.ldres = L.ptr(residual), (residual.stride(2) if residual is not None else 0)
+    Ho, Wo = H // stride, W // stride
+    if out is None and out_nchw_f32 is None:
+        out = torch.empty(N, Ho, Wo, cout, device=x.device, dtype=BF16)
+    a.out, a.ldo = L.ptr(out), (out.stride(2) if out is not None else 0)
+    a.out_nchw_f32 = L.ptr(out_nchw_f32)
+    L.check(L.lib().b2d_conv2d(C.byref(a), _s()), "b2d_conv2d")
+    return out if out is not None else out_nchw_f32
+
+
+def conv2d_wgrad(x, dy, dw, ksize=1, stride=1, x2=None, c1=None, c2=None, cout=None):
+    """Accumulate dw (fp32 [Cout][taps*(C1+C2)]) from x (+x2) and dy (N,Ho,Wo,Cout) bf16."""
+    N, H, W, ldx = x.shape
+    a = L.WgradArgs()
+    a.x, a.ldx, a.C1 = x.data_ptr(), x.stride(2), (ldx if c1 is None else c1)
+    if x2 is not None:
+        a.x2, a.ldx2, a.C2 = x2.data_ptr(), x2.stride(2), (x2.shape[3] if c2 is None else c2)
+    else:
+        a.x2, a.ldx2, a.C2 = None, 0, 0
+    a.N, a.H, a.W, a.ksize, a.stride = N, H, W, ksize, stride
+    cout = dy.shape[3] if cout is None else cout
+    ktot = ksize * ksize * (a.C1 + a.C2)
+    co0 = 0
+    while co0 < cout:  # kernel handles Cout == 64 or a multiple of 128 per launch
+        rem = cout - co0
+        chunk = rem - rem % 128 if rem >= 128 else 64
+        a.dy, a.lddy, a.Cout = dy.data_ptr() + 2 * co0, dy.stride(2), chunk
+        a.dw = dw.data_ptr() + 4 * co0 * ktot
+        L.check(L.lib().b2d_conv2d_wgrad(C.byref(a), _s()), "b2d_conv2d_wgrad")
+        co0 += chunk
+    return dw
+
+
+_gn_ws: dict = {}
+
+
+def _gn_workspace(dev, N, Ct):
+    nbytes = L.lib().b2d_groupnorm_workspace_bytes(N, Ct)
+    key = (dev, torch.cuda.current_stream().cuda_stream)
+    ws = _gn_ws.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(max(nbytes, 1 << 20), device=dev, dtype=torch.uint8)
+        _gn_ws[key] = ws
+    return ws
+
+
+def _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed):
+    N = x1.shape[0]
+    HW = x1.shape[1] * x1.shape[2]
+    a = L.GnArgs()
+    a.x1, a.ld1, a.C1 = x1.data_ptr(), x1.stride(2), x1.shape[3]
+    if x2 is not None:
+        a.x2, a.ld2, a.C2 = x2.data_ptr(), x2.stride(2), x2.shape[3]
+    else:
+        a.x2, a.ld2, a.C2 = None, 0, 0
+    a.N, a.HW = N, HW
+    a.gamma, a.beta, a.eps, a.act, a.drop_p, a.seed = gamma.data_ptr(), beta.data_ptr(), eps, int(act), drop_p, seed
+    return a
+
+
+def groupnorm_fwd(x1, gamma, beta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed=0):
+    """Returns (y bf16 (N,H,W,C1+C2), mean (N,32), rstd (N,32))."""
+    L.require_cuda(x1)
+    N, H, W, C1 = x1.shape
+    Ct = C1 + (x2.shape[3] if x2 is not None else 0)
+    a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed)
+    y = torch.empty(N, H, W, Ct, device=x1.device, dtype=BF16)
+    mean = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
+    rstd = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
+    ws = _gn_workspace(x1.device, N, Ct)
+    L.check(L.lib().b2d_groupnorm_fwd(C.byref(a), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), ws.data_ptr(),
+                                      ws.numel(), _s()), "b2d_groupnorm_fwd")
+    return y, mean, rstd
+
+
+def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed=0,
+                  add_a=None, add_b=None, add_a_full=False):
+    """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (bf16, any channel pitch) are added to dx1."""
+    N, H, W, C1 = x1.shape
+    Ct = C1 + (x2.shape[3] if x2 is not None else 0)
+    a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed)
+    dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=BF16)
+    dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=BF16) if x2 is not None else None
+    ws = _gn_workspace(x1.device, N, Ct)
+    L.check(L.lib().b2d_groupnorm_bwd(
+        C.byref(a), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx1.data_ptr(), C1,
+        L.ptr(dx2), (dx2.shape[3] if dx2 is not None else 0),
+        L.ptr(add_a), (add_a.stride(2) if add_a is not None else 0),
+        L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
+        dgamma.data_ptr(), dbeta.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "b2d_groupnorm_bwd")
+    return dx1, dx2
+
+
+def attention_fwd(qkv, heads, new_order=False):
+    """qkv (N,H,W,3C) bf16 -> (out (N,H,W,C) bf16, lse (N,heads,L) fp32)."""
+    N, H, W, C3 = qkv.shape
+    Cc = C3 // 3
+    ch = Cc // heads
+    out = torch.empty(N, H, W, Cc, device=qkv.device, dtype=BF16)
+    lse = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
+    L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
+                                      out.data_ptr(), Cc, lse.data_ptr(), _s()), "b2d_attention_fwd")
+    return out, lse
+
+
+def attention_bwd(qkv, out, d_out, lse, heads, new_order=False):
+    N, H, W, C3 = qkv.shape
+    Cc = C3 // 3
+    ch = Cc // heads
+    dqkv = torch.empty(N, H, W, C3, device=qkv.device, dtype=BF16)
+    delta = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
+    L.check(L.lib().b2d_attention_bwd(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2), d_out.data_ptr(),
+                                      d_out.stride(2), lse.data_ptr(), N, H * W, heads, ch, int(new_order),
+                                      dqkv.data_ptr(), C3, delta.data_ptr(), _s()), "b2d_attention_bwd")
+    return dqkv
+
+
+def assemble_input(xt, cond, wcond, audio, cpad):
+    N, Cin, S, _ = xt.shape
+    Cim = wcond.shape[0] if wcond is not None else 0
+    Cc = cond.shape[1] if cond is not None else 0
+    Hc, Wc = (cond.shape[2], cond.shape[3]) if cond is not None else (0, 0)
+    A = audio.shape[1] if audio is not None else 0
+    out = torch.empty(N, S, S, cpad, device=xt.device, dtype=BF16)
+    L.check(L.lib().b2d_assemble_input(xt.data_ptr(), L.ptr(cond), L.ptr(wcond), L.ptr(audio), N, S, Cin, Cc, Hc, Wc,
+                                       Cim, A, cpad, out.data_ptr(), _s()), "b2d_assemble_input")
+    return out
+
+
+def assemble_input_bwd(dX, cond, cin, cim, A, d_wcond, d_audio):
+    N, S, _, cpad = dX.shape
+    Cc = cond.shape[1] if cond is not None else 0
+    Hc, Wc = (cond.shape[2], cond.shape[3]) if cond is not None else (0, 0)
+    L.check(L.lib().b2d_assemble_input_bwd(dX.data_ptr(), L.ptr(cond), N, S, cin, Cc, Hc, Wc, cim, A, cpad,
+                                           L.ptr(d_wcond), L.ptr(d_audio), _s()), "b2d_assemble_input_bwd")
+
+
+def upsample2x(x):
+    N, H, W, Cc = x.shape
+    y = torch.empty(N, 2 * H, 2 * W, Cc, device=x.device, dtype=BF16)
+    L.check(L.lib().b2d_upsample2x(x.data_ptr(), y.data_ptr(), N, H, W, Cc, _s()), "b2d_upsample2x")
+    return y
+
+
+def upsample2x_bwd(dy):
+    N, H2, W2, Cc = dy.shape
+    dx = torch.empty(N, H2 // 2, W2 // 2, Cc, device=dy.device, dtype=BF16)
+    L.check(L.lib().b2d_upsample2x_bwd(dy.data_ptr(), dx.data_ptr(), N, H2 // 2, W2 // 2, Cc, _s()), "b2d_upsample2x_bwd")
+    return dx
+
+
+def zero_insert2x(dy):
+    N, Ho, Wo, Cc = dy.shape
+    z = torch.empty(N, 2 * Ho, 2 * Wo, Cc, device=dy.device, dtype=BF16)
+    L.check(L.lib().b2d_zero_insert2x(dy.data_ptr(), z.data_ptr(), N, Ho, Wo, Cc, _s()), "b2d_zero_insert2x")
+    return z
+
+
+def nchw_to_pixel_major(src, cpad):
+    N, Cc, H, W = src.shape
+    dst = torch.empty(N, H, W, cpad, device=src.device, dtype=BF16)
+    L.check(L.lib().b2d_nchw_to_pixel_major(src.data_ptr(), dst.data_ptr(), N, Cc, H * W, cpad, _s()),
+            "b2d_nchw_to_pixel_major")
+    return dst
+
+
+def colsum(x, out, c_off=0, C_=None):
+    """out[n][c] += sum over pixels of x[n,:,:,c_off+c];  x (N,H,W,ld) bf16, out (N,C) fp32."""
+    N, H, W, ld = x.shape
+    C_ = out.shape[1] if C_ is None else C_
+    L.check(L.lib().b2d_colsum(x.data_ptr(), x.stride(2), c_off, C_, N, H * W, out.data_ptr(), out.stride(0), _s()), "b2d_colsum")
+    return out
+
+
+def reduce_rows(inp, out):
+    R, Cc = inp.shape
+    L.check(L.lib().b2d_reduce_rows(inp.data_ptr(), R, Cc, inp.stride(0), out.data_ptr(), _s()), "b2d_reduce_rows")
+    return out
+
+
+def timestep_embedding(t, dim, freqs):
+    N = t.shape[0]
+    out = torch.empty(N, dim, device=t.device, dtype=torch.float32)
+    L.check(L.lib().b2d_timestep_embedding(t.data_ptr(), N, dim, freqs.data_ptr(), out.data_ptr(), _s()),
+            "b2d_timestep_embedding")
+    return out
+
+
+def linear_fwd(x, w, bias, silu_in=False, relu_out=False):
+    M, K = x.shape
+    Nout = w.shape[0]
+    y = torch.empty(M, Nout, device=x.device, dtype=torch.float32)
+    L.check(L.lib().b2d_linear_fwd(x.data_ptr(), w.data_ptr(), L.ptr(bias), y.data_ptr(), M, K, Nout, int(silu_in),
+                                   int(relu_out), _s()), "b2d_linear_fwd")
+    return y
+
+
+def linear_bwd(x, w, y, dy, dw, db, need_dx=True, silu_in=False, relu_out=False):
+    M, K = x.shape
+    Nout = w.shape[0]
+    dx = torch.empty(M, K, device=x.device, dtype=torch.float32) if need_dx else None
+    L.check(L.lib().b2d_linear_bwd(x.data_ptr(), w.data_ptr(), L.ptr(y), dy.data_ptr(), L.ptr(dx), dw.data_ptr(),
+                                   L.ptr(db), M, K, Nout, int(silu_in), int(relu_out), _s()), "b2d_linear_bwd")
+    return dx

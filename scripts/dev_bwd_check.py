@@ -78,7 +78,7 @@ def gn(N, HW, C1, C2, act, with_add):
     dx1 = torch.empty_like(x1); dx2 = torch.empty_like(x2) if C2 else None
     dg = torch.zeros(Ct, device=dev); db = torch.zeros(Ct, device=dev)
     L.check(lib.b2d_groupnorm_bwd(C.byref(a), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx1.data_ptr(), C1,
-                                  L.ptr(dx2), C2, L.ptr(add_a), C1, None, 0, dg.data_ptr(), db.data_ptr(),
+                                  L.ptr(dx2), C2, L.ptr(add_a), C1, None, 0, 0, dg.data_ptr(), db.data_ptr(),
                                   ws.data_ptr(), wsb, L.stream_ptr()), "gn bwd")
     torch.cuda.synchronize()
     xin = (x1 if not C2 else torch.cat([x1, x2], -1)).float().requires_grad_(True)

@@ -34,7 +34,7 @@ def run_conv(N, H, W, C1, C2, Cout, k, stride, extras=True):
     a.x2, a.ldx2, a.C2 = (x2.data_ptr() if C2 else None), C2, C2
     a.N, a.H, a.W, a.ksize, a.stride = N, H, W, k, stride
     a.w, a.Cout, a.CoutPad = wp.data_ptr(), Cout, cop
-    a.bias = L.ptr(bias); a.emb = L.ptr(emb); a.residual = L.ptr(res); a.ldres = Cout
+    a.bias = L.ptr(bias); a.emb = L.ptr(emb); a.ldemb = Cout; a.residual = L.ptr(res); a.ldres = Cout
     a.out, a.ldo = out.data_ptr(), Cout
     a.out_nchw_f32 = None
     L.check(L.lib().b2d_conv2d(C.byref(a), L.stream_ptr()), "conv2d")
