@@ -243,3 +243,35 @@ def fill_params(named_tensors, seed=0):
         else:
             out[name] = 0.05 * v
     return out
+
+
+def is_zero_module_tensor(name: str) -> bool:
+    """Tensors the reference zero-initialises (zero_module at unet.py:222-224, :306, :627)."""
+    return (".out_layers.3." in name) or (".proj_out." in name) or name.startswith("out.2.")
+
+
+def protocol_params(named_tensors, seed=0):
+    """The initialisation BASELINE.md section 2 / SURVEY section 8(d) prescribe for parity and bench runs, generated
+    deterministically per tensor name (the reference's own RNG stream cannot be replayed on the GPU box):
+    PyTorch's default Conv/Linear init distribution U(-1/sqrt(fan_in), 1/sqrt(fan_in)) for weights and biases
+    (nn.Conv2d / nn.Linear reset_parameters), GroupNorm weight 1 / bias 0, and every zero_module'd tensor
+    re-initialised N(0, 0.02) ("un_zero") so that parity is not vacuous."""
+    g = torch.Generator().manual_seed(seed)
+    fan = {}
+    for name, t in named_tensors.items():
+        if t.dim() >= 2:
+            fan[name.rsplit(".", 1)[0]] = t[0].numel()
+    out = {}
+    for name in sorted(named_tensors):
+        t = named_tensors[name]
+        mod = name.rsplit(".", 1)[0]
+        if is_zero_module_tensor(name):
+            out[name] = torch.randn(t.shape, generator=g, dtype=torch.float32) * 0.02
+        elif mod in fan:
+            bound = 1.0 / math.sqrt(fan[mod])
+            out[name] = (torch.rand(t.shape, generator=g, dtype=torch.float32) * 2 - 1) * bound
+        elif name.endswith("weight"):
+            out[name] = torch.ones(t.shape, dtype=torch.float32)
+        else:
+            out[name] = torch.zeros(t.shape, dtype=torch.float32)
+    return out

@@ -10,11 +10,13 @@ class Stub(torch.nn.Module):
     def forward(self, audio): return audio["feats"]
 
 S = int(sys.argv[1]) if len(sys.argv) > 1 else 64
-N = 2
+N = int(sys.argv[2]) if len(sys.argv) > 2 else 2
+INIT = sys.argv[3] if len(sys.argv) > 3 else 'fill'
 cfg = dict(image_size=S, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=2,
            attention_resolutions=(1, 2, 4), dropout=0.0, audio_feature_dim=768, projected_audio_dim=128)
 model = P.UNetAudio(**cfg, audio_encoder=Stub())
-sd = R.fill_params(model.state_dict(), seed=3)
+sd = (R.protocol_params if INIT == 'protocol' else R.fill_params)(model.state_dict(), seed=3)
+print('config: S', S, 'N', N, 'init', INIT)
 model.load_state_dict(sd)
 model = model.cuda().train()
 g = torch.Generator().manual_seed(5)
