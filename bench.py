@@ -1,0 +1,297 @@
+"""bench.py -- denoiser train step throughput (clips/s), BASELINE.json configs[1]:
+single B200, batch 16 clips x 16 frames 64x64 (N = 256 images folded into the batch), bf16 train step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload train64|train128|sample128]
+
+One "step" = q_sample + UNetAudio forward (wav2vec2 + sm_100a torso) + MSE + backward + Adam step on one
+batch of synthetic clips (train.py:109-134).  Prints ONE JSON line (see DESIGN.md "measurement").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+os.environ.setdefault("B2D_WAV2VEC2_RANDOM_INIT", "1")   # no network: wav2vec2-base weights are random-init
+
+import torch  # noqa: E402
+
+WORKLOADS = {
+    # name: (clips per GPU, frames per clip, S, kind)
+    "train64": (16, 16, 64, "train"),      # BASELINE configs[1]
+    "train128": (16, 16, 128, "train"),    # BASELINE configs[2] per-GPU shape
+    "sample128": (8, 16, 128, "sample"),   # BASELINE configs[3] per-GPU shape
+}
+FWD_GFLOP_PER_IMAGE = {64: 43.87, 128: 470.21}     # SURVEY section 8(d), algorithmic, UNet torso
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d.get("bf16_tflops", 1590.0), d.get("bf16_tflops_sustained", 1400.0), d.get("hbm_gbs", 6650.0), "measured"
+    return 1590.0, 1400.0, 6650.0, "fallback"
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons during the timed region (B200_PROFILING.md clocks line)."""
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._th = index, [], threading.Event(), None
+
+    def _run(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        while not self._stop.is_set():
+            try:
+                o = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={q}", "--format=csv,noheader,nounits"],
+                                   capture_output=True, text=True, timeout=5).stdout.strip()
+                if o:
+                    self.rows.append([c.strip() for c in o.split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.2)
+
+    def __enter__(self):
+        self._th = threading.Thread(target=self._run, daemon=True)
+        self._th.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop.set()
+        self._th.join(timeout=6)
+
+    def summary(self):
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows for i in range(4) if len(r) > 2 + i and r[2 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(self.rows)}
+
+
+def make_batch(n_img, S, seed, device, pinned=False):
+    """SURVEY section 8(d) synthetic inputs: x0, reference image ~ U(-1,1); audio ~ N(0,1) (N,4000); one clip shares
+    its frame-0 reference image across its frames."""
+    g = torch.Generator().manual_seed(seed)
+    x0 = torch.rand(n_img, 3, S, S, generator=g) * 2 - 1
+    cond = torch.rand(n_img, 3, S, S, generator=g) * 2 - 1
+    audio = torch.randn(n_img, 4000, generator=g)
+    if pinned:
+        return x0.pin_memory(), cond.pin_memory(), audio.pin_memory()
+    return x0.to(device), cond.to(device), audio.to(device)
+
+
+def build_model(S, device, seed=0):
+    import lipreading_video_generation_b200 as P
+    torch.manual_seed(seed)
+    model = P.UNetAudio(image_size=S, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=2,
+                        attention_resolutions=(1, 2, 4), audio_feature_dim=768, projected_audio_dim=128)   # train.py:88-97
+    # un_zero: zero_module'd tensors get N(0, 0.02) so that no layer's work is skipped by zeros
+    g = torch.Generator().manual_seed(seed + 1)
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if (".out_layers.3." in name) or (".proj_out." in name) or name.startswith("out.2."):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+    return model.to(device)
+
+
+class TrainStep:
+    """train.py:109-134 on the product: zero_grad, q_sample, model, MSE, backward, (grad all-reduce), Adam."""
+
+    def __init__(self, model, S, world, device):
+        import lipreading_video_generation_b200 as P
+        from lipreading_video_generation_b200.parallel import GradientAllReducer
+        self.P, self.model, self.device, self.world = P, model, device, world
+        self.sched = P.LinearNoiseScheduler(1000, 0.00085, 0.012)
+        self.crit = P.MSELoss()
+        self.opt = torch.optim.Adam(model.parameters(), lr=1e-2, fused=True)          # train.py:102
+        self.reducer = GradientAllReducer(model) if world > 1 else None
+        model.train()
+
+    def __call__(self, x0, cond, audio, t):
+        self.opt.zero_grad(set_to_none=True)
+        noise = torch.randn_like(x0)                                                  # train.py:122
+        xt = self.sched.add_noise(x0, noise, t)
+        with torch.autocast("cuda", dtype=torch.bfloat16):                           # HF wav2vec2 only; torso is ours
+            feats = self.model.encode_audio({"input_values": audio})
+        pred = self.model(xt, cond, None, t, audio_features=feats.float())
+        loss = self.crit(pred, noise)
+        loss.backward()
+        if self.reducer is not None:
+            self.reducer.finish()
+        self.opt.step()
+        return loss
+
+
+def cpu_baseline(S, threads, seconds_budget=25.0):
+    """The oracle port (CPU restatement of the reference, fp32) timed on the host: fwd + bwd of the torso on a
+    bounded sample of the same workload (images of the same shape, as many as fit the time budget)."""
+    from oracle import restatement as R
+    import lipreading_video_generation_b200 as P
+    torch.set_num_threads(threads)
+
+    class Stub(torch.nn.Module):
+        def forward(self, a):
+            return a["feats"]
+    m = P.UNetAudio(image_size=S, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=2,
+                    attention_resolutions=(1, 2, 4), dropout=0.0, audio_feature_dim=768, projected_audio_dim=128,
+                    audio_encoder=Stub())
+    sd = R.protocol_params(m.state_dict(), seed=0)
+    cfg = dict(image_size=S, model_channels=64, num_res_blocks=2, attention_resolutions=(1, 2, 4), channel_mult=(1, 2, 4), num_heads=1)
+    n = 2
+    g = torch.Generator().manual_seed(0)
+    xt = torch.randn(n, 3, S, S, generator=g); cond = torch.rand(n, 3, S, S, generator=g)
+    fm = torch.randn(n, 768, generator=g); eps = torch.randn(n, 3, S, S, generator=g); t = torch.randint(0, 1000, (n,), generator=g)
+
+    def one():
+        sdr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        loss = R.mse(R.unet_audio_forward(sdr, cfg, xt, cond, fm, t), eps)
+        loss.backward()
+    one()                                   # warm-up
+    times = []
+    t_end = time.time() + seconds_budget
+    while len(times) < 5 and time.time() < t_end:
+        t0 = time.time(); one(); times.append(time.time() - t0)
+    med = sorted(times)[len(times) // 2]
+    return n, med, len(times)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200")
+    ap.add_argument("--workload", default="train64", choices=list(WORKLOADS))
+    a = ap.parse_args()
+    clips, frames, S, kind = WORKLOADS[a.workload]
+    rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    cores = os.cpu_count() or 1
+    config = {"workload": f"{a.workload}: denoiser {kind} step, {clips} clips x {frames} frames {S}x{S} per GPU "
+                          f"(N={clips * frames} images folded into the batch), UNetAudio train.py config + wav2vec2-base",
+              "clips_per_gpu": clips, "frames": frames, "image": S, "parallelism": f"dp{world}",
+              "l2_policy": "inputs+activations >> L2 (126 MB): >10 GB touched per step"}
+
+    if a.impl == "reference":
+        # The reference is PyTorch-CPU here (/root/reference does not travel): its oracle port, all host threads.
+        if rank != 0:
+            return
+        vals = []
+        for _ in range(max(1, min(a.steps, 3))):
+            n, sec, reps = cpu_baseline(S, cores, seconds_budget=40.0)
+            vals.append((n / frames) / sec)
+        v = sorted(vals)[len(vals) // 2]
+        print(json.dumps({"impl": "reference", "metric": "denoiser_train_clips_per_s", "value": v, "unit": "clips/s",
+                          "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1000.0 * (2 / frames) / v,
+                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+                          "data": "synthetic", "config": config,
+                          "cpu_baseline": {"value": v, "unit": "clips/s", "cores": cores, "kind": "port",
+                                           "sample": f"2 images {S}x{S} (1/{frames // 2 if frames >= 2 else 1} clip): torso fwd+bwd fp32, no wav2vec2/Adam"},
+                          "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        return
+
+    assert torch.cuda.is_available(), "bench.py needs a B200; there is no CPU fallback for the product path"
+    torch.cuda.set_device(local)
+    device = torch.device("cuda", local)
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=device)
+    from lipreading_video_generation_b200 import _lib as L, ops
+    from lipreading_video_generation_b200.parallel import broadcast_parameters
+    L.check(L.lib().b2d_check_device(), "b2d_check_device")
+    n_img = clips * frames
+    model = build_model(S, device)
+    if world > 1:
+        broadcast_parameters(model)
+    step = TrainStep(model, S, world, device)
+    x0, cond, audio = make_batch(n_img, S, 1234 + rank, device)
+    hx0, hcond, haudio = make_batch(n_img, S, 1234 + rank, device, pinned=True)
+    gt = torch.Generator().manual_seed(99 + rank)
+    t_dev = torch.randint(0, 1000, (n_img,), generator=gt).to(device)
+    t_host = torch.randint(0, 1000, (n_img,), generator=gt).pin_memory()
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        step(x0, cond, audio, t_dev)
+    # ---------------- timed region 1: inputs resident in HBM ("value") + roofline events on attention kernels
+    barrier()
+    l0 = L.lib().b2d_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
+        e0.record()
+        for _ in range(a.steps):
+            step(x0, cond, audio, t_dev)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1) / a.steps
+    launches = (L.lib().b2d_launch_count() - l0) // a.steps
+    # ---------------- timed region 2: end to end through the public API with HOST buffers
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(a.steps):
+        dx0 = hx0.to(device, non_blocking=True); dc = hcond.to(device, non_blocking=True)
+        da = haudio.to(device, non_blocking=True); dt = t_host.to(device, non_blocking=True)
+        loss = step(dx0, dc, da, dt)
+        loss_host = loss.item()                    # device -> host read of the step's result
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1) / a.steps
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=device)
+        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+        ms, ms_e2e = tt.tolist()
+    if rank != 0:
+        if world > 1:
+            torch.distributed.destroy_process_group()
+        return
+    burst, sustained, hbm, which = peaks()
+    # roofline of the dominant kernel class: full-resolution (ch = 64) attention, forward
+    tot = kt.totals()
+    dom = None
+    for (name, meta), (t_ms, cnt) in tot.items():
+        Nn, Lq, heads, ch = meta
+        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lq * ch * heads * Nn
+        rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, launches_per_step=cnt // a.steps,
+                   tflops=flops / (t_ms / cnt) / 1e9, ms_per_step=t_ms / a.steps)
+        if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
+            dom = rec
+    roof = {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
+            "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
+            "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
+            "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N fwd, 10*L^2*ch*N bwd"}
+    n_cpu, sec_cpu, reps = cpu_baseline(S, cores)
+    cpu_v = (n_cpu / frames) / sec_cpu
+    value = clips * world / (ms / 1000.0)
+    train_tflop = 3 * FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
+    h2d = sum(t.numel() * t.element_size() for t in (hx0, hcond, haudio, t_host))
+    out = {"metric": "denoiser_train_clips_per_s", "value": round(value, 3), "unit": "clips/s", "n_gpus": world,
+           "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+           "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 3), "unit": "clips/s", "h2d_bytes_per_step": h2d,
+                   "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
+           "gpu_launches": int(launches), "roofline": roof,
+           "step_tflops_algorithmic": round(train_tflop / (ms / 1000.0), 1),
+           "step_frac_of_sustained_peak": round(train_tflop / (ms / 1000.0) / sustained, 4),
+           "cpu_baseline": {"value": round(cpu_v, 5), "unit": "clips/s", "cores": cores, "kind": "port",
+                            "sample": f"{n_cpu} images {S}x{S}: oracle torso fwd+bwd fp32, median of {reps}, {sec_cpu:.2f} s"},
+           "clocks": clk.summary(), "last_loss": loss_host}
+    print(json.dumps(out))
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

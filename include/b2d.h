@@ -35,6 +35,8 @@ int b2d_version(void);
 const char* b2d_last_error(void);
 /* 0 when the current device is sm_100-class, B2D_ERR_ARCH otherwise. */
 int b2d_check_device(void);
+/* Number of kernels this library has launched in this process (bench.py's gpu_launches). */
+long long b2d_launch_count(void);
 
 /* ------------------------------------------------------------------------
  * Diffusion math (elementwise, HBM bound, fp32).

@@ -58,6 +58,7 @@ SIGNATURES = {
     "b2d_version": (c_int, []),
     "b2d_last_error": (C.c_char_p, []),
     "b2d_check_device": (c_int, []),
+    "b2d_launch_count": (C.c_longlong, []),
     "b2d_q_sample": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_void_p, c_int64, c_int64,
                              c_void_p, c_void_p]),
     "b2d_ddpm_step": (c_int, [c_void_p, c_void_p, c_void_p, c_float, c_float, c_float, c_float, c_float, c_int,

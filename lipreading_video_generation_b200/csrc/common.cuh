@@ -23,6 +23,7 @@ int set_err(int code, const char* fmt, ...);
 
 #define B2D_CHECK_LAUNCH()                                                     \
   do {                                                                         \
+    b2d::count_launch();                                                       \
     cudaError_t _e = cudaGetLastError();                                       \
     if (_e != cudaSuccess)                                                     \
       return b2d::set_err(B2D_ERR_CUDA, "kernel launch failed: %s (%s:%d)",    \
@@ -37,6 +38,7 @@ int set_err(int code, const char* fmt, ...);
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 int num_sms();  // cached SM count of the current device (148 on B200)
+void count_launch();  // bumps the counter returned by b2d_launch_count()
 
 // ---------------------------------------------------------------------------
 // device helpers

@@ -1,5 +1,6 @@
 // runtime.cu -- error reporting, device checks, version.
 #include "common.cuh"
+#include <atomic>
 #include <mutex>
 
 namespace b2d {
@@ -31,7 +32,11 @@ int num_sms() {
 
 }  // namespace b2d
 
+static std::atomic<long long> g_launches{0};
+namespace b2d { void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); } }
+
 extern "C" int b2d_version(void) { return 100; }  // 0.1.0
+extern "C" long long b2d_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 extern "C" const char* b2d_last_error(void) { return b2d::err_buf(); }
 

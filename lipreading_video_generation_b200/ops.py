@@ -19,6 +19,49 @@ def _s():
     return L.stream_ptr()
 
 
+class KernelTimer:
+    """Optional CUDA-event timing of selected ABI calls on the launching stream (bench.py's roofline leg).
+    `classes` is a set of names ("attention_fwd", "attention_bwd", "conv2d", "conv2d_wgrad");
+    records (name, meta, start_event, end_event)."""
+    active = None
+
+    def __init__(self, classes):
+        self.classes, self.records = set(classes), []
+
+    def __enter__(self):
+        KernelTimer.active = self
+        return self
+
+    def __exit__(self, *a):
+        KernelTimer.active = None
+
+    def totals(self):
+        out = {}
+        for name, meta, e0, e1 in self.records:
+            d = out.setdefault((name, meta), [0.0, 0])
+            d[0] += e0.elapsed_time(e1)
+            d[1] += 1
+        return out
+
+
+class _timed:
+    def __init__(self, name, meta=None):
+        t = KernelTimer.active
+        self.on = t is not None and name in t.classes
+        self.name, self.meta = name, meta
+
+    def __enter__(self):
+        if self.on:
+            self.e0 = torch.cuda.Event(enable_timing=True)
+            self.e0.record()
+
+    def __exit__(self, *a):
+        if self.on:
+            e1 = torch.cuda.Event(enable_timing=True)
+            e1.record()
+            KernelTimer.active.records.append((self.name, self.meta, self.e0, e1))
+
+
 def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: int = 16) -> torch.Tensor:
     """OIHW (or OI / OIK for Linear / Conv1d) fp32 -> bf16 [CoutPad][kh*kw*CinPad] (tap-major, channel-minor)."""
     if w.dim() == 2:
@@ -69,7 +112,8 @@ def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, r
         out = torch.empty(N, Ho, Wo, cout, device=x.device, dtype=BF16)
     a.out, a.ldo = L.ptr(out), (out.stride(2) if out is not None else 0)
     a.out_nchw_f32 = L.ptr(out_nchw_f32)
-    L.check(L.lib().b2d_conv2d(C.byref(a), _s()), "b2d_conv2d")
+    with _timed("conv2d", (N, H, W, a.C1 + a.C2, cout, ksize, stride)):
+        L.check(L.lib().b2d_conv2d(C.byref(a), _s()), "b2d_conv2d")
     return out if out is not None else out_nchw_f32
 
 
@@ -91,7 +135,8 @@ def conv2d_wgrad(x, dy, dw, ksize=1, stride=1, x2=None, c1=None, c2=None, cout=N
         chunk = rem - rem % 128 if rem >= 128 else 64
         a.dy, a.lddy, a.Cout = dy.data_ptr() + 2 * co0, dy.stride(2), chunk
         a.dw = dw.data_ptr() + 4 * co0 * ktot
-        L.check(L.lib().b2d_conv2d_wgrad(C.byref(a), _s()), "b2d_conv2d_wgrad")
+        with _timed("conv2d_wgrad", (N, H, W, a.C1 + a.C2, chunk, ksize, stride)):
+            L.check(L.lib().b2d_conv2d_wgrad(C.byref(a), _s()), "b2d_conv2d_wgrad")
         co0 += chunk
     return dw
 
@@ -163,8 +208,9 @@ def attention_fwd(qkv, heads, new_order=False):
     ch = Cc // heads
     out = torch.empty(N, H, W, Cc, device=qkv.device, dtype=BF16)
     lse = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
-    L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
-                                      out.data_ptr(), Cc, lse.data_ptr(), _s()), "b2d_attention_fwd")
+    with _timed("attention_fwd", (N, H * W, heads, ch)):
+        L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
+                                          out.data_ptr(), Cc, lse.data_ptr(), _s()), "b2d_attention_fwd")
     return out, lse
 
 
@@ -174,9 +220,11 @@ def attention_bwd(qkv, out, d_out, lse, heads, new_order=False):
     ch = Cc // heads
     dqkv = torch.empty(N, H, W, C3, device=qkv.device, dtype=BF16)
     delta = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
-    L.check(L.lib().b2d_attention_bwd(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2), d_out.data_ptr(),
-                                      d_out.stride(2), lse.data_ptr(), N, H * W, heads, ch, int(new_order),
-                                      dqkv.data_ptr(), C3, delta.data_ptr(), _s()), "b2d_attention_bwd")
+    with _timed("attention_bwd", (N, H * W, heads, ch)):
+        L.check(L.lib().b2d_attention_bwd(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2),
+                                          d_out.data_ptr(), d_out.stride(2), lse.data_ptr(), N, H * W, heads, ch,
+                                          int(new_order), dqkv.data_ptr(), C3, delta.data_ptr(), _s()),
+                "b2d_attention_bwd")
     return dqkv
 
 

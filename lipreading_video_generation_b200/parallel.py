@@ -1,0 +1,108 @@
+"""Data-parallel training across the GPUs of one box (north_star item 4; the reference has no distributed
+code at all -- SURVEY section 5 / 8e).  One process per GPU, torch.distributed for the plumbing, NCCL all-reduce
+of gradient buckets on a side stream, launched as soon as each backward stage has finished writing its slice
+of the engine's flat gradient buffer, so that the transfer overlaps the remaining backward kernels.
+
+The unit of sharding is the clip (frames folded into the batch): no data-path collective, one gradient
+exchange per step; sampling needs no exchange at all (replicas only).
+"""
+from __future__ import annotations
+
+import torch
+import torch.distributed as dist
+
+
+def shard_range(n_items: int, rank: int, world: int):
+    """Contiguous [lo, hi) slice of n_items owned by `rank` (remainder spread over the first ranks)."""
+    base, rem = divmod(n_items, world)
+    lo = rank * base + min(rank, rem)
+    return lo, lo + base + (1 if rank < rem else 0)
+
+
+def plan_buckets(stage_end, bucket_elems):
+    """Group consecutive backward stages into buckets of >= bucket_elems fp32 elements.
+    stage_end[i] = end offset of stage i in the flat buffer.  Returns [(last_stage, lo, hi)]."""
+    buckets, lo = [], 0
+    for i, end in enumerate(stage_end):
+        last = i == len(stage_end) - 1
+        if end - lo >= bucket_elems or (last and end > lo):
+            buckets.append((i, lo, end))
+            lo = end
+    if buckets and buckets[-1][2] != stage_end[-1]:
+        buckets.append((len(stage_end) - 1, lo, stage_end[-1]))
+    return buckets
+
+
+class GradientAllReducer:
+    """Attach to a UNetModel / UNetAudio: averages the torso gradients across ranks during backward and the
+    remaining parameters (the wav2vec2 encoder) in `finish()`, which must run before optimizer.step()."""
+
+    def __init__(self, model, group=None, bucket_mb: float = 25.0):
+        self.model, self.group = model, group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.bucket_elems = int(bucket_mb * (1 << 20) / 4)
+        self._buckets = None
+        self._next = 0
+        self._comm = None
+        self._torso_ids = {id(p) for p in model.engine().torso_params()}
+        self.other_params = [p for p in model.parameters() if id(p) not in self._torso_ids and p.requires_grad]
+        model._grad_stage_hook = self._on_stage
+        model._grad_final_hook = self._on_final
+        self.bytes_reduced = 0
+
+    def _stream(self, device):
+        if self._comm is None and device.type == "cuda":
+            self._comm = torch.cuda.Stream(device=device)
+        return self._comm
+
+    def _all_reduce(self, t):
+        if self.world > 1:
+            if t.is_cuda:
+                dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group)
+            else:                                  # gloo (CPU tests) has no AVG
+                dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+                t.div_(self.world)
+        self.bytes_reduced += t.numel() * 4
+
+    def _on_stage(self, G, stage):
+        if self._buckets is None:
+            self._buckets = plan_buckets(G.stage_end, self.bucket_elems)
+        if stage == 0:
+            self._next = 0
+        while self._next < len(self._buckets) and self._buckets[self._next][0] <= stage:
+            _, lo, hi = self._buckets[self._next]
+            self._next += 1
+            view = G.flat[lo:hi]
+            comm = self._stream(view.device)
+            if comm is not None:
+                comm.wait_stream(torch.cuda.current_stream())
+                with torch.cuda.stream(comm):
+                    self._all_reduce(view)
+                view.record_stream(comm)
+            else:
+                self._all_reduce(view)
+
+    def _on_final(self, G):
+        if self._comm is not None:
+            torch.cuda.current_stream().wait_stream(self._comm)
+
+    def finish(self):
+        """All-reduce the gradients of the non-torso parameters (audio encoder) in one flat bucket."""
+        grads = [p.grad for p in self.other_params if p.grad is not None]
+        if not grads or self.world == 1:
+            return
+        flat = torch.cat([g.reshape(-1) for g in grads])
+        self._all_reduce(flat)
+        off = 0
+        for g in grads:
+            g.copy_(flat[off:off + g.numel()].view_as(g))
+            off += g.numel()
+
+
+def broadcast_parameters(model, src: int = 0, group=None):
+    """Identical weights on every rank before the first step."""
+    if not dist.is_initialized() or dist.get_world_size(group) == 1:
+        return
+    with torch.no_grad():
+        for t in list(model.parameters()) + list(model.buffers()):
+            dist.broadcast(t, src=src, group=group)
