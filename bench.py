@@ -272,7 +272,10 @@ def main():
             "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
             "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
             "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N fwd, 10*L^2*ch*N bwd"}
-    n_cpu, sec_cpu, reps = cpu_baseline(S, cores)
+    if os.environ.get("B2D_BENCH_NO_CPU") == "1":          # profiling runs only (ncu): skip the host-side leg
+        n_cpu, sec_cpu, reps = 2, float("inf"), 0
+    else:
+        n_cpu, sec_cpu, reps = cpu_baseline(S, cores)
     cpu_v = (n_cpu / frames) / sec_cpu
     value = clips * world / (ms / 1000.0)
     train_tflop = 3 * FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0

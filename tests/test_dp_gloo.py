@@ -1,0 +1,110 @@
+"""CPU, world_size 2 over gloo: the data-parallel host logic (bucket planning, stage-triggered all-reduce of the
+engine's flat gradient buffer, parameter broadcast, clip sharding).  The NCCL path itself runs on the GPU box."""
+import os
+import socket
+import sys
+
+import torch
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_shard_range_partitions_clips():
+    from lipreading_video_generation_b200.parallel import shard_range
+    for n, w in ((16, 8), (17, 4), (3, 8), (0, 2)):
+        spans = [shard_range(n, r, w) for r in range(w)]
+        assert spans[0][0] == 0 and spans[-1][1] == n
+        for a, b in zip(spans, spans[1:]):
+            assert a[1] == b[0]
+        sizes = [hi - lo for lo, hi in spans]
+        assert max(sizes) - min(sizes) <= 1
+
+
+def test_plan_buckets_covers_buffer_in_stage_order():
+    from lipreading_video_generation_b200.parallel import plan_buckets
+    ends = [10, 10, 50, 120, 121, 300]
+    b = plan_buckets(ends, 100)
+    assert b[0][1] == 0 and b[-1][2] == 300
+    for x, y in zip(b, b[1:]):
+        assert x[2] == y[1] and x[0] < y[0]
+    assert all(hi - lo >= 100 for _, lo, hi in b[:-1])
+    assert plan_buckets([5], 100) == [(0, 0, 5)]
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, q):
+    try:
+        sys.path.insert(0, ROOT)
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), B2D_WAV2VEC2_RANDOM_INIT="1")
+        import torch.distributed as dist
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        import lipreading_video_generation_b200 as P
+        from lipreading_video_generation_b200.engine import _Grads
+        from lipreading_video_generation_b200.parallel import GradientAllReducer, broadcast_parameters
+
+        class Enc(torch.nn.Module):                  # stands for the wav2vec2 encoder: a non-torso parameter
+            def __init__(self):
+                super().__init__()
+                self.w = torch.nn.Parameter(torch.zeros(7))
+
+            def forward(self, a):
+                return a["feats"]
+        torch.manual_seed(100 + rank)               # different init per rank: broadcast must equalise it
+        m = P.UNetAudio(image_size=32, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=1,
+                        attention_resolutions=(1, 2), channel_mult=(1, 2), dropout=0.0, audio_feature_dim=768,
+                        projected_audio_dim=128, audio_encoder=Enc())
+        broadcast_parameters(m)
+        chk = torch.stack([p.detach().double().sum() for p in m.parameters()])
+        gathered = [torch.zeros_like(chk) for _ in range(world)]
+        dist.all_gather(gathered, chk)
+        assert all(torch.equal(gathered[0], g) for g in gathered), "parameters differ after broadcast"
+
+        red = GradientAllReducer(m, bucket_mb=0.5)
+        eng = m.engine()
+        G = _Grads(eng, "cpu")
+        n = G.flat.numel()
+        base = torch.arange(n, dtype=torch.float32) % 97
+        G.flat.copy_(base * (rank + 1))
+        # replay the backward: stage k finishes -> hook; a bucket is reduced only once all its stages are done
+        reduced_upto = 0
+        for stage in range(eng.n_stages):
+            m._grad_stage_hook(G, stage)
+            done = [b for b in red._buckets if b[0] <= stage]
+            reduced_upto = done[-1][2] if done else 0
+            want_done = base[:reduced_upto] * (sum(range(1, world + 1)) / world)
+            assert torch.allclose(G.flat[:reduced_upto], want_done), f"stage {stage}"
+            assert torch.equal(G.flat[reduced_upto:], base[reduced_upto:] * (rank + 1)), "bucket reduced too early"
+        m._grad_final_hook(G)
+        assert reduced_upto == n
+        assert len(red._buckets) > 1
+        m.audio_encoder.w.grad = torch.full((7,), float(rank + 1))
+        red.finish()
+        assert torch.allclose(m.audio_encoder.w.grad, torch.full((7,), sum(range(1, world + 1)) / world))
+        assert red.bytes_reduced == 4 * (n + 7)
+        dist.destroy_process_group()
+        q.put((rank, "ok"))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc() + repr(e)))
+
+
+def test_gradient_all_reducer_world2_gloo():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res

@@ -88,7 +88,9 @@ def test_eval_forward_no_grad_matches_train_forward(golden):
     model.eval()
     with torch.no_grad():
         b = model(xt, g["cond"].cuda(), {"feats": g["feats"].cuda()}, t)
-    assert torch.equal(a, b)
+    # same kernels, same schedule; GroupNorm statistics are accumulated with fp32 shared-memory atomics, so two
+    # runs may differ by bf16 re-rounding of a few activations (not a parity bar: both are checked vs golden)
+    assert rel(a, b) <= 2e-3
 
 
 def test_cpu_input_fails_loudly(golden):

@@ -1,0 +1,162 @@
+"""CPU: the oracle (oracle/restatement.py) against the golden vectors that oracle/make_golden.py produced by
+running the REAL reference modules (imported from /root/reference) -- this is what pins the oracle.
+Also pins the host-side schedule tables of the product (built with the reference's own torch ops)."""
+import math
+
+import pytest
+import torch
+
+from oracle import restatement as R
+
+
+def test_linear_schedule_tables_bit_exact_vs_reference(golden):
+    g = golden("schedules.pt")
+    for name in ("lin100", "lin1000", "v2_500"):
+        tabs = R.linear_tables(*g[name]["args"])
+        for k, v in tabs.items():
+            assert torch.equal(v, g[name][k]), (name, k)
+
+
+def test_cosine_schedule_tables_bit_exact_vs_reference(golden):
+    g = golden("schedules.pt")["cos1000"]
+    tabs = R.cosine_tables(*g["args"])
+    for k, v in tabs.items():
+        assert torch.equal(v, g[k]), k
+
+
+def test_schedule_known_answers_from_survey():
+    """SURVEY.md section 4 KAT values measured from the reference (fp32)."""
+    t = R.linear_tables(100, 0.00085, 0.012)
+    assert [float(t["betas"][i]) for i in (0, 1, 50, 99)] == [
+        0.0008499999530613422, 0.00089800771092996, 0.004865849856287241, 0.011999999172985554]
+    assert [float(t["alpha_cum_prod"][i]) for i in (0, 50, 99)] == [
+        0.9991499781608582, 0.8761393427848816, 0.5839923620223999]
+    assert [float(t["sqrt_one_minus_alpha_cum_prod"][i]) for i in (0, 50, 99)] == [
+        0.029155133292078972, 0.3519384264945984, 0.6449865698814392]
+    v2 = R.linear_tables(500, 5e-5, 0.015)
+    assert [float(v2["alpha_cum_prod"][i]) for i in (0, 250, 499)] == [
+        0.9999499917030334, 0.6730650067329407, 0.06946355104446411]
+    c = R.cosine_tables(1000)
+    assert [float(c["alphas_cumprod"][i]) for i in (0, 500, 999)] == [
+        0.9998445510864258, 0.4937668740749359, 2.428544121357845e-06]
+
+
+def test_product_scheduler_tables_equal_reference(golden):
+    """The product's scheduler classes build their public tables on the host: bit-exact, no GPU needed."""
+    import lipreading_video_generation_b200 as P
+    g = golden("schedules.pt")
+    for name, cls in (("lin100", P.LinearNoiseScheduler), ("lin1000", P.LinearNoiseScheduler),
+                      ("v2_500", P.LinearNoiseSchedulerV2)):
+        s = cls(*g[name]["args"])
+        for k in ("betas", "alphas", "alpha_cum_prod", "sqrt_alpha_cum_prod", "sqrt_one_minus_alpha_cum_prod"):
+            assert torch.equal(getattr(s, k), g[name][k]), (name, k)
+    c = P.CosineNoiseScheduler(1000)
+    for k in ("alphas_cumprod", "sqrt_alphas_cumprod", "sqrt_one_minus_alphas_cumprod"):
+        assert torch.equal(getattr(c, k), g["cos1000"][k]), k
+
+
+def test_q_sample_bit_exact_vs_reference(golden):
+    g = golden("q_sample.pt")
+    xt = R.add_noise(R.linear_tables(1000, 0.00085, 0.012), g["x0"], g["eps"], g["t"])
+    assert torch.equal(xt, g["xt"])
+
+
+def test_samplers_bit_exact_vs_reference(golden):
+    g = golden("samplers.pt")
+    lin, v2, cos = R.linear_tables(1000, 0.00085, 0.012), R.linear_tables(500, 5e-5, 0.015), R.cosine_tables(1000)
+    seen = set()
+    for c in g["cases"]:
+        if c["kind"] == "ddpm":
+            a, b = R.ddpm_step(lin, g["xt"], g["eps"], c["t"], c["z"])
+        elif c["kind"] == "v2":
+            a, b = R.ddpm_v2_step(v2, g["xt"], g["eps"], c["t"], c["z"])
+        else:
+            a, b = R.cosine_step(cos, g["xt"], g["eps"], c["t"], c["z"])
+        assert torch.equal(a, c["x_prev"]) and torch.equal(b, c["second"]), (c["kind"], c["t"])
+        seen.add(c["kind"])
+    assert seen == {"ddpm", "v2", "cos"}
+
+
+def test_ddpm_t0_returns_mean_without_noise(golden):
+    """linear_noise_scheduler.py:64-65: at t == 0 the noise must not be added."""
+    g = golden("samplers.pt")
+    lin = R.linear_tables(1000, 0.00085, 0.012)
+    a, _ = R.ddpm_step(lin, g["xt"], g["eps"], 0, torch.full_like(g["xt"], 1e6))
+    b, _ = R.ddpm_step(lin, g["xt"], g["eps"], 0, torch.zeros_like(g["xt"]))
+    assert torch.equal(a, b)
+
+
+def _tiny_cfg(g):
+    c = g["cfg"]
+    return dict(image_size=c["image_size"], model_channels=c["model_channels"], num_res_blocks=c["num_res_blocks"],
+                attention_resolutions=c["attention_resolutions"], channel_mult=c["channel_mult"], num_heads=1)
+
+
+def test_unet_audio_forward_loss_grads_vs_reference_golden(golden):
+    """fp32 bar of north_star: relative error <= 1e-4 on output, loss and gradients."""
+    import lipreading_video_generation_b200 as P
+
+    class Stub(torch.nn.Module):
+        def forward(self, a):
+            return a["feats"]
+    g = golden("unet_tiny.pt")
+    model = P.UNetAudio(**g["cfg"], audio_encoder=Stub())
+    sd = R.fill_params(model.state_dict(), seed=g["seed"])
+    sdr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+    pred = R.unet_audio_forward(sdr, _tiny_cfg(g), g["xt"], g["cond"], g["feats"].mean(dim=1), g["t"])
+    loss = R.mse(pred, g["eps"])
+    loss.backward()
+    assert ((pred - g["pred"]).norm() / g["pred"].norm()).item() <= 1e-4
+    assert abs(loss.item() - g["loss"].item()) <= 1e-4 * abs(g["loss"].item())
+    for k, ref in g["grads"].items():
+        e = ((sdr[k].grad - ref).norm() / ref.norm()).item()
+        assert e <= 1e-4, (k, e)
+    for k, n_ref in g["grad_norms"].items():
+        assert abs(sdr[k].grad.norm().item() - n_ref) <= 1e-4 * n_ref + 1e-9, k
+
+
+def test_timestep_embedding_order_and_values():
+    """utils.py:140-158: cos first, then sin."""
+    t = torch.tensor([0, 1, 999])
+    e = R.timestep_embedding(t, 64)
+    assert e.shape == (3, 64)
+    assert torch.equal(e[0, :32], torch.ones(32)) and torch.equal(e[0, 32:], torch.zeros(32))
+    f1 = math.exp(-math.log(10000) * 1 / 32)
+    assert abs(e[1, 1].item() - math.cos(f1)) < 1e-6 and abs(e[1, 33].item() - math.sin(f1)) < 1e-6
+
+
+def test_attention_legacy_and_new_order_agree_for_one_head():
+    g = torch.Generator().manual_seed(0)
+    qkv = torch.randn(2, 3 * 16, 10, generator=g)
+    assert torch.allclose(R.qkv_attention_legacy(qkv, 1), R.qkv_attention_new(qkv, 1), atol=1e-6)
+    # with 2 heads the channel orders differ ([head][q|k|v][ch] vs [q|k|v][head][ch]): permuting makes them agree
+    qkv2 = torch.randn(2, 3 * 2 * 8, 10, generator=g)
+    legacy_as_new = qkv2.view(2, 2, 3, 8, 10).permute(0, 2, 1, 3, 4).reshape(2, 48, 10)
+    assert torch.allclose(R.qkv_attention_legacy(qkv2, 2), R.qkv_attention_new(legacy_as_new, 2), atol=1e-6)
+
+
+def test_ddim_final_step_returns_x0():
+    """DDIM eta=0 (parity unpinned -- not in the reference): with alpha_bar_prev = 1 the result is x0_pred."""
+    acp = R.linear_tables(1000, 0.00085, 0.012)["alpha_cum_prod"]
+    g = torch.Generator().manual_seed(0)
+    xt, e = torch.randn(2, 3, 8, 8, generator=g) * 0.1, torch.randn(2, 3, 8, 8, generator=g) * 0.1
+    xp, x0 = R.ddim_step(acp, xt, e, 10, -1)
+    assert torch.allclose(xp, x0)
+
+
+@pytest.mark.skipif(not __import__("oracle.ref_import", fromlist=["x"]).available(), reason="/root/reference absent")
+def test_restatement_matches_live_reference_attention_block():
+    """Where the reference is present (build container) compare one AttentionBlock and one ResBlock live."""
+    from oracle import ref_import
+    ref = ref_import.load()
+    torch.manual_seed(0)
+    ab = ref.unet.AttentionBlock(64, num_heads=2)
+    sd = R.fill_params(dict(ab.state_dict()), seed=3)
+    ab.load_state_dict(sd)
+    x = torch.randn(2, 64, 6, 6)
+    assert torch.allclose(ab._forward(x), R.attention_block(sd, "", x, 2), atol=2e-6)
+    rb = ref.unet.ResBlock(64, 256, 0.0, out_channels=128)
+    sdr = R.fill_params(dict(rb.state_dict()), seed=4)
+    rb.load_state_dict(sdr)
+    emb = torch.randn(2, 256)
+    assert torch.allclose(rb._forward(x, emb), R.res_block(sdr, "", x, emb), atol=2e-6)
