@@ -103,10 +103,14 @@ int b2d_mse_bwd(const float* pred, const float* target, const float* grad_out,
 
 /* ------------------------------------------------------------------------
  * Denoiser kernels.  Activation layout inside the library is PIXEL-MAJOR
- * (N,H,W,C) bf16 -- the channels-last image of the reference's NCHW / (B,C,L)
+ * (N,H,W,C) fp16 -- the channels-last image of the reference's NCHW / (B,C,L)
  * tensors -- so that one row of a tile is one K-major 128-byte line for the
- * tcgen05 tensor cores.  Weights stay fp32 OIHW in state_dict; the host side
- * packs bf16 copies [Cout][tap][Cin] for these calls.
+ * tcgen05 tensor cores; accumulation is always fp32.  Gradient tensors are fp16
+ * too and carry a power-of-two loss scale (b2d_grad_scale).  NOTE: parameter
+ * comments below that say "bf16" predate the switch and mean "fp16" (bf16
+ * storage missed north_star's 2e-2 gradient tolerance).
+ * Weights stay fp32 OIHW in state_dict; the host side packs fp16 copies
+ * [Cout][tap][Cin] for these calls.
  * ---------------------------------------------------------------------- */
 
 /* Implicit-GEMM convolution on tcgen05/TMEM fed by TMA.
@@ -208,8 +212,16 @@ int b2d_upsample2x(const void* x, void* y, int N, int H, int W, int C, void* str
 int b2d_upsample2x_bwd(const void* dy, void* dx, int N, int H, int W, int C, void* stream);
 /* z[n,2h,2w,:] = dy[n,h,w,:], zero elsewhere (stride-2 Downsample dgrad as a stride-1 conv). */
 int b2d_zero_insert2x(const void* dy, void* z, int N, int Ho, int Wo, int C, void* stream);
-/* fp32 (N,C,HW) -> bf16 (N,HW,Cpad) with zero-padded channels. */
-int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad, void* stream);
+/* fp32 (N,C,HW) -> fp16 (N,HW,Cpad) with zero-padded channels, multiplied by *scale (device scalar) when
+ * scale != NULL (the loss scale of the incoming gradient d loss / d pred). */
+int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad, const float* scale,
+                            void* stream);
+/* Loss scale for the fp16 gradient tensors, chosen on the device (no host sync): scale2[0] = 2^k such that
+ * max|x| * 2^k lies in [target/2, target), scale2[1] = 2^-k.  (The reference's own low-precision design is fp16
+ * with dynamic loss scaling: fp16_util.py:148-233 MixedPrecisionTrainer.) */
+int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream);
+/* x[i] *= *scale  (unscale the fp32 parameter gradients). */
+int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream);
 /* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x bf16 (N,HW,ld)): emb_out / bias / audio gradients. */
 int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */

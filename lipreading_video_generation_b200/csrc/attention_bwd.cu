@@ -23,7 +23,7 @@ struct AttnBwdParams {
   float scale;        // 1/sqrt(ch)
   const float* lse;   // (N, heads, L) log2 domain
   const float* delta; // (N, heads, L)
-  __nv_bfloat16* dqkv; long long lddqkv;  // (N, L, 3C)
+  __half* dqkv; long long lddqkv;  // (N, L, 3C)
 };
 
 struct AttnBwdMaps {
@@ -41,7 +41,7 @@ __device__ __forceinline__ void named_bar_sync(int id, int count) {
 
 // ------------------------------------------------------------------ delta = rowsum(dO * O)
 __global__ void __launch_bounds__(256)
-attn_delta_kernel(const __nv_bfloat16* __restrict__ o, long long ldo, const __nv_bfloat16* __restrict__ d_o,
+attn_delta_kernel(const __half* __restrict__ o, long long ldo, const __half* __restrict__ d_o,
                   long long lddo, int N, int L, int heads, int ch, float* __restrict__ delta) {
   // one warp per (n, l, head)
   const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -50,12 +50,12 @@ attn_delta_kernel(const __nv_bfloat16* __restrict__ o, long long ldo, const __nv
   if (w >= total) return;
   const int h = (int)(w % heads);
   const long long nl = w / heads;
-  const __nv_bfloat16* po = o + nl * ldo + h * ch;
-  const __nv_bfloat16* pd = d_o + nl * lddo + h * ch;
+  const __half* po = o + nl * ldo + h * ch;
+  const __half* pd = d_o + nl * lddo + h * ch;
   float acc = 0.f;
   for (int c = lane * 2; c < ch; c += 64) {
-    const float2 a = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(po + c));
-    const float2 b = unpack_bf16x2(*reinterpret_cast<const uint32_t*>(pd + c));
+    const float2 a = unpack_f16x2(*reinterpret_cast<const uint32_t*>(po + c));   // O: forward tensor, fp16
+    const float2 b = unpack_f16x2(*reinterpret_cast<const uint32_t*>(pd + c));
     acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc);
   }
   acc = warp_sum(acc);
@@ -140,8 +140,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc_s = make_idesc_bf16(128, BQ, 0, 0);
-    const uint32_t idesc_g = make_idesc_bf16(128, DH, 0, 1);
+    const uint32_t idesc_s = make_idesc(128, BQ, 0, 0, FMT_F16, FMT_F16);    // S^T  = K Q^T   (fp16 x fp16)
+    const uint32_t idesc_p = make_idesc(128, BQ, 0, 0, FMT_F16, FMT_F16);   // dP^T = V dO^T  (fp16 x bf16)
+    const uint32_t idesc_v = make_idesc(128, DH, 0, 1, FMT_F16, FMT_F16);   // dV  += P^T dO  (fp16 x bf16)
+    const uint32_t idesc_k = make_idesc(128, DH, 0, 1, FMT_F16, FMT_F16);   // dK  += dS^T Q  (bf16 x fp16)
     const uint32_t k_addr = smem_u32(k_s), v_addr = smem_u32(v_s);
     const uint32_t pt_addr = smem_u32(pt_s), dst_addr = smem_u32(dst_s);
     mbar_wait(kv_full, 0);
@@ -156,15 +158,15 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BQ * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::ST_COL, make_sdesc_sw128(k_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::ST_COL, make_sdesc_sw128(k_addr + ao, 16, 1024),
                       make_sdesc_sw128(q_addr + bo, 16, 1024), idesc_s, (uint32_t)(kk != 0));
         }
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BQ * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::DPT_COL, make_sdesc_sw128(v_addr + ao, 16, 1024),
-                      make_sdesc_sw128(do_addr + bo, 16, 1024), idesc_s, (uint32_t)(kk != 0));
+          mma_f16_ss(tmem_base + Cfg::DPT_COL, make_sdesc_sw128(v_addr + ao, 16, 1024),
+                      make_sdesc_sw128(do_addr + bo, 16, 1024), idesc_p, (uint32_t)(kk != 0));
         }
         mma_commit(s_full);
       }
@@ -176,14 +178,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
 #pragma unroll
         for (int kk = 0; kk < BQ / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::DV_COL, make_sdesc_sw128(pt_addr + ao, 16, 1024),
-                      make_sdesc_sw128(do_addr + goff + kk * 2048, BQ * 128, 1024), idesc_g, (uint32_t)((j | kk) != 0));
+          mma_f16_ss(tmem_base + Cfg::DV_COL, make_sdesc_sw128(pt_addr + ao, 16, 1024),
+                      make_sdesc_sw128(do_addr + goff + kk * 2048, BQ * 128, 1024), idesc_v, (uint32_t)((j | kk) != 0));
         }
 #pragma unroll
         for (int kk = 0; kk < BQ / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::DK_COL, make_sdesc_sw128(dst_addr + ao, 16, 1024),
-                      make_sdesc_sw128(q_addr + goff + kk * 2048, BQ * 128, 1024), idesc_g, (uint32_t)((j | kk) != 0));
+          mma_f16_ss(tmem_base + Cfg::DK_COL, make_sdesc_sw128(dst_addr + ao, 16, 1024),
+                      make_sdesc_sw128(q_addr + goff + kk * 2048, BQ * 128, 1024), idesc_k, (uint32_t)((j | kk) != 0));
         }
         mma_commit(&empty[s]);
         mma_commit(acc_done);
@@ -228,10 +230,10 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint4 u, w;
-          u.x = pack_bf16x2(pv[8 * g + 0], pv[8 * g + 1]); u.y = pack_bf16x2(pv[8 * g + 2], pv[8 * g + 3]);
-          u.z = pack_bf16x2(pv[8 * g + 4], pv[8 * g + 5]); u.w = pack_bf16x2(pv[8 * g + 6], pv[8 * g + 7]);
-          w.x = pack_bf16x2(dv[8 * g + 0], dv[8 * g + 1]); w.y = pack_bf16x2(dv[8 * g + 2], dv[8 * g + 3]);
-          w.z = pack_bf16x2(dv[8 * g + 4], dv[8 * g + 5]); w.w = pack_bf16x2(dv[8 * g + 6], dv[8 * g + 7]);
+          u.x = pack_f16x2_nosat(pv[8 * g + 0], pv[8 * g + 1]); u.y = pack_f16x2_nosat(pv[8 * g + 2], pv[8 * g + 3]);
+          u.z = pack_f16x2_nosat(pv[8 * g + 4], pv[8 * g + 5]); u.w = pack_f16x2_nosat(pv[8 * g + 6], pv[8 * g + 7]);
+          w.x = pack_f16x2(dv[8 * g + 0], dv[8 * g + 1]); w.y = pack_f16x2(dv[8 * g + 2], dv[8 * g + 3]);
+          w.z = pack_f16x2(dv[8 * g + 4], dv[8 * g + 5]); w.w = pack_f16x2(dv[8 * g + 6], dv[8 * g + 7]);
           const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8 * g));
           *reinterpret_cast<uint4*>(pblk + off) = u;
           *reinterpret_cast<uint4*>(dblk + off) = w;
@@ -245,7 +247,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
     tc_fence_after();
     const int ki = kv0 + row;
     const bool valid = ki < p.L;
-    __nv_bfloat16* base = p.dqkv + ((long long)n * p.L + ki) * p.lddqkv;
+    __half* base = p.dqkv + ((long long)n * p.L + ki) * p.lddqkv;
 #pragma unroll
     for (int c0 = 0; c0 < DH; c0 += 16) {
       uint32_t a[16], b[16];
@@ -254,17 +256,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
       tmem_ld_wait();
       if (valid) {
         uint4 o0, o1, k0, k1;
-        o0.x = pack_bf16x2(__uint_as_float(a[0]), __uint_as_float(a[1]));   o0.y = pack_bf16x2(__uint_as_float(a[2]), __uint_as_float(a[3]));
-        o0.z = pack_bf16x2(__uint_as_float(a[4]), __uint_as_float(a[5]));   o0.w = pack_bf16x2(__uint_as_float(a[6]), __uint_as_float(a[7]));
-        o1.x = pack_bf16x2(__uint_as_float(a[8]), __uint_as_float(a[9]));   o1.y = pack_bf16x2(__uint_as_float(a[10]), __uint_as_float(a[11]));
-        o1.z = pack_bf16x2(__uint_as_float(a[12]), __uint_as_float(a[13])); o1.w = pack_bf16x2(__uint_as_float(a[14]), __uint_as_float(a[15]));
+        o0.x = pack_f16x2(__uint_as_float(a[0]), __uint_as_float(a[1]));   o0.y = pack_f16x2(__uint_as_float(a[2]), __uint_as_float(a[3]));
+        o0.z = pack_f16x2(__uint_as_float(a[4]), __uint_as_float(a[5]));   o0.w = pack_f16x2(__uint_as_float(a[6]), __uint_as_float(a[7]));
+        o1.x = pack_f16x2(__uint_as_float(a[8]), __uint_as_float(a[9]));   o1.y = pack_f16x2(__uint_as_float(a[10]), __uint_as_float(a[11]));
+        o1.z = pack_f16x2(__uint_as_float(a[12]), __uint_as_float(a[13])); o1.w = pack_f16x2(__uint_as_float(a[14]), __uint_as_float(a[15]));
         const float sc = p.scale;
-        k0.x = pack_bf16x2(__uint_as_float(b[0]) * sc, __uint_as_float(b[1]) * sc);   k0.y = pack_bf16x2(__uint_as_float(b[2]) * sc, __uint_as_float(b[3]) * sc);
-        k0.z = pack_bf16x2(__uint_as_float(b[4]) * sc, __uint_as_float(b[5]) * sc);   k0.w = pack_bf16x2(__uint_as_float(b[6]) * sc, __uint_as_float(b[7]) * sc);
-        k1.x = pack_bf16x2(__uint_as_float(b[8]) * sc, __uint_as_float(b[9]) * sc);   k1.y = pack_bf16x2(__uint_as_float(b[10]) * sc, __uint_as_float(b[11]) * sc);
-        k1.z = pack_bf16x2(__uint_as_float(b[12]) * sc, __uint_as_float(b[13]) * sc); k1.w = pack_bf16x2(__uint_as_float(b[14]) * sc, __uint_as_float(b[15]) * sc);
-        __nv_bfloat16* pv_ = base + vc + half * DH + c0;
-        __nv_bfloat16* pk_ = base + kc + half * DH + c0;
+        k0.x = pack_f16x2(__uint_as_float(b[0]) * sc, __uint_as_float(b[1]) * sc);   k0.y = pack_f16x2(__uint_as_float(b[2]) * sc, __uint_as_float(b[3]) * sc);
+        k0.z = pack_f16x2(__uint_as_float(b[4]) * sc, __uint_as_float(b[5]) * sc);   k0.w = pack_f16x2(__uint_as_float(b[6]) * sc, __uint_as_float(b[7]) * sc);
+        k1.x = pack_f16x2(__uint_as_float(b[8]) * sc, __uint_as_float(b[9]) * sc);   k1.y = pack_f16x2(__uint_as_float(b[10]) * sc, __uint_as_float(b[11]) * sc);
+        k1.z = pack_f16x2(__uint_as_float(b[12]) * sc, __uint_as_float(b[13]) * sc); k1.w = pack_f16x2(__uint_as_float(b[14]) * sc, __uint_as_float(b[15]) * sc);
+        __half* pv_ = base + vc + half * DH + c0;
+        __half* pk_ = base + kc + half * DH + c0;
         *reinterpret_cast<uint4*>(pv_) = o0; *reinterpret_cast<uint4*>(pv_ + 8) = o1;
         *reinterpret_cast<uint4*>(pk_) = k0; *reinterpret_cast<uint4*>(pk_ + 8) = k1;
       }
@@ -347,8 +349,9 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc_s = make_idesc_bf16(128, BKV, 0, 0);
-    const uint32_t idesc_g = make_idesc_bf16(128, D, 0, 1);
+    const uint32_t idesc_s = make_idesc(128, BKV, 0, 0, FMT_F16, FMT_F16);   // S   = Q K^T   (fp16 x fp16)
+    const uint32_t idesc_p = make_idesc(128, BKV, 0, 0, FMT_F16, FMT_F16);  // dP  = dO V^T  (bf16 x fp16)
+    const uint32_t idesc_g = make_idesc(128, D, 0, 1, FMT_F16, FMT_F16);    // dQ += dS K    (bf16 x fp16)
     const uint32_t q_addr = smem_u32(q_s), do_addr = smem_u32(do_s), ds_addr = smem_u32(ds_s);
     mbar_wait(q_full, 0);
     for (int j = 0; j < n_kv; ++j) {
@@ -362,15 +365,15 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::S_COL, make_sdesc_sw128(q_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::S_COL, make_sdesc_sw128(q_addr + ao, 16, 1024),
                       make_sdesc_sw128(k_addr + bo, 16, 1024), idesc_s, (uint32_t)(kk != 0));
         }
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::DP_COL, make_sdesc_sw128(do_addr + ao, 16, 1024),
-                      make_sdesc_sw128(v_addr + bo, 16, 1024), idesc_s, (uint32_t)(kk != 0));
+          mma_f16_ss(tmem_base + Cfg::DP_COL, make_sdesc_sw128(do_addr + ao, 16, 1024),
+                      make_sdesc_sw128(v_addr + bo, 16, 1024), idesc_p, (uint32_t)(kk != 0));
         }
         mma_commit(s_full);
       }
@@ -381,7 +384,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
 #pragma unroll
         for (int kk = 0; kk < BKV / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
-          mma_bf16_ss(tmem_base + Cfg::DQ_COL, make_sdesc_sw128(ds_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::DQ_COL, make_sdesc_sw128(ds_addr + ao, 16, 1024),
                       make_sdesc_sw128(k_addr + kk * 2048, BKV * 128, 1024), idesc_g, (uint32_t)((j | kk) != 0));
         }
         mma_commit(&empty[s]);
@@ -419,8 +422,8 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint4 w;
-          w.x = pack_bf16x2(dv[8 * g + 0], dv[8 * g + 1]); w.y = pack_bf16x2(dv[8 * g + 2], dv[8 * g + 3]);
-          w.z = pack_bf16x2(dv[8 * g + 4], dv[8 * g + 5]); w.w = pack_bf16x2(dv[8 * g + 6], dv[8 * g + 7]);
+          w.x = pack_f16x2(dv[8 * g + 0], dv[8 * g + 1]); w.y = pack_f16x2(dv[8 * g + 2], dv[8 * g + 3]);
+          w.z = pack_f16x2(dv[8 * g + 4], dv[8 * g + 5]); w.w = pack_f16x2(dv[8 * g + 6], dv[8 * g + 7]);
           *reinterpret_cast<uint4*>(dblk + sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8 * g))) = w;
         }
       }
@@ -430,7 +433,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
     }
     mbar_wait(acc_done, (uint32_t)((n_kv - 1) & 1));
     tc_fence_after();
-    __nv_bfloat16* dst = p.dqkv + ((long long)n * p.L + qi) * p.lddqkv + qc;
+    __half* dst = p.dqkv + ((long long)n * p.L + qi) * p.lddqkv + qc;
     const float sc = p.scale;
 #pragma unroll
     for (int c0 = 0; c0 < D; c0 += 16) {
@@ -439,10 +442,10 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
       tmem_ld_wait();
       if (valid) {
         uint4 o0, o1;
-        o0.x = pack_bf16x2(__uint_as_float(a[0]) * sc, __uint_as_float(a[1]) * sc);   o0.y = pack_bf16x2(__uint_as_float(a[2]) * sc, __uint_as_float(a[3]) * sc);
-        o0.z = pack_bf16x2(__uint_as_float(a[4]) * sc, __uint_as_float(a[5]) * sc);   o0.w = pack_bf16x2(__uint_as_float(a[6]) * sc, __uint_as_float(a[7]) * sc);
-        o1.x = pack_bf16x2(__uint_as_float(a[8]) * sc, __uint_as_float(a[9]) * sc);   o1.y = pack_bf16x2(__uint_as_float(a[10]) * sc, __uint_as_float(a[11]) * sc);
-        o1.z = pack_bf16x2(__uint_as_float(a[12]) * sc, __uint_as_float(a[13]) * sc); o1.w = pack_bf16x2(__uint_as_float(a[14]) * sc, __uint_as_float(a[15]) * sc);
+        o0.x = pack_f16x2(__uint_as_float(a[0]) * sc, __uint_as_float(a[1]) * sc);   o0.y = pack_f16x2(__uint_as_float(a[2]) * sc, __uint_as_float(a[3]) * sc);
+        o0.z = pack_f16x2(__uint_as_float(a[4]) * sc, __uint_as_float(a[5]) * sc);   o0.w = pack_f16x2(__uint_as_float(a[6]) * sc, __uint_as_float(a[7]) * sc);
+        o1.x = pack_f16x2(__uint_as_float(a[8]) * sc, __uint_as_float(a[9]) * sc);   o1.y = pack_f16x2(__uint_as_float(a[10]) * sc, __uint_as_float(a[11]) * sc);
+        o1.z = pack_f16x2(__uint_as_float(a[12]) * sc, __uint_as_float(a[13]) * sc); o1.w = pack_f16x2(__uint_as_float(a[14]) * sc, __uint_as_float(a[15]) * sc);
         *reinterpret_cast<uint4*>(dst + c0) = o0;
         *reinterpret_cast<uint4*>(dst + c0 + 8) = o1;
       }
@@ -475,10 +478,10 @@ static int launch_attn_bwd(const void* qkv, int64_t ldqkv, const void* d_o, int6
   {  // kernel A: streamed tiles are BQ queries
     AttnBwdMaps m;
     const uint32_t boxT[3] = {64u, (uint32_t)BQ, 1u};
-    if ((rc = make_tmap_bf16(&m.qkv128, qkv, 3, dims, str, box128))) return rc;
-    if ((rc = make_tmap_bf16(&m.qkvT, qkv, 3, dims, str, boxT))) return rc;
-    if ((rc = make_tmap_bf16(&m.doR, d_o, 3, ddims, dstr, box128))) return rc;
-    if ((rc = make_tmap_bf16(&m.doT, d_o, 3, ddims, dstr, boxT))) return rc;
+    if ((rc = make_tmap_16b(&m.qkv128, qkv, 3, dims, str, box128))) return rc;
+    if ((rc = make_tmap_16b(&m.qkvT, qkv, 3, dims, str, boxT))) return rc;
+    if ((rc = make_tmap_16b(&m.doR, d_o, 3, ddims, dstr, box128))) return rc;
+    if ((rc = make_tmap_16b(&m.doT, d_o, 3, ddims, dstr, boxT))) return rc;
     dim3 grid((unsigned)(((L + 127) / 128) * (D / DH)), (unsigned)heads, (unsigned)N);
     attn_bwd_dkv_kernel<D, DH, BQ><<<grid, AB_THREADS, CA::SMEM_TOTAL, st>>>(m, p);
     B2D_CHECK_LAUNCH();
@@ -486,9 +489,9 @@ static int launch_attn_bwd(const void* qkv, int64_t ldqkv, const void* d_o, int6
   {  // kernel B: streamed tiles are BKV keys
     AttnBwdMaps m;
     const uint32_t boxT[3] = {64u, (uint32_t)BKV, 1u};
-    if ((rc = make_tmap_bf16(&m.qkv128, qkv, 3, dims, str, box128))) return rc;
-    if ((rc = make_tmap_bf16(&m.qkvT, qkv, 3, dims, str, boxT))) return rc;
-    if ((rc = make_tmap_bf16(&m.doR, d_o, 3, ddims, dstr, box128))) return rc;
+    if ((rc = make_tmap_16b(&m.qkv128, qkv, 3, dims, str, box128))) return rc;
+    if ((rc = make_tmap_16b(&m.qkvT, qkv, 3, dims, str, boxT))) return rc;
+    if ((rc = make_tmap_16b(&m.doR, d_o, 3, ddims, dstr, box128))) return rc;
     m.doT = m.doR;
     dim3 grid((unsigned)((L + 127) / 128), (unsigned)heads, (unsigned)N);
     attn_bwd_dq_kernel<D, BKV><<<grid, AB_THREADS, CB::SMEM_TOTAL, st>>>(m, p);
@@ -516,12 +519,12 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
   p.scale = 1.0f / sqrtf((float)ch);
   p.scale_log2 = 1.4426950408889634f * p.scale;
   p.lse = lse; p.delta = delta_ws;
-  p.dqkv = (__nv_bfloat16*)dqkv; p.lddqkv = lddqkv;
+  p.dqkv = (__half*)dqkv; p.lddqkv = lddqkv;
   {
     const long long warps = (long long)N * L * heads;
     const long long blocks = (warps * 32 + 255) / 256;
     attn_delta_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
-        (const __nv_bfloat16*)out, ldo, (const __nv_bfloat16*)d_out, lddo, N, L, heads, ch, delta_ws);
+        (const __half*)out, ldo, (const __half*)d_out, lddo, N, L, heads, ch, delta_ws);
     B2D_CHECK_LAUNCH();
   }
   if (ch == 64) return launch_attn_bwd<64, 64, 128, 128>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);

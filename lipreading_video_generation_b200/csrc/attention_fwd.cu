@@ -20,7 +20,7 @@ struct AttnFwdParams {
   int L, heads;
   int q_off, k_off, v_off, head_stride;  // channel offsets inside the 3C row
   float scale_log2;                      // log2(e) / sqrt(ch)
-  __nv_bfloat16* out; long long ldo;     // (N, L, ldo), head h at channel h*D
+  __half* out; long long ldo;     // (N, L, ldo), head h at channel h*D
   float* lse;                            // (N, heads, L): log2-domain log-sum-exp of the scaled logits
 };
 
@@ -113,8 +113,8 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
     }
   } else if (warp == 1) {
     // ---------------------------------------------------------------- MMA issuer
-    const uint32_t idesc_s = make_idesc_bf16(128, BKV, 0, 0);  // S = Q K^T, both K-major
-    const uint32_t idesc_o = make_idesc_bf16(128, D, 0, 1);    // O += P V, V MN-major
+    const uint32_t idesc_s = make_idesc(128, BKV, 0, 0, FMT_F16, FMT_F16);  // S = Q K^T, both K-major
+    const uint32_t idesc_o = make_idesc(128, D, 0, 1, FMT_F16, FMT_F16);    // O += P V, V MN-major
     const uint32_t q_addr = smem_u32(q_s);
     const uint32_t p_addr = smem_u32(p_s);
     auto issue_s = [&](int j) {
@@ -128,7 +128,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t a = q_addr + (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t b = k_addr + (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-          mma_bf16_ss(d_tmem, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, 16, 1024), idesc_s, (uint32_t)(kk != 0));
+          mma_f16_ss(d_tmem, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, 16, 1024), idesc_s, (uint32_t)(kk != 0));
         }
         mma_commit(&s_full[j & 1]);
       }
@@ -148,7 +148,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
         for (int kk = 0; kk < BKV / 16; ++kk) {
           const uint32_t a = p_addr + (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t b = v_addr + kk * 2048;
-          mma_bf16_ss(tmem_base + Cfg::O_COL, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, BKV * 128, 1024),
+          mma_f16_ss(tmem_base + Cfg::O_COL, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, BKV * 128, 1024),
                       idesc_o, (uint32_t)((j | kk) != 0));
         }
         mma_commit(&kv_empty[s]);
@@ -204,7 +204,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
         }
         tmem_st_wait();
       }
-      // pass 2: p = exp2(c*s - c*m), row sum, P -> swizzled smem (bf16)
+      // pass 2: p = exp2(c*s - c*m), row sum, P -> swizzled smem (fp16)
       const float mc = m_used * c;
 #pragma unroll
       for (int c0 = 0; c0 < BKV; c0 += 32) {
@@ -222,10 +222,10 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint4 u;
-          u.x = pack_bf16x2(pv[8 * g + 0], pv[8 * g + 1]);
-          u.y = pack_bf16x2(pv[8 * g + 2], pv[8 * g + 3]);
-          u.z = pack_bf16x2(pv[8 * g + 4], pv[8 * g + 5]);
-          u.w = pack_bf16x2(pv[8 * g + 6], pv[8 * g + 7]);
+          u.x = pack_f16x2_nosat(pv[8 * g + 0], pv[8 * g + 1]);
+          u.y = pack_f16x2_nosat(pv[8 * g + 2], pv[8 * g + 3]);
+          u.z = pack_f16x2_nosat(pv[8 * g + 4], pv[8 * g + 5]);
+          u.w = pack_f16x2_nosat(pv[8 * g + 6], pv[8 * g + 7]);
           const uint32_t col = (uint32_t)((c0 & 63) + 8 * g);
           *reinterpret_cast<uint4*>(blk + sw128_offset((uint32_t)row, col)) = u;
         }
@@ -240,7 +240,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
     const int qi = q0 + row;
     const bool valid = qi < p.L;
     const float inv_l = 1.0f / l_sum;
-    __nv_bfloat16* op = p.out + ((long long)n * p.L + qi) * p.ldo + head * D;
+    __half* op = p.out + ((long long)n * p.L + qi) * p.ldo + head * D;
 #pragma unroll
     for (int c0 = 0; c0 < D; c0 += 16) {
       uint32_t r[16];
@@ -248,14 +248,14 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
       tmem_ld_wait();
       if (valid) {
         uint4 o0, o1;
-        o0.x = pack_bf16x2(__uint_as_float(r[0]) * inv_l, __uint_as_float(r[1]) * inv_l);
-        o0.y = pack_bf16x2(__uint_as_float(r[2]) * inv_l, __uint_as_float(r[3]) * inv_l);
-        o0.z = pack_bf16x2(__uint_as_float(r[4]) * inv_l, __uint_as_float(r[5]) * inv_l);
-        o0.w = pack_bf16x2(__uint_as_float(r[6]) * inv_l, __uint_as_float(r[7]) * inv_l);
-        o1.x = pack_bf16x2(__uint_as_float(r[8]) * inv_l, __uint_as_float(r[9]) * inv_l);
-        o1.y = pack_bf16x2(__uint_as_float(r[10]) * inv_l, __uint_as_float(r[11]) * inv_l);
-        o1.z = pack_bf16x2(__uint_as_float(r[12]) * inv_l, __uint_as_float(r[13]) * inv_l);
-        o1.w = pack_bf16x2(__uint_as_float(r[14]) * inv_l, __uint_as_float(r[15]) * inv_l);
+        o0.x = pack_f16x2(__uint_as_float(r[0]) * inv_l, __uint_as_float(r[1]) * inv_l);
+        o0.y = pack_f16x2(__uint_as_float(r[2]) * inv_l, __uint_as_float(r[3]) * inv_l);
+        o0.z = pack_f16x2(__uint_as_float(r[4]) * inv_l, __uint_as_float(r[5]) * inv_l);
+        o0.w = pack_f16x2(__uint_as_float(r[6]) * inv_l, __uint_as_float(r[7]) * inv_l);
+        o1.x = pack_f16x2(__uint_as_float(r[8]) * inv_l, __uint_as_float(r[9]) * inv_l);
+        o1.y = pack_f16x2(__uint_as_float(r[10]) * inv_l, __uint_as_float(r[11]) * inv_l);
+        o1.z = pack_f16x2(__uint_as_float(r[12]) * inv_l, __uint_as_float(r[13]) * inv_l);
+        o1.w = pack_f16x2(__uint_as_float(r[14]) * inv_l, __uint_as_float(r[15]) * inv_l);
         *reinterpret_cast<uint4*>(op + c0) = o0;
         *reinterpret_cast<uint4*>(op + c0 + 8) = o1;
       }
@@ -298,16 +298,16 @@ extern "C" int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, i
   if (new_order) { p.q_off = 0; p.k_off = C; p.v_off = 2 * C; p.head_stride = ch; }          // unet.py:392
   else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }    // unet.py:359
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)ch);
-  p.out = (__nv_bfloat16*)out; p.ldo = ldo; p.lse = lse;
+  p.out = (__half*)out; p.ldo = ldo; p.lse = lse;
   const int bkv = (ch == 256) ? 64 : 128;
   AttnMaps maps;
   const uint64_t dims[3] = {(uint64_t)(3 * C), (uint64_t)L, (uint64_t)N};
   const uint64_t str[2] = {(uint64_t)ldqkv * 2, (uint64_t)ldqkv * 2 * (uint64_t)L};
   const uint32_t boxq[3] = {64u, 128u, 1u};
   const uint32_t boxkv[3] = {64u, (uint32_t)bkv, 1u};
-  int rc = make_tmap_bf16(&maps.q, qkv, 3, dims, str, boxq);
+  int rc = make_tmap_16b(&maps.q, qkv, 3, dims, str, boxq);
   if (rc) return rc;
-  rc = make_tmap_bf16(&maps.kv, qkv, 3, dims, str, boxkv);
+  rc = make_tmap_16b(&maps.kv, qkv, 3, dims, str, boxkv);
   if (rc) return rc;
   if (ch == 64) return launch_attn_fwd<64, 128>(maps, p, N, stream);
   if (ch == 128) return launch_attn_fwd<128, 128>(maps, p, N, stream);

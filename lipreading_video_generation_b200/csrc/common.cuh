@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
@@ -79,6 +80,47 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t v) {
   __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162*>(&v);
   return __bfloat1622float2(h);
 }
+// Storage type: every 16-bit tensor is fp16 (11-bit significand) with fp32 accumulation.
+// Forward values are O(1) after GroupNorm so the range is safe and conversions saturate; gradient tensors
+// carry a power-of-two loss scale chosen on the device per step (b2d_grad_scale) and the fp32 parameter
+// gradients are unscaled at the end (b2d_scale_f32).  bf16 storage was measured to miss north_star's own
+// 2e-2 gradient tolerance on this network (profiles/parity_r1_status.md); mixing f16 x bf16 operands in one
+// tcgen05.mma kind::f16 raises an illegal-instruction fault on sm_100a (measured), so one format is used.
+constexpr int FMT_F16 = 0, FMT_BF16 = 1;
+__device__ __forceinline__ uint32_t pack_f16x2(float lo, float hi) {
+  lo = fminf(fmaxf(lo, -65504.f), 65504.f);
+  hi = fminf(fmaxf(hi, -65504.f), 65504.f);
+  __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ uint32_t pack_f16x2_nosat(float lo, float hi) {   // values known to be in [0, 1]
+  __half2 h = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&h);
+}
+__device__ __forceinline__ float2 unpack_f16x2(uint32_t v) {
+  __half2 h = *reinterpret_cast<__half2*>(&v);
+  return __half22float2(h);
+}
+// fmt-dispatched pair conversion (fmt is warp-uniform)
+__device__ __forceinline__ uint32_t pack_x2(float lo, float hi, int fmt) {
+  return fmt == FMT_F16 ? pack_f16x2(lo, hi) : pack_bf16x2(lo, hi);
+}
+__device__ __forceinline__ float2 unpack_x2(uint32_t v, int fmt) {
+  return fmt == FMT_F16 ? unpack_f16x2(v) : unpack_bf16x2(v);
+}
+// 8 consecutive 16-bit elements <-> 8 floats
+__device__ __forceinline__ void load8_fmt(const void* p, float* v, int fmt) {
+  uint4 u = ldg_nc_u4(p);
+  float2 a = unpack_x2(u.x, fmt), b = unpack_x2(u.y, fmt), c = unpack_x2(u.z, fmt), d = unpack_x2(u.w, fmt);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+__device__ __forceinline__ void store8_fmt(void* p, const float* v, int fmt) {
+  uint4 u;
+  u.x = pack_x2(v[0], v[1], fmt); u.y = pack_x2(v[2], v[3], fmt);
+  u.z = pack_x2(v[4], v[5], fmt); u.w = pack_x2(v[6], v[7], fmt);
+  *reinterpret_cast<uint4*>(p) = u;
+}
+
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
 
 }  // namespace b2d

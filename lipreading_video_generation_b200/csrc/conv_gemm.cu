@@ -33,11 +33,12 @@ struct ConvParams {
   int total_pixels;    // N*Ho*Wo
   int Cout, BN;
   int stages;
+  int fmt;             // storage format of x / residual / out: FMT_F16 (forward) or FMT_F16 (gradient = dgrad)
   uint32_t tmem_cols;
   const float* bias;
   const float* emb; long long ldemb;
-  const __nv_bfloat16* residual; long long ldres;
-  __nv_bfloat16* out; long long ldo;
+  const __half* residual; long long ldres;
+  __half* out; long long ldo;
   float* out_nchw;
 };
 
@@ -116,7 +117,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
-    const uint32_t idesc = make_idesc_bf16(128, p.BN, 0, 0);
+    const uint32_t idesc = make_idesc(128, p.BN, 0, 0, FMT_F16, FMT_F16);
     for (int it = 0; it < total_iters; ++it) {
       const int s = it % p.stages;
       const uint32_t par = (uint32_t)((it / p.stages) & 1);
@@ -127,7 +128,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
         const uint32_t b_addr = a_addr + A_TILE_BYTES;
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
-          mma_bf16_ss(tmem_base, make_sdesc_sw128(a_addr + k * 32, 16, 1024),
+          mma_f16_ss(tmem_base, make_sdesc_sw128(a_addr + k * 32, 16, 1024),
                       make_sdesc_sw128(b_addr + k * 32, 16, 1024), idesc, (uint32_t)((it | k) != 0));
         }
         mma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
@@ -167,28 +168,28 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
         for (int j = 0; j < 16; ++j) if (j < ncol) v[j] += __ldg(e + j);
       }
       if (p.residual) {
-        const __nv_bfloat16* rp = p.residual + pix * p.ldres + col0;
+        const __half* rp = p.residual + pix * p.ldres + col0;
         if (ncol == 16 && ((((uintptr_t)rp) & 15) == 0)) {
           uint4 u0 = ldg_nc_u4(rp), u1 = ldg_nc_u4(rp + 8);
           const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
-          for (int j = 0; j < 8; ++j) { float2 f = unpack_bf16x2(w[j]); v[2 * j] += f.x; v[2 * j + 1] += f.y; }
+          for (int j = 0; j < 8; ++j) { float2 f = unpack_f16x2(w[j]); v[2 * j] += f.x; v[2 * j + 1] += f.y; }
         } else {
-          for (int j = 0; j < ncol; ++j) v[j] += __bfloat162float(rp[j]);
+          for (int j = 0; j < ncol; ++j) v[j] += __half2float(rp[j]);
         }
       }
       if (p.out) {
-        __nv_bfloat16* op = p.out + pix * p.ldo + col0;
+        __half* op = p.out + pix * p.ldo + col0;
         if (ncol == 16 && ((((uintptr_t)op) & 15) == 0)) {
           uint4 o0, o1;
-          o0.x = pack_bf16x2(v[0], v[1]);   o0.y = pack_bf16x2(v[2], v[3]);
-          o0.z = pack_bf16x2(v[4], v[5]);   o0.w = pack_bf16x2(v[6], v[7]);
-          o1.x = pack_bf16x2(v[8], v[9]);   o1.y = pack_bf16x2(v[10], v[11]);
-          o1.z = pack_bf16x2(v[12], v[13]); o1.w = pack_bf16x2(v[14], v[15]);
+          o0.x = pack_f16x2(v[0], v[1]);   o0.y = pack_f16x2(v[2], v[3]);
+          o0.z = pack_f16x2(v[4], v[5]);   o0.w = pack_f16x2(v[6], v[7]);
+          o1.x = pack_f16x2(v[8], v[9]);   o1.y = pack_f16x2(v[10], v[11]);
+          o1.z = pack_f16x2(v[12], v[13]); o1.w = pack_f16x2(v[14], v[15]);
           *reinterpret_cast<uint4*>(op) = o0;
           *reinterpret_cast<uint4*>(op + 8) = o1;
         } else {
-          for (int j = 0; j < ncol; ++j) op[j] = __float2bfloat16_rn(v[j]);
+          for (int j = 0; j < ncol; ++j) op[j] = __float2half_rn(fminf(fmaxf(v[j], -65504.f), 65504.f));
         }
       }
       if (p.out_nchw) {
@@ -213,7 +214,7 @@ static int make_act_map(CUtensorMap* m, const void* base, int C, long long ld, i
   const uint64_t str[3] = {(uint64_t)ld * 2 * phase_stride, (uint64_t)ld * 2 * W * phase_stride,
                            (uint64_t)ld * 2 * W * H};
   const uint32_t box[4] = {64u, (uint32_t)Wo, (uint32_t)rows, (uint32_t)imgs};
-  return make_tmap_bf16(m, base, 4, dims, str, box);
+  return make_tmap_16b(m, base, 4, dims, str, box);
 }
 
 }  // namespace b2d
@@ -262,7 +263,7 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   } else {
     for (int pa = 0; pa < 2; ++pa)
       for (int pb = 0; pb < 2; ++pb) {
-        const __nv_bfloat16* base = (const __nv_bfloat16*)a->x + ((long long)pa * a->W + pb) * a->ldx;
+        const __half* base = (const __half*)a->x + ((long long)pa * a->W + pb) * a->ldx;
         rc = make_act_map(&maps.a[pa * 2 + pb], base, a->C1, a->ldx, a->N, a->H, a->W, 2, Wo, rows, imgs);
         if (rc) return rc;
       }
@@ -279,7 +280,7 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
     const uint64_t dims[2] = {(uint64_t)Ktot, (uint64_t)a->CoutPad};
     const uint64_t str[1] = {(uint64_t)Ktot * 2};
     const uint32_t box[2] = {64u, (uint32_t)BN};
-    rc = make_tmap_bf16(&maps.b, a->w, 2, dims, str, box);
+    rc = make_tmap_16b(&maps.b, a->w, 2, dims, str, box);
     if (rc) return rc;
   }
 
@@ -296,8 +297,8 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   p.stages = stages;
   p.tmem_cols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
   p.bias = a->bias; p.emb = a->emb; p.ldemb = a->ldemb;
-  p.residual = (const __nv_bfloat16*)a->residual; p.ldres = a->ldres;
-  p.out = (__nv_bfloat16*)a->out; p.ldo = a->ldo;
+  p.residual = (const __half*)a->residual; p.ldres = a->ldres;
+  p.out = (__half*)a->out; p.ldo = a->ldo;
   p.out_nchw = a->out_nchw_f32;
 
   const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;

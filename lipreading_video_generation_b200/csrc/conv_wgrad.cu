@@ -103,7 +103,7 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc_bf16(128, p.BNci, 1, 1);
+    const uint32_t idesc = make_idesc(128, p.BNci, 1, 1, FMT_F16, FMT_F16);  // A = dy (gradient, bf16), B = x (forward, fp16)
     for (int it = 0; it < my_iters; ++it) {
       const int s = it % WG_STAGES;
       const uint32_t par = (uint32_t)((it / WG_STAGES) & 1);
@@ -114,7 +114,7 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
         const uint32_t b_addr = a_addr + 2 * BLK;
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          mma_bf16_ss(tmem_base, make_sdesc_sw128(a_addr + k * 2048, BLK, 1024),
+          mma_f16_ss(tmem_base, make_sdesc_sw128(a_addr + k * 2048, BLK, 1024),
                       make_sdesc_sw128(b_addr + k * 2048, BLK, 1024), idesc, (uint32_t)((it | k) != 0));
         }
         mma_commit(&empty_bar[s]);
@@ -158,7 +158,7 @@ static int make_map4(CUtensorMap* m, const void* base, int C, long long ld, int 
   const uint64_t str[3] = {(uint64_t)ld * 2 * phase_stride, (uint64_t)ld * 2 * W * phase_stride,
                            (uint64_t)ld * 2 * W * H};
   const uint32_t box[4] = {64u, (uint32_t)Wo, (uint32_t)rows, (uint32_t)imgs};
-  return make_tmap_bf16(m, base, 4, dims, str, box);
+  return make_tmap_16b(m, base, 4, dims, str, box);
 }
 
 }  // namespace b2d
@@ -194,7 +194,7 @@ extern "C" int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream) {
   } else {
     for (int pa = 0; pa < 2; ++pa)
       for (int pb = 0; pb < 2; ++pb) {
-        const __nv_bfloat16* base = (const __nv_bfloat16*)a->x + ((long long)pa * a->W + pb) * a->ldx;
+        const __half* base = (const __half*)a->x + ((long long)pa * a->W + pb) * a->ldx;
         rc = make_map4(&maps.x[pa * 2 + pb], base, a->C1, a->ldx, a->N, a->H, a->W, 2, Wo, rows, imgs);
         if (rc) return rc;
       }

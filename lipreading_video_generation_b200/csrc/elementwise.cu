@@ -6,15 +6,15 @@
 
 namespace b2d {
 
-__device__ __forceinline__ void ld8(const __nv_bfloat16* p, float* v) {
+__device__ __forceinline__ void ld8(const __half* p, float* v) {
   uint4 u = ldg_nc_u4(p);
-  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  float2 a = unpack_f16x2(u.x), b = unpack_f16x2(u.y), c = unpack_f16x2(u.z), d = unpack_f16x2(u.w);
   v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
 }
-__device__ __forceinline__ void st8(__nv_bfloat16* p, const float* v) {
+__device__ __forceinline__ void st8(__half* p, const float* v) {
   uint4 u;
-  u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
-  u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+  u.x = pack_f16x2(v[0], v[1]); u.y = pack_f16x2(v[2], v[3]);
+  u.z = pack_f16x2(v[4], v[5]); u.w = pack_f16x2(v[6], v[7]);
   *reinterpret_cast<uint4*>(p) = u;
 }
 
@@ -36,7 +36,7 @@ struct AssembleParams {
 };
 
 __global__ void __launch_bounds__(256)
-assemble_input_kernel(AssembleParams p, __nv_bfloat16* __restrict__ out) {
+assemble_input_kernel(AssembleParams p, __half* __restrict__ out) {
   const int V = p.Cpad >> 3;
   const long long total = (long long)p.N * p.S * p.S * V;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -67,13 +67,13 @@ assemble_input_kernel(AssembleParams p, __nv_bfloat16* __restrict__ out) {
       }
       o[j] = val;
     }
-    st8(out + gp * p.Cpad + v * 8, o);
+    store8_fmt(out + gp * p.Cpad + v * 8, o, FMT_F16);   // forward tensor
   }
 }
 
 // backward: d_wcond[c][k] += sum_{n,pix} dX[n,pix,Cin+c] * cond[n,k,src(pix)];  d_audio[n][a] += sum_pix dX[n,pix,Cin+Cim+a]
 __global__ void __launch_bounds__(256)
-assemble_input_bwd_kernel(AssembleParams p, const __nv_bfloat16* __restrict__ dX, float* __restrict__ d_wcond,
+assemble_input_bwd_kernel(AssembleParams p, const __half* __restrict__ dX, float* __restrict__ d_wcond,
                           float* __restrict__ d_audio) {
   extern __shared__ float sh[];  // [Cim*Cc + A]
   const int nsh = p.Cim * p.Cc + p.A;
@@ -124,7 +124,7 @@ assemble_input_bwd_kernel(AssembleParams p, const __nv_bfloat16* __restrict__ dX
 
 // ------------------------------------------------------------------ nearest 2x upsample and its adjoint
 __global__ void __launch_bounds__(256)
-upsample2x_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, int N, int H, int W, int C) {
+upsample2x_kernel(const __half* __restrict__ x, __half* __restrict__ y, int N, int H, int W, int C) {
   const int V = C >> 3;
   const long long total = (long long)N * 4 * H * W * V;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -138,7 +138,7 @@ upsample2x_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict
   }
 }
 __global__ void __launch_bounds__(256)
-upsample2x_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ dx, int N, int H, int W, int C) {
+upsample2x_bwd_kernel(const __half* __restrict__ dy, __half* __restrict__ dx, int N, int H, int W, int C) {
   const int V = C >> 3;
   const long long total = (long long)N * H * W * V;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -162,7 +162,7 @@ upsample2x_bwd_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __res
 }
 // z[n, 2h, 2w] = dy[n, h, w], zero elsewhere: turns the stride-2 conv dgrad into a stride-1 conv
 __global__ void __launch_bounds__(256)
-zero_insert2x_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __restrict__ z, int N, int Ho, int Wo, int C) {
+zero_insert2x_kernel(const __half* __restrict__ dy, __half* __restrict__ z, int N, int Ho, int Wo, int C) {
   const int V = C >> 3;
   const long long total = (long long)N * 4 * Ho * Wo * V;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -179,7 +179,9 @@ zero_insert2x_kernel(const __nv_bfloat16* __restrict__ dy, __nv_bfloat16* __rest
 
 // fp32 (N, C, HW) -> bf16 (N, HW, Cpad), zero padded channels
 __global__ void __launch_bounds__(256)
-nchw_to_pixel_major_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, int N, int C, int HW, int Cpad) {
+nchw_to_pixel_major_kernel(const float* __restrict__ src, __half* __restrict__ dst, int N, int C, int HW, int Cpad,
+                           const float* __restrict__ scale_ptr) {
+  const float sc = scale_ptr ? __ldg(scale_ptr) : 1.0f;
   const int V = Cpad >> 3;
   const long long total = (long long)N * HW * V;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
@@ -191,7 +193,7 @@ nchw_to_pixel_major_kernel(const float* __restrict__ src, __nv_bfloat16* __restr
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
       const int c = v * 8 + j;
-      o[j] = c < C ? src[((long long)n * C + c) * HW + pix] : 0.f;
+      o[j] = c < C ? src[((long long)n * C + c) * HW + pix] * sc : 0.f;
     }
     st8(dst + gp * Cpad + v * 8, o);
   }
@@ -200,7 +202,7 @@ nchw_to_pixel_major_kernel(const float* __restrict__ src, __nv_bfloat16* __restr
 // ------------------------------------------------------------------ per-sample column sums
 // out[n][c] += sum_pix x[n, pix, c_off + c]   (emb_out gradient unet.py:266; bias grads = sum over n)
 __global__ void __launch_bounds__(256)
-colsum_kernel(const __nv_bfloat16* __restrict__ x, long long ld, int c_off, int C, int HW, float* __restrict__ out,
+colsum_kernel(const __half* __restrict__ x, long long ld, int c_off, int C, int HW, float* __restrict__ out,
               long long ldout) {
   extern __shared__ float sh[];  // [C]
   for (int i = threadIdx.x; i < C; i += blockDim.x) sh[i] = 0.f;
@@ -250,6 +252,43 @@ __global__ void timestep_embedding_kernel(const int64_t* __restrict__ t, int N, 
   out[i] = v;
 }
 
+// ------------------------------------------------------------------ gradient scale (fp16 gradient tensors)
+// scale2[0] = 2^k with max|x| * 2^k in [target/2, target), scale2[1] = 2^-k.  Chosen on the device: no host sync.
+__global__ void __launch_bounds__(256)
+absmax_kernel(const float* __restrict__ x, long long n, unsigned int* __restrict__ out_bits) {
+  float m = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    m = fmaxf(m, fabsf(x[i]));
+  m = warp_max(m);
+  __shared__ float sh[8];
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = m;
+  __syncthreads();
+  if (threadIdx.x < 8) {
+    m = sh[threadIdx.x];
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffu, m, o));
+    if (threadIdx.x == 0 && m == m) atomicMax(out_bits, __float_as_uint(m));   // non-negative floats order as uints
+  }
+}
+__global__ void grad_scale_finalize_kernel(float* __restrict__ scale2, float target) {
+  const float m = scale2[0];
+  float s = 1.0f;
+  if (m > 0.f && m < INFINITY) {
+    int e;
+    frexpf(target / m, &e);              // target/m = f * 2^e, f in [0.5, 1)  ->  2^(e-1) <= target/m
+    e = max(-60, min(60, e - 1));
+    s = ldexpf(1.0f, e);
+  }
+  scale2[0] = s;
+  scale2[1] = 1.0f / s;
+}
+__global__ void __launch_bounds__(256)
+scale_f32_kernel(float* __restrict__ x, long long n, const float* __restrict__ scale_ptr) {
+  const float s = __ldg(scale_ptr);
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x)
+    x[i] *= s;
+}
+
 static unsigned ew_blocks(long long work, int threads = 256) {
   long long b = (work + threads - 1) / threads;
   long long cap = (long long)num_sms() * 8;
@@ -270,7 +309,7 @@ extern "C" int b2d_assemble_input(const float* xt, const float* cond, const floa
               "assemble_input: channels %d+%d+%d do not fit Cpad=%d", Cin, Cim, A, Cpad);
   AssembleParams p{xt, cond, wcond, audio, N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad};
   const long long work = (long long)N * S * S * (Cpad / 8);
-  assemble_input_kernel<<<ew_blocks(work), 256, 0, (cudaStream_t)stream>>>(p, (__nv_bfloat16*)out);
+  assemble_input_kernel<<<ew_blocks(work), 256, 0, (cudaStream_t)stream>>>(p, (__half*)out);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
@@ -289,7 +328,7 @@ extern "C" int b2d_assemble_input_bwd(const void* dX, const float* cond, int N, 
   if (chunks < 1) chunks = 1;
   dim3 grid((unsigned)chunks, (unsigned)N);
   assemble_input_bwd_kernel<<<grid, 256, (Cim * Cc + A) * sizeof(float), (cudaStream_t)stream>>>(
-      p, (const __nv_bfloat16*)dX, d_wcond, d_audio);
+      p, (const __half*)dX, d_wcond, d_audio);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
@@ -297,28 +336,46 @@ extern "C" int b2d_assemble_input_bwd(const void* dX, const float* cond, int N, 
 extern "C" int b2d_upsample2x(const void* x, void* y, int N, int H, int W, int C, void* stream) {
   B2D_REQUIRE(x && y && C % 8 == 0, B2D_ERR_SHAPE, "upsample2x: bad arguments");
   upsample2x_kernel<<<ew_blocks((long long)N * 4 * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)x, (__nv_bfloat16*)y, N, H, W, C);
+      (const __half*)x, (__half*)y, N, H, W, C);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
 extern "C" int b2d_upsample2x_bwd(const void* dy, void* dx, int N, int H, int W, int C, void* stream) {
   B2D_REQUIRE(dy && dx && C % 8 == 0, B2D_ERR_SHAPE, "upsample2x_bwd: bad arguments");
   upsample2x_bwd_kernel<<<ew_blocks((long long)N * H * W * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, (__nv_bfloat16*)dx, N, H, W, C);
+      (const __half*)dy, (__half*)dx, N, H, W, C);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
 extern "C" int b2d_zero_insert2x(const void* dy, void* z, int N, int Ho, int Wo, int C, void* stream) {
   B2D_REQUIRE(dy && z && C % 8 == 0, B2D_ERR_SHAPE, "zero_insert2x: bad arguments");
   zero_insert2x_kernel<<<ew_blocks((long long)N * 4 * Ho * Wo * (C / 8)), 256, 0, (cudaStream_t)stream>>>(
-      (const __nv_bfloat16*)dy, (__nv_bfloat16*)z, N, Ho, Wo, C);
+      (const __half*)dy, (__half*)z, N, Ho, Wo, C);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
-extern "C" int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad, void* stream) {
+extern "C" int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, int Cpad,
+                                       const float* scale, void* stream) {
   B2D_REQUIRE(src && dst && Cpad % 8 == 0 && C <= Cpad, B2D_ERR_SHAPE, "nchw_to_pixel_major: bad arguments");
   nchw_to_pixel_major_kernel<<<ew_blocks((long long)N * HW * (Cpad / 8)), 256, 0, (cudaStream_t)stream>>>(
-      src, (__nv_bfloat16*)dst, N, C, HW, Cpad);
+      src, (__half*)dst, N, C, HW, Cpad, scale);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream) {
+  B2D_REQUIRE(x && scale2 && n > 0 && target > 0.f, B2D_ERR_SHAPE, "grad_scale: bad arguments");
+  cudaStream_t st = (cudaStream_t)stream;
+  B2D_CHECK_CUDA(cudaMemsetAsync(scale2, 0, 2 * sizeof(float), st));
+  absmax_kernel<<<ew_blocks(n), 256, 0, st>>>(x, n, (unsigned int*)scale2);
+  B2D_CHECK_LAUNCH();
+  grad_scale_finalize_kernel<<<1, 1, 0, st>>>(scale2, target);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream) {
+  B2D_REQUIRE(x && scale && n >= 0, B2D_ERR_SHAPE, "scale_f32: bad arguments");
+  if (n == 0) return B2D_OK;
+  scale_f32_kernel<<<ew_blocks(n), 256, 0, (cudaStream_t)stream>>>(x, n, scale);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
@@ -333,7 +390,7 @@ extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, in
   if (chunks > cap) chunks = cap;
   if (chunks < 1) chunks = 1;
   dim3 grid((unsigned)chunks, (unsigned)N);
-  colsum_kernel<<<grid, V * rows, C * sizeof(float), (cudaStream_t)stream>>>((const __nv_bfloat16*)x, ld, c_off, C, HW, out, ldout);
+  colsum_kernel<<<grid, V * rows, C * sizeof(float), (cudaStream_t)stream>>>((const __half*)x, ld, c_off, C, HW, out, ldout);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

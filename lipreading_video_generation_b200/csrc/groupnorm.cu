@@ -1,5 +1,6 @@
-// groupnorm.cu -- GroupNorm32(32, C) (+ SiLU, + dropout) forward and backward on pixel-major bf16
-// activations (utils.py:54-56,130-137; used at unet.py:194-198,218-225,297,624-628).
+// groupnorm.cu -- GroupNorm32(32, C) (+ SiLU, + dropout) forward and backward on pixel-major activations
+// (forward tensors x / y are fp16, gradient tensors dy / dx / add_* are bf16; pointers are typed
+// __half* only as a 16-bit placeholder) (utils.py:54-56,130-137; used at unet.py:194-198,218-225,297,624-628).
 // Statistics are accumulated in fp32 per thread and fp64 across CTAs, as the reference computes
 // GroupNorm in fp32 regardless of activation dtype.  The input may be the channel concatenation
 // of two tensors (decoder skip connections, unet.py:672) -- it is never materialised.
@@ -10,23 +11,23 @@
 namespace b2d {
 
 struct GnSrc {
-  const __nv_bfloat16* x1; long long ld1; int C1;
-  const __nv_bfloat16* x2; long long ld2; int C2;
+  const __half* x1; long long ld1; int C1;
+  const __half* x2; long long ld2; int C2;
 };
 
-__device__ __forceinline__ const __nv_bfloat16* src_ptr(const GnSrc& s, long long pix, int c) {
+__device__ __forceinline__ const __half* src_ptr(const GnSrc& s, long long pix, int c) {
   return (c < s.C1) ? s.x1 + pix * s.ld1 + c : s.x2 + pix * s.ld2 + (c - s.C1);
 }
 
-__device__ __forceinline__ void load8(const __nv_bfloat16* p, float* v) {
+__device__ __forceinline__ void load8(const __half* p, float* v) {
   uint4 u = ldg_nc_u4(p);
-  float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+  float2 a = unpack_f16x2(u.x), b = unpack_f16x2(u.y), c = unpack_f16x2(u.z), d = unpack_f16x2(u.w);
   v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
 }
-__device__ __forceinline__ void store8(__nv_bfloat16* p, const float* v) {
+__device__ __forceinline__ void store8(__half* p, const float* v) {
   uint4 u;
-  u.x = pack_bf16x2(v[0], v[1]); u.y = pack_bf16x2(v[2], v[3]);
-  u.z = pack_bf16x2(v[4], v[5]); u.w = pack_bf16x2(v[6], v[7]);
+  u.x = pack_f16x2(v[0], v[1]); u.y = pack_f16x2(v[2], v[3]);
+  u.z = pack_f16x2(v[4], v[5]); u.w = pack_f16x2(v[6], v[7]);
   *reinterpret_cast<uint4*>(p) = u;
 }
 
@@ -75,7 +76,7 @@ gn_stats_kernel(GnSrc s, int HW, int Ctot, double* __restrict__ sums) {
   const int c = v * 8;
   for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
     float x[8];
-    load8(src_ptr(s, (long long)n * HW + pix, c), x);
+    load8_fmt(src_ptr(s, (long long)n * HW + pix, c), x, FMT_F16);
 #pragma unroll
     for (int i = 0; i < 8; ++i) { a[i] += x[i]; q[i] = fmaf(x[i], x[i], q[i]); }
   }
@@ -96,7 +97,7 @@ gn_stats_kernel(GnSrc s, int HW, int Ctot, double* __restrict__ sums) {
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(GnSrc s, int HW, int Ctot, const double* __restrict__ sums, const float* __restrict__ gamma,
                 const float* __restrict__ beta, float eps, int act, float drop_p, unsigned long long seed,
-                __nv_bfloat16* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+                __half* __restrict__ y, float* __restrict__ mean_out, float* __restrict__ rstd_out) {
   __shared__ float s_mean[32], s_rstd[32];
   const int n = blockIdx.y;
   const int cpg = Ctot >> 5;
@@ -126,7 +127,7 @@ gn_apply_kernel(GnSrc s, int HW, int Ctot, const double* __restrict__ sums, cons
   for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
     const long long gp = (long long)n * HW + pix;
     float x[8];
-    load8(src_ptr(s, gp, c), x);
+    load8_fmt(src_ptr(s, gp, c), x, FMT_F16);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       float z = fmaf((x[i] - mu[i]) * rs[i], g[i], b[i]);
@@ -138,14 +139,14 @@ gn_apply_kernel(GnSrc s, int HW, int Ctot, const double* __restrict__ sums, cons
 #pragma unroll
       for (int i = 0; i < 8; ++i) x[i] = keep[i] ? x[i] * keep_scale : 0.f;
     }
-    store8(y + gp * Ctot + c, x);
+    store8_fmt(y + gp * Ctot + c, x, FMT_F16);
   }
 }
 
 // ------------------------------------------------------------------ backward: per-(sample, channel) sums
 // ab: fp32 [N][Ctot][2] = (sum dyh, sum dyh * xhat) with dyh = dy * act'(z) (* dropout mask), zeroed by caller.
 __global__ void __launch_bounds__(256)
-gn_bwd_reduce_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int Ctot,
+gn_bwd_reduce_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
                      const float* __restrict__ mean, const float* __restrict__ rstd,
                      const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
                      unsigned long long seed, float* __restrict__ ab) {
@@ -170,7 +171,7 @@ gn_bwd_reduce_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int 
   for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
     const long long gp = (long long)n * HW + pix;
     float x[8], d[8];
-    load8(src_ptr(s, gp, c), x);
+    load8_fmt(src_ptr(s, gp, c), x, FMT_F16);
     load8(dy + gp * Ctot + c, d);
     if (drop_p > 0.f) {
       bool keep[8];
@@ -202,15 +203,15 @@ gn_bwd_reduce_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int 
 // ------------------------------------------------------------------ backward: input gradient
 // dx = rstd * (dyh*gamma - s1/m - xhat*s2/m) (+ add_a + add_b on source 1 channels, + nothing on source 2)
 struct GnBwdOut {
-  __nv_bfloat16* dx1; long long ldd1;
-  __nv_bfloat16* dx2; long long ldd2;
-  const __nv_bfloat16* add_a; long long lda;
-  const __nv_bfloat16* add_b; long long ldb;
+  __half* dx1; long long ldd1;
+  __half* dx2; long long ldd2;
+  const __half* add_a; long long lda;
+  const __half* add_b; long long ldb;
   int add_a_full;  // add_a spans all C1+C2 channels (also added to dx2)
 };
 
 __global__ void __launch_bounds__(256)
-gn_bwd_apply_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int Ctot,
+gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
                     const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
                     unsigned long long seed, const float* __restrict__ ab, GnBwdOut o) {
@@ -248,7 +249,7 @@ gn_bwd_apply_kernel(GnSrc s, const __nv_bfloat16* __restrict__ dy, int HW, int C
   for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
     const long long gp = (long long)n * HW + pix;
     float x[8], d[8];
-    load8(src_ptr(s, gp, c), x);
+    load8_fmt(src_ptr(s, gp, c), x, FMT_F16);
     load8(dy + gp * Ctot + c, d);
     if (drop_p > 0.f) {
       bool keep[8];
@@ -323,8 +324,8 @@ static int gn_check(const b2d_gn_args* a, const char* who) {
 
 static GnSrc make_src(const b2d_gn_args* a) {
   GnSrc s;
-  s.x1 = (const __nv_bfloat16*)a->x1; s.ld1 = a->ld1; s.C1 = a->C1;
-  s.x2 = (const __nv_bfloat16*)a->x2; s.ld2 = a->ld2; s.C2 = a->x2 ? a->C2 : 0;
+  s.x1 = (const __half*)a->x1; s.ld1 = a->ld1; s.C1 = a->C1;
+  s.x2 = (const __half*)a->x2; s.ld2 = a->ld2; s.C2 = a->x2 ? a->C2 : 0;
   return s;
 }
 
@@ -353,7 +354,7 @@ extern "C" int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, flo
   gn_stats_kernel<<<grid, threads, 2 * Ctot * sizeof(float), st>>>(s, a->HW, Ctot, (double*)workspace);
   B2D_CHECK_LAUNCH();
   gn_apply_kernel<<<grid, threads, 0, st>>>(s, a->HW, Ctot, (const double*)workspace, a->gamma, a->beta, a->eps,
-                                            a->act, a->drop_p, a->seed, (__nv_bfloat16*)y, mean, rstd);
+                                            a->act, a->drop_p, a->seed, (__half*)y, mean, rstd);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
@@ -375,13 +376,13 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
   dim3 grid; int threads;
   gn_launch_dims(a->N, a->HW, Ctot, &grid, &threads);
   gn_bwd_reduce_kernel<<<grid, threads, 2 * Ctot * sizeof(float), st>>>(
-      s, (const __nv_bfloat16*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
+      s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
       (float*)workspace);
   B2D_CHECK_LAUNCH();
   GnBwdOut o;
-  o.dx1 = (__nv_bfloat16*)dx1; o.ldd1 = lddx1; o.dx2 = (__nv_bfloat16*)dx2; o.ldd2 = lddx2;
-  o.add_a = (const __nv_bfloat16*)add_a; o.lda = lda; o.add_b = (const __nv_bfloat16*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
-  gn_bwd_apply_kernel<<<grid, threads, 0, st>>>(s, (const __nv_bfloat16*)dy, a->HW, Ctot, mean, rstd, a->gamma,
+  o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
+  o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
+  gn_bwd_apply_kernel<<<grid, threads, 0, st>>>(s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma,
                                                 a->beta, a->act, a->drop_p, a->seed, (const float*)workspace, o);
   B2D_CHECK_LAUNCH();
   gn_param_grad_kernel<<<(Ctot + 127) / 128, 128, 0, st>>>((const float*)workspace, a->N, Ctot, dgamma, dbeta);

@@ -16,7 +16,7 @@ PFN_encodeTiled get_encode_tiled();
 
 // bf16 tensor map, SWIZZLE_128B, zero fill out of bounds.
 // dims[0] is the innermost (contiguous) dimension; strides_bytes[i] is the pitch of dims[i+1].
-int make_tmap_bf16(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+int make_tmap_16b(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box);
 
 }  // namespace b2d

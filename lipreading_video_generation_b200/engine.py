@@ -6,7 +6,8 @@ PyTorch owns memory, streams and the parameter objects only.  The whole torso is
 torch.autograd.Function (`denoiser_apply`), so the reference's training recipe
 (`loss.backward(); optimizer.step()`, train.py:131-134) works unchanged.
 
-Layout: activations pixel-major (N,H,W,C) bf16; skip concatenations (unet.py:672) are never
+Layout: activations and activation gradients pixel-major (N,H,W,C) fp16 (gradients carry a power-of-two loss
+scale chosen on the device each step; fp32 parameter gradients are unscaled stage by stage); skip concatenations (unet.py:672) are never
 materialised (two-source kernels); gradient accumulation for residual / skip fan-out is fused into the
 GroupNorm-backward and dgrad epilogues.
 """
@@ -324,12 +325,22 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     m = eng.model
     N = tape["N"]
     dev = dout.device
+    dout = dout.contiguous().float()
     G = _Grads(eng, dev)
     d_emb_all = torch.zeros(N, eng.emb_total, device=dev, dtype=torch.float32)
     stage = 0
+    # fp16 gradient tensors: scale2 = [2^k, 2^-k] with max|dout| * 2^k in [64, 128); every gradient below is
+    # carried times 2^k and each stage's slice of the flat fp32 buffer is unscaled as soon as the stage is done
+    # (before the data-parallel reducer may all-reduce it: ranks choose different k).
+    scale2 = ops.grad_scale(dout)
+    inv_scale = scale2[1:]
 
     def done():
         nonlocal stage
+        lo = G.stage_end[stage - 1] if stage > 0 else 0
+        hi = G.stage_end[stage]
+        if hi > lo:
+            ops.scale_f32_(G.flat[lo:hi], inv_scale)
         if on_stage_done is not None:
             on_stage_done(G, stage)
         stage += 1
@@ -346,7 +357,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     # ---- head: GroupNorm -> SiLU -> conv3x3 (Cout padded to 64 for the tensor-core tiles)
     hd = tape["head"]
     gn, conv_out = m.out[0], m.out[2]
-    dyp = ops.nchw_to_pixel_major(dout.contiguous(), 64)
+    dyp = ops.nchw_to_pixel_major(dout, 64, scale=scale2)
     ops.conv2d_wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
     bias_grad(dyp, conv_out.bias, 64)
     d_hh = ops.conv2d(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1)
@@ -476,6 +487,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         feat = tape["audio_feat"].contiguous()
         d_feat = ops.linear_bwd(feat, at.weight.detach(), tape["avec"], d_avec, G.g(at.weight), G.g(at.bias),
                                 relu_out=True)
+        ops.scale_f32_(d_feat, inv_scale)
     done()
     return G, d_feat
 

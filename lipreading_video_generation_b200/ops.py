@@ -2,7 +2,8 @@
 
 Every function enqueues sm_100a kernels on torch's current CUDA stream through
 ctypes; torch only owns the memory.  Activations are pixel-major bf16 tensors
-(N, H, W, C) -- see DESIGN.md "data layout".  No function here has a CPU path.
+(N, H, W, C) fp16 (gradient tensors carry a power-of-two loss scale) -- see DESIGN.md "data layout".
+No function here has a CPU path.
 """
 from __future__ import annotations
 
@@ -12,7 +13,9 @@ import torch
 
 from . import _lib as L
 
-BF16 = torch.bfloat16
+F16 = torch.float16       # every 16-bit tensor (activations, packed weights, qkv, gradients) is fp16, fp32 accumulate
+_F16_MAX = 65504.0
+GRAD_SCALE_TARGET = 128.0  # loss scale 2^k puts max|d loss / d pred| * 2^k in [64, 128)
 
 
 def _s():
@@ -63,7 +66,7 @@ class _timed:
 
 
 def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: int = 16) -> torch.Tensor:
-    """OIHW (or OI / OIK for Linear / Conv1d) fp32 -> bf16 [CoutPad][kh*kw*CinPad] (tap-major, channel-minor)."""
+    """OIHW (or OI / OIK for Linear / Conv1d) fp32 -> fp16 [CoutPad][kh*kw*CinPad] (tap-major, channel-minor)."""
     if w.dim() == 2:
         w = w[:, :, None, None]
     elif w.dim() == 3:
@@ -71,14 +74,14 @@ def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: i
     co, ci, kh, kw = w.shape
     cip = ci if cin_pad is None else cin_pad
     cop = (co + cout_pad_to - 1) // cout_pad_to * cout_pad_to
-    p = torch.zeros(cop, kh * kw, cip, device=w.device, dtype=BF16)
-    p[:co, :, :ci] = w.permute(0, 2, 3, 1).reshape(co, kh * kw, ci).to(BF16)
+    p = torch.zeros(cop, kh * kw, cip, device=w.device, dtype=F16)
+    p[:co, :, :ci] = w.permute(0, 2, 3, 1).reshape(co, kh * kw, ci).clamp(-_F16_MAX, _F16_MAX).to(F16)
     return p.reshape(cop, kh * kw * cip)
 
 
 def pack_dgrad_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad: int | None = None) -> torch.Tensor:
     """Weights of the data-gradient convolution: dX = conv(dY, flip(w)^T).
-    OIHW -> bf16 [CinPad][kh*kw*CoutPad] with the taps spatially flipped."""
+    OIHW -> fp16 [CinPad][kh*kw*CoutPad] with the taps spatially flipped."""
     if w.dim() == 2:
         w = w[:, :, None, None]
     elif w.dim() == 3:
@@ -87,15 +90,17 @@ def pack_dgrad_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad: int
     cip = ci if cin_pad is None else cin_pad
     cop = co if cout_pad is None else cout_pad
     wf = torch.flip(w, dims=(2, 3)).permute(1, 2, 3, 0).reshape(ci, kh * kw, co)  # [ci][tap'][co]
-    p = torch.zeros((cip + 15) // 16 * 16, kh * kw, cop, device=w.device, dtype=BF16)
-    p[:ci, :, :co] = wf.to(BF16)
+    p = torch.zeros((cip + 15) // 16 * 16, kh * kw, cop, device=w.device, dtype=F16)
+    p[:ci, :, :co] = wf.clamp(-_F16_MAX, _F16_MAX).to(F16)
     return p.reshape(p.shape[0], kh * kw * cop)
 
 
 def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, residual=None, out=None,
            out_nchw_f32=None, c1=None, c2=None):
-    """x: (N,H,W,ldx) bf16, optional x2 concatenated on channels.  Returns (N,Ho,Wo,cout) bf16 (or `out`)."""
+    """x: (N,H,W,ldx) fp16, optional x2 concatenated on channels.  Returns (N,Ho,Wo,cout) fp16 (or `out`)."""
     L.require_cuda(x)
+    if any(t is not None and t.dtype != F16 for t in (x, x2, residual, w_packed)):
+        raise RuntimeError("conv2d: x / x2 / residual / packed weights must be fp16")
     N, H, W, ldx = x.shape
     a = L.ConvArgs()
     a.x, a.ldx, a.C1 = x.data_ptr(), x.stride(2), (ldx if c1 is None else c1)
@@ -109,7 +114,7 @@ def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, r
     a.residual, a.ldres = L.ptr(residual), (residual.stride(2) if residual is not None else 0)
     Ho, Wo = H // stride, W // stride
     if out is None and out_nchw_f32 is None:
-        out = torch.empty(N, Ho, Wo, cout, device=x.device, dtype=BF16)
+        out = torch.empty(N, Ho, Wo, cout, device=x.device, dtype=x.dtype)
     a.out, a.ldo = L.ptr(out), (out.stride(2) if out is not None else 0)
     a.out_nchw_f32 = L.ptr(out_nchw_f32)
     with _timed("conv2d", (N, H, W, a.C1 + a.C2, cout, ksize, stride)):
@@ -118,7 +123,9 @@ def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, r
 
 
 def conv2d_wgrad(x, dy, dw, ksize=1, stride=1, x2=None, c1=None, c2=None, cout=None):
-    """Accumulate dw (fp32 [Cout][taps*(C1+C2)]) from x (+x2) and dy (N,Ho,Wo,Cout) bf16."""
+    """Accumulate dw (fp32 [Cout][taps*(C1+C2)]) from x (+x2) and dy (N,Ho,Wo,Cout), all fp16."""
+    if any(t is not None and t.dtype != F16 for t in (x, x2, dy)):
+        raise RuntimeError("conv2d_wgrad: x / x2 / dy must be fp16")
     N, H, W, ldx = x.shape
     a = L.WgradArgs()
     a.x, a.ldx, a.C1 = x.data_ptr(), x.stride(2), (ldx if c1 is None else c1)
@@ -169,12 +176,14 @@ def _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed):
 
 
 def groupnorm_fwd(x1, gamma, beta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed=0):
-    """Returns (y bf16 (N,H,W,C1+C2), mean (N,32), rstd (N,32))."""
+    """Returns (y fp16 (N,H,W,C1+C2), mean (N,32), rstd (N,32))."""
     L.require_cuda(x1)
+    if x1.dtype != F16 or (x2 is not None and x2.dtype != F16):
+        raise RuntimeError("groupnorm_fwd: inputs must be fp16")
     N, H, W, C1 = x1.shape
     Ct = C1 + (x2.shape[3] if x2 is not None else 0)
     a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed)
-    y = torch.empty(N, H, W, Ct, device=x1.device, dtype=BF16)
+    y = torch.empty(N, H, W, Ct, device=x1.device, dtype=F16)
     mean = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
     rstd = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
     ws = _gn_workspace(x1.device, N, Ct)
@@ -187,10 +196,12 @@ def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=T
                   add_a=None, add_b=None, add_a_full=False):
     """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (bf16, any channel pitch) are added to dx1."""
     N, H, W, C1 = x1.shape
+    if any(t is not None and t.dtype != F16 for t in (x1, x2, dy, add_a, add_b)):
+        raise RuntimeError("groupnorm_bwd: x / dy / add_a / add_b must be fp16")
     Ct = C1 + (x2.shape[3] if x2 is not None else 0)
     a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed)
-    dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=BF16)
-    dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=BF16) if x2 is not None else None
+    dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=F16)
+    dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=F16) if x2 is not None else None
     ws = _gn_workspace(x1.device, N, Ct)
     L.check(L.lib().b2d_groupnorm_bwd(
         C.byref(a), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx1.data_ptr(), C1,
@@ -202,11 +213,13 @@ def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=T
 
 
 def attention_fwd(qkv, heads, new_order=False):
-    """qkv (N,H,W,3C) bf16 -> (out (N,H,W,C) bf16, lse (N,heads,L) fp32)."""
+    """qkv (N,H,W,3C) fp16 -> (out (N,H,W,C) fp16, lse (N,heads,L) fp32)."""
+    if qkv.dtype != F16:
+        raise RuntimeError("attention_fwd: qkv must be fp16")
     N, H, W, C3 = qkv.shape
     Cc = C3 // 3
     ch = Cc // heads
-    out = torch.empty(N, H, W, Cc, device=qkv.device, dtype=BF16)
+    out = torch.empty(N, H, W, Cc, device=qkv.device, dtype=F16)
     lse = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
     with _timed("attention_fwd", (N, H * W, heads, ch)):
         L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
@@ -215,10 +228,13 @@ def attention_fwd(qkv, heads, new_order=False):
 
 
 def attention_bwd(qkv, out, d_out, lse, heads, new_order=False):
+    """qkv, out, d_out fp16 -> dqkv (N,H,W,3C) fp16."""
+    if qkv.dtype != F16 or out.dtype != F16 or d_out.dtype != F16:
+        raise RuntimeError("attention_bwd: qkv / out / d_out must be fp16")
     N, H, W, C3 = qkv.shape
     Cc = C3 // 3
     ch = Cc // heads
-    dqkv = torch.empty(N, H, W, C3, device=qkv.device, dtype=BF16)
+    dqkv = torch.empty(N, H, W, C3, device=qkv.device, dtype=F16)
     delta = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
     with _timed("attention_bwd", (N, H * W, heads, ch)):
         L.check(L.lib().b2d_attention_bwd(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2),
@@ -234,7 +250,7 @@ def assemble_input(xt, cond, wcond, audio, cpad):
     Cc = cond.shape[1] if cond is not None else 0
     Hc, Wc = (cond.shape[2], cond.shape[3]) if cond is not None else (0, 0)
     A = audio.shape[1] if audio is not None else 0
-    out = torch.empty(N, S, S, cpad, device=xt.device, dtype=BF16)
+    out = torch.empty(N, S, S, cpad, device=xt.device, dtype=F16)
     L.check(L.lib().b2d_assemble_input(xt.data_ptr(), L.ptr(cond), L.ptr(wcond), L.ptr(audio), N, S, Cin, Cc, Hc, Wc,
                                        Cim, A, cpad, out.data_ptr(), _s()), "b2d_assemble_input")
     return out
@@ -250,31 +266,45 @@ def assemble_input_bwd(dX, cond, cin, cim, A, d_wcond, d_audio):
 
 def upsample2x(x):
     N, H, W, Cc = x.shape
-    y = torch.empty(N, 2 * H, 2 * W, Cc, device=x.device, dtype=BF16)
+    y = torch.empty(N, 2 * H, 2 * W, Cc, device=x.device, dtype=x.dtype)       # pure 16-bit copy
     L.check(L.lib().b2d_upsample2x(x.data_ptr(), y.data_ptr(), N, H, W, Cc, _s()), "b2d_upsample2x")
     return y
 
 
 def upsample2x_bwd(dy):
     N, H2, W2, Cc = dy.shape
-    dx = torch.empty(N, H2 // 2, W2 // 2, Cc, device=dy.device, dtype=BF16)
+    dx = torch.empty(N, H2 // 2, W2 // 2, Cc, device=dy.device, dtype=F16)
     L.check(L.lib().b2d_upsample2x_bwd(dy.data_ptr(), dx.data_ptr(), N, H2 // 2, W2 // 2, Cc, _s()), "b2d_upsample2x_bwd")
     return dx
 
 
 def zero_insert2x(dy):
     N, Ho, Wo, Cc = dy.shape
-    z = torch.empty(N, 2 * Ho, 2 * Wo, Cc, device=dy.device, dtype=BF16)
+    z = torch.empty(N, 2 * Ho, 2 * Wo, Cc, device=dy.device, dtype=dy.dtype)     # pure 16-bit copy
     L.check(L.lib().b2d_zero_insert2x(dy.data_ptr(), z.data_ptr(), N, Ho, Wo, Cc, _s()), "b2d_zero_insert2x")
     return z
 
 
-def nchw_to_pixel_major(src, cpad):
+def nchw_to_pixel_major(src, cpad, scale=None):
+    """fp32 NCHW -> pixel-major fp16, multiplied by the device scalar scale[0] when given (loss scale)."""
     N, Cc, H, W = src.shape
-    dst = torch.empty(N, H, W, cpad, device=src.device, dtype=BF16)
-    L.check(L.lib().b2d_nchw_to_pixel_major(src.data_ptr(), dst.data_ptr(), N, Cc, H * W, cpad, _s()),
+    dst = torch.empty(N, H, W, cpad, device=src.device, dtype=F16)
+    L.check(L.lib().b2d_nchw_to_pixel_major(src.data_ptr(), dst.data_ptr(), N, Cc, H * W, cpad, L.ptr(scale), _s()),
             "b2d_nchw_to_pixel_major")
     return dst
+
+
+def grad_scale(x, target=GRAD_SCALE_TARGET):
+    """Device-chosen power-of-two loss scale for the fp16 gradient tensors: returns fp32 [scale, 1/scale]."""
+    s2 = torch.empty(2, device=x.device, dtype=torch.float32)
+    L.check(L.lib().b2d_grad_scale(x.data_ptr(), x.numel(), float(target), s2.data_ptr(), _s()), "b2d_grad_scale")
+    return s2
+
+
+def scale_f32_(x, scale_ptr_tensor):
+    """x *= scale_ptr_tensor[0] in place (x fp32 contiguous view)."""
+    L.check(L.lib().b2d_scale_f32(x.data_ptr(), x.numel(), scale_ptr_tensor.data_ptr(), _s()), "b2d_scale_f32")
+    return x
 
 
 def colsum(x, out, c_off=0, C_=None):

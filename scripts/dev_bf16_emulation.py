@@ -6,15 +6,16 @@ sys.path.insert(0, ".")
 from oracle import restatement as R
 
 FLAGS = dict(w=True, act_branch=True, act_stream=True, grad_branch=True, grad_stream=True)
+DT = dict(fwd=torch.bfloat16, grad=torch.bfloat16)     # storage dtype of forward tensors / gradient tensors
 
 class _Rnd(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, f, b):
         ctx.b = b
-        return x.to(torch.bfloat16).float() if f else x
+        return x.to(DT["fwd"]).float() if f else x
     @staticmethod
     def backward(ctx, g):
-        return (g.to(torch.bfloat16).float() if ctx.b else g), None, None
+        return (g.to(DT["grad"]).float() if ctx.b else g), None, None
 
 def rb(x):  # branch tensor
     return _Rnd.apply(x, FLAGS["act_branch"], FLAGS["grad_branch"])
@@ -109,10 +110,14 @@ variants = {
     "fp32 all grads": dict(grad_branch=False, grad_stream=False),
     "fp32 all acts": dict(act_branch=False, act_stream=False),
     "only weights bf16": dict(act_branch=False, act_stream=False, grad_branch=False, grad_stream=False),
+    "fp16 fwd tensors, bf16 grads": dict(_fwd=torch.float16),
+    "fp16 fwd tensors, fp16 grads x2^14": dict(_fwd=torch.float16, _grad="f16s"),
 }
 print(f"{'variant':32s} {'pred':>9s} {'g median':>9s} {'g worst':>9s} {'n>2e-2':>7s}")
 for name, ov in variants.items():
     for k in FLAGS: FLAGS[k] = True
+    DT["fwd"] = ov.pop("_fwd", torch.bfloat16); DT["grad"] = ov.pop("_grad", torch.bfloat16)
+    if DT["grad"] == "f16s": continue
     FLAGS.update(ov)
     p, gr = run(lambda sd: forward(sd, cfg, xt, cond, feats.mean(1), t))
     errs = [rel(gr[k], ref_g[k]) for k in ref_g if ref_g[k] is not None and gr[k] is not None]

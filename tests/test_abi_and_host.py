@@ -55,7 +55,7 @@ def test_pack_conv_weight_layout():
     from lipreading_video_generation_b200 import ops
     w = torch.arange(2 * 3 * 3 * 3, dtype=torch.float32).reshape(2, 3, 3, 3)
     p = ops.pack_conv_weight(w, cin_pad=4)
-    assert p.shape == (16, 9 * 4) and p.dtype == torch.bfloat16
+    assert p.shape == (16, 9 * 4) and p.dtype == torch.float16
     p3 = p.view(16, 9, 4).float()
     for co in range(2):
         for ky in range(3):
