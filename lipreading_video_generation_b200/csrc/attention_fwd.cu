@@ -9,6 +9,7 @@
 //
 // Warp roles (192 threads): warp 0 = TMA producer (Q once, K/V ring), warp 1 = MMA issuer,
 // warps 2..5 = softmax / O-rescale / epilogue.
+#include <stdlib.h>
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
@@ -281,6 +282,9 @@ static int launch_attn_fwd(const AttnMaps& maps, const AttnFwdParams& p, int N, 
   return B2D_OK;
 }
 
+int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order, void* out,
+                            int64_t ldo, float* lse, void* stream);   // attention_fwd2.cu
+
 }  // namespace b2d
 
 using namespace b2d;
@@ -292,6 +296,10 @@ extern "C" int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, i
   B2D_REQUIRE(ch == 64 || ch == 128 || ch == 256, B2D_ERR_SHAPE, "attention_fwd: head dim %d not in {64,128,256}", ch);
   B2D_REQUIRE(N <= 65535 && heads <= 65535, B2D_ERR_SHAPE, "attention_fwd: grid too large");
   B2D_REQUIRE(ldo % 8 == 0 && aligned16(out), B2D_ERR_ALIGN, "attention_fwd: output must be 16-byte aligned rows");
+  // two-query-tile kernel for the large layers; B2D_ATTN_FWD_V1=1 forces the single-tile variant (A/B timing)
+  static const bool force_v1 = getenv("B2D_ATTN_FWD_V1") != nullptr;
+  if (!force_v1 && (ch == 64 || ch == 128) && L > 128)
+    return attention_fwd2_dispatch(qkv, ldqkv, N, L, heads, ch, new_order, out, ldo, lse, stream);
   const int C = heads * ch;
   AttnFwdParams p;
   p.L = L; p.heads = heads;

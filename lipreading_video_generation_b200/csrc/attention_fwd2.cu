@@ -1,0 +1,326 @@
+// attention_fwd2.cu -- flash-style self-attention forward, two query tiles per CTA (QKVAttentionLegacy /
+// QKVAttention, unet.py:340-405).  Used for head dim 64 / 128 when L > 128; attention_fwd.cu keeps the
+// single-tile variant for head dim 256 and tiny L.
+//
+// One CTA = 256 queries (two 128-row tiles) of one (sample, head); K/V tiles are streamed ONCE for both.
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = tcgen05 issuer, warps 2..5 = softmax group 0
+// (query tile 0), warps 6..9 = softmax group 1 (query tile 1).  TMEM: S0 | S1 | O0 | O1.  While one group
+// runs exp2 on its S tile the tensor pipe computes the other tile's S = Q K^T and O += P V, so the MUFU and
+// the tensor pipe overlap instead of alternating (the single-tile kernel spent ~7.9k clk per 128x128 tile
+// against a ~1k clk MUFU floor: profiles/r1_attention_ncu.md).
+//
+// Per KV tile j and query tile t:   s_full[t] (S ready) -> group t loads S into registers -> s_free[t]
+// (issuer may overwrite S_t with tile j+1) -> max / lazy O rescale / exp2 / P -> smem -> p_full[t]
+// -> issuer: O_t += P_t V_j -> pv_done[t] (P_t buffer and O_t reusable).
+#include "common.cuh"
+#include "tmap.cuh"
+#include "umma.cuh"
+
+namespace b2d {
+using namespace umma;
+
+struct AttnFwd2Params {
+  int L, heads;
+  int q_off, k_off, v_off, head_stride;
+  float scale_log2;
+  __half* out; long long ldo;
+  float* lse;
+};
+
+struct AttnFwd2Maps {
+  CUtensorMap q;   // box (64, 128, 1)
+  CUtensorMap kv;  // box (64, BKV, 1)
+};
+
+constexpr int ATT2_THREADS = 320;
+
+template <int D, int BKV>
+struct Fwd2Cfg {
+  static constexpr int ST = 3;
+  static constexpr int QT_BYTES = 128 * D * 2;          // one query tile
+  static constexpr int K_BYTES = BKV * D * 2;
+  static constexpr int STAGE_BYTES = 2 * K_BYTES;       // K + V
+  static constexpr int PT_BYTES = 128 * BKV * 2;        // one P tile
+  static constexpr int SMEM_DATA = 2 * QT_BYTES + ST * STAGE_BYTES + 2 * PT_BYTES;
+  static constexpr int NBARS = 1 + 3 * ST + 8;
+  static constexpr int SMEM_TOTAL = SMEM_DATA + NBARS * 8 + 16 + 1024;
+  static constexpr uint32_t S_COL = 0;                  // S_t at t * 128
+  static constexpr uint32_t O_COL = 256;                // O_t at 256 + t * D
+  static_assert(BKV <= 128 && 256 + 2 * D <= 512, "TMEM budget");
+};
+
+template <int D, int BKV>
+__global__ void __launch_bounds__(ATT2_THREADS, 1)
+attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params p) {
+  using Cfg = Fwd2Cfg<D, BKV>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint8_t* q_s = smem;
+  uint8_t* kv_s = q_s + 2 * Cfg::QT_BYTES;
+  uint8_t* p_s = kv_s + Cfg::ST * Cfg::STAGE_BYTES;
+  uint64_t* bars = (uint64_t*)(p_s + 2 * Cfg::PT_BYTES);
+  uint64_t* q_full = bars;
+  uint64_t* k_full = bars + 1;
+  uint64_t* v_full = k_full + Cfg::ST;
+  uint64_t* kv_empty = v_full + Cfg::ST;
+  uint64_t* s_full = kv_empty + Cfg::ST;   // [2]
+  uint64_t* s_free = s_full + 2;           // [2]
+  uint64_t* p_full = s_free + 2;           // [2]
+  uint64_t* pv_done = p_full + 2;          // [2]
+  uint32_t* tmem_slot = (uint32_t*)(pv_done + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int q0 = blockIdx.x * 256;
+  const int head = blockIdx.y;
+  const int n = blockIdx.z;
+  const int n_kv = (p.L + BKV - 1) / BKV;
+  const int qc = p.q_off + head * p.head_stride;
+  const int kc = p.k_off + head * p.head_stride;
+  const int vc = p.v_off + head * p.head_stride;
+
+  if (threadIdx.x == 0) {
+    mbar_init(q_full, 1);
+    for (int s = 0; s < Cfg::ST; ++s) { mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&kv_empty[s], 1); }
+    for (int t = 0; t < 2; ++t) {
+      mbar_init(&s_full[t], 1); mbar_init(&s_free[t], 128); mbar_init(&p_full[t], 128); mbar_init(&pv_done[t], 1);
+    }
+    fence_barrier_init();
+    prefetch_tmap(&maps.q);
+    prefetch_tmap(&maps.kv);
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ---------------------------------------------------------------- TMA producer
+    if (elect_one()) {
+      mbar_expect_tx(q_full, 2 * Cfg::QT_BYTES);
+#pragma unroll
+      for (int t = 0; t < 2; ++t)
+#pragma unroll
+        for (int b = 0; b < D / 64; ++b)
+          tma_load_3d(q_s + t * Cfg::QT_BYTES + b * (128 * 128), &maps.q, q_full, qc + b * 64, q0 + t * 128, n);
+      for (int j = 0; j < n_kv; ++j) {
+        const int s = j % Cfg::ST;
+        mbar_wait(&kv_empty[s], (uint32_t)(((j / Cfg::ST) & 1) ^ 1));
+        uint8_t* k_dst = kv_s + s * Cfg::STAGE_BYTES;
+        uint8_t* v_dst = k_dst + Cfg::K_BYTES;
+        mbar_expect_tx(&k_full[s], Cfg::K_BYTES);
+#pragma unroll
+        for (int b = 0; b < D / 64; ++b) tma_load_3d(k_dst + b * (BKV * 128), &maps.kv, &k_full[s], kc + b * 64, j * BKV, n);
+        mbar_expect_tx(&v_full[s], Cfg::K_BYTES);
+#pragma unroll
+        for (int b = 0; b < D / 64; ++b) tma_load_3d(v_dst + b * (BKV * 128), &maps.kv, &v_full[s], vc + b * 64, j * BKV, n);
+      }
+    }
+  } else if (warp == 1) {
+    // ---------------------------------------------------------------- tcgen05 issuer
+    const uint32_t idesc_s = make_idesc(128, BKV, 0, 0, FMT_F16, FMT_F16);  // S = Q K^T, both K-major
+    const uint32_t idesc_o = make_idesc(128, D, 0, 1, FMT_F16, FMT_F16);    // O += P V, V MN-major
+    const uint32_t q_addr = smem_u32(q_s);
+    const uint32_t p_addr = smem_u32(p_s);
+    auto issue_s = [&](int j, int t) {     // S_t(j) = Q_t K_j^T ; caller has waited for K_j and for S_t to be free
+      if (elect_one()) {
+        const uint32_t k_addr = smem_u32(kv_s + (j % Cfg::ST) * Cfg::STAGE_BYTES);
+        const uint32_t d_tmem = tmem_base + Cfg::S_COL + (uint32_t)t * 128u;
+#pragma unroll
+        for (int kk = 0; kk < D / 16; ++kk) {
+          const uint32_t a = q_addr + t * Cfg::QT_BYTES + (kk >> 2) * (128 * 128) + (kk & 3) * 32;
+          const uint32_t b = k_addr + (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
+          mma_f16_ss(d_tmem, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, 16, 1024), idesc_s, (uint32_t)(kk != 0));
+        }
+        mma_commit(&s_full[t]);
+      }
+      __syncwarp();
+    };
+    auto issue_pv = [&](int j, int t, bool last_reader) {
+      if (elect_one()) {
+        const int s = j % Cfg::ST;
+        const uint32_t v_addr = smem_u32(kv_s + s * Cfg::STAGE_BYTES + Cfg::K_BYTES);
+        const uint32_t d_tmem = tmem_base + Cfg::O_COL + (uint32_t)(t * D);
+#pragma unroll
+        for (int kk = 0; kk < BKV / 16; ++kk) {
+          const uint32_t a = p_addr + t * Cfg::PT_BYTES + (kk >> 2) * (128 * 128) + (kk & 3) * 32;
+          const uint32_t b = v_addr + kk * 2048;
+          mma_f16_ss(d_tmem, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, BKV * 128, 1024), idesc_o,
+                     (uint32_t)((j | kk) != 0));
+        }
+        mma_commit(&pv_done[t]);
+        if (last_reader) mma_commit(&kv_empty[s]);
+      }
+      __syncwarp();
+    };
+    mbar_wait(q_full, 0);
+    mbar_wait(&k_full[0], 0);
+    tc_fence_after();
+    issue_s(0, 0);
+    issue_s(0, 1);
+    for (int j = 0; j < n_kv; ++j) {
+      const uint32_t par = (uint32_t)(j & 1);
+      const bool more = j + 1 < n_kv;
+      if (more) mbar_wait(&k_full[(j + 1) % Cfg::ST], (uint32_t)(((j + 1) / Cfg::ST) & 1));
+      mbar_wait(&v_full[j % Cfg::ST], (uint32_t)((j / Cfg::ST) & 1));
+#pragma unroll
+      for (int t = 0; t < 2; ++t) {
+        if (more) {
+          mbar_wait(&s_free[t], par);
+          tc_fence_after();
+          issue_s(j + 1, t);
+        }
+        mbar_wait(&p_full[t], par);
+        tc_fence_after();
+        issue_pv(j, t, t == 1);
+      }
+    }
+  } else {
+    // ---------------------------------------------------------------- softmax groups / epilogue
+    const int t = (warp - 2) >> 2;          // query tile of this group
+    const int qd = warp & 3;                // TMEM lane quarter this warp may touch
+    const int row = qd * 32 + lane;
+    const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
+    const uint32_t s_addr = lane_base + Cfg::S_COL + (uint32_t)t * 128u;
+    const uint32_t o_addr = lane_base + Cfg::O_COL + (uint32_t)(t * D);
+    uint8_t* pt_s = p_s + t * Cfg::PT_BYTES;
+    const float c = p.scale_log2;
+    float m_used = -INFINITY;
+    float l_sum = 0.f;
+    for (int j = 0; j < n_kv; ++j) {
+      mbar_wait(&s_full[t], (uint32_t)(j & 1));
+      tc_fence_after();
+      uint32_t sr[BKV];                    // this thread's row of S, kept in registers (raw fp32 bits)
+#pragma unroll
+      for (int c0 = 0; c0 < BKV; c0 += 32) tmem_ld32(s_addr + c0, sr + c0);
+      tmem_ld_wait();
+      tc_fence_before();
+      mbar_arrive(&s_free[t]);             // S_t may be overwritten by the next tile's Q K^T
+      const int kv_valid = p.L - j * BKV;  // keys of this tile that exist (>= BKV except on the last tile)
+      if (kv_valid < BKV) {
+#pragma unroll
+        for (int i = 0; i < BKV; ++i) if (i >= kv_valid) sr[i] = 0xff800000u;   // -inf
+      }
+      float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
+#pragma unroll
+      for (int i = 2; i < BKV; i += 2) {
+        mx0 = fmaxf(mx0, __uint_as_float(sr[i]));
+        mx1 = fmaxf(mx1, __uint_as_float(sr[i + 1]));
+      }
+      const float mx = fmaxf(mx0, mx1);
+      // previous O_t += P_t V must be complete before P_t is overwritten or O_t rescaled
+      if (j > 0) { mbar_wait(&pv_done[t], (uint32_t)((j - 1) & 1)); tc_fence_after(); }
+      const bool grow = (mx - m_used) * c > 8.0f;   // lazy rescale: move the offset only for > 2^8 growth
+      if (j == 0) {
+        m_used = mx;
+      } else if (__any_sync(0xffffffffu, grow)) {
+        const float m_new = fmaxf(m_used, mx);
+        const float f = exp2f((m_used - m_new) * c);
+        m_used = m_new;
+        l_sum *= f;
+#pragma unroll
+        for (int c0 = 0; c0 < D; c0 += 16) {
+          uint32_t r[16];
+          tmem_ld16(o_addr + c0, r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 16; ++i) r[i] = __float_as_uint(__uint_as_float(r[i]) * f);
+          tmem_st16(o_addr + c0, r);
+        }
+        tmem_st_wait();
+      }
+      const float mc = m_used * c;
+#pragma unroll
+      for (int i = 0; i < BKV; ++i)        // exp2(-inf) = 0 for masked keys
+        sr[i] = __float_as_uint(exp2f(fmaf(__uint_as_float(sr[i]), c, -mc)));
+      float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;
+#pragma unroll
+      for (int i = 0; i < BKV; i += 4) {
+        ls0 += __uint_as_float(sr[i]);     ls1 += __uint_as_float(sr[i + 1]);
+        ls2 += __uint_as_float(sr[i + 2]); ls3 += __uint_as_float(sr[i + 3]);
+      }
+      l_sum += (ls0 + ls1) + (ls2 + ls3);
+#pragma unroll
+      for (int g = 0; g < BKV / 8; ++g) {
+        uint4 u;
+        u.x = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 0]), __uint_as_float(sr[8 * g + 1]));
+        u.y = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 2]), __uint_as_float(sr[8 * g + 3]));
+        u.z = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 4]), __uint_as_float(sr[8 * g + 5]));
+        u.w = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 6]), __uint_as_float(sr[8 * g + 7]));
+        uint8_t* blk = pt_s + (g >> 3) * (128 * 128);
+        *reinterpret_cast<uint4*>(blk + sw128_offset((uint32_t)row, (uint32_t)((g & 7) * 8))) = u;
+      }
+      fence_proxy_async_smem();
+      tc_fence_before();
+      mbar_arrive(&p_full[t]);
+    }
+    // epilogue: O / l -> fp16 global, lse
+    mbar_wait(&pv_done[t], (uint32_t)((n_kv - 1) & 1));
+    tc_fence_after();
+    const int qi = q0 + t * 128 + row;
+    const bool valid = qi < p.L;
+    const float inv_l = 1.0f / l_sum;
+    __half* op = p.out + ((long long)n * p.L + qi) * p.ldo + head * D;
+#pragma unroll
+    for (int c0 = 0; c0 < D; c0 += 32) {
+      uint32_t r[32];
+      tmem_ld32(o_addr + c0, r);
+      tmem_ld_wait();
+      if (valid) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint4 o;
+          o.x = pack_f16x2(__uint_as_float(r[8 * g + 0]) * inv_l, __uint_as_float(r[8 * g + 1]) * inv_l);
+          o.y = pack_f16x2(__uint_as_float(r[8 * g + 2]) * inv_l, __uint_as_float(r[8 * g + 3]) * inv_l);
+          o.z = pack_f16x2(__uint_as_float(r[8 * g + 4]) * inv_l, __uint_as_float(r[8 * g + 5]) * inv_l);
+          o.w = pack_f16x2(__uint_as_float(r[8 * g + 6]) * inv_l, __uint_as_float(r[8 * g + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(op + c0 + 8 * g) = o;
+        }
+      }
+    }
+    if (valid && p.lse) p.lse[((long long)n * p.heads + head) * p.L + qi] = m_used * c + log2f(l_sum);
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+template <int D, int BKV>
+static int launch_attn_fwd2(const void* qkv, int64_t ldqkv, int N, int C3, const AttnFwd2Params& p, void* stream) {
+  using Cfg = Fwd2Cfg<D, BKV>;
+  static bool attr_set = false;
+  if (!attr_set) {
+    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd2_kernel<D, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_TOTAL));
+    attr_set = true;
+  }
+  AttnFwd2Maps maps;
+  const uint64_t dims[3] = {(uint64_t)C3, (uint64_t)p.L, (uint64_t)N};
+  const uint64_t str[2] = {(uint64_t)ldqkv * 2, (uint64_t)ldqkv * 2 * (uint64_t)p.L};
+  const uint32_t boxq[3] = {64u, 128u, 1u};
+  const uint32_t boxkv[3] = {64u, (uint32_t)BKV, 1u};
+  int rc = make_tmap_16b(&maps.q, qkv, 3, dims, str, boxq);
+  if (rc) return rc;
+  rc = make_tmap_16b(&maps.kv, qkv, 3, dims, str, boxkv);
+  if (rc) return rc;
+  dim3 grid((unsigned)((p.L + 255) / 256), (unsigned)p.heads, (unsigned)N);
+  attn_fwd2_kernel<D, BKV><<<grid, ATT2_THREADS, Cfg::SMEM_TOTAL, (cudaStream_t)stream>>>(maps, p);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+// called by b2d_attention_fwd (attention_fwd.cu) for ch in {64, 128} and L > 128
+int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order, void* out,
+                            int64_t ldo, float* lse, void* stream) {
+  const int C = heads * ch;
+  AttnFwd2Params p;
+  p.L = L; p.heads = heads;
+  if (new_order) { p.q_off = 0; p.k_off = C; p.v_off = 2 * C; p.head_stride = ch; }          // unet.py:392
+  else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }    // unet.py:359
+  p.scale_log2 = 1.4426950408889634f / sqrtf((float)ch);
+  p.out = (__half*)out; p.ldo = ldo; p.lse = lse;
+  if (ch == 64) return launch_attn_fwd2<64, 128>(qkv, ldqkv, N, 3 * C, p, stream);
+  return launch_attn_fwd2<128, 64>(qkv, ldqkv, N, 3 * C, p, stream);
+}
+
+}  // namespace b2d

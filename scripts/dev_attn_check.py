@@ -1,4 +1,4 @@
-"""Developer check (GPU): attention fwd (and bwd when present) vs fp32 torch on bf16-rounded inputs."""
+"""Developer check (GPU): attention fwd (and bwd when present) vs fp32 torch on fp16-rounded inputs."""
 import math
 import sys
 
@@ -28,8 +28,8 @@ def run(N, Lq, heads, ch, new_order=0, std=1.0, time_it=False):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(3)
     C = heads * ch
-    qkv = (torch.randn(N, Lq, 3 * C, device=dev, generator=g) * std).to(torch.bfloat16)
-    out = torch.empty(N, Lq, C, device=dev, dtype=torch.bfloat16)
+    qkv = (torch.randn(N, Lq, 3 * C, device=dev, generator=g) * std).to(torch.float16)
+    out = torch.empty(N, Lq, C, device=dev, dtype=torch.float16)
     lse = torch.empty(N, heads, Lq, device=dev)
     lib = L.lib()
 
@@ -68,6 +68,8 @@ if __name__ == "__main__":
     worst = max(worst, run(1, 64, 1, 256))          # L smaller than a tile
     worst = max(worst, run(1, 1024, 1, 64, std=4.0))  # large logits: exercises the lazy rescale
     run(64, 4096, 1, 64, time_it=True)
+    run(256, 4096, 1, 64, time_it=True)        # bench shape (cfg2 full-res layer)
+    run(256, 1024, 1, 128, time_it=True)       # cfg2 half-res layer
     run(64, 1024, 1, 128, time_it=True)
     run(64, 256, 1, 256, time_it=True)
     run(8, 16384, 1, 64, time_it=True)

@@ -19,11 +19,11 @@ def attn_bwd(N, Lq, heads, ch, new_order=0, time_it=False):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(5)
     Cc = heads * ch
-    qkv = torch.randn(N, Lq, 3 * Cc, device=dev, generator=g).to(torch.bfloat16)
-    d_o = torch.randn(N, Lq, Cc, device=dev, generator=g).to(torch.bfloat16)
-    out = torch.empty(N, Lq, Cc, device=dev, dtype=torch.bfloat16)
+    qkv = torch.randn(N, Lq, 3 * Cc, device=dev, generator=g).to(torch.float16)
+    d_o = torch.randn(N, Lq, Cc, device=dev, generator=g).to(torch.float16)
+    out = torch.empty(N, Lq, Cc, device=dev, dtype=torch.float16)
     lse = torch.empty(N, heads, Lq, device=dev)
-    dqkv = torch.full((N, Lq, 3 * Cc), float("nan"), device=dev, dtype=torch.bfloat16)
+    dqkv = torch.full((N, Lq, 3 * Cc), float("nan"), device=dev, dtype=torch.float16)
     delta = torch.empty(N, heads, Lq, device=dev)
     lib = L.lib()
     L.check(lib.b2d_attention_fwd(qkv.data_ptr(), 3 * Cc, N, Lq, heads, ch, new_order, out.data_ptr(), Cc,
@@ -58,11 +58,11 @@ def gn(N, HW, C1, C2, act, with_add):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(7)
     Ct = C1 + C2
-    x1 = (torch.randn(N, HW, C1, device=dev, generator=g) * 2 + 0.5).to(torch.bfloat16)
-    x2 = (torch.randn(N, HW, C2, device=dev, generator=g)).to(torch.bfloat16) if C2 else None
+    x1 = (torch.randn(N, HW, C1, device=dev, generator=g) * 2 + 0.5).to(torch.float16)
+    x2 = (torch.randn(N, HW, C2, device=dev, generator=g)).to(torch.float16) if C2 else None
     gamma = torch.randn(Ct, device=dev, generator=g); beta = torch.randn(Ct, device=dev, generator=g)
-    dy = torch.randn(N, HW, Ct, device=dev, generator=g).to(torch.bfloat16)
-    add_a = torch.randn(N, HW, C1, device=dev, generator=g).to(torch.bfloat16) if with_add else None
+    dy = torch.randn(N, HW, Ct, device=dev, generator=g).to(torch.float16)
+    add_a = torch.randn(N, HW, C1, device=dev, generator=g).to(torch.float16) if with_add else None
     a = L.GnArgs()
     a.x1, a.ld1, a.C1 = x1.data_ptr(), C1, C1
     a.x2, a.ld2, a.C2 = (x2.data_ptr() if C2 else None), C2, C2
@@ -71,7 +71,7 @@ def gn(N, HW, C1, C2, act, with_add):
     lib = L.lib()
     wsb = lib.b2d_groupnorm_workspace_bytes(N, Ct)
     ws = torch.empty(wsb, device=dev, dtype=torch.uint8)
-    y = torch.empty(N, HW, Ct, device=dev, dtype=torch.bfloat16)
+    y = torch.empty(N, HW, Ct, device=dev, dtype=torch.float16)
     mean = torch.empty(N, 32, device=dev); rstd = torch.empty(N, 32, device=dev)
     L.check(lib.b2d_groupnorm_fwd(C.byref(a), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), ws.data_ptr(), wsb,
                                   L.stream_ptr()), "gn fwd")

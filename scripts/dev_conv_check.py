@@ -1,4 +1,4 @@
-"""Developer check (GPU): conv2d / wgrad kernels against torch fp32 on bf16-rounded inputs."""
+"""Developer check (GPU): conv2d / wgrad kernels against torch fp32 on fp16-rounded inputs."""
 import ctypes as C
 import sys
 
@@ -12,23 +12,23 @@ from lipreading_video_generation_b200 import _lib as L  # noqa: E402
 def pack_w(w):  # OIHW fp32 -> [CoutPad][tap][Cin] bf16
     co, ci, kh, kw = w.shape
     cop = (co + 15) // 16 * 16
-    p = torch.zeros(cop, kh * kw * ci, device=w.device, dtype=torch.bfloat16)
-    p[:co] = w.permute(0, 2, 3, 1).reshape(co, -1).to(torch.bfloat16)
+    p = torch.zeros(cop, kh * kw * ci, device=w.device, dtype=torch.float16)
+    p[:co] = w.permute(0, 2, 3, 1).reshape(co, -1).to(torch.float16)
     return p, cop
 
 
 def run_conv(N, H, W, C1, C2, Cout, k, stride, extras=True):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(1)
-    x = torch.randn(N, H, W, C1, device=dev, generator=g).to(torch.bfloat16)
-    x2 = torch.randn(N, H, W, C2, device=dev, generator=g).to(torch.bfloat16) if C2 else None
+    x = torch.randn(N, H, W, C1, device=dev, generator=g).to(torch.float16)
+    x2 = torch.randn(N, H, W, C2, device=dev, generator=g).to(torch.float16) if C2 else None
     w = torch.randn(Cout, C1 + C2, k, k, device=dev, generator=g) * 0.05
     wp, cop = pack_w(w)
     Ho, Wo = H // stride, W // stride
     bias = torch.randn(Cout, device=dev, generator=g) if extras else None
     emb = torch.randn(N, Cout, device=dev, generator=g) if extras else None
-    res = torch.randn(N, Ho, Wo, Cout, device=dev, generator=g).to(torch.bfloat16) if extras else None
-    out = torch.empty(N, Ho, Wo, Cout, device=dev, dtype=torch.bfloat16)
+    res = torch.randn(N, Ho, Wo, Cout, device=dev, generator=g).to(torch.float16) if extras else None
+    out = torch.empty(N, Ho, Wo, Cout, device=dev, dtype=torch.float16)
     a = L.ConvArgs()
     a.x, a.ldx, a.C1 = x.data_ptr(), C1, C1
     a.x2, a.ldx2, a.C2 = (x2.data_ptr() if C2 else None), C2, C2
@@ -40,7 +40,7 @@ def run_conv(N, H, W, C1, C2, Cout, k, stride, extras=True):
     L.check(L.lib().b2d_conv2d(C.byref(a), L.stream_ptr()), "conv2d")
     torch.cuda.synchronize()
     xin = x if not C2 else torch.cat([x, x2], -1)
-    ref = F.conv2d(xin.float().permute(0, 3, 1, 2), w.to(torch.bfloat16).float(), None, stride, k // 2)
+    ref = F.conv2d(xin.float().permute(0, 3, 1, 2), w.to(torch.float16).float(), None, stride, k // 2)
     if extras:
         ref = ref + bias[None, :, None, None] + emb[:, :, None, None] + res.float().permute(0, 3, 1, 2)
     ref = ref.permute(0, 2, 3, 1)
@@ -52,10 +52,10 @@ def run_conv(N, H, W, C1, C2, Cout, k, stride, extras=True):
 def run_wgrad(N, H, W, C1, C2, Cout, k, stride):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(2)
-    x = torch.randn(N, H, W, C1, device=dev, generator=g).to(torch.bfloat16)
-    x2 = torch.randn(N, H, W, C2, device=dev, generator=g).to(torch.bfloat16) if C2 else None
+    x = torch.randn(N, H, W, C1, device=dev, generator=g).to(torch.float16)
+    x2 = torch.randn(N, H, W, C2, device=dev, generator=g).to(torch.float16) if C2 else None
     Ho, Wo = H // stride, W // stride
-    dy = torch.randn(N, Ho, Wo, Cout, device=dev, generator=g).to(torch.bfloat16)
+    dy = torch.randn(N, Ho, Wo, Cout, device=dev, generator=g).to(torch.float16)
     dw = torch.zeros(Cout, k * k * (C1 + C2), device=dev)
     a = L.WgradArgs()
     a.x, a.ldx, a.C1 = x.data_ptr(), C1, C1
