@@ -229,7 +229,7 @@ def main():
     barrier()
     l0 = L.lib().b2d_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
+    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd", "conv2d", "conv2d_wgrad", "groupnorm_fwd", "groupnorm_bwd"}) as kt:
         e0.record()
         for _ in range(a.steps):
             step(x0, cond, audio, t_dev)
@@ -261,7 +261,14 @@ def main():
     # roofline of the dominant kernel class: full-resolution (ch = 64) attention, forward
     tot = kt.totals()
     dom = None
+    by_class = {}
     for (name, meta), (t_ms, cnt) in tot.items():
+        by_class[name] = by_class.get(name, 0.0) + t_ms / a.steps
+        print(f"[kernel] {name:14s} {str(meta):40s} x{cnt // a.steps:3d}/step  {t_ms / cnt:8.4f} ms/launch  {t_ms / a.steps:8.3f} ms/step",
+              file=sys.stderr)
+    for (name, meta), (t_ms, cnt) in tot.items():
+        if not name.startswith("attention"):
+            continue
         Nn, Lq, heads, ch = meta
         flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lq * ch * heads * Nn
         rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, launches_per_step=cnt // a.steps,
@@ -282,7 +289,7 @@ def main():
     h2d = sum(t.numel() * t.element_size() for t in (hx0, hcond, haudio, t_host))
     out = {"metric": "denoiser_train_clips_per_s", "value": round(value, 3), "unit": "clips/s", "n_gpus": world,
            "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
-           "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic", "config": config,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
            "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 3), "unit": "clips/s", "h2d_bytes_per_step": h2d,
                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
            "gpu_launches": int(launches), "roofline": roof,
@@ -290,6 +297,7 @@ def main():
            "step_frac_of_sustained_peak": round(train_tflop / (ms / 1000.0) / sustained, 4),
            "cpu_baseline": {"value": round(cpu_v, 5), "unit": "clips/s", "cores": cores, "kind": "port",
                             "sample": f"{n_cpu} images {S}x{S}: oracle torso fwd+bwd fp32, median of {reps}, {sec_cpu:.2f} s"},
+           "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
            "clocks": clk.summary(), "last_loss": loss_host}
     print(json.dumps(out))
     if world > 1:

@@ -9,6 +9,7 @@
 //   kernel B (one CTA per 128-query tile): S = Q K^T, dP = dO V^T, dS = P (dP - delta);  dQ += dS K
 // All four "second" GEMMs read their B operand (dO, Q, K) in the pixel-major layout through an
 // MN-major tcgen05 descriptor, so no transposed copies of q/k/v/dO are ever written.
+#include <stdlib.h>
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
@@ -221,7 +222,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
         float pv[32], dv[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const float pe = exp2f(fmaf(__uint_as_float(sr[i]), c, -ls[c0 + i]));
+          const float pe = fast_exp2(fmaf(__uint_as_float(sr[i]), c, -ls[c0 + i]));
           pv[i] = pe;
           dv[i] = pe * (__uint_as_float(dr[i]) - ds[c0 + i]);
         }
@@ -235,8 +236,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
           w.x = pack_f16x2(dv[8 * g + 0], dv[8 * g + 1]); w.y = pack_f16x2(dv[8 * g + 2], dv[8 * g + 3]);
           w.z = pack_f16x2(dv[8 * g + 4], dv[8 * g + 5]); w.w = pack_f16x2(dv[8 * g + 6], dv[8 * g + 7]);
           const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8 * g));
-          *reinterpret_cast<uint4*>(pblk + off) = u;
-          *reinterpret_cast<uint4*>(dblk + off) = w;
+          sts128(smem_u32(pblk) + off, u);
+          sts128(smem_u32(dblk) + off, w);
         }
       }
       fence_proxy_async_smem();
@@ -415,7 +416,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
         float dv[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const float pe = exp2f(fmaf(__uint_as_float(sr[i]), c, -lse_i));
+          const float pe = fast_exp2(fmaf(__uint_as_float(sr[i]), c, -lse_i));
           dv[i] = pe * (__uint_as_float(dr[i]) - del_i);
         }
         uint8_t* dblk = ds_s + (c0 >> 6) * (128 * 128);
@@ -424,7 +425,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
           uint4 w;
           w.x = pack_f16x2(dv[8 * g + 0], dv[8 * g + 1]); w.y = pack_f16x2(dv[8 * g + 2], dv[8 * g + 3]);
           w.z = pack_f16x2(dv[8 * g + 4], dv[8 * g + 5]); w.w = pack_f16x2(dv[8 * g + 6], dv[8 * g + 7]);
-          *reinterpret_cast<uint4*>(dblk + sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8 * g))) = w;
+          sts128(smem_u32(dblk) + sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8 * g)), w);
         }
       }
       fence_proxy_async_smem();
@@ -500,6 +501,10 @@ static int launch_attn_bwd(const void* qkv, int64_t ldqkv, const void* d_o, int6
   return B2D_OK;
 }
 
+int attention_bwd2_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
+                            int new_order, const float* lse, const float* delta, void* dqkv, int64_t lddqkv,
+                            void* stream);   // attention_bwd2.cu
+
 }  // namespace b2d
 
 using namespace b2d;
@@ -527,6 +532,9 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
         (const __half*)out, ldo, (const __half*)d_out, lddo, N, L, heads, ch, delta_ws);
     B2D_CHECK_LAUNCH();
   }
+  static const bool force_v1 = getenv("B2D_ATTN_BWD_V1") != nullptr;   // A/B timing of the single-tile kernels
+  if (!force_v1 && ch == 64 && L > 128)
+    return attention_bwd2_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws, dqkv, lddqkv, stream);
   if (ch == 64) return launch_attn_bwd<64, 64, 128, 128>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
   if (ch == 128) return launch_attn_bwd<128, 128, 64, 64>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
   return launch_attn_bwd<256, 128, 64, 64>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);

@@ -191,7 +191,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
         m_used = mx;
       } else if (__any_sync(0xffffffffu, grow)) {
         const float m_new = fmaxf(m_used, mx);
-        const float f = exp2f((m_used - m_new) * c);
+        const float f = fast_exp2((m_used - m_new) * c);
         m_used = m_new;
         l_sum *= f;
 #pragma unroll
@@ -215,7 +215,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
         float pv[32];
 #pragma unroll
         for (int i = 0; i < 32; ++i) {
-          const float e = exp2f(fmaf(__uint_as_float(r[i]), c, -mc));
+          const float e = fast_exp2(fmaf(__uint_as_float(r[i]), c, -mc));
           pv[i] = (c0 + i < kv_valid) ? e : 0.f;
           l_sum += pv[i];
         }
@@ -228,7 +228,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
           u.z = pack_f16x2_nosat(pv[8 * g + 4], pv[8 * g + 5]);
           u.w = pack_f16x2_nosat(pv[8 * g + 6], pv[8 * g + 7]);
           const uint32_t col = (uint32_t)((c0 & 63) + 8 * g);
-          *reinterpret_cast<uint4*>(blk + sw128_offset((uint32_t)row, col)) = u;
+          sts128(smem_u32(blk) + sw128_offset((uint32_t)row, col), u);
         }
       }
       fence_proxy_async_smem();

@@ -184,7 +184,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const uint32_t s_addr = lane_base + Cfg::S_COL + (uint32_t)t * 128u;
     const uint32_t o_addr = lane_base + Cfg::O_COL + (uint32_t)(t * D);
-    uint8_t* pt_s = p_s + t * Cfg::PT_BYTES;
+    const uint32_t pt_u32 = smem_u32(p_s + t * Cfg::PT_BYTES);
     const float c = p.scale_log2;
     float m_used = -INFINITY;
     float l_sum = 0.f;
@@ -216,7 +216,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
         m_used = mx;
       } else if (__any_sync(0xffffffffu, grow)) {
         const float m_new = fmaxf(m_used, mx);
-        const float f = exp2f((m_used - m_new) * c);
+        const float f = fast_exp2((m_used - m_new) * c);
         m_used = m_new;
         l_sum *= f;
 #pragma unroll
@@ -233,7 +233,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
       const float mc = m_used * c;
 #pragma unroll
       for (int i = 0; i < BKV; ++i)        // exp2(-inf) = 0 for masked keys
-        sr[i] = __float_as_uint(exp2f(fmaf(__uint_as_float(sr[i]), c, -mc)));
+        sr[i] = __float_as_uint(fast_exp2(fmaf(__uint_as_float(sr[i]), c, -mc)));
       float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;
 #pragma unroll
       for (int i = 0; i < BKV; i += 4) {
@@ -248,8 +248,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
         u.y = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 2]), __uint_as_float(sr[8 * g + 3]));
         u.z = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 4]), __uint_as_float(sr[8 * g + 5]));
         u.w = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 6]), __uint_as_float(sr[8 * g + 7]));
-        uint8_t* blk = pt_s + (g >> 3) * (128 * 128);
-        *reinterpret_cast<uint4*>(blk + sw128_offset((uint32_t)row, (uint32_t)((g & 7) * 8))) = u;
+        sts128(pt_u32 + (uint32_t)(g >> 3) * (128u * 128u) + sw128_offset((uint32_t)row, (uint32_t)((g & 7) * 8)), u);
       }
       fence_proxy_async_smem();
       tc_fence_before();

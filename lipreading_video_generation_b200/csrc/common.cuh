@@ -121,6 +121,13 @@ __device__ __forceinline__ void store8_fmt(void* p, const float* v, int fmt) {
   *reinterpret_cast<uint4*>(p) = u;
 }
 
+// one MUFU.EX2 (exp2f() adds a denormal-range pre/post scale: FSETP + 2 FMUL per element)
+__device__ __forceinline__ float fast_exp2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
 
 }  // namespace b2d

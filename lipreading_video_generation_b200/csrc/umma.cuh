@@ -160,6 +160,22 @@ __device__ __forceinline__ uint64_t make_sdesc_sw128(uint32_t saddr, uint32_t lb
   return d;
 }
 
+// 16-byte store to shared memory through a 32-bit shared-window address.  (A store through a generic pointer
+// rebuilt from uintptr_t arithmetic compiles to ST.E split into 32/64-bit pieces: measured 7 excess wavefronts
+// per store in the attention kernels, profiles/r1_attention_ncu.md.)
+__device__ __forceinline__ void sts128(uint32_t saddr, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" :: "r"(saddr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+__device__ __forceinline__ float4 lds128f(uint32_t saddr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(saddr));
+  return v;
+}
+__device__ __forceinline__ void sts32f(uint32_t saddr, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" :: "r"(saddr), "f"(v) : "memory");
+}
+
 // byte offset of element (row, col) inside a K-major SW128 tile [rows][64 bf16]
 __device__ __forceinline__ uint32_t sw128_offset(uint32_t row, uint32_t col) {
   return row * 128u + ((((col >> 3) ^ (row & 7u)) << 4) | ((col & 7u) << 1));

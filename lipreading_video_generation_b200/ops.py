@@ -187,8 +187,9 @@ def groupnorm_fwd(x1, gamma, beta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed
     mean = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
     rstd = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
     ws = _gn_workspace(x1.device, N, Ct)
-    L.check(L.lib().b2d_groupnorm_fwd(C.byref(a), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), ws.data_ptr(),
-                                      ws.numel(), _s()), "b2d_groupnorm_fwd")
+    with _timed("groupnorm_fwd", (N, H * W, Ct)):
+        L.check(L.lib().b2d_groupnorm_fwd(C.byref(a), y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), ws.data_ptr(),
+                                          ws.numel(), _s()), "b2d_groupnorm_fwd")
     return y, mean, rstd
 
 
@@ -203,12 +204,13 @@ def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=T
     dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=F16)
     dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=F16) if x2 is not None else None
     ws = _gn_workspace(x1.device, N, Ct)
-    L.check(L.lib().b2d_groupnorm_bwd(
-        C.byref(a), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx1.data_ptr(), C1,
-        L.ptr(dx2), (dx2.shape[3] if dx2 is not None else 0),
-        L.ptr(add_a), (add_a.stride(2) if add_a is not None else 0),
-        L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
-        dgamma.data_ptr(), dbeta.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "b2d_groupnorm_bwd")
+    with _timed("groupnorm_bwd", (N, H * W, Ct)):
+        L.check(L.lib().b2d_groupnorm_bwd(
+            C.byref(a), dy.data_ptr(), mean.data_ptr(), rstd.data_ptr(), dx1.data_ptr(), C1,
+            L.ptr(dx2), (dx2.shape[3] if dx2 is not None else 0),
+            L.ptr(add_a), (add_a.stride(2) if add_a is not None else 0),
+            L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
+            dgamma.data_ptr(), dbeta.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "b2d_groupnorm_bwd")
     return dx1, dx2
 
 

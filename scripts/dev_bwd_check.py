@@ -110,6 +110,8 @@ if __name__ == "__main__":
     worst = max(worst, attn_bwd(1, 200, 2, 64, 1))
     worst = max(worst, attn_bwd(1, 64, 1, 256))
     attn_bwd(64, 4096, 1, 64, time_it=True)
+    attn_bwd(256, 4096, 1, 64, time_it=True)     # bench shape (cfg2 full-res layer)
+    attn_bwd(256, 1024, 1, 128, time_it=True)    # cfg2 half-res layer
     attn_bwd(64, 1024, 1, 128, time_it=True)
     attn_bwd(64, 256, 1, 256, time_it=True)
     print("WORST", worst)
