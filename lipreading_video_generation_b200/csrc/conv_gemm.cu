@@ -31,6 +31,7 @@ struct ConvParams {
   int HoWo, Wo;        // output plane
   int rows, imgs;      // box: rows per tile, images per tile
   int total_pixels;    // N*Ho*Wo
+  int m_tiles, n_tiles; // persistent tile loop: tile = tile_m * n_tiles + tile_n
   int Cout, BN;
   int stages;
   int fmt;             // storage format of x / residual / out: FMT_F16 (forward) or FMT_F16 (gradient = dgrad)
@@ -55,22 +56,26 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   const uint32_t stage_bytes = A_TILE_BYTES + b_tile_bytes;
   uint64_t* full_bar = (uint64_t*)(smem + (size_t)p.stages * stage_bytes);
   uint64_t* empty_bar = full_bar + p.stages;
-  uint64_t* acc_bar = empty_bar + p.stages;
-  uint32_t* tmem_slot = (uint32_t*)(acc_bar + 1);
+  uint64_t* acc_full = empty_bar + p.stages;   // [2] accumulator buffer b holds a finished tile
+  uint64_t* acc_empty = acc_full + 2;          // [2] epilogue has drained buffer b
+  uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
 
-  const int tile_m = blockIdx.x;
-  const int n0 = blockIdx.y * p.BN;
+  // Persistent CTA: tiles tile0, tile0 + gridDim.x, ...; the TMA ring and the two TMEM accumulator buffers run
+  // across tile boundaries, so tile i's epilogue overlaps tile i+1's loads and MMAs (the non-persistent
+  // version spent ~22k clk per CTA on a 1.2k-clk mainloop: profiles/r1_conv.md).
+  const int total_tiles = p.m_tiles * p.n_tiles;
   const int chunks = p.kc1 + p.kc2;
   const int total_iters = p.taps * chunks;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
-    mbar_init(acc_bar, 1);
+    mbar_init(&acc_full[0], 1); mbar_init(&acc_full[1], 1);
+    mbar_init(&acc_empty[0], 128); mbar_init(&acc_empty[1], 128);
     fence_barrier_init();
     prefetch_tmap(&maps.a[0]);
     prefetch_tmap(&maps.b);
   }
-  if (warp == 1) tmem_alloc(tmem_slot, p.tmem_cols);
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * p.tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -79,6 +84,10 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   if (warp == 0) {
     // ------------------------------------------------------------ TMA producer
     if (elect_one()) {
+      int it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const int tile_m = tile / p.n_tiles;
+      const int n0 = (tile - tile_m * p.n_tiles) * p.BN;
       int img0, h0;
       if (p.HoWo >= 128) {
         const int tpi = p.HoWo >> 7;
@@ -89,7 +98,6 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
         h0 = 0;
       }
       const int pad = p.ksize >> 1;
-      int it = 0;
       for (int tap = 0; tap < p.taps; ++tap) {
         const int dy = tap / p.ksize, dx = tap - dy * p.ksize;
         int hc, wc, ph = 0;
@@ -114,39 +122,52 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
           tma_load_2d(b_dst, &maps.b, &full_bar[s], (tap * chunks + ch) * 64, n0);
         }
       }
+      }  // tile
     }
   } else if (warp == 1) {
     // ------------------------------------------------------------ MMA issuer
     const uint32_t idesc = make_idesc(128, p.BN, 0, 0, FMT_F16, FMT_F16);
-    for (int it = 0; it < total_iters; ++it) {
-      const int s = it % p.stages;
-      const uint32_t par = (uint32_t)((it / p.stages) & 1);
-      mbar_wait(&full_bar[s], par);
+    int git = 0, lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+      const int buf = lt & 1;
+      mbar_wait(&acc_empty[buf], (uint32_t)(((lt >> 1) & 1) ^ 1));   // epilogue drained this buffer (2 tiles ago)
       tc_fence_after();
-      if (elect_one()) {
-        const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-        const uint32_t b_addr = a_addr + A_TILE_BYTES;
+      const uint32_t d_tmem = tmem_base + (uint32_t)buf * p.tmem_cols;
+      for (int it = 0; it < total_iters; ++it, ++git) {
+        const int s = git % p.stages;
+        const uint32_t par = (uint32_t)((git / p.stages) & 1);
+        mbar_wait(&full_bar[s], par);
+        tc_fence_after();
+        if (elect_one()) {
+          const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+          const uint32_t b_addr = a_addr + A_TILE_BYTES;
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          mma_f16_ss(tmem_base, make_sdesc_sw128(a_addr + k * 32, 16, 1024),
-                      make_sdesc_sw128(b_addr + k * 32, 16, 1024), idesc, (uint32_t)((it | k) != 0));
+          for (int k = 0; k < 4; ++k) {
+            mma_f16_ss(d_tmem, make_sdesc_sw128(a_addr + k * 32, 16, 1024),
+                       make_sdesc_sw128(b_addr + k * 32, 16, 1024), idesc, (uint32_t)((it | k) != 0));
+          }
+          mma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
+          if (it == total_iters - 1) mma_commit(&acc_full[buf]);
         }
-        mma_commit(&empty_bar[s]);  // frees the smem stage once these MMAs have read it
-        if (it == total_iters - 1) mma_commit(acc_bar);
+        __syncwarp();
       }
-      __syncwarp();
     }
   } else {
     // ------------------------------------------------------------ epilogue (warps 2..5)
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
+    const int buf = lt & 1;
+    const int tile_m = tile / p.n_tiles;
+    const int n0 = (tile - tile_m * p.n_tiles) * p.BN;
     const long long pix = (long long)tile_m * 128 + row;
     const bool valid = pix < p.total_pixels;
     const int n_img = valid ? (int)(pix / p.HoWo) : 0;
     const int hw = valid ? (int)(pix - (long long)n_img * p.HoWo) : 0;
-    mbar_wait(acc_bar, 0);
+    mbar_wait(&acc_full[buf], (uint32_t)((lt >> 1) & 1));
     tc_fence_after();
-    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * p.tmem_cols;
     for (int c0 = 0; c0 < p.BN; c0 += 16) {
       uint32_t r[16];
       __syncwarp();
@@ -198,10 +219,13 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       }
       }  // valid
     }
+    tc_fence_before();
+    mbar_arrive(&acc_empty[buf]);   // all of this thread's TMEM reads of the buffer have completed (ld wait above)
+    }  // tile
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 1) tmem_dealloc(tmem_base, p.tmem_cols);
+  if (warp == 1) tmem_dealloc(tmem_base, 2 * p.tmem_cols);
 }
 
 static bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
@@ -301,13 +325,18 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   p.out = (__half*)a->out; p.ldo = a->ldo;
   p.out_nchw = a->out_nchw_f32;
 
-  const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 1) * 8 + 16 + 1024;
+  const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 4) * 8 + 16 + 1024;
   static size_t smem_set = 0;
   if (smem > smem_set) {
     B2D_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     smem_set = 200 * 1024;
   }
-  dim3 grid((unsigned)((p.total_pixels + 127) / 128), (unsigned)((a->CoutPad + BN - 1) / BN));
+  p.m_tiles = (p.total_pixels + 127) / 128;
+  p.n_tiles = (a->CoutPad + BN - 1) / BN;
+  const long long tiles = (long long)p.m_tiles * p.n_tiles;
+  long long ctas = 2LL * num_sms();            // two persistent CTAs per SM (<= 96 KB ring, <= 256 TMEM columns each)
+  if (ctas > tiles) ctas = tiles;
+  dim3 grid((unsigned)ctas);
   conv_gemm_kernel<<<grid, CONV_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
