@@ -19,10 +19,16 @@
 namespace b2d {
 using namespace umma;
 
+__device__ __forceinline__ void named_bar_sync(int id, int count) {
+  asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(count) : "memory");
+}
+
 struct ConvMaps {
   CUtensorMap a[4];  // source 1 (4 phases when stride == 2, else a[0])
   CUtensorMap a2;    // source 2 (stride 1 only)
   CUtensorMap b;     // weights
+  CUtensorMap o;     // output   (N,Ho,Wo,ldo): box (64, Wo, rows, imgs)   [TMA-store epilogue]
+  CUtensorMap r;     // residual (N,Ho,Wo,ldres): same box
 };
 
 struct ConvParams {
@@ -31,6 +37,8 @@ struct ConvParams {
   int HoWo, Wo;        // output plane
   int rows, imgs;      // box: rows per tile, images per tile
   int total_pixels;    // N*Ho*Wo
+  int n_images;
+  int tma_out;         // epilogue stages the tile in smem and uses TMA for the residual load and the output store
   int m_tiles, n_tiles; // persistent tile loop: tile = tile_m * n_tiles + tile_n
   int Cout, BN;
   int stages;
@@ -44,6 +52,7 @@ struct ConvParams {
 };
 
 constexpr int CONV_THREADS = 192;
+constexpr int EB_FLOATS = 512;              // images per tile x BN <= 512 (bias + emb staging)
 constexpr int A_TILE_BYTES = 128 * 128;  // 128 pixels x 64 bf16
 
 __global__ void __launch_bounds__(CONV_THREADS)
@@ -59,6 +68,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   uint64_t* acc_full = empty_bar + p.stages;   // [2] accumulator buffer b holds a finished tile
   uint64_t* acc_empty = acc_full + 2;          // [2] epilogue has drained buffer b
   uint32_t* tmem_slot = (uint32_t*)(acc_empty + 2);
+  const uint32_t eb_base = smem_u32(tmem_slot + 4);   // float [2][EB_FLOATS]: bias + emb of the current tile
+  uint64_t* res_full = (uint64_t*)(tmem_slot + 2);    // residual tile landed in the staging buffer
+  uint8_t* stage_out = smem + (size_t)p.stages * stage_bytes + 1024 + 2 * EB_FLOATS * 4;   // 2 x [128 pix][64 ch] fp16, 1024-aligned
 
   // Persistent CTA: tiles tile0, tile0 + gridDim.x, ...; the TMA ring and the two TMEM accumulator buffers run
   // across tile boundaries, so tile i's epilogue overlaps tile i+1's loads and MMAs (the non-persistent
@@ -71,6 +83,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(&acc_full[0], 1); mbar_init(&acc_full[1], 1);
     mbar_init(&acc_empty[0], 128); mbar_init(&acc_empty[1], 128);
+    mbar_init(res_full, 1);
     fence_barrier_init();
     prefetch_tmap(&maps.a[0]);
     prefetch_tmap(&maps.b);
@@ -154,8 +167,15 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     }
   } else {
     // ------------------------------------------------------------ epilogue (warps 2..5)
+    // Per tile: (1) stage bias + emb for the tile's images in smem and issue ALL residual loads of this thread's
+    // row into registers BEFORE waiting for the accumulator, so their HBM latency hides behind the tile's MMAs
+    // (the first version loaded them 16 columns at a time after the wait: 62 % of its samples were long_sb);
+    // (2) TMEM -> registers -> + (bias + emb) -> + residual -> fp16 / fp32-NCHW global.
     const int q = warp & 3;  // TMEM lane quarter this warp may access
     const int row = q * 32 + lane;
+    const int et = threadIdx.x - 64;        // 0..127 among the epilogue threads
+    const bool has_eb = (p.bias != nullptr) || (p.emb != nullptr);
+    const int imgs_in_tile = p.HoWo >= 128 ? 1 : p.imgs;
     int lt = 0;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++lt) {
     const int buf = lt & 1;
@@ -165,10 +185,98 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     const bool valid = pix < p.total_pixels;
     const int n_img = valid ? (int)(pix / p.HoWo) : 0;
     const int hw = valid ? (int)(pix - (long long)n_img * p.HoWo) : 0;
+    const int img_first = (int)(((long long)tile_m * 128) / p.HoWo);
+    const uint32_t eb_u32 = eb_base + (uint32_t)buf * (EB_FLOATS * 4u);
+    if (has_eb) {
+      for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
+        const int im = idx / p.BN, c = idx - im * p.BN;
+        const int col = n0 + c, img = img_first + im;
+        float v = 0.f;
+        if (col < p.Cout) {
+          if (p.bias) v = __ldg(p.bias + col);
+          if (p.emb && img < p.n_images) v += __ldg(p.emb + (long long)img * p.ldemb + col);
+        }
+        sts32f(eb_u32 + (uint32_t)idx * 4u, v);
+      }
+    }
+    int img0, h0;                                      // tile origin for the TMA boxes (as in the producer)
+    if (p.HoWo >= 128) { const int tpi = p.HoWo >> 7; img0 = tile_m / tpi; h0 = (tile_m - img0 * tpi) * p.rows; }
+    else { img0 = tile_m * p.imgs; h0 = 0; }
+    const int nblk = p.BN >> 6;
+    if (p.tma_out && et == 0) {
+      tma_store_wait_read();                           // previous tile's store has finished reading the staging buffer
+      if (p.residual) {
+        mbar_expect_tx(res_full, (uint32_t)nblk * A_TILE_BYTES);
+        for (int b = 0; b < nblk; ++b) tma_load_4d(stage_out + b * A_TILE_BYTES, &maps.r, res_full, n0 + b * 64, 0, h0, img0);
+      }
+    }
+    const bool fast_cols = (n0 + p.BN <= p.Cout);      // whole tile inside the logical channels: vector path
+    uint4 rres[16];                                    // residual row segment: up to 128 columns of fp16
+    const bool res_vec = !p.tma_out && p.residual && valid && fast_cols && ((p.ldres & 7) == 0) && ((((uintptr_t)p.residual) & 15) == 0);
+    if (res_vec) {
+      const __half* rp = p.residual + pix * p.ldres + n0;
+#pragma unroll
+      for (int g = 0; g < 16; ++g) if (g * 8 < p.BN) rres[g] = ldg_nc_u4(rp + g * 8);
+    }
+    named_bar_sync(1, 128);                            // eb staging visible to the four epilogue warps
     mbar_wait(&acc_full[buf], (uint32_t)((lt >> 1) & 1));
     tc_fence_after();
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * p.tmem_cols;
-    for (int c0 = 0; c0 < p.BN; c0 += 16) {
+    const uint32_t eb_row = eb_u32 + (uint32_t)((n_img - img_first) * p.BN) * 4u;
+    if (p.tma_out) {
+      // ---- staged path: residual arrives by TMA in the 128B-swizzled tile layout, results go back to the same
+      // smem slots (conflict-free 16-byte accesses) and leave with one TMA store per 64-channel block
+      const uint32_t so_u32 = smem_u32(stage_out);
+      if (p.residual) mbar_wait(res_full, (uint32_t)(lt & 1));
+#pragma unroll
+      for (int cc = 0; cc < 8; ++cc) {
+        const int c0 = cc * 16;
+        if (c0 < p.BN) {
+          uint32_t r[16];
+          __syncwarp();
+          tmem_ld16(taddr + (uint32_t)c0, r);
+          tmem_ld_wait();
+          float v[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+          if (has_eb) {
+#pragma unroll
+            for (int j4 = 0; j4 < 4; ++j4) {
+              const float4 e = lds128f(eb_row + (uint32_t)(c0 + 4 * j4) * 4u);
+              v[4 * j4] += e.x; v[4 * j4 + 1] += e.y; v[4 * j4 + 2] += e.z; v[4 * j4 + 3] += e.w;
+            }
+          }
+          const uint32_t a0 = so_u32 + (uint32_t)(c0 >> 6) * A_TILE_BYTES + sw128_offset((uint32_t)row, (uint32_t)(c0 & 63));
+          const uint32_t a1 = so_u32 + (uint32_t)(c0 >> 6) * A_TILE_BYTES + sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8));
+          if (p.residual) {
+            const uint4 u0 = lds128(a0), u1 = lds128(a1);
+            const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { float2 f = unpack_f16x2(w[j]); v[2 * j] += f.x; v[2 * j + 1] += f.y; }
+          }
+          uint4 o0, o1;
+          o0.x = pack_f16x2(v[0], v[1]);   o0.y = pack_f16x2(v[2], v[3]);
+          o0.z = pack_f16x2(v[4], v[5]);   o0.w = pack_f16x2(v[6], v[7]);
+          o1.x = pack_f16x2(v[8], v[9]);   o1.y = pack_f16x2(v[10], v[11]);
+          o1.z = pack_f16x2(v[12], v[13]); o1.w = pack_f16x2(v[14], v[15]);
+          sts128(a0, o0);
+          sts128(a1, o1);
+        }
+      }
+      tc_fence_before();
+      mbar_arrive(&acc_empty[buf]);
+      fence_proxy_async_smem();                        // staged tile visible to the TMA engine
+      named_bar_sync(2, 128);
+      if (et == 0) {
+        for (int b = 0; b < nblk; ++b) tma_store_4d(&maps.o, stage_out + b * A_TILE_BYTES, n0 + b * 64, 0, h0, img0);
+        tma_store_commit();
+      }
+      continue;
+    }
+#pragma unroll
+    for (int cc = 0; cc < 8; ++cc) {
+      const int c0 = cc * 16;
+      if (c0 < p.BN) {
       uint32_t r[16];
       __syncwarp();
       tmem_ld16(taddr + (uint32_t)c0, r);
@@ -179,23 +287,21 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
 #pragma unroll
       for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
       const int ncol = min(16, p.Cout - col0);
-      if (p.bias) {
+      if (has_eb) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) if (j < ncol) v[j] += __ldg(p.bias + col0 + j);
-      }
-      if (p.emb) {
-        const float* e = p.emb + (long long)n_img * p.ldemb + col0;
-#pragma unroll
-        for (int j = 0; j < 16; ++j) if (j < ncol) v[j] += __ldg(e + j);
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const float4 e = lds128f(eb_row + (uint32_t)(c0 + 4 * j4) * 4u);   // zero beyond Cout
+          v[4 * j4] += e.x; v[4 * j4 + 1] += e.y; v[4 * j4 + 2] += e.z; v[4 * j4 + 3] += e.w;
+        }
       }
       if (p.residual) {
-        const __half* rp = p.residual + pix * p.ldres + col0;
-        if (ncol == 16 && ((((uintptr_t)rp) & 15) == 0)) {
-          uint4 u0 = ldg_nc_u4(rp), u1 = ldg_nc_u4(rp + 8);
+        if (res_vec) {
+          const uint4 u0 = rres[2 * cc], u1 = rres[2 * cc + 1];
           const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
           for (int j = 0; j < 8; ++j) { float2 f = unpack_f16x2(w[j]); v[2 * j] += f.x; v[2 * j + 1] += f.y; }
         } else {
+          const __half* rp = p.residual + pix * p.ldres + col0;
           for (int j = 0; j < ncol; ++j) v[j] += __half2float(rp[j]);
         }
       }
@@ -218,10 +324,12 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
           p.out_nchw[((long long)n_img * p.Cout + col0 + j) * p.HoWo + hw] = v[j];
       }
       }  // valid
+      }  // c0 < BN
     }
     tc_fence_before();
     mbar_arrive(&acc_empty[buf]);   // all of this thread's TMEM reads of the buffer have completed (ld wait above)
     }  // tile
+    if (p.tma_out && et == 0) tma_store_wait_all();
   }
   tc_fence_before();
   __syncthreads();
@@ -263,6 +371,7 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
     B2D_REQUIRE((128 % (Ho * Wo)) == 0, B2D_ERR_SHAPE, "conv2d: plane %dx%d does not tile 128 pixels", Ho, Wo);
     rows = Ho;
     imgs = 128 / (Ho * Wo);
+    B2D_REQUIRE(imgs <= 8, B2D_ERR_SHAPE, "conv2d: plane %dx%d too small (more than 8 images per 128-pixel tile)", Ho, Wo);
   } else {
     B2D_REQUIRE(Ho % rows == 0, B2D_ERR_SHAPE, "conv2d: height %d not a multiple of %d tile rows", Ho, rows);
   }
@@ -308,16 +417,37 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
     if (rc) return rc;
   }
 
+  const bool tma_out = a->out != nullptr && a->out_nchw_f32 == nullptr && a->Cout % 64 == 0 && BN % 64 == 0 &&
+                       a->ldo % 8 == 0 && aligned16(a->out) &&
+                       (a->residual == nullptr || (a->ldres % 8 == 0 && aligned16(a->residual)));
+  if (tma_out) {
+    rc = make_act_map(&maps.o, a->out, a->Cout, a->ldo, a->N, Ho, Wo, 1, Wo, rows, imgs);
+    if (rc) return rc;
+    if (a->residual) {
+      rc = make_act_map(&maps.r, a->residual, a->Cout, a->ldres, a->N, Ho, Wo, 1, Wo, rows, imgs);
+      if (rc) return rc;
+    } else {
+      maps.r = maps.o;
+    }
+  } else {
+    maps.o = maps.a[0]; maps.r = maps.a[0];
+  }
+
   ConvParams p;
+  p.tma_out = tma_out ? 1 : 0;
   p.taps = taps; p.ksize = a->ksize; p.stride = a->stride;
   p.kc1 = a->C1 / 64; p.kc2 = C2 / 64;
   p.HoWo = Ho * Wo; p.Wo = Wo; p.rows = rows; p.imgs = imgs;
   p.total_pixels = a->N * Ho * Wo;
+  p.n_images = a->N;
   p.Cout = a->Cout; p.BN = BN;
   const uint32_t stage_bytes = A_TILE_BYTES + (uint32_t)BN * 128u;
-  int stages = (int)(98304u / stage_bytes);  // <= 96 KB of operand ring: two CTAs per SM
-  if (stages < 3) stages = 3;
+  // smem per CTA <= 112 KB so that two persistent CTAs share an SM: 72 KB operand ring + 32 KB output staging
+  // + 4 KB bias/emb staging + barriers
+  int stages = (int)(73728u / stage_bytes);
+  if (stages < 2) stages = 2;
   if (stages > 6) stages = 6;
+  B2D_REQUIRE(imgs * BN <= EB_FLOATS, B2D_ERR_SHAPE, "conv2d: %d images x %d channels per tile exceed the epilogue staging", imgs, BN);
   p.stages = stages;
   p.tmem_cols = BN <= 32 ? 32 : BN <= 64 ? 64 : BN <= 128 ? 128 : 256;
   p.bias = a->bias; p.emb = a->emb; p.ldemb = a->ldemb;
@@ -325,7 +455,7 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   p.out = (__half*)a->out; p.ldo = a->ldo;
   p.out_nchw = a->out_nchw_f32;
 
-  const size_t smem = (size_t)stages * stage_bytes + (2 * stages + 4) * 8 + 16 + 1024;
+  const size_t smem = (size_t)stages * stage_bytes + 1024 /* barriers */ + 2 * EB_FLOATS * 4 + 2 * A_TILE_BYTES + 1024;
   static size_t smem_set = 0;
   if (smem > smem_set) {
     B2D_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
