@@ -102,6 +102,31 @@ def build_model(S, device, seed=0):
     return model.to(device)
 
 
+class SampleStep:
+    """test.py:57-65 on the product: one reverse-diffusion step for a batch of frames -- model forward (no autograd
+    graph, conditioning encoded once and reused: it is loop invariant) + DDPM posterior update with fresh noise."""
+
+    def __init__(self, model, S, device):
+        import lipreading_video_generation_b200 as P
+        self.model, self.device = model.eval(), device
+        self.sched = P.LinearNoiseScheduler(1000, 0.00085, 0.012)
+        self.i = 999
+        self.feats = None
+
+    def prepare(self, audio):
+        with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+            self.feats = self.model.encode_audio({"input_values": audio}).float()
+
+    @torch.no_grad()
+    def __call__(self, xt, cond):
+        i = self.i
+        self.i = i - 1 if i > 1 else 999
+        t = torch.full((xt.shape[0],), i, device=self.device, dtype=torch.long)
+        eps = self.model(xt, cond, None, t, audio_features=self.feats)
+        x_prev, x0 = self.sched.sample_prev_timestep(xt, eps, i)
+        return x_prev, x0
+
+
 class TrainStep:
     """train.py:109-134 on the product: zero_grad, q_sample, model, MSE, backward, (grad all-reduce), Adam."""
 
@@ -163,6 +188,87 @@ def cpu_baseline(S, threads, seconds_budget=25.0):
     return n, med, len(times)
 
 
+def main_sample(a, model, S, clips, frames, world, rank, local, device, config, cores):
+    """sampler frames/s (BASELINE configs[3] per-GPU shape): replicas only, no collective on the data path."""
+    from lipreading_video_generation_b200 import _lib as L, ops
+    n_img = clips * frames
+    step = SampleStep(model, S, device)
+    x0, cond, audio = make_batch(n_img, S, 1234 + rank, device)
+    hx0, hcond, haudio = make_batch(n_img, S, 1234 + rank, device, pinned=True)
+    step.prepare(audio)
+    xt = torch.randn(n_img, 3, S, S, device=device)
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+    for _ in range(a.warmup):
+        xt, _ = step(xt, cond)
+    barrier()
+    l0 = L.lib().b2d_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "conv2d", "groupnorm_fwd"}) as kt:
+        e0.record()
+        for _ in range(a.steps):
+            xt, x0p = step(xt, cond)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1) / a.steps
+    launches = (L.lib().b2d_launch_count() - l0) // a.steps
+    # end to end: conditioning + x_T from pinned host memory, wav2vec2 encoding, K steps, x0_pred back to the host
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    hxt = torch.randn(n_img, 3, S, S).pin_memory()
+    hout = torch.empty(n_img, 3, S, S).pin_memory()
+    f0.record()
+    dc = hcond.to(device, non_blocking=True); da = haudio.to(device, non_blocking=True); dx = hxt.to(device, non_blocking=True)
+    step.prepare(da)
+    for _ in range(a.steps):
+        dx, x0p = step(dx, dc)
+    hout.copy_(x0p, non_blocking=True)
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1) / a.steps
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=device)
+        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+        ms, ms_e2e = tt.tolist()
+        torch.distributed.destroy_process_group()
+    if rank != 0:
+        return
+    burst, sustained, hbm, which = peaks()
+    tot = kt.totals()
+    by_class, dom = {}, None
+    for (name, meta), (t_ms, cnt) in tot.items():
+        by_class[name] = by_class.get(name, 0.0) + t_ms / a.steps
+        if name == "attention_fwd":
+            Nn, Lq, heads, ch = meta
+            rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, tflops=4.0 * Lq * Lq * ch * heads * Nn / (t_ms / cnt) / 1e9,
+                       ms_per_step=t_ms / a.steps)
+            if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
+                dom = rec
+    T = 1000
+    value = n_img * world / (T * ms / 1000.0)
+    fwd_tflop = FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
+    out = {"metric": "sampler_frames_per_s", "value": round(value, 4), "unit": "frames/s (1000-step DDPM)", "n_gpus": world,
+           "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
+           "frames_per_s_50_step_ddim": round(n_img * world / (50 * ms / 1000.0), 3),
+           "e2e": {"value": round(n_img * world / (T * ms_e2e / 1000.0), 4), "unit": "frames/s (1000-step DDPM)",
+                   "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in (hcond, haudio, hxt)) // a.steps,
+                   "d2h_bytes_per_step": hout.numel() * 4 // a.steps, "ms_per_step": round(ms_e2e, 3)},
+           "gpu_launches": int(launches),
+           "roofline": {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
+                        "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
+                        "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
+                        "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N"},
+           "step_tflops_algorithmic": round(fwd_tflop / (ms / 1000.0), 1),
+           "step_frac_of_sustained_peak": round(fwd_tflop / (ms / 1000.0) / sustained, 4),
+           "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
+           "cpu_baseline": None, "clocks": clk.summary()}
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -211,6 +317,8 @@ def main():
     model = build_model(S, device)
     if world > 1:
         broadcast_parameters(model)
+    if kind == "sample":
+        return main_sample(a, model, S, clips, frames, world, rank, local, device, config, cores)
     step = TrainStep(model, S, world, device)
     x0, cond, audio = make_batch(n_img, S, 1234 + rank, device)
     hx0, hcond, haudio = make_batch(n_img, S, 1234 + rank, device, pinned=True)
