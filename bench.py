@@ -19,6 +19,7 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 os.environ.setdefault("B2D_WAV2VEC2_RANDOM_INIT", "1")   # no network: wav2vec2-base weights are random-init
+os.environ.setdefault("NCCL_DEBUG", "WARN")              # keep stdout to the one JSON line
 
 import torch  # noqa: E402
 
@@ -305,6 +306,7 @@ def main():
         return
 
     assert torch.cuda.is_available(), "bench.py needs a B200; there is no CPU fallback for the product path"
+    torch.backends.cudnn.benchmark = True      # third-party wav2vec2 (HF / cuDNN) only: let cuDNN pick its conv kernels
     torch.cuda.set_device(local)
     device = torch.device("cuda", local)
     if world > 1:

@@ -180,18 +180,21 @@ attn_bwd_dkv2_kernel(const __grid_constant__ AttnBwd2Maps maps, const AttnBwd2Pa
     const float c = p.scale_log2;
     const float* lse_g = p.lse + ((long long)n * p.heads + head) * p.L;
     const float* del_g = p.delta + ((long long)n * p.heads + head) * p.L;
-    auto stage_vec = [&](int j) {
+    // lse / delta of query tile j -> smem, software pipelined: the global load for tile j+2 is issued a full
+    // step before its value is stored (a load -> store in the same step stalled every step on the HBM latency)
+    auto ld_vec = [&](int j) -> float {
       const int qi = j * 64 + (gt & 63);
-      float v;
-      if (gt < 64) v = qi < p.L ? __ldg(lse_g + qi) : INFINITY;
-      else         v = qi < p.L ? __ldg(del_g + qi) : 0.f;
-      sts32f(vec_u32 + (uint32_t)((j % 3) * 128 + gt) * 4u, v);
+      if (gt < 64) return qi < p.L ? __ldg(lse_g + qi) : INFINITY;
+      return qi < p.L ? __ldg(del_g + qi) : 0.f;
     };
-    stage_vec(0);
+    auto st_vec = [&](int j, float v) { sts32f(vec_u32 + (uint32_t)((j % 3) * 128 + gt) * 4u, v); };
+    st_vec(0, ld_vec(0));
+    float pend = n_q > 1 ? ld_vec(1) : 0.f;
     for (int j = 0; j < n_q; ++j) {
       // three buffers: a thread past this barrier writes buffer (j+2)%3 at the top of step j+1 while a slower
       // thread may still read buffer j%3; buffer (j+1)%3 was written before this barrier
-      if (j + 1 < n_q) stage_vec(j + 1);
+      if (j + 1 < n_q) st_vec(j + 1, pend);
+      if (j + 2 < n_q) pend = ld_vec(j + 2);
       named_bar_sync2(1 + t, 128);
       const uint32_t ls_u32 = vec_u32 + (uint32_t)(j % 3) * 512u, dl_u32 = ls_u32 + 256u;
       mbar_wait(&sdp_full[t], (uint32_t)(j & 1));
