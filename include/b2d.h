@@ -241,7 +241,9 @@ int b2d_linear_bwd(const float* x, const float* w, const float* y, const float* 
 /* Backward of b2d_attention_fwd w.r.t. the packed qkv tensor (replaces autograd through
  * unet.py:356-366 and the checkpoint recompute of utils.py:179-207).  out / lse are the forward's
  * results; d_out: bf16 (N,L,lddo) gradient w.r.t. out; dqkv: bf16 (N,L,lddqkv) fully written;
- * delta_ws: fp32 workspace of N*heads*L elements. */
+ * delta_ws: fp32 workspace of b2d_attention_bwd_ws_floats(N, L, heads, ch) elements (the per-row delta, plus
+ * the fp32 dQ accumulator of the single-pass kernel where that one is used). */
+int64_t b2d_attention_bwd_ws_floats(int N, int L, int heads, int ch);
 int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out, int64_t ldo, const void* d_out,
                       int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
                       void* dqkv, int64_t lddqkv, float* delta_ws, void* stream);

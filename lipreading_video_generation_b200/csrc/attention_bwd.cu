@@ -504,10 +504,18 @@ static int launch_attn_bwd(const void* qkv, int64_t ldqkv, const void* d_o, int6
 int attention_bwd2_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
                             int new_order, const float* lse, const float* delta, void* dqkv, int64_t lddqkv,
                             void* stream);   // attention_bwd2.cu
+int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
+                            int new_order, const float* lse, const float* delta, float* dq_acc, void* dqkv,
+                            int64_t lddqkv, void* stream);   // attention_bwd3.cu
 
 }  // namespace b2d
 
 using namespace b2d;
+
+extern "C" int64_t b2d_attention_bwd_ws_floats(int N, int L, int heads, int ch) {
+  const int64_t rows = (int64_t)N * heads * L;
+  return (ch == 64 && L > 128) ? rows * 65 : rows;   // delta + the fp32 dQ accumulator of the fused kernel
+}
 
 extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out, int64_t ldo, const void* d_out,
                                  int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
@@ -533,6 +541,10 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
     B2D_CHECK_LAUNCH();
   }
   static const bool force_v1 = getenv("B2D_ATTN_BWD_V1") != nullptr;   // A/B timing of the single-tile kernels
+  static const bool force_v2 = getenv("B2D_ATTN_BWD_V2") != nullptr;   // A/B timing of the two-kernel variant
+  if (!force_v1 && !force_v2 && ch == 64 && L > 128)
+    return attention_bwd3_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws,
+                                   delta_ws + (long long)N * heads * L, dqkv, lddqkv, stream);
   if (!force_v1 && ch == 64 && L > 128)
     return attention_bwd2_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws, dqkv, lddqkv, stream);
   if (ch == 64) return launch_attn_bwd<64, 64, 128, 128>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);

@@ -18,5 +18,8 @@ PFN_encodeTiled get_encode_tiled();
 // dims[0] is the innermost (contiguous) dimension; strides_bytes[i] is the pitch of dims[i+1].
 int make_tmap_16b(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box);
+// same for fp32 elements (box[0] * 4 bytes <= 128)
+int make_tmap_f32(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                  const uint64_t* strides_bytes, const uint32_t* box);
 
 }  // namespace b2d

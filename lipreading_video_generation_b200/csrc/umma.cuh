@@ -81,6 +81,12 @@ __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* s
       "cp.async.bulk.tensor.4d.global.shared::cta.tile.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
       :: "l"(m), "r"(smem_u32(src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
 }
+// smem -> global element-wise fp32 add (bulk async group): the L2 performs the reduction on whole lines
+__device__ __forceinline__ void tma_reduce_add_3d(const CUtensorMap* m, uint32_t src_saddr, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];"
+      :: "l"(m), "r"(src_saddr), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 // all prior bulk stores of this thread have finished READING their smem source
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }

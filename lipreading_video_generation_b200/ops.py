@@ -237,7 +237,8 @@ def attention_bwd(qkv, out, d_out, lse, heads, new_order=False):
     Cc = C3 // 3
     ch = Cc // heads
     dqkv = torch.empty(N, H, W, C3, device=qkv.device, dtype=F16)
-    delta = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
+    delta = torch.empty(int(L.lib().b2d_attention_bwd_ws_floats(N, H * W, heads, ch)), device=qkv.device,
+                        dtype=torch.float32)
     with _timed("attention_bwd", (N, H * W, heads, ch)):
         L.check(L.lib().b2d_attention_bwd(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2),
                                           d_out.data_ptr(), d_out.stride(2), lse.data_ptr(), N, H * W, heads, ch,

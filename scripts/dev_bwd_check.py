@@ -24,8 +24,8 @@ def attn_bwd(N, Lq, heads, ch, new_order=0, time_it=False):
     out = torch.empty(N, Lq, Cc, device=dev, dtype=torch.float16)
     lse = torch.empty(N, heads, Lq, device=dev)
     dqkv = torch.full((N, Lq, 3 * Cc), float("nan"), device=dev, dtype=torch.float16)
-    delta = torch.empty(N, heads, Lq, device=dev)
     lib = L.lib()
+    delta = torch.empty(int(lib.b2d_attention_bwd_ws_floats(N, Lq, heads, ch)), device=dev)
     L.check(lib.b2d_attention_fwd(qkv.data_ptr(), 3 * Cc, N, Lq, heads, ch, new_order, out.data_ptr(), Cc,
                                   lse.data_ptr(), L.stream_ptr()), "fwd")
 
