@@ -15,7 +15,7 @@
 //   L1 sectors per instruction and held the loop at ~6k clk per pair, profiles/r1_attention_ncu.md);
 //   dq_finalize_kernel scales the accumulator into the fp16 dqkv columns afterwards.
 // TMEM (512 columns): S^T|dP^T of group b at b*128 (64 + 64); dV 256; dK 320; dQ double buffer 384 / 448.
-// Warps: 0 = TMA producer, 1 = tcgen05 issuer, 2..5 = compute group 0, 6..9 = compute group 1.
+// Warps: 0 = TMA producer, 1 = tcgen05 issuer, 2..17 = compute: group (w-2)/4 % 2, column half (w-2)/8.
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
@@ -40,7 +40,7 @@ struct AttnBwd3Maps {
   CUtensorMap dq;      // box (32, 128, 1) on the fp32 dQ accumulator (N, L, heads*64)
 };
 
-constexpr int AB3_THREADS = 320;
+constexpr int AB3_THREADS = 576;   // TMA warp + MMA warp + 16 compute warps
 constexpr int AB3_ST = 4;
 constexpr int B3_T128 = 128 * 128;   // [128 rows][64 ch] fp16
 constexpr int B3_T64 = 64 * 128;     // [64 rows][64 ch] fp16
@@ -54,7 +54,7 @@ struct Bwd3Smem {
   static constexpr int DQ_OFF = DS_OFF + 2 * B3_T128;             // fp32 dQ staging [2 groups][128 q][32 ch], SW128
   static constexpr int VEC_OFF = DQ_OFF + 2 * B3_T128;            // lse/delta staging [2 groups][3 bufs][128]
   static constexpr int BAR_OFF = VEC_OFF + 2 * 3 * 128 * 4;
-  static constexpr int NBARS = 1 + 2 * AB3_ST + 10;
+  static constexpr int NBARS = 1 + 2 * AB3_ST + 12;
   static constexpr int TOTAL = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
@@ -76,7 +76,8 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
   uint64_t* p_ready = s_free + 2;        // [2] per group: P^T, dS^T written to smem
   uint64_t* pair_done = p_ready + 2;     // [2] per dQ buffer: every MMA up to and including dQ_m has completed
   uint64_t* dq_free = pair_done + 2;     // [2] per dQ buffer: both groups have read the dQ tile
-  uint32_t* tmem_slot = (uint32_t*)(dq_free + 2);
+  uint64_t* stg_free = dq_free + 2;      // [2] per group: its fp32 dQ staging buffer may be overwritten
+  uint32_t* tmem_slot = (uint32_t*)(stg_free + 2);
 
   // S2R shares the MUFU issue path with ex2: an opaque copy keeps the compiler from re-reading %tid.x in the loop
   uint32_t tid;
@@ -92,8 +93,8 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     mbar_init(kv_full, 1);
     for (int s = 0; s < AB3_ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(&sdp_full[b], 1); mbar_init(&s_free[b], 128); mbar_init(&p_ready[b], 128);
-      mbar_init(&pair_done[b], 1); mbar_init(&dq_free[b], 256);
+      mbar_init(&sdp_full[b], 1); mbar_init(&s_free[b], 256); mbar_init(&p_ready[b], 256);
+      mbar_init(&pair_done[b], 1); mbar_init(&dq_free[b], 512); mbar_init(&stg_free[b], 1);
     }
     fence_barrier_init();
   }
@@ -187,65 +188,76 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       }
     }
   } else {
-    const int b = (warp - 2) >> 2;
+    // 16 compute warps: group b (which steps) x column half h (which 32 of the step's 64 queries); the TMEM lane
+    // quarter is fixed by warp % 4.  Four warps per scheduler keep the exp / pack chains of one step overlapped
+    // with the TMEM loads, barrier waits and staging of the others (two warps per scheduler ran at ~5k clk/pair).
+    const int cw = warp - 2;
+    const int b = (cw >> 2) & 1, h = cw >> 3;
     const int qd = warp & 3;
     const int row = qd * 32 + lane;                 // TMEM lane: key (S^T, dV, dK) or query within the pair (dQ)
-    const int gt = (int)tid - 64 - b * 128;          // 0..127 within the group
+    const int gt = h * 128 + (cw & 3) * 32 + lane;  // 0..255 within the group
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
-    const uint32_t s_addr = lane_base + (uint32_t)b * 128u;
+    const uint32_t s_addr = lane_base + (uint32_t)b * 128u + (uint32_t)h * 32u;
     const uint32_t pt_u32 = smem_u32(smem + SM::PT_OFF + b * B3_T128);
     const uint32_t ds_u32 = smem_u32(smem + SM::DS_OFF + b * B3_T128);
     const uint32_t vec_u32 = smem_u32(smem + SM::VEC_OFF) + (uint32_t)b * 384u * 4u;   // [3 bufs][64 lse | 64 delta]
     const float c = p.scale_log2;
     const float* lse_g = p.lse + ((long long)n * p.heads + head) * p.L;
     const float* del_g = p.delta + ((long long)n * p.heads + head) * p.L;
-    // lse / delta of this group's i-th step (query tile 2i + b), staged two steps ahead (see attention_bwd2.cu)
+    // lse / delta of this group's i-th step (query tile 2i + b), staged two steps ahead (see attention_bwd2.cu);
+    // threads 0..127 of the group carry them
     auto ld_vec = [&](int i) -> float {
       const int qi = (2 * i + b) * 64 + (gt & 63);
       if (gt < 64) return qi < p.L ? __ldg(lse_g + qi) : INFINITY;
       return qi < p.L ? __ldg(del_g + qi) : 0.f;
     };
     auto st_vec = [&](int i, float v) { sts32f(vec_u32 + (uint32_t)((i % 3) * 128 + gt) * 4u, v); };
-    // this group's half (32 columns) of the dQ tile of pair m -> smem staging -> TMA reduce-add into the global
-    // fp32 accumulator.  The caller guarantees (wait_group.read by thread 0 + a group barrier) that the previous
-    // bulk reduction has finished reading the staging buffer.
+    // this thread's 16 columns of the dQ tile of pair m (group b owns columns b*32.., half h 16 of them) -> smem
+    // staging -> TMA reduce-add into the global fp32 accumulator.
     const uint32_t stg_u32 = smem_u32(smem + SM::DQ_OFF + b * B3_T128);
     auto reduce_dq = [&](int m) {
       const int db = m & 1;
-      uint32_t a[32];
-      tmem_ld32(lane_base + 384u + (uint32_t)db * 64u + (uint32_t)b * 32u, a);
+      uint32_t a[16];
+      tmem_ld16(lane_base + 384u + (uint32_t)db * 64u + (uint32_t)b * 32u + (uint32_t)h * 16u, a);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&dq_free[db]);
+      // the previous bulk reduction (issued one whole step ago) has finished reading the staging buffer
+      if (gt == 0) { tma_store_wait_read(); mbar_arrive(&stg_free[b]); }
+      mbar_wait(&stg_free[b], (uint32_t)(m & 1));
 #pragma unroll
-      for (int g = 0; g < 8; ++g)
-        sts128(stg_u32 + (uint32_t)row * 128u + (uint32_t)((g ^ (row & 7)) << 4),
+      for (int g = 0; g < 4; ++g)
+        sts128(stg_u32 + (uint32_t)row * 128u + (uint32_t)(((h * 4 + g) ^ (row & 7)) << 4),
                make_uint4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3]));
       fence_proxy_async_smem();
-      named_bar_sync3(1 + b, 128);
+      named_bar_sync3(1 + b, 256);
       if (gt == 0) {
         tma_reduce_add_3d(&maps.dq, stg_u32, head * 64 + b * 32, m * 128, n);   // rows past L are clipped
         tma_store_commit();
       }
     };
-    st_vec(0, ld_vec(0));
-    float pend = n_pairs > 1 ? ld_vec(1) : 0.f;
+    float pend = 0.f;
+    if (h == 0) {
+      st_vec(0, ld_vec(0));
+      if (n_pairs > 1) pend = ld_vec(1);
+    }
     for (int m = 0; m < n_pairs; ++m) {
-      if (m + 1 < n_pairs) st_vec(m + 1, pend);
-      if (m + 2 < n_pairs) pend = ld_vec(m + 2);
-      if (gt == 0) tma_store_wait_read();   // staging buffer of reduce_dq is reusable after the barrier
-      named_bar_sync3(1 + b, 128);
-      const uint32_t ls_u32 = vec_u32 + (uint32_t)(m % 3) * 512u, dl_u32 = ls_u32 + 256u;
+      if (h == 0) {
+        if (m + 1 < n_pairs) st_vec(m + 1, pend);
+        if (m + 2 < n_pairs) pend = ld_vec(m + 2);
+      }
+      named_bar_sync3(1 + b, 256);
+      const uint32_t ls_u32 = vec_u32 + (uint32_t)(m % 3) * 512u + (uint32_t)h * 128u, dl_u32 = ls_u32 + 256u;
       mbar_wait(&sdp_full[b], (uint32_t)(m & 1));
       tc_fence_after();
-      uint32_t sr[64], dr[64];
-      tmem_ld32(s_addr, sr); tmem_ld32(s_addr + 32, sr + 32);
-      tmem_ld32(s_addr + 64, dr); tmem_ld32(s_addr + 96, dr + 32);
+      uint32_t sr[32], dr[32];
+      tmem_ld32(s_addr, sr);
+      tmem_ld32(s_addr + 64, dr);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&s_free[b]);
 #pragma unroll
-      for (int i4 = 0; i4 < 64; i4 += 4) {
+      for (int i4 = 0; i4 < 32; i4 += 4) {
         const float4 l4 = lds128f(ls_u32 + i4 * 4);   // warp-uniform address: broadcast LDS.128
         const float4 d4 = lds128f(dl_u32 + i4 * 4);
         const float lv[4] = {l4.x, l4.y, l4.z, l4.w}, dv[4] = {d4.x, d4.y, d4.z, d4.w};
@@ -260,7 +272,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       // dV/dK of this group's previous step and dQ of the previous pair have read P^T / dS^T
       if (m > 0) { mbar_wait(&pair_done[(m - 1) & 1], (uint32_t)(((m - 1) >> 1) & 1)); tc_fence_after(); }
 #pragma unroll
-      for (int g = 0; g < 8; ++g) {
+      for (int g = 0; g < 4; ++g) {
         uint4 u, w;
         u.x = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 0]), __uint_as_float(sr[8 * g + 1]));
         u.y = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 2]), __uint_as_float(sr[8 * g + 3]));
@@ -270,7 +282,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
         w.y = pack_f16x2(__uint_as_float(dr[8 * g + 2]), __uint_as_float(dr[8 * g + 3]));
         w.z = pack_f16x2(__uint_as_float(dr[8 * g + 4]), __uint_as_float(dr[8 * g + 5]));
         w.w = pack_f16x2(__uint_as_float(dr[8 * g + 6]), __uint_as_float(dr[8 * g + 7]));
-        const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)(8 * g));
+        const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)(8 * (h * 4 + g)));
         sts128(pt_u32 + off, u);
         sts128(ds_u32 + off, w);
       }
@@ -281,19 +293,15 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     }
     mbar_wait(&pair_done[(n_pairs - 1) & 1], (uint32_t)(((n_pairs - 1) >> 1) & 1));
     tc_fence_after();
-    if (gt == 0) tma_store_wait_read();
-    named_bar_sync3(1 + b, 128);
     reduce_dq(n_pairs - 1);
-    // group 0 writes dV, group 1 writes dK * scale
+    // group 0 writes dV, group 1 writes dK * scale; half h the columns h*32..
     const int ki = kv0 + row;
     const bool valid = ki < p.L;
-    __half* dst = p.dqkv + ((long long)n * p.L + ki) * p.lddqkv + (b == 0 ? vc : kc);
+    __half* dst = p.dqkv + ((long long)n * p.L + ki) * p.lddqkv + (b == 0 ? vc : kc) + h * 32;
     const float sc = b == 0 ? 1.f : p.scale;
-    const uint32_t acc_addr = lane_base + 256u + (uint32_t)b * 64u;
-#pragma unroll
-    for (int c0 = 0; c0 < 64; c0 += 32) {
+    {
       uint32_t a[32];
-      tmem_ld32(acc_addr + c0, a);   // warp-collective: outside the row guard
+      tmem_ld32(lane_base + 256u + (uint32_t)b * 64u + (uint32_t)h * 32u, a);   // warp-collective: outside the row guard
       tmem_ld_wait();
       if (valid) {
 #pragma unroll
@@ -303,7 +311,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
           o.y = pack_f16x2(__uint_as_float(a[8 * g + 2]) * sc, __uint_as_float(a[8 * g + 3]) * sc);
           o.z = pack_f16x2(__uint_as_float(a[8 * g + 4]) * sc, __uint_as_float(a[8 * g + 5]) * sc);
           o.w = pack_f16x2(__uint_as_float(a[8 * g + 6]) * sc, __uint_as_float(a[8 * g + 7]) * sc);
-          *reinterpret_cast<uint4*>(dst + c0 + 8 * g) = o;
+          *reinterpret_cast<uint4*>(dst + 8 * g) = o;
         }
       }
     }

@@ -14,6 +14,66 @@ import torch.nn as nn
 from .unet import UNetModel
 
 
+POS_CONV_TOEPLITZ_MAX_T = 32
+
+
+def _pos_conv_short_sequence(mod, hidden_states):
+    """Wav2Vec2PositionalConvEmbedding.forward (HF transformers; third-party arithmetic, unchanged) for short
+    sequences.  train.py / test.py feed 4000-sample windows = 12 frames, but the grouped Conv1d(768, 768, k=128,
+    pad=64, groups=16) makes cuDNN run its direct grouped kernels over all 128 taps: 8.9 ms forward + 17 ms
+    backward per step on B200 (profiles/r1_launch_list.md), almost all of it multiplying zero padding.  For
+    T <= POS_CONV_TOEPLITZ_MAX_T the same sums are one batched GEMM per group against the Toeplitz matrix of the
+    taps that can touch a real frame:  out[b, co, t] = sum_{ci, t'} w[co, ci, t' - t + pad] x[b, ci, t']."""
+    conv = mod.conv
+    B, T, C = hidden_states.shape
+    K, pad, G = conv.kernel_size[0], conv.padding[0], conv.groups
+    if (T > POS_CONV_TOEPLITZ_MAX_T or conv.stride[0] != 1 or conv.dilation[0] != 1 or K % 2 != 0 or pad != K // 2
+            or T - 1 > pad or conv.padding_mode != "zeros"):
+        return mod._b2d_stock_forward(hidden_states)
+    cg = C // G
+    w = conv.weight                                                   # (C, C/G, K), weight-norm evaluated here
+    tt = torch.arange(T, device=w.device)
+    idx = tt[:, None] - tt[None, :] + pad                             # [t', t] -> tap, always inside [0, K)
+    m = w[:, :, idx]                                                  # (C, cg, T', T)
+    m = m.view(G, cg, cg, T, T).permute(0, 2, 3, 1, 4).reshape(G, cg * T, cg * T)      # [g][(ci, t')][(co, t)]
+    x = hidden_states.reshape(B, T, G, cg).permute(2, 0, 3, 1).reshape(G, B, cg * T)   # [g][b][(ci, t')]
+    y = torch.bmm(x, m.to(x.dtype) if not torch.is_autocast_enabled() else m)          # (G, B, (co, t))
+    y = y.view(G, B, cg, T).permute(1, 3, 0, 2).reshape(B, T, C)
+    if conv.bias is not None:
+        y = y + conv.bias.to(y.dtype)
+    return mod.activation(y)
+
+
+def _conv1d_single_channel(conv, x):
+    """nn.Conv1d forward for in_channels == 1 (wav2vec2 feature_extractor.conv_layers[0]: Conv1d(1, 512, k=10,
+    stride=5) over the raw waveform).  cuDNN serves this shape with its direct grouped kernels -- 8.9 ms forward and
+    17 ms backward per step on B200 for 2 GFLOP (profiles/r1_launch_list.md); as a strided window view times
+    the (k, C_out) weight it is one small GEMM."""
+    if (conv.in_channels != 1 or conv.groups != 1 or conv.dilation[0] != 1 or conv.padding[0] != 0
+            or x.dim() != 3):
+        return conv._b2d_stock_forward(x)
+    cols = x[:, 0].unfold(-1, conv.kernel_size[0], conv.stride[0])           # (B, T_out, k) view
+    y = torch.matmul(cols, conv.weight[:, 0, :].t())                          # (B, T_out, C_out)
+    if conv.bias is not None:
+        y = y + conv.bias.to(y.dtype)
+    return y.transpose(1, 2)
+
+
+def patch_pos_conv(wav2vec2):
+    """Route the positional conv embedding of a HF Wav2Vec2Model through _pos_conv_short_sequence and the
+    single-channel waveform conv through _conv1d_single_channel (same arithmetic, library GEMMs)."""
+    import types
+    pce = wav2vec2.encoder.pos_conv_embed
+    if not hasattr(pce, "_b2d_stock_forward"):
+        pce._b2d_stock_forward = pce.forward
+        pce.forward = types.MethodType(_pos_conv_short_sequence, pce)
+    conv0 = wav2vec2.feature_extractor.conv_layers[0].conv
+    if conv0.in_channels == 1 and not hasattr(conv0, "_b2d_stock_forward"):
+        conv0._b2d_stock_forward = conv0.forward
+        conv0.forward = types.MethodType(_conv1d_single_channel, conv0)
+    return wav2vec2
+
+
 class Wav2Vec2Encoder(nn.Module):
     """unet_audio.py:10-18.  `from_pretrained` needs the checkpoint in the HF cache; pass
     `pretrained=False` (or set B2D_WAV2VEC2_RANDOM_INIT=1) for a random-init wav2vec2-base."""
@@ -29,6 +89,8 @@ class Wav2Vec2Encoder(nn.Module):
             self.wav2vec2 = Wav2Vec2Model.from_pretrained(model_name, cache_dir=cache_dir)
         else:
             self.wav2vec2 = Wav2Vec2Model(Wav2Vec2Config())
+        if os.environ.get("B2D_WAV2VEC2_STOCK", "0") != "1":     # A/B switch: leave the HF module untouched
+            patch_pos_conv(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

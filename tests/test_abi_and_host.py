@@ -1,5 +1,6 @@
 """CPU: the C-ABI library loads and exports every symbol include/b2d.h declares (no compute calls),
 and the host-side logic (weight packing, gradient layout, state_dict keys, error behaviour)."""
+import copy
 import os
 import re
 
@@ -167,3 +168,59 @@ def test_sampler_index_errors_match_reference_behaviour():
         s.sample_prev_timestep(x, x, torch.tensor([499]))
     with pytest.raises(RuntimeError):          # a (B,) t with B > 1 does not broadcast in the reference either
         s.sample_prev_timestep(x, x, torch.tensor([1, 2]))
+
+
+# ------------------------------------------------------------------ wav2vec2 positional conv, short sequences
+@pytest.mark.parametrize("T", [1, 12, 32, 40])
+def test_pos_conv_short_sequence_matches_stock_module(T):
+    """unet_audio._pos_conv_short_sequence restates HF's Wav2Vec2PositionalConvEmbedding.forward as one batched
+    GEMM per group for T <= 32 frames (train.py feeds 12): same outputs and gradients as the stock module,
+    fp32 tolerance 1e-5 relative; T = 40 takes the stock path."""
+    import types
+    from transformers import Wav2Vec2Config
+    from transformers.models.wav2vec2.modeling_wav2vec2 import Wav2Vec2PositionalConvEmbedding
+    from lipreading_video_generation_b200 import unet_audio as UA
+
+    torch.manual_seed(0)
+    cfg = Wav2Vec2Config(hidden_size=64, num_conv_pos_embeddings=128, num_conv_pos_embedding_groups=16)
+    stock = Wav2Vec2PositionalConvEmbedding(cfg)
+    fast = copy.deepcopy(stock)
+    fast._b2d_stock_forward = fast.forward
+    fast.forward = types.MethodType(UA._pos_conv_short_sequence, fast)
+    x = torch.randn(5, T, 64)
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    y1, y2 = stock(x1), fast(x2)
+    assert y1.shape == y2.shape == (5, T, 64)
+    r = torch.randn_like(y1)
+    (y1 * r).sum().backward()
+    (y2 * r).sum().backward()
+
+    def rel(a, b):
+        return float((a - b).norm() / b.norm())
+    assert rel(y2, y1) <= 1e-5
+    assert rel(x2.grad, x1.grad) <= 1e-5
+    for (n1, p1), (_, p2) in zip(stock.named_parameters(), fast.named_parameters()):
+        assert rel(p2.grad, p1.grad) <= 1e-5, n1
+
+
+def test_single_channel_conv1d_matches_stock_module():
+    """unet_audio._conv1d_single_channel (the waveform conv of the wav2vec2 feature extractor as a window view
+    times the weight) against nn.Conv1d: outputs and gradients, fp32 tolerance 1e-5 relative."""
+    import types
+    from lipreading_video_generation_b200 import unet_audio as UA
+
+    torch.manual_seed(0)
+    for bias in (False, True):
+        stock = torch.nn.Conv1d(1, 32, kernel_size=10, stride=5, bias=bias)
+        fast = copy.deepcopy(stock)
+        fast._b2d_stock_forward = fast.forward
+        fast.forward = types.MethodType(UA._conv1d_single_channel, fast)
+        x = torch.randn(4, 1, 403)
+        y1, y2 = stock(x), fast(x)
+        assert y1.shape == y2.shape == (4, 32, 79)
+        r = torch.randn_like(y1)
+        (y1 * r).sum().backward()
+        (y2 * r).sum().backward()
+        assert float((y2 - y1).norm() / y1.norm()) <= 1e-5
+        for (n1, p1), (_, p2) in zip(stock.named_parameters(), fast.named_parameters()):
+            assert float((p2.grad - p1.grad).norm() / p1.grad.norm()) <= 1e-5, n1
