@@ -127,6 +127,16 @@ __device__ __forceinline__ float fast_exp2(float x) {
   return y;
 }
 
-__device__ __forceinline__ float silu_f(float x) { return x / (1.0f + __expf(-x)); }
+// sigmoid with one MUFU.EX2 and one MUFU.RCP.  (1.0f / (1.0f + __expf(-z)) compiles to an IEEE division with a
+// slow-path branch plus the denormal-range rescale of ex2: ~26 instructions per element measured in gn_apply,
+// which made the GroupNorm kernels issue-bound at 65 % instead of HBM-bound; profiles/r1_groupnorm.md.)
+__device__ __forceinline__ float fast_sigmoid(float z) {
+  float r;
+  const float e = fast_exp2(-1.4426950408889634f * z);
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return r;
+}
+
+__device__ __forceinline__ float silu_f(float x) { return x * fast_sigmoid(x); }
 
 }  // namespace b2d

@@ -173,7 +173,7 @@ gn_apply_kernel(GnSrc s, int HW, int Ctot, const double* __restrict__ sums, cons
 
 // ------------------------------------------------------------------ backward: per-(sample, channel) sums
 // ab: fp32 [N][Ctot][2] = (sum dyh, sum dyh * xhat) with dyh = dy * act'(z) (* dropout mask), zeroed by caller.
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 gn_bwd_reduce_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
                      const float* __restrict__ mean, const float* __restrict__ rstd,
                      const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
@@ -188,11 +188,14 @@ gn_bwd_reduce_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
   for (int i = threadIdx.x; i < 2 * Ctot; i += blockDim.x) sh[i] = 0.f;
   __syncthreads();
   const int c = v * 8;
-  float g[8], b[8], mu[8], rs[8], A[8], B[8];
+  // z = xhat * gamma + beta = x * rg + bb;  sum dyh * xhat = rstd * (sum dyh * x) - mean * rstd * (sum dyh):
+  // two folded constants per channel in the loop instead of four keeps the kernel at 3 blocks / SM
+  float rg[8], bb[8], A[8], B[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    g[i] = __ldg(gamma + c + i); b[i] = __ldg(beta + c + i);
-    mu[i] = __ldg(mean + n * 32 + (c + i) / cpg); rs[i] = __ldg(rstd + n * 32 + (c + i) / cpg);
+    const float rs_ = __ldg(rstd + n * 32 + (c + i) / cpg), mu_ = __ldg(mean + n * 32 + (c + i) / cpg);
+    rg[i] = rs_ * __ldg(gamma + c + i);
+    bb[i] = fmaf(-mu_, rg[i], __ldg(beta + c + i));
     A[i] = 0.f; B[i] = 0.f;
   }
   const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
@@ -223,19 +226,22 @@ gn_bwd_reduce_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const float xh = (x[i] - mu[i]) * rs[i];
       float dh = d[i];
       if (act) {
-        const float z = fmaf(xh, g[i], b[i]);
-        const float sg = 1.0f / (1.0f + __expf(-z));
+        const float z = fmaf(x[i], rg[i], bb[i]);
+        const float sg = fast_sigmoid(z);
         dh *= sg * (1.0f + z * (1.0f - sg));
       }
-      A[i] += dh; B[i] = fmaf(dh, xh, B[i]);
+      A[i] += dh; B[i] = fmaf(dh, x[i], B[i]);
     }
     }
   }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) { atomicAdd(&sh[c + i], A[i]); atomicAdd(&sh[Ctot + c + i], B[i]); }
+  for (int i = 0; i < 8; ++i) {
+    const float rs_ = __ldg(rstd + n * 32 + (c + i) / cpg), mu_ = __ldg(mean + n * 32 + (c + i) / cpg);
+    atomicAdd(&sh[c + i], A[i]);
+    atomicAdd(&sh[Ctot + c + i], rs_ * (B[i] - mu_ * A[i]));
+  }
   __syncthreads();
   for (int i = threadIdx.x; i < Ctot; i += blockDim.x) {
     atomicAdd(&ab[((long long)n * Ctot + i) * 2 + 0], sh[i]);
@@ -253,7 +259,7 @@ struct GnBwdOut {
   int add_a_full;  // add_a spans all C1+C2 channels (also added to dx2)
 };
 
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 3)
 gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
                     const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
@@ -279,13 +285,16 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
   const int prow = threadIdx.x / V;
   const int rows = blockDim.x / V;
   const int c = v * 8;
-  float g[8], b[8], mu[8], rs[8], m1[8], m2[8];
+  // z = x * rg + bb;  dx = rstd * (dyh * gamma - s1 - xhat * s2) = dyh * rg + x * pp + qq
+  float rg[8], bb[8], pp[8], qq[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     const int gi = (c + i) / cpg;
-    g[i] = __ldg(gamma + c + i); b[i] = __ldg(beta + c + i);
-    mu[i] = __ldg(mean + n * 32 + gi); rs[i] = __ldg(rstd + n * 32 + gi);
-    m1[i] = s1[gi]; m2[i] = s2[gi];
+    const float rs_ = __ldg(rstd + n * 32 + gi), mu_ = __ldg(mean + n * 32 + gi);
+    rg[i] = rs_ * __ldg(gamma + c + i);
+    bb[i] = fmaf(-mu_, rg[i], __ldg(beta + c + i));
+    pp[i] = -rs_ * rs_ * s2[gi];
+    qq[i] = -mu_ * pp[i] - rs_ * s1[gi];
   }
   const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
   const bool first = c < s.C1;
@@ -320,14 +329,13 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
     }
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      const float xh = (x[i] - mu[i]) * rs[i];
       float dh = d[i];
       if (act) {
-        const float z = fmaf(xh, g[i], b[i]);
-        const float sg = 1.0f / (1.0f + __expf(-z));
+        const float z = fmaf(x[i], rg[i], bb[i]);
+        const float sg = fast_sigmoid(z);
         dh *= sg * (1.0f + z * (1.0f - sg));
       }
-      x[i] = rs[i] * (dh * g[i] - m1[i] - xh * m2[i]);
+      x[i] = fmaf(dh, rg[i], fmaf(x[i], pp[i], qq[i]));
     }
     if (has_a) { float t[8]; unpack8(ra[u], t);
 #pragma unroll
