@@ -11,6 +11,11 @@
 // MN-major SWIZZLE_128B descriptor (SBO = 1024 B to the next 8 pixels, LBO = 16 KB to the next
 // 64-channel block).  The X box is shifted by the tap and zero-filled out of bounds exactly as in
 // the forward kernel, so padding and stride-2 phases are handled identically.
+//
+// Cout == 64 ("swap" mode): dy fills only half of an M = 128 tile, and these layers are bound by the L2 -> smem
+// traffic per stage (48 KB per 256 tensor-pipe cycles), not by the MMA.  The operands swap roles instead: two
+// shifted X blocks -- consecutive (tap, 64-channel block) pairs -- form the M = 128 operand and the single dy
+// block is the N = 64 operand, D[(x block, ci)][co]: the same bytes per stage carry twice the useful FLOPs.
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
@@ -31,7 +36,9 @@ struct WgradParams {
   int pixel_tiles;       // ceil(N*Ho*Wo / 128)
   int Cout;
   int co_tiles, ci_tiles, BNci;
-  int co_blocks;         // 64-channel dy blocks loaded per stage (1 when Cout == 64: loaded twice)
+  int co_blocks;         // 64-channel dy blocks loaded per stage
+  int swap;              // Cout == 64: M = two X blocks, N = dy
+  int cib, xb_total;     // swap mode: 64-channel X blocks per tap, taps * cib
   float* dw;
 };
 
@@ -53,11 +60,12 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
   uint32_t* tmem_slot = (uint32_t*)(acc_bar + 1);
 
   // work item decode: blockIdx.x = (tap * co_tiles + co_t) * ci_tiles + ci_t
+  // (swap mode: blockIdx.x = pair of consecutive X blocks, X block = tap * cib + ci block)
   int w = blockIdx.x;
   const int ci_t = w % p.ci_tiles; w /= p.ci_tiles;
   const int co_t = w % p.co_tiles; w /= p.co_tiles;
   const int tap = w;
-  const int co0 = co_t * 128;
+  const int co0 = p.swap ? 0 : co_t * 128;
   const int ci0 = ci_t * p.BNci;
   const int split = blockIdx.y, nsplit = gridDim.y;
   const int my_iters = (p.pixel_tiles - split + nsplit - 1) / nsplit;
@@ -77,10 +85,28 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
   if (warp == 0) {
     if (elect_one()) {
       const int pad = p.ksize >> 1;
-      const int dy_ = tap / p.ksize, dx_ = tap - dy_ * p.ksize;
-      int hoff, wc, ph = 0;
-      if (p.stride == 1) { hoff = dy_ - pad; wc = dx_ - pad; }
-      else { ph = ((dy_ + 1) & 1) * 2 + ((dx_ + 1) & 1); hoff = (dy_ == 0 ? -1 : 0); wc = (dx_ == 0 ? -1 : 0); }
+      // tap -> (row offset, column offset, stride-2 phase map)
+      auto tap_geom = [&](int t, int& hoff, int& wc, int& ph) {
+        const int dy_ = t / p.ksize, dx_ = t - dy_ * p.ksize;
+        ph = 0;
+        if (p.stride == 1) { hoff = dy_ - pad; wc = dx_ - pad; }
+        else { ph = ((dy_ + 1) & 1) * 2 + ((dx_ + 1) & 1); hoff = (dy_ == 0 ? -1 : 0); wc = (dx_ == 0 ? -1 : 0); }
+      };
+      int hoff[2], wc[2], ph[2], cx[2];
+      if (p.swap) {
+        for (int j = 0; j < 2; ++j) {
+          int xb = 2 * (int)blockIdx.x + j;
+          if (xb >= p.xb_total) xb = p.xb_total - 1;    // odd block count: the last pair repeats its block
+          tap_geom(xb / p.cib, hoff[j], wc[j], ph[j]);
+          cx[j] = (xb % p.cib) * 64;
+        }
+      } else {
+        tap_geom(tap, hoff[0], wc[0], ph[0]);
+      }
+      auto load_x = [&](uint8_t* dst, uint64_t* bar, int c, int j, int h0, int img0) {
+        if (c < p.C1) tma_load_4d(dst, &maps.x[ph[j]], bar, c, wc[j], h0 + hoff[j], img0);
+        else          tma_load_4d(dst, &maps.x2, bar, c - p.C1, wc[j], h0 + hoff[j], img0);
+      };
       for (int it = 0; it < my_iters; ++it) {
         const int tile = split + it * nsplit;
         int img0, h0;
@@ -91,19 +117,21 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
         mbar_wait(&empty_bar[s], par ^ 1u);
         uint8_t* base = smem + (size_t)s * stage_bytes;
         mbar_expect_tx(&full_bar[s], stage_bytes);
-        // A: dy blocks (two 64-channel blocks; the same block twice when Cout == 64)
-        tma_load_4d(base, &maps.dy, &full_bar[s], co0, 0, h0, img0);
-        tma_load_4d(base + BLK, &maps.dy, &full_bar[s], p.co_blocks == 2 ? co0 + 64 : co0, 0, h0, img0);
-        // B: shifted X blocks
-        for (int j = 0; j < nb; ++j) {
-          const int c = ci0 + j * 64;
-          if (c < p.C1) tma_load_4d(base + (2 + j) * BLK, &maps.x[ph], &full_bar[s], c, wc, h0 + hoff, img0);
-          else          tma_load_4d(base + (2 + j) * BLK, &maps.x2, &full_bar[s], c - p.C1, wc, h0 + hoff, img0);
+        if (p.swap) {
+          // A: two shifted X blocks; B: the dy block
+          load_x(base, &full_bar[s], cx[0], 0, h0, img0);
+          load_x(base + BLK, &full_bar[s], cx[1], 1, h0, img0);
+          tma_load_4d(base + 2 * BLK, &maps.dy, &full_bar[s], 0, 0, h0, img0);
+        } else {
+          // A: two 64-channel dy blocks; B: shifted X blocks
+          tma_load_4d(base, &maps.dy, &full_bar[s], co0, 0, h0, img0);
+          tma_load_4d(base + BLK, &maps.dy, &full_bar[s], co0 + 64, 0, h0, img0);
+          for (int j = 0; j < nb; ++j) load_x(base + (2 + j) * BLK, &full_bar[s], ci0 + j * 64, 0, h0, img0);
         }
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc(128, p.BNci, 1, 1, FMT_F16, FMT_F16);  // A = dy (gradient, bf16), B = x (forward, fp16)
+    const uint32_t idesc = make_idesc(128, p.BNci, 1, 1, FMT_F16, FMT_F16);  // both operands MN-major
     for (int it = 0; it < my_iters; ++it) {
       const int s = it % WG_STAGES;
       const uint32_t par = (uint32_t)((it / WG_STAGES) & 1);
@@ -124,23 +152,40 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
     }
   } else {
     const int q = warp & 3;
-    const int row = q * 32 + lane;  // output channel within the tile
-    const int co = co0 + row;
-    const bool valid = (my_iters > 0) && (co < p.Cout) && (p.co_blocks == 2 || row < 64);
+    const int row = q * 32 + lane;  // accumulator row: output channel, or (X block, input channel) in swap mode
     if (my_iters > 0) {
       mbar_wait(acc_bar, 0);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
       const long long Ktot = (long long)p.taps * p.Ctot;
-      for (int c0 = 0; c0 < p.BNci; c0 += 16) {
-        uint32_t r[16];
-        __syncwarp();
-        tmem_ld16(taddr + (uint32_t)c0, r);
-        tmem_ld_wait();
-        if (valid) {
-          float* dst = p.dw + (long long)co * Ktot + (long long)tap * p.Ctot + ci0 + c0;
+      if (p.swap) {
+        const int xb = 2 * (int)blockIdx.x + (row >> 6);
+        const bool valid = xb < p.xb_total;
+        // dw[co][tap][ci]: lanes hold consecutive ci -> each atomic instruction covers 128 contiguous bytes
+        float* dst = p.dw + (long long)(xb / p.cib) * p.Ctot + (xb % p.cib) * 64 + (row & 63);
+        for (int c0 = 0; c0 < 64; c0 += 16) {
+          uint32_t r[16];
+          __syncwarp();
+          tmem_ld16(taddr + (uint32_t)c0, r);
+          tmem_ld_wait();
+          if (valid) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) atomicAdd(dst + j, __uint_as_float(r[j]));
+            for (int j = 0; j < 16; ++j) atomicAdd(dst + (long long)(c0 + j) * Ktot, __uint_as_float(r[j]));
+          }
+        }
+      } else {
+        const int co = co0 + row;
+        const bool valid = co < p.Cout;
+        for (int c0 = 0; c0 < p.BNci; c0 += 16) {
+          uint32_t r[16];
+          __syncwarp();
+          tmem_ld16(taddr + (uint32_t)c0, r);
+          tmem_ld_wait();
+          if (valid) {
+            float* dst = p.dw + (long long)co * Ktot + (long long)tap * p.Ctot + ci0 + c0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) atomicAdd(dst + j, __uint_as_float(r[j]));
+          }
         }
       }
     }
@@ -212,13 +257,16 @@ extern "C" int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream) {
   p.pixel_tiles = (int)((total_pixels + 127) / 128);
   p.Cout = a->Cout;
   p.co_tiles = (a->Cout + 127) / 128;
-  p.co_blocks = (a->Cout % 128 == 0) ? 2 : 1;
-  B2D_REQUIRE(p.co_blocks == 2 || a->Cout == 64, B2D_ERR_SHAPE, "wgrad: Cout=%d must be 64 or a multiple of 128", a->Cout);
+  p.co_blocks = 2;
+  p.swap = a->Cout == 64;
+  B2D_REQUIRE(p.swap || a->Cout % 128 == 0, B2D_ERR_SHAPE, "wgrad: Cout=%d must be 64 or a multiple of 128", a->Cout);
   // a 128-wide ci tile must not straddle the two sources unless both are multiples of 128
-  p.BNci = (a->C1 % 128 == 0 && C2 % 128 == 0) ? 128 : 64;
+  p.BNci = (!p.swap && a->C1 % 128 == 0 && C2 % 128 == 0) ? 128 : 64;
   p.ci_tiles = p.Ctot / p.BNci;
+  p.cib = p.Ctot / 64;
+  p.xb_total = p.taps * p.cib;
   p.dw = a->dw;
-  const int items = p.taps * p.co_tiles * p.ci_tiles;
+  const int items = p.swap ? (p.xb_total + 1) / 2 : p.taps * p.co_tiles * p.ci_tiles;
   int nsplit = (2 * num_sms() + items - 1) / items;
   if (nsplit > p.pixel_tiles) nsplit = p.pixel_tiles;
   if (nsplit < 1) nsplit = 1;

@@ -178,7 +178,9 @@ def test_conv2d_head_writes_fp32_nchw_and_small_cout():
 
 @pytest.mark.parametrize("N,H,C1,C2,Cout,k,stride", [
     (2, 32, 64, 0, 64, 3, 1), (2, 16, 128, 128, 128, 3, 1), (2, 32, 64, 0, 64, 3, 2), (4, 8, 256, 128, 256, 1, 1),
-    (3, 16, 128, 0, 384, 1, 1)])
+    (3, 16, 128, 0, 384, 1, 1),
+    # Cout == 64 takes the wgrad swap mode (X blocks paired into M): odd / even block counts, both sources, 1x1
+    (2, 16, 128, 64, 64, 3, 1), (2, 16, 128, 0, 64, 1, 1), (2, 16, 64, 0, 64, 1, 1), (2, 64, 192, 64, 64, 3, 1)])
 def test_conv2d_dgrad_and_wgrad_vs_autograd(N, H, C1, C2, Cout, k, stride):
     """dgrad = the same implicit-GEMM kernel on dY with flipped weights; wgrad = MN-major operands, fp32 atomics."""
     from lipreading_video_generation_b200 import ops
