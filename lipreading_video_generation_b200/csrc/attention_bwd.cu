@@ -44,24 +44,48 @@ __device__ __forceinline__ void named_bar_sync(int id, int count) {
 __global__ void __launch_bounds__(256)
 attn_delta_kernel(const __half* __restrict__ o, long long ldo, const __half* __restrict__ d_o,
                   long long lddo, int N, int L, int heads, int ch, float* __restrict__ delta) {
-  // one warp per (n, l, head)
-  const long long w = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  // ch / 8 lanes per (n, l, head) row, one 16-byte load of O and of dO each; two rows per thread in flight
+  const int G = ch >> 3;                       // 8, 16 or 32 lanes per row
+  const int rows_per_warp = 32 / G;
   const int lane = threadIdx.x & 31;
+  const int sub = lane / G, li = lane - sub * G;
   const long long total = (long long)N * L * heads;
-  if (w >= total) return;
-  const int h = (int)(w % heads);
-  const long long nl = w / heads;
-  const __half* po = o + nl * ldo + h * ch;
-  const __half* pd = d_o + nl * lddo + h * ch;
-  float acc = 0.f;
-  for (int c = lane * 2; c < ch; c += 64) {
-    const float2 a = unpack_f16x2(*reinterpret_cast<const uint32_t*>(po + c));   // O: forward tensor, fp16
-    const float2 b = unpack_f16x2(*reinterpret_cast<const uint32_t*>(pd + c));
-    acc = fmaf(a.x, b.x, acc); acc = fmaf(a.y, b.y, acc);
+  const long long warp_id = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long r0 = warp_id * (2 * rows_per_warp) + sub;
+  float acc[2] = {0.f, 0.f};
+  uint4 ra[2], rb[2];
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const long long r = r0 + u * rows_per_warp;
+    if (r < total) {
+      const int h = (int)(r % heads);
+      const long long nl = r / heads;
+      ra[u] = ldg_nc_u4(o + nl * ldo + h * ch + li * 8);
+      rb[u] = ldg_nc_u4(d_o + nl * lddo + h * ch + li * 8);
+    }
   }
-  acc = warp_sum(acc);
-  const int n = (int)(nl / L), l = (int)(nl - (long long)n * L);
-  if (lane == 0) delta[((long long)n * heads + h) * L + l] = acc;
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    const long long r = r0 + u * rows_per_warp;
+    if (r < total) {
+      float a[8], b[8];
+      unpack8(ra[u], a);
+      unpack8(rb[u], b);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) acc[u] = fmaf(a[i], b[i], acc[u]);
+    }
+  }
+#pragma unroll
+  for (int u = 0; u < 2; ++u) {
+    for (int off = G >> 1; off > 0; off >>= 1) acc[u] += __shfl_xor_sync(0xffffffffu, acc[u], off);
+    const long long r = r0 + u * rows_per_warp;
+    if (li == 0 && r < total) {
+      const int h = (int)(r % heads);
+      const long long nl = r / heads;
+      const int n = (int)(nl / L), l = (int)(nl - (long long)n * L);
+      delta[((long long)n * heads + h) * L + l] = acc[u];
+    }
+  }
 }
 
 // ------------------------------------------------------------------ kernel A: dK, dV
@@ -534,7 +558,8 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
   p.lse = lse; p.delta = delta_ws;
   p.dqkv = (__half*)dqkv; p.lddqkv = lddqkv;
   {
-    const long long warps = (long long)N * L * heads;
+    const long long rows_per_warp = 2 * (32 / (ch >> 3));
+    const long long warps = ((long long)N * L * heads + rows_per_warp - 1) / rows_per_warp;
     const long long blocks = (warps * 32 + 255) / 256;
     attn_delta_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
         (const __half*)out, ldo, (const __half*)d_out, lddo, N, L, heads, ch, delta_ws);

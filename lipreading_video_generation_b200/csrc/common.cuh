@@ -120,6 +120,12 @@ __device__ __forceinline__ void store8_fmt(void* p, const float* v, int fmt) {
   *reinterpret_cast<uint4*>(p) = u;
 }
 
+// 8 packed fp16 -> fp32
+__device__ __forceinline__ void unpack8(const uint4& u, float* v) {
+  float2 a = unpack_f16x2(u.x), b = unpack_f16x2(u.y), c = unpack_f16x2(u.z), d = unpack_f16x2(u.w);
+  v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+}
+
 // one MUFU.EX2 (exp2f() adds a denormal-range pre/post scale: FSETP + 2 FMUL per element)
 __device__ __forceinline__ float fast_exp2(float x) {
   float y;

@@ -213,11 +213,20 @@ colsum_kernel(const __half* __restrict__ x, long long ld, int c_off, int C, int 
   const int rows = blockDim.x / V;
   const int prow = threadIdx.x / V;
   float a[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
-    float t[8];
-    ld8(x + ((long long)n * HW + pix) * ld + c_off + v * 8, t);
+  const int step = gridDim.x * rows;
+  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 4 * step) {   // four 16-byte loads in flight
+    uint4 raw[4];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) a[j] += t[j];
+    for (int u = 0; u < 4; ++u)
+      if (pix0 + u * step < HW) raw[u] = ldg_nc_u4(x + ((long long)n * HW + pix0 + u * step) * ld + c_off + v * 8);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (pix0 + u * step >= HW) continue;
+      float t[8];
+      unpack8(raw[u], t);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) a[j] += t[j];
+    }
   }
 #pragma unroll
   for (int j = 0; j < 8; ++j) atomicAdd(&sh[v * 8 + j], a[j]);
@@ -226,12 +235,29 @@ colsum_kernel(const __half* __restrict__ x, long long ld, int c_off, int C, int 
 }
 
 // out[c] += sum_r in[r][c]
-__global__ void reduce_rows_kernel(const float* __restrict__ in, int R, int C, long long ld, float* __restrict__ out) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// block = 32 columns x 8 row lanes; each lane sums every 8th row with four loads in flight
+__global__ void __launch_bounds__(256)
+reduce_rows_kernel(const float* __restrict__ in, int R, int C, long long ld, float* __restrict__ out) {
+  __shared__ float sh[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
   float a = 0.f;
-  for (int r = 0; r < R; ++r) a += in[(long long)r * ld + c];
-  out[c] += a;
+  if (c < C) {
+    for (int r0 = ty; r0 < R; r0 += 32) {
+      float t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = (r0 + 8 * u < R) ? __ldg(in + (long long)(r0 + 8 * u) * ld + c) : 0.f;
+      a += (t[0] + t[1]) + (t[2] + t[3]);
+    }
+  }
+  sh[ty][tx] = a;
+  __syncthreads();
+  if (ty == 0 && c < C) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sh[i][tx];
+    out[c] += t;
+  }
 }
 
 // ------------------------------------------------------------------ timestep embedding (utils.py:140-158)
@@ -396,7 +422,7 @@ extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, in
 }
 extern "C" int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream) {
   B2D_REQUIRE(in && out && R > 0 && C > 0, B2D_ERR_SHAPE, "reduce_rows: bad arguments");
-  reduce_rows_kernel<<<(C + 127) / 128, 128, 0, (cudaStream_t)stream>>>(in, R, C, ld, out);
+  reduce_rows_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)stream>>>(in, R, C, ld, out);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
