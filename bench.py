@@ -343,8 +343,10 @@ def main():
     # per-class breakdown (~530 event pairs per step, which costs 2-3 ms of step time) runs in an untimed pass below
     with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
         e0.record()
+        h0 = time.perf_counter()
         for _ in range(a.steps):
             step(x0, cond, audio, t_dev)
+        host_ms = (time.perf_counter() - h0) * 1e3 / a.steps     # host time to enqueue one step (no sync inside)
         e1.record()
         barrier()
     ms = e0.elapsed_time(e1) / a.steps
@@ -408,7 +410,7 @@ def main():
            "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
            "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 3), "unit": "clips/s", "h2d_bytes_per_step": h2d,
                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
-           "gpu_launches": int(launches), "roofline": roof,
+           "gpu_launches": int(launches), "host_enqueue_ms_per_step": round(host_ms, 3), "roofline": roof,
            "step_tflops_algorithmic": round(train_tflop / (ms / 1000.0), 1),
            "step_frac_of_sustained_peak": round(train_tflop / (ms / 1000.0) / sustained, 4),
            "cpu_baseline": {"value": round(cpu_v, 5), "unit": "clips/s", "cores": cores, "kind": "port",

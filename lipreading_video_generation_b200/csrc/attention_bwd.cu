@@ -567,7 +567,7 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
   }
   static const bool force_v1 = getenv("B2D_ATTN_BWD_V1") != nullptr;   // A/B timing of the single-tile kernels
   static const bool force_v2 = getenv("B2D_ATTN_BWD_V2") != nullptr;   // A/B timing of the two-kernel variant
-  if (!force_v1 && !force_v2 && ch == 64 && L > 128)
+  if (!force_v1 && !force_v2 && ch == 64 && L > 128 && L % 4 == 0)   // L % 4: 16-byte pitch of the lse / delta maps
     return attention_bwd3_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws,
                                    delta_ws + (long long)N * heads * L, dqkv, lddqkv, stream);
   if (!force_v1 && ch == 64 && L > 128)

@@ -38,6 +38,8 @@ struct AttnBwd3Maps {
   CUtensorMap qkv64;   // box (64, 64, 1)  on qkv : streamed Q_j
   CUtensorMap do64;    // box (64, 64, 1)  on dO  : streamed dO_j
   CUtensorMap dq;      // box (32, 128, 1) on the fp32 dQ accumulator (N, L, heads*64)
+  CUtensorMap lse;     // box (64, 1) on lse   (L, N*heads) fp32, no swizzle
+  CUtensorMap delta;   // box (64, 1) on delta (L, N*heads) fp32, no swizzle
 };
 
 constexpr int AB3_THREADS = 576;   // TMA warp + MMA warp + 16 compute warps
@@ -48,12 +50,12 @@ constexpr int B3_T64 = 64 * 128;     // [64 rows][64 ch] fp16
 struct Bwd3Smem {
   static constexpr int K_OFF = 0;
   static constexpr int V_OFF = B3_T128;
-  static constexpr int ST_OFF = 2 * B3_T128;                      // ring of {Q_j, dO_j}
-  static constexpr int PT_OFF = ST_OFF + AB3_ST * 2 * B3_T64;     // P^T of group b  : [128 keys][64 queries]
+  static constexpr int STAGE = 2 * B3_T64 + 1024;                 // {Q_j, dO_j, lse_j[64] | delta_j[64] (+ pad)}
+  static constexpr int ST_OFF = 2 * B3_T128;                      // ring of stages
+  static constexpr int PT_OFF = ST_OFF + AB3_ST * STAGE;          // P^T of group b  : [128 keys][64 queries]
   static constexpr int DS_OFF = PT_OFF + 2 * B3_T128;             // dS^T of group b : adjacent, 16 KB apart
   static constexpr int DQ_OFF = DS_OFF + 2 * B3_T128;             // fp32 dQ staging [2 groups][128 q][32 ch], SW128
-  static constexpr int VEC_OFF = DQ_OFF + 2 * B3_T128;            // lse/delta staging [2 groups][3 bufs][128]
-  static constexpr int BAR_OFF = VEC_OFF + 2 * 3 * 128 * 4;
+  static constexpr int BAR_OFF = DQ_OFF + 2 * B3_T128;
   static constexpr int NBARS = 1 + 2 * AB3_ST + 12;
   static constexpr int TOTAL = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
@@ -112,10 +114,12 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       for (int j = 0; j < n_steps; ++j) {
         const int s = j % AB3_ST;
         mbar_wait(&empty[s], (uint32_t)(((j / AB3_ST) & 1) ^ 1));
-        uint8_t* q_dst = smem + SM::ST_OFF + s * 2 * B3_T64;
-        mbar_expect_tx(&full[s], 2 * B3_T64);
+        uint8_t* q_dst = smem + SM::ST_OFF + s * SM::STAGE;
+        mbar_expect_tx(&full[s], 2 * B3_T64 + 512);
         tma_load_3d(q_dst, &maps.qkv64, &full[s], qc, j * 64, n);            // rows past L arrive as zeros
         tma_load_3d(q_dst + B3_T64, &maps.do64, &full[s], head * 64, j * 64, n);
+        tma_load_2d(q_dst + 2 * B3_T64, &maps.lse, &full[s], j * 64, n * p.heads + head);
+        tma_load_2d(q_dst + 2 * B3_T64 + 256, &maps.delta, &full[s], j * 64, n * p.heads + head);
       }
     }
   } else if (warp == 1) {
@@ -130,7 +134,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       mbar_wait(&full[j % AB3_ST], (uint32_t)((j / AB3_ST) & 1));
       tc_fence_after();
       if (elect_one()) {
-        const uint32_t q_addr = st_addr + (j % AB3_ST) * 2 * B3_T64, do_addr = q_addr + B3_T64;
+        const uint32_t q_addr = st_addr + (j % AB3_ST) * SM::STAGE, do_addr = q_addr + B3_T64;
         const uint32_t d_s = tmem_base + (uint32_t)b * 128u, d_dp = d_s + 64u;
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
@@ -159,7 +163,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       tc_fence_after();
       if (elect_one()) {
         const int s = j % AB3_ST;
-        const uint32_t q_addr = st_addr + s * 2 * B3_T64, do_addr = q_addr + B3_T64;
+        const uint32_t q_addr = st_addr + s * SM::STAGE, do_addr = q_addr + B3_T64;
         const uint32_t d_dv = tmem_base + 256u, d_dk = tmem_base + 320u;
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
@@ -200,22 +204,12 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     const uint32_t s_addr = lane_base + (uint32_t)b * 128u + (uint32_t)h * 32u;
     const uint32_t pt_u32 = smem_u32(smem + SM::PT_OFF + b * B3_T128);
     const uint32_t ds_u32 = smem_u32(smem + SM::DS_OFF + b * B3_T128);
-    const uint32_t vec_u32 = smem_u32(smem + SM::VEC_OFF) + (uint32_t)b * 384u * 4u;   // [3 bufs][64 lse | 64 delta]
+    const uint32_t st_u32 = smem_u32(smem + SM::ST_OFF);
     const float c = p.scale_log2;
-    const float* lse_g = p.lse + ((long long)n * p.heads + head) * p.L;
-    const float* del_g = p.delta + ((long long)n * p.heads + head) * p.L;
-    // lse / delta of this group's i-th step (query tile 2i + b), staged two steps ahead (see attention_bwd2.cu);
-    // threads 0..127 of the group carry them
-    auto ld_vec = [&](int i) -> float {
-      const int qi = (2 * i + b) * 64 + (gt & 63);
-      if (gt < 64) return qi < p.L ? __ldg(lse_g + qi) : INFINITY;
-      return qi < p.L ? __ldg(del_g + qi) : 0.f;
-    };
-    auto st_vec = [&](int i, float v) { sts32f(vec_u32 + (uint32_t)((i % 3) * 128 + gt) * 4u, v); };
     // this thread's 16 columns of the dQ tile of pair m (group b owns columns b*32.., half h 16 of them) -> smem
     // staging -> TMA reduce-add into the global fp32 accumulator.
     const uint32_t stg_u32 = smem_u32(smem + SM::DQ_OFF + b * B3_T128);
-    auto reduce_dq = [&](int m) {
+    auto stage_dq = [&](int m) {
       const int db = m & 1;
       uint32_t a[16];
       tmem_ld16(lane_base + 384u + (uint32_t)db * 64u + (uint32_t)b * 32u + (uint32_t)h * 16u, a);
@@ -229,25 +223,21 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       for (int g = 0; g < 4; ++g)
         sts128(stg_u32 + (uint32_t)row * 128u + (uint32_t)(((h * 4 + g) ^ (row & 7)) << 4),
                make_uint4(a[4 * g], a[4 * g + 1], a[4 * g + 2], a[4 * g + 3]));
-      fence_proxy_async_smem();
+    };
+    // after a proxy fence by every thread of the group
+    auto issue_dq = [&](int m) {
       named_bar_sync3(1 + b, 256);
       if (gt == 0) {
         tma_reduce_add_3d(&maps.dq, stg_u32, head * 64 + b * 32, m * 128, n);   // rows past L are clipped
         tma_store_commit();
       }
     };
-    float pend = 0.f;
-    if (h == 0) {
-      st_vec(0, ld_vec(0));
-      if (n_pairs > 1) pend = ld_vec(1);
-    }
     for (int m = 0; m < n_pairs; ++m) {
-      if (h == 0) {
-        if (m + 1 < n_pairs) st_vec(m + 1, pend);
-        if (m + 2 < n_pairs) pend = ld_vec(m + 2);
-      }
-      named_bar_sync3(1 + b, 256);
-      const uint32_t ls_u32 = vec_u32 + (uint32_t)(m % 3) * 512u + (uint32_t)h * 128u, dl_u32 = ls_u32 + 256u;
+      // lse / delta of the step's 64 queries arrived with its Q / dO stage (rows past L read as 0: with Q = dO = 0
+      // that gives P = 1, dS = 0, and the zero dO / Q rows keep dV / dK untouched)
+      const int j = 2 * m + b, stg = j % AB3_ST;
+      const uint32_t ls_u32 = st_u32 + (uint32_t)stg * SM::STAGE + 2 * B3_T64 + (uint32_t)h * 128u, dl_u32 = ls_u32 + 256u;
+      mbar_wait(&full[stg], (uint32_t)((j / AB3_ST) & 1));
       mbar_wait(&sdp_full[b], (uint32_t)(m & 1));
       tc_fence_after();
       uint32_t sr[32], dr[32];
@@ -289,11 +279,15 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&p_ready[b]);
-      if (m > 0) reduce_dq(m - 1);
+      // dQ tile of the previous pair -> staging -> bulk reduction, off the p_ready path (staging it under the
+      // fence above saved a fence but delayed p_ready: 4.33 ms vs 4.0 ms at the bench shape)
+      if (m > 0) { stage_dq(m - 1); fence_proxy_async_smem(); issue_dq(m - 1); }
     }
     mbar_wait(&pair_done[(n_pairs - 1) & 1], (uint32_t)(((n_pairs - 1) >> 1) & 1));
     tc_fence_after();
-    reduce_dq(n_pairs - 1);
+    stage_dq(n_pairs - 1);
+    fence_proxy_async_smem();
+    issue_dq(n_pairs - 1);
     // group 0 writes dV, group 1 writes dK * scale; half h the columns h*32..
     const int ki = kv0 + row;
     const bool valid = ki < p.L;
@@ -376,6 +370,11 @@ int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int
   const uint64_t qstr[2] = {(uint64_t)C * 4, (uint64_t)C * 4 * (uint64_t)L};
   const uint32_t qbox[3] = {32u, 128u, 1u};
   if ((rc = make_tmap_f32(&m.dq, dq_acc, 3, qdims, qstr, qbox))) return rc;
+  const uint64_t vdims[2] = {(uint64_t)L, (uint64_t)N * heads};
+  const uint64_t vstr[1] = {(uint64_t)L * 4};
+  const uint32_t vbox[2] = {64u, 1u};
+  if ((rc = make_tmap_f32_linear(&m.lse, lse, 2, vdims, vstr, vbox))) return rc;
+  if ((rc = make_tmap_f32_linear(&m.delta, delta, 2, vdims, vstr, vbox))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   const long long rows = (long long)N * L;
   B2D_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * heads * 64 * sizeof(float), st));

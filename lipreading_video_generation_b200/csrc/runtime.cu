@@ -72,7 +72,8 @@ PFN_encodeTiled get_encode_tiled() {
 }
 
 static int make_tmap_typed(CUtensorMap* m, CUtensorMapDataType dtype, const void* base, int rank,
-                           const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box);
+                           const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
+                           CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B);
 
 int make_tmap_16b(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
                    const uint64_t* strides_bytes, const uint32_t* box) {
@@ -84,8 +85,15 @@ int make_tmap_f32(CUtensorMap* m, const void* base, int rank, const uint64_t* di
   return make_tmap_typed(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_bytes, box);
 }
 
+int make_tmap_f32_linear(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                         const uint64_t* strides_bytes, const uint32_t* box) {
+  return make_tmap_typed(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, base, rank, dims, strides_bytes, box,
+                         CU_TENSOR_MAP_SWIZZLE_NONE);
+}
+
 static int make_tmap_typed(CUtensorMap* m, CUtensorMapDataType dtype, const void* base, int rank,
-                           const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box) {
+                           const uint64_t* dims, const uint64_t* strides_bytes, const uint32_t* box,
+                           CUtensorMapSwizzle swz) {
   PFN_encodeTiled enc = get_encode_tiled();
   B2D_REQUIRE(enc != nullptr, B2D_ERR_CUDA, "cuTensorMapEncodeTiled entry point not available");
   B2D_REQUIRE(aligned16(base), B2D_ERR_ALIGN, "tensor map base %p is not 16-byte aligned", base);
@@ -99,7 +107,7 @@ static int make_tmap_typed(CUtensorMap* m, CUtensorMapDataType dtype, const void
                 (unsigned long long)gstr[i]);
   }
   CUresult r = enc(m, dtype, (cuuint32_t)rank, const_cast<void*>(base), gdim, gstr, bx,
-                   es, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   es, CU_TENSOR_MAP_INTERLEAVE_NONE, swz,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   B2D_REQUIRE(r == CUDA_SUCCESS, B2D_ERR_CUDA,
               "cuTensorMapEncodeTiled failed (%d): rank=%d dims=[%llu,%llu,%llu,%llu] box=[%u,%u,%u,%u]", (int)r,

@@ -21,5 +21,8 @@ int make_tmap_16b(CUtensorMap* m, const void* base, int rank, const uint64_t* di
 // same for fp32 elements (box[0] * 4 bytes <= 128)
 int make_tmap_f32(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
                   const uint64_t* strides_bytes, const uint32_t* box);
+// fp32, no swizzle (plain row-major box in shared memory)
+int make_tmap_f32_linear(CUtensorMap* m, const void* base, int rank, const uint64_t* dims,
+                         const uint64_t* strides_bytes, const uint32_t* box);
 
 }  // namespace b2d
