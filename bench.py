@@ -28,6 +28,7 @@ WORKLOADS = {
     "train64": (16, 16, 64, "train"),      # BASELINE configs[1]
     "train128": (16, 16, 128, "train"),    # BASELINE configs[2] per-GPU shape
     "sample128": (8, 16, 128, "sample"),   # BASELINE configs[3] per-GPU shape
+    "train64_1clip": (1, 16, 64, "train"),  # diagnostic: 16x less GPU work, same launches -> host cost of one step
 }
 FWD_GFLOP_PER_IMAGE = {64: 43.87, 128: 470.21}     # SURVEY section 8(d), algorithmic, UNet torso
 
