@@ -106,9 +106,8 @@ int b2d_mse_bwd(const float* pred, const float* target, const float* grad_out,
  * (N,H,W,C) fp16 -- the channels-last image of the reference's NCHW / (B,C,L)
  * tensors -- so that one row of a tile is one K-major 128-byte line for the
  * tcgen05 tensor cores; accumulation is always fp32.  Gradient tensors are fp16
- * too and carry a power-of-two loss scale (b2d_grad_scale).  NOTE: parameter
- * comments below that say "bf16" predate the switch and mean "fp16" (bf16
- * storage missed north_star's 2e-2 gradient tolerance).
+ * too and carry a power-of-two loss scale (b2d_grad_scale).  (bf16 storage
+ * missed north_star's 2e-2 gradient tolerance)
  * Weights stay fp32 OIHW in state_dict; the host side packs fp16 copies
  * [Cout][tap][Cin] for these calls.
  * ---------------------------------------------------------------------- */
@@ -122,18 +121,18 @@ int b2d_mse_bwd(const float* pred, const float* target, const float* grad_out,
  * X is the channel concatenation [x | x2] (torch.cat at unet.py:672) without
  * materialising it.  C1, C2 multiples of 64; W a power of two <= 128. */
 typedef struct b2d_conv_args {
-  const void* x;   int64_t ldx;  int C1;     /* bf16 (N,H,W,ldx), channels [0,C1) used */
+  const void* x;   int64_t ldx;  int C1;     /* fp16 (N,H,W,ldx), channels [0,C1) used */
   const void* x2;  int64_t ldx2; int C2;     /* optional second source, or NULL / 0 */
   int N, H, W;                               /* input spatial size */
   int ksize;                                 /* 1 or 3 (padding ksize/2) */
   int stride;                                /* 1 or 2 */
-  const void* w;                             /* bf16 [CoutPad][ksize*ksize*(C1+C2)] */
+  const void* w;                             /* fp16 [CoutPad][ksize*ksize*(C1+C2)] */
   int Cout;                                  /* logical output channels */
   int CoutPad;                               /* rows of w: multiple of 16 */
   const float* bias;                         /* [Cout] or NULL */
   const float* emb; int64_t ldemb;           /* [N][ldemb] per-sample add (unet.py:266) or NULL */
-  const void* residual; int64_t ldres;       /* bf16 (N,Ho,Wo,ldres) added in the epilogue, or NULL */
-  void* out; int64_t ldo;                    /* bf16 (N,Ho,Wo,ldo) or NULL */
+  const void* residual; int64_t ldres;       /* fp16 (N,Ho,Wo,ldres) added in the epilogue, or NULL */
+  void* out; int64_t ldo;                    /* fp16 (N,Ho,Wo,ldo) or NULL */
   float* out_nchw_f32;                       /* optional fp32 (N,Cout,Ho,Wo) output (model output) */
 } b2d_conv_args;
 
@@ -141,7 +140,7 @@ int b2d_conv2d(const b2d_conv_args* a, void* stream);
 
 /* Weight gradient of the same convolution (fp32, ACCUMULATED into dw):
  *   dw[co][tap][ci] += sum_{n,ho,wo} dy[n,ho,wo,co] * X[n, ho*s+dy-p, wo*s+dx-p, ci]
- * dy: bf16 (N,Ho,Wo,lddy).  dw: fp32 [Cout][taps*(C1+C2)] (caller zeroes). */
+ * dy: fp16 (N,Ho,Wo,lddy).  dw: fp32 [Cout][taps*(C1+C2)] (caller zeroes). */
 typedef struct b2d_wgrad_args {
   const void* x;   int64_t ldx;  int C1;
   const void* x2;  int64_t ldx2; int C2;
@@ -156,14 +155,14 @@ int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream);
 /* Flash-style self-attention forward (QKVAttentionLegacy.forward unet.py:349-366 when
  * new_order == 0; QKVAttention.forward unet.py:382-401 when new_order == 1):
  *   a = softmax_fp32((q*ch^-1/4)^T (k*ch^-1/4)) v   per (sample, head), L = H*W tokens.
- * qkv: bf16 (N, L, ldqkv) pixel-major image of the reference's (N, 3*heads*ch, L) tensor, with the
+ * qkv: fp16 (N, L, ldqkv) pixel-major image of the reference's (N, 3*heads*ch, L) tensor, with the
  * reference's channel order ([head][q|k|v][ch] legacy, [q|k|v][head][ch] new).
- * out: bf16 (N, L, ldo), head h at channels [h*ch, (h+1)*ch).  lse: fp32 (N, heads, L) or NULL,
+ * out: fp16 (N, L, ldo), head h at channels [h*ch, (h+1)*ch).  lse: fp32 (N, heads, L) or NULL,
  * log2-domain log-sum-exp of the scaled logits (saved for the backward).  ch in {64,128,256}. */
 int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
                       void* out, int64_t ldo, float* lse, void* stream);
 
-/* GroupNorm32(32, C) [+ SiLU] [+ dropout] on pixel-major bf16 (utils.py:54-56,130-137; call sites
+/* GroupNorm32(32, C) [+ SiLU] [+ dropout] on pixel-major fp16 (utils.py:54-56,130-137; call sites
  * unet.py:194-198 in_layers, :218-225 out_layers incl. nn.Dropout, :297 attention norm, :624-628 head).
  * Statistics in fp32/fp64 as the reference's `.float()` GroupNorm.  The input is the channel
  * concatenation [x1 | x2] (x2 may be NULL).  act: 0 none, 1 SiLU.  drop_p > 0 applies an inverted
@@ -180,11 +179,11 @@ typedef struct b2d_gn_args {
 } b2d_gn_args;
 
 size_t b2d_groupnorm_workspace_bytes(int N, int Ctot);
-/* y: bf16 (N,HW,C1+C2) contiguous; mean, rstd: fp32 [N][32] (saved for the backward). */
+/* y: fp16 (N,HW,C1+C2) contiguous; mean, rstd: fp32 [N][32] (saved for the backward). */
 int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, float* rstd, void* workspace,
                       size_t workspace_bytes, void* stream);
-/* dy: bf16 (N,HW,C1+C2) gradient w.r.t. y.  dx1 (N,HW,lddx1) / dx2 (N,HW,lddx2) receive the input
- * gradients; add_a / add_b (optional, bf16, channel pitch lda / ldb) are ADDED to dx1 so that the
+/* dy: fp16 (N,HW,C1+C2) gradient w.r.t. y.  dx1 (N,HW,lddx1) / dx2 (N,HW,lddx2) receive the input
+ * gradients; add_a / add_b (optional, fp16, channel pitch lda / ldb) are ADDED to dx1 so that the
  * residual / skip gradient accumulation is fused; with add_a_full != 0, add_a spans all C1+C2
  * channels and its upper C2 channels are added to dx2.  dgamma/dbeta: fp32 [C1+C2], accumulated. */
 int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
@@ -199,11 +198,11 @@ int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, c
 /* UNetAudio.forward conditioning assembly (unet_audio.py:53-61) fused with the NCHW->pixel-major
  * conversion:  out[n,h,w,:] = [ x_t (Cin) | cond_conv_in(nearest(cond)) (Cim) | audio[n] (A) | 0 ... ]
  * xt fp32 (N,Cin,S,S); cond fp32 (N,Cc,Hc,Wc) resized with F.interpolate's default 'nearest';
- * wcond fp32 (Cim,Cc) = cond_conv_in.weight; audio fp32 (N,A); out bf16 (N,S,S,Cpad). */
+ * wcond fp32 (Cim,Cc) = cond_conv_in.weight; audio fp32 (N,A); out fp16 (N,S,S,Cpad). */
 int b2d_assemble_input(const float* xt, const float* cond, const float* wcond, const float* audio, int N,
                        int S, int Cin, int Cc, int Hc, int Wc, int Cim, int A, int Cpad, void* out,
                        void* stream);
-/* Adjoint: d_wcond (Cim,Cc) and d_audio (N,A) are ACCUMULATED from dX bf16 (N,S,S,Cpad). */
+/* Adjoint: d_wcond (Cim,Cc) and d_audio (N,A) are ACCUMULATED from dX fp16 (N,S,S,Cpad). */
 int b2d_assemble_input_bwd(const void* dX, const float* cond, int N, int S, int Cin, int Cc, int Hc, int Wc,
                            int Cim, int A, int Cpad, float* d_wcond, float* d_audio, void* stream);
 
@@ -222,7 +221,7 @@ int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, i
 int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream);
 /* x[i] *= *scale  (unscale the fp32 parameter gradients). */
 int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream);
-/* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x bf16 (N,HW,ld)): emb_out / bias / audio gradients. */
+/* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x fp16 (N,HW,ld)): emb_out / bias / audio gradients. */
 int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */
 int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream);
@@ -240,7 +239,7 @@ int b2d_linear_bwd(const float* x, const float* w, const float* y, const float* 
 
 /* Backward of b2d_attention_fwd w.r.t. the packed qkv tensor (replaces autograd through
  * unet.py:356-366 and the checkpoint recompute of utils.py:179-207).  out / lse are the forward's
- * results; d_out: bf16 (N,L,lddo) gradient w.r.t. out; dqkv: bf16 (N,L,lddqkv) fully written;
+ * results; d_out: fp16 (N,L,lddo) gradient w.r.t. out; dqkv: fp16 (N,L,lddqkv) fully written;
  * delta_ws: fp32 workspace of b2d_attention_bwd_ws_floats(N, L, heads, ch) elements (the per-row delta, plus
  * the fp32 dQ accumulator of the single-pass kernel where that one is used). */
 int64_t b2d_attention_bwd_ws_floats(int N, int L, int heads, int ch);

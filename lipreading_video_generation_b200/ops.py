@@ -1,7 +1,7 @@
 """Thin tensor-level wrappers over the C ABI (include/b2d.h).
 
 Every function enqueues sm_100a kernels on torch's current CUDA stream through
-ctypes; torch only owns the memory.  Activations are pixel-major bf16 tensors
+ctypes; torch only owns the memory.  Activations are pixel-major fp16 tensors
 (N, H, W, C) fp16 (gradient tensors carry a power-of-two loss scale) -- see DESIGN.md "data layout".
 No function here has a CPU path.
 """
@@ -195,7 +195,7 @@ def groupnorm_fwd(x1, gamma, beta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed
 
 def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed=0,
                   add_a=None, add_b=None, add_a_full=False):
-    """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (bf16, any channel pitch) are added to dx1."""
+    """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (fp16, any channel pitch) are added to dx1."""
     N, H, W, C1 = x1.shape
     if any(t is not None and t.dtype != F16 for t in (x1, x2, dy, add_a, add_b)):
         raise RuntimeError("groupnorm_bwd: x / dy / add_a / add_b must be fp16")
@@ -311,7 +311,7 @@ def scale_f32_(x, scale_ptr_tensor):
 
 
 def colsum(x, out, c_off=0, C_=None):
-    """out[n][c] += sum over pixels of x[n,:,:,c_off+c];  x (N,H,W,ld) bf16, out (N,C) fp32."""
+    """out[n][c] += sum over pixels of x[n,:,:,c_off+c];  x (N,H,W,ld) fp16, out (N,C) fp32."""
     N, H, W, ld = x.shape
     C_ = out.shape[1] if C_ is None else C_
     L.check(L.lib().b2d_colsum(x.data_ptr(), x.stride(2), c_off, C_, N, H * W, out.data_ptr(), out.stride(0), _s()), "b2d_colsum")
