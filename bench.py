@@ -394,8 +394,16 @@ def main():
                    tflops=flops / (t_ms / cnt) / 1e9, ms_per_step=t_ms / a.steps)
         if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
             dom = rec
+    traffic = None          # DRAM bytes per launch of the dominant kernel from one `ncu --set full` capture
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
+            tj = json.load(f)
+        if dom["kernel"] == "attention_bwd L=4096 ch=64" and n_img == 256:
+            traffic = tj["traffic_bytes_per_launch"]
+    except (OSError, KeyError, ValueError):
+        pass
     roof = {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
-            "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
+            "frac": round(dom["tflops"] / sustained, 4), "traffic": traffic, "kernel": dom["kernel"],
             "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
             "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N fwd, 10*L^2*ch*N bwd"}
     if os.environ.get("B2D_BENCH_NO_CPU") == "1":          # profiling runs only (ncu): skip the host-side leg
