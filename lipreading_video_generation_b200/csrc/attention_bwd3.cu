@@ -52,8 +52,7 @@ struct Bwd3Smem {
   static constexpr int V_OFF = B3_T128;
   static constexpr int STAGE = 2 * B3_T64 + 1024;                 // {Q_j, dO_j, lse_j[64] | delta_j[64] (+ pad)}
   static constexpr int ST_OFF = 2 * B3_T128;                      // ring of stages
-  static constexpr int PT_OFF = ST_OFF + AB3_ST * STAGE;          // P^T of group b  : [128 keys][64 queries]
-  static constexpr int DS_OFF = PT_OFF + 2 * B3_T128;             // dS^T of group b : adjacent, 16 KB apart
+  static constexpr int DS_OFF = ST_OFF + AB3_ST * STAGE;          // dS^T of group b : [128 keys][64 queries], 16 KB apart
   static constexpr int DQ_OFF = DS_OFF + 2 * B3_T128;             // fp32 dQ staging [2 groups][128 q][32 ch], SW128
   static constexpr int BAR_OFF = DQ_OFF + 2 * B3_T128;
   static constexpr int NBARS = 1 + 2 * AB3_ST + 12;
@@ -95,7 +94,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     mbar_init(kv_full, 1);
     for (int s = 0; s < AB3_ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int b = 0; b < 2; ++b) {
-      mbar_init(&sdp_full[b], 1); mbar_init(&s_free[b], 256); mbar_init(&p_ready[b], 256);
+      mbar_init(&sdp_full[b], 1); mbar_init(&s_free[b], 1); mbar_init(&p_ready[b], 256);
       mbar_init(&pair_done[b], 1); mbar_init(&dq_free[b], 512); mbar_init(&stg_free[b], 1);
     }
     fence_barrier_init();
@@ -127,7 +126,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     const uint32_t idesc_g = make_idesc(128, 64, 0, 1, FMT_F16, FMT_F16);   // dV, dK    : B operand MN-major
     const uint32_t idesc_q = make_idesc(128, 64, 1, 1, FMT_F16, FMT_F16);   // dQ        : both operands MN-major
     const uint32_t k_addr = smem_u32(smem + SM::K_OFF), v_addr = smem_u32(smem + SM::V_OFF);
-    const uint32_t pt_addr = smem_u32(smem + SM::PT_OFF), ds_addr = smem_u32(smem + SM::DS_OFF);
+    const uint32_t ds_addr = smem_u32(smem + SM::DS_OFF);
     const uint32_t st_addr = smem_u32(smem + SM::ST_OFF);
     auto issue_sdp = [&](int j) {
       const int b = j & 1;
@@ -154,24 +153,22 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     for (int j = 0; j < n_steps; ++j) {
       const int b = j & 1, m = j >> 1;
       const uint32_t par = (uint32_t)(m & 1);
-      if (j + 2 < n_steps) {   // next step of the same group as soon as its S^T | dP^T columns are free
-        mbar_wait(&s_free[b], par);
-        tc_fence_after();
-        issue_sdp(j + 2);
-      }
       mbar_wait(&p_ready[b], par);
       tc_fence_after();
       if (elect_one()) {
         const int s = j % AB3_ST;
         const uint32_t q_addr = st_addr + s * SM::STAGE, do_addr = q_addr + B3_T64;
         const uint32_t d_dv = tmem_base + 256u, d_dk = tmem_base + 320u;
+        // A = P^T / dS^T from tensor memory: fp16 pairs packed over the group's own S^T / dP^T columns, 16 columns
+        // per column half (kk = 0,1 -> half 0, kk = 2,3 -> half 1); B = dO_j / Q_j MN-major from shared memory
+        const uint32_t a_p = tmem_base + (uint32_t)b * 128u, a_ds = a_p + 64u;
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          mma_f16_ss(d_dv, make_sdesc_sw128(pt_addr + b * B3_T128 + kk * 32, 16, 1024),
+          mma_f16_ts(d_dv, a_p + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8),
                      make_sdesc_sw128(do_addr + kk * 2048, B3_T64, 1024), idesc_g, (uint32_t)((j | kk) != 0));
 #pragma unroll
         for (int kk = 0; kk < 4; ++kk)
-          mma_f16_ss(d_dk, make_sdesc_sw128(ds_addr + b * B3_T128 + kk * 32, 16, 1024),
+          mma_f16_ts(d_dk, a_ds + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8),
                      make_sdesc_sw128(q_addr + kk * 2048, B3_T64, 1024), idesc_g, (uint32_t)((j | kk) != 0));
         mma_commit(&empty[s]);
       }
@@ -190,6 +187,9 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
         }
         __syncwarp();
       }
+      // S^T | dP^T of the group's next step overwrite the columns P^T / dS^T were read from: issued behind the
+      // dV / dK MMAs of this step (the tensor pipe executes in issue order); the group stages its dQ tile meanwhile
+      if (j + 2 < n_steps) issue_sdp(j + 2);
     }
   } else {
     // 16 compute warps: group b (which steps) x column half h (which 32 of the step's 64 queries); the TMEM lane
@@ -202,7 +202,6 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     const int gt = h * 128 + (cw & 3) * 32 + lane;  // 0..255 within the group
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const uint32_t s_addr = lane_base + (uint32_t)b * 128u + (uint32_t)h * 32u;
-    const uint32_t pt_u32 = smem_u32(smem + SM::PT_OFF + b * B3_T128);
     const uint32_t ds_u32 = smem_u32(smem + SM::DS_OFF + b * B3_T128);
     const uint32_t st_u32 = smem_u32(smem + SM::ST_OFF);
     const float c = p.scale_log2;
@@ -244,8 +243,6 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       tmem_ld32(s_addr, sr);
       tmem_ld32(s_addr + 64, dr);
       tmem_ld_wait();
-      tc_fence_before();
-      mbar_arrive(&s_free[b]);
 #pragma unroll
       for (int i4 = 0; i4 < 32; i4 += 4) {
         const float4 l4 = lds128f(ls_u32 + i4 * 4);   // warp-uniform address: broadcast LDS.128
@@ -261,21 +258,21 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       }
       // dV/dK of this group's previous step and dQ of the previous pair have read P^T / dS^T
       if (m > 0) { mbar_wait(&pair_done[(m - 1) & 1], (uint32_t)(((m - 1) >> 1) & 1)); tc_fence_after(); }
+      // P^T -> tensor memory over this thread's own S^T columns, dS^T -> tensor memory over its dP^T columns (A
+      // operands of dV / dK) and -> shared memory (MN-major A operand of dQ)
+      uint32_t pp[16], dd[16];
 #pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        uint4 u, w;
-        u.x = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 0]), __uint_as_float(sr[8 * g + 1]));
-        u.y = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 2]), __uint_as_float(sr[8 * g + 3]));
-        u.z = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 4]), __uint_as_float(sr[8 * g + 5]));
-        u.w = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 6]), __uint_as_float(sr[8 * g + 7]));
-        w.x = pack_f16x2(__uint_as_float(dr[8 * g + 0]), __uint_as_float(dr[8 * g + 1]));
-        w.y = pack_f16x2(__uint_as_float(dr[8 * g + 2]), __uint_as_float(dr[8 * g + 3]));
-        w.z = pack_f16x2(__uint_as_float(dr[8 * g + 4]), __uint_as_float(dr[8 * g + 5]));
-        w.w = pack_f16x2(__uint_as_float(dr[8 * g + 6]), __uint_as_float(dr[8 * g + 7]));
-        const uint32_t off = sw128_offset((uint32_t)row, (uint32_t)(8 * (h * 4 + g)));
-        sts128(pt_u32 + off, u);
-        sts128(ds_u32 + off, w);
+      for (int i = 0; i < 16; ++i) {
+        pp[i] = pack_f16x2_nosat(__uint_as_float(sr[2 * i]), __uint_as_float(sr[2 * i + 1]));
+        dd[i] = pack_f16x2(__uint_as_float(dr[2 * i]), __uint_as_float(dr[2 * i + 1]));
       }
+      tmem_st16(s_addr, pp);
+      tmem_st16(s_addr + 64, dd);
+#pragma unroll
+      for (int g = 0; g < 4; ++g)
+        sts128(ds_u32 + sw128_offset((uint32_t)row, (uint32_t)(8 * (h * 4 + g))),
+               make_uint4(dd[4 * g], dd[4 * g + 1], dd[4 * g + 2], dd[4 * g + 3]));
+      tmem_st_wait();
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&p_ready[b]);
