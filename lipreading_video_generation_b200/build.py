@@ -23,7 +23,7 @@ NVCC_FLAGS = [
     "-Xcompiler", "-fPIC",
     "--expt-relaxed-constexpr",
     "-Xptxas", "-v",
-]
+] + os.environ.get("B2D_EXTRA_NVCC_FLAGS", "").split()      # developer builds only (e.g. -DB3_TRACE)
 
 
 def _nvcc() -> str:

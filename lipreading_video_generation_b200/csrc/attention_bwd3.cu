@@ -14,11 +14,20 @@
 //   (every key-tile CTA of the image contributes; per-thread red.global of row-strided 16-byte pieces cost 32
 //   L1 sectors per instruction and held the loop at ~6k clk per pair, profiles/r1_attention_ncu.md);
 //   dq_finalize_kernel scales the accumulator into the fp16 dqkv columns afterwards.
-// TMEM (512 columns): S^T|dP^T of group b at b*128 (64 + 64); dV 256; dK 320; dQ double buffer 384 / 448.
+// TMEM (512 columns): S^T|dP^T of group b at b*128 (64 + 64), overwritten in place by the fp16 P^T | dS^T operands;
+// dV 256; dK 320; dQ 384; K_t 448 and V_t 480 as fp16 pairs (A operands of S^T / dP^T).
 // Warps: 0 = TMA producer, 1 = tcgen05 issuer, 2..17 = compute: group (w-2)/4 % 2, column half (w-2)/8.
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
+
+// Developer timeline: compile with -DB3_TRACE and set B2D_BWD3_TRACE=<file> to dump clock64() stamps of CTA (0,0,0):
+// [(group*32 + step)*8 + k] for the compute groups, [512 + j*6 + k] for the tcgen05 issuer (scripts/dev_bwd3_trace.py).
+#ifdef B3_TRACE
+#define B3_TR(cond, idx) do { if (cond) p.trace[(idx)] = clock64(); } while (0)
+#else
+#define B3_TR(cond, idx) do { } while (0)
+#endif
 
 namespace b2d {
 using namespace umma;
@@ -31,6 +40,7 @@ struct AttnBwd3Params {
   const float* delta;  // (N, heads, L)
   float* dq_acc;       // (N, L, heads, 64) fp32, zeroed before the launch
   __half* dqkv; long long lddqkv;
+  long long* trace;    // developer timeline buffer (B3_TRACE builds), else null
 };
 
 struct AttnBwd3Maps {
@@ -55,7 +65,7 @@ struct Bwd3Smem {
   static constexpr int DS_OFF = ST_OFF + AB3_ST * STAGE;          // dS^T of group b : [128 keys][64 queries], 16 KB apart
   static constexpr int DQ_OFF = DS_OFF + 2 * B3_T128;             // fp32 dQ staging [2 groups][128 q][32 ch], SW128
   static constexpr int BAR_OFF = DQ_OFF + 2 * B3_T128;
-  static constexpr int NBARS = 1 + 2 * AB3_ST + 12;
+  static constexpr int NBARS = 1 + 2 * AB3_ST + 13;
   static constexpr int TOTAL = BAR_OFF + NBARS * 8 + 16 + 1024;
 };
 
@@ -78,7 +88,8 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
   uint64_t* pair_done = p_ready + 2;     // [2] per dQ buffer: every MMA up to and including dQ_m has completed
   uint64_t* dq_free = pair_done + 2;     // [2] per dQ buffer: both groups have read the dQ tile
   uint64_t* stg_free = dq_free + 2;      // [2] per group: its fp32 dQ staging buffer may be overwritten
-  uint32_t* tmem_slot = (uint32_t*)(stg_free + 2);
+  uint64_t* kv_tmem = stg_free + 2;      // K_t, V_t copied to tensor memory by the compute warps
+  uint32_t* tmem_slot = (uint32_t*)(kv_tmem + 1);
 
   // S2R shares the MUFU issue path with ex2: an opaque copy keeps the compiler from re-reading %tid.x in the loop
   uint32_t tid;
@@ -92,6 +103,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
 
   if (tid == 0) {
     mbar_init(kv_full, 1);
+    mbar_init(kv_tmem, 512);
     for (int s = 0; s < AB3_ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&sdp_full[b], 1); mbar_init(&s_free[b], 1); mbar_init(&p_ready[b], 256);
@@ -125,7 +137,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     const uint32_t idesc_s = make_idesc(128, 64, 0, 0, FMT_F16, FMT_F16);   // S^T, dP^T : both operands K-major
     const uint32_t idesc_g = make_idesc(128, 64, 0, 1, FMT_F16, FMT_F16);   // dV, dK    : B operand MN-major
     const uint32_t idesc_q = make_idesc(128, 64, 1, 1, FMT_F16, FMT_F16);   // dQ        : both operands MN-major
-    const uint32_t k_addr = smem_u32(smem + SM::K_OFF), v_addr = smem_u32(smem + SM::V_OFF);
+    const uint32_t k_addr = smem_u32(smem + SM::K_OFF);
     const uint32_t ds_addr = smem_u32(smem + SM::DS_OFF);
     const uint32_t st_addr = smem_u32(smem + SM::ST_OFF);
     auto issue_sdp = [&](int j) {
@@ -135,25 +147,30 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       if (elect_one()) {
         const uint32_t q_addr = st_addr + (j % AB3_ST) * SM::STAGE, do_addr = q_addr + B3_T64;
         const uint32_t d_s = tmem_base + (uint32_t)b * 128u, d_dp = d_s + 64u;
+        // A = K_t / V_t from tensor memory (8 columns per K = 16 channels), B = Q_j / dO_j K-major from smem
+        // (the two accumulators alternate so that consecutive instructions are independent)
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          mma_f16_ss(d_s, make_sdesc_sw128(k_addr + kk * 32, 16, 1024),
+        for (int kk = 0; kk < 4; ++kk) {
+          mma_f16_ts(d_s, tmem_base + 448u + (uint32_t)kk * 8u,
                      make_sdesc_sw128(q_addr + kk * 32, 16, 1024), idesc_s, (uint32_t)(kk != 0));
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-          mma_f16_ss(d_dp, make_sdesc_sw128(v_addr + kk * 32, 16, 1024),
+          mma_f16_ts(d_dp, tmem_base + 480u + (uint32_t)kk * 8u,
                      make_sdesc_sw128(do_addr + kk * 32, 16, 1024), idesc_s, (uint32_t)(kk != 0));
+        }
         mma_commit(&sdp_full[b]);
       }
       __syncwarp();
     };
-    mbar_wait(kv_full, 0);
+    mbar_wait(kv_tmem, 0);
+    tc_fence_after();
     issue_sdp(0);
     issue_sdp(1);
+    const bool tr = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0;
     for (int j = 0; j < n_steps; ++j) {
       const int b = j & 1, m = j >> 1;
       const uint32_t par = (uint32_t)(m & 1);
+      B3_TR(tr && j < 64, 512 + j * 6 + 0);
       mbar_wait(&p_ready[b], par);
+      B3_TR(tr && j < 64, 512 + j * 6 + 1);
       tc_fence_after();
       if (elect_one()) {
         const int s = j % AB3_ST;
@@ -163,21 +180,21 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
         // per column half (kk = 0,1 -> half 0, kk = 2,3 -> half 1); B = dO_j / Q_j MN-major from shared memory
         const uint32_t a_p = tmem_base + (uint32_t)b * 128u, a_ds = a_p + 64u;
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
+        for (int kk = 0; kk < 4; ++kk) {
           mma_f16_ts(d_dv, a_p + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8),
                      make_sdesc_sw128(do_addr + kk * 2048, B3_T64, 1024), idesc_g, (uint32_t)((j | kk) != 0));
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
           mma_f16_ts(d_dk, a_ds + (uint32_t)((kk >> 1) * 32 + (kk & 1) * 8),
                      make_sdesc_sw128(q_addr + kk * 2048, B3_T64, 1024), idesc_g, (uint32_t)((j | kk) != 0));
+        }
         mma_commit(&empty[s]);
       }
       __syncwarp();
+      B3_TR(tr && j < 64, 512 + j * 6 + 2);
       if (b == 1) {
-        const int db = m & 1;
-        if (m >= 2) { mbar_wait(&dq_free[db], (uint32_t)(((m >> 1) - 1) & 1)); tc_fence_after(); }
+        const int db = m & 1;     // barrier slot only: the dQ tile itself is single-buffered
+        if (m >= 1) { mbar_wait(&dq_free[(m - 1) & 1], (uint32_t)(((m - 1) >> 1) & 1)); tc_fence_after(); }
         if (elect_one()) {
-          const uint32_t d_dq = tmem_base + 384u + (uint32_t)db * 64u;
+          const uint32_t d_dq = tmem_base + 384u;
           // A = dS (M = 128 queries: two 64-query groups = the two dS^T buffers, K = keys = smem rows)
 #pragma unroll
           for (int kk = 0; kk < 8; ++kk)
@@ -189,7 +206,9 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       }
       // S^T | dP^T of the group's next step overwrite the columns P^T / dS^T were read from: issued behind the
       // dV / dK MMAs of this step (the tensor pipe executes in issue order); the group stages its dQ tile meanwhile
+      B3_TR(tr && j < 64, 512 + j * 6 + 3);
       if (j + 2 < n_steps) issue_sdp(j + 2);
+      B3_TR(tr && j < 64, 512 + j * 6 + 4);
     }
   } else {
     // 16 compute warps: group b (which steps) x column half h (which 32 of the step's 64 queries); the TMEM lane
@@ -211,7 +230,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     auto stage_dq = [&](int m) {
       const int db = m & 1;
       uint32_t a[16];
-      tmem_ld16(lane_base + 384u + (uint32_t)db * 64u + (uint32_t)b * 32u + (uint32_t)h * 16u, a);
+      tmem_ld16(lane_base + 384u + (uint32_t)b * 32u + (uint32_t)h * 16u, a);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&dq_free[db]);
@@ -231,18 +250,39 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
         tma_store_commit();
       }
     };
+    {
+      // K_t and V_t also live in tensor memory (columns 448..479 / 480..511, fp16 pairs) as the A operands of S^T and
+      // dP^T: an N = 64 MMA with both operands in shared memory wants 192 B/clk of a 128 B/clk port (measured ~72 clk
+      // per instruction against 47 with A in tensor memory).  Warp (b, h) copies 32 channels of one of them.
+      mbar_wait(kv_full, 0);
+      const uint32_t src = smem_u32(smem + (b == 0 ? SM::K_OFF : SM::V_OFF));
+      uint32_t kv[16];
+#pragma unroll
+      for (int g = 0; g < 4; ++g) {
+        const uint4 u = lds128(src + sw128_offset((uint32_t)row, (uint32_t)(8 * (h * 4 + g))));
+        kv[4 * g] = u.x; kv[4 * g + 1] = u.y; kv[4 * g + 2] = u.z; kv[4 * g + 3] = u.w;
+      }
+      tmem_st16(lane_base + 448u + (uint32_t)b * 32u + (uint32_t)h * 16u, kv);
+      tmem_st_wait();
+      tc_fence_before();
+      mbar_arrive(kv_tmem);
+    }
+    const bool tr = p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && lane == 0 && qd == 0 && h == 0;
     for (int m = 0; m < n_pairs; ++m) {
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 0);
       // lse / delta of the step's 64 queries arrived with its Q / dO stage (rows past L read as 0: with Q = dO = 0
       // that gives P = 1, dS = 0, and the zero dO / Q rows keep dV / dK untouched)
       const int j = 2 * m + b, stg = j % AB3_ST;
       const uint32_t ls_u32 = st_u32 + (uint32_t)stg * SM::STAGE + 2 * B3_T64 + (uint32_t)h * 128u, dl_u32 = ls_u32 + 256u;
       mbar_wait(&full[stg], (uint32_t)((j / AB3_ST) & 1));
       mbar_wait(&sdp_full[b], (uint32_t)(m & 1));
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 1);
       tc_fence_after();
       uint32_t sr[32], dr[32];
       tmem_ld32(s_addr, sr);
       tmem_ld32(s_addr + 64, dr);
       tmem_ld_wait();
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 2);
 #pragma unroll
       for (int i4 = 0; i4 < 32; i4 += 4) {
         const float4 l4 = lds128f(ls_u32 + i4 * 4);   // warp-uniform address: broadcast LDS.128
@@ -257,7 +297,9 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
         }
       }
       // dV/dK of this group's previous step and dQ of the previous pair have read P^T / dS^T
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 3);
       if (m > 0) { mbar_wait(&pair_done[(m - 1) & 1], (uint32_t)(((m - 1) >> 1) & 1)); tc_fence_after(); }
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 4);
       // P^T -> tensor memory over this thread's own S^T columns, dS^T -> tensor memory over its dP^T columns (A
       // operands of dV / dK) and -> shared memory (MN-major A operand of dQ)
       uint32_t pp[16], dd[16];
@@ -276,9 +318,11 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
       fence_proxy_async_smem();
       tc_fence_before();
       mbar_arrive(&p_ready[b]);
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 5);
       // dQ tile of the previous pair -> staging -> bulk reduction, off the p_ready path (staging it under the
       // fence above saved a fence but delayed p_ready: 4.33 ms vs 4.0 ms at the bench shape)
-      if (m > 0) { stage_dq(m - 1); fence_proxy_async_smem(); issue_dq(m - 1); }
+      if (m > 0) { stage_dq(m - 1); fence_proxy_async_smem(); B3_TR(tr && m < 32, (b * 32 + m) * 8 + 6); issue_dq(m - 1); }
+      B3_TR(tr && m < 32, (b * 32 + m) * 8 + 7);
     }
     mbar_wait(&pair_done[(n_pairs - 1) & 1], (uint32_t)(((n_pairs - 1) >> 1) & 1));
     tc_fence_after();
@@ -373,11 +417,26 @@ int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int
   if ((rc = make_tmap_f32_linear(&m.lse, lse, 2, vdims, vstr, vbox))) return rc;
   if ((rc = make_tmap_f32_linear(&m.delta, delta, 2, vdims, vstr, vbox))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  p.trace = nullptr;
+#ifdef B3_TRACE
+  const char* trace_path = getenv("B2D_BWD3_TRACE");
+  if (trace_path) { cudaMalloc(&p.trace, 1024 * 8); cudaMemset(p.trace, 0, 1024 * 8); }
+#endif
   const long long rows = (long long)N * L;
   B2D_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * heads * 64 * sizeof(float), st));
   dim3 grid((unsigned)((L + 127) / 128), (unsigned)heads, (unsigned)N);
   attn_bwd_fused_kernel<<<grid, AB3_THREADS, Bwd3Smem::TOTAL, st>>>(m, p);
   B2D_CHECK_LAUNCH();
+#ifdef B3_TRACE
+  if (trace_path) {
+    static long long host[1024];
+    cudaDeviceSynchronize();
+    cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
+    FILE* f = fopen(trace_path, "wb");
+    if (f) { fwrite(host, 1, sizeof(host), f); fclose(f); }
+    cudaFree(p.trace);
+  }
+#endif
   const long long groups = rows * heads * 8;
   const unsigned fin_blocks = (unsigned)((groups + 255) / 256 < 148 * 16 ? (groups + 255) / 256 : 148 * 16);
   dq_finalize_kernel<<<fin_blocks, 256, 0, st>>>(dq_acc, (__half*)dqkv, lddqkv, rows, heads, p.q_off, p.head_stride, p.scale);
