@@ -4,14 +4,14 @@
 //
 // One CTA = 256 queries (two 128-row tiles) of one (sample, head); K/V tiles are streamed ONCE for both.
 // Warp roles (320 threads): warp 0 = TMA producer, warp 1 = tcgen05 issuer, warps 2..5 = softmax group 0
-// (query tile 0), warps 6..9 = softmax group 1 (query tile 1).  TMEM: S0 | S1 | O0 | O1.  While one group
+// (query tile 0), warps 6..9 = softmax group 1 (query tile 1).  TMEM: S0 | S1 | O0 | O1 | P0 | P1.  While one group
 // runs exp2 on its S tile the tensor pipe computes the other tile's S = Q K^T and O += P V, so the MUFU and
 // the tensor pipe overlap instead of alternating (the single-tile kernel spent ~7.9k clk per 128x128 tile
 // against a ~1k clk MUFU floor: profiles/r1_attention_ncu.md).
 //
 // Per KV tile j and query tile t:   s_full[t] (S ready) -> group t loads S into registers -> s_free[t]
-// (issuer may overwrite S_t with tile j+1) -> max / lazy O rescale / exp2 / P -> smem -> p_full[t]
-// -> issuer: O_t += P_t V_j -> pv_done[t] (P_t buffer and O_t reusable).
+// (issuer may overwrite S_t with tile j+1) -> max / lazy O rescale / exp2 / P -> tensor memory -> p_full[t]
+// -> issuer: O_t += P_t V_j (A from tensor memory) -> pv_done[t] (P_t columns and O_t reusable).
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
@@ -41,12 +41,17 @@ struct Fwd2Cfg {
   static constexpr int K_BYTES = BKV * D * 2;
   static constexpr int STAGE_BYTES = 2 * K_BYTES;       // K + V
   static constexpr int PT_BYTES = 128 * BKV * 2;        // one P tile
-  static constexpr int SMEM_DATA = 2 * QT_BYTES + ST * STAGE_BYTES + 2 * PT_BYTES;
+  static constexpr int SMEM_DATA = 2 * QT_BYTES + ST * STAGE_BYTES;
   static constexpr int NBARS = 1 + 3 * ST + 8;
   static constexpr int SMEM_TOTAL = SMEM_DATA + NBARS * 8 + 16 + 1024;
   static constexpr uint32_t S_COL = 0;                  // S_t at t * 128
   static constexpr uint32_t O_COL = 256;                // O_t at 256 + t * D
+  // P_t as fp16 pairs (BKV / 2 columns), the tensor-memory A operand of O += P V: behind O for D = 64, in the
+  // unused half of the S_t slot for D = 128
+  static constexpr uint32_t P_COL = (D == 64) ? 384 : 64;
+  static constexpr uint32_t P_STRIDE = (D == 64) ? 64 : 128;
   static_assert(BKV <= 128 && 256 + 2 * D <= 512, "TMEM budget");
+  static_assert((D == 64 && BKV == 128) || (D == 128 && BKV == 64), "P placement");
 };
 
 template <int D, int BKV>
@@ -57,8 +62,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint8_t* q_s = smem;
   uint8_t* kv_s = q_s + 2 * Cfg::QT_BYTES;
-  uint8_t* p_s = kv_s + Cfg::ST * Cfg::STAGE_BYTES;
-  uint64_t* bars = (uint64_t*)(p_s + 2 * Cfg::PT_BYTES);
+  uint64_t* bars = (uint64_t*)(kv_s + Cfg::ST * Cfg::STAGE_BYTES);
   uint64_t* q_full = bars;
   uint64_t* k_full = bars + 1;
   uint64_t* v_full = k_full + Cfg::ST;
@@ -122,7 +126,6 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
     const uint32_t idesc_s = make_idesc(128, BKV, 0, 0, FMT_F16, FMT_F16);  // S = Q K^T, both K-major
     const uint32_t idesc_o = make_idesc(128, D, 0, 1, FMT_F16, FMT_F16);    // O += P V, V MN-major
     const uint32_t q_addr = smem_u32(q_s);
-    const uint32_t p_addr = smem_u32(p_s);
     auto issue_s = [&](int j, int t) {     // S_t(j) = Q_t K_j^T ; caller has waited for K_j and for S_t to be free
       if (elect_one()) {
         const uint32_t k_addr = smem_u32(kv_s + (j % Cfg::ST) * Cfg::STAGE_BYTES);
@@ -142,11 +145,13 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
         const int s = j % Cfg::ST;
         const uint32_t v_addr = smem_u32(kv_s + s * Cfg::STAGE_BYTES + Cfg::K_BYTES);
         const uint32_t d_tmem = tmem_base + Cfg::O_COL + (uint32_t)(t * D);
+        // A = P_t from tensor memory (an N = 64 instruction with both operands in shared memory wants 192 B/clk of
+        // a 128 B/clk port: profiles/r1_attention_ncu.md), B = V_j MN-major from shared memory
+        const uint32_t a_tmem = tmem_base + Cfg::P_COL + (uint32_t)t * Cfg::P_STRIDE;
 #pragma unroll
         for (int kk = 0; kk < BKV / 16; ++kk) {
-          const uint32_t a = p_addr + t * Cfg::PT_BYTES + (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t b = v_addr + kk * 2048;
-          mma_f16_ss(d_tmem, make_sdesc_sw128(a, 16, 1024), make_sdesc_sw128(b, BKV * 128, 1024), idesc_o,
+          mma_f16_ts(d_tmem, a_tmem + (uint32_t)kk * 8u, make_sdesc_sw128(b, BKV * 128, 1024), idesc_o,
                      (uint32_t)((j | kk) != 0));
         }
         mma_commit(&pv_done[t]);
@@ -184,7 +189,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const uint32_t s_addr = lane_base + Cfg::S_COL + (uint32_t)t * 128u;
     const uint32_t o_addr = lane_base + Cfg::O_COL + (uint32_t)(t * D);
-    const uint32_t pt_u32 = smem_u32(p_s + t * Cfg::PT_BYTES);
+    const uint32_t p_taddr = lane_base + Cfg::P_COL + (uint32_t)t * Cfg::P_STRIDE;
     const float c = p.scale_log2;
     float m_used = -INFINITY;
     float l_sum = 0.f;
@@ -242,15 +247,14 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
       }
       l_sum += (ls0 + ls1) + (ls2 + ls3);
 #pragma unroll
-      for (int g = 0; g < BKV / 8; ++g) {
-        uint4 u;
-        u.x = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 0]), __uint_as_float(sr[8 * g + 1]));
-        u.y = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 2]), __uint_as_float(sr[8 * g + 3]));
-        u.z = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 4]), __uint_as_float(sr[8 * g + 5]));
-        u.w = pack_f16x2_nosat(__uint_as_float(sr[8 * g + 6]), __uint_as_float(sr[8 * g + 7]));
-        sts128(pt_u32 + (uint32_t)(g >> 3) * (128u * 128u) + sw128_offset((uint32_t)row, (uint32_t)((g & 7) * 8)), u);
+      for (int c0 = 0; c0 < BKV / 2; c0 += 16) {       // P_t -> tensor memory, two fp16 per column
+        uint32_t pk[16];
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+          pk[i] = pack_f16x2_nosat(__uint_as_float(sr[2 * (c0 + i)]), __uint_as_float(sr[2 * (c0 + i) + 1]));
+        tmem_st16(p_taddr + (uint32_t)c0, pk);
       }
-      fence_proxy_async_smem();
+      tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&p_full[t]);
     }
