@@ -35,39 +35,53 @@ struct AssembleParams {
   int N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad;
 };
 
+// grid = (pixel chunks, N); a thread owns one 8-channel vector (fixed for its lifetime) and walks pixels: everything
+// that depends only on the channel (class of each channel, the 1x1 cond_conv_in weights, the per-sample audio
+// values) is hoisted out of the pixel loop.  Cc <= 4 (the reference's conditioning image has 3 channels).
 __global__ void __launch_bounds__(256)
 assemble_input_kernel(AssembleParams p, __half* __restrict__ out) {
   const int V = p.Cpad >> 3;
-  const long long total = (long long)p.N * p.S * p.S * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
-    const int v = (int)(i % V);
-    const long long gp = i / V;
-    const int n = (int)(gp / (p.S * p.S));
-    const int pix = (int)(gp - (long long)n * p.S * p.S);
-    const int h = pix / p.S, w = pix - h * p.S;
+  const int v = threadIdx.x % V;
+  const int prow = threadIdx.x / V;
+  const int rows = blockDim.x / V;
+  const int n = blockIdx.y;
+  const int HW = p.S * p.S;
+  int kind[8];            // 0 zero, 1 x_t channel, 2 cond_conv_in output, 3 audio
+  float wq[8][4];         // kind 2: weights; kind 3: wq[j][0] = the value itself
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int c = v * 8 + j;
+    kind[j] = 0;
+    wq[j][0] = wq[j][1] = wq[j][2] = wq[j][3] = 0.f;
+    if (c < p.Cin) kind[j] = 1;
+    else if (c < p.Cin + p.Cim) {
+      kind[j] = 2;
+      for (int k = 0; k < p.Cc; ++k) wq[j][k] = __ldg(p.wcond + (long long)(c - p.Cin) * p.Cc + k);
+    } else if (c < p.Cin + p.Cim + p.A) {
+      kind[j] = 3;
+      wq[j][0] = __ldg(p.audio + (long long)n * p.A + (c - p.Cin - p.Cim));
+    }
+  }
+  bool any_cond = false, any_xt = false;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { any_cond |= kind[j] == 2; any_xt |= kind[j] == 1; }
+  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
+    float cv[4] = {0.f, 0.f, 0.f, 0.f};
+    if (any_cond) {
+      const int h = pix / p.S, w = pix - h * p.S;
+      const int sh = nearest_src(h, p.Hc, p.S), sw = nearest_src(w, p.Wc, p.S);
+      for (int k = 0; k < p.Cc; ++k) cv[k] = __ldg(p.cond + ((long long)n * p.Cc + k) * p.Hc * p.Wc + sh * p.Wc + sw);
+    }
     float o[8];
-    float cv[8];
-    bool have_cond = false;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int c = v * 8 + j;
       float val = 0.f;
-      if (c < p.Cin) {
-        val = p.xt[((long long)n * p.Cin + c) * p.S * p.S + pix];
-      } else if (c < p.Cin + p.Cim) {
-        if (!have_cond) {
-          const int sh = nearest_src(h, p.Hc, p.S), sw = nearest_src(w, p.Wc, p.S);
-          for (int k = 0; k < p.Cc && k < 8; ++k) cv[k] = p.cond[((long long)n * p.Cc + k) * p.Hc * p.Wc + sh * p.Wc + sw];
-          have_cond = true;
-        }
-        const float* wr = p.wcond + (long long)(c - p.Cin) * p.Cc;
-        for (int k = 0; k < p.Cc && k < 8; ++k) val = fmaf(__ldg(wr + k), cv[k], val);
-      } else if (c < p.Cin + p.Cim + p.A) {
-        val = __ldg(p.audio + (long long)n * p.A + (c - p.Cin - p.Cim));
-      }
+      if (kind[j] == 3) val = wq[j][0];
+      else if (kind[j] == 2) val = fmaf(wq[j][3], cv[3], fmaf(wq[j][2], cv[2], fmaf(wq[j][1], cv[1], wq[j][0] * cv[0])));
+      else if (kind[j] == 1 && any_xt) val = __ldg(p.xt + ((long long)n * p.Cin + v * 8 + j) * HW + pix);
       o[j] = val;
     }
-    store8_fmt(out + gp * p.Cpad + v * 8, o, FMT_F16);   // forward tensor
+    store8_fmt(out + ((long long)n * HW + pix) * p.Cpad + v * 8, o, FMT_F16);   // forward tensor
   }
 }
 
@@ -334,8 +348,13 @@ extern "C" int b2d_assemble_input(const float* xt, const float* cond, const floa
   B2D_REQUIRE(Cpad % 8 == 0 && Cin + Cim + A <= Cpad && Cc <= 8 && aligned16(out), B2D_ERR_SHAPE,
               "assemble_input: channels %d+%d+%d do not fit Cpad=%d", Cin, Cim, A, Cpad);
   AssembleParams p{xt, cond, wcond, audio, N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad};
-  const long long work = (long long)N * S * S * (Cpad / 8);
-  assemble_input_kernel<<<ew_blocks(work), 256, 0, (cudaStream_t)stream>>>(p, (__half*)out);
+  B2D_REQUIRE(Cc <= 4 && Cpad / 8 <= 256 && N <= 65535, B2D_ERR_SHAPE, "assemble_input: Cc=%d (max 4), Cpad=%d, N=%d", Cc, Cpad, N);
+  const int V = Cpad / 8, rows = 256 / V;
+  long long chunks = ((long long)S * S + rows - 1) / rows;
+  const long long cap = ((long long)num_sms() * 8 + N - 1) / N;
+  if (chunks > cap) chunks = cap;
+  if (chunks < 1) chunks = 1;
+  assemble_input_kernel<<<dim3((unsigned)chunks, (unsigned)N), V * rows, 0, (cudaStream_t)stream>>>(p, (__half*)out);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
