@@ -62,10 +62,82 @@ class DenoiserEngine:
         return val
 
     def w_fwd(self, conv, cin_pad=None):
-        return self._packed((id(conv), "f"), conv.weight, lambda w: ops.pack_conv_weight(w, cin_pad))
+        """Packed forward weights; for a Conv3d 3x3x3 (dims=3) a list of three 2-D tap groups [kt = 0, 1, 2]."""
+        def fn(w):
+            if w.dim() == 5:
+                if w.shape[2] == 1:
+                    return ops.pack_conv_weight(w[:, :, 0], cin_pad)
+                return [ops.pack_conv_weight(w[:, :, kt], cin_pad) for kt in range(w.shape[2])]
+            return ops.pack_conv_weight(w, cin_pad)
+        return self._packed((id(conv), "f"), conv.weight, fn)
 
     def w_dgrad(self, conv, cin_pad=None, cout_pad=None):
-        return self._packed((id(conv), "d"), conv.weight, lambda w: ops.pack_dgrad_weight(w, cin_pad, cout_pad))
+        """Packed data-gradient weights; Conv3d: temporally flipped list, so that `_conv` (out[t] = sum_kt
+        C(x[t + kt - 1], w[kt])) computes dx[t] = sum_kt D(dy[t - kt + 1], w[:, :, kt])."""
+        def fn(w):
+            if w.dim() == 5:
+                if w.shape[2] == 1:
+                    return ops.pack_dgrad_weight(w[:, :, 0], cin_pad, cout_pad)
+                return [ops.pack_dgrad_weight(w[:, :, kt], cin_pad, cout_pad) for kt in reversed(range(w.shape[2]))]
+            return ops.pack_dgrad_weight(w, cin_pad, cout_pad)
+        return self._packed((id(conv), "d"), conv.weight, fn)
+
+    # ------------------------------------------------------------------ dims=3 helpers (T frames folded into N)
+    def _conv(self, x, wp, cout, k, stride, x2=None, bias=None, emb=None, residual=None):
+        """conv2d, or -- for a list of three temporal tap groups -- the Conv3d sum over time-shifted frames:
+        the centre tap carries bias / emb / residual, the side taps accumulate in place through the residual input
+        on the frame ranges that have a neighbour (zero padding in time = no contribution)."""
+        if not isinstance(wp, list):
+            return ops.conv2d(x, wp, cout, k, stride, x2=x2, bias=bias, emb=emb, residual=residual)
+        T = self.T
+        out = ops.conv2d(x, wp[1], cout, k, stride, x2=x2, bias=bias, emb=emb, residual=residual)
+        if T > 1:
+            for lo in range(0, x.shape[0], T):
+                hi = lo + T
+                o = out[lo:hi]
+                ops.conv2d(x[lo:hi - 1], wp[0], cout, k, stride, x2=None if x2 is None else x2[lo:hi - 1],
+                           residual=o[1:], out=o[1:])
+                ops.conv2d(x[lo + 1:hi], wp[2], cout, k, stride, x2=None if x2 is None else x2[lo + 1:hi],
+                           residual=o[:T - 1], out=o[:T - 1])
+        return out
+
+    def _wgrad(self, x, dy, gbuf, k, stride, x2=None):
+        """conv2d_wgrad into a packed gradient; Conv3d gradients are packed [kt][Cout][tap][Cin]."""
+        if gbuf.dim() == 2:
+            return ops.conv2d_wgrad(x, dy, gbuf, k, stride, x2=x2)
+        T = self.T
+        ops.conv2d_wgrad(x, dy, gbuf[1], k, stride, x2=x2)
+        if T > 1:
+            for lo in range(0, x.shape[0], T):
+                hi = lo + T
+                ops.conv2d_wgrad(x[lo:hi - 1], dy[lo + 1:hi], gbuf[0], k, stride,
+                                 x2=None if x2 is None else x2[lo:hi - 1])
+                ops.conv2d_wgrad(x[lo + 1:hi], dy[lo:hi - 1], gbuf[2], k, stride,
+                                 x2=None if x2 is None else x2[lo + 1:hi])
+
+    def _fold(self, t):
+        """(B*T, H, W, C) -> (B, T*H, W, C): GroupNorm statistics and attention run over all T*H*W positions of a sample."""
+        if t is None or self.T == 1:
+            return t
+        n, h, w, c = t.shape
+        return t.view(n // self.T, self.T * h, w, c)
+
+    def _unfold(self, t, like):
+        if t is None or self.T == 1:
+            return t
+        return t.view(like.shape[0], like.shape[1], like.shape[2], t.shape[3])
+
+    def _gn_fwd(self, x, gn, x2=None, act=True, drop_p=0.0, seed=0):
+        y, mean, rstd = ops.groupnorm_fwd(self._fold(x), gn.weight.detach(), gn.bias.detach(), x2=self._fold(x2), act=act,
+                                          eps=gn.eps, drop_p=drop_p, seed=seed)
+        return self._unfold(y, x), mean, rstd
+
+    def _gn_bwd(self, G, x, gn, dy, mean, rstd, x2=None, act=True, drop_p=0.0, seed=0, add_a=None, add_b=None,
+                add_a_full=False):
+        dx1, dx2 = ops.groupnorm_bwd(self._fold(x), gn.weight.detach(), gn.bias.detach(), self._fold(dy), mean, rstd,
+                                     G.g(gn.weight), G.g(gn.bias), x2=self._fold(x2), act=act, eps=gn.eps, drop_p=drop_p,
+                                     seed=seed, add_a=self._fold(add_a), add_b=self._fold(add_b), add_a_full=add_a_full)
+        return self._unfold(dx1, x), self._unfold(dx2, x2) if x2 is not None else None
 
     def emb_cat(self):
         ws = [rb.emb_layers[1].weight for rb in self.resblocks]
@@ -89,8 +161,14 @@ class DenoiserEngine:
         """Returns (eps_pred fp32 (N,out_ch,S,S), tape).  tape is None when train is False."""
         m = self.model
         dev = xt.device
-        N, _, S, _ = xt.shape
-        tape = {"N": N, "S": S} if train else None
+        if xt.dim() == 5:                                 # dims=3: (B, C, T, S, S), frames folded into the batch
+            B, _, T, S, _ = xt.shape
+            N = B * T
+        else:
+            N, _, S, _ = xt.shape
+            B, T = N, 1
+        self.T = T
+        tape = {"N": N, "S": S, "B": B, "T": T} if train else None
         drop_p = float(m.dropout) if (m.training and train) else 0.0
         self._step_seed += 1
         seed_base = (self._step_seed << 20)
@@ -102,6 +180,8 @@ class DenoiserEngine:
         emb = ops.linear_fwd(e1, l2.weight.detach(), l2.bias.detach(), silu_in=True)
         wcat, bcat = self.emb_cat()
         emb_all = ops.linear_fwd(emb, wcat, bcat, silu_in=True)
+        if T > 1:                                         # one row per folded frame (unet.py:262-263 broadcasts over T)
+            emb_all = emb_all.repeat_interleave(T, dim=0)
         # --- input assembly (unet_audio.py:53-61) or plain NCHW -> pixel-major
         if self.is_audio:
             at = m.audio_transformer.transform[0]
@@ -110,7 +190,7 @@ class DenoiserEngine:
             x0 = ops.assemble_input(xt.contiguous(), cond.contiguous() if m.image_cond else None, wcond, avec, self.cin_pad)
         else:
             avec = None
-            x0 = ops.nchw_to_pixel_major(xt.contiguous(), self.cin_pad)
+            x0 = ops.nchw_to_pixel_major(xt.contiguous().view(B, xt.shape[1], T * S, S), self.cin_pad).view(N, S, S, self.cin_pad)
         if train:
             tape.update(te=te, e1=e1, emb=emb, emb_all=emb_all, avec=avec, x0=x0, cond=cond, audio_feat=audio_feat,
                         drop_p=drop_p)
@@ -122,18 +202,18 @@ class DenoiserEngine:
             if isinstance(layer, AttentionBlock):
                 return self._attn_fwd(layer, h, train)
             if isinstance(layer, Downsample):
-                out = ops.conv2d(h, self.w_fwd(layer.op), layer.out_channels, 3, 2, bias=layer.op.bias.detach())
+                out = self._conv(h, self.w_fwd(layer.op), layer.out_channels, 3, 2, bias=layer.op.bias.detach())
                 ctx = _Ctx("down", layer); ctx.t["x"] = h
                 return out, ctx
             if isinstance(layer, Upsample):
                 u = ops.upsample2x(h)
-                out = ops.conv2d(u, self.w_fwd(layer.conv), layer.out_channels, 3, 1, bias=layer.conv.bias.detach())
+                out = self._conv(u, self.w_fwd(layer.conv), layer.out_channels, 3, 1, bias=layer.conv.bias.detach())
                 ctx = _Ctx("up", layer); ctx.t["u"] = u
                 return out, ctx
             raise RuntimeError(f"unexpected layer {type(layer)}")
 
         conv_in = m.input_blocks[0][0]
-        h = ops.conv2d(x0, self.w_fwd(conv_in, self.cin_pad), conv_in.out_channels, 3, 1, bias=conv_in.bias.detach())
+        h = self._conv(x0, self.w_fwd(conv_in, self.cin_pad), conv_in.out_channels, 3, 1, bias=conv_in.bias.detach())
         hs = [h]
         idx = 0
         enc, mid, dec = [], [], []
@@ -160,9 +240,23 @@ class DenoiserEngine:
         if train:
             tape.update(enc=enc, mid=mid, dec=dec)
         gn, conv_out = m.out[0], m.out[2]
-        hh, mean, rstd = ops.groupnorm_fwd(h, gn.weight.detach(), gn.bias.detach(), act=True, eps=gn.eps)
+        hh, mean, rstd = self._gn_fwd(h, gn, act=True)
         out = torch.empty(N, m.out_channels, S, S, device=dev, dtype=torch.float32)
-        ops.conv2d(hh, self.w_fwd(conv_out), m.out_channels, 3, 1, bias=conv_out.bias.detach(), out_nchw_f32=out)
+        wo = self.w_fwd(conv_out)
+        if isinstance(wo, list):        # Conv3d head: the fp32 NCHW writer cannot accumulate, so the two side taps go
+            ops.conv2d(hh, wo[1], m.out_channels, 3, 1, bias=conv_out.bias.detach(), out_nchw_f32=out)   # through 3-channel
+            if T > 1:                                                                                      # temporaries
+                for lo in range(0, N, T):
+                    hi = lo + T
+                    tmp = torch.empty(T - 1, m.out_channels, S, S, device=dev, dtype=torch.float32)
+                    ops.conv2d(hh[lo:hi - 1], wo[0], m.out_channels, 3, 1, out_nchw_f32=tmp)
+                    out[lo + 1:hi] += tmp
+                    ops.conv2d(hh[lo + 1:hi], wo[2], m.out_channels, 3, 1, out_nchw_f32=tmp)
+                    out[lo:hi - 1] += tmp
+        else:
+            ops.conv2d(hh, wo, m.out_channels, 3, 1, bias=conv_out.bias.detach(), out_nchw_f32=out)
+        if xt.dim() == 5:
+            out = out.view(B, T, m.out_channels, S, S).permute(0, 2, 1, 3, 4).contiguous()
         if train:
             tape.update(head=dict(h=h, hh=hh, mean=mean, rstd=rstd))
         return out, tape
@@ -171,17 +265,16 @@ class DenoiserEngine:
         gn1, conv1 = rb.in_layers[0], rb.in_layers[2]
         gn2, conv2 = rb.out_layers[0], rb.out_layers[3]
         cout = rb.out_channels
-        h1, mean1, rstd1 = ops.groupnorm_fwd(x, gn1.weight.detach(), gn1.bias.detach(), x2=x2, act=True, eps=gn1.eps)
+        h1, mean1, rstd1 = self._gn_fwd(x, gn1, x2=x2, act=True)
         off = self.emb_off[id(rb)]
-        h2 = ops.conv2d(h1, self.w_fwd(conv1), cout, 3, 1, bias=conv1.bias.detach(), emb=emb_all[:, off:off + cout])
-        h3, mean2, rstd2 = ops.groupnorm_fwd(h2, gn2.weight.detach(), gn2.bias.detach(), act=True, eps=gn2.eps,
-                                             drop_p=drop_p, seed=seed)
+        h2 = self._conv(h1, self.w_fwd(conv1), cout, 3, 1, bias=conv1.bias.detach(), emb=emb_all[:, off:off + cout])
+        h3, mean2, rstd2 = self._gn_fwd(h2, gn2, act=True, drop_p=drop_p, seed=seed)
         if isinstance(rb.skip_connection, torch.nn.Identity):
             res = x
         else:
             sc = rb.skip_connection
             res = ops.conv2d(x, self.w_fwd(sc), cout, 1, 1, x2=x2, bias=sc.bias.detach())
-        out = ops.conv2d(h3, self.w_fwd(conv2), cout, 3, 1, bias=conv2.bias.detach(), residual=res)
+        out = self._conv(h3, self.w_fwd(conv2), cout, 3, 1, bias=conv2.bias.detach(), residual=res)
         ctx = None
         if train:
             ctx = _Ctx("res", rb)
@@ -192,9 +285,10 @@ class DenoiserEngine:
     def _attn_fwd(self, ab, x, train):
         gn = ab.norm
         C_ = ab.channels
-        hn, mean, rstd = ops.groupnorm_fwd(x, gn.weight.detach(), gn.bias.detach(), act=False, eps=gn.eps)
+        hn, mean, rstd = self._gn_fwd(x, gn, act=False)
         qkv = ops.conv2d(hn, self.w_fwd(ab.qkv), 3 * C_, 1, 1, bias=ab.qkv.bias.detach())
-        a, lse = ops.attention_fwd(qkv, ab.num_heads, ab.use_new_attention_order)
+        a, lse = ops.attention_fwd(self._fold(qkv), ab.num_heads, ab.use_new_attention_order)   # L = T*H*W (unet.py:312)
+        a = self._unfold(a, qkv)
         out = ops.conv2d(a, self.w_fwd(ab.proj_out), C_, 1, 1, bias=ab.proj_out.bias.detach(), residual=x)
         ctx = None
         if train:
@@ -218,7 +312,10 @@ class DenoiserEngine:
             w = conv.weight
             co, ci = w.shape[0], w.shape[1]
             taps = w.numel() // (co * ci)
-            return (max(64, _pad64(co)) if co < 64 else co, taps * (cin_pad or ci))
+            cop = max(64, _pad64(co)) if co < 64 else co
+            if w.dim() == 5 and w.shape[2] > 1:           # Conv3d: [kt][Cout][kh*kw][Cin]
+                return (w.shape[2], cop, (taps // w.shape[2]) * (cin_pad or ci))
+            return (cop, taps * (cin_pad or ci))
 
         def add_layer(stage, layer):
             if isinstance(layer, ResBlock):
@@ -308,7 +405,13 @@ class _Grads:
         if p.dim() == 1:                       # padded bias (head conv)
             return buf[:p.shape[0]]
         co, ci = p.shape[0], p.shape[1]
+        if p.dim() == 5 and buf.dim() == 3:     # Conv3d 3x3x3: packed [kt][CoutPad][9 * CinPad] -> (O, I, kt, kh, kw)
+            kt, kh, kw = p.shape[2:]
+            cip = buf.shape[2] // (kh * kw)
+            return buf.view(kt, buf.shape[1], kh, kw, cip)[:, :co, :, :, :ci].permute(1, 4, 0, 2, 3)
         taps = p.numel() // (co * ci)
+        if p.dim() == 5:                        # Conv3d 1x1x1
+            return buf.view(buf.shape[0], buf.shape[1] // taps)[:co, :ci].reshape(p.shape)
         k = int(round(taps ** 0.5)) if p.dim() == 4 else 1
         cip = buf.shape[1] // taps
         v = buf.view(buf.shape[0], taps, cip)[:co, :, :ci]         # [co][tap][ci]
@@ -323,9 +426,12 @@ class _Grads:
 def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     """Hand-scheduled backward.  dout: fp32 (N,out_ch,S,S).  Returns (_Grads, d_audio_feat or None)."""
     m = eng.model
-    N = tape["N"]
+    N, B, T = tape["N"], tape["B"], tape["T"]
+    eng.T = T
     dev = dout.device
     dout = dout.contiguous().float()
+    if dout.dim() == 5:                                   # (B, C, T, S, S) -> frames folded into the batch
+        dout = dout.permute(0, 2, 1, 3, 4).reshape(N, dout.shape[1], dout.shape[3], dout.shape[4]).contiguous()
     G = _Grads(eng, dev)
     d_emb_all = torch.zeros(N, eng.emb_total, device=dev, dtype=torch.float32)
     stage = 0
@@ -358,11 +464,10 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     hd = tape["head"]
     gn, conv_out = m.out[0], m.out[2]
     dyp = ops.nchw_to_pixel_major(dout, 64, scale=scale2)
-    ops.conv2d_wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
+    eng._wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
     bias_grad(dyp, conv_out.bias, 64)
-    d_hh = ops.conv2d(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1)
-    dh, _ = ops.groupnorm_bwd(hd["h"], gn.weight.detach(), gn.bias.detach(), d_hh, hd["mean"], hd["rstd"],
-                              G.g(gn.weight), G.g(gn.bias), act=True, eps=gn.eps)
+    d_hh = eng._conv(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1)
+    dh, _ = eng._gn_bwd(G, hd["h"], gn, d_hh, hd["mean"], hd["rstd"], act=True)
     done()
 
     def res_bwd(ctx, dout_, extra):
@@ -373,18 +478,16 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         x, x2 = t["x"], t["x2"]
         has_skip_conv = not isinstance(rb.skip_connection, torch.nn.Identity)
         # conv2 (out_layers[3]) and the skip path share dout_
-        ops.conv2d_wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
+        eng._wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
         bias_grad(dout_, conv2.bias, also=rb.skip_connection.bias if has_skip_conv else None)
-        d_h3 = ops.conv2d(dout_, eng.w_dgrad(conv2), cout, 3, 1)
-        d_h2, _ = ops.groupnorm_bwd(t["h2"], gn2.weight.detach(), gn2.bias.detach(), d_h3, t["mean2"], t["rstd2"],
-                                    G.g(gn2.weight), G.g(gn2.bias), act=True, eps=gn2.eps, drop_p=t["drop_p"],
-                                    seed=t["seed"])
+        d_h3 = eng._conv(dout_, eng.w_dgrad(conv2), cout, 3, 1)
+        d_h2, _ = eng._gn_bwd(G, t["h2"], gn2, d_h3, t["mean2"], t["rstd2"], act=True, drop_p=t["drop_p"], seed=t["seed"])
         off = eng.emb_off[id(rb)]
         ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)      # d emb_out (unet.py:266) and conv1 bias
         ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
-        ops.conv2d_wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
+        eng._wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
         cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
-        d_h1 = ops.conv2d(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1)
+        d_h1 = eng._conv(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1)
         if has_skip_conv:
             sc = rb.skip_connection
             ops.conv2d_wgrad(x, dout_, G.g(sc.weight), 1, 1, x2=x2)
@@ -392,9 +495,8 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
             full = True
         else:
             add_a, full = dout_, False
-        dx1, dx2 = ops.groupnorm_bwd(x, gn1.weight.detach(), gn1.bias.detach(), d_h1, t["mean1"], t["rstd1"],
-                                     G.g(gn1.weight), G.g(gn1.bias), x2=x2, act=True, eps=gn1.eps,
-                                     add_a=add_a, add_b=extra, add_a_full=full)
+        dx1, dx2 = eng._gn_bwd(G, x, gn1, d_h1, t["mean1"], t["rstd1"], x2=x2, act=True,
+                               add_a=add_a, add_b=extra, add_a_full=full)
         return dx1, dx2
 
     def attn_bwd(ctx, dout_, extra):
@@ -404,26 +506,26 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         ops.conv2d_wgrad(t["a"], dout_, G.g(ab.proj_out.weight), 1, 1)
         bias_grad(dout_, ab.proj_out.bias)
         d_a = ops.conv2d(dout_, eng.w_dgrad(ab.proj_out), C_, 1, 1)
-        dqkv = ops.attention_bwd(t["qkv"], t["a"], d_a, t["lse"], ab.num_heads, ab.use_new_attention_order)
+        dqkv = eng._unfold(ops.attention_bwd(eng._fold(t["qkv"]), eng._fold(t["a"]), eng._fold(d_a), t["lse"], ab.num_heads,
+                                             ab.use_new_attention_order), t["qkv"])
         ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
         bias_grad(dqkv, ab.qkv.bias)
         d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1)
-        dx, _ = ops.groupnorm_bwd(t["x"], gn_.weight.detach(), gn_.bias.detach(), d_hn, t["mean"], t["rstd"],
-                                  G.g(gn_.weight), G.g(gn_.bias), act=False, eps=gn_.eps, add_a=dout_, add_b=extra)
+        dx, _ = eng._gn_bwd(G, t["x"], gn_, d_hn, t["mean"], t["rstd"], act=False, add_a=dout_, add_b=extra)
         return dx
 
     def down_bwd(ctx, dout_, extra):
         layer, x = ctx.mod, ctx.t["x"]
-        ops.conv2d_wgrad(x, dout_, G.g(layer.op.weight), 3, 2)
+        eng._wgrad(x, dout_, G.g(layer.op.weight), 3, 2)
         bias_grad(dout_, layer.op.bias)
         z = ops.zero_insert2x(dout_)
-        return ops.conv2d(z, eng.w_dgrad(layer.op), layer.channels, 3, 1, residual=extra)
+        return eng._conv(z, eng.w_dgrad(layer.op), layer.channels, 3, 1, residual=extra)
 
     def up_bwd(ctx, dout_):
         layer, u = ctx.mod, ctx.t["u"]
-        ops.conv2d_wgrad(u, dout_, G.g(layer.conv.weight), 3, 1)
+        eng._wgrad(u, dout_, G.g(layer.conv.weight), 3, 1)
         bias_grad(dout_, layer.conv.bias)
-        du = ops.conv2d(dout_, eng.w_dgrad(layer.conv), layer.channels, 3, 1)
+        du = eng._conv(dout_, eng.w_dgrad(layer.conv), layer.channels, 3, 1)
         return ops.upsample2x_bwd(du)
 
     def layer_bwd(ctx, dout_, extra):
@@ -459,11 +561,11 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     # ---- input convolution
     conv_in = m.input_blocks[0][0]
     x0 = tape["x0"]
-    ops.conv2d_wgrad(x0, dh, G.g(conv_in.weight), 3, 1)
+    eng._wgrad(x0, dh, G.g(conv_in.weight), 3, 1)
     bias_grad(dh, conv_in.bias)
     d_feat = None
     if eng.is_audio:
-        dx0 = ops.conv2d(dh, eng.w_dgrad(conv_in, cin_pad=eng.cin_pad), eng.cin_pad, 3, 1)
+        dx0 = eng._conv(dh, eng.w_dgrad(conv_in, cin_pad=eng.cin_pad), eng.cin_pad, 3, 1)
     done()
     # ---- conditioning vectors
     wcat, _ = eng.emb_cat()
@@ -474,6 +576,8 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     off_b, _ = G.offsets[id(first_b)]
     dbcat = G.flat[off_b:off_b + eng.emb_total]
     l0, l2 = m.time_embed[0], m.time_embed[2]
+    if T > 1:                                             # emb_out was broadcast over the T frames of a sample
+        d_emb_all = d_emb_all.view(B, T, -1).sum(dim=1)
     d_emb = ops.linear_bwd(tape["emb"], wcat, None, d_emb_all, dwcat, dbcat, silu_in=True)
     d_e1 = ops.linear_bwd(tape["e1"], l2.weight.detach(), None, d_emb, G.g(l2.weight), G.g(l2.bias), silu_in=True)
     ops.linear_bwd(tape["te"], l0.weight.detach(), None, d_e1, G.g(l0.weight), G.g(l0.bias), need_dx=False)

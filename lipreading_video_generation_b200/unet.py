@@ -30,6 +30,15 @@ def normalization(channels: int) -> GroupNorm32:
     return GroupNorm32(32, channels)
 
 
+def conv_nd(dims: int, *args, **kwargs) -> nn.Module:
+    """utils.py:59-69 (parameter holder: Conv2d / Conv3d own the OIHW / OIDHW tensors under the reference keys)."""
+    if dims == 2:
+        return nn.Conv2d(*args, **kwargs)
+    if dims == 3:
+        return nn.Conv3d(*args, **kwargs)
+    raise ValueError(f"unsupported dimensions: {dims}")
+
+
 class TimestepEmbedSequential(nn.Sequential):
     """unet.py:78-90 (container only; dispatch happens in the engine)."""
 
@@ -42,7 +51,7 @@ class Upsample(nn.Module):
         if not use_conv:
             raise NotImplementedError("conv_resample=False is not on the train.py/test.py path")
         self.channels, self.out_channels, self.use_conv, self.dims = channels, out_channels or channels, use_conv, dims
-        self.conv = nn.Conv2d(self.channels, self.out_channels, 3, padding=1)
+        self.conv = conv_nd(dims, self.channels, self.out_channels, 3, padding=1)
 
 
 class Downsample(nn.Module):
@@ -53,7 +62,7 @@ class Downsample(nn.Module):
         if not use_conv:
             raise NotImplementedError("conv_resample=False is not on the train.py/test.py path")
         self.channels, self.out_channels, self.use_conv, self.dims = channels, out_channels or channels, use_conv, dims
-        self.op = nn.Conv2d(self.channels, self.out_channels, 3, stride=2, padding=1)
+        self.op = conv_nd(dims, self.channels, self.out_channels, 3, stride=2 if dims != 3 else (1, 2, 2), padding=1)  # unet.py:141
 
 
 class ResBlock(nn.Module):
@@ -68,14 +77,14 @@ class ResBlock(nn.Module):
         self.out_channels = out_channels or channels
         self.use_checkpoint = use_checkpoint
         self.in_layers = nn.Sequential(normalization(channels), nn.SiLU(),
-                                       nn.Conv2d(channels, self.out_channels, 3, padding=1))
+                                       conv_nd(dims, channels, self.out_channels, 3, padding=1))
         self.emb_layers = nn.Sequential(nn.SiLU(), nn.Linear(emb_channels, self.out_channels))
         self.out_layers = nn.Sequential(normalization(self.out_channels), nn.SiLU(), nn.Dropout(p=dropout),
-                                        zero_module(nn.Conv2d(self.out_channels, self.out_channels, 3, padding=1)))
+                                        zero_module(conv_nd(dims, self.out_channels, self.out_channels, 3, padding=1)))
         if self.out_channels == channels:
             self.skip_connection = nn.Identity()
         else:
-            self.skip_connection = nn.Conv2d(channels, self.out_channels, 1)
+            self.skip_connection = conv_nd(dims, channels, self.out_channels, 1)
 
 
 class AttentionBlock(nn.Module):
@@ -107,8 +116,8 @@ class UNetModel(nn.Module):
                  num_heads_upsample=-1, use_scale_shift_norm=False, resblock_updown=False,
                  use_new_attention_order=False):
         super().__init__()
-        if dims != 2:
-            raise NotImplementedError("dims=3 (temporal variant, SURVEY section 8 row a22) is not built yet")
+        if dims not in (2, 3):
+            raise NotImplementedError("dims=1 is never used by the reference's callers")
         if num_classes is not None or use_fp16 or resblock_updown or use_scale_shift_norm or not conv_resample:
             raise NotImplementedError("num_classes / use_fp16 / resblock_updown / use_scale_shift_norm / "
                                       "conv_resample=False are never used by train.py / test.py")
@@ -117,6 +126,7 @@ class UNetModel(nn.Module):
         if num_heads_upsample == -1:
             num_heads_upsample = num_heads
         self.image_size, self.in_channels, self.model_channels = image_size, in_channels, model_channels
+        self.dims = dims
         self.out_channels, self.num_res_blocks = out_channels, num_res_blocks
         self.attention_resolutions, self.dropout, self.channel_mult = attention_resolutions, dropout, channel_mult
         self.conv_resample, self.num_classes, self.use_checkpoint = conv_resample, num_classes, use_checkpoint
@@ -127,12 +137,12 @@ class UNetModel(nn.Module):
         self.time_embed = nn.Sequential(nn.Linear(model_channels, time_embed_dim), nn.SiLU(),
                                         nn.Linear(time_embed_dim, time_embed_dim))
         ch = input_ch = int(channel_mult[0] * model_channels)
-        self.input_blocks = nn.ModuleList([TimestepEmbedSequential(nn.Conv2d(in_channels, ch, 3, padding=1))])
+        self.input_blocks = nn.ModuleList([TimestepEmbedSequential(conv_nd(dims, in_channels, ch, 3, padding=1))])
         input_block_chans = [ch]
         ds = 1
         for level, mult in enumerate(channel_mult):
             for _ in range(num_res_blocks):
-                layers = [ResBlock(ch, time_embed_dim, dropout, out_channels=int(mult * model_channels),
+                layers = [ResBlock(ch, time_embed_dim, dropout, out_channels=int(mult * model_channels), dims=dims,
                                    use_checkpoint=use_checkpoint)]
                 ch = int(mult * model_channels)
                 if ds in attention_resolutions:
@@ -142,19 +152,19 @@ class UNetModel(nn.Module):
                 self.input_blocks.append(TimestepEmbedSequential(*layers))
                 input_block_chans.append(ch)
             if level != len(channel_mult) - 1:
-                self.input_blocks.append(TimestepEmbedSequential(Downsample(ch, conv_resample, out_channels=ch)))
+                self.input_blocks.append(TimestepEmbedSequential(Downsample(ch, conv_resample, dims=dims, out_channels=ch)))
                 input_block_chans.append(ch)
                 ds *= 2
         self.middle_block = TimestepEmbedSequential(
-            ResBlock(ch, time_embed_dim, dropout, use_checkpoint=use_checkpoint),
+            ResBlock(ch, time_embed_dim, dropout, dims=dims, use_checkpoint=use_checkpoint),
             AttentionBlock(ch, use_checkpoint=use_checkpoint, num_heads=num_heads,
                            num_head_channels=num_head_channels, use_new_attention_order=use_new_attention_order),
-            ResBlock(ch, time_embed_dim, dropout, use_checkpoint=use_checkpoint))
+            ResBlock(ch, time_embed_dim, dropout, dims=dims, use_checkpoint=use_checkpoint))
         self.output_blocks = nn.ModuleList([])
         for level, mult in list(enumerate(channel_mult))[::-1]:
             for i in range(num_res_blocks + 1):
                 ich = input_block_chans.pop()
-                layers = [ResBlock(ch + ich, time_embed_dim, dropout, out_channels=int(model_channels * mult),
+                layers = [ResBlock(ch + ich, time_embed_dim, dropout, out_channels=int(model_channels * mult), dims=dims,
                                    use_checkpoint=use_checkpoint)]
                 ch = int(model_channels * mult)
                 if ds in attention_resolutions:
@@ -162,11 +172,11 @@ class UNetModel(nn.Module):
                                                  num_head_channels=num_head_channels,
                                                  use_new_attention_order=use_new_attention_order))
                 if level and i == num_res_blocks:
-                    layers.append(Upsample(ch, conv_resample, out_channels=ch))
+                    layers.append(Upsample(ch, conv_resample, dims=dims, out_channels=ch))
                     ds //= 2
                 self.output_blocks.append(TimestepEmbedSequential(*layers))
         self.out = nn.Sequential(normalization(ch), nn.SiLU(),
-                                 zero_module(nn.Conv2d(input_ch, out_channels, 3, padding=1)))
+                                 zero_module(conv_nd(dims, input_ch, out_channels, 3, padding=1)))
         self._engine = None
 
     # -- engine plumbing -------------------------------------------------
@@ -181,7 +191,11 @@ class UNetModel(nn.Module):
         return denoiser_apply(self, xt, cond, audio_feat, timesteps)
 
     def forward(self, x, timesteps, y=None):
-        """unet.py:646-675.  x: (N, in_channels, S, S) fp32 on an sm_100a device."""
+        """unet.py:646-675.  x: (N, in_channels, S, S) fp32 on an sm_100a device; (B, in_channels, T, S, S) under
+        dims=3 (Conv3d 3x3x3 = three time-shifted 2-D tap groups on the frame-folded batch, GroupNorm and attention
+        over T*S*S tokens per sample, Downsample stride (1,2,2), Upsample (T, 2H, 2W): engine.py)."""
+        if x.dim() != self.dims + 2:
+            raise RuntimeError(f"expected a {self.dims + 2}-D input for dims={self.dims}, got {tuple(x.shape)}")
         assert (y is not None) == (self.num_classes is not None), \
             "must specify y if and only if the model is class-conditional"
         return self._torso(x, None, None, timesteps)

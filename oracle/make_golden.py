@@ -145,6 +145,43 @@ def unet_vectors(ref):
                 grads={k: grads[k] for k in keep})
 
 
+TINY3D = dict(image_size=16, in_channels=64, model_channels=64, out_channels=3, num_res_blocks=1,
+              attention_resolutions=(1, 2), dropout=0.0, channel_mult=(1, 2), dims=3, num_heads=1)
+
+
+def unet3d_vectors(ref):
+    """Tiny UNetModel(dims=3): forward, MSE loss and parameter gradients from the real
+    reference class on a (2, 64, 4, 16, 16) input; pins the restatement's conv_nd / temporal paths."""
+    torch.manual_seed(0)
+    model = ref.unet.UNetModel(**TINY3D)
+    new = R.fill_params({k: v for k, v in model.state_dict().items()}, seed=2)
+    model.load_state_dict(new)
+    model.train()
+    g = torch.Generator().manual_seed(31)
+    B, C, T, S = 2, TINY3D["in_channels"], 4, TINY3D["image_size"]
+    x = torch.randn(B, C, T, S, S, generator=g)
+    target = torch.randn(B, 3, T, S, S, generator=g)
+    t = torch.tensor([17, 903])
+    pred = model(x, t)
+    loss = torch.nn.MSELoss()(pred, target)
+    loss.backward()
+    grads = {k: p.grad.clone() for k, p in model.named_parameters() if p.grad is not None}
+    cfg = dict(model_channels=64, num_res_blocks=1, attention_resolutions=(1, 2), channel_mult=(1, 2), num_heads=1)
+    sdr = {k: v.clone().requires_grad_(True) for k, v in new.items()}
+    rp = R.unet_forward(sdr, cfg, x, t)
+    rl = R.mse(rp, target)
+    rl.backward()
+    assert (rp - pred).abs().max().item() <= 2e-5, (rp - pred).abs().max().item()
+    worst = max(((sdr[k].grad - gv).norm() / (gv.norm() + 1e-12)).item() for k, gv in grads.items())
+    assert worst <= 1e-4, worst
+    print(f"dims=3 restatement pinned: max|pred diff| {(rp - pred).abs().max().item():.2e}, worst grad rel {worst:.2e}")
+    keep = ["out.2.weight", "input_blocks.0.0.weight", "input_blocks.2.0.op.weight", "output_blocks.1.2.conv.weight",
+            "middle_block.1.qkv.weight", "input_blocks.1.0.in_layers.2.weight", "output_blocks.0.0.skip_connection.weight",
+            "input_blocks.1.0.emb_layers.1.weight", "time_embed.0.weight", "out.2.bias"]
+    return dict(cfg=dict(TINY3D), oracle_cfg=cfg, seed=2, x=x, target=target, t=t, pred=pred.detach(), loss=loss.detach(),
+                grad_norms={k: v.norm().item() for k, v in grads.items()}, grads={k: grads[k] for k in keep})
+
+
 def main():
     torch.set_num_threads(max(1, os.cpu_count() or 1))
     ref = ref_import.load()
@@ -153,6 +190,7 @@ def main():
     torch.save(sampler_vectors(ref), os.path.join(GOLD, "samplers.pt"))
     torch.save(q_sample_vectors(ref), os.path.join(GOLD, "q_sample.pt"))
     torch.save(unet_vectors(ref), os.path.join(GOLD, "unet_tiny.pt"))
+    torch.save(unet3d_vectors(ref), os.path.join(GOLD, "unet3d_tiny.pt"))
     for f in sorted(os.listdir(GOLD)):
         print(f, os.path.getsize(os.path.join(GOLD, f)))
 

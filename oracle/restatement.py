@@ -110,18 +110,26 @@ def group_norm32(x, w, b):
     return F.group_norm(x.float(), 32, w, b, 1e-5).type(x.dtype)
 
 
+def conv_nd(x, w, b=None, stride=1, padding=0):
+    """utils.py:59-69 conv_nd: nn.Conv2d for dims=2, nn.Conv3d for dims=3 (chosen here by the weight's rank);
+    a stride-2 downsample is (1, 2, 2) under dims=3 (unet.py:141)."""
+    if w.dim() == 5:
+        return F.conv3d(x, w, b, stride=(1, stride, stride) if stride != 1 else 1, padding=padding)
+    return F.conv2d(x, w, b, stride=stride, padding=padding)
+
+
 def res_block(sd, pre, x, emb, dropout_mask=None):
     """unet.py:248-268 (use_scale_shift_norm=False, no up/down)."""
-    h = F.conv2d(F.silu(group_norm32(x, sd[pre + "in_layers.0.weight"], sd[pre + "in_layers.0.bias"])),
-                 sd[pre + "in_layers.2.weight"], sd[pre + "in_layers.2.bias"], padding=1)
+    h = conv_nd(F.silu(group_norm32(x, sd[pre + "in_layers.0.weight"], sd[pre + "in_layers.0.bias"])),
+                sd[pre + "in_layers.2.weight"], sd[pre + "in_layers.2.bias"], padding=1)
     emb_out = F.linear(F.silu(emb), sd[pre + "emb_layers.1.weight"], sd[pre + "emb_layers.1.bias"])
-    h = h + emb_out[:, :, None, None]
+    h = h + emb_out.reshape(emb_out.shape + (1,) * (h.dim() - 2))        # unet.py:262-263
     h = F.silu(group_norm32(h, sd[pre + "out_layers.0.weight"], sd[pre + "out_layers.0.bias"]))
     if dropout_mask is not None:
         h = h * dropout_mask
-    h = F.conv2d(h, sd[pre + "out_layers.3.weight"], sd[pre + "out_layers.3.bias"], padding=1)
+    h = conv_nd(h, sd[pre + "out_layers.3.weight"], sd[pre + "out_layers.3.bias"], padding=1)
     if pre + "skip_connection.weight" in sd:
-        x = F.conv2d(x, sd[pre + "skip_connection.weight"], sd[pre + "skip_connection.bias"])
+        x = conv_nd(x, sd[pre + "skip_connection.weight"], sd[pre + "skip_connection.bias"])
     return x + h
 
 
@@ -163,13 +171,14 @@ def attention_block(sd, pre, x, n_heads, new_order=False):
 
 def unet_forward(sd, cfg, x, timesteps):
     """unet.py:646-675 with the block structure of unet.py:497-628 re-derived from cfg =
-    dict(model_channels, num_res_blocks, attention_resolutions, channel_mult, num_heads[, new_order])."""
+    dict(model_channels, num_res_blocks, attention_resolutions, channel_mult, num_heads[, new_order]).
+    dims=3 (x of rank 5, Conv3d weights in sd) follows the same code through conv_nd."""
     mc, nrb = cfg["model_channels"], cfg["num_res_blocks"]
     heads, new_order = cfg.get("num_heads", 1), cfg.get("new_order", False)
     emb = F.linear(timestep_embedding(timesteps, mc), sd["time_embed.0.weight"], sd["time_embed.0.bias"])
     emb = F.linear(F.silu(emb), sd["time_embed.2.weight"], sd["time_embed.2.bias"])
     hs = []
-    h = F.conv2d(x, sd["input_blocks.0.0.weight"], sd["input_blocks.0.0.bias"], padding=1)
+    h = conv_nd(x, sd["input_blocks.0.0.weight"], sd["input_blocks.0.0.bias"], padding=1)
     hs.append(h)
     idx, ds = 1, 1
     n_levels = len(cfg["channel_mult"])
@@ -181,7 +190,7 @@ def unet_forward(sd, cfg, x, timesteps):
             hs.append(h)
             idx += 1
         if level != n_levels - 1:
-            h = F.conv2d(h, sd[f"input_blocks.{idx}.0.op.weight"], sd[f"input_blocks.{idx}.0.op.bias"], stride=2, padding=1)
+            h = conv_nd(h, sd[f"input_blocks.{idx}.0.op.weight"], sd[f"input_blocks.{idx}.0.op.bias"], stride=2, padding=1)
             hs.append(h)
             idx += 1
             ds *= 2
@@ -198,12 +207,15 @@ def unet_forward(sd, cfg, x, timesteps):
                 h = attention_block(sd, f"output_blocks.{idx}.{j}.", h, heads, new_order)
                 j += 1
             if level and i == nrb:
-                h = F.interpolate(h, scale_factor=2, mode="nearest")
-                h = F.conv2d(h, sd[f"output_blocks.{idx}.{j}.conv.weight"], sd[f"output_blocks.{idx}.{j}.conv.bias"], padding=1)
+                if h.dim() == 5:                                      # unet.py:114-117: time axis kept
+                    h = F.interpolate(h, (h.shape[2], h.shape[3] * 2, h.shape[4] * 2), mode="nearest")
+                else:
+                    h = F.interpolate(h, scale_factor=2, mode="nearest")
+                h = conv_nd(h, sd[f"output_blocks.{idx}.{j}.conv.weight"], sd[f"output_blocks.{idx}.{j}.conv.bias"], padding=1)
                 ds //= 2
             idx += 1
     h = F.silu(group_norm32(h, sd["out.0.weight"], sd["out.0.bias"]))
-    return F.conv2d(h, sd["out.2.weight"], sd["out.2.bias"], padding=1)
+    return conv_nd(h, sd["out.2.weight"], sd["out.2.bias"], padding=1)
 
 
 def unet_audio_forward(sd, cfg, image, cond_image, audio_feat_mean, timesteps):

@@ -154,7 +154,7 @@ def test_full_config_state_dict_equals_live_reference():
 
 def test_unsupported_constructor_options_raise_not_implemented():
     import lipreading_video_generation_b200 as P
-    for kw in (dict(dims=3), dict(num_classes=10), dict(use_scale_shift_norm=True), dict(resblock_updown=True),
+    for kw in (dict(dims=1), dict(num_classes=10), dict(use_scale_shift_norm=True), dict(resblock_updown=True),
                dict(use_fp16=True), dict(conv_resample=False)):
         with pytest.raises(NotImplementedError):
             P.UNetModel(32, 64, 64, 3, 1, (1,), channel_mult=(1,), **kw)
@@ -224,3 +224,22 @@ def test_single_channel_conv1d_matches_stock_module():
         assert float((y2 - y1).norm() / y1.norm()) <= 1e-5
         for (n1, p1), (_, p2) in zip(stock.named_parameters(), fast.named_parameters()):
             assert float((p2.grad - p1.grad).norm() / p1.grad.norm()) <= 1e-5, n1
+
+
+def test_dims3_module_tree_has_the_reference_keys_and_conv3d_shapes():
+    """UNetModel(dims=3): same state_dict keys as dims=2, Conv3d (O, I, 3, 3, 3) weights,
+    Downsample stride (1, 2, 2) (unet.py:141); where /root/reference is mounted, keys and shapes equal the live class."""
+    import lipreading_video_generation_b200 as P
+    kw = dict(image_size=16, in_channels=64, model_channels=64, out_channels=3, num_res_blocks=1,
+              attention_resolutions=(1, 2), channel_mult=(1, 2))
+    m3, m2 = P.UNetModel(dims=3, **kw), P.UNetModel(dims=2, **kw)
+    assert list(m3.state_dict()) == list(m2.state_dict())
+    assert tuple(m3.input_blocks[0][0].weight.shape) == (64, 64, 3, 3, 3)
+    assert tuple(m3.input_blocks[2][0].op.stride) == (1, 2, 2)
+    assert tuple(m3.input_blocks[3][0].skip_connection.weight.shape) == (128, 64, 1, 1, 1)
+    if os.path.isdir("/root/reference/video-generation/diffusion"):
+        from oracle import ref_import
+        ref = ref_import.load()
+        r = ref.unet.UNetModel(dims=3, **kw)
+        assert {k: tuple(v.shape) for k, v in r.state_dict().items()} == \
+               {k: tuple(v.shape) for k, v in m3.state_dict().items()}
