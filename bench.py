@@ -29,6 +29,8 @@ WORKLOADS = {
     "train128": (16, 16, 128, "train"),    # BASELINE configs[2] per-GPU shape
     "sample128": (8, 16, 128, "sample"),   # BASELINE configs[3] per-GPU shape
     "train64_1clip": (1, 16, 64, "train"),  # diagnostic: 16x less GPU work, same launches -> host cost of one step
+    "train3d_cfg5": (1, 64, 128, "train3d"),   # BASELINE configs[4]: UNetModel(dims=3) on one (195, 64, 128, 128) clip
+    "train3d_small": (1, 16, 64, "train3d"),   # the same path at (195, 16, 64, 64)
 }
 FWD_GFLOP_PER_IMAGE = {64: 43.87, 128: 470.21}     # SURVEY section 8(d), algorithmic, UNet torso
 
@@ -271,6 +273,101 @@ def main_sample(a, model, S, clips, frames, world, rank, local, device, config, 
     print(json.dumps(out))
 
 
+def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores):
+    """UNetModel(dims=3) train step on whole clips: x (B, 195, T, S, S) -> eps (B, 3, T, S, S),
+    MSE, backward, Adam.  Attention runs over L = T*S*S positions per clip (1,048,576 at cfg5), which the reference
+    cannot materialise; clips shard over ranks like the 2-D path."""
+    import lipreading_video_generation_b200 as P
+    from lipreading_video_generation_b200 import _lib as L, ops
+    assert world == 1, "train3d workloads are single-GPU for now (no gradient all-reduce is wired for them)"
+    torch.manual_seed(0)
+    model = P.UNetModel(image_size=S, in_channels=195, model_channels=64, out_channels=3, num_res_blocks=2,
+                        attention_resolutions=(1, 2, 4), dropout=0.1, channel_mult=(1, 2, 4), dims=3)
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for name, p in model.named_parameters():
+            if (".out_layers.3." in name) or (".proj_out." in name) or name.startswith("out.2."):
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+    model = model.to(device).train()
+    opt = torch.optim.Adam(model.parameters(), lr=1e-2, fused=True)
+    crit = P.MSELoss()
+    gi = torch.Generator().manual_seed(1234 + rank)
+    hx = torch.randn(clips, 195, frames, S, S, generator=gi).pin_memory()
+    heps = torch.randn(clips, 3, frames, S, S, generator=gi).pin_memory()
+    ht = torch.randint(0, 1000, (clips,), generator=gi).pin_memory()
+    x, eps, t = hx.to(device), heps.to(device), ht.to(device)
+
+    def step(x_, eps_, t_):
+        opt.zero_grad(set_to_none=True)
+        loss = crit(model(x_, t_), eps_)
+        loss.backward()
+        opt.step()
+        return loss
+
+    def barrier():
+        if world > 1:
+            torch.distributed.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(a.warmup):
+        step(x, eps, t)
+    barrier()
+    l0 = L.lib().b2d_launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
+        e0.record()
+        for _ in range(a.steps):
+            step(x, eps, t)
+        e1.record()
+        barrier()
+    ms = e0.elapsed_time(e1) / a.steps
+    launches = (L.lib().b2d_launch_count() - l0) // a.steps
+    barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(a.steps):
+        loss = step(hx.to(device, non_blocking=True), heps.to(device, non_blocking=True), ht.to(device, non_blocking=True))
+        loss_host = loss.item()
+    f1.record()
+    barrier()
+    ms_e2e = f0.elapsed_time(f1) / a.steps
+    with ops.KernelTimer({"attention_fwd", "attention_bwd", "conv2d", "conv2d_wgrad", "groupnorm_fwd", "groupnorm_bwd"}) as kt_all:
+        step(x, eps, t)
+        barrier()
+    if world > 1:
+        tt = torch.tensor([ms, ms_e2e], device=device)
+        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+        ms, ms_e2e = tt.tolist()
+        torch.distributed.destroy_process_group()
+    if rank != 0:
+        return
+    burst, sustained, hbm, which = peaks()
+    dom, by_class = None, {}
+    for (name, meta), (t_ms, cnt) in kt_all.totals().items():
+        by_class[name] = by_class.get(name, 0.0) + t_ms
+    for (name, meta), (t_ms, cnt) in kt.totals().items():
+        Nn, Lq, heads, ch = meta
+        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lq * ch * heads * Nn
+        rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, tflops=flops / (t_ms / cnt) / 1e9,
+                   ms_per_step=t_ms / a.steps)
+        if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
+            dom = rec
+    h2d = sum(v.numel() * v.element_size() for v in (hx, heps, ht))
+    out = {"metric": "denoiser_train_clips_per_s", "value": round(clips * world / (ms / 1000.0), 4), "unit": "clips/s",
+           "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
+           "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
+           "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 4), "unit": "clips/s", "h2d_bytes_per_step": h2d,
+                   "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
+           "gpu_launches": int(launches),
+           "roofline": {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
+                        "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
+                        "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
+                        "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch fwd, 10*L^2*ch bwd"},
+           "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
+           "cpu_baseline": None, "clocks": clk.summary(), "last_loss": loss_host}
+    print(json.dumps(out))
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -287,6 +384,10 @@ def main():
                           f"(N={clips * frames} images folded into the batch), UNetAudio train.py config + wav2vec2-base",
               "clips_per_gpu": clips, "frames": frames, "image": S, "parallelism": f"dp{world}",
               "l2_policy": "inputs+activations >> L2 (126 MB): >10 GB touched per step"}
+    if kind == "train3d":
+        config["workload"] = (f"{a.workload}: UNetModel(dims=3) train step on {clips} clip(s) (195, {frames}, {S}, {S}) per GPU, "
+                              f"train.py torso config (64 ch, mult (1,2,4), 2 res blocks, attention at all levels over "
+                              f"L = T*S*S = {frames * S * S} positions), MSE + backward + Adam, no audio encoder")
 
     if a.impl == "reference":
         # The reference is PyTorch-CPU here (/root/reference does not travel): its oracle port, all host threads.
@@ -317,6 +418,8 @@ def main():
     from lipreading_video_generation_b200.parallel import broadcast_parameters
     L.check(L.lib().b2d_check_device(), "b2d_check_device")
     n_img = clips * frames
+    if kind == "train3d":
+        return main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
     model = build_model(S, device)
     if world > 1:
         broadcast_parameters(model)
