@@ -221,6 +221,14 @@ int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, i
 int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream);
 /* x[i] *= *scale  (unscale the fp32 parameter gradients). */
 int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream);
+/* fp32 convolution weights (state_dict layout, element strides s_o / s_i / s_k over Cout / Cin / the K = kh*kw
+ * taps; a Conv3d temporal slice is a strided view) -> the fp16 operand layout of b2d_conv2d:
+ *   transpose == 0 (fprop):  out[co][k][ci]      = w[co][ci][k]        rows_pad >= Cout, inner_pad >= Cin
+ *   transpose == 1 (dgrad):  out[ci][K-1-k][co]  = w[co][ci][k]        rows_pad >= Cin,  inner_pad >= Cout
+ * zero padded, saturated to +-65504.  Replaces the host side's permute / clamp / cast / scatter chain
+ * (~10 PyTorch launches per convolution per optimiser step). */
+int b2d_pack_conv_weight(const float* w, int64_t s_o, int64_t s_i, int64_t s_k, int Cout, int Cin, int K,
+                         int transpose, void* out, int rows_pad, int inner_pad, void* stream);
 /* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x fp16 (N,HW,ld)): emb_out / bias / audio gradients. */
 int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */

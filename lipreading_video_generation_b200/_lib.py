@@ -76,6 +76,8 @@ SIGNATURES = {
     "b2d_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
     "b2d_attention_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p,
                                   c_void_p]),
+    "b2d_pack_conv_weight": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int,
+                                     c_void_p]),
     "b2d_attention_bwd_ws_floats": (c_int64, [c_int, c_int, c_int, c_int]),
     "b2d_attention_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int, c_int,
                                   c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),

@@ -213,6 +213,24 @@ nchw_to_pixel_major_kernel(const float* __restrict__ src, __half* __restrict__ d
   }
 }
 
+// ------------------------------------------------------------------ weight packing (fp32 state_dict -> fp16 operand)
+__global__ void __launch_bounds__(256)
+pack_conv_weight_kernel(const float* __restrict__ w, long long s_o, long long s_i, long long s_k, int Cout, int Cin,
+                        int K, int transpose, __half* __restrict__ out, int rows_pad, int inner_pad) {
+  const long long total = (long long)rows_pad * K * inner_pad;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % inner_pad);
+    const long long rk = i / inner_pad;
+    const int k = (int)(rk % K);
+    const int r = (int)(rk / K);
+    const int co = transpose ? c : r, ci = transpose ? r : c;
+    const int kw = transpose ? K - 1 - k : k;
+    float v = 0.f;
+    if (co < Cout && ci < Cin) v = fminf(fmaxf(__ldg(w + co * s_o + ci * s_i + kw * s_k), -65504.f), 65504.f);
+    out[i] = __float2half_rn(v);
+  }
+}
+
 // ------------------------------------------------------------------ per-sample column sums
 // out[n][c] += sum_pix x[n, pix, c_off + c]   (emb_out gradient unet.py:266; bias grads = sum over n)
 __global__ void __launch_bounds__(256)
@@ -436,6 +454,17 @@ extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, in
   if (chunks < 1) chunks = 1;
   dim3 grid((unsigned)chunks, (unsigned)N);
   colsum_kernel<<<grid, V * rows, C * sizeof(float), (cudaStream_t)stream>>>((const __half*)x, ld, c_off, C, HW, out, ldout);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_pack_conv_weight(const float* w, int64_t s_o, int64_t s_i, int64_t s_k, int Cout, int Cin, int K,
+                                    int transpose, void* out, int rows_pad, int inner_pad, void* stream) {
+  B2D_REQUIRE(w && out && Cout > 0 && Cin > 0 && K > 0, B2D_ERR_SHAPE, "pack_conv_weight: bad arguments");
+  B2D_REQUIRE(rows_pad >= (transpose ? Cin : Cout) && inner_pad >= (transpose ? Cout : Cin), B2D_ERR_SHAPE,
+              "pack_conv_weight: padded shape (%d, %d) smaller than the weights (%d, %d)", rows_pad, inner_pad, Cout, Cin);
+  const long long total = (long long)rows_pad * K * inner_pad;
+  pack_conv_weight_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(w, s_o, s_i, s_k, Cout, Cin, K, transpose,
+                                                                                 (__half*)out, rows_pad, inner_pad);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

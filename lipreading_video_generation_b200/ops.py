@@ -65,6 +65,17 @@ class _timed:
             KernelTimer.active.records.append((self.name, self.meta, self.e0, e1))
 
 
+def _pack_on_device(w4: torch.Tensor, transpose: int, rows_pad: int, inner_pad: int) -> torch.Tensor:
+    """One launch of b2d_pack_conv_weight on the (possibly strided) OIHW view; same values as the torch chain below."""
+    co, ci, kh, kw = w4.shape
+    if kh * kw > 1 and w4.stride(2) != kw * w4.stride(3):
+        w4 = w4.contiguous()
+    out = torch.empty(rows_pad, kh * kw * inner_pad, device=w4.device, dtype=F16)
+    L.check(L.lib().b2d_pack_conv_weight(w4.data_ptr(), w4.stride(0), w4.stride(1), w4.stride(3), co, ci, kh * kw,
+                                         transpose, out.data_ptr(), rows_pad, inner_pad, _s()), "b2d_pack_conv_weight")
+    return out
+
+
 def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: int = 16) -> torch.Tensor:
     """OIHW (or OI / OIK for Linear / Conv1d) fp32 -> fp16 [CoutPad][kh*kw*CinPad] (tap-major, channel-minor)."""
     if w.dim() == 2:
@@ -74,6 +85,8 @@ def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: i
     co, ci, kh, kw = w.shape
     cip = ci if cin_pad is None else cin_pad
     cop = (co + cout_pad_to - 1) // cout_pad_to * cout_pad_to
+    if w.is_cuda and w.dtype == torch.float32:
+        return _pack_on_device(w, 0, cop, cip)
     p = torch.zeros(cop, kh * kw, cip, device=w.device, dtype=F16)
     p[:co, :, :ci] = w.permute(0, 2, 3, 1).reshape(co, kh * kw, ci).clamp(-_F16_MAX, _F16_MAX).to(F16)
     return p.reshape(cop, kh * kw * cip)
@@ -89,6 +102,8 @@ def pack_dgrad_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad: int
     co, ci, kh, kw = w.shape
     cip = ci if cin_pad is None else cin_pad
     cop = co if cout_pad is None else cout_pad
+    if w.is_cuda and w.dtype == torch.float32:
+        return _pack_on_device(w, 1, (cip + 15) // 16 * 16, cop)
     wf = torch.flip(w, dims=(2, 3)).permute(1, 2, 3, 0).reshape(ci, kh * kw, co)  # [ci][tap'][co]
     p = torch.zeros((cip + 15) // 16 * 16, kh * kw, cop, device=w.device, dtype=F16)
     p[:ci, :, :co] = wf.clamp(-_F16_MAX, _F16_MAX).to(F16)

@@ -318,3 +318,18 @@ def test_attention_full_resolution_row_sums():
     vmean = qkv2[..., 128:].float().mean(dim=(1, 2), keepdim=True)
     assert (out2.float().cpu() - vmean).abs().max().item() <= 2e-3
     assert torch.allclose(lse.cpu(), torch.full_like(lse.cpu(), math.log2(H * H)), atol=1e-4)
+
+
+def test_device_weight_packing_equals_host_chain_bit_exactly():
+    """b2d_pack_conv_weight (one launch) against the torch permute / clamp / cast / scatter chain it replaces: fprop and
+    dgrad layouts, channel padding, a value beyond the fp16 range, and a strided Conv3d temporal slice."""
+    from lipreading_video_generation_b200 import ops
+    g = gen(11)
+    w = torch.randn(24, 40, 3, 3, generator=g)
+    w[0, 0, 0, 0] = 1e6
+    w5 = torch.randn(16, 24, 3, 3, 3, generator=g)
+    cases = [(w, dict(cin_pad=64)), (w, dict()), (w5[:, :, 1], dict(cin_pad=64)), (torch.randn(8, 16, 1, generator=g), dict())]
+    for wt, kw in cases:
+        assert torch.equal(ops.pack_conv_weight(wt.cuda(), **kw).cpu(), ops.pack_conv_weight(wt, **kw))
+    for wt, kw in [(w, dict(cin_pad=64, cout_pad=64)), (w, dict()), (w5[:, :, 2], dict())]:
+        assert torch.equal(ops.pack_dgrad_weight(wt.cuda(), **kw).cpu(), ops.pack_dgrad_weight(wt, **kw))
