@@ -229,6 +229,20 @@ int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream);
  * (~10 PyTorch launches per convolution per optimiser step). */
 int b2d_pack_conv_weight(const float* w, int64_t s_o, int64_t s_i, int64_t s_k, int Cout, int Cin, int K,
                          int transpose, void* out, int rows_pad, int inner_pad, void* stream);
+/* Audio encoder front end.  unet_audio.py:10-18 instantiates HF transformers' Wav2Vec2Model (third-party, not in
+ * the reference tree); the first feature-extractor layer (`Wav2Vec2GroupNormConvLayer`: Conv1d(1 -> C, kernel K = 10,
+ * stride, no padding) -> GroupNorm(C, C) -> erf GELU) produces the encoder's largest activation, (N, C, T) with
+ * T = (S - K) / stride + 1 <= 800.  These two calls replace the layer's conv / norm / activation library ops:
+ *   fwd:  out (N, C, T) in out_dtype (0 = fp32, 1 = bf16, 2 = fp16), mean / rstd (N, C) fp32 kept for the backward;
+ *   bwd:  dw (C, K), dbias (C, may be NULL), dgamma (C), dbeta (C) are ACCUMULATED (+=); the waveform gets no gradient.
+ * audio (N, S) fp32 with row stride ld_audio; bias may be NULL (wav2vec2-base has conv_bias = false). */
+int b2d_w2v_layer0_fwd(const float* audio, int64_t ld_audio, const float* w, const float* bias, const float* gamma,
+                       const float* beta, int N, int S, int C, int K, int stride, float eps, void* out, int out_dtype,
+                       float* mean, float* rstd, void* stream);
+int b2d_w2v_layer0_bwd(const float* audio, int64_t ld_audio, const float* w, const float* bias, const float* gamma,
+                       const float* beta, int N, int S, int C, int K, int stride, float eps, const void* dout,
+                       int dout_dtype, const float* mean, const float* rstd, float* dw, float* dbias, float* dgamma,
+                       float* dbeta, void* stream);
 /* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x fp16 (N,HW,ld)): emb_out / bias / audio gradients. */
 int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */

@@ -1,0 +1,272 @@
+// wav2vec2_frontend.cu -- the first feature-extractor layer of the audio encoder the reference instantiates in
+// unet_audio.py:10-18 (HF transformers `Wav2Vec2Model`, third-party; layer class `Wav2Vec2GroupNormConvLayer`:
+// Conv1d(1 -> C, kernel 10, stride 5, no padding) -> GroupNorm(C groups of one channel, affine) -> GELU(erf)).
+//
+// At the training shape (256 windows x 4000 samples -> (256, 512, 799)) this single layer produces the largest
+// activation of the whole encoder; run as separate library ops (conv, fp32 GroupNorm with its casts, GELU and their
+// backwards) it moves that 105 M-element tensor ~20 times.  Here the waveform window sits in shared memory, the conv
+// output of one (window, channel) row lives in the registers of one warp, and the row is written once (forward) or
+// read once (backward: d_out) -- the only HBM traffic left.
+//
+//   forward : out[n,c,t] = gelu(gamma_c * (y - mean_nc) * rstd_nc + beta_c),  y[n,c,t] = b_c + sum_k w[c,k] a[n, t*stride+k]
+//   backward: d_w[c,k], d_b[c], d_gamma[c], d_beta[c]  (+=; the waveform needs no gradient)
+#include "common.cuh"
+#include <cuda_bf16.h>
+
+namespace b2d {
+
+constexpr int W2V_K = 10;     // kernel width of layer 0 (Wav2Vec2Config.conv_kernel[0])
+constexpr int W2V_TPL = 25;   // time steps per lane: T <= 800 (4000-sample windows give 799)
+constexpr float RSQRT2 = 0.70710678118654752f;
+constexpr float RSQRT2PI = 0.39894228040143268f;
+
+struct W2vParams {
+  const float* audio; long long ld_audio;
+  const float* w; const float* bias; const float* gamma; const float* beta;
+  int N, S, C, T, stride;
+  float eps;
+};
+
+template <typename T> __device__ __forceinline__ float w2v_ld(const T* p) { return (float)*p; }
+template <> __device__ __forceinline__ float w2v_ld<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+template <> __device__ __forceinline__ float w2v_ld<__half>(const __half* p) { return __half2float(*p); }
+template <typename T> __device__ __forceinline__ void w2v_st(T* p, float v) { *p = v; }
+template <> __device__ __forceinline__ void w2v_st<__nv_bfloat16>(__nv_bfloat16* p, float v) { *p = __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ void w2v_st<__half>(__half* p, float v) { *p = __float2half_rn(v); }
+
+// Normal cdf / pdf at z without the data-dependent branch of erff() (whose two ranges diverge inside nearly every warp
+// for N(0,1)-like z): erf by Abramowitz & Stegun 7.1.26, |error| <= 1.5e-7, sharing exp(-z^2/2) with the pdf.
+// One MUFU.RCP + one MUFU.EX2 + 8 FMA-class instructions.
+__device__ __forceinline__ void normal_cdf_pdf(float z, float& cdf, float& pdf) {
+  const float u = fabsf(z) * RSQRT2;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, u, 1.0f)));
+  const float e = fast_exp2(-0.72134752044448170f * z * z);   // exp(-z^2 / 2)
+  float q = fmaf(1.061405429f, t, -1.453152027f);
+  q = fmaf(q, t, 1.421413741f);
+  q = fmaf(q, t, -0.284496736f);
+  q = fmaf(q, t, 0.254829592f);
+  q = 0.5f * q * t * e;
+  cdf = z >= 0.f ? 1.0f - q : q;
+  pdf = e * RSQRT2PI;
+}
+
+__device__ __forceinline__ void load_window(float* sa, const W2vParams& p, int n) {
+  const float* a = p.audio + (long long)n * p.ld_audio;
+  for (int i = threadIdx.x; i < p.S; i += blockDim.x) sa[i] = __ldg(a + i);
+}
+
+// grid = (ceil(C / CPB), N), 256 threads; a warp owns channels warp, warp + 8, ... of the block's CPB channels.
+constexpr int W2V_FWD_CPB = 32;
+
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+w2v_layer0_fwd_kernel(W2vParams p, OutT* __restrict__ out, float* __restrict__ mean, float* __restrict__ rstd) {
+  extern __shared__ float sa[];
+  const int n = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  load_window(sa, p, n);
+  __syncthreads();
+  const float inv_T = 1.0f / (float)p.T;
+  for (int cc = warp; cc < W2V_FWD_CPB; cc += 8) {
+    const int c = blockIdx.x * W2V_FWD_CPB + cc;
+    if (c >= p.C) break;
+    float w[W2V_K];
+#pragma unroll
+    for (int k = 0; k < W2V_K; ++k) w[k] = __ldg(p.w + c * W2V_K + k);
+    const float b = p.bias ? __ldg(p.bias + c) : 0.f;
+    float y[W2V_TPL];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < W2V_TPL; ++i) {
+      const int t = lane + 32 * i;
+      float acc = 0.f;
+      if (t < p.T) {
+        acc = b;
+        const float* a = sa + t * p.stride;
+#pragma unroll
+        for (int k = 0; k < W2V_K; ++k) acc = fmaf(w[k], a[k], acc);
+        s += acc;
+      }
+      y[i] = acc;
+    }
+    const float mu = warp_sum(s) * inv_T;
+    float v = 0.f;
+#pragma unroll
+    for (int i = 0; i < W2V_TPL; ++i) {
+      const float d = y[i] - mu;
+      if (lane + 32 * i < p.T) v = fmaf(d, d, v);
+    }
+    const float rs = rsqrtf(warp_sum(v) * inv_T + p.eps);
+    const float g = __ldg(p.gamma + c) * rs;
+    const float bb = __ldg(p.beta + c);
+    OutT* o = out + ((long long)n * p.C + c) * p.T;
+#pragma unroll
+    for (int i = 0; i < W2V_TPL; ++i) {
+      const int t = lane + 32 * i;
+      const float z = fmaf(y[i] - mu, g, bb);   // centred first: well conditioned even for a constant row
+      float cdf, pdf;
+      normal_cdf_pdf(z, cdf, pdf);
+      if (t < p.T) w2v_st(o + t, z * cdf);
+    }
+    if (lane == 0) {
+      mean[(long long)n * p.C + c] = mu;
+      rstd[(long long)n * p.C + c] = rs;
+    }
+  }
+}
+
+// grid = (ceil(C / 8), ceil(N / n_chunk)), 256 threads; a warp owns one channel and walks the windows of its chunk,
+// keeping the parameter-gradient partial sums in registers; one set of atomics per (channel, chunk).
+template <typename GT>
+__global__ void __launch_bounds__(256, 2)
+w2v_layer0_bwd_kernel(W2vParams p, const GT* __restrict__ dout, const float* __restrict__ mean,
+                      const float* __restrict__ rstd, float* __restrict__ dw, float* __restrict__ dbias,
+                      float* __restrict__ dgamma, float* __restrict__ dbeta, int n_chunk) {
+  extern __shared__ float sa[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int c = blockIdx.x * 8 + warp;
+  const bool active = c < p.C;
+  const int n0 = blockIdx.y * n_chunk;
+  const int n1 = min(p.N, n0 + n_chunk);
+  float w[W2V_K], aw[W2V_K];
+#pragma unroll
+  for (int k = 0; k < W2V_K; ++k) { w[k] = active ? __ldg(p.w + c * W2V_K + k) : 0.f; aw[k] = 0.f; }
+  const float b = (active && p.bias) ? __ldg(p.bias + c) : 0.f;
+  const float gam = active ? __ldg(p.gamma + c) : 0.f, bet = active ? __ldg(p.beta + c) : 0.f;
+  const float inv_T = 1.0f / (float)p.T;
+  float a_gamma = 0.f, a_beta = 0.f, a_bias = 0.f;
+  for (int n = n0; n < n1; ++n) {
+    __syncthreads();
+    load_window(sa, p, n);
+    __syncthreads();
+    if (!active) continue;
+    const float mu = __ldg(mean + (long long)n * p.C + c), rs = __ldg(rstd + (long long)n * p.C + c);
+    const GT* g_in = dout + ((long long)n * p.C + c) * p.T;
+    float gz[W2V_TPL];   // d_out * gelu'(z); x_hat is recomputed in the second pass from the taps it loads anyway
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < W2V_TPL; ++i)      // all of the row's d_out loads in flight before the first use
+      gz[i] = (lane + 32 * i < p.T) ? w2v_ld(g_in + lane + 32 * i) : 0.f;
+#pragma unroll
+    for (int i = 0; i < W2V_TPL; ++i) {
+      const int t = lane + 32 * i;
+      float dz = 0.f;
+      if (t < p.T) {
+        float acc = b;
+        const float* a = sa + t * p.stride;
+#pragma unroll
+        for (int k = 0; k < W2V_K; ++k) acc = fmaf(w[k], a[k], acc);
+        const float x = (acc - mu) * rs;
+        const float z = fmaf(x, gam, bet);
+        float cdf, pdf;
+        normal_cdf_pdf(z, cdf, pdf);
+        dz = gz[i] * fmaf(z, pdf, cdf);
+        s1 += dz;
+        s2 = fmaf(dz, x, s2);
+      }
+      gz[i] = dz;
+    }
+    s1 = warp_sum(s1);
+    s2 = warp_sum(s2);
+    a_beta += s1;
+    a_gamma += s2;
+    const float m1 = gam * s1 * inv_T, m2 = gam * s2 * inv_T;
+#pragma unroll
+    for (int i = 0; i < W2V_TPL; ++i) {
+      const int t = lane + 32 * i;
+      if (t < p.T) {
+        const float* a = sa + t * p.stride;
+        float av[W2V_K];
+        float acc = b;
+#pragma unroll
+        for (int k = 0; k < W2V_K; ++k) { av[k] = a[k]; acc = fmaf(w[k], av[k], acc); }
+        const float x = (acc - mu) * rs;
+        const float dy = rs * (fmaf(gam, gz[i], -m1) - x * m2);
+        a_bias += dy;
+#pragma unroll
+        for (int k = 0; k < W2V_K; ++k) aw[k] = fmaf(dy, av[k], aw[k]);
+      }
+    }
+  }
+  if (!active) return;
+#pragma unroll
+  for (int k = 0; k < W2V_K; ++k) aw[k] = warp_sum(aw[k]);
+  a_bias = warp_sum(a_bias);
+  if (lane == 0) {
+#pragma unroll
+    for (int k = 0; k < W2V_K; ++k) atomicAdd(dw + c * W2V_K + k, aw[k]);
+    atomicAdd(dgamma + c, a_gamma);   // a_gamma / a_beta are already warp-uniform totals
+    atomicAdd(dbeta + c, a_beta);
+    if (dbias) atomicAdd(dbias + c, a_bias);
+  }
+}
+
+static int w2v_check(const W2vParams& p, int K) {
+  B2D_REQUIRE(p.audio && p.w && p.gamma && p.beta && p.N > 0 && p.C > 0 && p.S > 0, B2D_ERR_SHAPE,
+              "w2v_layer0: bad arguments");
+  B2D_REQUIRE(K == W2V_K && p.stride > 0 && p.S >= K, B2D_ERR_SHAPE,
+              "w2v_layer0: kernel width %d / stride %d / %d samples unsupported (built for width %d)", K, p.stride, p.S,
+              W2V_K);
+  B2D_REQUIRE(p.T <= 32 * W2V_TPL, B2D_ERR_SHAPE, "w2v_layer0: %d output steps exceed the %d a warp keeps in registers",
+              p.T, 32 * W2V_TPL);
+  B2D_REQUIRE((size_t)p.S * sizeof(float) <= 200 * 1024, B2D_ERR_SHAPE, "w2v_layer0: window of %d samples exceeds shared memory", p.S);
+  return B2D_OK;
+}
+
+template <typename Kern> static int w2v_smem(Kern k, size_t bytes) {
+  if (bytes > 48 * 1024) B2D_CHECK_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return B2D_OK;
+}
+
+}  // namespace b2d
+
+using namespace b2d;
+
+extern "C" int b2d_w2v_layer0_fwd(const float* audio, int64_t ld_audio, const float* w, const float* bias,
+                                  const float* gamma, const float* beta, int N, int S, int C, int K, int stride,
+                                  float eps, void* out, int out_dtype, float* mean, float* rstd, void* stream) {
+  W2vParams p{audio, ld_audio, w, bias, gamma, beta, N, S, C, S >= K && stride > 0 ? (S - K) / stride + 1 : 0, stride, eps};
+  if (int e = w2v_check(p, K)) return e;
+  B2D_REQUIRE(out && mean && rstd && out_dtype >= 0 && out_dtype <= 2, B2D_ERR_SHAPE, "w2v_layer0_fwd: bad outputs");
+  const dim3 grid((C + W2V_FWD_CPB - 1) / W2V_FWD_CPB, N);
+  const size_t smem = (size_t)S * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (out_dtype == 0) {
+    if (int e = w2v_smem(w2v_layer0_fwd_kernel<float>, smem)) return e;
+    w2v_layer0_fwd_kernel<float><<<grid, 256, smem, st>>>(p, (float*)out, mean, rstd);
+  } else if (out_dtype == 1) {
+    if (int e = w2v_smem(w2v_layer0_fwd_kernel<__nv_bfloat16>, smem)) return e;
+    w2v_layer0_fwd_kernel<__nv_bfloat16><<<grid, 256, smem, st>>>(p, (__nv_bfloat16*)out, mean, rstd);
+  } else {
+    if (int e = w2v_smem(w2v_layer0_fwd_kernel<__half>, smem)) return e;
+    w2v_layer0_fwd_kernel<__half><<<grid, 256, smem, st>>>(p, (__half*)out, mean, rstd);
+  }
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_w2v_layer0_bwd(const float* audio, int64_t ld_audio, const float* w, const float* bias,
+                                  const float* gamma, const float* beta, int N, int S, int C, int K, int stride,
+                                  float eps, const void* dout, int dout_dtype, const float* mean, const float* rstd,
+                                  float* dw, float* dbias, float* dgamma, float* dbeta, void* stream) {
+  W2vParams p{audio, ld_audio, w, bias, gamma, beta, N, S, C, S >= K && stride > 0 ? (S - K) / stride + 1 : 0, stride, eps};
+  if (int e = w2v_check(p, K)) return e;
+  B2D_REQUIRE(dout && mean && rstd && dw && dgamma && dbeta && dout_dtype >= 0 && dout_dtype <= 2, B2D_ERR_SHAPE,
+              "w2v_layer0_bwd: bad arguments");
+  const int n_chunk = N >= 64 ? 8 : 1;
+  const dim3 grid((C + 7) / 8, (N + n_chunk - 1) / n_chunk);
+  const size_t smem = (size_t)S * sizeof(float);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (dout_dtype == 0) {
+    if (int e = w2v_smem(w2v_layer0_bwd_kernel<float>, smem)) return e;
+    w2v_layer0_bwd_kernel<float><<<grid, 256, smem, st>>>(p, (const float*)dout, mean, rstd, dw, dbias, dgamma, dbeta, n_chunk);
+  } else if (dout_dtype == 1) {
+    if (int e = w2v_smem(w2v_layer0_bwd_kernel<__nv_bfloat16>, smem)) return e;
+    w2v_layer0_bwd_kernel<__nv_bfloat16><<<grid, 256, smem, st>>>(p, (const __nv_bfloat16*)dout, mean, rstd, dw, dbias, dgamma, dbeta, n_chunk);
+  } else {
+    if (int e = w2v_smem(w2v_layer0_bwd_kernel<__half>, smem)) return e;
+    w2v_layer0_bwd_kernel<__half><<<grid, 256, smem, st>>>(p, (const __half*)dout, mean, rstd, dw, dbias, dgamma, dbeta, n_chunk);
+  }
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}

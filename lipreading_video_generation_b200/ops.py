@@ -333,6 +333,40 @@ def colsum(x, out, c_off=0, C_=None):
     return out
 
 
+_W2V_DT = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
+
+
+def w2v_layer0_fwd(audio, w, bias, gamma, beta, stride, eps, out_dtype):
+    """Fused first feature-extractor layer of wav2vec2 (conv k=10 -> per-channel GroupNorm -> erf GELU).
+    audio (N,S) fp32, w (C,1,K) fp32 -> out (N,C,T) in out_dtype, mean (N,C), rstd (N,C)."""
+    N, S = audio.shape
+    Cc, _, K = w.shape
+    T = (S - K) // stride + 1
+    out = torch.empty(N, Cc, T, device=audio.device, dtype=out_dtype)
+    mean = torch.empty(N, Cc, device=audio.device, dtype=torch.float32)
+    rstd = torch.empty_like(mean)
+    L.check(L.lib().b2d_w2v_layer0_fwd(audio.data_ptr(), audio.stride(0), w.data_ptr(),
+                                       None if bias is None else bias.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                       N, S, Cc, K, stride, float(eps), out.data_ptr(), _W2V_DT[out_dtype],
+                                       mean.data_ptr(), rstd.data_ptr(), _s()), "b2d_w2v_layer0_fwd")
+    return out, mean, rstd
+
+
+def w2v_layer0_bwd(audio, w, bias, gamma, beta, stride, eps, dout, mean, rstd):
+    """Parameter gradients of the fused layer: (dw (C,1,K), dbias (C) or None, dgamma (C), dbeta (C)), fp32."""
+    N, S = audio.shape
+    Cc, _, K = w.shape
+    flat = torch.zeros(Cc * (K + 3), device=audio.device, dtype=torch.float32)
+    dw, dbias, dgamma, dbeta = flat[:Cc * K], flat[Cc * K:Cc * (K + 1)], flat[Cc * (K + 1):Cc * (K + 2)], flat[Cc * (K + 2):]
+    L.check(L.lib().b2d_w2v_layer0_bwd(audio.data_ptr(), audio.stride(0), w.data_ptr(),
+                                       None if bias is None else bias.data_ptr(), gamma.data_ptr(), beta.data_ptr(),
+                                       N, S, Cc, K, stride, float(eps), dout.data_ptr(), _W2V_DT[dout.dtype],
+                                       mean.data_ptr(), rstd.data_ptr(), dw.data_ptr(),
+                                       None if bias is None else dbias.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(),
+                                       _s()), "b2d_w2v_layer0_bwd")
+    return dw.view(Cc, 1, K), (None if bias is None else dbias), dgamma, dbeta
+
+
 def reduce_rows(inp, out):
     R, Cc = inp.shape
     L.check(L.lib().b2d_reduce_rows(inp.data_ptr(), R, Cc, inp.stride(0), out.data_ptr(), _s()), "b2d_reduce_rows")

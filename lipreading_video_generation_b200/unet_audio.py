@@ -59,6 +59,62 @@ def _conv1d_single_channel(conv, x):
     return y.transpose(1, 2)
 
 
+W2V_LAYER0_MAX_STEPS = 800      # b2d_w2v_layer0_*: output steps one warp keeps in registers
+
+
+class _FeatureLayer0Fn(torch.autograd.Function):
+    """conv(1 -> C, k = 10) -> GroupNorm(C, C) -> erf GELU of HF's `Wav2Vec2GroupNormConvLayer` as one kernel each way
+    (csrc/wav2vec2_frontend.cu).  fp32 arithmetic from the fp32 waveform; output in the autocast dtype."""
+
+    @staticmethod
+    def forward(ctx, audio, w, bias, gamma, beta, stride, eps, out_dtype):
+        from . import ops
+        out, mean, rstd = ops.w2v_layer0_fwd(audio, w, bias, gamma, beta, stride, eps, out_dtype)
+        ctx.save_for_backward(audio, w, bias, gamma, beta, mean, rstd)
+        ctx.stride, ctx.eps = stride, eps
+        return out
+
+    @staticmethod
+    def backward(ctx, dout):
+        from . import ops
+        audio, w, bias, gamma, beta, mean, rstd = ctx.saved_tensors
+        dw, dbias, dgamma, dbeta = ops.w2v_layer0_bwd(audio, w, bias, gamma, beta, ctx.stride, ctx.eps,
+                                                      dout.contiguous(), mean, rstd)
+        return None, dw, dbias, dgamma, dbeta, None, None, None
+
+
+def _feature_layer0_fused(self, hidden_states):
+    """Drop-in for `Wav2Vec2GroupNormConvLayer.forward` on CUDA tensors; anything the kernel is not built for
+    (other kernel width, longer windows, CPU tensors) takes the stock HF path."""
+    conv, gn = self.conv, self.layer_norm
+    S = hidden_states.shape[-1]
+    ok = (hidden_states.is_cuda and hidden_states.dim() == 3 and hidden_states.shape[1] == 1
+          and conv.kernel_size[0] == 10 and conv.padding[0] == 0 and conv.dilation[0] == 1
+          and S >= 10 and 2 <= (S - 10) // conv.stride[0] + 1 <= W2V_LAYER0_MAX_STEPS and S * 4 <= 200 * 1024
+          and conv.weight.dtype == torch.float32)
+    if not ok:
+        return self._b2d_stock_forward(hidden_states)
+    out_dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else torch.float32
+    audio = hidden_states[:, 0].float().contiguous()
+    return _FeatureLayer0Fn.apply(audio, conv.weight, conv.bias, gn.weight, gn.bias, conv.stride[0], gn.eps, out_dtype)
+
+
+def patch_feature_layer0(wav2vec2):
+    """Route the first feature-extractor layer through the fused kernels when it is the group-norm variant with an
+    exact (erf) GELU -- wav2vec2-base's configuration."""
+    import types
+    layer0 = wav2vec2.feature_extractor.conv_layers[0]
+    gn = getattr(layer0, "layer_norm", None)
+    conv = getattr(layer0, "conv", None)
+    if (isinstance(gn, nn.GroupNorm) and isinstance(conv, nn.Conv1d) and conv.in_channels == 1
+            and gn.num_groups == gn.num_channels == conv.out_channels and gn.affine
+            and getattr(wav2vec2.config, "feat_extract_activation", None) == "gelu"
+            and not hasattr(layer0, "_b2d_stock_forward")):
+        layer0._b2d_stock_forward = layer0.forward
+        layer0.forward = types.MethodType(_feature_layer0_fused, layer0)
+    return wav2vec2
+
+
 def patch_pos_conv(wav2vec2):
     """Route the positional conv embedding of a HF Wav2Vec2Model through _pos_conv_short_sequence and the
     single-channel waveform conv through _conv1d_single_channel (same arithmetic, library GEMMs)."""
@@ -91,6 +147,7 @@ class Wav2Vec2Encoder(nn.Module):
             self.wav2vec2 = Wav2Vec2Model(Wav2Vec2Config())
         if os.environ.get("B2D_WAV2VEC2_STOCK", "0") != "1":     # A/B switch: leave the HF module untouched
             patch_pos_conv(self.wav2vec2)
+            patch_feature_layer0(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

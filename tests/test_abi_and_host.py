@@ -243,3 +243,20 @@ def test_dims3_module_tree_has_the_reference_keys_and_conv3d_shapes():
         r = ref.unet.UNetModel(dims=3, **kw)
         assert {k: tuple(v.shape) for k, v in r.state_dict().items()} == \
                {k: tuple(v.shape) for k, v in m3.state_dict().items()}
+
+
+def test_feature_layer0_patch_is_installed_and_cpu_tensors_take_the_stock_path():
+    """patch_feature_layer0 only reroutes CUDA tensors (the kernel is the product path there); on CPU tensors the
+    third-party layer runs untouched, so the patched module equals the stock one bit for bit."""
+    import copy
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(0)
+    m = Wav2Vec2Model(Wav2Vec2Config(num_hidden_layers=1))
+    p = UA.patch_feature_layer0(copy.deepcopy(m))
+    l0 = p.feature_extractor.conv_layers[0]
+    assert hasattr(l0, "_b2d_stock_forward")
+    a = torch.randn(2, 1, 4000)
+    assert torch.equal(l0(a), m.feature_extractor.conv_layers[0](a))
+    UA.patch_feature_layer0(p)                                   # idempotent
+    assert l0._b2d_stock_forward.__func__ is type(l0).forward

@@ -333,3 +333,63 @@ def test_device_weight_packing_equals_host_chain_bit_exactly():
         assert torch.equal(ops.pack_conv_weight(wt.cuda(), **kw).cpu(), ops.pack_conv_weight(wt, **kw))
     for wt, kw in [(w, dict(cin_pad=64, cout_pad=64)), (w, dict()), (w5[:, :, 2], dict())]:
         assert torch.equal(ops.pack_dgrad_weight(wt.cuda(), **kw).cpu(), ops.pack_dgrad_weight(wt, **kw))
+
+
+# ----------------------------------------------------------------------------- wav2vec2 front end (fused layer 0)
+def _w2v_layer0_pair(seed=0):
+    """(stock, fused) copies of HF's first feature-extractor layer with non-trivial GroupNorm affine parameters."""
+    import copy
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(seed)
+    m = Wav2Vec2Model(Wav2Vec2Config())
+    with torch.no_grad():
+        gn = m.feature_extractor.conv_layers[0].layer_norm
+        gn.weight.uniform_(0.5, 1.5)
+        gn.bias.uniform_(-0.5, 0.5)
+    stock = copy.deepcopy(m).cuda()
+    fused = UA.patch_feature_layer0(copy.deepcopy(m)).cuda()
+    assert hasattr(fused.feature_extractor.conv_layers[0], "_b2d_stock_forward")
+    return stock.feature_extractor.conv_layers[0], fused.feature_extractor.conv_layers[0]
+
+
+@pytest.mark.parametrize("N,S", [(3, 4000), (70, 4000), (2, 1234), (1, 15)])
+def test_w2v_layer0_fused_matches_stock_fp32(N, S):
+    """conv -> GroupNorm -> GELU of the third-party layer (unet_audio.py:10-18 instantiates it) against the stock
+    library ops run in float64 (fp32 cuDNN takes TF32 paths for the weight gradient): output and the three parameter
+    gradients within 1e-4 (north_star's fp32 bar; measured ~3e-7)."""
+    stock, fused = _w2v_layer0_pair()
+    stock = stock.double()
+    a = torch.randn(N, 1, S, generator=gen(1)).cuda()
+    r = torch.randn(N, 512, (S - 10) // 5 + 1, generator=gen(2)).cuda()
+    ys, yf = stock(a.double()), fused(a)
+    assert yf.dtype == torch.float32 and yf.shape == ys.shape
+    assert rel(yf, ys) <= 1e-4
+    (ys * r.double()).sum().backward()
+    (yf * r).sum().backward()
+    for name in ("conv.weight", "layer_norm.weight", "layer_norm.bias"):
+        gs, gf = stock.get_parameter(name).grad, fused.get_parameter(name).grad
+        assert rel(gf, gs) <= 1e-4, name
+
+
+def test_w2v_layer0_fused_autocast_output_dtype_and_bar():
+    """Under the bf16 autocast the encoder runs in, the fused layer writes bf16 and stays inside the 2e-2 bar of the
+    fp32 stock layer (it computes in fp32 from the fp32 waveform; the stock autocast path rounds the waveform)."""
+    stock, fused = _w2v_layer0_pair()
+    a = torch.randn(8, 1, 4000, generator=gen(3)).cuda()
+    r = torch.randn(8, 512, 799, generator=gen(4)).cuda()
+    ys = stock(a)
+    (ys * r).sum().backward()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        yf = fused(a)
+    assert yf.dtype == torch.bfloat16
+    (yf.float() * r).sum().backward()
+    assert rel(yf, ys) <= TOL16_KERNEL
+    for name in ("conv.weight", "layer_norm.weight", "layer_norm.bias"):
+        assert rel(fused.get_parameter(name).grad, stock.get_parameter(name).grad) <= TOL16_KERNEL, name
+
+
+def test_w2v_layer0_unsupported_shapes_take_the_stock_path():
+    stock, fused = _w2v_layer0_pair()
+    a = torch.randn(1, 1, 6000, generator=gen(5)).cuda()       # 1199 steps > 800
+    assert torch.equal(fused(a), stock(a))
