@@ -243,6 +243,17 @@ int b2d_w2v_layer0_bwd(const float* audio, int64_t ld_audio, const float* w, con
                        const float* beta, int N, int S, int C, int K, int stride, float eps, const void* dout,
                        int dout_dtype, const float* mean, const float* rstd, float* dw, float* dbias, float* dgamma,
                        float* dbeta, void* stream);
+/* Self-attention over very short sequences (L <= 16 tokens, head dim D = 64): the attention function behind HF
+ * transformers' `Wav2Vec2Attention` (the audio encoder of unet_audio.py:10-18 sees 12 frames per 4000-sample window).
+ * q / k / v: (B, H, L, D) views with element strides (sb, sh, sl, 1); out, dout, dq, dk, dv: contiguous (B, L, H, D);
+ * dtype 0 = fp32, 1 = bf16, 2 = fp16 for all tensors.  Dropout with probability drop_p acts on the probabilities
+ * (Philox keyed by `seed`; the backward must be given the forward's seed: it recomputes the mask). */
+int b2d_short_attention_fwd(const void* q, const void* k, const void* v, int64_t sb, int64_t sl, int64_t sh, int B,
+                            int H, int L, int D, int dtype, float scale, float drop_p, uint64_t seed, void* out,
+                            void* stream);
+int b2d_short_attention_bwd(const void* q, const void* k, const void* v, int64_t sb, int64_t sl, int64_t sh,
+                            const void* dout, int B, int H, int L, int D, int dtype, float scale, float drop_p,
+                            uint64_t seed, void* dq, void* dk, void* dv, void* stream);
 /* out[n*ldout + c] += sum_pix x[n,pix,c_off+c]  (x fp16 (N,HW,ld)): emb_out / bias / audio gradients. */
 int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */

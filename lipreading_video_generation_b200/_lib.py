@@ -99,6 +99,11 @@ SIGNATURES = {
     "b2d_w2v_layer0_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                    c_float, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                    c_void_p]),
+    "b2d_short_attention_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int,
+                                        c_int, c_float, c_float, C.c_uint64, c_void_p, c_void_p]),
+    "b2d_short_attention_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_int64, c_int64, c_void_p, c_int, c_int,
+                                        c_int, c_int, c_int, c_float, c_float, C.c_uint64, c_void_p, c_void_p, c_void_p,
+                                        c_void_p]),
     "b2d_colsum": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "b2d_reduce_rows": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
     "b2d_timestep_embedding": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),

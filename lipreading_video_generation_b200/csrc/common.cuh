@@ -145,4 +145,19 @@ __device__ __forceinline__ float fast_sigmoid(float z) {
 
 __device__ __forceinline__ float silu_f(float x) { return x * fast_sigmoid(x); }
 
+// Philox-4x32-10 keyed by (seed, element index / 4): dropout masks reproducible in the backward
+// (GroupNorm dropout, short-sequence attention dropout).
+__device__ __forceinline__ uint4 philox4(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1) {
+  uint32_t x0 = c0, x1 = c1, x2 = 0x243F6A88u, x3 = 0x85A308D3u;
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, x0), lo0 = 0xD2511F53u * x0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, x2), lo1 = 0xCD9E8D57u * x2;
+    const uint32_t y0 = hi1 ^ x1 ^ k0, y2 = hi0 ^ x3 ^ k1;
+    x0 = y0; x1 = lo1; x2 = y2; x3 = lo0;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  return make_uint4(x0, x1, x2, x3);
+}
+
 }  // namespace b2d

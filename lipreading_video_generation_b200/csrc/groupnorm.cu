@@ -34,19 +34,6 @@ __device__ __forceinline__ void store8(__half* p, const float* v) {
 // HBM-bound kernels below keep several independent 16-byte loads in flight per thread (UNROLL pixels per
 // iteration): with one load per thread the first version sustained ~2 TB/s (16 KB in flight per SM).
 
-// Philox-4x32-10 keyed by (seed, element index / 4): dropout mask reproducible in the backward.
-__device__ __forceinline__ uint4 philox4(uint32_t k0, uint32_t k1, uint32_t c0, uint32_t c1) {
-  uint32_t x0 = c0, x1 = c1, x2 = 0x243F6A88u, x3 = 0x85A308D3u;
-#pragma unroll
-  for (int r = 0; r < 10; ++r) {
-    const uint32_t hi0 = __umulhi(0xD2511F53u, x0), lo0 = 0xD2511F53u * x0;
-    const uint32_t hi1 = __umulhi(0xCD9E8D57u, x2), lo1 = 0xCD9E8D57u * x2;
-    const uint32_t y0 = hi1 ^ x1 ^ k0, y2 = hi0 ^ x3 ^ k1;
-    x0 = y0; x1 = lo1; x2 = y2; x3 = lo0;
-    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
-  }
-  return make_uint4(x0, x1, x2, x3);
-}
 // keep-mask for 8 consecutive elements starting at element index e (multiple of 8)
 __device__ __forceinline__ void dropout_keep8(unsigned long long seed, unsigned long long e, float p, bool* keep) {
   const unsigned long long blk = e >> 3;

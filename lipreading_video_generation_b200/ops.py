@@ -367,6 +367,34 @@ def w2v_layer0_bwd(audio, w, bias, gamma, beta, stride, eps, dout, mean, rstd):
     return dw.view(Cc, 1, K), (None if bias is None else dbias), dgamma, dbeta
 
 
+def _sa_strides(q, k, v):
+    B, H, Lq, D = q.shape
+    if not (q.shape == k.shape == v.shape and q.dtype == k.dtype == v.dtype and q.stride() == k.stride() == v.stride()
+            and q.stride(3) == 1):
+        raise ValueError("short_attention: q, k, v must share shape, dtype and strides with a unit head-dim stride")
+    return B, H, Lq, D, q.stride(0), q.stride(2), q.stride(1)
+
+
+def short_attention_fwd(q, k, v, scale, drop_p=0.0, seed=0):
+    """q, k, v (B, H, L, 64) strided views, L <= 16 -> out (B, L, H, 64) contiguous."""
+    B, H, Lq, D, sb, sl, sh = _sa_strides(q, k, v)
+    out = torch.empty(B, Lq, H, D, device=q.device, dtype=q.dtype)
+    L.check(L.lib().b2d_short_attention_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), sb, sl, sh, B, H, Lq, D,
+                                            _W2V_DT[q.dtype], float(scale), float(drop_p), int(seed), out.data_ptr(), _s()),
+            "b2d_short_attention_fwd")
+    return out
+
+
+def short_attention_bwd(q, k, v, dout, scale, drop_p=0.0, seed=0):
+    """Gradients (dq, dk, dv), each (B, L, H, 64) contiguous; dout (B, L, H, 64) contiguous."""
+    B, H, Lq, D, sb, sl, sh = _sa_strides(q, k, v)
+    g = torch.empty(3, B, Lq, H, D, device=q.device, dtype=q.dtype)
+    L.check(L.lib().b2d_short_attention_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), sb, sl, sh, dout.data_ptr(), B, H, Lq,
+                                            D, _W2V_DT[q.dtype], float(scale), float(drop_p), int(seed), g[0].data_ptr(),
+                                            g[1].data_ptr(), g[2].data_ptr(), _s()), "b2d_short_attention_bwd")
+    return g[0], g[1], g[2]
+
+
 def reduce_rows(inp, out):
     R, Cc = inp.shape
     L.check(L.lib().b2d_reduce_rows(inp.data_ptr(), R, Cc, inp.stride(0), out.data_ptr(), _s()), "b2d_reduce_rows")

@@ -28,13 +28,14 @@ def _pos_conv_short_sequence(mod, hidden_states):
     B, T, C = hidden_states.shape
     K, pad, G = conv.kernel_size[0], conv.padding[0], conv.groups
     if (T > POS_CONV_TOEPLITZ_MAX_T or conv.stride[0] != 1 or conv.dilation[0] != 1 or K % 2 != 0 or pad != K // 2
-            or T - 1 > pad or conv.padding_mode != "zeros"):
+            or T - 1 > pad or pad + T > K or conv.padding_mode != "zeros"):
         return mod._b2d_stock_forward(hidden_states)
     cg = C // G
     w = conv.weight                                                   # (C, C/G, K), weight-norm evaluated here
-    tt = torch.arange(T, device=w.device)
-    idx = tt[:, None] - tt[None, :] + pad                             # [t', t] -> tap, always inside [0, K)
-    m = w[:, :, idx]                                                  # (C, cg, T', T)
+    # m[c, i, t', t] = w[c, i, t' - t + pad]: windows of the tap axis (w.unfold: U[.., j, s] = w[.., j + s]) taken at
+    # j = pad - t, s = t'.  (An index gather w[:, :, idx] builds the same tensor, but its backward is an
+    # index_put with accumulation: 0.7 ms per step against ~30 us for unfold's.)
+    m = w.unfold(-1, T, 1)[:, :, pad - T + 1:pad + 1].flip(2).transpose(2, 3)          # (C, cg, T', T)
     m = m.view(G, cg, cg, T, T).permute(0, 2, 3, 1, 4).reshape(G, cg * T, cg * T)      # [g][(ci, t')][(co, t)]
     x = hidden_states.reshape(B, T, G, cg).permute(2, 0, 3, 1).reshape(G, B, cg * T)   # [g][b][(ci, t')]
     y = torch.bmm(x, m.to(x.dtype) if not torch.is_autocast_enabled() else m)          # (G, B, (co, t))
@@ -115,6 +116,58 @@ def patch_feature_layer0(wav2vec2):
     return wav2vec2
 
 
+SHORT_ATTENTION_MAX_TOKENS = 16      # b2d_short_attention_*: one warp per (window, head)
+SHORT_ATTENTION_NAME = "b2d_short"
+_short_attention_calls = [0]
+
+
+class _ShortAttentionFn(torch.autograd.Function):
+    """softmax(scale q k^T) -> dropout -> @ v for L <= 16, head dim 64 (csrc/short_attention.cu)."""
+
+    @staticmethod
+    def forward(ctx, q, k, v, scale, drop_p, seed):
+        from . import ops
+        ctx.save_for_backward(q, k, v)
+        ctx.cfg = (scale, drop_p, seed)
+        return ops.short_attention_fwd(q, k, v, scale, drop_p, seed)
+
+    @staticmethod
+    def backward(ctx, dout):
+        from . import ops
+        q, k, v = ctx.saved_tensors
+        scale, drop_p, seed = ctx.cfg
+        dq, dk, dv = ops.short_attention_bwd(q, k, v, dout.contiguous(), scale, drop_p, seed)
+        return dq.transpose(1, 2), dk.transpose(1, 2), dv.transpose(1, 2), None, None, None
+
+
+def _short_attention_interface(module, query, key, value, attention_mask, dropout=0.0, scaling=None, **kwargs):
+    """HF attention-interface function (same contract as transformers' `sdpa_attention_forward`): returns
+    ((B, L, H, D) output, None).  Shapes the kernel is not built for go to the library SDPA path."""
+    B, H, Lq, D = query.shape
+    ok = (query.is_cuda and attention_mask is None and D == 64 and Lq <= SHORT_ATTENTION_MAX_TOKENS
+          and key.shape == query.shape and value.shape == query.shape and not kwargs.get("output_attentions")
+          and query.dtype == key.dtype == value.dtype and query.dtype in (torch.float32, torch.bfloat16, torch.float16)
+          and query.stride() == key.stride() == value.stride() and query.stride(3) == 1)
+    if not ok:
+        from transformers.modeling_utils import ALL_ATTENTION_FUNCTIONS
+        return ALL_ATTENTION_FUNCTIONS["sdpa"](module, query, key, value, attention_mask, dropout=dropout,
+                                               scaling=scaling, **kwargs)
+    scale = float(scaling) if scaling is not None else D ** -0.5
+    _short_attention_calls[0] += 1
+    seed = (torch.initial_seed() * 0x9E3779B97F4A7C15 + _short_attention_calls[0]) & 0x7FFFFFFFFFFFFFFF
+    return _ShortAttentionFn.apply(query, key, value, scale, float(dropout), seed), None
+
+
+def patch_short_attention(wav2vec2):
+    """Select the short-sequence attention kernel for every encoder layer through transformers' attention-interface
+    registry (the public hook for custom attention functions)."""
+    from transformers import AttentionInterface
+    AttentionInterface.register(SHORT_ATTENTION_NAME, _short_attention_interface)
+    if wav2vec2.config._attn_implementation in ("sdpa", "eager"):
+        wav2vec2.config._attn_implementation = SHORT_ATTENTION_NAME
+    return wav2vec2
+
+
 def patch_pos_conv(wav2vec2):
     """Route the positional conv embedding of a HF Wav2Vec2Model through _pos_conv_short_sequence and the
     single-channel waveform conv through _conv1d_single_channel (same arithmetic, library GEMMs)."""
@@ -148,6 +201,7 @@ class Wav2Vec2Encoder(nn.Module):
         if os.environ.get("B2D_WAV2VEC2_STOCK", "0") != "1":     # A/B switch: leave the HF module untouched
             patch_pos_conv(self.wav2vec2)
             patch_feature_layer0(self.wav2vec2)
+            patch_short_attention(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

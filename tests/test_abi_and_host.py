@@ -260,3 +260,21 @@ def test_feature_layer0_patch_is_installed_and_cpu_tensors_take_the_stock_path()
     assert torch.equal(l0(a), m.feature_extractor.conv_layers[0](a))
     UA.patch_feature_layer0(p)                                   # idempotent
     assert l0._b2d_stock_forward.__func__ is type(l0).forward
+
+
+def test_short_attention_interface_falls_back_to_library_sdpa_on_cpu_tensors():
+    """patch_short_attention registers the kernel through transformers' attention-interface registry; CPU tensors
+    (and any shape the kernel is not built for) are served by the library SDPA function, so the patched encoder
+    equals the stock one on CPU."""
+    import copy
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(0)
+    stock = Wav2Vec2Model(Wav2Vec2Config(num_hidden_layers=2)).eval()
+    fast = UA.patch_short_attention(copy.deepcopy(stock))
+    assert fast.config._attn_implementation == UA.SHORT_ATTENTION_NAME
+    a = torch.randn(2, 4000)
+    n0 = UA._short_attention_calls[0]
+    with torch.no_grad():
+        assert torch.equal(fast(input_values=a).last_hidden_state, stock(input_values=a).last_hidden_state)
+    assert UA._short_attention_calls[0] == n0

@@ -393,3 +393,92 @@ def test_w2v_layer0_unsupported_shapes_take_the_stock_path():
     stock, fused = _w2v_layer0_pair()
     a = torch.randn(1, 1, 6000, generator=gen(5)).cuda()       # 1199 steps > 800
     assert torch.equal(fused(a), stock(a))
+
+
+# ----------------------------------------------------------------------------- short-sequence attention (wav2vec2 encoder)
+def _sa_inputs(B, H, L, dtype, seed=0):
+    """q, k, v as HF's Wav2Vec2Attention builds them: (B, L, H*64) Linear outputs viewed (B, H, L, 64)."""
+    g = gen(seed)
+    mk = lambda: torch.randn(B, L, H * 64, generator=g).cuda().to(dtype).requires_grad_(True)  # noqa: E731
+    flat = [mk(), mk(), mk()]
+    return flat, [t.view(B, L, H, 64).transpose(1, 2) for t in flat]
+
+
+def _sa_eager(q, k, v, scale, keep=None, p=0.0):
+    """fp32 statement of eager_attention_forward (HF transformers), optional fixed keep-mask (B, H, L, L)."""
+    w = torch.softmax(torch.matmul(q.float(), k.float().transpose(2, 3)) * scale, dim=-1)
+    if keep is not None:
+        w = w * keep / (1.0 - p)
+    return torch.matmul(w, v.float()).transpose(1, 2).contiguous()
+
+
+@pytest.mark.parametrize("B,H,L", [(3, 12, 12), (2, 5, 16), (7, 1, 1), (1, 3, 5)])
+@pytest.mark.parametrize("dtype,tol", [(torch.float32, 1e-5), (torch.bfloat16, TOL16_KERNEL)])
+def test_short_attention_matches_eager_math(B, H, L, dtype, tol):
+    import lipreading_video_generation_b200.unet_audio as UA
+    flat, (q, k, v) = _sa_inputs(B, H, L, dtype)
+    out = UA._ShortAttentionFn.apply(q, k, v, 0.125, 0.0, 0)
+    assert out.shape == (B, L, H, 64) and out.dtype == dtype
+    r = torch.randn(B, L, H, 64, generator=gen(9)).cuda()
+    (out.float() * r).sum().backward()
+    got = [t.grad.clone() for t in flat]
+    ref_flat, (q2, k2, v2) = _sa_inputs(B, H, L, dtype)
+    ref = _sa_eager(q2, k2, v2, 0.125)
+    (ref * r).sum().backward()
+    assert rel(out, ref) <= tol
+    for g_, t in zip(got, ref_flat):
+        assert rel(g_, t.grad) <= (tol if dtype == torch.float32 else TOL16), "q/k/v gradient"
+
+
+def test_short_attention_dropout_mask_rate_and_consistent_backward():
+    """Dropout acts on the probabilities with the kernel's own Philox stream (no library mask to match bit for bit):
+    recover the mask with one-hot value rows, check its rate and that forward and backward used the same mask."""
+    import lipreading_video_generation_b200.unet_audio as UA
+    B, H, L, p, seed = 64, 12, 12, 0.1, 1234
+    flat, (q, k, v) = _sa_inputs(B, H, L, torch.float32, seed=3)
+    eye = torch.zeros(B, L, H, 64, device="cuda")
+    eye[..., :L] = torch.eye(L, device="cuda")[:, None, :]
+    eye = eye.view(B, L, H * 64).view(B, L, H, 64).transpose(1, 2)            # same strides as q / k
+    pd = UA._ShortAttentionFn.apply(q, k, eye, 0.125, p, seed)[..., :L].permute(0, 2, 1, 3)      # (B, H, L, L) dropped P
+    keep = (pd != 0).float()
+    rate = keep.mean().item()
+    assert abs(rate - (1 - p)) < 4 * math.sqrt(p * (1 - p) / keep.numel()) + 1e-3, rate
+    assert not torch.equal(keep[0], keep[1])                       # different (window, head) pairs draw different masks
+    out = UA._ShortAttentionFn.apply(q, k, v, 0.125, p, seed)
+    r = torch.randn(B, L, H, 64, generator=gen(5)).cuda()
+    (out * r).sum().backward()
+    got = [t.grad.clone() for t in flat]
+    ref_flat, (q2, k2, v2) = _sa_inputs(B, H, L, torch.float32, seed=3)
+    ref = _sa_eager(q2, k2, v2, 0.125, keep, p)
+    (ref * r).sum().backward()
+    assert rel(out, ref) <= 1e-5
+    for g_, t in zip(got, ref_flat):
+        assert rel(g_, t.grad) <= 1e-5
+    other = UA._ShortAttentionFn.apply(q, k, eye, 0.125, p, seed + 1)[..., :L].permute(0, 2, 1, 3)
+    assert not torch.equal(other != 0, pd != 0)                    # a new seed draws a new mask
+
+
+def test_wav2vec2_with_short_attention_matches_stock_encoder():
+    """Whole HF encoder, eval mode (no dropout / layerdrop), fp32: attention interface + fused layer 0 + positional
+    conv restatement against the untouched module, 1e-4."""
+    import copy
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(0)
+    stock = Wav2Vec2Model(Wav2Vec2Config(num_hidden_layers=3)).cuda().eval()
+    fast = copy.deepcopy(stock)
+    UA.patch_pos_conv(fast)
+    UA.patch_feature_layer0(fast)
+    UA.patch_short_attention(fast)
+    assert fast.config._attn_implementation == UA.SHORT_ATTENTION_NAME and stock.config._attn_implementation == "sdpa"
+    a = torch.randn(4, 4000, generator=gen(6)).cuda()
+    n0 = UA._short_attention_calls[0]
+    old = torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = False      # stock convs default to TF32
+    try:
+        with torch.no_grad():
+            ys, yf = stock(input_values=a).last_hidden_state, fast(input_values=a).last_hidden_state
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+    assert UA._short_attention_calls[0] == n0 + 3
+    assert rel(yf, ys) <= 1e-4
