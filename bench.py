@@ -140,7 +140,10 @@ class TrainStep:
         self.P, self.model, self.device, self.world = P, model, device, world
         self.sched = P.LinearNoiseScheduler(1000, 0.00085, 0.012)
         self.crit = P.MSELoss()
-        self.opt = torch.optim.Adam(model.parameters(), lr=1e-2, fused=True)          # train.py:102
+        if os.environ.get("B2D_TORCH_ADAM") == "1":          # A/B runs only
+            self.opt = torch.optim.Adam(model.parameters(), lr=1e-2, fused=True)
+        else:
+            self.opt = P.Adam(model.parameters(), lr=1e-2)                            # train.py:102, one launch
         self.reducer = GradientAllReducer(model) if world > 1 else None
         model.train()
 
@@ -289,7 +292,7 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
             if (".out_layers.3." in name) or (".proj_out." in name) or name.startswith("out.2."):
                 p.copy_(torch.randn(p.shape, generator=g) * 0.02)
     model = model.to(device).train()
-    opt = torch.optim.Adam(model.parameters(), lr=1e-2, fused=True)
+    opt = P.Adam(model.parameters(), lr=1e-2)
     crit = P.MSELoss()
     gi = torch.Generator().manual_seed(1234 + rank)
     hx = torch.randn(clips, 195, frames, S, S, generator=gi).pin_memory()

@@ -229,6 +229,19 @@ int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream);
  * (~10 PyTorch launches per convolution per optimiser step). */
 int b2d_pack_conv_weight(const float* w, int64_t s_o, int64_t s_i, int64_t s_k, int Cout, int Cin, int K,
                          int transpose, void* out, int rows_pad, int inner_pad, void* stream);
+/* The same for EVERY convolution of the model in one launch (the refresh of the operand copies after an optimiser
+ * step): descs_dev is a device array of n_descs descriptors; descriptor d owns the CTAs
+ * [block_begin[d], block_begin[d+1]) with ceil(rows_pad*K*inner_pad / b2d_pack_block_elems()) CTAs each, block_begin
+ * ascending from 0; total_blocks = their sum.  Output buffers are written in place (stable addresses). */
+typedef struct B2dPackDesc {
+  const float* w;
+  void* out;
+  int64_t s_o, s_i, s_k;
+  int32_t Cout, Cin, K, transpose, rows_pad, inner_pad;
+  int32_t block_begin, reserved;
+} B2dPackDesc;
+int b2d_pack_block_elems(void);
+int b2d_pack_conv_weights_multi(const B2dPackDesc* descs_dev, int n_descs, int total_blocks, void* stream);
 /* Audio encoder front end.  unet_audio.py:10-18 instantiates HF transformers' Wav2Vec2Model (third-party, not in
  * the reference tree); the first feature-extractor layer (`Wav2Vec2GroupNormConvLayer`: Conv1d(1 -> C, kernel K = 10,
  * stride, no padding) -> GroupNorm(C, C) -> erf GELU) produces the encoder's largest activation, (N, C, T) with
@@ -279,6 +292,30 @@ int64_t b2d_attention_bwd_ws_floats(int N, int L, int heads, int ch);
 int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out, int64_t ldo, const void* d_out,
                       int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
                       void* dqkv, int64_t lddqkv, float* delta_ws, void* stream);
+
+/* ------------------------------------------------------------------------
+ * Optimiser step.
+ * ---------------------------------------------------------------------- */
+
+/* One run of consecutive fp32 elements of one parameter tensor and its gradient / Adam moments. */
+typedef struct B2dAdamChunk {
+  float* param;
+  const float* grad;
+  float* exp_avg;
+  float* exp_avg_sq;
+  int64_t n;
+} B2dAdamChunk;
+
+/* `optimizer.step()` of `torch.optim.Adam(model.parameters(), 1e-2)` (video-generation/diffusion/train.py:102,134)
+ * for every parameter tensor in ONE launch: chunks_dev is a device array of n_chunks descriptors (one CTA each; the
+ * caller splits tensors into runs of <= 65536 elements).  Update, in torch's evaluation order
+ * (torch/optim/adam.py _single_tensor_adam, amsgrad = maximize = False):
+ *   g += weight_decay * p;  m = m + (1-beta1)(g - m);  v = beta2 v + (1-beta2) g^2;
+ *   p -= (lr / bias_correction1) * m / (sqrt(v) / sqrt(bias_correction2) + eps)
+ * with bias_correction{1,2} = 1 - beta{1,2}^step computed by the caller in double (1 - beta is formed in double and
+ * rounded once, as torch does: 1.f - 0.999f is 4.7e-5 off).  All arrays fp32, updated in place. */
+int b2d_adam_step(const B2dAdamChunk* chunks_dev, int n_chunks, double lr, double beta1, double beta2, float eps,
+                  float weight_decay, double bias_correction1, double bias_correction2, void* stream);
 
 /* B2D_DENOISER_ABI_BEGIN -- further denoiser kernels are declared below */
 

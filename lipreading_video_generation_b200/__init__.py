@@ -5,6 +5,7 @@ from .schedulers import CosineNoiseScheduler, LinearNoiseScheduler, LinearNoiseS
 from .unet import UNetModel
 from .unet_audio import AudioFeatureTransformer, UNetAudio, Wav2Vec2Encoder
 from .sampling import sample_images
+from .optim import Adam
 
 __all__ = ["UNetModel", "UNetAudio", "Wav2Vec2Encoder", "AudioFeatureTransformer", "LinearNoiseScheduler",
-           "LinearNoiseSchedulerV2", "CosineNoiseScheduler", "MSELoss", "mse_loss", "sample_images"]
+           "LinearNoiseSchedulerV2", "CosineNoiseScheduler", "MSELoss", "mse_loss", "sample_images", "Adam"]

@@ -231,6 +231,39 @@ pack_conv_weight_kernel(const float* __restrict__ w, long long s_o, long long s_
   }
 }
 
+// Every convolution's operand copy in ONE launch (the refresh after an optimiser step): a CTA owns PACK_BLOCK_ELEMS
+// consecutive output elements of one descriptor, found by binary search over the descriptors' first-CTA index.
+constexpr int PACK_BLOCK_ELEMS = 4096;
+__global__ void __launch_bounds__(256)
+pack_conv_weights_multi_kernel(const B2dPackDesc* __restrict__ descs, int n_descs) {
+  __shared__ int s_idx;
+  if (threadIdx.x == 0) {
+    int lo = 0, hi = n_descs - 1;
+    while (lo < hi) {
+      const int mid = (lo + hi + 1) >> 1;
+      if (descs[mid].block_begin <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+    }
+    s_idx = lo;
+  }
+  __syncthreads();
+  const B2dPackDesc d = descs[s_idx];
+  const long long total = (long long)d.rows_pad * d.K * d.inner_pad;
+  const long long base = (long long)((int)blockIdx.x - d.block_begin) * PACK_BLOCK_ELEMS;
+  const long long end = base + PACK_BLOCK_ELEMS < total ? base + PACK_BLOCK_ELEMS : total;
+  __half* __restrict__ out = reinterpret_cast<__half*>(d.out);
+  for (long long i = base + threadIdx.x; i < end; i += 256) {
+    const int c = (int)(i % d.inner_pad);
+    const long long rk = i / d.inner_pad;
+    const int k = (int)(rk % d.K);
+    const int r = (int)(rk / d.K);
+    const int co = d.transpose ? c : r, ci = d.transpose ? r : c;
+    const int kw = d.transpose ? d.K - 1 - k : k;
+    float v = 0.f;
+    if (co < d.Cout && ci < d.Cin) v = fminf(fmaxf(__ldg(d.w + co * d.s_o + ci * d.s_i + kw * d.s_k), -65504.f), 65504.f);
+    out[i] = __float2half_rn(v);
+  }
+}
+
 // ------------------------------------------------------------------ per-sample column sums
 // out[n][c] += sum_pix x[n, pix, c_off + c]   (emb_out gradient unet.py:266; bias grads = sum over n)
 __global__ void __launch_bounds__(256)
@@ -465,6 +498,15 @@ extern "C" int b2d_pack_conv_weight(const float* w, int64_t s_o, int64_t s_i, in
   const long long total = (long long)rows_pad * K * inner_pad;
   pack_conv_weight_kernel<<<ew_blocks(total), 256, 0, (cudaStream_t)stream>>>(w, s_o, s_i, s_k, Cout, Cin, K, transpose,
                                                                                  (__half*)out, rows_pad, inner_pad);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_pack_block_elems(void) { return b2d::PACK_BLOCK_ELEMS; }
+extern "C" int b2d_pack_conv_weights_multi(const B2dPackDesc* descs_dev, int n_descs, int total_blocks, void* stream) {
+  if (n_descs == 0 || total_blocks == 0) return B2D_OK;
+  B2D_REQUIRE(descs_dev && n_descs > 0 && total_blocks > 0, B2D_ERR_SHAPE, "pack_conv_weights_multi: bad arguments");
+  B2D_REQUIRE((reinterpret_cast<uintptr_t>(descs_dev) & 7) == 0, B2D_ERR_ALIGN, "pack_conv_weights_multi: table must be 8-byte aligned");
+  pack_conv_weights_multi_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>(descs_dev, n_descs);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

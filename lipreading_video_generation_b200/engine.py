@@ -46,6 +46,8 @@ class DenoiserEngine:
         self.emb_total = off
         self._freqs = None
         self._wcache = {}
+        self._pack_table = None
+        self._weights_maybe_stale = False
         self._step_seed = 0
         # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
         self._grad_layout = None
@@ -56,10 +58,43 @@ class DenoiserEngine:
         hit = self._wcache.get(key)
         if hit is not None and hit[0] == ver:
             return hit[1]
-        with torch.no_grad():
-            val = fn(param.detach())
-        self._wcache[key] = (ver, val)
+        ops.pack_records = recs = []
+        try:
+            with torch.no_grad():
+                val = fn(param.detach())
+        finally:
+            ops.pack_records = None
+        self._wcache[key] = [ver, val, param, recs]
+        self._pack_table = None
         return val
+
+    def refresh_packed(self):
+        """Called at the start of every forward.  The fp16 operand copies are keyed on (`_version`, `data_ptr`) of
+        their parameter, but an optimiser may update parameters without bumping `_version` (torch.optim.Adam(fused=True)
+        does not), so after any forward that recorded a tape (`_weights_maybe_stale`) every copy is re-packed from its
+        fp32 parameter -- in place, ONE launch of b2d_pack_conv_weights_multi for all convolutions and directions."""
+        stale = self._weights_maybe_stale
+        self._weights_maybe_stale = False
+        entries = [(k, e) for k, e in self._wcache.items() if k != "embcat"]
+        moved = [k for k, e in entries if e[0][1] != e[2].data_ptr() or any(r is None for r in e[3])]
+        if moved:                                   # parameter storage replaced (.to(), assign): re-made lazily
+            for k in moved:
+                del self._wcache[k]
+            self._pack_table = None
+            entries = [(k, e) for k, e in entries if k not in set(moved)]
+        if not stale and all(e[0][0] == e[2]._version for _, e in entries):
+            return
+        self._wcache.pop("embcat", None)
+        if not entries:
+            return
+        if self._pack_table is None:
+            recs = [r for _, e in entries for r in e[3]]
+            host, blocks = ops.build_pack_table(recs, ops.L.lib().b2d_pack_block_elems())
+            pinned = torch.from_numpy(host.view("uint8").reshape(-1).copy()).pin_memory()
+            self._pack_table = (pinned.to(entries[0][1][2].device, non_blocking=True), len(recs), blocks, pinned)
+        ops.repack_all(self._pack_table[0], self._pack_table[1], self._pack_table[2])
+        for _, e in entries:
+            e[0] = (e[2]._version, e[2].data_ptr())
 
     def w_fwd(self, conv, cin_pad=None):
         """Packed forward weights; for a Conv3d 3x3x3 (dims=3) a list of three 2-D tap groups [kt = 0, 1, 2]."""
@@ -168,6 +203,8 @@ class DenoiserEngine:
             N, _, S, _ = xt.shape
             B, T = N, 1
         self.T = T
+        self.refresh_packed()
+        self._weights_maybe_stale = bool(train)
         tape = {"N": N, "S": S, "B": B, "T": T} if train else None
         drop_p = float(m.dropout) if (m.training and train) else 0.0
         self._step_seed += 1

@@ -9,6 +9,7 @@ from __future__ import annotations
 
 import ctypes as C
 
+import numpy as np
 import torch
 
 from . import _lib as L
@@ -65,15 +66,42 @@ class _timed:
             KernelTimer.active.records.append((self.name, self.meta, self.e0, e1))
 
 
+pack_records = None      # a list while the engine records how one cached operand copy was made (see repack_all)
+_PACK_DESC = np.dtype([("w", "<u8"), ("out", "<u8"), ("s_o", "<i8"), ("s_i", "<i8"), ("s_k", "<i8"), ("Cout", "<i4"),
+                       ("Cin", "<i4"), ("K", "<i4"), ("transpose", "<i4"), ("rows_pad", "<i4"), ("inner_pad", "<i4"),
+                       ("block_begin", "<i4"), ("reserved", "<i4")])      # B2dPackDesc, include/b2d.h
+
+
 def _pack_on_device(w4: torch.Tensor, transpose: int, rows_pad: int, inner_pad: int) -> torch.Tensor:
     """One launch of b2d_pack_conv_weight on the (possibly strided) OIHW view; same values as the torch chain below."""
     co, ci, kh, kw = w4.shape
+    refreshable = True
     if kh * kw > 1 and w4.stride(2) != kw * w4.stride(3):
         w4 = w4.contiguous()
+        refreshable = False                 # packed from a temporary: cannot be re-packed from the parameter in place
     out = torch.empty(rows_pad, kh * kw * inner_pad, device=w4.device, dtype=F16)
     L.check(L.lib().b2d_pack_conv_weight(w4.data_ptr(), w4.stride(0), w4.stride(1), w4.stride(3), co, ci, kh * kw,
                                          transpose, out.data_ptr(), rows_pad, inner_pad, _s()), "b2d_pack_conv_weight")
+    if pack_records is not None:
+        pack_records.append((w4.data_ptr(), out, w4.stride(0), w4.stride(1), w4.stride(3), co, ci, kh * kw, transpose,
+                             rows_pad, inner_pad) if refreshable else None)
     return out
+
+
+def build_pack_table(records, block_elems: int):
+    """Host logic of b2d_pack_conv_weights_multi: (B2dPackDesc[] as a numpy structured array, total CTAs)."""
+    t = np.zeros(len(records), dtype=_PACK_DESC)
+    blk = 0
+    for i, (wptr, out, s_o, s_i, s_k, co, ci, K, tr, rp, ip) in enumerate(records):
+        t[i] = (wptr, out if isinstance(out, int) else out.data_ptr(), s_o, s_i, s_k, co, ci, K, tr, rp, ip, blk, 0)
+        blk += (rp * K * ip + block_elems - 1) // block_elems
+    return t, blk
+
+
+def repack_all(table_dev: torch.Tensor, n_descs: int, total_blocks: int) -> None:
+    """Refresh every recorded fp16 operand copy from its fp32 parameter, in place, in ONE launch."""
+    L.check(L.lib().b2d_pack_conv_weights_multi(table_dev.data_ptr(), n_descs, total_blocks, _s()),
+            "b2d_pack_conv_weights_multi")
 
 
 def pack_conv_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad_to: int = 16) -> torch.Tensor:

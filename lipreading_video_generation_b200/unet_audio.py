@@ -168,6 +168,50 @@ def patch_short_attention(wav2vec2):
     return wav2vec2
 
 
+def _mask_hidden_states_no_sync(self, hidden_states, mask_time_indices=None, attention_mask=None):
+    """HF `Wav2Vec2Model._mask_hidden_states` (SpecAugment) without its four host<->device synchronisations per train
+    step: the stock code uploads the numpy mask from pageable memory (`torch.tensor(mask, device=...)` -- a stream
+    sync) and applies it with boolean-mask indexing (`nonzero` -- a device->host read, again in the backward), which
+    drains the launch queue twice per step and leaves the GPU idle while the host re-fills it.  Same mask (the same
+    `_compute_mask_indices` calls, so the numpy RNG stream is consumed identically), uploaded through pinned memory
+    and applied with `torch.where`: identical values, nothing waits."""
+    from transformers.models.wav2vec2 import modeling_wav2vec2 as W
+    if not getattr(self.config, "apply_spec_augment", True):
+        return hidden_states
+    if not hidden_states.is_cuda:
+        return self._b2d_stock_mask_hidden_states(hidden_states, mask_time_indices=mask_time_indices,
+                                                  attention_mask=attention_mask)
+    batch_size, sequence_length, hidden_size = hidden_states.size()
+
+    def upload(mask_np):
+        host = torch.from_numpy(mask_np.astype("bool", copy=False)).pin_memory()
+        return host.to(hidden_states.device, non_blocking=True)
+
+    if mask_time_indices is not None:
+        m = mask_time_indices.to(torch.bool)
+        hidden_states = torch.where(m[:, :, None], self.masked_spec_embed.to(hidden_states.dtype), hidden_states)
+    elif self.config.mask_time_prob > 0 and self.training:
+        m = upload(W._compute_mask_indices((batch_size, sequence_length), mask_prob=self.config.mask_time_prob,
+                                           mask_length=self.config.mask_time_length, attention_mask=attention_mask,
+                                           min_masks=self.config.mask_time_min_masks))
+        hidden_states = torch.where(m[:, :, None], self.masked_spec_embed.to(hidden_states.dtype), hidden_states)
+    if self.config.mask_feature_prob > 0 and self.training:
+        f = upload(W._compute_mask_indices((batch_size, hidden_size), mask_prob=self.config.mask_feature_prob,
+                                           mask_length=self.config.mask_feature_length,
+                                           min_masks=self.config.mask_feature_min_masks))
+        hidden_states = torch.where(f[:, None, :], torch.zeros((), dtype=hidden_states.dtype, device=hidden_states.device),
+                                    hidden_states)
+    return hidden_states
+
+
+def patch_spec_augment(wav2vec2):
+    """Replace the SpecAugment masking step of a HF Wav2Vec2Model by the synchronisation-free restatement above."""
+    import types
+    if not hasattr(wav2vec2, "_b2d_stock_mask_hidden_states"):
+        wav2vec2._b2d_stock_mask_hidden_states = wav2vec2._mask_hidden_states
+        wav2vec2._mask_hidden_states = types.MethodType(_mask_hidden_states_no_sync, wav2vec2)
+
+
 def patch_pos_conv(wav2vec2):
     """Route the positional conv embedding of a HF Wav2Vec2Model through _pos_conv_short_sequence and the
     single-channel waveform conv through _conv1d_single_channel (same arithmetic, library GEMMs)."""
@@ -202,6 +246,7 @@ class Wav2Vec2Encoder(nn.Module):
             patch_pos_conv(self.wav2vec2)
             patch_feature_layer0(self.wav2vec2)
             patch_short_attention(self.wav2vec2)
+            patch_spec_augment(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

@@ -278,3 +278,42 @@ def test_short_attention_interface_falls_back_to_library_sdpa_on_cpu_tensors():
     with torch.no_grad():
         assert torch.equal(fast(input_values=a).last_hidden_state, stock(input_values=a).last_hidden_state)
     assert UA._short_attention_calls[0] == n0
+
+
+# ----------------------------------------------------------------------------- Adam (row N3) host logic
+def test_adam_chunk_table_splits_tensors_into_runs_and_matches_the_c_struct():
+    import ctypes as C
+    from lipreading_video_generation_b200 import optim
+    assert optim._CHUNK_DTYPE.itemsize == 40          # sizeof(B2dAdamChunk): 4 pointers + int64
+    t = optim.build_chunk_table([(1000, 2000, 3000, 4000, 10), (1 << 20, 2 << 20, 3 << 20, 4 << 20, 2 * 65536 + 5)], chunk=65536)
+    assert len(t) == 4
+    assert t["n"].tolist() == [10, 65536, 65536, 5]
+    assert t["param"].tolist() == [1000, 1 << 20, (1 << 20) + 4 * 65536, (1 << 20) + 8 * 65536]
+    assert t["exp_avg_sq"][3] == (4 << 20) + 8 * 65536
+    assert sum(t["n"].tolist()) == 10 + 2 * 65536 + 5
+    assert len(optim.build_chunk_table([(8, 8, 8, 8, 0)])) == 0       # empty tensor: no chunk
+
+
+def test_adam_rejects_cpu_parameters_and_unused_options():
+    import lipreading_video_generation_b200 as P
+    w = torch.nn.Parameter(torch.ones(4))
+    w.grad = torch.ones(4)
+    with pytest.raises(RuntimeError):
+        P.Adam([w], lr=1e-2).step()
+    with pytest.raises(NotImplementedError):
+        P.Adam([w], amsgrad=True)
+    with pytest.raises(ValueError):
+        P.Adam([w], lr=-1.0)
+    o = P.Adam([w], lr=1e-2)
+    assert set(o.state_dict()["param_groups"][0]) >= {"lr", "betas", "eps", "weight_decay"}
+
+
+def test_pack_table_block_ranges_are_contiguous_and_match_the_c_struct():
+    from lipreading_video_generation_b200 import ops
+    assert ops._PACK_DESC.itemsize == 72             # sizeof(B2dPackDesc)
+    recs = [(4096, 8192, 576, 9, 1, 64, 64, 9, 0, 64, 64),       # 64x64 3x3 fprop: 36864 elements -> 9 CTAs of 4096
+            (4096, 16384, 576, 9, 1, 64, 64, 9, 1, 64, 64),      # its dgrad copy
+            (1 << 20, 1 << 21, 195, 1, 1, 3, 195, 1, 0, 16, 256)]  # padded 1x1: 4096 elements -> 1 CTA
+    t, blocks = ops.build_pack_table(recs, 4096)
+    assert t["block_begin"].tolist() == [0, 9, 18] and blocks == 19
+    assert t["out"].tolist() == [8192, 16384, 1 << 21] and t["transpose"].tolist() == [0, 1, 0]

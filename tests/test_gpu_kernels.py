@@ -482,3 +482,129 @@ def test_wav2vec2_with_short_attention_matches_stock_encoder():
         torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
     assert UA._short_attention_calls[0] == n0 + 3
     assert rel(yf, ys) <= 1e-4
+
+
+# ----------------------------------------------------------------------------- Adam (row N3)
+@pytest.mark.parametrize("wd", [0.0, 0.01])
+def test_adam_multi_tensor_matches_torch_adam(wd):
+    """train.py:102,134: `Adam(model.parameters(), 1e-2)` + `step()`.  Oracle = torch.optim.Adam itself on the CPU
+    (fp32, single-tensor path).  Ragged sizes: 1 element, odd, a tail after a full 65536-element chunk, a misaligned
+    view.  Tolerance 2e-6 relative per tensor after 5 steps (fp32 op-for-op the same formula; FMA contraction and
+    the reciprocal differ in the last bit)."""
+    import lipreading_video_generation_b200 as P
+    g = gen(7)
+    sizes = [(1,), (7,), (3, 5, 3, 3), (65536 + 13,), (300, 257)]
+    base = [torch.randn(s, generator=g) for s in sizes]
+    big = torch.randn(1001, generator=g)
+    ref = [torch.nn.Parameter(b.clone()) for b in base] + [torch.nn.Parameter(big[1:].clone())]
+    dev_store = big.cuda()
+    ours = [torch.nn.Parameter(b.clone().cuda()) for b in base] + [torch.nn.Parameter(dev_store[1:])]   # 4-byte aligned only
+    o_ref = torch.optim.Adam(ref, lr=1e-2, weight_decay=wd)
+    o = P.Adam(ours, lr=1e-2, weight_decay=wd)
+    for step in range(5):
+        for r, w in zip(ref, ours):
+            gr = torch.randn(r.shape, generator=g) * (10.0 ** (step - 2))
+            r.grad = gr.clone()
+            w.grad = gr.cuda()
+        v0 = ours[0]._version
+        o_ref.step(); o.step()
+        assert ours[0]._version > v0            # packed fp16 operand copies are keyed on the version counter
+    for r, w in zip(ref, ours):
+        assert rel(w, r) <= 2e-6
+        assert rel(o.state[w]["exp_avg"], o_ref.state[r]["exp_avg"]) <= 2e-6
+        assert rel(o.state[w]["exp_avg_sq"], o_ref.state[r]["exp_avg_sq"]) <= 2e-6
+    sd = o.state_dict()
+    assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == 5.0
+    o_ref2 = torch.optim.Adam([torch.nn.Parameter(w.detach().clone()) for w in ours], lr=1e-2, weight_decay=wd)
+    o_ref2.load_state_dict(sd)                  # optimiser checkpoints move between the two classes
+
+
+def test_adam_skips_parameters_without_gradient_and_groups_by_step():
+    import lipreading_video_generation_b200 as P
+    a = torch.nn.Parameter(torch.ones(10, device="cuda"))
+    b = torch.nn.Parameter(torch.ones(10, device="cuda"))
+    o = P.Adam([a, b], lr=0.1)
+    a.grad = torch.ones_like(a)
+    o.step()                                      # only a moves; first Adam step = -lr * sign(g)
+    assert torch.allclose(a, torch.full_like(a, 0.9), atol=1e-6) and torch.equal(b, torch.ones_like(b))
+    a.grad = torch.ones_like(a); b.grad = torch.ones_like(b)
+    o.step()                                      # a at step 2, b at step 1: different bias corrections, two launches
+    assert torch.allclose(b, torch.full_like(b, 0.9), atol=1e-6)
+    assert torch.allclose(a, torch.full_like(a, 0.8), atol=1e-5)
+
+
+def test_operand_copies_follow_an_optimiser_that_does_not_bump_versions():
+    """torch.optim.Adam(fused=True) updates parameters without touching `_version`; the engine must still run the next
+    forward on the NEW weights (one b2d_pack_conv_weights_multi launch re-packs every convolution in place), and the
+    refreshed copies must equal a from-scratch pack."""
+    import lipreading_video_generation_b200 as P
+    from lipreading_video_generation_b200 import _lib, ops
+    torch.manual_seed(0)
+    m = P.UNetModel(32, 64, 64, 3, 1, (1,), channel_mult=(1, 2)).cuda().train()
+    with torch.no_grad():
+        for p in m.parameters():
+            if p.abs().max() == 0:
+                p.normal_(0, 0.02)
+    x = torch.randn(2, 64, 32, 32, device="cuda"); t = torch.tensor([3, 700], device="cuda")
+    opt = torch.optim.Adam(m.parameters(), lr=1e-2, fused=True)
+    out0 = m(x, t)
+    out0.square().mean().backward()
+    v0 = m.out[2].weight._version
+    opt.step()
+    assert m.out[2].weight._version == v0        # the premise of this test
+    l0 = _lib.lib().b2d_launch_count()
+    with torch.no_grad():
+        out1 = m(x, t)
+    eng = m.engine()
+    n_pack = sum(len(e[3]) for k, e in eng._wcache.items() if k != "embcat")
+    assert n_pack >= 10
+    assert rel(out1, out0) > 1e-3                # lr 1e-2 on every weight: the output must move
+    for k, e in eng._wcache.items():             # refreshed in place == packed from scratch
+        if k == "embcat":
+            continue
+        conv_w = e[2].detach()
+        fresh = ops.pack_conv_weight(conv_w, e[1].shape[1] // (conv_w[0, 0].numel())) if k[1] == "f" else None
+        if fresh is not None and fresh.shape == e[1].shape:
+            assert torch.equal(fresh, e[1]), k
+    m2 = P.UNetModel(32, 64, 64, 3, 1, (1,), channel_mult=(1, 2)).cuda().eval()
+    m2.load_state_dict(m.state_dict())
+    with torch.no_grad():
+        assert rel(m2(x, t), out1) <= 1e-3       # a fresh engine on the same weights agrees (GroupNorm statistics
+        #                                           use fp32 atomics: run-to-run differences at rounding level)
+        l1 = _lib.lib().b2d_launch_count()
+        m(x, t); l2 = _lib.lib().b2d_launch_count()
+        m(x, t); l3 = _lib.lib().b2d_launch_count()
+    assert l3 - l2 == l2 - l1 or l3 - l2 == l2 - l1 - 1    # eval loop: no re-pack once the weights are known current
+
+
+def test_spec_augment_restatement_equals_stock_masking_and_does_not_synchronise():
+    """HF Wav2Vec2Model._mask_hidden_states (third-party, kept) vs the synchronisation-free restatement installed by
+    patch_spec_augment: same numpy RNG stream -> identical masked tensor and identical gradients (bit-exact: masking
+    only selects values; the embedding's gradient is a sum whose order differs)."""
+    import numpy as np
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    from lipreading_video_generation_b200.unet_audio import patch_spec_augment
+    cfg = Wav2Vec2Config(num_hidden_layers=1, hidden_size=64, num_attention_heads=2, intermediate_size=64,
+                         mask_time_prob=0.3, mask_time_length=2, mask_time_min_masks=2,
+                         mask_feature_prob=0.2, mask_feature_length=4, mask_feature_min_masks=1)
+    w = Wav2Vec2Model(cfg).cuda().train()
+    h0 = torch.randn(6, 12, 64, device="cuda")
+    outs = []
+    for patched in (False, True):
+        if patched:
+            patch_spec_augment(w)
+        np.random.seed(5)
+        h = h0.clone().requires_grad_(True)
+        w.masked_spec_embed.grad = None
+        if patched:
+            torch.cuda.synchronize()
+            torch.cuda.set_sync_debug_mode("error")       # any synchronising call raises
+        try:
+            y = w._mask_hidden_states(h * 1.0)
+            (y * y).sum().backward()
+        finally:
+            torch.cuda.set_sync_debug_mode("default")
+        outs.append((y.detach().clone(), h.grad.clone(), w.masked_spec_embed.grad.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert rel(outs[1][2], outs[0][2]) <= 1e-5            # d masked_spec_embed: a sum over masked frames, order differs
+    assert (outs[0][0] != h0).any()                        # the mask did something
