@@ -462,11 +462,24 @@ def main():
     barrier()
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
-    for _ in range(a.steps):
+    # the loss of every step is copied to pinned host memory and READ on the host one step later (after the next step
+    # has been enqueued), the last one before the timer stops: logging the loss does not drain the launch queue
+    loss_pin = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    losses_host = []
+    for i in range(a.steps):
         dx0 = hx0.to(device, non_blocking=True); dc = hcond.to(device, non_blocking=True)
         da = haudio.to(device, non_blocking=True); dt = t_host.to(device, non_blocking=True)
         loss = step(dx0, dc, da, dt)
-        loss_host = loss.item()                    # device -> host read of the step's result
+        loss_pin[i % 2].copy_(loss.detach(), non_blocking=True)     # device -> host read of the step's result
+        loss_ev[i % 2].record()
+        if i > 0:
+            loss_ev[(i - 1) % 2].synchronize()
+            losses_host.append(float(loss_pin[(i - 1) % 2]))
+    loss_ev[(a.steps - 1) % 2].synchronize()
+    losses_host.append(float(loss_pin[(a.steps - 1) % 2]))
+    loss_host = losses_host[-1]
+    assert len(losses_host) == a.steps
     f1.record()
     barrier()
     ms_e2e = f0.elapsed_time(f1) / a.steps
