@@ -7,6 +7,7 @@
 //
 // HBM-bound kernels: every thread moves 16-byte vectors (8 bf16 channels of one pixel).
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace b2d {
 
@@ -363,6 +364,312 @@ gn_param_grad_kernel(const float* __restrict__ ab, int N, int Ctot, float* __res
   }
 }
 
+// ====================================================================== single-pass (cluster) variants
+// The two-kernel forms above read x (and dy) from HBM twice: statistics, then apply.  Here one thread-block CLUSTER
+// owns one sample: each CTA stages its pixel range of x in shared memory with cp.async (every thread re-reads only the
+// 16-byte vectors it loaded itself, so no CTA barrier guards the tile), the per-group partial sums are exchanged through
+// distributed shared memory (64 floats per CTA) across one cluster barrier, and the apply pass reads x from shared
+// memory.  HBM traffic: forward 1 read + 1 write (was 2 + 1); backward x once, dy once from HBM and once more from L2
+// (it was read microseconds earlier by the same SM; the in-flight footprint is < 30 MB), dx once (was 2 + 2 + 1).
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory"); }
+__device__ __forceinline__ float ld_dsmem_f32(const float* local_ptr, uint32_t rank) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(local_ptr);
+  uint32_t ra;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(ra) : "r"(a), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(ra) : "memory");
+  return v;
+}
+__device__ __forceinline__ void cp_async16(void* smem, const void* g) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(smem);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"(a), "l"(g) : "memory");
+}
+__device__ __forceinline__ void cp_async_wait_all() {
+  asm volatile("cp.async.commit_group;" ::: "memory");
+  asm volatile("cp.async.wait_group 0;" ::: "memory");
+}
+
+// grid (CL, N), cluster (CL, 1, 1); block = V * rows threads; dynamic smem = ppc * Ctot * 2 + (2 * Ctot + 64) * 4 bytes
+__global__ void __launch_bounds__(256)
+gn_fwd_fused_kernel(GnSrc s, int HW, int Ctot, int ppc, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    float eps, int act, float drop_p, unsigned long long seed, __half* __restrict__ y,
+                    float* __restrict__ mean_out, float* __restrict__ rstd_out) {
+  extern __shared__ __align__(16) unsigned char gn_smem[];
+  uint4* tile = reinterpret_cast<uint4*>(gn_smem);                                   // [ppc][V]
+  float* sh = reinterpret_cast<float*>(gn_smem + (size_t)ppc * Ctot * 2);            // [2 * Ctot]
+  float* part = sh + 2 * Ctot;                                                       // [32][2]
+  __shared__ float s_mean[32], s_rstd[32];
+  const int CL = gridDim.x, rank = blockIdx.x, n = blockIdx.y;
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V, prow = threadIdx.x / V, rows = blockDim.x / V;
+  const int c = v * 8;
+  const int cpg = Ctot >> 5;
+  const int p0 = rank * ppc;
+  const int p1 = (p0 + ppc < HW) ? p0 + ppc : HW;
+  for (int pix = p0 + prow; pix < p1; pix += rows)
+    cp_async16(&tile[(pix - p0) * V + v], src_ptr(s, (long long)n * HW + pix, c));
+  for (int i = threadIdx.x; i < 2 * Ctot; i += blockDim.x) sh[i] = 0.f;
+  cp_async_wait_all();
+  __syncthreads();
+  float a[8], q[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { a[i] = 0.f; q[i] = 0.f; }
+  for (int pix = p0 + prow; pix < p1; pix += rows) {
+    float x[8];
+    unpack8(tile[(pix - p0) * V + v], x);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a[i] += x[i]; q[i] = fmaf(x[i], x[i], q[i]); }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { atomicAdd(&sh[c + i], a[i]); atomicAdd(&sh[Ctot + c + i], q[i]); }
+  __syncthreads();
+  if (threadIdx.x < 32) {
+    float sa = 0.f, sq = 0.f;
+    for (int i = 0; i < cpg; ++i) { sa += sh[threadIdx.x * cpg + i]; sq += sh[Ctot + threadIdx.x * cpg + i]; }
+    part[threadIdx.x * 2] = sa;
+    part[threadIdx.x * 2 + 1] = sq;
+  }
+  cluster_arrive();
+  cluster_wait();                                       // every CTA's partial sums are visible cluster-wide
+  if (threadIdx.x < 32) {
+    double S = 0.0, Q = 0.0;
+    for (int r = 0; r < CL; ++r) {
+      S += (double)ld_dsmem_f32(&part[threadIdx.x * 2], r);
+      Q += (double)ld_dsmem_f32(&part[threadIdx.x * 2 + 1], r);
+    }
+    const double cnt = (double)cpg * (double)HW;
+    const double m = S / cnt;
+    double var = Q / cnt - m * m;
+    if (var < 0.0) var = 0.0;
+    const float rs = (float)(1.0 / sqrt(var + (double)eps));
+    s_mean[threadIdx.x] = (float)m;
+    s_rstd[threadIdx.x] = rs;
+    if (rank == 0) { mean_out[n * 32 + threadIdx.x] = (float)m; rstd_out[n * 32 + threadIdx.x] = rs; }
+  }
+  cluster_arrive();                                     // done with the peers' shared memory (waited on before exit)
+  __syncthreads();
+  float g[8], b[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float gm = __ldg(gamma + c + i), rs_ = s_rstd[(c + i) / cpg];
+    g[i] = gm * rs_;
+    b[i] = fmaf(-s_mean[(c + i) / cpg], g[i], __ldg(beta + c + i));
+  }
+  const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
+  for (int pix = p0 + prow; pix < p1; pix += rows) {
+    const long long gp = (long long)n * HW + pix;
+    float x[8];
+    unpack8(tile[(pix - p0) * V + v], x);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const float z = fmaf(x[i], g[i], b[i]);
+      x[i] = act ? silu_f(z) : z;
+    }
+    if (drop_p > 0.f) {
+      bool keep[8];
+      dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) x[i] = keep[i] ? x[i] * keep_scale : 0.f;
+    }
+    store8_fmt(y + gp * Ctot + c, x, FMT_F16);
+  }
+  cluster_wait();
+}
+
+__global__ void __launch_bounds__(256, 3)
+gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, int ppc,
+                    const float* __restrict__ mean, const float* __restrict__ rstd,
+                    const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
+                    unsigned long long seed, float* __restrict__ ab, GnBwdOut o) {
+  extern __shared__ __align__(16) unsigned char gn_smem[];
+  uint4* tile = reinterpret_cast<uint4*>(gn_smem);                                   // x, [ppc][V]
+  float* sh = reinterpret_cast<float*>(gn_smem + (size_t)ppc * Ctot * 2);            // [2 * Ctot]
+  float* part = sh + 2 * Ctot;                                                       // [32][2]
+  __shared__ float s1[32], s2[32];
+  const int CL = gridDim.x, rank = blockIdx.x, n = blockIdx.y;
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V, prow = threadIdx.x / V, rows = blockDim.x / V;
+  const int c = v * 8;
+  const int cpg = Ctot >> 5;
+  const int p0 = rank * ppc;
+  const int p1 = (p0 + ppc < HW) ? p0 + ppc : HW;
+  for (int pix = p0 + prow; pix < p1; pix += rows)
+    cp_async16(&tile[(pix - p0) * V + v], src_ptr(s, (long long)n * HW + pix, c));
+  for (int i = threadIdx.x; i < 2 * Ctot; i += blockDim.x) sh[i] = 0.f;
+  float rg[8], bb[8], pp[8], qq[8];                     // pp / qq hold the running sums A / B in the first pass
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int gi = (c + i) / cpg;
+    const float rs_ = __ldg(rstd + n * 32 + gi), mu_ = __ldg(mean + n * 32 + gi);
+    rg[i] = rs_ * __ldg(gamma + c + i);
+    bb[i] = fmaf(-mu_, rg[i], __ldg(beta + c + i));
+    pp[i] = 0.f; qq[i] = 0.f;
+  }
+  const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
+  cp_async_wait_all();
+  __syncthreads();
+  for (int pix0 = p0 + prow; pix0 < p1; pix0 += 4 * rows) {
+    uint4 rd[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (pix0 + u * rows < p1) rd[u] = ldg_nc_u4(dy + ((long long)n * HW + pix0 + u * rows) * Ctot + c);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int pix = pix0 + u * rows;
+      if (pix >= p1) continue;
+      const long long gp = (long long)n * HW + pix;
+      float x[8], d[8];
+      unpack8(tile[(pix - p0) * V + v], x);
+      unpack8(rd[u], d);
+      if (drop_p > 0.f) {
+        bool keep[8];
+        dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d[i] = keep[i] ? d[i] * keep_scale : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dh = d[i];
+        if (act) {
+          const float z = fmaf(x[i], rg[i], bb[i]);
+          const float sg = fast_sigmoid(z);
+          dh *= sg * (1.0f + z * (1.0f - sg));
+        }
+        pp[i] += dh; qq[i] = fmaf(dh, x[i], qq[i]);
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float rs_ = __ldg(rstd + n * 32 + (c + i) / cpg), mu_ = __ldg(mean + n * 32 + (c + i) / cpg);
+    atomicAdd(&sh[c + i], pp[i]);
+    atomicAdd(&sh[Ctot + c + i], rs_ * (qq[i] - mu_ * pp[i]));
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < Ctot; i += blockDim.x) {        // per-channel sums for dgamma / dbeta
+    atomicAdd(&ab[((long long)n * Ctot + i) * 2 + 0], sh[i]);
+    atomicAdd(&ab[((long long)n * Ctot + i) * 2 + 1], sh[Ctot + i]);
+  }
+  if (threadIdx.x < 32) {
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < cpg; ++i) {
+      const int ch = threadIdx.x * cpg + i;
+      const float gm = __ldg(gamma + ch);
+      a = fmaf(gm, sh[ch], a);
+      b = fmaf(gm, sh[Ctot + ch], b);
+    }
+    part[threadIdx.x * 2] = a;
+    part[threadIdx.x * 2 + 1] = b;
+  }
+  cluster_arrive();
+  cluster_wait();
+  if (threadIdx.x < 32) {
+    float a = 0.f, b = 0.f;
+    for (int r = 0; r < CL; ++r) {
+      a += ld_dsmem_f32(&part[threadIdx.x * 2], r);
+      b += ld_dsmem_f32(&part[threadIdx.x * 2 + 1], r);
+    }
+    const float inv_m = 1.0f / ((float)cpg * (float)HW);
+    s1[threadIdx.x] = a * inv_m;
+    s2[threadIdx.x] = b * inv_m;
+  }
+  cluster_arrive();
+  __syncthreads();
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int gi = (c + i) / cpg;
+    const float rs_ = __ldg(rstd + n * 32 + gi), mu_ = __ldg(mean + n * 32 + gi);
+    pp[i] = -rs_ * rs_ * s2[gi];
+    qq[i] = -mu_ * pp[i] - rs_ * s1[gi];
+  }
+  const bool first = c < s.C1;
+  const bool has_a = o.add_a && (first || o.add_a_full);
+  const bool has_b = o.add_b && first;
+  for (int pix0 = p0 + prow; pix0 < p1; pix0 += 2 * rows) {
+    uint4 rd[2], ra[2], rb[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (pix0 + u * rows < p1) {
+        const long long gp = (long long)n * HW + pix0 + u * rows;
+        rd[u] = ldg_nc_u4(dy + gp * Ctot + c);
+        if (has_a) ra[u] = ldg_nc_u4(o.add_a + gp * o.lda + c);
+        if (has_b) rb[u] = ldg_nc_u4(o.add_b + gp * o.ldb + c);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int pix = pix0 + u * rows;
+      if (pix >= p1) continue;
+      const long long gp = (long long)n * HW + pix;
+      float x[8], d[8];
+      unpack8(tile[(pix - p0) * V + v], x);
+      unpack8(rd[u], d);
+      if (drop_p > 0.f) {
+        bool keep[8];
+        dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) d[i] = keep[i] ? d[i] * keep_scale : 0.f;
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float dh = d[i];
+        if (act) {
+          const float z = fmaf(x[i], rg[i], bb[i]);
+          const float sg = fast_sigmoid(z);
+          dh *= sg * (1.0f + z * (1.0f - sg));
+        }
+        x[i] = fmaf(dh, rg[i], fmaf(x[i], pp[i], qq[i]));
+      }
+      if (has_a) { float t[8]; unpack8(ra[u], t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+      if (has_b) { float t[8]; unpack8(rb[u], t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+      if (first) store8(o.dx1 + gp * o.ldd1 + c, x);
+      else       store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+    }
+  }
+  cluster_wait();
+}
+
+// Cluster size and pixels per CTA for the single-pass kernels, or 0 for the two-kernel path.  Measured on the train64
+// step (N = 256; profiles/r2_groupnorm_fused.md): the single pass wins only while a sample fits one or two CTAs of
+// <= 72 KB (HW = 256: 0.021 vs 0.033 ms forward, 0.060 vs 0.078 ms backward at C = 128); with 4 - 8 CTAs per sample the
+// load -> reduce -> barrier -> apply phases of a CTA serialise and only 1 - 3 CTAs fit an SM, so the kernel becomes
+// latency bound (HW = 4096, C = 128: 2.03 vs 0.90 ms) although it moves 40 % fewer bytes.  B2D_GN_FUSED=0 disables the
+// single pass, =2 forces it wherever the tile fits 200 KB at cluster 8 (the A/B switch behind those numbers).
+static int gn_fused_plan(int HW, int Ctot, int* ppc, size_t* smem) {
+  static const int mode = [] { const char* e = getenv("B2D_GN_FUSED"); return e ? atoi(e) : 1; }();
+  if (mode == 0) return 0;
+  const size_t extra = (size_t)(2 * Ctot + 64) * sizeof(float);
+  const int max_cl = mode == 2 ? 8 : 2;
+  for (int cl = 1; cl <= max_cl; cl *= 2) {
+    const int p = (HW + cl - 1) / cl;
+    const size_t bytes = (size_t)p * Ctot * 2 + extra;
+    if (bytes <= (size_t)(cl == 8 && mode == 2 ? 200 : 72) * 1024) { *ppc = p; *smem = bytes; return cl; }
+  }
+  return 0;
+}
+
+template <typename... Args>
+static cudaError_t gn_launch_cluster(void (*kern)(Args...), int cl, int N, int threads, size_t smem, cudaStream_t st,
+                                     Args... args) {
+  cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024 + 4096);
+  if (e != cudaSuccess) return e;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((unsigned)cl, (unsigned)N);
+  cfg.blockDim = dim3((unsigned)threads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = (unsigned)cl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kern, args...);
+}
+
 // blocks_per_sm: grid size in blocks per SM (more blocks = shorter pixel runs per block but better balance)
 static int gn_launch_dims(int N, int HW, int Ctot, int blocks_per_sm, dim3* grid, int* threads) {
   const int V = Ctot / 8;
@@ -416,8 +723,17 @@ extern "C" int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, flo
   const int Ctot = s.C1 + s.C2;
   B2D_REQUIRE(workspace_bytes >= (size_t)a->N * 64 * sizeof(double), B2D_ERR_WORKSPACE, "groupnorm_fwd: workspace");
   cudaStream_t st = (cudaStream_t)stream;
-  B2D_CHECK_CUDA(cudaMemsetAsync(workspace, 0, (size_t)a->N * 64 * sizeof(double), st));
   dim3 grid; int threads;
+  int ppc = 0; size_t fsmem = 0;
+  if (const int cl = gn_fused_plan(a->HW, Ctot, &ppc, &fsmem)) {
+    gn_launch_dims(a->N, a->HW, Ctot, 1, &grid, &threads);
+    B2D_CHECK_CUDA(gn_launch_cluster(gn_fwd_fused_kernel, cl, a->N, threads, fsmem, st, s, a->HW, Ctot, ppc, a->gamma,
+                                     a->beta, a->eps, a->act, a->drop_p, (unsigned long long)a->seed, (__half*)y, mean,
+                                     rstd));
+    B2D_CHECK_LAUNCH();
+    return B2D_OK;
+  }
+  B2D_CHECK_CUDA(cudaMemsetAsync(workspace, 0, (size_t)a->N * 64 * sizeof(double), st));
   gn_launch_dims(a->N, a->HW, Ctot, 3, &grid, &threads);   // measured on the train64 step: 3 -> 3.84 ms, 8 -> 4.43 ms
   gn_stats_kernel<<<grid, threads, 2 * Ctot * sizeof(float), st>>>(s, a->HW, Ctot, (double*)workspace);
   B2D_CHECK_LAUNCH();
@@ -442,14 +758,25 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
   cudaStream_t st = (cudaStream_t)stream;
   B2D_CHECK_CUDA(cudaMemsetAsync(workspace, 0, (size_t)a->N * Ctot * 2 * sizeof(float), st));
   dim3 grid; int threads;
+  GnBwdOut o;
+  o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
+  o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
+  int ppc = 0; size_t fsmem = 0;
+  if (const int cl = gn_fused_plan(a->HW, Ctot, &ppc, &fsmem)) {
+    gn_launch_dims(a->N, a->HW, Ctot, 1, &grid, &threads);
+    B2D_CHECK_CUDA(gn_launch_cluster(gn_bwd_fused_kernel, cl, a->N, threads, fsmem, st, s, (const __half*)dy, a->HW, Ctot,
+                                     ppc, mean, rstd, a->gamma, a->beta, a->act, a->drop_p,
+                                     (unsigned long long)a->seed, (float*)workspace, o));
+    B2D_CHECK_LAUNCH();
+    gn_param_grad_kernel<<<(Ctot + 31) / 32, 256, 0, st>>>((const float*)workspace, a->N, Ctot, dgamma, dbeta);
+    B2D_CHECK_LAUNCH();
+    return B2D_OK;
+  }
   gn_launch_dims(a->N, a->HW, Ctot, 8, &grid, &threads);   // measured: 8 -> 10.4 ms, 3 -> 12.1 ms
   gn_bwd_reduce_kernel<<<grid, threads, 2 * Ctot * sizeof(float), st>>>(
       s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
       (float*)workspace);
   B2D_CHECK_LAUNCH();
-  GnBwdOut o;
-  o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
-  o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
   gn_bwd_apply_kernel<<<grid, threads, 0, st>>>(s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma,
                                                 a->beta, a->act, a->drop_p, a->seed, (const float*)workspace, o);
   B2D_CHECK_LAUNCH();
