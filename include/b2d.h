@@ -185,11 +185,14 @@ int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, float* rstd, v
 /* dy: fp16 (N,HW,C1+C2) gradient w.r.t. y.  dx1 (N,HW,lddx1) / dx2 (N,HW,lddx2) receive the input
  * gradients; add_a / add_b (optional, fp16, channel pitch lda / ldb) are ADDED to dx1 so that the
  * residual / skip gradient accumulation is fused; with add_a_full != 0, add_a spans all C1+C2
- * channels and its upper C2 channels are added to dx2.  dgamma/dbeta: fp32 [C1+C2], accumulated. */
+ * channels and its upper C2 channels are added to dx2.  dgamma/dbeta: fp32 [C1+C2], accumulated.
+ * dx1_colsum (optional, fp32 [N][ld_colsum], ACCUMULATED): per-sample sums over pixels of dx1's C1 channels -- the
+ * bias / timestep-embedding gradient of the convolution whose output gradient dx1 is (unet.py:266), produced while
+ * dx1 is still in registers instead of by a second pass over it (b2d_colsum). */
 int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
                       void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
-                      const void* add_b, int64_t ldb, int add_a_full, float* dgamma, float* dbeta, void* workspace,
-                      size_t workspace_bytes, void* stream);
+                      const void* add_b, int64_t ldb, int add_a_full, float* dx1_colsum, int64_t ld_colsum,
+                      float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes, void* stream);
 
 /* ------------------------------------------------------------------------
  * Layout / conditioning helpers (HBM bound).

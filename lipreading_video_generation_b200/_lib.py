@@ -84,8 +84,8 @@ SIGNATURES = {
     "b2d_groupnorm_workspace_bytes": (c_size_t, [c_int, c_int]),
     "b2d_groupnorm_fwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "b2d_groupnorm_bwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
-                                  c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_void_p, c_void_p,
-                                  c_size_t, c_void_p]),
+                                  c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_void_p,
+                                  c_void_p, c_size_t, c_void_p]),
     "b2d_assemble_input": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p] + [c_int] * 9 + [c_void_p, c_void_p]),
     "b2d_assemble_input_bwd": (c_int, [c_void_p, c_void_p] + [c_int] * 9 + [c_void_p, c_void_p, c_void_p]),
     "b2d_upsample2x": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]),

@@ -241,14 +241,32 @@ struct GnBwdOut {
   const __half* add_a; long long lda;
   const __half* add_b; long long ldb;
   int add_a_full;  // add_a spans all C1+C2 channels (also added to dx2)
+  float* colsum; long long ldcs;  // optional: colsum[n][c] += sum over pixels of dx1[n, :, c] (c < C1), fp32
 };
 
-__global__ void __launch_bounds__(256, 3)
+// Per-sample column sums of the dx1 values a thread produced (cs[8], channels c..c+7 of source 1), folded into
+// o.colsum through a shared-memory stage: the consumer of dx1 as a convolution's output gradient needs exactly these
+// sums for the bias (and timestep-embedding) gradients, and a separate pass would read the tensor from HBM again.
+__device__ __forceinline__ void gn_colsum_flush(const GnBwdOut& o, float* shc, const float* cs, int C1, int c, int n,
+                                                bool first) {
+  for (int i = threadIdx.x; i < C1; i += blockDim.x) shc[i] = 0.f;
+  __syncthreads();
+  if (first) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) atomicAdd(&shc[c + i], cs[i]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C1; i += blockDim.x) atomicAdd(&o.colsum[(long long)n * o.ldcs + i], shc[i]);
+}
+
+template <bool CS>   // CS: also accumulate the per-sample column sums of dx1 (8 more live registers: 2 CTAs / SM)
+__global__ void __launch_bounds__(256, CS ? 2 : 3)
 gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
                     const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
                     unsigned long long seed, const float* __restrict__ ab, GnBwdOut o) {
   __shared__ float s1[32], s2[32];
+  extern __shared__ float shc[];   // [C1] when o.colsum
   const int n = blockIdx.y;
   const int cpg = Ctot >> 5;
   if (threadIdx.x < 32) {
@@ -284,6 +302,7 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
   const bool first = c < s.C1;
   const bool has_a = o.add_a && (first || o.add_a_full);
   const bool has_b = o.add_b && first;
+  float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   const int step = gridDim.x * rows;
   for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 2 * step) {
     uint4 rx[2], rd[2], ra[2], rb[2];
@@ -327,10 +346,18 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
     if (has_b) { float t[8]; unpack8(rb[u], t);
 #pragma unroll
       for (int i = 0; i < 8; ++i) x[i] += t[i]; }
-    if (first) store8(o.dx1 + gp * o.ldd1 + c, x);
-    else       store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+    if (first) {
+      store8(o.dx1 + gp * o.ldd1 + c, x);
+      if (CS) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) cs[i] += x[i];
+      }
+    } else {
+      store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+    }
     }
   }
+  if (CS) gn_colsum_flush(o, shc, cs, s.C1, c, n, first);
 }
 
 // dgamma[c] = sum_n ab[n][c][1], dbeta[c] = sum_n ab[n][c][0]  (accumulated into fp32 grads)
@@ -477,7 +504,8 @@ gn_fwd_fused_kernel(GnSrc s, int HW, int Ctot, int ppc, const float* __restrict_
   cluster_wait();
 }
 
-__global__ void __launch_bounds__(256, 3)
+template <bool CS>
+__global__ void __launch_bounds__(256, CS ? 2 : 3)
 gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, int ppc,
                     const float* __restrict__ mean, const float* __restrict__ rstd,
                     const float* __restrict__ gamma, const float* __restrict__ beta, int act, float drop_p,
@@ -586,6 +614,7 @@ gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, in
   const bool first = c < s.C1;
   const bool has_a = o.add_a && (first || o.add_a_full);
   const bool has_b = o.add_b && first;
+  float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
   for (int pix0 = p0 + prow; pix0 < p1; pix0 += 2 * rows) {
     uint4 rd[2], ra[2], rb[2];
 #pragma unroll
@@ -627,15 +656,23 @@ gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, in
       if (has_b) { float t[8]; unpack8(rb[u], t);
 #pragma unroll
         for (int i = 0; i < 8; ++i) x[i] += t[i]; }
-      if (first) store8(o.dx1 + gp * o.ldd1 + c, x);
-      else       store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+      if (first) {
+        store8(o.dx1 + gp * o.ldd1 + c, x);
+        if (CS) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) cs[i] += x[i];
+        }
+      } else {
+        store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+      }
     }
   }
-  cluster_wait();
+  cluster_wait();                                       // after it no peer reads this CTA's `part`; `sh` is free for reuse
+  if (CS) gn_colsum_flush(o, sh, cs, s.C1, c, n, first);
 }
 
 // Cluster size and pixels per CTA for the single-pass kernels, or 0 for the two-kernel path.  Measured on the train64
-// step (N = 256; profiles/r2_groupnorm_fused.md): the single pass wins only while a sample fits one or two CTAs of
+// step (N = 256; profiles/r1_groupnorm_fused.md): the single pass wins only while a sample fits one or two CTAs of
 // <= 72 KB (HW = 256: 0.021 vs 0.033 ms forward, 0.060 vs 0.078 ms backward at C = 128); with 4 - 8 CTAs per sample the
 // load -> reduce -> barrier -> apply phases of a CTA serialise and only 1 - 3 CTAs fit an SM, so the kernel becomes
 // latency bound (HW = 4096, C = 128: 2.03 vs 0.90 ms) although it moves 40 % fewer bytes.  B2D_GN_FUSED=0 disables the
@@ -745,8 +782,8 @@ extern "C" int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, flo
 
 extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
                                  void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
-                                 const void* add_b, int64_t ldb, int add_a_full, float* dgamma, float* dbeta, void* workspace,
-                                 size_t workspace_bytes, void* stream) {
+                                 const void* add_b, int64_t ldb, int add_a_full, float* dx1_colsum, int64_t ld_colsum,
+                                 float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = gn_check(a, "groupnorm_bwd");
   if (rc) return rc;
   const GnSrc s = make_src(a);
@@ -761,10 +798,12 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
   GnBwdOut o;
   o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
   o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
+  o.colsum = dx1_colsum; o.ldcs = ld_colsum;
   int ppc = 0; size_t fsmem = 0;
   if (const int cl = gn_fused_plan(a->HW, Ctot, &ppc, &fsmem)) {
     gn_launch_dims(a->N, a->HW, Ctot, 1, &grid, &threads);
-    B2D_CHECK_CUDA(gn_launch_cluster(gn_bwd_fused_kernel, cl, a->N, threads, fsmem, st, s, (const __half*)dy, a->HW, Ctot,
+    B2D_CHECK_CUDA(gn_launch_cluster(dx1_colsum ? gn_bwd_fused_kernel<true> : gn_bwd_fused_kernel<false>, cl, a->N, threads,
+                                     fsmem, st, s, (const __half*)dy, a->HW, Ctot,
                                      ppc, mean, rstd, a->gamma, a->beta, a->act, a->drop_p,
                                      (unsigned long long)a->seed, (float*)workspace, o));
     B2D_CHECK_LAUNCH();
@@ -777,8 +816,14 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
       s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
       (float*)workspace);
   B2D_CHECK_LAUNCH();
-  gn_bwd_apply_kernel<<<grid, threads, 0, st>>>(s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma,
-                                                a->beta, a->act, a->drop_p, a->seed, (const float*)workspace, o);
+  if (dx1_colsum)
+    gn_bwd_apply_kernel<true><<<grid, threads, s.C1 * sizeof(float), st>>>(
+        s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
+        (const float*)workspace, o);
+  else
+    gn_bwd_apply_kernel<false><<<grid, threads, 0, st>>>(
+        s, (const __half*)dy, a->HW, Ctot, mean, rstd, a->gamma, a->beta, a->act, a->drop_p, a->seed,
+        (const float*)workspace, o);
   B2D_CHECK_LAUNCH();
   gn_param_grad_kernel<<<(Ctot + 31) / 32, 256, 0, st>>>((const float*)workspace, a->N, Ctot, dgamma, dbeta);
   B2D_CHECK_LAUNCH();

@@ -48,6 +48,7 @@ class DenoiserEngine:
         self._wcache = {}
         self._pack_table = None
         self._weights_maybe_stale = False
+        self._colsums = {}
         self._step_seed = 0
         # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
         self._grad_layout = None
@@ -168,11 +169,20 @@ class DenoiserEngine:
         return self._unfold(y, x), mean, rstd
 
     def _gn_bwd(self, G, x, gn, dy, mean, rstd, x2=None, act=True, drop_p=0.0, seed=0, add_a=None, add_b=None,
-                add_a_full=False):
+                add_a_full=False, colsum_out=None, want_colsum=False):
+        """want_colsum: also produce the per-sample pixel sums of dx1 (fp32 (N, C1)) inside the same kernel and remember
+        them under dx1's address: the layer that consumes dx1 as a convolution's output gradient takes its bias
+        gradient from there instead of re-reading dx1 (`bias_grad` in `_engine_backward`)."""
+        if want_colsum and colsum_out is None and self.T == 1:
+            colsum_out = torch.zeros(x.shape[0], x.shape[-1], device=x.device, dtype=torch.float32)
         dx1, dx2 = ops.groupnorm_bwd(self._fold(x), gn.weight.detach(), gn.bias.detach(), self._fold(dy), mean, rstd,
                                      G.g(gn.weight), G.g(gn.bias), x2=self._fold(x2), act=act, eps=gn.eps, drop_p=drop_p,
-                                     seed=seed, add_a=self._fold(add_a), add_b=self._fold(add_b), add_a_full=add_a_full)
-        return self._unfold(dx1, x), self._unfold(dx2, x2) if x2 is not None else None
+                                     seed=seed, add_a=self._fold(add_a), add_b=self._fold(add_b), add_a_full=add_a_full,
+                                     colsum_out=colsum_out)
+        dx1 = self._unfold(dx1, x)
+        if want_colsum and colsum_out is not None:
+            self._colsums = {dx1.data_ptr(): (colsum_out, dx1)}     # only the most recent one can be consumed next
+        return dx1, self._unfold(dx2, x2) if x2 is not None else None
 
     def emb_cat(self):
         ws = [rb.emb_layers[1].weight for rb in self.resblocks]
@@ -491,8 +501,12 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     def bias_grad(dy, bias_param, cout=None, also=None):
         """bias gradient = column sums of dy over samples and pixels."""
         cout = dy.shape[3] if cout is None else cout
-        tmp = torch.zeros(N, cout, device=dev, dtype=torch.float32)
-        ops.colsum(dy, tmp, 0, cout)
+        hit = eng._colsums.get(dy.data_ptr())
+        if hit is not None and hit[1].shape == dy.shape and hit[1].stride() == dy.stride() and hit[0].shape[1] == cout:
+            tmp = hit[0]                                  # produced by the GroupNorm backward that wrote dy
+        else:
+            tmp = torch.zeros(N, cout, device=dev, dtype=torch.float32)
+            ops.colsum(dy, tmp, 0, cout)
         ops.reduce_rows(tmp, G.g(bias_param))
         if also is not None:
             ops.reduce_rows(tmp, G.g(also))
@@ -518,9 +532,12 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         eng._wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
         bias_grad(dout_, conv2.bias, also=rb.skip_connection.bias if has_skip_conv else None)
         d_h3 = eng._conv(dout_, eng.w_dgrad(conv2), cout, 3, 1)
-        d_h2, _ = eng._gn_bwd(G, t["h2"], gn2, d_h3, t["mean2"], t["rstd2"], act=True, drop_p=t["drop_p"], seed=t["seed"])
         off = eng.emb_off[id(rb)]
-        ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)      # d emb_out (unet.py:266) and conv1 bias
+        fused_cs = eng.T == 1                              # d emb_out (unet.py:266) and conv1 bias: sums of d_h2
+        d_h2, _ = eng._gn_bwd(G, t["h2"], gn2, d_h3, t["mean2"], t["rstd2"], act=True, drop_p=t["drop_p"], seed=t["seed"],
+                              colsum_out=d_emb_all[:, off:off + cout] if fused_cs else None)
+        if not fused_cs:
+            ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)
         ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
         eng._wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
         cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
@@ -533,7 +550,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         else:
             add_a, full = dout_, False
         dx1, dx2 = eng._gn_bwd(G, x, gn1, d_h1, t["mean1"], t["rstd1"], x2=x2, act=True,
-                               add_a=add_a, add_b=extra, add_a_full=full)
+                               add_a=add_a, add_b=extra, add_a_full=full, want_colsum=True)
         return dx1, dx2
 
     def attn_bwd(ctx, dout_, extra):
@@ -548,7 +565,8 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
         bias_grad(dqkv, ab.qkv.bias)
         d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1)
-        dx, _ = eng._gn_bwd(G, t["x"], gn_, d_hn, t["mean"], t["rstd"], act=False, add_a=dout_, add_b=extra)
+        dx, _ = eng._gn_bwd(G, t["x"], gn_, d_hn, t["mean"], t["rstd"], act=False, add_a=dout_, add_b=extra,
+                            want_colsum=True)
         return dx
 
     def down_bwd(ctx, dout_, extra):

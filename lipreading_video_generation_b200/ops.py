@@ -237,8 +237,9 @@ def groupnorm_fwd(x1, gamma, beta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed
 
 
 def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed=0,
-                  add_a=None, add_b=None, add_a_full=False):
-    """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (fp16, any channel pitch) are added to dx1."""
+                  add_a=None, add_b=None, add_a_full=False, colsum_out=None):
+    """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (fp16, any channel pitch) are added to dx1;
+    colsum_out (fp32 (N, >= C1) view, accumulated): per-sample pixel sums of dx1."""
     N, H, W, C1 = x1.shape
     if any(t is not None and t.dtype != F16 for t in (x1, x2, dy, add_a, add_b)):
         raise RuntimeError("groupnorm_bwd: x / dy / add_a / add_b must be fp16")
@@ -253,6 +254,7 @@ def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=T
             L.ptr(dx2), (dx2.shape[3] if dx2 is not None else 0),
             L.ptr(add_a), (add_a.stride(2) if add_a is not None else 0),
             L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
+            L.ptr(colsum_out), (colsum_out.stride(0) if colsum_out is not None else 0),
             dgamma.data_ptr(), dbeta.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "b2d_groupnorm_bwd")
     return dx1, dx2
 
