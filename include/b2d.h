@@ -320,6 +320,37 @@ typedef struct B2dAdamChunk {
 int b2d_adam_step(const B2dAdamChunk* chunks_dev, int n_chunks, double lr, double beta1, double beta2, float eps,
                   float weight_decay, double bias_correction1, double bias_correction2, void* stream);
 
+/* ------------------------------------------------------------------------
+ * Input pipeline: TalkingFaceFrameDataset.__getitem__,
+ * video-generation/dataset.py:78-136, batched, one CTA per item.
+ * ---------------------------------------------------------------------- */
+
+/* Audio window of every item (dataset.py:98,112-130).  Decoded mono tracks of all videos are concatenated in
+ * `waveforms` (fp32), video v occupying [wave_offset[v], wave_offset[v] + wave_len[v]).  Per item i: video_id[i],
+ * frame_end[i], total_frames[i], fps[i] (double), sample_rate[i].  Index arithmetic in IEEE double, bit-exact with
+ * the reference's Python floats:
+ *   idx = min(frame_end, total_frames - 1);  d = 1 / fps;
+ *   start = int(sr * max(0, (idx - 5) * d));  end = int(sr * (idx * d))        -> index_out[i] = (idx, start, end)
+ * then waveform[start:end] (clipped like a Python slice) -> high-pass biquad with biquad[i] = (b0, b1, b2, a1, a2) / a0
+ * (torchaudio.functional.highpass_biquad at 300 Hz, dataset.py:30-32; clamp to [-1, 1] after the recursion) ->
+ * (x - mean) / unbiased std (dataset.py:34-37) -> the reference's Resample(orig_freq = 1, new_freq = 16000) of which
+ * dataset.py:62-64 keeps outputs [0, 4000): out = sinc_rows (4000 x 15 fp32, filters 0..3999 of torchaudio's
+ * sinc_interp_hann kernel) applied to the zero-padded first 8 samples -> (x - mean) / sqrt(var + 1e-7)
+ * (Wav2Vec2FeatureExtractor, dataset.py:130).  out: fp32 (n_items, 4000).  A window shorter than 2 samples sets
+ * *err_flag = 1 and writes NaN (the reference's std is NaN there); one longer than b2d_audio_window_max_samples()
+ * sets 2. */
+int b2d_audio_window_max_samples(void);
+int b2d_audio_window(const float* waveforms, const int64_t* wave_offset, const int64_t* wave_len,
+                     const int32_t* video_id, const int64_t* frame_end, const int64_t* total_frames,
+                     const double* fps, const int32_t* sample_rate, const float* sinc_rows, const float* biquad,
+                     int n_items, float* out, int64_t* index_out, int* err_flag, void* stream);
+/* Frame gather + transforms (dataset.py:97-110, diffusion/train.py:70-75 without the host-side Resize): frames uint8
+ * (all videos concatenated, H, W, 3); for item i the input frame is frame 0 of its video and the output frame is
+ * index_out[i][0]; out fp32 (n_items, 2, 3, H, W) = ((v / 255) - 0.5) / 0.5, each operation rounded separately
+ * (bit-exact with ToTensor + Normalize). */
+int b2d_frame_gather(const uint8_t* frames, const int64_t* video_first_frame, const int32_t* video_id,
+                     const int64_t* index_out, int n_items, int H, int W, float* out, void* stream);
+
 /* B2D_DENOISER_ABI_BEGIN -- further denoiser kernels are declared below */
 
 #ifdef __cplusplus

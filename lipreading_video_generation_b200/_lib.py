@@ -111,6 +111,9 @@ SIGNATURES = {
     "b2d_linear_bwd": (c_int, [c_void_p] * 7 + [c_int] * 5 + [c_void_p]),
     "b2d_pack_block_elems": (c_int, []),
     "b2d_pack_conv_weights_multi": (c_int, [c_void_p, c_int, c_int, c_void_p]),
+    "b2d_audio_window_max_samples": (c_int, []),
+    "b2d_audio_window": (c_int, [c_void_p] * 10 + [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b2d_frame_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
     "b2d_adam_step": (c_int, [c_void_p, c_int, C.c_double, C.c_double, C.c_double, c_float, c_float, C.c_double, C.c_double,
                               c_void_p]),
 }

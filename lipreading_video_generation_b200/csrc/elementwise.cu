@@ -56,7 +56,9 @@ assemble_input_kernel(AssembleParams p, __half* __restrict__ out) {
     if (c < p.Cin) kind[j] = 1;
     else if (c < p.Cin + p.Cim) {
       kind[j] = 2;
-      for (int k = 0; k < p.Cc; ++k) wq[j][k] = __ldg(p.wcond + (long long)(c - p.Cin) * p.Cc + k);
+#pragma unroll
+      for (int k = 0; k < 4; ++k)                     // fixed trip count: a runtime bound put wq in local memory
+        if (k < p.Cc) wq[j][k] = __ldg(p.wcond + (long long)(c - p.Cin) * p.Cc + k);
     } else if (c < p.Cin + p.Cim + p.A) {
       kind[j] = 3;
       wq[j][0] = __ldg(p.audio + (long long)n * p.A + (c - p.Cin - p.Cim));
@@ -65,23 +67,61 @@ assemble_input_kernel(AssembleParams p, __half* __restrict__ out) {
   bool any_cond = false, any_xt = false;
 #pragma unroll
   for (int j = 0; j < 8; ++j) { any_cond |= kind[j] == 2; any_xt |= kind[j] == 1; }
-  for (int pix = blockIdx.x * rows + prow; pix < HW; pix += gridDim.x * rows) {
-    float cv[4] = {0.f, 0.f, 0.f, 0.f};
-    if (any_cond) {
-      const int h = pix / p.S, w = pix - h * p.S;
-      const int sh = nearest_src(h, p.Hc, p.S), sw = nearest_src(w, p.Wc, p.S);
-      for (int k = 0; k < p.Cc; ++k) cv[k] = __ldg(p.cond + ((long long)n * p.Cc + k) * p.Hc * p.Wc + sh * p.Wc + sw);
-    }
+  const int step = gridDim.x * rows;
+  __half* const obase = out + (long long)n * HW * p.Cpad + v * 8;
+  if (!any_cond && !any_xt) {
+    // audio / zero-padding vectors (2/3 of the tensor): the value does not depend on the pixel -- a pure store stream
     float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      float val = 0.f;
-      if (kind[j] == 3) val = wq[j][0];
-      else if (kind[j] == 2) val = fmaf(wq[j][3], cv[3], fmaf(wq[j][2], cv[2], fmaf(wq[j][1], cv[1], wq[j][0] * cv[0])));
-      else if (kind[j] == 1 && any_xt) val = __ldg(p.xt + ((long long)n * p.Cin + v * 8 + j) * HW + pix);
-      o[j] = val;
+    for (int j = 0; j < 8; ++j) o[j] = kind[j] == 3 ? wq[j][0] : 0.f;
+    uint4 u;
+    u.x = pack_f16x2(o[0], o[1]); u.y = pack_f16x2(o[2], o[3]); u.z = pack_f16x2(o[4], o[5]); u.w = pack_f16x2(o[6], o[7]);
+    for (int pix = blockIdx.x * rows + prow; pix < HW; pix += step)
+      *reinterpret_cast<uint4*>(obase + (long long)pix * p.Cpad) = u;
+    return;
+  }
+  const long long cstride = (long long)p.Hc * p.Wc;
+  const float* cbase = p.cond ? p.cond + (long long)n * p.Cc * cstride : nullptr;
+  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 4 * step) {
+    float cv[4][4], xv[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {                     // all loads of four pixels first
+      const int pix = pix0 + u * step;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) cv[u][k] = 0.f;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) xv[u][j] = 0.f;
+      if (pix < HW) {
+        if (any_cond) {
+          const int h = pix / p.S, w = pix - h * p.S;
+          const int so = nearest_src(h, p.Hc, p.S) * p.Wc + nearest_src(w, p.Wc, p.S);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            if (k < p.Cc) cv[u][k] = __ldg(cbase + k * cstride + so);
+        }
+        if (any_xt) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (kind[j] == 1) xv[u][j] = __ldg(p.xt + ((long long)n * p.Cin + v * 8 + j) * HW + pix);
+        }
+      }
     }
-    store8_fmt(out + ((long long)n * HW + pix) * p.Cpad + v * 8, o, FMT_F16);   // forward tensor
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int pix = pix0 + u * step;
+      if (pix >= HW) continue;
+      float o[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        float val = 0.f;
+        if (kind[j] == 3) val = wq[j][0];
+        else if (kind[j] == 2)
+          val = fmaf(wq[j][3], cv[u][3], fmaf(wq[j][2], cv[u][2], fmaf(wq[j][1], cv[u][1], wq[j][0] * cv[u][0])));
+        else if (kind[j] == 1) val = xv[u][j];
+        o[j] = val;
+      }
+      store8_fmt(obase + (long long)pix * p.Cpad, o, FMT_F16);   // forward tensor
+    }
   }
 }
 
