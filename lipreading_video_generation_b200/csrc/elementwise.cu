@@ -80,46 +80,44 @@ assemble_input_kernel(AssembleParams p, __half* __restrict__ out) {
       *reinterpret_cast<uint4*>(obase + (long long)pix * p.Cpad) = u;
     return;
   }
+  // general vectors (x_t and cond_conv_in channels, 9 of 32 lanes): every channel is the same arithmetic form
+  //   o_j = w_j0 cv0 + w_j1 cv1 + w_j2 cv2 + w_j3 cv3 + e_j x_j + f_j
+  // with per-lane coefficients (x_t: e = 1; audio: f = value; zero padding: all 0), so the loop body has no per-channel
+  // branches (the first version selected on kind[j] per element: ~310 instructions per pixel, issue bound at 0.98 ms).
+  float ej[8], fj[8];
+  long long xoff[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    ej[j] = kind[j] == 1 ? 1.f : 0.f;
+    fj[j] = kind[j] == 3 ? wq[j][0] : 0.f;
+    if (kind[j] != 2) { wq[j][0] = wq[j][1] = wq[j][2] = wq[j][3] = 0.f; }
+    const int cx = (v * 8 + j < p.Cin) ? v * 8 + j : p.Cin - 1;       // clamped: loaded but multiplied by e = 0
+    xoff[j] = ((long long)n * p.Cin + cx) * HW;
+  }
   const long long cstride = (long long)p.Hc * p.Wc;
-  const float* cbase = p.cond ? p.cond + (long long)n * p.Cc * cstride : nullptr;
-  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 4 * step) {
-    float cv[4][4], xv[4][8];
+  const float* cbase = p.cond ? p.cond + (long long)n * p.Cc * cstride : p.xt;
+  const int ncc = p.cond ? p.Cc : 0;
+  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 2 * step) {
+    float cv[2][4], xv[2][8];
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {                     // all loads of four pixels first
-      const int pix = pix0 + u * step;
+    for (int u = 0; u < 2; ++u) {                     // the loads of two pixels first
+      const int pix = pix0 + u * step < HW ? pix0 + u * step : pix0;
+      const int h = pix / p.S, w = pix - h * p.S;
+      const int so = nearest_src(h, p.Hc, p.S) * p.Wc + nearest_src(w, p.Wc, p.S);
 #pragma unroll
-      for (int k = 0; k < 4; ++k) cv[u][k] = 0.f;
+      for (int k = 0; k < 4; ++k) cv[u][k] = k < ncc ? __ldg(cbase + k * cstride + so) : 0.f;
 #pragma unroll
-      for (int j = 0; j < 8; ++j) xv[u][j] = 0.f;
-      if (pix < HW) {
-        if (any_cond) {
-          const int h = pix / p.S, w = pix - h * p.S;
-          const int so = nearest_src(h, p.Hc, p.S) * p.Wc + nearest_src(w, p.Wc, p.S);
-#pragma unroll
-          for (int k = 0; k < 4; ++k)
-            if (k < p.Cc) cv[u][k] = __ldg(cbase + k * cstride + so);
-        }
-        if (any_xt) {
-#pragma unroll
-          for (int j = 0; j < 8; ++j)
-            if (kind[j] == 1) xv[u][j] = __ldg(p.xt + ((long long)n * p.Cin + v * 8 + j) * HW + pix);
-        }
-      }
+      for (int j = 0; j < 8; ++j) xv[u][j] = any_xt ? __ldg(p.xt + xoff[j] + pix) : 0.f;
     }
 #pragma unroll
-    for (int u = 0; u < 4; ++u) {
+    for (int u = 0; u < 2; ++u) {
       const int pix = pix0 + u * step;
       if (pix >= HW) continue;
       float o[8];
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        float val = 0.f;
-        if (kind[j] == 3) val = wq[j][0];
-        else if (kind[j] == 2)
-          val = fmaf(wq[j][3], cv[u][3], fmaf(wq[j][2], cv[u][2], fmaf(wq[j][1], cv[u][1], wq[j][0] * cv[u][0])));
-        else if (kind[j] == 1) val = xv[u][j];
-        o[j] = val;
-      }
+      for (int j = 0; j < 8; ++j)
+        o[j] = fmaf(wq[j][3], cv[u][3], fmaf(wq[j][2], cv[u][2], fmaf(wq[j][1], cv[u][1],
+               fmaf(wq[j][0], cv[u][0], fmaf(ej[j], xv[u][j], fj[j])))));
       store8_fmt(obase + (long long)pix * p.Cpad, o, FMT_F16);   // forward tensor
     }
   }
