@@ -279,10 +279,11 @@ def main_sample(a, model, S, clips, frames, world, rank, local, device, config, 
 def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores):
     """UNetModel(dims=3) train step on whole clips: x (B, 195, T, S, S) -> eps (B, 3, T, S, S),
     MSE, backward, Adam.  Attention runs over L = T*S*S positions per clip (1,048,576 at cfg5), which the reference
-    cannot materialise; clips shard over ranks like the 2-D path."""
+    cannot materialise.  With N > 1 GPUs the ONE clip is split across the ranks (row N1, strong scaling): attention is
+    sharded by query rows (parallel.SequenceParallelAttention: all-gather of the output, all-reduce of dqkv), the rest of
+    the torso runs replicated on identical inputs, parameter gradients are averaged to keep the replicas identical."""
     import lipreading_video_generation_b200 as P
     from lipreading_video_generation_b200 import _lib as L, ops
-    assert world == 1, "train3d workloads are single-GPU for now (no gradient all-reduce is wired for them)"
     torch.manual_seed(0)
     model = P.UNetModel(image_size=S, in_channels=195, model_channels=64, out_channels=3, num_res_blocks=2,
                         attention_resolutions=(1, 2, 4), dropout=0.1, channel_mult=(1, 2, 4), dims=3)
@@ -294,7 +295,15 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
     model = model.to(device).train()
     opt = P.Adam(model.parameters(), lr=1e-2)
     crit = P.MSELoss()
-    gi = torch.Generator().manual_seed(1234 + rank)
+    reducer = sp = None
+    if world > 1:
+        from lipreading_video_generation_b200.parallel import (GradientAllReducer, SequenceParallelAttention,
+                                                               broadcast_parameters)
+        broadcast_parameters(model)
+        sp = SequenceParallelAttention(model)
+        reducer = GradientAllReducer(model)
+        config["parallelism"] = f"sp{world}: one clip, attention sharded by query rows, torso replicated"
+    gi = torch.Generator().manual_seed(1234)              # every rank works on the SAME clip
     hx = torch.randn(clips, 195, frames, S, S, generator=gi).pin_memory()
     heps = torch.randn(clips, 3, frames, S, S, generator=gi).pin_memory()
     ht = torch.randint(0, 1000, (clips,), generator=gi).pin_memory()
@@ -304,6 +313,8 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
         opt.zero_grad(set_to_none=True)
         loss = crit(model(x_, t_), eps_)
         loss.backward()
+        if reducer is not None:
+            reducer.finish()
         opt.step()
         return loss
 
@@ -349,17 +360,19 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
     for (name, meta), (t_ms, cnt) in kt_all.totals().items():
         by_class[name] = by_class.get(name, 0.0) + t_ms
     for (name, meta), (t_ms, cnt) in kt.totals().items():
-        Nn, Lq, heads, ch = meta
-        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lq * ch * heads * Nn
-        rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, tflops=flops / (t_ms / cnt) / 1e9,
-                   ms_per_step=t_ms / a.steps)
+        Nn, Lk, heads, ch = meta[:4]
+        Lq = meta[4] if len(meta) > 4 else Lk             # a sequence-parallel shard visits Lq of the Lk query rows
+        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lk * ch * heads * Nn
+        rec = dict(kernel=f"{name} L={Lk} ch={ch}" + (f" (query rows {Lq} of {Lk} per GPU)" if Lq != Lk else ""),
+                   ms_per_launch=t_ms / cnt, tflops=flops / (t_ms / cnt) / 1e9, ms_per_step=t_ms / a.steps)
         if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
             dom = rec
     h2d = sum(v.numel() * v.element_size() for v in (hx, heps, ht))
-    out = {"metric": "denoiser_train_clips_per_s", "value": round(clips * world / (ms / 1000.0), 4), "unit": "clips/s",
+    out = {"metric": "denoiser_train_clips_per_s", "value": round(clips / (ms / 1000.0), 4), "unit": "clips/s",
            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
-           "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
-           "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 4), "unit": "clips/s", "h2d_bytes_per_step": h2d,
+           "scaling": "strong" if world > 1 else "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
+           "seq_parallel_bytes_per_step": (sp.bytes_moved // (a.warmup + 2 * a.steps + 1)) if sp is not None else 0,
+           "e2e": {"value": round(clips / (ms_e2e / 1000.0), 4), "unit": "clips/s", "h2d_bytes_per_step": h2d,
                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
            "gpu_launches": int(launches),
            "roofline": {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",

@@ -296,6 +296,20 @@ int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out, int64_t l
                       int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
                       void* dqkv, int64_t lddqkv, float* delta_ws, void* stream);
 
+/* Sequence-parallel shards of the two calls above (one clip's attention over T*H*W positions
+ * split across GPUs by QUERY rows; every rank holds the full qkv, so no K/V exchange is needed).
+ *   fwd_rows: only query rows [q_row0, q_row0 + q_rows) are computed against all L keys (256-aligned, head dim 64 / 128,
+ *             L > 128); out / lse rows outside the range are left untouched -- an all-gather of `out` completes it.
+ *   bwd_rows: head dim 64, L > 128, 128-aligned rows; dqkv is fully written: Q columns = dQ for the shard's rows and
+ *             zero elsewhere, K / V columns = the shard's PARTIAL dK / dV; the sum of the shards' dqkv tensors (one
+ *             all-reduce) is the full gradient.  out / lse need to be valid on the shard's rows only... out on all rows
+ *             is not required: delta is evaluated for every row but only the shard's rows are read. */
+int b2d_attention_fwd_rows(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
+                           int q_row0, int q_rows, void* out, int64_t ldo, float* lse, void* stream);
+int b2d_attention_bwd_rows(const void* qkv, int64_t ldqkv, const void* out, int64_t ldo, const void* d_out,
+                           int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
+                           int q_row0, int q_rows, void* dqkv, int64_t lddqkv, float* delta_ws, void* stream);
+
 /* ------------------------------------------------------------------------
  * Optimiser step.
  * ---------------------------------------------------------------------- */

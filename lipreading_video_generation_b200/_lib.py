@@ -114,6 +114,10 @@ SIGNATURES = {
     "b2d_audio_window_max_samples": (c_int, []),
     "b2d_audio_window": (c_int, [c_void_p] * 10 + [c_int, c_void_p, c_void_p, c_void_p, c_void_p]),
     "b2d_frame_gather": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b2d_attention_fwd_rows": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64,
+                                       c_void_p, c_void_p]),
+    "b2d_attention_bwd_rows": (c_int, [c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int, c_int,
+                                       c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "b2d_adam_step": (c_int, [c_void_p, c_int, C.c_double, C.c_double, C.c_double, c_float, c_float, C.c_double, C.c_double,
                               c_void_p]),
 }

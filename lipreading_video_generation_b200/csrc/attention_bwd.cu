@@ -530,7 +530,7 @@ int attention_bwd2_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int
                             void* stream);   // attention_bwd2.cu
 int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
                             int new_order, const float* lse, const float* delta, float* dq_acc, void* dqkv,
-                            int64_t lddqkv, void* stream);   // attention_bwd3.cu
+                            int64_t lddqkv, int q_row0, int q_rows, void* stream);   // attention_bwd3.cu
 
 }  // namespace b2d
 
@@ -569,10 +569,34 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
   static const bool force_v2 = getenv("B2D_ATTN_BWD_V2") != nullptr;   // A/B timing of the two-kernel variant
   if (!force_v1 && !force_v2 && ch == 64 && L > 128 && L % 4 == 0)   // L % 4: 16-byte pitch of the lse / delta maps
     return attention_bwd3_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws,
-                                   delta_ws + (long long)N * heads * L, dqkv, lddqkv, stream);
+                                   delta_ws + (long long)N * heads * L, dqkv, lddqkv, 0, L, stream);
   if (!force_v1 && ch == 64 && L > 128)
     return attention_bwd2_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws, dqkv, lddqkv, stream);
   if (ch == 64) return launch_attn_bwd<64, 64, 128, 128>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
   if (ch == 128) return launch_attn_bwd<128, 128, 64, 64>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
   return launch_attn_bwd<256, 128, 64, 64>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
+}
+
+// Sequence-parallel shard of the fused single-pass backward (head dim 64): only query rows
+// [q_row0, q_row0 + q_rows) are visited.  dqkv is fully written: the Q columns hold dQ for those rows and ZERO elsewhere,
+// the K / V columns hold this shard's PARTIAL dK / dV -- the sum of the shards' dqkv tensors is the full gradient.
+extern "C" int b2d_attention_bwd_rows(const void* qkv, int64_t ldqkv, const void* out, int64_t ldo, const void* d_out,
+                                      int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
+                                      int q_row0, int q_rows, void* dqkv, int64_t lddqkv, float* delta_ws, void* stream) {
+  B2D_REQUIRE(qkv && out && d_out && lse && dqkv && delta_ws, B2D_ERR_SHAPE, "attention_bwd_rows: null pointer");
+  B2D_REQUIRE(ch == 64 && L > 128 && L % 4 == 0, B2D_ERR_SHAPE, "attention_bwd_rows: head dim 64 and L > 128 only (ch=%d L=%d)", ch, L);
+  B2D_REQUIRE(N > 0 && heads > 0 && N <= 65535 && heads <= 65535, B2D_ERR_SHAPE, "attention_bwd_rows: bad sizes");
+  B2D_REQUIRE(q_row0 >= 0 && q_rows > 0 && q_row0 % 128 == 0 && q_rows % 128 == 0 && q_row0 + q_rows <= L, B2D_ERR_SHAPE,
+              "attention_bwd_rows: rows [%d, +%d) must be 128-aligned inside L=%d", q_row0, q_rows, L);
+  B2D_REQUIRE(lddqkv % 8 == 0 && aligned16(dqkv), B2D_ERR_ALIGN, "attention_bwd_rows: dqkv rows must be 16-byte aligned");
+  {
+    const long long rows_per_warp = 2 * (32 / (ch >> 3));
+    const long long warps = ((long long)N * L * heads + rows_per_warp - 1) / rows_per_warp;
+    const long long blocks = (warps * 32 + 255) / 256;
+    attn_delta_kernel<<<(unsigned)blocks, 256, 0, (cudaStream_t)stream>>>(
+        (const __half*)out, ldo, (const __half*)d_out, lddo, N, L, heads, ch, delta_ws);
+    B2D_CHECK_LAUNCH();
+  }
+  return attention_bwd3_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws,
+                                 delta_ws + (long long)N * heads * L, dqkv, lddqkv, q_row0, q_rows, stream);
 }

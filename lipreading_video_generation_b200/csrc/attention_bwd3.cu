@@ -34,6 +34,8 @@ using namespace umma;
 
 struct AttnBwd3Params {
   int L, heads;
+  int q_row0, q_rows;  // query rows [q_row0, q_row0 + q_rows) are visited (sequence-parallel shard): dQ of those rows is
+                       // complete, dK / dV are this shard's partial sums over them
   int q_off, k_off, v_off, head_stride;
   float scale_log2, scale;
   const float* lse;    // (N, heads, L) log2 domain
@@ -97,7 +99,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
   const int warp = tid >> 5, lane = tid & 31;
   const int kv0 = blockIdx.x * 128;
   const int head = blockIdx.y, n = blockIdx.z;
-  const int n_pairs = (p.L + 127) / 128;
+  const int n_pairs = (p.q_rows + 127) / 128;
   const int n_steps = 2 * n_pairs;       // an odd trailing 64-query tile is padded with an all-masked step
   const int qc = p.q_off + head * p.head_stride, kc = p.k_off + head * p.head_stride, vc = p.v_off + head * p.head_stride;
 
@@ -127,10 +129,10 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
         mbar_wait(&empty[s], (uint32_t)(((j / AB3_ST) & 1) ^ 1));
         uint8_t* q_dst = smem + SM::ST_OFF + s * SM::STAGE;
         mbar_expect_tx(&full[s], 2 * B3_T64 + 512);
-        tma_load_3d(q_dst, &maps.qkv64, &full[s], qc, j * 64, n);            // rows past L arrive as zeros
-        tma_load_3d(q_dst + B3_T64, &maps.do64, &full[s], head * 64, j * 64, n);
-        tma_load_2d(q_dst + 2 * B3_T64, &maps.lse, &full[s], j * 64, n * p.heads + head);
-        tma_load_2d(q_dst + 2 * B3_T64 + 256, &maps.delta, &full[s], j * 64, n * p.heads + head);
+        tma_load_3d(q_dst, &maps.qkv64, &full[s], qc, p.q_row0 + j * 64, n);            // rows past L arrive as zeros
+        tma_load_3d(q_dst + B3_T64, &maps.do64, &full[s], head * 64, p.q_row0 + j * 64, n);
+        tma_load_2d(q_dst + 2 * B3_T64, &maps.lse, &full[s], p.q_row0 + j * 64, n * p.heads + head);
+        tma_load_2d(q_dst + 2 * B3_T64 + 256, &maps.delta, &full[s], p.q_row0 + j * 64, n * p.heads + head);
       }
     }
   } else if (warp == 1) {
@@ -246,7 +248,7 @@ attn_bwd_fused_kernel(const __grid_constant__ AttnBwd3Maps maps, const AttnBwd3P
     auto issue_dq = [&](int m) {
       named_bar_sync3(1 + b, 256);
       if (gt == 0) {
-        tma_reduce_add_3d(&maps.dq, stg_u32, head * 64 + b * 32, m * 128, n);   // rows past L are clipped
+        tma_reduce_add_3d(&maps.dq, stg_u32, head * 64 + b * 32, p.q_row0 + m * 128, n);   // rows past L are clipped
         tma_store_commit();
       }
     };
@@ -382,7 +384,7 @@ dq_finalize_kernel(const float* __restrict__ acc, __half* __restrict__ dqkv, lon
 // dq_acc: N*L*heads*64 floats of workspace.
 int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
                             int new_order, const float* lse, const float* delta, float* dq_acc, void* dqkv,
-                            int64_t lddqkv, void* stream) {
+                            int64_t lddqkv, int q_row0, int q_rows, void* stream) {
   static bool attr_set = false;
   if (!attr_set) {
     B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Bwd3Smem::TOTAL));
@@ -391,6 +393,7 @@ int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int
   const int ch = 64, C = heads * ch;
   AttnBwd3Params p;
   p.L = L; p.heads = heads;
+  p.q_row0 = q_row0; p.q_rows = q_rows;
   if (new_order) { p.q_off = 0; p.k_off = C; p.v_off = 2 * C; p.head_stride = ch; }
   else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }
   p.scale = 1.0f / sqrtf((float)ch);

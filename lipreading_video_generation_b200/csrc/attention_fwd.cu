@@ -283,7 +283,7 @@ static int launch_attn_fwd(const AttnMaps& maps, const AttnFwdParams& p, int N, 
 }
 
 int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order, void* out,
-                            int64_t ldo, float* lse, void* stream);   // attention_fwd2.cu
+                            int64_t ldo, float* lse, int q_row0, int q_rows, void* stream);   // attention_fwd2.cu
 
 }  // namespace b2d
 
@@ -299,7 +299,7 @@ extern "C" int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, i
   // two-query-tile kernel for the large layers; B2D_ATTN_FWD_V1=1 forces the single-tile variant (A/B timing)
   static const bool force_v1 = getenv("B2D_ATTN_FWD_V1") != nullptr;
   if (!force_v1 && (ch == 64 || ch == 128) && L > 128)
-    return attention_fwd2_dispatch(qkv, ldqkv, N, L, heads, ch, new_order, out, ldo, lse, stream);
+    return attention_fwd2_dispatch(qkv, ldqkv, N, L, heads, ch, new_order, out, ldo, lse, 0, L, stream);
   const int C = heads * ch;
   AttnFwdParams p;
   p.L = L; p.heads = heads;
@@ -320,4 +320,17 @@ extern "C" int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, i
   if (ch == 64) return launch_attn_fwd<64, 128>(maps, p, N, stream);
   if (ch == 128) return launch_attn_fwd<128, 128>(maps, p, N, stream);
   return launch_attn_fwd<256, 64>(maps, p, N, stream);
+}
+
+// Sequence-parallel shard: only query rows [q_row0, q_row0 + q_rows) are computed, against all L
+// keys; out / lse rows outside the range are not touched.
+extern "C" int b2d_attention_fwd_rows(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
+                                      int q_row0, int q_rows, void* out, int64_t ldo, float* lse, void* stream) {
+  B2D_REQUIRE(qkv && out, B2D_ERR_SHAPE, "attention_fwd_rows: null pointer");
+  B2D_REQUIRE(N > 0 && L > 128 && heads > 0 && N <= 65535 && heads <= 65535, B2D_ERR_SHAPE, "attention_fwd_rows: bad sizes");
+  B2D_REQUIRE(ch == 64 || ch == 128, B2D_ERR_SHAPE, "attention_fwd_rows: head dim %d not in {64,128}", ch);
+  B2D_REQUIRE(q_row0 >= 0 && q_rows > 0 && q_row0 % 256 == 0 && q_rows % 256 == 0 && q_row0 + q_rows <= L, B2D_ERR_SHAPE,
+              "attention_fwd_rows: rows [%d, +%d) must be 256-aligned inside L=%d", q_row0, q_rows, L);
+  B2D_REQUIRE(ldo % 8 == 0 && aligned16(out), B2D_ERR_ALIGN, "attention_fwd_rows: output must be 16-byte aligned rows");
+  return attention_fwd2_dispatch(qkv, ldqkv, N, L, heads, ch, new_order, out, ldo, lse, q_row0, q_rows, stream);
 }

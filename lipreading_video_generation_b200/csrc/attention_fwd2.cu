@@ -21,6 +21,7 @@ using namespace umma;
 
 struct AttnFwd2Params {
   int L, heads;
+  int q_row0, q_rows;   // query rows [q_row0, q_row0 + q_rows) are computed (sequence-parallel shard); keys: all L
   int q_off, k_off, v_off, head_stride;
   float scale_log2;
   __half* out; long long ldo;
@@ -75,7 +76,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * 256;
+  const int q0 = p.q_row0 + blockIdx.x * 256;
   const int head = blockIdx.y;
   const int n = blockIdx.z;
   const int n_kv = (p.L + BKV - 1) / BKV;
@@ -306,7 +307,7 @@ static int launch_attn_fwd2(const void* qkv, int64_t ldqkv, int N, int C3, const
   if (rc) return rc;
   rc = make_tmap_16b(&maps.kv, qkv, 3, dims, str, boxkv);
   if (rc) return rc;
-  dim3 grid((unsigned)((p.L + 255) / 256), (unsigned)p.heads, (unsigned)N);
+  dim3 grid((unsigned)((p.q_rows + 255) / 256), (unsigned)p.heads, (unsigned)N);
   attn_fwd2_kernel<D, BKV><<<grid, ATT2_THREADS, Cfg::SMEM_TOTAL, (cudaStream_t)stream>>>(maps, p);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
@@ -314,10 +315,11 @@ static int launch_attn_fwd2(const void* qkv, int64_t ldqkv, int N, int C3, const
 
 // called by b2d_attention_fwd (attention_fwd.cu) for ch in {64, 128} and L > 128
 int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order, void* out,
-                            int64_t ldo, float* lse, void* stream) {
+                            int64_t ldo, float* lse, int q_row0, int q_rows, void* stream) {
   const int C = heads * ch;
   AttnFwd2Params p;
   p.L = L; p.heads = heads;
+  p.q_row0 = q_row0; p.q_rows = q_rows;
   if (new_order) { p.q_off = 0; p.k_off = C; p.v_off = 2 * C; p.head_stride = ch; }          // unet.py:392
   else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }    // unet.py:359
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)ch);

@@ -49,6 +49,7 @@ class DenoiserEngine:
         self._pack_table = None
         self._weights_maybe_stale = False
         self._colsums = {}
+        self.seq_parallel = None              # parallel.SequenceParallelAttention, when one clip is split across GPUs
         self._step_seed = 0
         # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
         self._grad_layout = None
@@ -334,13 +335,18 @@ class DenoiserEngine:
         C_ = ab.channels
         hn, mean, rstd = self._gn_fwd(x, gn, act=False)
         qkv = ops.conv2d(hn, self.w_fwd(ab.qkv), 3 * C_, 1, 1, bias=ab.qkv.bias.detach())
-        a, lse = ops.attention_fwd(self._fold(qkv), ab.num_heads, ab.use_new_attention_order)   # L = T*H*W (unet.py:312)
+        fq = self._fold(qkv)
+        sp = self.seq_parallel
+        rows = sp.rows(fq.shape[0], fq.shape[1] * fq.shape[2], C_ // ab.num_heads, ab.num_heads) if sp is not None else None
+        a, lse = ops.attention_fwd(fq, ab.num_heads, ab.use_new_attention_order, rows=rows)   # L = T*H*W (unet.py:312)
+        if rows is not None:
+            sp.all_gather_rows(a, rows)                   # every rank needs the full attention output
         a = self._unfold(a, qkv)
         out = ops.conv2d(a, self.w_fwd(ab.proj_out), C_, 1, 1, bias=ab.proj_out.bias.detach(), residual=x)
         ctx = None
         if train:
             ctx = _Ctx("attn", ab)
-            ctx.t.update(x=x, hn=hn, qkv=qkv, a=a, lse=lse, mean=mean, rstd=rstd)
+            ctx.t.update(x=x, hn=hn, qkv=qkv, a=a, lse=lse, mean=mean, rstd=rstd, rows=rows)
         return out, ctx
 
     # ------------------------------------------------------------------ gradient storage
@@ -560,8 +566,15 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         ops.conv2d_wgrad(t["a"], dout_, G.g(ab.proj_out.weight), 1, 1)
         bias_grad(dout_, ab.proj_out.bias)
         d_a = ops.conv2d(dout_, eng.w_dgrad(ab.proj_out), C_, 1, 1)
-        dqkv = eng._unfold(ops.attention_bwd(eng._fold(t["qkv"]), eng._fold(t["a"]), eng._fold(d_a), t["lse"], ab.num_heads,
-                                             ab.use_new_attention_order), t["qkv"])
+        rows = t.get("rows")
+        bwd_rows = rows if (rows is not None and C_ // ab.num_heads == 64) else None    # fused single-pass kernel only
+        if rows is not None and bwd_rows is None:
+            eng.seq_parallel.all_gather_lse(t["lse"], rows)   # un-sharded backward variant: it reads every row's lse
+        dqkv = ops.attention_bwd(eng._fold(t["qkv"]), eng._fold(t["a"]), eng._fold(d_a), t["lse"], ab.num_heads,
+                                 ab.use_new_attention_order, rows=bwd_rows)
+        if bwd_rows is not None:
+            eng.seq_parallel.all_reduce_sum(dqkv)         # dQ rows from their owner, dK / dV summed over the shards
+        dqkv = eng._unfold(dqkv, t["qkv"])
         ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
         bias_grad(dqkv, ab.qkv.bias)
         d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1)

@@ -259,8 +259,9 @@ def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=T
     return dx1, dx2
 
 
-def attention_fwd(qkv, heads, new_order=False):
-    """qkv (N,H,W,3C) fp16 -> (out (N,H,W,C) fp16, lse (N,heads,L) fp32)."""
+def attention_fwd(qkv, heads, new_order=False, rows=None):
+    """qkv (N,H,W,3C) fp16 -> (out (N,H,W,C) fp16, lse (N,heads,L) fp32).  rows = (q_row0, q_rows): sequence-parallel
+    shard -- only those query rows of out / lse are written (the caller all-gathers `out`)."""
     if qkv.dtype != F16:
         raise RuntimeError("attention_fwd: qkv must be fp16")
     N, H, W, C3 = qkv.shape
@@ -268,14 +269,21 @@ def attention_fwd(qkv, heads, new_order=False):
     ch = Cc // heads
     out = torch.empty(N, H, W, Cc, device=qkv.device, dtype=F16)
     lse = torch.empty(N, heads, H * W, device=qkv.device, dtype=torch.float32)
+    if rows is not None:
+        with _timed("attention_fwd", (N, H * W, heads, ch, rows[1])):
+            L.check(L.lib().b2d_attention_fwd_rows(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
+                                                   int(rows[0]), int(rows[1]), out.data_ptr(), Cc, lse.data_ptr(), _s()),
+                    "b2d_attention_fwd_rows")
+        return out, lse
     with _timed("attention_fwd", (N, H * W, heads, ch)):
         L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
                                           out.data_ptr(), Cc, lse.data_ptr(), _s()), "b2d_attention_fwd")
     return out, lse
 
 
-def attention_bwd(qkv, out, d_out, lse, heads, new_order=False):
-    """qkv, out, d_out fp16 -> dqkv (N,H,W,3C) fp16."""
+def attention_bwd(qkv, out, d_out, lse, heads, new_order=False, rows=None):
+    """qkv, out, d_out fp16 -> dqkv (N,H,W,3C) fp16.  rows = (q_row0, q_rows): this shard's partial dqkv (sum the
+    shards' tensors for the full gradient)."""
     if qkv.dtype != F16 or out.dtype != F16 or d_out.dtype != F16:
         raise RuntimeError("attention_bwd: qkv / out / d_out must be fp16")
     N, H, W, C3 = qkv.shape
@@ -284,6 +292,13 @@ def attention_bwd(qkv, out, d_out, lse, heads, new_order=False):
     dqkv = torch.empty(N, H, W, C3, device=qkv.device, dtype=F16)
     delta = torch.empty(int(L.lib().b2d_attention_bwd_ws_floats(N, H * W, heads, ch)), device=qkv.device,
                         dtype=torch.float32)
+    if rows is not None:
+        with _timed("attention_bwd", (N, H * W, heads, ch, rows[1])):
+            L.check(L.lib().b2d_attention_bwd_rows(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2),
+                                                   d_out.data_ptr(), d_out.stride(2), lse.data_ptr(), N, H * W, heads, ch,
+                                                   int(new_order), int(rows[0]), int(rows[1]), dqkv.data_ptr(), C3,
+                                                   delta.data_ptr(), _s()), "b2d_attention_bwd_rows")
+        return dqkv
     with _timed("attention_bwd", (N, H * W, heads, ch)):
         L.check(L.lib().b2d_attention_bwd(qkv.data_ptr(), qkv.stride(2), out.data_ptr(), out.stride(2),
                                           d_out.data_ptr(), d_out.stride(2), lse.data_ptr(), N, H * W, heads, ch,

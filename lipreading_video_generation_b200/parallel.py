@@ -99,6 +99,70 @@ class GradientAllReducer:
             off += g.numel()
 
 
+def shard_rows(L: int, rank: int, world: int, align: int = 256):
+    """Query rows [q_row0, q_row0 + q_rows) of an attention over L positions owned by `rank`: equal `align`-aligned
+    shares, or None when L does not split that way (the layer then runs replicated)."""
+    if world <= 1 or L % (world * align) != 0:
+        return None
+    per = L // world
+    return rank * per, per
+
+
+class SequenceParallelAttention:
+    """ONE clip (UNetModel(dims=3): attention over L = T*H*W positions, 1,048,576 at cfg5) split
+    across the GPUs of a box.  Attention is >= 99 % of that step's FLOPs, so everything else (convolutions, GroupNorm,
+    weight gradients) runs replicated on every rank with identical inputs and only the attention core is sharded, by
+    QUERY rows: each rank already holds the full qkv tensor, so there is no K/V exchange --
+      forward : rank r computes out[q rows of r] against all keys; one all-gather of `out` (L x C fp16);
+      backward: rank r visits its query rows only (b2d_attention_bwd_rows): dQ for its rows, partial dK / dV; one
+                all-reduce(sum) of dqkv (L x 3C fp16) yields the full gradient on every rank.
+    Layers whose L does not split into 256-aligned shares, or whose head dim has no row-range kernel, run replicated.
+    Parameter gradients are identical on all ranks up to atomic-order rounding; `GradientAllReducer` (AVG) keeps the
+    replicas bit-identical."""
+
+    def __init__(self, model, group=None, min_rows: int = 4096):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.min_rows = min_rows
+        self.bytes_moved = 0
+        model.engine().seq_parallel = self if self.world > 1 else None
+
+    def rows(self, n_samples: int, L: int, head_dim: int, heads: int = 1):
+        """(q_row0, q_rows) of this rank, or None when the layer runs replicated: one sample (the row shares must be
+        contiguous for the in-place all-gather), a head dim with a row-range kernel, enough rows to be worth it; head
+        dim 128 (un-sharded backward, which reads every row's lse) additionally needs a single head."""
+        if n_samples != 1 or head_dim not in (64, 128) or L < self.min_rows * self.world:
+            return None
+        if head_dim == 128 and heads != 1:
+            return None
+        return shard_rows(L, self.rank, self.world)
+
+    def _gather(self, flat, rows):
+        mine = flat[rows[0]:rows[0] + rows[1]]
+        if flat.is_cuda:
+            dist.all_gather_into_tensor(flat, mine, group=self.group)      # in place: the input is this rank's slice
+        else:                                                               # gloo (CPU tests)
+            parts = [torch.empty_like(mine) for _ in range(self.world)]
+            dist.all_gather(parts, mine.clone(), group=self.group)
+            for r, part in enumerate(parts):
+                flat[r * rows[1]:(r + 1) * rows[1]].copy_(part)
+        self.bytes_moved += flat.numel() * flat.element_size()
+
+    def all_gather_rows(self, out, rows):
+        """out (1, H', W, C) contiguous with only this rank's rows valid -> all rows valid (in place)."""
+        self._gather(out.view(-1, out.shape[-1]), rows)
+
+    def all_gather_lse(self, lse, rows):
+        if lse.shape[0] * lse.shape[1] != 1:
+            raise RuntimeError("sequence-parallel lse gather expects one sample and one head")
+        self._gather(lse.view(-1), rows)
+
+    def all_reduce_sum(self, t):
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        self.bytes_moved += t.numel() * t.element_size()
+
+
 def broadcast_parameters(model, src: int = 0, group=None):
     """Identical weights on every rank before the first step."""
     if not dist.is_initialized() or dist.get_world_size(group) == 1:

@@ -608,3 +608,45 @@ def test_spec_augment_restatement_equals_stock_masking_and_does_not_synchronise(
     assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
     assert rel(outs[1][2], outs[0][2]) <= 1e-5            # d masked_spec_embed: a sum over masked frames, order differs
     assert (outs[0][0] != h0).any()                        # the mask did something
+
+
+# ----------------------------------------------------------------------------- sequence-parallel attention shards (row N1)
+@pytest.mark.parametrize("ch,L", [(64, 1024), (128, 512)])
+def test_attention_row_shards_reassemble_to_the_unsharded_result(ch, L):
+    """b2d_attention_fwd_rows / b2d_attention_bwd_rows on ONE GPU: the shards of a 2- and 4-way query split, put
+    together the way parallel.SequenceParallelAttention does over NCCL (rows of `out` gathered, dqkv tensors summed),
+    equal the un-sharded kernels: forward rows bit-exact (same kernel, same tiles), backward <= 2e-3 (fp16 partial
+    dK / dV are rounded per shard before the sum)."""
+    from lipreading_video_generation_b200 import ops
+    g = gen(11)
+    qkv = (torch.randn(1, L // 32, 32, 3 * ch, generator=g) * 0.7).half().cuda()
+    d_out = (torch.randn(1, L // 32, 32, ch, generator=g) * 0.5).half().cuda()
+    out, lse = ops.attention_fwd(qkv, 1)
+    dqkv = ops.attention_bwd(qkv, out, d_out, lse, 1)
+    for world in (2, 4):
+        per = L // world
+        if per % 256:
+            continue
+        o_acc = torch.zeros_like(out); l_acc = torch.zeros_like(lse)
+        d_acc = torch.zeros_like(dqkv, dtype=torch.float32)
+        for r in range(world):
+            rows = (r * per, per)
+            o_r, l_r = ops.attention_fwd(qkv, 1, rows=rows)
+            o_acc.view(-1, ch)[rows[0]:rows[0] + per] = o_r.view(-1, ch)[rows[0]:rows[0] + per]
+            l_acc.view(-1)[rows[0]:rows[0] + per] = l_r.view(-1)[rows[0]:rows[0] + per]
+            if ch == 64:
+                # the shard only has ITS rows of out / lse: poison the others to prove they are not read
+                o_p = torch.full_like(out, float("nan")); l_p = torch.full_like(lse, float("nan"))
+                o_p.view(-1, ch)[rows[0]:rows[0] + per] = o_r.view(-1, ch)[rows[0]:rows[0] + per]
+                l_p.view(-1)[rows[0]:rows[0] + per] = l_r.view(-1)[rows[0]:rows[0] + per]
+                d_r = ops.attention_bwd(qkv, o_p, d_out, l_p, 1, rows=rows)
+                q_cols = d_r.view(-1, 3 * ch)[:, :ch]
+                outside = torch.ones(L, dtype=torch.bool, device="cuda"); outside[rows[0]:rows[0] + per] = False
+                assert (q_cols[outside] == 0).all()          # dQ of rows it does not own: exactly zero
+                d_acc += d_r.float()
+        assert torch.equal(o_acc, out) and torch.equal(l_acc, lse)
+        if ch == 64:
+            assert torch.isfinite(d_acc).all()
+            assert rel(d_acc, dqkv) <= 2e-3
+    with pytest.raises(RuntimeError):
+        ops.attention_fwd(qkv, 1, rows=(128, 256))          # not 256-aligned
