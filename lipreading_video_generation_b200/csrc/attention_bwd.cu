@@ -19,6 +19,7 @@ using namespace umma;
 
 struct AttnBwdParams {
   int L, heads;
+  int q_row0, q_rows;  // query rows visited (sequence-parallel shard; 0, L otherwise)
   int q_off, k_off, v_off, head_stride;
   float scale_log2;   // log2(e)/sqrt(ch)
   float scale;        // 1/sqrt(ch)
@@ -128,7 +129,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
   const int half = blockIdx.x % HALVES;
   const int kv0 = (blockIdx.x / HALVES) * 128;
   const int head = blockIdx.y, n = blockIdx.z;
-  const int n_q = (p.L + BQ - 1) / BQ;
+  const int n_q = (p.q_rows + BQ - 1) / BQ;
   const int qc = p.q_off + head * p.head_stride, kc = p.k_off + head * p.head_stride, vc = p.v_off + head * p.head_stride;
 
   if (threadIdx.x == 0) {
@@ -159,8 +160,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
         mbar_expect_tx(&full[s], Cfg::STAGE_BYTES);
 #pragma unroll
         for (int b = 0; b < D / 64; ++b) {
-          tma_load_3d(q_dst + b * (BQ * 128), &maps.qkvT, &full[s], qc + b * 64, j * BQ, n);
-          tma_load_3d(do_dst + b * (BQ * 128), &maps.doT, &full[s], head * D + b * 64, j * BQ, n);
+          tma_load_3d(q_dst + b * (BQ * 128), &maps.qkvT, &full[s], qc + b * 64, p.q_row0 + j * BQ, n);
+          tma_load_3d(do_dst + b * (BQ * 128), &maps.doT, &full[s], head * D + b * 64, p.q_row0 + j * BQ, n);
         }
       }
     }
@@ -229,7 +230,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
       float* ls = lse_s + (j & 1) * BQ;
       float* ds = del_s + (j & 1) * BQ;
       if (ct < BQ) {
-        const int qi = j * BQ + ct;
+        const int qi = p.q_row0 + j * BQ + ct;
         ls[ct] = qi < p.L ? __ldg(lse_g + qi) : INFINITY;
         ds[ct] = qi < p.L ? __ldg(del_g + qi) : 0.f;
       }
@@ -335,7 +336,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
   uint32_t* tmem_slot = (uint32_t*)(acc_done + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int q0 = blockIdx.x * 128;
+  const int q0 = p.q_row0 + blockIdx.x * 128;
   const int head = blockIdx.y, n = blockIdx.z;
   const int n_kv = (p.L + BKV - 1) / BKV;
   const int qc = p.q_off + head * p.head_stride, kc = p.k_off + head * p.head_stride, vc = p.v_off + head * p.head_stride;
@@ -518,7 +519,7 @@ static int launch_attn_bwd(const void* qkv, int64_t ldqkv, const void* d_o, int6
     if ((rc = make_tmap_16b(&m.qkvT, qkv, 3, dims, str, boxT))) return rc;
     if ((rc = make_tmap_16b(&m.doR, d_o, 3, ddims, dstr, box128))) return rc;
     m.doT = m.doR;
-    dim3 grid((unsigned)((L + 127) / 128), (unsigned)heads, (unsigned)N);
+    dim3 grid((unsigned)((p.q_rows + 127) / 128), (unsigned)heads, (unsigned)N);
     attn_bwd_dq_kernel<D, BKV><<<grid, AB_THREADS, CB::SMEM_TOTAL, st>>>(m, p);
     B2D_CHECK_LAUNCH();
   }
@@ -551,6 +552,7 @@ extern "C" int b2d_attention_bwd(const void* qkv, int64_t ldqkv, const void* out
   const int C = heads * ch;
   AttnBwdParams p;
   p.L = L; p.heads = heads;
+  p.q_row0 = 0; p.q_rows = L;
   if (new_order) { p.q_off = 0; p.k_off = C; p.v_off = 2 * C; p.head_stride = ch; }
   else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }
   p.scale = 1.0f / sqrtf((float)ch);
@@ -584,7 +586,8 @@ extern "C" int b2d_attention_bwd_rows(const void* qkv, int64_t ldqkv, const void
                                       int64_t lddo, const float* lse, int N, int L, int heads, int ch, int new_order,
                                       int q_row0, int q_rows, void* dqkv, int64_t lddqkv, float* delta_ws, void* stream) {
   B2D_REQUIRE(qkv && out && d_out && lse && dqkv && delta_ws, B2D_ERR_SHAPE, "attention_bwd_rows: null pointer");
-  B2D_REQUIRE(ch == 64 && L > 128 && L % 4 == 0, B2D_ERR_SHAPE, "attention_bwd_rows: head dim 64 and L > 128 only (ch=%d L=%d)", ch, L);
+  B2D_REQUIRE((ch == 64 && L > 128 && L % 4 == 0) || ch == 128 || ch == 256, B2D_ERR_SHAPE,
+              "attention_bwd_rows: head dim 64 (L > 128) / 128 / 256 only (ch=%d L=%d)", ch, L);
   B2D_REQUIRE(N > 0 && heads > 0 && N <= 65535 && heads <= 65535, B2D_ERR_SHAPE, "attention_bwd_rows: bad sizes");
   B2D_REQUIRE(q_row0 >= 0 && q_rows > 0 && q_row0 % 128 == 0 && q_rows % 128 == 0 && q_row0 + q_rows <= L, B2D_ERR_SHAPE,
               "attention_bwd_rows: rows [%d, +%d) must be 128-aligned inside L=%d", q_row0, q_rows, L);
@@ -597,6 +600,22 @@ extern "C" int b2d_attention_bwd_rows(const void* qkv, int64_t ldqkv, const void
         (const __half*)out, ldo, (const __half*)d_out, lddo, N, L, heads, ch, delta_ws);
     B2D_CHECK_LAUNCH();
   }
-  return attention_bwd3_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws,
-                                 delta_ws + (long long)N * heads * L, dqkv, lddqkv, q_row0, q_rows, stream);
+  if (ch == 64)
+    return attention_bwd3_dispatch(qkv, ldqkv, d_out, lddo, N, L, heads, new_order, lse, delta_ws,
+                                   delta_ws + (long long)N * heads * L, dqkv, lddqkv, q_row0, q_rows, stream);
+  // head dim 128 / 256: the two-kernel variant -- dK / dV kernel over the shard's query tiles, dQ kernel on the shard's
+  // query tiles only; the Q columns of the other rows are zeroed first
+  B2D_CHECK_CUDA(cudaMemsetAsync(dqkv, 0, (size_t)N * L * lddqkv * 2, (cudaStream_t)stream));
+  const int C = heads * ch;
+  AttnBwdParams p;
+  p.L = L; p.heads = heads;
+  p.q_row0 = q_row0; p.q_rows = q_rows;
+  if (new_order) { p.q_off = 0; p.k_off = C; p.v_off = 2 * C; p.head_stride = ch; }
+  else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }
+  p.scale = 1.0f / sqrtf((float)ch);
+  p.scale_log2 = 1.4426950408889634f * p.scale;
+  p.lse = lse; p.delta = delta_ws;
+  p.dqkv = (__half*)dqkv; p.lddqkv = lddqkv;
+  if (ch == 128) return launch_attn_bwd<128, 128, 64, 64>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
+  return launch_attn_bwd<256, 128, 64, 64>(qkv, ldqkv, d_out, lddo, N, L, heads, p, stream);
 }

@@ -566,13 +566,10 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         ops.conv2d_wgrad(t["a"], dout_, G.g(ab.proj_out.weight), 1, 1)
         bias_grad(dout_, ab.proj_out.bias)
         d_a = ops.conv2d(dout_, eng.w_dgrad(ab.proj_out), C_, 1, 1)
-        rows = t.get("rows")
-        bwd_rows = rows if (rows is not None and C_ // ab.num_heads == 64) else None    # fused single-pass kernel only
-        if rows is not None and bwd_rows is None:
-            eng.seq_parallel.all_gather_lse(t["lse"], rows)   # un-sharded backward variant: it reads every row's lse
+        rows = t.get("rows")                              # sequence-parallel shard: this rank's query rows
         dqkv = ops.attention_bwd(eng._fold(t["qkv"]), eng._fold(t["a"]), eng._fold(d_a), t["lse"], ab.num_heads,
-                                 ab.use_new_attention_order, rows=bwd_rows)
-        if bwd_rows is not None:
+                                 ab.use_new_attention_order, rows=rows)
+        if rows is not None:
             eng.seq_parallel.all_reduce_sum(dqkv)         # dQ rows from their owner, dK / dV summed over the shards
         dqkv = eng._unfold(dqkv, t["qkv"])
         ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)

@@ -116,7 +116,7 @@ class SequenceParallelAttention:
       forward : rank r computes out[q rows of r] against all keys; one all-gather of `out` (L x C fp16);
       backward: rank r visits its query rows only (b2d_attention_bwd_rows): dQ for its rows, partial dK / dV; one
                 all-reduce(sum) of dqkv (L x 3C fp16) yields the full gradient on every rank.
-    Layers whose L does not split into 256-aligned shares, or whose head dim has no row-range kernel, run replicated.
+    Layers whose L does not split into 256-aligned shares, or with head dim 256 (0.3 % of the FLOPs), run replicated.
     Parameter gradients are identical on all ranks up to atomic-order rounding; `GradientAllReducer` (AVG) keeps the
     replicas bit-identical."""
 
@@ -130,11 +130,9 @@ class SequenceParallelAttention:
 
     def rows(self, n_samples: int, L: int, head_dim: int, heads: int = 1):
         """(q_row0, q_rows) of this rank, or None when the layer runs replicated: one sample (the row shares must be
-        contiguous for the in-place all-gather), a head dim with a row-range kernel, enough rows to be worth it; head
-        dim 128 (un-sharded backward, which reads every row's lse) additionally needs a single head."""
+        contiguous for the in-place all-gather), a head dim whose forward has a row-range kernel (64, 128), enough
+        rows to be worth two collectives."""
         if n_samples != 1 or head_dim not in (64, 128) or L < self.min_rows * self.world:
-            return None
-        if head_dim == 128 and heads != 1:
             return None
         return shard_rows(L, self.rank, self.world)
 
