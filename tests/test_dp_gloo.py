@@ -108,3 +108,68 @@ def test_gradient_all_reducer_world2_gloo():
     for p in procs:
         p.join(timeout=60)
     assert all(r[1] == "ok" for r in res), res
+
+
+# ----------------------------------------------------------------------------- sequence-parallel attention (row N1)
+def test_shard_rows_gives_equal_aligned_query_shares():
+    from lipreading_video_generation_b200.parallel import shard_rows
+    assert [shard_rows(1048576, r, 8) for r in (0, 7)] == [(0, 131072), (917504, 131072)]   # cfg5, 8 GPUs
+    assert [shard_rows(4096, r, 2) for r in range(2)] == [(0, 2048), (2048, 2048)]
+    assert shard_rows(4096, 0, 1) is None                  # single rank: replicated path
+    assert shard_rows(1024, 0, 8) is None                  # 128 rows per rank: not 256-aligned -> layer runs replicated
+    assert shard_rows(768, 0, 2) is None
+
+
+def _sp_worker(rank, world, port, q):
+    try:
+        sys.path.insert(0, ROOT)
+        os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+        import torch.distributed as dist
+        dist.init_process_group("gloo", rank=rank, world_size=world)
+        import lipreading_video_generation_b200 as P
+        from lipreading_video_generation_b200.parallel import SequenceParallelAttention
+        m = P.UNetModel(32, 64, 64, 3, 1, (1,), channel_mult=(1,), dims=3)
+        sp = SequenceParallelAttention(m, min_rows=256)
+        assert m.engine().seq_parallel is sp
+        L_, C_ = 1024, 8
+        assert sp.rows(1, L_, 64) == (rank * 512, 512) and sp.rows(1, L_, 128) == (rank * 512, 512)
+        assert sp.rows(2, L_, 64) is None                  # two samples: shares are not contiguous
+        assert sp.rows(1, L_, 256) is None                 # no row-range forward kernel for head dim 256
+        assert sp.rows(1, 256, 64) is None                 # too short to be worth two collectives
+        # forward contract: each rank fills ITS rows of `out`, the gather completes it in place
+        full = torch.arange(L_ * C_, dtype=torch.float32).view(1, 32, 32, C_)
+        out = torch.full_like(full, -1.0)
+        r0, n = sp.rows(1, L_, 64)
+        out.view(-1, C_)[r0:r0 + n] = full.view(-1, C_)[r0:r0 + n]
+        sp.all_gather_rows(out, (r0, n))
+        assert torch.equal(out, full)
+        lse = torch.full((1, 1, L_), -1.0)
+        lse.view(-1)[r0:r0 + n] = torch.arange(r0, r0 + n, dtype=torch.float32)
+        sp.all_gather_lse(lse, (r0, n))
+        assert torch.equal(lse.view(-1), torch.arange(L_, dtype=torch.float32))
+        # backward contract: dQ rows only from their owner (zero elsewhere), dK / dV partial everywhere -> one sum
+        dqkv = torch.zeros(1, 32, 32, 3 * C_)
+        dqkv.view(-1, 3 * C_)[r0:r0 + n, :C_] = 5.0
+        dqkv.view(-1, 3 * C_)[:, C_:] = float(rank + 1)
+        sp.all_reduce_sum(dqkv)
+        assert (dqkv.view(-1, 3 * C_)[:, :C_] == 5.0).all() and (dqkv.view(-1, 3 * C_)[:, C_:] == 3.0).all()
+        assert sp.bytes_moved > 0
+        dist.destroy_process_group()
+        q.put((rank, "ok"))
+    except Exception as e:  # noqa: BLE001
+        import traceback
+        q.put((rank, traceback.format_exc() + repr(e)))
+
+
+def test_sequence_parallel_attention_contract_world2_gloo():
+    world = 2
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_sp_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=240) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+    assert all(r[1] == "ok" for r in res), res
