@@ -158,6 +158,10 @@ class SequenceParallelAttention:
 
     def all_reduce_sum(self, t):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        if t.dtype == torch.float16:
+            # the kernels store gradients with saturating conversions (+-65504); the fp16 sum of the shards' partial
+            # dK / dV can pass that and become inf where the un-sharded kernel would have saturated: do the same here
+            t.clamp_(-65504.0, 65504.0)
         self.bytes_moved += t.numel() * t.element_size()
 
 
