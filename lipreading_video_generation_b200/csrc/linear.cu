@@ -33,11 +33,14 @@ gemm_f32_kernel(GemmF32 g) {
   const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
   float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
   for (int k0 = 0; k0 < g.K; k0 += 32) {
+    // consecutive threads walk whichever index of the operand is contiguous in memory (the transposed operands of
+    // the forward (w[n][k]) and of the weight gradient (dy[m][n] as A(n, m)) were read with a stride of a full row)
+    const bool a_k_fast = g.sak == 1, b_n_fast = (g.sbn == 1) || !g.b;
     for (int i = threadIdx.x; i < 1024; i += 256) {
       const int r = i >> 5, cidx = i & 31;
-      // A tile: As[r = m][cidx = k]
       {
-        const int m = m0 + r, k = k0 + cidx;
+        const int mi = a_k_fast ? r : cidx, ki = a_k_fast ? cidx : r;
+        const int m = m0 + mi, k = k0 + ki;
         float v = 0.f;
         if (m < g.M && k < g.K) {
           const long long off = (long long)m * g.sam + (long long)k * g.sak;
@@ -45,17 +48,17 @@ gemm_f32_kernel(GemmF32 g) {
           if (g.amask) v = g.amask[off] > 0.f ? v : 0.f;
           if (g.act_a) v = silu_exact(v);
         }
-        As[r][cidx] = v;
+        As[mi][ki] = v;
       }
-      // B tile: Bs[r = k][cidx = n]
       {
-        const int k = k0 + r, n = n0 + cidx;
+        const int ki = b_n_fast ? r : cidx, ni = b_n_fast ? cidx : r;
+        const int k = k0 + ki, n = n0 + ni;
         float v = 0.f;
         if (k < g.K && n < g.N) {
           v = g.b ? g.b[(long long)k * g.sbk + (long long)n * g.sbn] : 1.0f;
           if (g.act_b) v = silu_exact(v);
         }
-        Bs[r][cidx] = v;
+        Bs[ki][ni] = v;
       }
     }
     __syncthreads();
