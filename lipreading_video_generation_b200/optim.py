@@ -88,6 +88,8 @@ class Adam(torch.optim.Optimizer):
                     st["step"] = torch.tensor(0.0, dtype=torch.float32)
                     st["exp_avg"] = torch.zeros_like(p, memory_format=torch.preserve_format)
                     st["exp_avg_sq"] = torch.zeros_like(p, memory_format=torch.preserve_format)
+                if st["step"].is_cuda:              # state loaded from torch's fused / capturable Adam: keep it on the host
+                    st["step"] = st["step"].detach().to("cpu", torch.float32)
                 steps.append(st["step"])
                 k = int(st["step"]) + 1
                 by_step.setdefault((k, p.device), []).append(

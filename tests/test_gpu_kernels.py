@@ -517,6 +517,18 @@ def test_adam_multi_tensor_matches_torch_adam(wd):
     assert set(sd["state"][0]) == {"step", "exp_avg", "exp_avg_sq"} and float(sd["state"][0]["step"]) == 5.0
     o_ref2 = torch.optim.Adam([torch.nn.Parameter(w.detach().clone()) for w in ours], lr=1e-2, weight_decay=wd)
     o_ref2.load_state_dict(sd)                  # optimiser checkpoints move between the two classes
+    # ... and back: state written by torch's fused Adam keeps `step` on the device
+    ws = [torch.nn.Parameter(w.detach().clone()) for w in ours]
+    o_f = torch.optim.Adam(ws, lr=1e-2, weight_decay=wd, fused=True)
+    for w in ws:
+        w.grad = torch.ones_like(w)
+    o_f.step()
+    o_back = P.Adam(ws, lr=1e-2, weight_decay=wd)
+    o_back.load_state_dict(o_f.state_dict())
+    before = ws[0].detach().clone()
+    o_back.step()
+    assert float(o_back.state[ws[0]]["step"]) == 2.0 and not o_back.state[ws[0]]["step"].is_cuda
+    assert not torch.equal(ws[0], before)
 
 
 def test_adam_skips_parameters_without_gradient_and_groups_by_step():
