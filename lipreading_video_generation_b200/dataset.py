@@ -136,6 +136,11 @@ class TalkingFaceFrameBatcher:
         if not st.frames.is_cuda:
             raise RuntimeError("TalkingFaceFrameBatcher runs on sm_100a kernels only (no CPU fallback)")
         B = len(indices)
+        if B == 0:
+            H, W = st.frames.shape[1:3]
+            z = torch.empty(0, 3, H, W, device=st.device, dtype=torch.float32)
+            self.last_indices = torch.empty(0, 3, device=st.device, dtype=torch.int64)
+            return z, z.clone(), {"input_values": torch.empty(0, 1, TARGET_LENGTH, device=st.device, dtype=torch.float32)}
         dev = [torch.from_numpy(a).pin_memory().to(st.device, non_blocking=True) for a in self.host_tables(indices)]
         vid, fend, tot, fps, sr, bq = dev
         audio = torch.empty(B, 1, TARGET_LENGTH, device=st.device, dtype=torch.float32)

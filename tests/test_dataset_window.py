@@ -115,3 +115,28 @@ def test_device_index_arithmetic_is_bit_exact_over_a_sweep():
     with pytest.raises(ValueError):
         b.check()                                        # 4-sample track: every window is empty -> flagged, NaN written
     assert torch.isnan(out).all()
+
+
+@pytest.mark.gpu
+def test_empty_batch_and_window_clipped_at_the_end_of_a_short_track(golden):
+    """Edge cases: an empty index list launches nothing; a window that runs past the end of the track is clipped like
+    the reference's Python slice (and still normalised over what is left)."""
+    import lipreading_video_generation_b200 as P
+    from lipreading_video_generation_b200 import _lib as L
+    g = golden("audio_window.pt")
+    st = _store(g, "cuda")
+    b = P.TalkingFaceFrameBatcher(st, [P.FrameItem(n, 0, fe) for n, fe in g["items"]])
+    l0 = L.lib().b2d_launch_count()
+    fin, fout, audio = b.batch([])
+    assert L.lib().b2d_launch_count() == l0
+    assert fin.shape[0] == 0 and fout.shape[0] == 0 and audio["input_values"].shape == (0, 1, 4000)
+    # a 1.0 s track at 16 kHz with 40 frames at 25 fps: frame 39 ends at 1.56 s -> window [21760, 24960) clipped to 16000
+    st2 = P.DeviceVideoStore("cuda")
+    wave = g["videos"][0]["wave"][:, :23000]
+    st2.add("short.mp4", g["videos"][0]["frames"], wave, 25.0, 16000)
+    b2 = P.TalkingFaceFrameBatcher(st2, [P.FrameItem("short.mp4", 0, 39)])
+    _, _, a2 = b2.batch([0])
+    assert b2.last_indices.cpu().tolist() == [[39, 21760, 24960]]          # indices are NOT clipped, the slice is
+    want = A.audio_window(wave[0].numpy(), 39, 40, 25.0, 16000)            # numpy slicing clips the same way
+    assert np.abs(a2["input_values"][0, 0].cpu().numpy() - want).max() <= TOL_FP32
+    b2.check()

@@ -661,3 +661,13 @@ def test_attention_row_shards_reassemble_to_the_unsharded_result(ch, L):
         assert rel(d_acc, dqkv) <= 2e-3
     with pytest.raises(RuntimeError):
         ops.attention_fwd(qkv, 1, rows=(128, 256))          # not 256-aligned
+
+
+def test_adam_without_gradients_launches_nothing():
+    import lipreading_video_generation_b200 as P
+    from lipreading_video_generation_b200 import _lib
+    w = torch.nn.Parameter(torch.ones(8, device="cuda"))
+    o = P.Adam([w], lr=0.1)
+    l0 = _lib.lib().b2d_launch_count()
+    o.step()
+    assert _lib.lib().b2d_launch_count() == l0 and torch.equal(w, torch.ones_like(w)) and len(o.state) == 0
