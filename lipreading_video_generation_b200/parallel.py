@@ -172,3 +172,6 @@ def broadcast_parameters(model, src: int = 0, group=None):
     with torch.no_grad():
         for t in list(model.parameters()) + list(model.buffers()):
             dist.broadcast(t, src=src, group=group)
+    eng = model.engine() if hasattr(model, "engine") else None
+    if eng is not None:
+        eng._weights_maybe_stale = True     # collectives write parameters without bumping `_version`: re-pack on next use
