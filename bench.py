@@ -1,14 +1,21 @@
-"""bench.py -- denoiser train step throughput (clips/s), BASELINE.json configs[1]:
-single B200, batch 16 clips x 16 frames 64x64 (N = 256 images folded into the batch), bf16 train step.
+"""bench.py -- BASELINE.json's metric: denoiser train clips/s and sampler frames/s on N B200s, % of roofline.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload train64|train128|sample128]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                    [--workload train64|train128|sample128|sample128_b1|train64_1clip|train3d_cfg5|train3d_small] [--no-extras]
 
-One "step" = q_sample + UNetAudio forward (wav2vec2 + sm_100a torso) + MSE + backward + Adam step on one
-batch of synthetic clips (train.py:109-134).  Prints ONE JSON line (see DESIGN.md "measurement").
+The default line is `train64` (BASELINE configs[1]: 16 clips x 16 frames 64x64 per GPU, N = 256 images folded into the
+batch); the SAME run then measures, as `extra` sub-records, the other half of the metric -- `sample128` (configs[3]:
+1000-step DDPM and a real 50-step DDIM loop, frames/s) -- and `train128` (configs[2] per-GPU shape), plus the achieved
+HBM rate of the elementwise kernels (q_sample, MSE, sampler update) at the configs[2]/[3] sizes.
+
+One train "step" = q_sample + UNetAudio forward (wav2vec2 + sm_100a torso) + MSE + backward + gradient all-reduce + Adam
+on one batch of synthetic clips (train.py:109-134); one sampler "step" = model forward + sample_prev_timestep
+(test.py:57-65).  Prints ONE JSON line.
 """
 from __future__ import annotations
 
 import argparse
+import gc
 import json
 import os
 import subprocess
@@ -19,7 +26,6 @@ import time
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 os.environ.setdefault("B2D_WAV2VEC2_RANDOM_INIT", "1")   # no network: wav2vec2-base weights are random-init
-os.environ.setdefault("NCCL_DEBUG", "WARN")              # keep stdout to the one JSON line
 
 import torch  # noqa: E402
 
@@ -28,11 +34,13 @@ WORKLOADS = {
     "train64": (16, 16, 64, "train"),      # BASELINE configs[1]
     "train128": (16, 16, 128, "train"),    # BASELINE configs[2] per-GPU shape
     "sample128": (8, 16, 128, "sample"),   # BASELINE configs[3] per-GPU shape
+    "sample128_b1": (1, 1, 128, "sample"),  # the reference's own sampling operating point (test.py:54): batch 1
     "train64_1clip": (1, 16, 64, "train"),  # diagnostic: 16x less GPU work, same launches -> host cost of one step
     "train3d_cfg5": (1, 64, 128, "train3d"),   # BASELINE configs[4]: UNetModel(dims=3) on one (195, 64, 128, 128) clip
     "train3d_small": (1, 16, 64, "train3d"),   # the same path at (195, 16, 64, 64)
 }
 FWD_GFLOP_PER_IMAGE = {64: 43.87, 128: 470.21}     # SURVEY section 8(d), algorithmic, UNet torso
+CLASSES = {"attention_fwd", "attention_bwd", "conv2d", "conv2d_wgrad", "groupnorm_fwd", "groupnorm_bwd"}
 
 
 def peaks():
@@ -108,13 +116,16 @@ def build_model(S, device, seed=0):
 
 class SampleStep:
     """test.py:57-65 on the product: one reverse-diffusion step for a batch of frames -- model forward (no autograd
-    graph, conditioning encoded once and reused: it is loop invariant) + DDPM posterior update with fresh noise."""
+    graph, conditioning encoded once and reused: it is loop invariant) + the sampler update with fresh noise.
+    mode "ddpm": LinearNoiseScheduler.sample_prev_timestep over t = 999..0; mode "ddim": the 50-step eta = 0
+    subsequence of the same schedule through scheduler.ddim_step."""
 
-    def __init__(self, model, S, device):
+    def __init__(self, model, S, device, mode="ddpm", ddim_steps=50):
         import lipreading_video_generation_b200 as P
-        self.model, self.device = model.eval(), device
+        self.model, self.device, self.mode = model.eval(), device, mode
         self.sched = P.LinearNoiseScheduler(1000, 0.00085, 0.012)
-        self.i = 999
+        self.seq = [int(round(v)) for v in torch.linspace(999, 0, ddim_steps).tolist()]
+        self.k = 0
         self.feats = None
 
     def prepare(self, audio):
@@ -123,12 +134,18 @@ class SampleStep:
 
     @torch.no_grad()
     def __call__(self, xt, cond):
-        i = self.i
-        self.i = i - 1 if i > 1 else 999
+        if self.mode == "ddpm":
+            i = 999 - (self.k % 999)                # never t = 0 inside a timed region: every step draws noise
+            self.k += 1
+            t = torch.full((xt.shape[0],), i, device=self.device, dtype=torch.long)
+            eps = self.model(xt, cond, None, t, audio_features=self.feats)
+            return self.sched.sample_prev_timestep(xt, eps, i)
+        k = self.k % len(self.seq)
+        self.k += 1
+        i, prev = self.seq[k], (self.seq[k + 1] if k + 1 < len(self.seq) else -1)
         t = torch.full((xt.shape[0],), i, device=self.device, dtype=torch.long)
         eps = self.model(xt, cond, None, t, audio_features=self.feats)
-        x_prev, x0 = self.sched.sample_prev_timestep(xt, eps, i)
-        return x_prev, x0
+        return self.sched.ddim_step(xt, eps, i, prev)
 
 
 class TrainStep:
@@ -161,119 +178,362 @@ class TrainStep:
         self.opt.step()
         return loss
 
+    def close(self):
+        if self.reducer is not None:
+            self.reducer.detach()
 
-def cpu_baseline(S, threads, seconds_budget=25.0):
-    """The oracle port (CPU restatement of the reference, fp32) timed on the host: fwd + bwd of the torso on a
-    bounded sample of the same workload (images of the same shape, as many as fit the time budget)."""
+
+# ----------------------------------------------------------------------------- CPU baselines (oracle port, host cores)
+def _cpu_name():
+    try:
+        for line in open("/proc/cpuinfo"):
+            if line.startswith("model name"):
+                return line.split(":", 1)[1].strip()
+    except OSError:
+        pass
+    return "unknown"
+
+
+class CpuTrainCfg1:
+    """BASELINE.md section 2 / SURVEY 8(d) 'config 1 exactly': the reference's train step (train.py:109-134) on the host
+    cores -- 2 clips x 8 frames = 16 images 64x64, fp32, HF wav2vec2-base (random init, train mode) + the oracle port of
+    the UNet torso (AttentionBlock under its always-on activation checkpoint, unet.py:309) + MSE + backward + Adam
+    over all 110.7 M parameters.  /root/reference does not exist on the GPU box, so the torso is oracle/restatement.py
+    (pinned against the real reference by oracle/make_golden*.py): kind = "port"."""
+    N, S = 16, 64
+
+    def __init__(self, threads):
+        from transformers import Wav2Vec2Config, Wav2Vec2Model
+        from oracle import restatement as R
+        import lipreading_video_generation_b200 as P
+        torch.set_num_threads(threads)
+        self.R = R
+
+        class Stub(torch.nn.Module):
+            def forward(self, a):
+                return a["feats"]
+        shell = P.UNetAudio(image_size=self.S, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=2,
+                            attention_resolutions=(1, 2, 4), audio_feature_dim=768, projected_audio_dim=128,
+                            audio_encoder=Stub())
+        sd = R.protocol_params(shell.state_dict(), seed=0)
+        self.sd = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
+        torch.manual_seed(0)
+        self.enc = Wav2Vec2Model(Wav2Vec2Config()).train()                     # unet_audio.py:14 (random init: no network)
+        self.cfg = dict(image_size=self.S, model_channels=64, num_res_blocks=2, attention_resolutions=(1, 2, 4),
+                        channel_mult=(1, 2, 4), num_heads=1, checkpoint_attention=True)
+        self.opt = torch.optim.Adam(list(self.sd.values()) + list(self.enc.parameters()), lr=1e-2)   # train.py:102
+        self.tab = R.linear_tables(1000, 0.00085, 0.012)
+        g = torch.Generator().manual_seed(1234)
+        self.x0 = torch.rand(self.N, 3, self.S, self.S, generator=g) * 2 - 1
+        self.cond = torch.rand(self.N, 3, self.S, self.S, generator=g) * 2 - 1
+        self.audio = torch.randn(self.N, 4000, generator=g)
+        self.g = g
+
+    def step(self):
+        R = self.R
+        t0 = time.perf_counter()
+        self.opt.zero_grad(set_to_none=True)
+        noise = torch.randn(self.x0.shape, generator=self.g)
+        t = torch.randint(0, 1000, (self.N,), generator=self.g)
+        xt = R.add_noise(self.tab, self.x0, noise, t)
+        feats = self.enc(input_values=self.audio, output_hidden_states=True).last_hidden_state      # unet_audio.py:16-18
+        pred = R.unet_audio_forward(self.sd, self.cfg, xt, self.cond, feats.mean(dim=1), t)
+        loss = R.mse(pred, noise)
+        loss.backward()
+        self.opt.step()
+        return time.perf_counter() - t0
+
+
+def cpu_train_baseline(cores, frames, reps=5, budget_s=100.0):
+    """1 warm-up + median of `reps` cfg1 steps; clips/s in units of `frames`-frame clips."""
+    b = CpuTrainCfg1(cores)
+    b.step()
+    times, t_end = [], time.perf_counter() + budget_s
+    while len(times) < reps and (not times or time.perf_counter() < t_end):
+        times.append(b.step())
+    med = sorted(times)[len(times) // 2]
+    return {"value": round((b.N / frames) / med, 5), "unit": "clips/s", "cores": cores, "kind": "port",
+            "sample": f"cfg1 exactly: 16 images 64x64 fp32 (2 clips x 8 frames; clips/s quoted in {frames}-frame clips), "
+                      f"HF wav2vec2-base + oracle torso (attention checkpointed as unet.py:309) fwd+bwd+Adam over 110.7 M "
+                      f"parameters, 1 warm-up + median of {len(times)}: {med:.2f} s/step",
+            "sec_per_step": round(med, 3), "reps": len(times), "cpu": _cpu_name(), "torch_threads": torch.get_num_threads()}
+
+
+def cpu_sampler_baseline(cores, steps=5, budget_s=75.0):
+    """test.py:57-65 on the host cores: `steps` steps of oracle model forward + sample_prev_timestep at 2 images 128x128
+    (conditioning hoisted like the product's loop), extrapolated linearly to 1000 / 50 steps."""
     from oracle import restatement as R
     import lipreading_video_generation_b200 as P
-    torch.set_num_threads(threads)
+    torch.set_num_threads(cores)
 
     class Stub(torch.nn.Module):
         def forward(self, a):
             return a["feats"]
-    m = P.UNetAudio(image_size=S, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=2,
-                    attention_resolutions=(1, 2, 4), dropout=0.0, audio_feature_dim=768, projected_audio_dim=128,
-                    audio_encoder=Stub())
-    sd = R.protocol_params(m.state_dict(), seed=0)
-    cfg = dict(image_size=S, model_channels=64, num_res_blocks=2, attention_resolutions=(1, 2, 4), channel_mult=(1, 2, 4), num_heads=1)
-    n = 2
-    g = torch.Generator().manual_seed(0)
-    xt = torch.randn(n, 3, S, S, generator=g); cond = torch.rand(n, 3, S, S, generator=g)
-    fm = torch.randn(n, 768, generator=g); eps = torch.randn(n, 3, S, S, generator=g); t = torch.randint(0, 1000, (n,), generator=g)
-
-    def one():
-        sdr = {k: v.clone().requires_grad_(True) for k, v in sd.items()}
-        loss = R.mse(R.unet_audio_forward(sdr, cfg, xt, cond, fm, t), eps)
-        loss.backward()
-    one()                                   # warm-up
+    S, n = 128, 2
+    shell = P.UNetAudio(image_size=S, in_channels=3, model_channels=64, out_channels=3, num_res_blocks=2,
+                        attention_resolutions=(1, 2, 4), audio_feature_dim=768, projected_audio_dim=128, audio_encoder=Stub())
+    sd = R.protocol_params(shell.state_dict(), seed=0)
+    cfg = dict(image_size=S, model_channels=64, num_res_blocks=2, attention_resolutions=(1, 2, 4), channel_mult=(1, 2, 4),
+               num_heads=1)
+    tab = R.linear_tables(1000, 0.00085, 0.012)
+    g = torch.Generator().manual_seed(1234)
+    xt = torch.randn(n, 3, S, S, generator=g)
+    cond = torch.rand(n, 3, S, S, generator=g) * 2 - 1
+    fm = torch.randn(n, 768, generator=g)
     times = []
-    t_end = time.time() + seconds_budget
-    while len(times) < 5 and time.time() < t_end:
-        t0 = time.time(); one(); times.append(time.time() - t0)
-    med = sorted(times)[len(times) // 2]
-    return n, med, len(times)
+    t_end = time.perf_counter() + budget_s
+    with torch.no_grad():
+        for k in range(steps):
+            if k >= 2 and time.perf_counter() > t_end:
+                break
+            i = 999 - k
+            t0 = time.perf_counter()
+            eps = R.unet_audio_forward(sd, cfg, xt, cond, fm, torch.full((n,), i))
+            xt, _ = R.ddpm_step(tab, xt, eps, i, torch.randn(xt.shape, generator=g))
+            times.append(time.perf_counter() - t0)
+    sec = sorted(times)[len(times) // 2]
+    return {"value": round(n / (1000 * sec), 6), "unit": "frames/s (1000-step DDPM)", "cores": cores, "kind": "port",
+            "value_50_step_ddim": round(n / (50 * sec), 5),
+            "sample": f"{len(times)} steps of oracle forward + ddpm_step at {n} images 128x128 fp32, median {sec:.2f} s/step, "
+                      f"EXTRAPOLATED linearly to 1000 / 50 steps", "sec_per_step": round(sec, 3), "cpu": _cpu_name()}
 
 
-def main_sample(a, model, S, clips, frames, world, rank, local, device, config, cores):
-    """sampler frames/s (BASELINE configs[3] per-GPU shape): replicas only, no collective on the data path."""
+# ----------------------------------------------------------------------------- GPU measurements
+def _barrier(world):
+    if world > 1:
+        torch.distributed.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_over_ranks(vals, world, device):
+    if world > 1:
+        tt = torch.tensor(vals, device=device, dtype=torch.float64)
+        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
+        return tt.tolist()
+    return list(vals)
+
+
+def _attention_roofline(totals, steps, ms_step, sustained, which):
+    dom = None
+    for (name, meta), (t_ms, cnt) in totals.items():
+        if not name.startswith("attention"):
+            continue
+        Nn, Lk, heads, ch = meta[:4]
+        Lq = meta[4] if len(meta) > 4 else Lk
+        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lk * ch * heads * Nn
+        rec = dict(kernel=f"{name} L={Lk} ch={ch}", ms_per_launch=t_ms / cnt, tflops=flops / (t_ms / cnt) / 1e9,
+                   ms_per_step=t_ms / steps)
+        if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
+            dom = rec
+    return {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
+            "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
+            "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms_step, 3),
+            "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N fwd, "
+                           f"10*L^2*ch*N bwd"}
+
+
+def measure_train(steps, warmup, S, clips, frames, world, rank, local, device, verbose=False):
+    """Returns the record of one train workload (all ranks run it; max over ranks)."""
     from lipreading_video_generation_b200 import _lib as L, ops
+    from lipreading_video_generation_b200.parallel import broadcast_parameters
     n_img = clips * frames
-    step = SampleStep(model, S, device)
+    model = build_model(S, device)
+    if world > 1:
+        broadcast_parameters(model)
+    step = TrainStep(model, S, world, device)
     x0, cond, audio = make_batch(n_img, S, 1234 + rank, device)
     hx0, hcond, haudio = make_batch(n_img, S, 1234 + rank, device, pinned=True)
-    step.prepare(audio)
-    xt = torch.randn(n_img, 3, S, S, device=device)
-
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
-    for _ in range(a.warmup):
-        xt, _ = step(xt, cond)
-    barrier()
+    gt = torch.Generator().manual_seed(99 + rank)
+    t_dev = torch.randint(0, 1000, (n_img,), generator=gt).to(device)
+    t_host = torch.randint(0, 1000, (n_img,), generator=gt).pin_memory()
+    for _ in range(warmup):
+        step(x0, cond, audio, t_dev)
+    # ---------------- timed region 1: inputs resident in HBM ("value") + roofline events on the attention kernels
+    _barrier(world)
     l0 = L.lib().b2d_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "conv2d", "groupnorm_fwd"}) as kt:
+    # only the candidate dominant kernels carry events inside the timed region (26 launches per step); the full
+    # per-class breakdown (~530 event pairs per step, which costs 2-3 ms of step time) runs in an untimed pass below
+    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
         e0.record()
-        for _ in range(a.steps):
-            xt, x0p = step(xt, cond)
+        h0 = time.perf_counter()
+        for _ in range(steps):
+            step(x0, cond, audio, t_dev)
+        host_ms = (time.perf_counter() - h0) * 1e3 / steps     # host time to enqueue one step (no sync inside)
         e1.record()
-        barrier()
-    ms = e0.elapsed_time(e1) / a.steps
-    launches = (L.lib().b2d_launch_count() - l0) // a.steps
-    # end to end: conditioning + x_T from pinned host memory, wav2vec2 encoding, K steps, x0_pred back to the host
-    barrier()
+        _barrier(world)
+    ms = e0.elapsed_time(e1) / steps
+    launches = (L.lib().b2d_launch_count() - l0) // steps
+    # ---------------- timed region 2: end to end through the public API with HOST buffers
+    _barrier(world)
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    hxt = torch.randn(n_img, 3, S, S).pin_memory()
-    hout = torch.empty(n_img, 3, S, S).pin_memory()
     f0.record()
-    dc = hcond.to(device, non_blocking=True); da = haudio.to(device, non_blocking=True); dx = hxt.to(device, non_blocking=True)
-    step.prepare(da)
-    for _ in range(a.steps):
-        dx, x0p = step(dx, dc)
-    hout.copy_(x0p, non_blocking=True)
+    # the loss of every step is copied to pinned host memory and READ on the host one step later (after the next step
+    # has been enqueued), the last one before the timer stops: logging the loss does not drain the launch queue
+    loss_pin = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
+    loss_ev = [torch.cuda.Event() for _ in range(2)]
+    losses_host = []
+    for i in range(steps):
+        dx0 = hx0.to(device, non_blocking=True); dc = hcond.to(device, non_blocking=True)
+        da = haudio.to(device, non_blocking=True); dt = t_host.to(device, non_blocking=True)
+        loss = step(dx0, dc, da, dt)
+        loss_pin[i % 2].copy_(loss.detach(), non_blocking=True)     # device -> host read of the step's result
+        loss_ev[i % 2].record()
+        if i > 0:
+            loss_ev[(i - 1) % 2].synchronize()
+            losses_host.append(float(loss_pin[(i - 1) % 2]))
+    loss_ev[(steps - 1) % 2].synchronize()
+    losses_host.append(float(loss_pin[(steps - 1) % 2]))
+    assert len(losses_host) == steps
     f1.record()
-    barrier()
-    ms_e2e = f0.elapsed_time(f1) / a.steps
-    if world > 1:
-        tt = torch.tensor([ms, ms_e2e], device=device)
-        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
-        ms, ms_e2e = tt.tolist()
-        torch.distributed.destroy_process_group()
-    if rank != 0:
-        return
+    _barrier(world)
+    ms_e2e = f0.elapsed_time(f1) / steps
+    # ---------------- untimed diagnostic pass: per-class kernel time of one step
+    with ops.KernelTimer(CLASSES) as kt_all:
+        step(x0, cond, audio, t_dev)
+        _barrier(world)
+    ms, ms_e2e = _max_over_ranks([ms, ms_e2e], world, device)
+    step.close()
     burst, sustained, hbm, which = peaks()
-    tot = kt.totals()
-    by_class, dom = {}, None
-    for (name, meta), (t_ms, cnt) in tot.items():
-        by_class[name] = by_class.get(name, 0.0) + t_ms / a.steps
-        if name == "attention_fwd":
-            Nn, Lq, heads, ch = meta
-            rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, tflops=4.0 * Lq * Lq * ch * heads * Nn / (t_ms / cnt) / 1e9,
-                       ms_per_step=t_ms / a.steps)
-            if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
-                dom = rec
-    T = 1000
-    value = n_img * world / (T * ms / 1000.0)
-    fwd_tflop = FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
-    out = {"metric": "sampler_frames_per_s", "value": round(value, 4), "unit": "frames/s (1000-step DDPM)", "n_gpus": world,
-           "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
-           "frames_per_s_50_step_ddim": round(n_img * world / (50 * ms / 1000.0), 3),
-           "e2e": {"value": round(n_img * world / (T * ms_e2e / 1000.0), 4), "unit": "frames/s (1000-step DDPM)",
-                   "h2d_bytes_per_step": sum(t.numel() * t.element_size() for t in (hcond, haudio, hxt)) // a.steps,
-                   "d2h_bytes_per_step": hout.numel() * 4 // a.steps, "ms_per_step": round(ms_e2e, 3)},
-           "gpu_launches": int(launches),
-           "roofline": {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
-                        "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
-                        "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
-                        "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N"},
-           "step_tflops_algorithmic": round(fwd_tflop / (ms / 1000.0), 1),
-           "step_frac_of_sustained_peak": round(fwd_tflop / (ms / 1000.0) / sustained, 4),
+    by_class = {}
+    for (name, meta), (t_ms, cnt) in kt_all.totals().items():
+        by_class[name] = by_class.get(name, 0.0) + t_ms
+        if verbose and rank == 0:
+            print(f"[kernel] {name:14s} {str(meta):40s} x{cnt:3d}/step  {t_ms / cnt:8.4f} ms/launch  {t_ms:8.3f} ms/step",
+                  file=sys.stderr)
+    roof = _attention_roofline(kt.totals(), steps, ms, sustained, which)
+    train_tflop = 3 * FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
+    h2d = sum(t.numel() * t.element_size() for t in (hx0, hcond, haudio, t_host))
+    rec = {"value": round(clips * world / (ms / 1000.0), 3), "unit": "clips/s", "steps": steps, "warmup": warmup,
+           "ms_per_step": round(ms, 3),
+           "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 3), "unit": "clips/s", "h2d_bytes_per_step": h2d,
+                   "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
+           "gpu_launches": int(launches), "host_enqueue_ms_per_step": round(host_ms, 3), "roofline": roof,
+           "step_tflops_algorithmic": round(train_tflop / (ms / 1000.0), 1),
+           "step_frac_of_sustained_peak": round(train_tflop / (ms / 1000.0) / sustained, 4),
            "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
-           "cpu_baseline": None, "clocks": clk.summary()}
-    print(json.dumps(out))
+           "clocks": clk.summary(), "last_loss": losses_host[-1], "images_per_gpu": n_img}
+    del step, model, x0, cond, audio
+    gc.collect()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def measure_sample(steps, warmup, S, clips, frames, world, rank, local, device):
+    """sampler frames/s (BASELINE configs[3] per-GPU shape): replicas only, no collective on the data path.
+    Times the 1000-step DDPM update (`value`) and, separately, a real 50-step DDIM loop."""
+    from lipreading_video_generation_b200 import _lib as L, ops
+    n_img = clips * frames
+    model = build_model(S, device)
+    x0, cond, audio = make_batch(n_img, S, 1234 + rank, device)
+    hx0, hcond, haudio = make_batch(n_img, S, 1234 + rank, device, pinned=True)
+    out = {}
+    for mode in ("ddpm", "ddim"):
+        step = SampleStep(model, S, device, mode=mode)
+        step.prepare(audio)
+        xt = torch.randn(n_img, 3, S, S, device=device)
+        for _ in range(warmup):
+            xt, _ = step(xt, cond)
+        _barrier(world)
+        l0 = L.lib().b2d_launch_count()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "conv2d", "groupnorm_fwd"}) as kt:
+            e0.record()
+            h0 = time.perf_counter()
+            for _ in range(steps):
+                xt, x0p = step(xt, cond)
+            host_ms = (time.perf_counter() - h0) * 1e3 / steps
+            e1.record()
+            _barrier(world)
+        ms = e0.elapsed_time(e1) / steps
+        launches = (L.lib().b2d_launch_count() - l0) // steps
+        # end to end: conditioning + x_T from pinned host memory, wav2vec2 encoding, K steps, x0_pred back to the host
+        _barrier(world)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        hxt = torch.randn(n_img, 3, S, S).pin_memory()
+        hout = torch.empty(n_img, 3, S, S).pin_memory()
+        f0.record()
+        dc = hcond.to(device, non_blocking=True); da = haudio.to(device, non_blocking=True); dx = hxt.to(device, non_blocking=True)
+        step.prepare(da)
+        for _ in range(steps):
+            dx, x0p = step(dx, dc)
+        hout.copy_(x0p, non_blocking=True)
+        f1.record()
+        _barrier(world)
+        ms_e2e = f0.elapsed_time(f1) / steps
+        ms, ms_e2e = _max_over_ranks([ms, ms_e2e], world, device)
+        out[mode] = dict(ms=ms, ms_e2e=ms_e2e, launches=launches, host_ms=host_ms, kt=kt, clk=clk.summary(),
+                         h2d=sum(t.numel() * t.element_size() for t in (hcond, haudio, hxt)) // steps,
+                         d2h=hout.numel() * 4 // steps)
+    burst, sustained, hbm, which = peaks()
+    d, i = out["ddpm"], out["ddim"]
+    by_class = {}
+    for (name, meta), (t_ms, cnt) in d["kt"].totals().items():
+        by_class[name] = by_class.get(name, 0.0) + t_ms / steps
+    fwd_tflop = FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
+    rec = {"value": round(n_img * world / (1000 * d["ms"] / 1000.0), 4), "unit": "frames/s (1000-step DDPM)",
+           "steps": steps, "warmup": warmup, "ms_per_step": round(d["ms"], 3),
+           "frames_per_s_50_step_ddim": round(n_img * world / (50 * i["ms"] / 1000.0), 3),
+           "ms_per_ddim_step": round(i["ms"], 3),
+           "ddim_note": "measured: a 50-step eta=0 subsequence of the same schedule run through scheduler.ddim_step",
+           "e2e": {"value": round(n_img * world / (1000 * d["ms_e2e"] / 1000.0), 4), "unit": "frames/s (1000-step DDPM)",
+                   "h2d_bytes_per_step": d["h2d"], "d2h_bytes_per_step": d["d2h"], "ms_per_step": round(d["ms_e2e"], 3),
+                   "frames_per_s_50_step_ddim": round(n_img * world / (50 * i["ms_e2e"] / 1000.0), 3)},
+           "gpu_launches": int(d["launches"]), "host_enqueue_ms_per_step": round(d["host_ms"], 3),
+           "roofline": _attention_roofline(d["kt"].totals(), steps, d["ms"], sustained, which),
+           "step_tflops_algorithmic": round(fwd_tflop / (d["ms"] / 1000.0), 1),
+           "step_frac_of_sustained_peak": round(fwd_tflop / (d["ms"] / 1000.0) / sustained, 4),
+           "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
+           "clocks": d["clk"], "images_per_gpu": n_img}
+    del model, x0, cond, audio
+    gc.collect()
+    torch.cuda.empty_cache()
+    return rec
+
+
+def measure_hbm_kernels(device):
+    """Achieved HBM rate of the elementwise / reduction kernels north_star names, at the BASELINE configs[2] (q_sample,
+    MSE: N = 256 images 128x128) and configs[3] (sampler update: N = 128) sizes.  CUDA events around 20 launches each
+    over buffers far larger than L2 (each launch touches 100-250 MB); algorithmic bytes per SURVEY 8(d)."""
+    import lipreading_video_generation_b200 as P
+    burst, sustained, hbm, which = peaks()
+    sched = P.LinearNoiseScheduler(1000, 0.00085, 0.012)
+    crit = P.MSELoss()
+    out = {}
+
+    def timed(fn, reps=20):
+        for _ in range(3):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+    with torch.no_grad():
+        n = 256
+        x0 = torch.rand(n, 3, 128, 128, device=device); eps = torch.randn_like(x0)
+        t = torch.randint(0, 1000, (n,), device=device)
+        E = x0.numel()
+        ms = timed(lambda: sched.add_noise(x0, eps, t))
+        out["q_sample"] = {"elements": E, "bytes": 12 * E, "ms": round(ms, 4), "gbs": round(12 * E / ms / 1e6, 1)}
+        ms = timed(lambda: crit(x0, eps))
+        out["mse_fwd"] = {"elements": E, "bytes": 8 * E, "ms": round(ms, 4), "gbs": round(8 * E / ms / 1e6, 1)}
+        n = 128
+        xt = torch.randn(n, 3, 128, 128, device=device); e = torch.randn_like(xt); z = torch.randn_like(xt)
+        E = xt.numel()
+        ms = timed(lambda: sched.sample_prev_timestep(xt, e, 500, z=z))
+        out["ddpm_step"] = {"elements": E, "bytes": 20 * E, "ms": round(ms, 4), "gbs": round(20 * E / ms / 1e6, 1)}
+        ms = timed(lambda: sched.ddim_step(xt, e, 500, 480))
+        out["ddim_step"] = {"elements": E, "bytes": 16 * E, "ms": round(ms, 4), "gbs": round(16 * E / ms / 1e6, 1)}
+    for v in out.values():
+        v["frac_of_hbm_peak"] = round(v["gbs"] / hbm, 3)
+    out["peak_gbs"] = hbm
+    out["note"] = ("ms includes the Python wrapper's output allocation; bytes are algorithmic (q_sample 12 B/elem, MSE 8, "
+                   "DDPM update 20, DDIM 16)")
+    return out
 
 
 def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores):
@@ -318,14 +578,9 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
         opt.step()
         return loss
 
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
-
     for _ in range(a.warmup):
         step(x, eps, t)
-    barrier()
+    _barrier(world)
     l0 = L.lib().b2d_launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
@@ -333,40 +588,30 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
         for _ in range(a.steps):
             step(x, eps, t)
         e1.record()
-        barrier()
+        _barrier(world)
     ms = e0.elapsed_time(e1) / a.steps
     launches = (L.lib().b2d_launch_count() - l0) // a.steps
-    barrier()
+    _barrier(world)
     f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     f0.record()
     for _ in range(a.steps):
         loss = step(hx.to(device, non_blocking=True), heps.to(device, non_blocking=True), ht.to(device, non_blocking=True))
         loss_host = loss.item()
     f1.record()
-    barrier()
+    _barrier(world)
     ms_e2e = f0.elapsed_time(f1) / a.steps
-    with ops.KernelTimer({"attention_fwd", "attention_bwd", "conv2d", "conv2d_wgrad", "groupnorm_fwd", "groupnorm_bwd"}) as kt_all:
+    with ops.KernelTimer(CLASSES) as kt_all:
         step(x, eps, t)
-        barrier()
+        _barrier(world)
+    ms, ms_e2e = _max_over_ranks([ms, ms_e2e], world, device)
     if world > 1:
-        tt = torch.tensor([ms, ms_e2e], device=device)
-        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
-        ms, ms_e2e = tt.tolist()
         torch.distributed.destroy_process_group()
     if rank != 0:
         return
     burst, sustained, hbm, which = peaks()
-    dom, by_class = None, {}
+    by_class = {}
     for (name, meta), (t_ms, cnt) in kt_all.totals().items():
         by_class[name] = by_class.get(name, 0.0) + t_ms
-    for (name, meta), (t_ms, cnt) in kt.totals().items():
-        Nn, Lk, heads, ch = meta[:4]
-        Lq = meta[4] if len(meta) > 4 else Lk             # a sequence-parallel shard visits Lq of the Lk query rows
-        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lk * ch * heads * Nn
-        rec = dict(kernel=f"{name} L={Lk} ch={ch}" + (f" (query rows {Lq} of {Lk} per GPU)" if Lq != Lk else ""),
-                   ms_per_launch=t_ms / cnt, tflops=flops / (t_ms / cnt) / 1e9, ms_per_step=t_ms / a.steps)
-        if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
-            dom = rec
     h2d = sum(v.numel() * v.element_size() for v in (hx, heps, ht))
     out = {"metric": "denoiser_train_clips_per_s", "value": round(clips / (ms / 1000.0), 4), "unit": "clips/s",
            "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
@@ -374,14 +619,63 @@ def main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
            "seq_parallel_bytes_per_step": (sp.bytes_moved // (a.warmup + 2 * a.steps + 1)) if sp is not None else 0,
            "e2e": {"value": round(clips / (ms_e2e / 1000.0), 4), "unit": "clips/s", "h2d_bytes_per_step": h2d,
                    "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
-           "gpu_launches": int(launches),
-           "roofline": {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
-                        "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
-                        "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
-                        "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch fwd, 10*L^2*ch bwd"},
+           "gpu_launches": int(launches), "roofline": _attention_roofline(kt.totals(), a.steps, ms, sustained, which),
            "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
            "cpu_baseline": None, "clocks": clk.summary(), "last_loss": loss_host}
     print(json.dumps(out))
+
+
+def _config(name, clips, frames, S, kind, world):
+    cfg = {"workload": f"{name}: denoiser {kind} step, {clips} clips x {frames} frames {S}x{S} per GPU "
+                       f"(N={clips * frames} images folded into the batch), UNetAudio train.py config + wav2vec2-base",
+           "clips_per_gpu": clips, "frames": frames, "image": S, "parallelism": f"dp{world}",
+           "l2_policy": "inputs+activations >> L2 (126 MB): >10 GB touched per step"}
+    if kind == "train3d":
+        cfg["workload"] = (f"{name}: UNetModel(dims=3) train step on {clips} clip(s) (195, {frames}, {S}, {S}) per GPU, "
+                           f"train.py torso config (64 ch, mult (1,2,4), 2 res blocks, attention at all levels over "
+                           f"L = T*S*S = {frames * S * S} positions), MSE + backward + Adam, no audio encoder")
+    return cfg
+
+
+def main_reference(a, frames, config, cores, kind):
+    """--impl reference: the reference's CPU path on the host cores (oracle port; /root/reference does not travel to
+    the GPU box).  Train workloads: each step is ONE cfg1 train step (16 images 64x64, fwd+bwd+Adam incl. wav2vec2) --
+    a bounded sample of the workload; W warm-up + K timed steps, capped by a wall-clock budget with the real number
+    of timed steps reported.  Sample workloads: steps of oracle forward + ddpm_step at 2 images 128x128."""
+    budget = float(os.environ.get("B2D_REF_BUDGET_S", "240"))
+    t_start = time.perf_counter()
+    if kind == "sample":
+        r = cpu_sampler_baseline(cores, steps=max(1, min(a.steps, 5)))
+        line = {"impl": "reference", "metric": "sampler_frames_per_s", "value": r["value"], "unit": r["unit"],
+                "n_gpus": a.gpus, "steps": max(1, min(a.steps, 5)), "steps_requested": a.steps, "warmup": 0,
+                "ms_per_step": r["sec_per_step"] * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "f32", "data": "synthetic", "config": config, "cpu_baseline": r,
+                "e2e": {"value": r["value"], "unit": r["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return
+    b = CpuTrainCfg1(cores)
+    warm = 0
+    for _ in range(max(1, a.warmup)):
+        b.step()
+        warm += 1
+        if time.perf_counter() - t_start > 0.25 * budget:
+            break
+    times = []
+    for _ in range(a.steps):
+        times.append(b.step())
+        if time.perf_counter() - t_start > budget:
+            break
+    mean = sum(times) / len(times)
+    v = (b.N / frames) / mean
+    cb = {"value": v, "unit": "clips/s", "cores": cores, "kind": "port", "cpu": _cpu_name(),
+          "sample": f"each step = cfg1 exactly: 16 images 64x64 fp32 (clips/s quoted in {frames}-frame clips), HF wav2vec2-base + "
+                    f"oracle torso (attention checkpointed as unet.py:309) fwd+bwd+Adam over 110.7 M parameters; "
+                    f"{warm} warm-up + {len(times)} timed steps, mean {mean:.2f} s/step"}
+    print(json.dumps({"impl": "reference", "metric": "denoiser_train_clips_per_s", "value": v, "unit": "clips/s",
+                      "n_gpus": a.gpus, "steps": len(times), "steps_requested": a.steps, "warmup": warm,
+                      "ms_per_step": mean * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                      "dtype": "f32", "data": "synthetic", "config": config, "cpu_baseline": cb,
+                      "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
 
 
 def main():
@@ -391,36 +685,18 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="train64", choices=list(WORKLOADS))
+    ap.add_argument("--no-extras", action="store_true", help="train64 only: skip the sample128 / train128 / HBM-kernel extras")
     a = ap.parse_args()
     clips, frames, S, kind = WORKLOADS[a.workload]
     rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     cores = os.cpu_count() or 1
-    config = {"workload": f"{a.workload}: denoiser {kind} step, {clips} clips x {frames} frames {S}x{S} per GPU "
-                          f"(N={clips * frames} images folded into the batch), UNetAudio train.py config + wav2vec2-base",
-              "clips_per_gpu": clips, "frames": frames, "image": S, "parallelism": f"dp{world}",
-              "l2_policy": "inputs+activations >> L2 (126 MB): >10 GB touched per step"}
-    if kind == "train3d":
-        config["workload"] = (f"{a.workload}: UNetModel(dims=3) train step on {clips} clip(s) (195, {frames}, {S}, {S}) per GPU, "
-                              f"train.py torso config (64 ch, mult (1,2,4), 2 res blocks, attention at all levels over "
-                              f"L = T*S*S = {frames * S * S} positions), MSE + backward + Adam, no audio encoder")
+    config = _config(a.workload, clips, frames, S, kind, world)
+    no_cpu = os.environ.get("B2D_BENCH_NO_CPU") == "1"      # profiling / development runs: skip the host-side legs
 
     if a.impl == "reference":
-        # The reference is PyTorch-CPU here (/root/reference does not travel): its oracle port, all host threads.
-        if rank != 0:
-            return
-        vals = []
-        for _ in range(max(1, min(a.steps, 3))):
-            n, sec, reps = cpu_baseline(S, cores, seconds_budget=40.0)
-            vals.append((n / frames) / sec)
-        v = sorted(vals)[len(vals) // 2]
-        print(json.dumps({"impl": "reference", "metric": "denoiser_train_clips_per_s", "value": v, "unit": "clips/s",
-                          "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup, "ms_per_step": 1000.0 * (2 / frames) / v,
-                          "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-                          "data": "synthetic", "config": config,
-                          "cpu_baseline": {"value": v, "unit": "clips/s", "cores": cores, "kind": "port",
-                                           "sample": f"2 images {S}x{S} (1/{frames // 2 if frames >= 2 else 1} clip): torso fwd+bwd fp32, no wav2vec2/Adam"},
-                          "e2e": {"value": v, "unit": "clips/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        if rank == 0:
+            main_reference(a, frames, config, cores, kind)
         return
 
     assert torch.cuda.is_available(), "bench.py needs a B200; there is no CPU fallback for the product path"
@@ -430,136 +706,58 @@ def main():
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=device)
-    from lipreading_video_generation_b200 import _lib as L, ops
-    from lipreading_video_generation_b200.parallel import broadcast_parameters
+    from lipreading_video_generation_b200 import _lib as L
     L.check(L.lib().b2d_check_device(), "b2d_check_device")
-    n_img = clips * frames
     if kind == "train3d":
         return main_train3d(a, S, clips, frames, world, rank, local, device, config, cores)
-    model = build_model(S, device)
-    if world > 1:
-        broadcast_parameters(model)
+
     if kind == "sample":
-        return main_sample(a, model, S, clips, frames, world, rank, local, device, config, cores)
-    step = TrainStep(model, S, world, device)
-    x0, cond, audio = make_batch(n_img, S, 1234 + rank, device)
-    hx0, hcond, haudio = make_batch(n_img, S, 1234 + rank, device, pinned=True)
-    gt = torch.Generator().manual_seed(99 + rank)
-    t_dev = torch.randint(0, 1000, (n_img,), generator=gt).to(device)
-    t_host = torch.randint(0, 1000, (n_img,), generator=gt).pin_memory()
-
-    def barrier():
-        if world > 1:
-            torch.distributed.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(a.warmup):
-        step(x0, cond, audio, t_dev)
-    # ---------------- timed region 1: inputs resident in HBM ("value") + roofline events on attention kernels
-    barrier()
-    l0 = L.lib().b2d_launch_count()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    # only the candidate dominant kernels carry events inside the timed region (26 launches per step); the full
-    # per-class breakdown (~530 event pairs per step, which costs 2-3 ms of step time) runs in an untimed pass below
-    with ClockSampler(local) as clk, ops.KernelTimer({"attention_fwd", "attention_bwd"}) as kt:
-        e0.record()
-        h0 = time.perf_counter()
-        for _ in range(a.steps):
-            step(x0, cond, audio, t_dev)
-        host_ms = (time.perf_counter() - h0) * 1e3 / a.steps     # host time to enqueue one step (no sync inside)
-        e1.record()
-        barrier()
-    ms = e0.elapsed_time(e1) / a.steps
-    launches = (L.lib().b2d_launch_count() - l0) // a.steps
-    # ---------------- timed region 2: end to end through the public API with HOST buffers
-    barrier()
-    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    f0.record()
-    # the loss of every step is copied to pinned host memory and READ on the host one step later (after the next step
-    # has been enqueued), the last one before the timer stops: logging the loss does not drain the launch queue
-    loss_pin = [torch.zeros((), dtype=torch.float32).pin_memory() for _ in range(2)]
-    loss_ev = [torch.cuda.Event() for _ in range(2)]
-    losses_host = []
-    for i in range(a.steps):
-        dx0 = hx0.to(device, non_blocking=True); dc = hcond.to(device, non_blocking=True)
-        da = haudio.to(device, non_blocking=True); dt = t_host.to(device, non_blocking=True)
-        loss = step(dx0, dc, da, dt)
-        loss_pin[i % 2].copy_(loss.detach(), non_blocking=True)     # device -> host read of the step's result
-        loss_ev[i % 2].record()
-        if i > 0:
-            loss_ev[(i - 1) % 2].synchronize()
-            losses_host.append(float(loss_pin[(i - 1) % 2]))
-    loss_ev[(a.steps - 1) % 2].synchronize()
-    losses_host.append(float(loss_pin[(a.steps - 1) % 2]))
-    loss_host = losses_host[-1]
-    assert len(losses_host) == a.steps
-    f1.record()
-    barrier()
-    ms_e2e = f0.elapsed_time(f1) / a.steps
-    # ---------------- untimed diagnostic pass: per-class kernel time of one step
-    with ops.KernelTimer({"attention_fwd", "attention_bwd", "conv2d", "conv2d_wgrad", "groupnorm_fwd", "groupnorm_bwd"}) as kt_all:
-        step(x0, cond, audio, t_dev)
-        barrier()
-    if world > 1:
-        tt = torch.tensor([ms, ms_e2e], device=device)
-        torch.distributed.all_reduce(tt, op=torch.distributed.ReduceOp.MAX)
-        ms, ms_e2e = tt.tolist()
-    if rank != 0:
+        rec = measure_sample(a.steps, a.warmup, S, clips, frames, world, rank, local, device)
+        out = {"metric": "sampler_frames_per_s", "n_gpus": world, "higher_is_better": True, "scaling": "weak",
+               "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config, **rec}
+        if rank == 0:
+            out["cpu_baseline"] = None if no_cpu else cpu_sampler_baseline(cores)
+            print(json.dumps(out))
         if world > 1:
             torch.distributed.destroy_process_group()
         return
-    burst, sustained, hbm, which = peaks()
-    # roofline of the dominant kernel class: full-resolution (ch = 64) attention, forward
-    tot = kt.totals()
-    dom = None
-    by_class = {}
-    for (name, meta), (t_ms, cnt) in kt_all.totals().items():
-        by_class[name] = by_class.get(name, 0.0) + t_ms
-        print(f"[kernel] {name:14s} {str(meta):40s} x{cnt:3d}/step  {t_ms / cnt:8.4f} ms/launch  {t_ms:8.3f} ms/step",
-              file=sys.stderr)
-    for (name, meta), (t_ms, cnt) in tot.items():
-        if not name.startswith("attention"):
-            continue
-        Nn, Lq, heads, ch = meta
-        flops = (4.0 if name == "attention_fwd" else 10.0) * Lq * Lq * ch * heads * Nn
-        rec = dict(kernel=f"{name} L={Lq} ch={ch}", ms_per_launch=t_ms / cnt, launches_per_step=cnt // a.steps,
-                   tflops=flops / (t_ms / cnt) / 1e9, ms_per_step=t_ms / a.steps)
-        if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
-            dom = rec
-    traffic = None          # DRAM bytes per launch of the dominant kernel from one `ncu --set full` capture
-    try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r1_traffic.json")) as f:
-            tj = json.load(f)
-        if dom["kernel"] == "attention_bwd L=4096 ch=64" and n_img == 256:
-            traffic = tj["traffic_bytes_per_launch"]
-    except (OSError, KeyError, ValueError):
-        pass
-    roof = {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
-            "frac": round(dom["tflops"] / sustained, 4), "traffic": traffic, "kernel": dom["kernel"],
-            "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms, 3),
-            "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which}); algorithmic FLOPs 4*L^2*ch*N fwd, 10*L^2*ch*N bwd"}
-    if os.environ.get("B2D_BENCH_NO_CPU") == "1":          # profiling runs only (ncu): skip the host-side leg
-        n_cpu, sec_cpu, reps = 2, float("inf"), 0
-    else:
-        n_cpu, sec_cpu, reps = cpu_baseline(S, cores)
-    cpu_v = (n_cpu / frames) / sec_cpu
-    value = clips * world / (ms / 1000.0)
-    train_tflop = 3 * FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
-    h2d = sum(t.numel() * t.element_size() for t in (hx0, hcond, haudio, t_host))
-    out = {"metric": "denoiser_train_clips_per_s", "value": round(value, 3), "unit": "clips/s", "n_gpus": world,
-           "steps": a.steps, "warmup": a.warmup, "ms_per_step": round(ms, 3), "higher_is_better": True,
-           "scaling": "weak", "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config,
-           "e2e": {"value": round(clips * world / (ms_e2e / 1000.0), 3), "unit": "clips/s", "h2d_bytes_per_step": h2d,
-                   "d2h_bytes_per_step": 4, "ms_per_step": round(ms_e2e, 3)},
-           "gpu_launches": int(launches), "host_enqueue_ms_per_step": round(host_ms, 3), "roofline": roof,
-           "step_tflops_algorithmic": round(train_tflop / (ms / 1000.0), 1),
-           "step_frac_of_sustained_peak": round(train_tflop / (ms / 1000.0) / sustained, 4),
-           "cpu_baseline": {"value": round(cpu_v, 5), "unit": "clips/s", "cores": cores, "kind": "port",
-                            "sample": f"{n_cpu} images {S}x{S}: oracle torso fwd+bwd fp32, median of {reps}, {sec_cpu:.2f} s"},
-           "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
-           "clocks": clk.summary(), "last_loss": loss_host}
-    print(json.dumps(out))
+
+    rec = measure_train(a.steps, a.warmup, S, clips, frames, world, rank, local, device, verbose=True)
+    if rec["roofline"]["kernel"] == "attention_bwd L=4096 ch=64" and clips * frames == 256:
+        try:          # DRAM bytes per launch of the dominant kernel from one `ncu --set full` capture at this shape
+            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
+                rec["roofline"]["traffic"] = json.load(f)["traffic_bytes_per_launch"]
+        except (OSError, KeyError, ValueError):
+            pass
+    out = {"metric": "denoiser_train_clips_per_s", "n_gpus": world, "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config, **rec}
+    extras = {}
+    if a.workload == "train64" and not a.no_extras:
+        ks = max(3, min(a.steps, 5))
+        c2, f2, s2, _ = WORKLOADS["sample128"]
+        r = measure_sample(ks, 3, s2, c2, f2, world, rank, local, device)
+        r["config"] = _config("sample128", c2, f2, s2, "sample", world)
+        extras["sample128"] = r
+        c3, f3, s3, _ = WORKLOADS["train128"]
+        r = measure_train(max(3, min(a.steps, 3)), 3, s3, c3, f3, world, rank, local, device)
+        r["config"] = _config("train128", c3, f3, s3, "train", world)
+        extras["train128"] = r
+        if rank == 0:
+            extras["hbm_kernels"] = measure_hbm_kernels(device)
     if world > 1:
+        torch.distributed.barrier()
+    if rank == 0:
+        if no_cpu:
+            out["cpu_baseline"] = {"value": None, "unit": "clips/s", "cores": cores, "kind": "port", "sample": "skipped (B2D_BENCH_NO_CPU=1)"}
+        else:
+            out["cpu_baseline"] = cpu_train_baseline(cores, frames)
+            if "sample128" in extras:
+                extras["sample128"]["cpu_baseline"] = cpu_sampler_baseline(cores)
+        if extras:
+            out["extra"] = extras
+        print(json.dumps(out))
+    if world > 1:
+        torch.distributed.barrier()
         torch.distributed.destroy_process_group()
 
 

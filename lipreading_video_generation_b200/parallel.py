@@ -34,21 +34,74 @@ def plan_buckets(stage_end, bucket_elems):
 
 
 class GradientAllReducer:
-    """Attach to a UNetModel / UNetAudio: averages the torso gradients across ranks during backward and the
-    remaining parameters (the wav2vec2 encoder) in `finish()`, which must run before optimizer.step()."""
+    """Attach to a UNetModel / UNetAudio: averages every gradient across the ranks while backward is still running.
 
-    def __init__(self, model, group=None, bucket_mb: float = 25.0):
+    Torso: the engine writes all torso gradients into one flat fp32 buffer in backward-completion order; its stage hook
+    all-reduces contiguous >= `bucket_mb` slices on a side stream as soon as the stages that fill them are done.
+
+    Every other parameter (the wav2vec2 encoder, 94 M of the 110 M parameters) lives in ONE persistent flat fp32 buffer
+    with a FIXED layout over all of them (reverse registration order = the order autograd finishes them, cut into
+    >= `bucket_mb` buckets).  A post-accumulate-grad hook per parameter counts its bucket down; when the last gradient
+    of a bucket has arrived the bucket's gradients are copied into the flat buffer by one multi-tensor copy, the slice
+    is all-reduced on the side stream -- while the encoder's backward continues -- and `p.grad` becomes a view of the
+    buffer (nothing is copied back).  A parameter that received no gradient on this rank (HF LayerDrop skips whole
+    encoder layers per rank and step) contributes zeros: the collective's length never depends on which layers ran,
+    which is what made the round-1 `torch.cat` of the present gradients unsafe.  Buckets are issued STRICTLY in index
+    order on every rank (NCCL matches collectives by issue order): forward pre-hooks on the modules that own the
+    parameters record which parameters take part in this step, so a bucket whose layer was skipped does not wait for
+    gradients that will never come; a bucket with an expected gradient still missing when backward ends is flushed by
+    `finish()`, which then makes the compute stream wait for the side stream; it must run before `optimizer.step()`."""
+
+    def __init__(self, model, group=None, bucket_mb: float = 25.0, force: bool = False):
         self.model, self.group = model, group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.active = self.world > 1 or force          # force: run the whole path on one rank (tests)
         self.bucket_elems = int(bucket_mb * (1 << 20) / 4)
         self._buckets = None
         self._next = 0
         self._comm = None
         self._torso_ids = {id(p) for p in model.engine().torso_params()}
-        self.other_params = [p for p in model.parameters() if id(p) not in self._torso_ids and p.requires_grad]
+        self.other_params = [p for p in reversed(list(model.parameters()))
+                             if id(p) not in self._torso_ids and p.requires_grad]
         model._grad_stage_hook = self._on_stage
         model._grad_final_hook = self._on_final
         self.bytes_reduced = 0
+        # ---- fixed layout of the non-torso gradients
+        self._flat = None
+        self._views = None
+        self._bucket_of = {}
+        self._obuckets = []                            # [lo, hi, [param indices]]
+        lo = off = 0
+        cur = []
+        for i, p in enumerate(self.other_params):
+            self._bucket_of[id(p)] = len(self._obuckets)
+            cur.append(i)
+            off += (p.numel() + 3) // 4 * 4            # 16-byte aligned views
+            if off - lo >= self.bucket_elems:
+                self._obuckets.append([lo, off, cur])
+                lo, cur = off, []
+        if cur:
+            self._obuckets.append([lo, off, cur])
+        self._other_total = off
+        self._remaining = [0] * len(self._obuckets)    # expected gradients of the bucket that have not arrived yet
+        self._expected = set()
+        self._next_other = 0                           # buckets [0, _next_other) have been issued this step
+        self._index = {id(p): i for i, p in enumerate(self.other_params)}
+        self._handles = []
+        if self.active:
+            for p in self.other_params:
+                self._handles.append(p.register_post_accumulate_grad_hook(self._on_param))
+            for mod in model.modules():
+                own = [p for p in mod.parameters(recurse=False) if id(p) in self._index]
+                if own:
+                    self._handles.append(mod.register_forward_pre_hook(self._make_expect(own)))
+
+    def detach(self):
+        for h in self._handles:
+            h.remove()
+        self._handles = []
+        self.model._grad_stage_hook = None
+        self.model._grad_final_hook = None
 
     def _stream(self, device):
         if self._comm is None and device.type == "cuda":
@@ -56,7 +109,7 @@ class GradientAllReducer:
         return self._comm
 
     def _all_reduce(self, t):
-        if self.world > 1:
+        if self.world > 1 or (self.active and dist.is_initialized()):
             if t.is_cuda:
                 dist.all_reduce(t, op=dist.ReduceOp.AVG, group=self.group)
             else:                                  # gloo (CPU tests) has no AVG
@@ -64,7 +117,21 @@ class GradientAllReducer:
                 t.div_(self.world)
         self.bytes_reduced += t.numel() * 4
 
+    def _reduce_async(self, view):
+        """All-reduce `view` on the side stream, ordered after everything enqueued on the current stream so far."""
+        comm = self._stream(view.device)
+        if comm is not None:
+            comm.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(comm):
+                self._all_reduce(view)
+            view.record_stream(comm)
+        else:
+            self._all_reduce(view)
+
+    # ---- torso: stage hooks of the engine's backward
     def _on_stage(self, G, stage):
+        if not self.active:
+            return
         if self._buckets is None:
             self._buckets = plan_buckets(G.stage_end, self.bucket_elems)
         if stage == 0:
@@ -72,31 +139,72 @@ class GradientAllReducer:
         while self._next < len(self._buckets) and self._buckets[self._next][0] <= stage:
             _, lo, hi = self._buckets[self._next]
             self._next += 1
-            view = G.flat[lo:hi]
-            comm = self._stream(view.device)
-            if comm is not None:
-                comm.wait_stream(torch.cuda.current_stream())
-                with torch.cuda.stream(comm):
-                    self._all_reduce(view)
-                view.record_stream(comm)
-            else:
-                self._all_reduce(view)
+            self._reduce_async(G.flat[lo:hi])
 
     def _on_final(self, G):
         if self._comm is not None:
             torch.cuda.current_stream().wait_stream(self._comm)
 
+    # ---- everything else: per-parameter hooks into the persistent flat buffer
+    def _ensure_flat(self, device):
+        if self._flat is None or self._flat.device != device:
+            self._flat = torch.zeros(max(self._other_total, 1), device=device, dtype=torch.float32)
+            self._views, off = [], 0
+            for p in self.other_params:
+                self._views.append(self._flat[off:off + p.numel()].view(p.shape))
+                off += (p.numel() + 3) // 4 * 4
+
+    def _make_expect(self, own):
+        def pre_hook(module, args):
+            if torch.is_grad_enabled():
+                for p in own:
+                    if id(p) not in self._expected:
+                        self._expected.add(id(p))
+                        self._remaining[self._bucket_of[id(p)]] += 1
+        return pre_hook
+
+    def _on_param(self, p):
+        b = self._bucket_of[id(p)]
+        if b < self._next_other:
+            raise RuntimeError("GradientAllReducer: a gradient arrived after its bucket had been all-reduced -- the "
+                               "parameter is used outside the forward() of the module that owns it")
+        if id(p) in self._expected:
+            self._expected.discard(id(p))
+            self._remaining[b] -= 1
+        while self._next_other < len(self._obuckets) and self._remaining[self._next_other] == 0 \
+                and self._next_other <= b:
+            self._launch_bucket(self._next_other)
+
+    def _launch_bucket(self, b):
+        lo, hi, idxs = self._obuckets[b]
+        ps = [self.other_params[i] for i in idxs]
+        self._ensure_flat(ps[0].device)
+        have = [(self._views[i], p.grad) for i, p in zip(idxs, ps)
+                if p.grad is not None and p.grad.data_ptr() != self._views[i].data_ptr()]
+        for i, p in zip(idxs, ps):
+            if p.grad is None:
+                self._views[i].zero_()
+        if have:
+            with torch.no_grad():
+                torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
+        self._reduce_async(self._flat[lo:hi])
+        for i, p in zip(idxs, ps):
+            p.grad = self._views[i]
+        self._next_other = b + 1
+
     def finish(self):
-        """All-reduce the gradients of the non-torso parameters (audio encoder) in one flat bucket."""
-        grads = [p.grad for p in self.other_params if p.grad is not None]
-        if not grads or self.world == 1:
+        """Flush the buckets whose parameters did not all receive a gradient this step, then make the compute stream
+        wait for every in-flight all-reduce.  Call between `loss.backward()` and `optimizer.step()`."""
+        if not self.active:
             return
-        flat = torch.cat([g.reshape(-1) for g in grads])
-        self._all_reduce(flat)
-        off = 0
-        for g in grads:
-            g.copy_(flat[off:off + g.numel()].view_as(g))
-            off += g.numel()
+        if self.other_params:
+            for b in range(self._next_other, len(self._obuckets)):
+                self._launch_bucket(b)
+            self._remaining = [0] * len(self._obuckets)
+            self._expected.clear()
+            self._next_other = 0
+        if self._comm is not None:
+            torch.cuda.current_stream().wait_stream(self._comm)
 
 
 def shard_rows(L: int, rank: int, world: int, align: int = 256):

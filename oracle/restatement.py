@@ -169,12 +169,25 @@ def attention_block(sd, pre, x, n_heads, new_order=False):
     return (xr + h).reshape(b, c, *spatial)
 
 
+def _attention_block_checkpointed(sd, pre, x, n_heads, new_order):
+    """unet.py:308-309 + utils.py:161-207: the reference ALWAYS runs AttentionBlock under its activation checkpoint
+    (forward re-run inside backward, the L x L matrices are not kept).  Same values and gradients as attention_block;
+    used by the timed CPU baseline so that its work and memory are the reference's."""
+    from torch.utils.checkpoint import checkpoint
+    keys = [pre + k for k in ("norm.weight", "norm.bias", "qkv.weight", "qkv.bias", "proj_out.weight", "proj_out.bias")]
+
+    def run(x_, *ws):
+        return attention_block(dict(zip(keys, ws)), pre, x_, n_heads, new_order)
+    return checkpoint(run, x, *[sd[k] for k in keys], use_reentrant=False)
+
+
 def unet_forward(sd, cfg, x, timesteps):
     """unet.py:646-675 with the block structure of unet.py:497-628 re-derived from cfg =
-    dict(model_channels, num_res_blocks, attention_resolutions, channel_mult, num_heads[, new_order]).
-    dims=3 (x of rank 5, Conv3d weights in sd) follows the same code through conv_nd."""
+    dict(model_channels, num_res_blocks, attention_resolutions, channel_mult, num_heads[, new_order]
+    [, checkpoint_attention]).  dims=3 (x of rank 5, Conv3d weights in sd) follows the same code through conv_nd."""
     mc, nrb = cfg["model_channels"], cfg["num_res_blocks"]
     heads, new_order = cfg.get("num_heads", 1), cfg.get("new_order", False)
+    attention_block = _attention_block_checkpointed if cfg.get("checkpoint_attention") else globals()["attention_block"]
     emb = F.linear(timestep_embedding(timesteps, mc), sd["time_embed.0.weight"], sd["time_embed.0.bias"])
     emb = F.linear(F.silu(emb), sd["time_embed.2.weight"], sd["time_embed.2.bias"])
     hs = []

@@ -54,6 +54,7 @@ def _worker(rank, world, port, q):
             def __init__(self):
                 super().__init__()
                 self.w = torch.nn.Parameter(torch.zeros(7))
+                self.dropped = torch.nn.Parameter(torch.zeros(5))     # a layer LayerDrop skips on rank 1 only
 
             def forward(self, a):
                 return a["feats"]
@@ -85,10 +86,23 @@ def _worker(rank, world, port, q):
         m._grad_final_hook(G)
         assert reduced_upto == n
         assert len(red._buckets) > 1
+        # non-torso parameters: fixed flat layout over ALL of them; a gradient missing on one rank counts as zeros
+        # (round-1 advisor finding: ranks all-reduced flat tensors of different lengths when LayerDrop differed)
         m.audio_encoder.w.grad = torch.full((7,), float(rank + 1))
+        if rank == 0:
+            m.audio_encoder.dropped.grad = torch.full((5,), 4.0)
         red.finish()
         assert torch.allclose(m.audio_encoder.w.grad, torch.full((7,), sum(range(1, world + 1)) / world))
-        assert red.bytes_reduced == 4 * (n + 7)
+        assert torch.allclose(m.audio_encoder.dropped.grad, torch.full((5,), 4.0 / world))
+        assert m.audio_encoder.w.grad.data_ptr() == red._views[red._index[id(m.audio_encoder.w)]].data_ptr()
+        assert red.bytes_reduced == 4 * (n + 8 + 8)               # views are padded to 16 bytes
+        # the hook path: gradients arriving through autograd trigger their bucket without finish() copying back
+        m.audio_encoder.w.grad = None
+        m.audio_encoder.dropped.grad = None
+        (m.audio_encoder.w * float(rank + 1)).sum().backward()
+        red.finish()
+        assert torch.allclose(m.audio_encoder.w.grad, torch.full((7,), sum(range(1, world + 1)) / world))
+        assert float(m.audio_encoder.dropped.grad.abs().sum()) == 0.0
         dist.destroy_process_group()
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
