@@ -134,9 +134,33 @@ typedef struct b2d_conv_args {
   const void* residual; int64_t ldres;       /* fp16 (N,Ho,Wo,ldres) added in the epilogue, or NULL */
   void* out; int64_t ldo;                    /* fp16 (N,Ho,Wo,ldo) or NULL */
   float* out_nchw_f32;                       /* optional fp32 (N,Cout,Ho,Wo) output (model output) */
+  /* ---- optional GroupNorm pieces fused into the epilogue (north_star item 2: "fused GroupNorm/SiLU/residual
+   * epilogues"; utils.py:54-56, unet.py:194-198,218-225,297).  Both need the staged epilogue (Cout % 64 == 0, fp16
+   * `out`), Ho*Wo % 32 == 0 and (images per 128-pixel tile) * (channels per tile) <= 256; b2d_conv2d_gn_fusable()
+   * tells.  All NULL / 0 = plain convolution. */
+  /* (1) statistics of the OUTPUT for the GroupNorm that consumes it: gn_stats_out[n][c/2][0..1] += sum / sum of
+   * squares over the pixels of image n of output channels (c, c+1), from the fp32 epilogue values.  fp64
+   * [N][Cout/2][2], caller zeroes.  The consumer (b2d_groupnorm_apply) forms its 32 group moments from these pairs,
+   * also across the two tensors of a skip concatenation -- the separate statistics pass over the tensor disappears. */
+  double* gn_stats_out;
+  /* (2) this convolution is the DATA GRADIENT that produces dL/dy for y = act(GroupNorm(x)) [* dropout mask]: the
+   * epilogue turns the accumulator dy into dyh = dy * act'(z) * mask/(1-p) (z = xhat*gamma + beta, from the saved mean
+   * / rstd and x loaded by TMA exactly like a residual tile), stores dyh in `out`, and accumulates
+   * gnb_ab[n][c][0..1] += (sum_pixels dyh, sum_pixels dyh * x): the reduce pass of the GroupNorm backward.
+   * x = [gnb_x1 | gnb_x2] (C1 multiple of 64, C1 + C2 == Cout); mean / rstd fp32 [N][32]; gamma / beta fp32 [Cout];
+   * gnb_mask: dropout keep bits written by b2d_groupnorm_apply ((N, Ho*Wo, Cout/8) bytes) or NULL. */
+  const void* gnb_x1; int64_t gnb_ld1; int gnb_C1;
+  const void* gnb_x2; int64_t gnb_ld2;
+  const float* gnb_mean; const float* gnb_rstd;
+  const float* gnb_gamma; const float* gnb_beta;
+  int gnb_act;
+  const uint8_t* gnb_mask; float gnb_keep_scale;
+  float* gnb_ab;                             /* fp32 [N][Cout][2], accumulated (caller zeroes) */
 } b2d_conv_args;
 
 int b2d_conv2d(const b2d_conv_args* a, void* stream);
+/* 1 when a convolution with this output plane / channel count can carry the fused GroupNorm pieces above. */
+int b2d_conv2d_gn_fusable(int Ho, int Wo, int Cout);
 
 /* Weight gradient of the same convolution (fp32, ACCUMULATED into dw):
  *   dw[co][tap][ci] += sum_{n,ho,wo} dy[n,ho,wo,co] * X[n, ho*s+dy-p, wo*s+dx-p, ci]
@@ -193,6 +217,28 @@ int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, c
                       void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
                       const void* add_b, int64_t ldb, int add_a_full, float* dx1_colsum, int64_t ld_colsum,
                       float* dgamma, float* dbeta, void* workspace, size_t workspace_bytes, void* stream);
+
+/* ---- GroupNorm with producer-fused statistics (the path the engine uses; the two calls above remain for inputs
+ * that no fused convolution produced).
+ * b2d_pair_stats: st[n][c/2][0..1] += (sum, sum of squares) over the HW pixels of sample n of channels (c, c+1) of
+ *   x fp16 (N, HW, ld): the same quantity b2d_conv2d's gn_stats_out emits (fp64 [N][C/2][2], caller zeroes).
+ * b2d_groupnorm_apply: y = [dropout](act(GroupNorm([x1 | x2]))) in ONE pass over the input: the group moments come
+ *   from the pair sums st1 (for x1) / st2 (for x2, NULL when there is no x2).  rows_per_sample > 1: sample n of this
+ *   call is rows_per_sample consecutive rows of the statistics (dims=3: the T frames of a clip were convolved as
+ *   separate images).  mean / rstd fp32 [N][32] are written for the backward.  mask_out (optional, (N, HW, Ctot/8)
+ *   bytes): dropout keep bits, bit i of byte j = channel 8j + i, for the fused backward.
+ * b2d_groupnorm_bwd_apply: the input-gradient pass given dyh = dy * act'(z) * mask (what the fused data-gradient
+ *   epilogue stores) and ab[n][c] = (sum dyh, sum dyh * x) (fp32 [N][Ctot][2]):
+ *     dx = rstd * (dyh*gamma - mean_g(dyh*gamma) - xhat * mean_g(dyh*gamma*xhat))  (+ add_a + add_b as above),
+ *   and dgamma[c] += sum_n rstd*(ab1 - mean*ab0), dbeta[c] += sum_n ab0.  overflow (optional, int32, accumulated):
+ *   number of threads that saw |dyh| or |dx| >= 65504, i.e. a saturated fp16 gradient (fp16_util.py:236-237). */
+int b2d_pair_stats(const void* x, int64_t ld, int C, int N, int HW, double* st, void* stream);
+int b2d_groupnorm_apply(const b2d_gn_args* a, const double* st1, const double* st2, int rows_per_sample, void* y,
+                        float* mean, float* rstd, uint8_t* mask_out, void* stream);
+int b2d_groupnorm_bwd_apply(const b2d_gn_args* a, const void* dyh, const float* mean, const float* rstd,
+                            const float* ab, void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a,
+                            int64_t lda, const void* add_b, int64_t ldb, int add_a_full, float* dx1_colsum,
+                            int64_t ld_colsum, float* dgamma, float* dbeta, int* overflow, void* stream);
 
 /* ------------------------------------------------------------------------
  * Layout / conditioning helpers (HBM bound).

@@ -29,6 +29,12 @@ class ConvArgs(C.Structure):
         ("residual", c_void_p), ("ldres", c_int64),
         ("out", c_void_p), ("ldo", c_int64),
         ("out_nchw_f32", c_void_p),
+        ("gn_stats_out", c_void_p),
+        ("gnb_x1", c_void_p), ("gnb_ld1", c_int64), ("gnb_C1", c_int),
+        ("gnb_x2", c_void_p), ("gnb_ld2", c_int64),
+        ("gnb_mean", c_void_p), ("gnb_rstd", c_void_p), ("gnb_gamma", c_void_p), ("gnb_beta", c_void_p),
+        ("gnb_act", c_int), ("gnb_mask", c_void_p), ("gnb_keep_scale", c_float),
+        ("gnb_ab", c_void_p),
     ]
 
 
@@ -73,7 +79,14 @@ SIGNATURES = {
     "b2d_mse_fwd": (c_int, [c_void_p, c_void_p, c_int64, c_void_p, c_size_t, c_void_p, c_void_p]),
     "b2d_mse_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_int64, c_void_p, c_void_p]),
     "b2d_conv2d": (c_int, [C.POINTER(ConvArgs), c_void_p]),
+    "b2d_conv2d_gn_fusable": (c_int, [c_int, c_int, c_int]),
     "b2d_conv2d_wgrad": (c_int, [C.POINTER(WgradArgs), c_void_p]),
+    "b2d_pair_stats": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_void_p, c_void_p]),
+    "b2d_groupnorm_apply": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                    c_void_p]),
+    "b2d_groupnorm_bwd_apply": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
+                                        c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64,
+                                        c_void_p, c_void_p, c_void_p, c_void_p]),
     "b2d_attention_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p,
                                   c_void_p]),
     "b2d_pack_conv_weight": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int,

@@ -15,6 +15,7 @@
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
+#include <mutex>
 
 namespace b2d {
 using namespace umma;
@@ -22,14 +23,26 @@ using namespace umma;
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(count) : "memory");
 }
+__device__ __forceinline__ void red_shared_add_f32(uint32_t saddr, float v) {
+  asm volatile("red.shared.add.f32 [%0], %1;" :: "r"(saddr), "f"(v) : "memory");
+}
 
 struct ConvMaps {
   CUtensorMap a[4];  // source 1 (4 phases when stride == 2, else a[0])
   CUtensorMap a2;    // source 2 (stride 1 only)
   CUtensorMap b;     // weights
   CUtensorMap o;     // output   (N,Ho,Wo,ldo): box (64, Wo, rows, imgs)   [TMA-store epilogue]
-  CUtensorMap r;     // residual (N,Ho,Wo,ldres): same box
+  CUtensorMap r;     // residual (N,Ho,Wo,ldres): same box; EPI_GNB: the GroupNorm input x1
+  CUtensorMap r2;    // EPI_GNB: the GroupNorm input x2 (second tensor of a skip concatenation)
 };
+
+// Epilogue variants (template parameter of the kernel; the plain one carries none of the extra code):
+//   EPI_PLAIN  bias + emb + residual
+//   EPI_STATS  the same, plus per-(image, channel pair) sum / sum of squares of the output for the GroupNorm that
+//              consumes it (b2d_conv_args.gn_stats_out)
+//   EPI_GNB    data-gradient convolution whose output is dL/dy of y = act(GroupNorm(x)): stores dyh = dy * act'(z) * mask
+//              and accumulates (sum dyh, sum dyh * x) per (image, channel) (b2d_conv_args.gnb_*)
+constexpr int EPI_PLAIN = 0, EPI_STATS = 1, EPI_GNB = 2;
 
 struct ConvParams {
   int taps, ksize, stride;
@@ -49,12 +62,42 @@ struct ConvParams {
   const __half* residual; long long ldres;
   __half* out; long long ldo;
   float* out_nchw;
+  // EPI_STATS
+  double* stats;           // [N][Cout/2][2]
+  // EPI_GNB
+  int gnb_C1, gnb_cpg, gnb_act;
+  const float* gnb_mean; const float* gnb_rstd; const float* gnb_gamma; const float* gnb_beta;
+  const uint8_t* gnb_mask; float gnb_keep_scale;
+  float* gnb_ab;           // [N][Cout][2]
 };
 
 constexpr int CONV_THREADS = 192;
 constexpr int EB_FLOATS = 512;              // images per tile x BN <= 512 (bias + emb staging)
+constexpr int SACC_FLOATS = 512;            // fused GroupNorm sums of one tile: images per tile x BN x 2 <= 512
 constexpr int A_TILE_BYTES = 128 * 128;  // 128 pixels x 64 bf16
 
+// Sum 16 per-lane values over the 32 lanes of a warp with 16 shuffles (reduce-scatter): on return v[0] of lane l holds
+// the warp total of value index ((l>>4)&1)*8 + ((l>>3)&1)*4 + ((l>>2)&1)*2 + ((l>>1)&1) (lanes l and l^1 hold the same).
+__device__ __forceinline__ void warp_reduce_scatter16(float* v, int lane) {
+#define B2D_RS_STEP(HALF, BIT)                                                      \
+  {                                                                                 \
+    const bool up = (lane & BIT) != 0;                                              \
+    _Pragma("unroll") for (int i = 0; i < HALF; ++i) {                              \
+      const float send = up ? v[i] : v[i + HALF];                                   \
+      const float keep = up ? v[i + HALF] : v[i];                                   \
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, BIT);                        \
+    }                                                                               \
+  }
+  B2D_RS_STEP(8, 16) B2D_RS_STEP(4, 8) B2D_RS_STEP(2, 4) B2D_RS_STEP(1, 2)
+  v[0] += __shfl_xor_sync(0xffffffffu, v[0], 1);
+}
+// The same for 32 values with 31 shuffles: lane l ends with the total of value index l.
+__device__ __forceinline__ void warp_reduce_scatter32(float* v, int lane) {
+  B2D_RS_STEP(16, 16) B2D_RS_STEP(8, 8) B2D_RS_STEP(4, 4) B2D_RS_STEP(2, 2) B2D_RS_STEP(1, 1)
+#undef B2D_RS_STEP
+}
+
+template <int EPI>
 __global__ void __launch_bounds__(CONV_THREADS)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -71,6 +114,10 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   const uint32_t eb_base = smem_u32(tmem_slot + 4);   // float [2][EB_FLOATS]: bias + emb of the current tile
   uint64_t* res_full = (uint64_t*)(tmem_slot + 2);    // residual tile landed in the staging buffer
   uint8_t* stage_out = smem + (size_t)p.stages * stage_bytes + 1024 + 2 * EB_FLOATS * 4;   // 2 x [128 pix][64 ch] fp16, 1024-aligned
+  const uint32_t sacc_u32 = smem_u32(stage_out + 2 * A_TILE_BYTES);   // float [SACC_FLOATS]: fused GroupNorm sums of the tile
+  if (EPI != EPI_PLAIN) {
+    for (int i = threadIdx.x; i < SACC_FLOATS; i += CONV_THREADS) sts32f(sacc_u32 + (uint32_t)i * 4u, 0.f);
+  }
 
   // Persistent CTA: tiles tile0, tile0 + gridDim.x, ...; the TMA ring and the two TMEM accumulator buffers run
   // across tile boundaries, so tile i's epilogue overlaps tile i+1's loads and MMAs (the non-persistent
@@ -187,7 +234,18 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     const int hw = valid ? (int)(pix - (long long)n_img * p.HoWo) : 0;
     const int img_first = (int)(((long long)tile_m * 128) / p.HoWo);
     const uint32_t eb_u32 = eb_base + (uint32_t)buf * (EB_FLOATS * 4u);
-    if (has_eb) {
+    if (EPI == EPI_GNB) {
+      // per (image of the tile, channel): z = x * rg + bb with rg = rstd * gamma, bb = beta - mean * rg
+      for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
+        const int im = idx / p.BN, c = idx - im * p.BN;
+        const int col = n0 + c, img = min(img_first + im, p.n_images - 1);
+        const int g = col / p.gnb_cpg;
+        const float rs = __ldg(p.gnb_rstd + img * 32 + g), mu = __ldg(p.gnb_mean + img * 32 + g);
+        const float rg = rs * __ldg(p.gnb_gamma + col);
+        sts32f(eb_u32 + (uint32_t)idx * 8u, rg);
+        sts32f(eb_u32 + (uint32_t)idx * 8u + 4u, fmaf(-mu, rg, __ldg(p.gnb_beta + col)));
+      }
+    } else if (has_eb) {
       for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
         const int im = idx / p.BN, c = idx - im * p.BN;
         const int col = n0 + c, img = img_first + im;
@@ -205,10 +263,24 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     const int nblk = p.BN >> 6;
     if (p.tma_out && et == 0) {
       tma_store_wait_read();                           // previous tile's store has finished reading the staging buffer
-      if (p.residual) {
+      if (EPI == EPI_GNB) {                            // the GroupNorm input x = [x1 | x2], 64-channel block by block
+        mbar_expect_tx(res_full, (uint32_t)nblk * A_TILE_BYTES);
+        for (int b = 0; b < nblk; ++b) {
+          const int c = n0 + b * 64;
+          if (c < p.gnb_C1) tma_load_4d(stage_out + b * A_TILE_BYTES, &maps.r, res_full, c, 0, h0, img0);
+          else              tma_load_4d(stage_out + b * A_TILE_BYTES, &maps.r2, res_full, c - p.gnb_C1, 0, h0, img0);
+        }
+      } else if (p.residual) {
         mbar_expect_tx(res_full, (uint32_t)nblk * A_TILE_BYTES);
         for (int b = 0; b < nblk; ++b) tma_load_4d(stage_out + b * A_TILE_BYTES, &maps.r, res_full, n0 + b * 64, 0, h0, img0);
       }
+    }
+    uint4 mbits = make_uint4(0xffffffffu, 0xffffffffu, 0xffffffffu, 0xffffffffu);   // EPI_GNB: dropout keep bits of this row
+    if (EPI == EPI_GNB && p.gnb_mask != nullptr && valid) {
+      const uint8_t* mp = p.gnb_mask + (pix * p.Cout + n0) / 8;                      // 8-byte aligned (n0 % 64 == 0)
+      const uint2 lo = __ldg(reinterpret_cast<const uint2*>(mp));
+      mbits.x = lo.x; mbits.y = lo.y;
+      if (p.BN > 64) { const uint2 hi = __ldg(reinterpret_cast<const uint2*>(mp + 8)); mbits.z = hi.x; mbits.w = hi.y; }
     }
     const bool fast_cols = (n0 + p.BN <= p.Cout);      // whole tile inside the logical channels: vector path
     uint4 rres[16];                                    // residual row segment: up to 128 columns of fp16
@@ -227,7 +299,11 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       // ---- staged path: residual arrives by TMA in the 128B-swizzled tile layout, results go back to the same
       // smem slots (conflict-free 16-byte accesses) and leave with one TMA store per 64-channel block
       const uint32_t so_u32 = smem_u32(stage_out);
-      if (p.residual) mbar_wait(res_full, (uint32_t)(lt & 1));
+      if (EPI == EPI_GNB || p.residual) mbar_wait(res_full, (uint32_t)(lt & 1));
+      // fused GroupNorm sums: this warp's 32 rows belong to one image (Ho*Wo % 32 == 0, checked on the host)
+      const long long wpix = (long long)tile_m * 128 + q * 32;
+      const bool wvalid = wpix < p.total_pixels;
+      const int wslot = wvalid ? (int)(wpix / p.HoWo) - img_first : 0;
 #pragma unroll
       for (int cc = 0; cc < 8; ++cc) {
         const int c0 = cc * 16;
@@ -239,7 +315,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
           float v[16];
 #pragma unroll
           for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
-          if (has_eb) {
+          if (EPI != EPI_GNB && has_eb) {
 #pragma unroll
             for (int j4 = 0; j4 < 4; ++j4) {
               const float4 e = lds128f(eb_row + (uint32_t)(c0 + 4 * j4) * 4u);
@@ -248,11 +324,55 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
           }
           const uint32_t a0 = so_u32 + (uint32_t)(c0 >> 6) * A_TILE_BYTES + sw128_offset((uint32_t)row, (uint32_t)(c0 & 63));
           const uint32_t a1 = so_u32 + (uint32_t)(c0 >> 6) * A_TILE_BYTES + sw128_offset((uint32_t)row, (uint32_t)((c0 & 63) + 8));
-          if (p.residual) {
+          if (EPI == EPI_GNB) {
+            // v = dy.  dyh = dy * silu'(z) * mask / (1 - p);  sums of dyh and dyh * x over the warp's 32 pixels
+            const uint4 u0 = lds128(a0), u1 = lds128(a1);
+            const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
+            float x[16];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { float2 f = unpack_f16x2(w[j]); x[2 * j] = f.x; x[2 * j + 1] = f.y; }
+            const uint32_t cst = eb_u32 + (uint32_t)((valid ? n_img - img_first : 0) * p.BN + c0) * 8u;
+            const uint32_t mword = cc < 2 ? mbits.x : cc < 4 ? mbits.y : cc < 6 ? mbits.z : mbits.w;
+            const uint32_t m16 = (mword >> ((cc & 1) * 16)) & 0xffffu;
+            float red[32];
+#pragma unroll
+            for (int j2 = 0; j2 < 8; ++j2) {
+              const float4 c4 = lds128f(cst + (uint32_t)j2 * 16u);      // (rg, bb) of channels 2*j2, 2*j2 + 1
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const int j = 2 * j2 + h;
+                float dh = v[j];
+                if (p.gnb_act) {
+                  const float z = fmaf(x[j], h ? c4.z : c4.x, h ? c4.w : c4.y);
+                  const float sg = fast_sigmoid(z);
+                  dh *= sg * fmaf(z, 1.0f - sg, 1.0f);
+                }
+                dh = ((m16 >> j) & 1u) ? dh * p.gnb_keep_scale : 0.f;
+                v[j] = dh;
+                red[2 * j] = wvalid ? dh : 0.f;
+                red[2 * j + 1] = wvalid ? dh * x[j] : 0.f;
+              }
+            }
+            warp_reduce_scatter32(red, lane);                           // lane l: channel c0 + l/2, quantity l & 1
+            red_shared_add_f32(sacc_u32 + (uint32_t)((wslot * p.BN + c0) * 2 + lane) * 4u, red[0]);
+          } else if (p.residual) {
             const uint4 u0 = lds128(a0), u1 = lds128(a1);
             const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
             for (int j = 0; j < 8; ++j) { float2 f = unpack_f16x2(w[j]); v[2 * j] += f.x; v[2 * j + 1] += f.y; }
+          }
+          if (EPI == EPI_STATS) {
+            float red[16];                                              // 8 channel pairs x (sum, sum of squares)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              red[2 * j] = wvalid ? v[2 * j] + v[2 * j + 1] : 0.f;
+              red[2 * j + 1] = wvalid ? fmaf(v[2 * j], v[2 * j], v[2 * j + 1] * v[2 * j + 1]) : 0.f;
+            }
+            warp_reduce_scatter16(red, lane);
+            if ((lane & 1) == 0) {
+              const int vi = ((lane >> 4) & 1) * 8 + ((lane >> 3) & 1) * 4 + ((lane >> 2) & 1) * 2 + ((lane >> 1) & 1);
+              red_shared_add_f32(sacc_u32 + (uint32_t)(wslot * p.BN + c0 + vi) * 4u, red[0]);
+            }
           }
           uint4 o0, o1;
           o0.x = pack_f16x2(v[0], v[1]);   o0.y = pack_f16x2(v[2], v[3]);
@@ -270,6 +390,30 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       if (et == 0) {
         for (int b = 0; b < nblk; ++b) tma_store_4d(&maps.o, stage_out + b * A_TILE_BYTES, n0 + b * 64, 0, h0, img0);
         tma_store_commit();
+      }
+      if (EPI == EPI_STATS) {
+        // sacc[slot][BN] -> stats[img][(n0 + k) / 2][k & 1] (fp64), re-zeroed for the next tile (whose sums start
+        // after its named barrier 1, which this thread reaches only after the stores below)
+        for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
+          const int im = idx / p.BN, k = idx - im * p.BN;
+          const int img = img_first + im;
+          const uint32_t sa = sacc_u32 + (uint32_t)idx * 4u;
+          float val;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(val) : "r"(sa));
+          sts32f(sa, 0.f);
+          if (img < p.n_images) atomicAdd(p.stats + ((long long)img * (p.Cout >> 1) + ((n0 + k) >> 1)) * 2 + (k & 1), (double)val);
+        }
+      }
+      if (EPI == EPI_GNB) {
+        for (int idx = et; idx < imgs_in_tile * p.BN * 2; idx += 128) {
+          const int im = idx / (p.BN * 2), k = idx - im * p.BN * 2;
+          const int img = img_first + im;
+          const uint32_t sa = sacc_u32 + (uint32_t)idx * 4u;
+          float val;
+          asm volatile("ld.shared.f32 %0, [%1];" : "=f"(val) : "r"(sa));
+          sts32f(sa, 0.f);
+          if (img < p.n_images) atomicAdd(p.gnb_ab + ((long long)img * p.Cout + n0) * 2 + k, val);
+        }
       }
       continue;
     }
@@ -420,17 +564,44 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   const bool tma_out = a->out != nullptr && a->out_nchw_f32 == nullptr && a->Cout % 64 == 0 && BN % 64 == 0 &&
                        a->ldo % 8 == 0 && aligned16(a->out) &&
                        (a->residual == nullptr || (a->ldres % 8 == 0 && aligned16(a->residual)));
+  const bool want_stats = a->gn_stats_out != nullptr;
+  const bool want_gnb = a->gnb_ab != nullptr;
+  if (want_stats || want_gnb) {
+    B2D_REQUIRE(!(want_stats && want_gnb), B2D_ERR_SHAPE, "conv2d: gn_stats_out and gnb_* are exclusive");
+    B2D_REQUIRE(tma_out && b2d_conv2d_gn_fusable(Ho, Wo, a->Cout), B2D_ERR_SHAPE,
+                "conv2d: fused GroupNorm epilogue needs Cout %% 64 == 0, fp16 out, Ho*Wo %% 32 == 0 (Cout=%d, plane %dx%d)",
+                a->Cout, Ho, Wo);
+    B2D_REQUIRE((128 / (Ho * Wo) <= 1 ? 1 : 128 / (Ho * Wo)) * BN * 2 <= SACC_FLOATS, B2D_ERR_SHAPE,
+                "conv2d: fused GroupNorm epilogue: %d images x %d channels per tile exceed the staging", imgs, BN);
+  }
+  if (want_gnb) {
+    B2D_REQUIRE(a->residual == nullptr && a->bias == nullptr && a->emb == nullptr, B2D_ERR_SHAPE,
+                "conv2d: the GroupNorm-backward epilogue takes no bias / emb / residual");
+    B2D_REQUIRE(a->gnb_x1 && a->gnb_mean && a->gnb_rstd && a->gnb_gamma && a->gnb_beta, B2D_ERR_SHAPE,
+                "conv2d: gnb_* pointers missing");
+    const int gC2 = a->Cout - a->gnb_C1;
+    B2D_REQUIRE(a->gnb_C1 > 0 && a->gnb_C1 % 64 == 0 && gC2 >= 0 && gC2 % 64 == 0 && (gC2 == 0 || a->gnb_x2), B2D_ERR_SHAPE,
+                "conv2d: gnb channel split (%d, %d) must be multiples of 64", a->gnb_C1, gC2);
+    B2D_REQUIRE(a->Cout % 32 == 0 && a->gnb_ld1 % 8 == 0 && aligned16(a->gnb_x1) &&
+                (gC2 == 0 || (a->gnb_ld2 % 8 == 0 && aligned16(a->gnb_x2))), B2D_ERR_ALIGN, "conv2d: gnb inputs misaligned");
+  }
   if (tma_out) {
     rc = make_act_map(&maps.o, a->out, a->Cout, a->ldo, a->N, Ho, Wo, 1, Wo, rows, imgs);
     if (rc) return rc;
-    if (a->residual) {
+    maps.r = maps.o; maps.r2 = maps.o;
+    if (want_gnb) {
+      rc = make_act_map(&maps.r, a->gnb_x1, a->gnb_C1, a->gnb_ld1, a->N, Ho, Wo, 1, Wo, rows, imgs);
+      if (rc) return rc;
+      if (a->Cout > a->gnb_C1) {
+        rc = make_act_map(&maps.r2, a->gnb_x2, a->Cout - a->gnb_C1, a->gnb_ld2, a->N, Ho, Wo, 1, Wo, rows, imgs);
+        if (rc) return rc;
+      }
+    } else if (a->residual) {
       rc = make_act_map(&maps.r, a->residual, a->Cout, a->ldres, a->N, Ho, Wo, 1, Wo, rows, imgs);
       if (rc) return rc;
-    } else {
-      maps.r = maps.o;
     }
   } else {
-    maps.o = maps.a[0]; maps.r = maps.a[0];
+    maps.o = maps.a[0]; maps.r = maps.a[0]; maps.r2 = maps.a[0];
   }
 
   ConvParams p;
@@ -454,20 +625,42 @@ extern "C" int b2d_conv2d(const b2d_conv_args* a, void* stream) {
   p.residual = (const __half*)a->residual; p.ldres = a->ldres;
   p.out = (__half*)a->out; p.ldo = a->ldo;
   p.out_nchw = a->out_nchw_f32;
+  p.stats = a->gn_stats_out;
+  p.gnb_C1 = a->gnb_C1; p.gnb_cpg = a->Cout / 32 > 0 ? a->Cout / 32 : 1; p.gnb_act = a->gnb_act;
+  p.gnb_mean = a->gnb_mean; p.gnb_rstd = a->gnb_rstd; p.gnb_gamma = a->gnb_gamma; p.gnb_beta = a->gnb_beta;
+  p.gnb_mask = a->gnb_mask; p.gnb_keep_scale = a->gnb_mask ? a->gnb_keep_scale : 1.0f;
+  p.gnb_ab = a->gnb_ab;
 
-  const size_t smem = (size_t)stages * stage_bytes + 1024 /* barriers */ + 2 * EB_FLOATS * 4 + 2 * A_TILE_BYTES + 1024;
-  static size_t smem_set = 0;
-  if (smem > smem_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(conv_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    smem_set = 200 * 1024;
-  }
+  const size_t smem = (size_t)stages * stage_bytes + 1024 /* barriers */ + 2 * EB_FLOATS * 4 + 2 * A_TILE_BYTES +
+                      SACC_FLOATS * 4 + 1024;
+  static std::once_flag attr_once;
+  static cudaError_t attr_err = cudaSuccess;
+  std::call_once(attr_once, [] {
+    for (auto fn : {(const void*)conv_gemm_kernel<EPI_PLAIN>, (const void*)conv_gemm_kernel<EPI_STATS>,
+                    (const void*)conv_gemm_kernel<EPI_GNB>}) {
+      cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      if (e != cudaSuccess) attr_err = e;
+    }
+  });
+  B2D_CHECK_CUDA(attr_err);
   p.m_tiles = (p.total_pixels + 127) / 128;
   p.n_tiles = (a->CoutPad + BN - 1) / BN;
   const long long tiles = (long long)p.m_tiles * p.n_tiles;
   long long ctas = 2LL * num_sms();            // two persistent CTAs per SM (<= 96 KB ring, <= 256 TMEM columns each)
   if (ctas > tiles) ctas = tiles;
   dim3 grid((unsigned)ctas);
-  conv_gemm_kernel<<<grid, CONV_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
+  if (want_gnb)        conv_gemm_kernel<EPI_GNB><<<grid, CONV_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
+  else if (want_stats) conv_gemm_kernel<EPI_STATS><<<grid, CONV_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
+  else                 conv_gemm_kernel<EPI_PLAIN><<<grid, CONV_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
+}
+
+extern "C" int b2d_conv2d_gn_fusable(int Ho, int Wo, int Cout) {
+  if (Ho <= 0 || Wo <= 0 || Cout <= 0 || Cout % 64 != 0) return 0;
+  const int hw = Ho * Wo;
+  if (hw % 32 != 0) return 0;
+  const int imgs = hw >= 128 ? 1 : 128 / hw;
+  const int BN = Cout <= 128 ? Cout : (Cout % 128 == 0 ? 128 : 64);
+  return imgs * BN * 2 <= 512 ? 1 : 0;
 }

@@ -671,6 +671,247 @@ gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, in
   if (CS) gn_colsum_flush(o, sh, cs, s.C1, c, n, first);
 }
 
+// ====================================================================== producer-fused statistics (engine path)
+// The convolution that produces a tensor emits, from its fp32 epilogue values, the per-(sample, channel pair) sum and
+// sum of squares (conv_gemm.cu EPI_STATS); the GroupNorm that consumes the tensor -- possibly as one half of a skip
+// concatenation -- forms its 32 group moments from those pairs: forward = ONE pass (read x, write y).  The
+// data-gradient convolution that produces dL/dy emits dyh = dy * act'(z) * mask and (sum dyh, sum dyh * x) per
+// (sample, channel) (EPI_GNB); backward = ONE pass (read x, dyh [, add_a, add_b], write dx) + the parameter sums.
+
+// st[n][c/2][0..1] += (sum, sum of squares) of channels (c, c+1) over the pixels of sample n.  grid (chunks, N).
+__global__ void __launch_bounds__(256)
+pair_stats_kernel(const __half* __restrict__ x, long long ld, int C, int HW, double* __restrict__ st) {
+  extern __shared__ float sh[];  // [C]: pair p -> sh[2p], sh[2p + 1]
+  const int V = C >> 3;
+  const int v = threadIdx.x % V, prow = threadIdx.x / V, rows = blockDim.x / V;
+  const int n = blockIdx.y;
+  for (int i = threadIdx.x; i < C; i += blockDim.x) sh[i] = 0.f;
+  __syncthreads();
+  float a[4] = {0.f, 0.f, 0.f, 0.f}, q[4] = {0.f, 0.f, 0.f, 0.f};
+  const int step = gridDim.x * rows;
+  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 4 * step) {
+    uint4 raw[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (pix0 + u * step < HW) raw[u] = ldg_nc_u4(x + ((long long)n * HW + pix0 + u * step) * ld + v * 8);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      if (pix0 + u * step < HW) {
+        float f[8];
+        unpack8(raw[u], f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          a[i] += f[2 * i] + f[2 * i + 1];
+          q[i] = fmaf(f[2 * i], f[2 * i], fmaf(f[2 * i + 1], f[2 * i + 1], q[i]));
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { atomicAdd(&sh[v * 8 + 2 * i], a[i]); atomicAdd(&sh[v * 8 + 2 * i + 1], q[i]); }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += blockDim.x) atomicAdd(&st[(long long)n * C + i], (double)sh[i]);
+}
+
+// group moments of sample n from the pair sums of the (up to two) source tensors
+__device__ __forceinline__ void gn_group_moments(const double* __restrict__ st1, const double* __restrict__ st2, int C1,
+                                                 int C2, int rps, int n, int g, int cpg, int HW, float eps, float* mean,
+                                                 float* rstd) {
+  double S = 0.0, Q = 0.0;
+  const int p0 = g * (cpg >> 1), p1 = p0 + (cpg >> 1), h1 = C1 >> 1, h2 = C2 >> 1;
+  for (int r = 0; r < rps; ++r) {
+    const long long row = (long long)n * rps + r;
+    for (int pi = p0; pi < p1; ++pi) {
+      const double* s = pi < h1 ? st1 + (row * h1 + pi) * 2 : st2 + (row * h2 + (pi - h1)) * 2;
+      S += s[0]; Q += s[1];
+    }
+  }
+  const double cnt = (double)cpg * (double)HW;
+  const double m = S / cnt;
+  double var = Q / cnt - m * m;
+  if (var < 0.0) var = 0.0;
+  *mean = (float)m;
+  *rstd = (float)(1.0 / sqrt(var + (double)eps));
+}
+
+__global__ void __launch_bounds__(256)
+gn_apply2_kernel(GnSrc s, int HW, int Ctot, const double* __restrict__ st1, const double* __restrict__ st2, int rps,
+                 const float* __restrict__ gamma, const float* __restrict__ beta, float eps, int act, float drop_p,
+                 unsigned long long seed, __half* __restrict__ y, float* __restrict__ mean_out,
+                 float* __restrict__ rstd_out, unsigned char* __restrict__ mask_out) {
+  __shared__ float s_mean[32], s_rstd[32];
+  const int n = blockIdx.y;
+  const int cpg = Ctot >> 5;
+  if (threadIdx.x < 32) {
+    float m, r;
+    gn_group_moments(st1, st2, s.C1, s.C2, rps, n, threadIdx.x, cpg, HW, eps, &m, &r);
+    s_mean[threadIdx.x] = m;
+    s_rstd[threadIdx.x] = r;
+    if (blockIdx.x == 0) { mean_out[n * 32 + threadIdx.x] = m; rstd_out[n * 32 + threadIdx.x] = r; }
+  }
+  __syncthreads();
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V, prow = threadIdx.x / V, rows = blockDim.x / V;
+  const int c = v * 8;
+  float g[8], b[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const float gm = __ldg(gamma + c + i), rs_ = s_rstd[(c + i) / cpg];
+    g[i] = gm * rs_;
+    b[i] = fmaf(-s_mean[(c + i) / cpg], g[i], __ldg(beta + c + i));
+  }
+  const float keep_scale = drop_p > 0.f ? 1.0f / (1.0f - drop_p) : 1.0f;
+  const int step = gridDim.x * rows;
+  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 4 * step) {
+    uint4 raw[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u)
+      if (pix0 + u * step < HW) raw[u] = ldg_nc_u4(src_ptr(s, (long long)n * HW + pix0 + u * step, c));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int pix = pix0 + u * step;
+      if (pix >= HW) continue;
+      const long long gp = (long long)n * HW + pix;
+      float x[8];
+      unpack8(raw[u], x);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const float z = fmaf(x[i], g[i], b[i]);
+        x[i] = act ? silu_f(z) : z;
+      }
+      if (drop_p > 0.f) {
+        bool keep[8];
+        dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
+        unsigned bits = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { x[i] = keep[i] ? x[i] * keep_scale : 0.f; bits |= keep[i] ? (1u << i) : 0u; }
+        if (mask_out) mask_out[gp * V + v] = (unsigned char)bits;
+      }
+      store8_fmt(y + gp * Ctot + c, x, FMT_F16);
+    }
+  }
+}
+
+// dx = dyh * rg + x * pp + qq (+ add_a + add_b); ab[n][c] = (sum dyh, sum dyh * x)
+template <bool CS>
+__global__ void __launch_bounds__(256, CS ? 2 : 3)
+gn_bwd_apply2_kernel(GnSrc s, const __half* __restrict__ dyh, int HW, int Ctot, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ ab,
+                     GnBwdOut o, int* __restrict__ overflow) {
+  __shared__ float s1[32], s2[32];
+  extern __shared__ float shc[];   // [C1] when o.colsum
+  const int n = blockIdx.y;
+  const int cpg = Ctot >> 5;
+  if (threadIdx.x < 32) {
+    const float rs_ = __ldg(rstd + n * 32 + threadIdx.x), mu_ = __ldg(mean + n * 32 + threadIdx.x);
+    float a = 0.f, b = 0.f;
+    for (int i = 0; i < cpg; ++i) {
+      const int ch = threadIdx.x * cpg + i;
+      const float gm = __ldg(gamma + ch);
+      const float A = ab[((long long)n * Ctot + ch) * 2 + 0], B = ab[((long long)n * Ctot + ch) * 2 + 1];
+      a = fmaf(gm, A, a);
+      b = fmaf(gm, rs_ * (B - mu_ * A), b);          // sum dyh * xhat = rstd * (sum dyh * x - mean * sum dyh)
+    }
+    const float inv_m = 1.0f / ((float)cpg * (float)HW);
+    s1[threadIdx.x] = a * inv_m;
+    s2[threadIdx.x] = b * inv_m;
+  }
+  __syncthreads();
+  const int V = Ctot >> 3;
+  const int v = threadIdx.x % V, prow = threadIdx.x / V, rows = blockDim.x / V;
+  const int c = v * 8;
+  float rg[8], pp[8], qq[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int gi = (c + i) / cpg;
+    const float rs_ = __ldg(rstd + n * 32 + gi), mu_ = __ldg(mean + n * 32 + gi);
+    rg[i] = rs_ * __ldg(gamma + c + i);
+    pp[i] = -rs_ * rs_ * s2[gi];
+    qq[i] = -mu_ * pp[i] - rs_ * s1[gi];
+  }
+  const bool first = c < s.C1;
+  const bool has_a = o.add_a && (first || o.add_a_full);
+  const bool has_b = o.add_b && first;
+  float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float amax = 0.f;
+  const int step = gridDim.x * rows;
+  for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 2 * step) {
+    uint4 rx[2], rd[2], ra[2], rb[2];
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      if (pix0 + u * step < HW) {
+        const long long gp = (long long)n * HW + pix0 + u * step;
+        rx[u] = ldg_nc_u4(src_ptr(s, gp, c));
+        rd[u] = ldg_nc_u4(dyh + gp * Ctot + c);
+        if (has_a) ra[u] = ldg_nc_u4(o.add_a + gp * o.lda + c);
+        if (has_b) rb[u] = ldg_nc_u4(o.add_b + gp * o.ldb + c);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 2; ++u) {
+      const int pix = pix0 + u * step;
+      if (pix >= HW) continue;
+      const long long gp = (long long)n * HW + pix;
+      float x[8], d[8];
+      unpack8(rx[u], x);
+      unpack8(rd[u], d);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        amax = fmaxf(amax, fabsf(d[i]));
+        x[i] = fmaf(d[i], rg[i], fmaf(x[i], pp[i], qq[i]));
+      }
+      if (has_a) { float t[8]; unpack8(ra[u], t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+      if (has_b) { float t[8]; unpack8(rb[u], t);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(x[i]));
+      if (first) {
+        store8(o.dx1 + gp * o.ldd1 + c, x);
+        if (CS) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i) cs[i] += x[i];
+        }
+      } else {
+        store8(o.dx2 + gp * o.ldd2 + (c - s.C1), x);
+      }
+    }
+  }
+  if (overflow != nullptr && !(amax < 65504.f)) atomicAdd(overflow, 1);   // saturated (or NaN) fp16 gradient seen
+  if (CS) gn_colsum_flush(o, shc, cs, s.C1, c, n, first);
+}
+
+// dgamma[c] += sum_n rstd * (ab1 - mean * ab0), dbeta[c] += sum_n ab0.  block = 32 channels x 8 sample lanes.
+__global__ void __launch_bounds__(256)
+gn_param_grad2_kernel(const float* __restrict__ ab, const float* __restrict__ mean, const float* __restrict__ rstd, int N,
+                      int Ctot, float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  __shared__ float sa[8][33], sb[8][33];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 32 + tx;
+  const int cpg = Ctot >> 5;
+  float a = 0.f, b = 0.f;
+  if (c < Ctot) {
+    const int g = c / cpg;
+    for (int n = ty; n < N; n += 8) {
+      const float2 t = __ldg(reinterpret_cast<const float2*>(ab + ((long long)n * Ctot + c) * 2));
+      const float rs_ = __ldg(rstd + n * 32 + g), mu_ = __ldg(mean + n * 32 + g);
+      a += t.x;
+      b = fmaf(rs_, t.y - mu_ * t.x, b);
+    }
+  }
+  sa[ty][tx] = a; sb[ty][tx] = b;
+  __syncthreads();
+  if (ty == 0 && c < Ctot) {
+    float ta = 0.f, tb = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { ta += sa[i][tx]; tb += sb[i][tx]; }
+    dbeta[c] += ta;
+    dgamma[c] += tb;
+  }
+}
+
 // Cluster size and pixels per CTA for the single-pass kernels, or 0 for the two-kernel path.  Measured on the train64
 // step (N = 256; profiles/r1_groupnorm_fused.md): the single pass wins only while a sample fits one or two CTAs of
 // <= 72 KB (HW = 256: 0.021 vs 0.033 ms forward, 0.060 vs 0.078 ms backward at C = 128); with 4 - 8 CTAs per sample the
@@ -826,6 +1067,67 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
         (const float*)workspace, o);
   B2D_CHECK_LAUNCH();
   gn_param_grad_kernel<<<(Ctot + 31) / 32, 256, 0, st>>>((const float*)workspace, a->N, Ctot, dgamma, dbeta);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_pair_stats(const void* x, int64_t ld, int C, int N, int HW, double* st, void* stream) {
+  B2D_REQUIRE(x && st && C > 0 && C % 8 == 0 && C <= 2048 && N > 0 && N <= 65535 && HW > 0, B2D_ERR_SHAPE,
+              "pair_stats: bad arguments (C=%d N=%d HW=%d)", C, N, HW);
+  B2D_REQUIRE(ld % 8 == 0 && aligned16(x), B2D_ERR_ALIGN, "pair_stats: input must have 16-byte aligned rows");
+  dim3 grid; int threads;
+  gn_launch_dims(N, HW, C, 3, &grid, &threads);
+  pair_stats_kernel<<<grid, threads, C * sizeof(float), (cudaStream_t)stream>>>((const __half*)x, ld, C, HW, st);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_groupnorm_apply(const b2d_gn_args* a, const double* st1, const double* st2, int rows_per_sample,
+                                   void* y, float* mean, float* rstd, uint8_t* mask_out, void* stream) {
+  int rc = gn_check(a, "groupnorm_apply");
+  if (rc) return rc;
+  const GnSrc s = make_src(a);
+  const int Ctot = s.C1 + s.C2;
+  B2D_REQUIRE(y && mean && rstd && st1 && (s.C2 == 0 || st2) && a->gamma && a->beta && rows_per_sample >= 1, B2D_ERR_SHAPE,
+              "groupnorm_apply: null pointer");
+  B2D_REQUIRE(s.C1 % 2 == 0 && s.C2 % 2 == 0 && (Ctot / 32) % 2 == 0, B2D_ERR_SHAPE,
+              "groupnorm_apply: groups of %d channels do not split into channel pairs", Ctot / 32);
+  dim3 grid; int threads;
+  gn_launch_dims(a->N, a->HW, Ctot, 4, &grid, &threads);
+  gn_apply2_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(s, a->HW, Ctot, st1, st2, rows_per_sample, a->gamma, a->beta,
+                                                               a->eps, a->act, a->drop_p, a->seed, (__half*)y, mean, rstd,
+                                                               mask_out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_groupnorm_bwd_apply(const b2d_gn_args* a, const void* dyh, const float* mean, const float* rstd,
+                                       const float* ab, void* dx1, int64_t lddx1, void* dx2, int64_t lddx2,
+                                       const void* add_a, int64_t lda, const void* add_b, int64_t ldb, int add_a_full,
+                                       float* dx1_colsum, int64_t ld_colsum, float* dgamma, float* dbeta, int* overflow,
+                                       void* stream) {
+  int rc = gn_check(a, "groupnorm_bwd_apply");
+  if (rc) return rc;
+  const GnSrc s = make_src(a);
+  const int Ctot = s.C1 + s.C2;
+  B2D_REQUIRE(dyh && mean && rstd && ab && dx1 && a->gamma && dgamma && dbeta, B2D_ERR_SHAPE,
+              "groupnorm_bwd_apply: null pointer");
+  B2D_REQUIRE(s.C2 == 0 || dx2, B2D_ERR_SHAPE, "groupnorm_bwd_apply: dx2 required for a two-source input");
+  cudaStream_t st = (cudaStream_t)stream;
+  GnBwdOut o;
+  o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
+  o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
+  o.colsum = dx1_colsum; o.ldcs = ld_colsum;
+  dim3 grid; int threads;
+  gn_launch_dims(a->N, a->HW, Ctot, 8, &grid, &threads);
+  if (dx1_colsum)
+    gn_bwd_apply2_kernel<true><<<grid, threads, s.C1 * sizeof(float), st>>>(s, (const __half*)dyh, a->HW, Ctot, mean, rstd,
+                                                                           a->gamma, ab, o, overflow);
+  else
+    gn_bwd_apply2_kernel<false><<<grid, threads, 0, st>>>(s, (const __half*)dyh, a->HW, Ctot, mean, rstd, a->gamma, ab, o,
+                                                          overflow);
+  B2D_CHECK_LAUNCH();
+  gn_param_grad2_kernel<<<(Ctot + 31) / 32, 256, 0, st>>>(ab, mean, rstd, a->N, Ctot, dgamma, dbeta);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

@@ -13,6 +13,8 @@ GroupNorm-backward and dgrad epilogues.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import ops
@@ -21,6 +23,38 @@ from .unet import AttentionBlock, Downsample, ResBlock, Upsample, timestep_freqs
 
 def _pad64(c: int) -> int:
     return (c + 63) // 64 * 64
+
+
+class _ZeroArena:
+    """Zero-filled scratch for one forward (or one backward): the small accumulation buffers of a pass -- GroupNorm
+    pair statistics, per-channel gradient sums, bias / embedding column sums -- are slices of ONE buffer cleared by ONE
+    memset at the start of the pass instead of a `torch.zeros` (allocation + fill kernel) each.  The size is learnt
+    on the first pass; a request that does not fit the cleared part falls back to `torch.zeros` and grows the next
+    pass's buffer.  Slices are only valid until the next `begin()`: nothing handed out here is kept across passes."""
+
+    def __init__(self):
+        self.buf, self.off, self.need, self.cleared, self.device = None, 0, 0, 0, None
+
+    def begin(self, device):
+        self.device = device
+        if self.need and (self.buf is None or self.buf.device != device or self.buf.numel() < self.need):
+            self.buf = torch.empty(self.need, device=device, dtype=torch.uint8)
+        self.cleared = min(self.need, self.buf.numel()) if self.buf is not None else 0
+        if self.cleared:
+            self.buf[:self.cleared].zero_()
+        self.off = 0
+
+    def zeros(self, shape, dtype):
+        n = 1
+        for d in shape:
+            n *= d
+        nbytes = n * torch.empty((), dtype=dtype).element_size()
+        lo = self.off
+        self.off = (lo + nbytes + 255) // 256 * 256
+        self.need = max(self.need, self.off)
+        if self.off <= self.cleared:
+            return self.buf[lo:lo + nbytes].view(dtype).view(shape)
+        return torch.zeros(shape, device=self.device, dtype=dtype)
 
 
 class _Ctx:
@@ -49,6 +83,10 @@ class DenoiserEngine:
         self._pack_table = None
         self._weights_maybe_stale = False
         self._colsums = {}
+        self._stats = {}                      # data_ptr -> (pair statistics, tensor) of tensors a fused convolution produced
+        self._fwd_arena, self._bwd_arena = _ZeroArena(), _ZeroArena()
+        self._overflow = None                 # int32 device counter: saturated fp16 gradients seen by the backward
+        self.fuse_groupnorm = os.environ.get("B2D_GN_FUSE", "1") != "0"      # A/B switch for the fused epilogues
         self.seq_parallel = None              # parallel.SequenceParallelAttention, when one clip is split across GPUs
         self._step_seed = 0
         # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
@@ -120,12 +158,21 @@ class DenoiserEngine:
         return self._packed((id(conv), "d"), conv.weight, fn)
 
     # ------------------------------------------------------------------ dims=3 helpers (T frames folded into N)
-    def _conv(self, x, wp, cout, k, stride, x2=None, bias=None, emb=None, residual=None):
+    def _conv(self, x, wp, cout, k, stride, x2=None, bias=None, emb=None, residual=None, stats=False, gnb=None):
         """conv2d, or -- for a list of three temporal tap groups -- the Conv3d sum over time-shifted frames:
         the centre tap carries bias / emb / residual, the side taps accumulate in place through the residual input
-        on the frame ranges that have a neighbour (zero padding in time = no contribution)."""
+        on the frame ranges that have a neighbour (zero padding in time = no contribution).
+        stats: the output feeds a GroupNorm -- let the epilogue emit its pair statistics (remembered under the output's
+        address for `_gn_fwd`).  gnb: ops.GnBwdFuse (the output is the dL/dy of a GroupNorm)."""
         if not isinstance(wp, list):
-            return ops.conv2d(x, wp, cout, k, stride, x2=x2, bias=bias, emb=emb, residual=residual)
+            st = None
+            if stats and self.fuse_groupnorm and ops.gn_fusable(x.shape[1] // stride, x.shape[2] // stride, cout):
+                st = self._fwd_arena.zeros((x.shape[0], cout // 2, 2), torch.float64)
+            out = ops.conv2d(x, wp, cout, k, stride, x2=x2, bias=bias, emb=emb, residual=residual, stats_out=st, gnb=gnb)
+            if st is not None:
+                self._stats[out.data_ptr()] = (st, out)
+            return out
+        assert gnb is None
         T = self.T
         out = ops.conv2d(x, wp[1], cout, k, stride, x2=x2, bias=bias, emb=emb, residual=residual)
         if T > 1:
@@ -164,10 +211,50 @@ class DenoiserEngine:
             return t
         return t.view(like.shape[0], like.shape[1], like.shape[2], t.shape[3])
 
-    def _gn_fwd(self, x, gn, x2=None, act=True, drop_p=0.0, seed=0):
-        y, mean, rstd = ops.groupnorm_fwd(self._fold(x), gn.weight.detach(), gn.bias.detach(), x2=self._fold(x2), act=act,
-                                          eps=gn.eps, drop_p=drop_p, seed=seed)
-        return self._unfold(y, x), mean, rstd
+    def _pair_stats(self, t):
+        """Pair statistics of a GroupNorm input: from the epilogue of the convolution that produced it, else one pass."""
+        hit = self._stats.get(t.data_ptr())
+        if hit is not None and hit[1].shape == t.shape and hit[1].stride() == t.stride() and self.T == 1:
+            return hit[0]
+        f = self._fold(t)
+        return ops.pair_stats(f, self._fwd_arena.zeros((f.shape[0], f.shape[3] // 2, 2), torch.float64))
+
+    def _gn_fwd(self, x, gn, x2=None, act=True, drop_p=0.0, seed=0, want_mask=False):
+        """Returns (y, mean, rstd, dropout keep-bit mask or None)."""
+        if not self.fuse_groupnorm:
+            y, mean, rstd = ops.groupnorm_fwd(self._fold(x), gn.weight.detach(), gn.bias.detach(), x2=self._fold(x2),
+                                              act=act, eps=gn.eps, drop_p=drop_p, seed=seed)
+            return self._unfold(y, x), mean, rstd, None
+        st1 = self._pair_stats(x)
+        st2 = self._pair_stats(x2) if x2 is not None else None
+        y, mean, rstd, mask = ops.groupnorm_apply(self._fold(x), st1, gn.weight.detach(), gn.bias.detach(),
+                                                  x2=self._fold(x2), st2=st2, act=act, eps=gn.eps, drop_p=drop_p,
+                                                  seed=seed, want_mask=want_mask)
+        return self._unfold(y, x), mean, rstd, mask
+
+    def _gnb(self, x, gn, mean, rstd, x2=None, act=True, mask=None, drop_p=0.0):
+        """ops.GnBwdFuse for the data-gradient convolution that produces dL/dy of act(GroupNorm([x | x2])), or None when
+        the fused epilogue does not apply (dims=3 frame folding, planes the staging does not cover, dropout without
+        saved mask bits, A/B switch)."""
+        ct = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
+        if (not self.fuse_groupnorm or self.T != 1 or not ops.gn_fusable(x.shape[1], x.shape[2], ct)
+                or (drop_p > 0.0 and mask is None)):
+            return None
+        ab = self._bwd_arena.zeros((x.shape[0], ct, 2), torch.float32)
+        return ops.GnBwdFuse(x, x2, mean, rstd, gn.weight.detach(), gn.bias.detach(), act, ab, mask=mask,
+                             keep_scale=1.0 / (1.0 - drop_p) if drop_p > 0.0 else 1.0)
+
+    def _gn_bwd_fused(self, G, x, gn, gnb, dyh, x2=None, add_a=None, add_b=None, add_a_full=False, colsum_out=None,
+                      want_colsum=False):
+        """Input-gradient pass after a fused data-gradient epilogue (`gnb`) produced dyh and the channel sums."""
+        if want_colsum and colsum_out is None:
+            colsum_out = self._bwd_arena.zeros((x.shape[0], x.shape[-1]), torch.float32)
+        dx1, dx2 = ops.groupnorm_bwd_apply(x, gn.weight.detach(), gn.bias.detach(), dyh, gnb.mean, gnb.rstd, gnb.ab,
+                                           G.g(gn.weight), G.g(gn.bias), x2=x2, eps=gn.eps, add_a=add_a, add_b=add_b,
+                                           add_a_full=add_a_full, colsum_out=colsum_out, overflow=self._overflow)
+        if want_colsum and colsum_out is not None:
+            self._colsums = {dx1.data_ptr(): (colsum_out, dx1)}
+        return dx1, dx2
 
     def _gn_bwd(self, G, x, gn, dy, mean, rstd, x2=None, act=True, drop_p=0.0, seed=0, add_a=None, add_b=None,
                 add_a_full=False, colsum_out=None, want_colsum=False):
@@ -214,6 +301,8 @@ class DenoiserEngine:
             N, _, S, _ = xt.shape
             B, T = N, 1
         self.T = T
+        self._stats = {}
+        self._fwd_arena.begin(dev)
         self.refresh_packed()
         self._weights_maybe_stale = bool(train)
         tape = {"N": N, "S": S, "B": B, "T": T} if train else None
@@ -250,18 +339,20 @@ class DenoiserEngine:
             if isinstance(layer, AttentionBlock):
                 return self._attn_fwd(layer, h, train)
             if isinstance(layer, Downsample):
-                out = self._conv(h, self.w_fwd(layer.op), layer.out_channels, 3, 2, bias=layer.op.bias.detach())
+                out = self._conv(h, self.w_fwd(layer.op), layer.out_channels, 3, 2, bias=layer.op.bias.detach(), stats=True)
                 ctx = _Ctx("down", layer); ctx.t["x"] = h
                 return out, ctx
             if isinstance(layer, Upsample):
                 u = ops.upsample2x(h)
-                out = self._conv(u, self.w_fwd(layer.conv), layer.out_channels, 3, 1, bias=layer.conv.bias.detach())
+                out = self._conv(u, self.w_fwd(layer.conv), layer.out_channels, 3, 1, bias=layer.conv.bias.detach(),
+                                 stats=True)
                 ctx = _Ctx("up", layer); ctx.t["u"] = u
                 return out, ctx
             raise RuntimeError(f"unexpected layer {type(layer)}")
 
         conv_in = m.input_blocks[0][0]
-        h = self._conv(x0, self.w_fwd(conv_in, self.cin_pad), conv_in.out_channels, 3, 1, bias=conv_in.bias.detach())
+        h = self._conv(x0, self.w_fwd(conv_in, self.cin_pad), conv_in.out_channels, 3, 1, bias=conv_in.bias.detach(),
+                       stats=True)
         hs = [h]
         idx = 0
         enc, mid, dec = [], [], []
@@ -288,7 +379,7 @@ class DenoiserEngine:
         if train:
             tape.update(enc=enc, mid=mid, dec=dec)
         gn, conv_out = m.out[0], m.out[2]
-        hh, mean, rstd = self._gn_fwd(h, gn, act=True)
+        hh, mean, rstd, _ = self._gn_fwd(h, gn, act=True)
         out = torch.empty(N, m.out_channels, S, S, device=dev, dtype=torch.float32)
         wo = self.w_fwd(conv_out)
         if isinstance(wo, list):        # Conv3d head: the fp32 NCHW writer cannot accumulate, so the two side taps go
@@ -313,27 +404,28 @@ class DenoiserEngine:
         gn1, conv1 = rb.in_layers[0], rb.in_layers[2]
         gn2, conv2 = rb.out_layers[0], rb.out_layers[3]
         cout = rb.out_channels
-        h1, mean1, rstd1 = self._gn_fwd(x, gn1, x2=x2, act=True)
+        h1, mean1, rstd1, _ = self._gn_fwd(x, gn1, x2=x2, act=True)
         off = self.emb_off[id(rb)]
-        h2 = self._conv(h1, self.w_fwd(conv1), cout, 3, 1, bias=conv1.bias.detach(), emb=emb_all[:, off:off + cout])
-        h3, mean2, rstd2 = self._gn_fwd(h2, gn2, act=True, drop_p=drop_p, seed=seed)
+        h2 = self._conv(h1, self.w_fwd(conv1), cout, 3, 1, bias=conv1.bias.detach(), emb=emb_all[:, off:off + cout],
+                        stats=True)
+        h3, mean2, rstd2, mask2 = self._gn_fwd(h2, gn2, act=True, drop_p=drop_p, seed=seed, want_mask=train)
         if isinstance(rb.skip_connection, torch.nn.Identity):
             res = x
         else:
             sc = rb.skip_connection
             res = ops.conv2d(x, self.w_fwd(sc), cout, 1, 1, x2=x2, bias=sc.bias.detach())
-        out = self._conv(h3, self.w_fwd(conv2), cout, 3, 1, bias=conv2.bias.detach(), residual=res)
+        out = self._conv(h3, self.w_fwd(conv2), cout, 3, 1, bias=conv2.bias.detach(), residual=res, stats=True)
         ctx = None
         if train:
             ctx = _Ctx("res", rb)
             ctx.t.update(x=x, x2=x2, h1=h1, h2=h2, h3=h3, mean1=mean1, rstd1=rstd1, mean2=mean2, rstd2=rstd2,
-                         drop_p=drop_p, seed=seed)
+                         drop_p=drop_p, seed=seed, mask2=mask2)
         return out, ctx
 
     def _attn_fwd(self, ab, x, train):
         gn = ab.norm
         C_ = ab.channels
-        hn, mean, rstd = self._gn_fwd(x, gn, act=False)
+        hn, mean, rstd, _ = self._gn_fwd(x, gn, act=False)
         qkv = ops.conv2d(hn, self.w_fwd(ab.qkv), 3 * C_, 1, 1, bias=ab.qkv.bias.detach())
         fq = self._fold(qkv)
         sp = self.seq_parallel
@@ -342,7 +434,7 @@ class DenoiserEngine:
         if rows is not None:
             sp.all_gather_rows(a, rows)                   # every rank needs the full attention output
         a = self._unfold(a, qkv)
-        out = ops.conv2d(a, self.w_fwd(ab.proj_out), C_, 1, 1, bias=ab.proj_out.bias.detach(), residual=x)
+        out = self._conv(a, self.w_fwd(ab.proj_out), C_, 1, 1, bias=ab.proj_out.bias.detach(), residual=x, stats=True)
         ctx = None
         if train:
             ctx = _Ctx("attn", ab)
@@ -486,7 +578,10 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     if dout.dim() == 5:                                   # (B, C, T, S, S) -> frames folded into the batch
         dout = dout.permute(0, 2, 1, 3, 4).reshape(N, dout.shape[1], dout.shape[3], dout.shape[4]).contiguous()
     G = _Grads(eng, dev)
-    d_emb_all = torch.zeros(N, eng.emb_total, device=dev, dtype=torch.float32)
+    eng._bwd_arena.begin(dev)
+    if eng._overflow is None or eng._overflow.device != dev:
+        eng._overflow = torch.zeros(4, device=dev, dtype=torch.int32)
+    d_emb_all = eng._bwd_arena.zeros((N, eng.emb_total), torch.float32)
     stage = 0
     # fp16 gradient tensors: scale2 = [2^k, 2^-k] with max|dout| * 2^k in [64, 128); every gradient below is
     # carried times 2^k and each stage's slice of the flat fp32 buffer is unscaled as soon as the stage is done
@@ -511,7 +606,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         if hit is not None and hit[1].shape == dy.shape and hit[1].stride() == dy.stride() and hit[0].shape[1] == cout:
             tmp = hit[0]                                  # produced by the GroupNorm backward that wrote dy
         else:
-            tmp = torch.zeros(N, cout, device=dev, dtype=torch.float32)
+            tmp = eng._bwd_arena.zeros((N, cout), torch.float32)
             ops.colsum(dy, tmp, 0, cout)
         ops.reduce_rows(tmp, G.g(bias_param))
         if also is not None:
@@ -523,8 +618,12 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     dyp = ops.nchw_to_pixel_major(dout, 64, scale=scale2)
     eng._wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
     bias_grad(dyp, conv_out.bias, 64)
-    d_hh = eng._conv(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1)
-    dh, _ = eng._gn_bwd(G, hd["h"], gn, d_hh, hd["mean"], hd["rstd"], act=True)
+    gnb = eng._gnb(hd["h"], gn, hd["mean"], hd["rstd"], act=True)
+    d_hh = eng._conv(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1, gnb=gnb)
+    if gnb is not None:
+        dh, _ = eng._gn_bwd_fused(G, hd["h"], gn, gnb, d_hh)
+    else:
+        dh, _ = eng._gn_bwd(G, hd["h"], gn, d_hh, hd["mean"], hd["rstd"], act=True)
     done()
 
     def res_bwd(ctx, dout_, extra):
@@ -537,17 +636,22 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         # conv2 (out_layers[3]) and the skip path share dout_
         eng._wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
         bias_grad(dout_, conv2.bias, also=rb.skip_connection.bias if has_skip_conv else None)
-        d_h3 = eng._conv(dout_, eng.w_dgrad(conv2), cout, 3, 1)
+        gnb2 = eng._gnb(t["h2"], gn2, t["mean2"], t["rstd2"], act=True, mask=t.get("mask2"), drop_p=t["drop_p"])
+        d_h3 = eng._conv(dout_, eng.w_dgrad(conv2), cout, 3, 1, gnb=gnb2)
         off = eng.emb_off[id(rb)]
         fused_cs = eng.T == 1                              # d emb_out (unet.py:266) and conv1 bias: sums of d_h2
-        d_h2, _ = eng._gn_bwd(G, t["h2"], gn2, d_h3, t["mean2"], t["rstd2"], act=True, drop_p=t["drop_p"], seed=t["seed"],
-                              colsum_out=d_emb_all[:, off:off + cout] if fused_cs else None)
-        if not fused_cs:
-            ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)
+        if gnb2 is not None:
+            d_h2, _ = eng._gn_bwd_fused(G, t["h2"], gn2, gnb2, d_h3, colsum_out=d_emb_all[:, off:off + cout])
+        else:
+            d_h2, _ = eng._gn_bwd(G, t["h2"], gn2, d_h3, t["mean2"], t["rstd2"], act=True, drop_p=t["drop_p"],
+                                  seed=t["seed"], colsum_out=d_emb_all[:, off:off + cout] if fused_cs else None)
+            if not fused_cs:
+                ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)
         ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
         eng._wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
         cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
-        d_h1 = eng._conv(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1)
+        gnb1 = eng._gnb(x, gn1, t["mean1"], t["rstd1"], x2=x2, act=True)
+        d_h1 = eng._conv(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1, gnb=gnb1)
         if has_skip_conv:
             sc = rb.skip_connection
             ops.conv2d_wgrad(x, dout_, G.g(sc.weight), 1, 1, x2=x2)
@@ -555,6 +659,9 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
             full = True
         else:
             add_a, full = dout_, False
+        if gnb1 is not None:
+            return eng._gn_bwd_fused(G, x, gn1, gnb1, d_h1, x2=x2, add_a=add_a, add_b=extra, add_a_full=full,
+                                     want_colsum=True)
         dx1, dx2 = eng._gn_bwd(G, x, gn1, d_h1, t["mean1"], t["rstd1"], x2=x2, act=True,
                                add_a=add_a, add_b=extra, add_a_full=full, want_colsum=True)
         return dx1, dx2
@@ -574,9 +681,13 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         dqkv = eng._unfold(dqkv, t["qkv"])
         ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
         bias_grad(dqkv, ab.qkv.bias)
-        d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1)
-        dx, _ = eng._gn_bwd(G, t["x"], gn_, d_hn, t["mean"], t["rstd"], act=False, add_a=dout_, add_b=extra,
-                            want_colsum=True)
+        gnb = eng._gnb(t["x"], gn_, t["mean"], t["rstd"], act=False)
+        d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1, gnb=gnb)
+        if gnb is not None:
+            dx, _ = eng._gn_bwd_fused(G, t["x"], gn_, gnb, d_hn, add_a=dout_, add_b=extra, want_colsum=True)
+        else:
+            dx, _ = eng._gn_bwd(G, t["x"], gn_, d_hn, t["mean"], t["rstd"], act=False, add_a=dout_, add_b=extra,
+                                want_colsum=True)
         return dx
 
     def down_bwd(ctx, dout_, extra):
@@ -649,7 +760,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     if eng.is_audio:
         at = m.audio_transformer.transform[0]
         A = at.weight.shape[0]
-        d_avec = torch.zeros(N, A, device=dev, dtype=torch.float32)
+        d_avec = eng._bwd_arena.zeros((N, A), torch.float32)
         cim = m.cond_conv_in.weight.shape[0] if m.image_cond else 0
         ops.assemble_input_bwd(dx0, tape["cond"].contiguous() if m.image_cond else None, m.in_channels - A - cim, cim, A,
                                G.g(m.cond_conv_in.weight) if m.image_cond else None, d_avec)

@@ -138,9 +138,27 @@ def pack_dgrad_weight(w: torch.Tensor, cin_pad: int | None = None, cout_pad: int
     return p.reshape(p.shape[0], kh * kw * cop)
 
 
+def gn_fusable(Ho, Wo, cout) -> bool:
+    """True when a convolution with this output plane / channel count can carry the fused GroupNorm epilogues."""
+    return bool(L.lib().b2d_conv2d_gn_fusable(int(Ho), int(Wo), int(cout)))
+
+
+class GnBwdFuse:
+    """Arguments of the GroupNorm-backward prologue fused into a data-gradient convolution (b2d_conv_args.gnb_*):
+    the convolution's output becomes dyh = dy * act'(z) * mask / (1 - p) and `ab` (fp32 (N, C, 2), zeroed by the
+    caller) receives (sum dyh, sum dyh * x) per (sample, channel)."""
+    __slots__ = ("x1", "x2", "mean", "rstd", "gamma", "beta", "act", "mask", "keep_scale", "ab")
+
+    def __init__(self, x1, x2, mean, rstd, gamma, beta, act, ab, mask=None, keep_scale=1.0):
+        self.x1, self.x2, self.mean, self.rstd, self.gamma, self.beta = x1, x2, mean, rstd, gamma, beta
+        self.act, self.ab, self.mask, self.keep_scale = act, ab, mask, keep_scale
+
+
 def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, residual=None, out=None,
-           out_nchw_f32=None, c1=None, c2=None):
-    """x: (N,H,W,ldx) fp16, optional x2 concatenated on channels.  Returns (N,Ho,Wo,cout) fp16 (or `out`)."""
+           out_nchw_f32=None, c1=None, c2=None, stats_out=None, gnb=None):
+    """x: (N,H,W,ldx) fp16, optional x2 concatenated on channels.  Returns (N,Ho,Wo,cout) fp16 (or `out`).
+    stats_out: fp64 (N, cout/2, 2) zeroed buffer that receives the per-(image, channel pair) sum / sum of squares of
+    the output (consumed by groupnorm_apply); gnb: GnBwdFuse."""
     L.require_cuda(x)
     if any(t is not None and t.dtype != F16 for t in (x, x2, residual, w_packed)):
         raise RuntimeError("conv2d: x / x2 / residual / packed weights must be fp16")
@@ -160,6 +178,15 @@ def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, r
         out = torch.empty(N, Ho, Wo, cout, device=x.device, dtype=x.dtype)
     a.out, a.ldo = L.ptr(out), (out.stride(2) if out is not None else 0)
     a.out_nchw_f32 = L.ptr(out_nchw_f32)
+    a.gn_stats_out = L.ptr(stats_out)
+    if gnb is not None:
+        if gnb.ab.dtype != torch.float32 or gnb.x1.dtype != F16:
+            raise RuntimeError("conv2d: gnb.ab must be fp32, gnb.x1 fp16")
+        a.gnb_x1, a.gnb_ld1, a.gnb_C1 = gnb.x1.data_ptr(), gnb.x1.stride(2), gnb.x1.shape[3]
+        a.gnb_x2, a.gnb_ld2 = (gnb.x2.data_ptr(), gnb.x2.stride(2)) if gnb.x2 is not None else (None, 0)
+        a.gnb_mean, a.gnb_rstd = gnb.mean.data_ptr(), gnb.rstd.data_ptr()
+        a.gnb_gamma, a.gnb_beta, a.gnb_act = gnb.gamma.data_ptr(), gnb.beta.data_ptr(), int(gnb.act)
+        a.gnb_mask, a.gnb_keep_scale, a.gnb_ab = L.ptr(gnb.mask), float(gnb.keep_scale), gnb.ab.data_ptr()
     with _timed("conv2d", (N, H, W, a.C1 + a.C2, cout, ksize, stride)):
         L.check(L.lib().b2d_conv2d(C.byref(a), _s()), "b2d_conv2d")
     return out if out is not None else out_nchw_f32
@@ -256,6 +283,57 @@ def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=T
             L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
             L.ptr(colsum_out), (colsum_out.stride(0) if colsum_out is not None else 0),
             dgamma.data_ptr(), dbeta.data_ptr(), ws.data_ptr(), ws.numel(), _s()), "b2d_groupnorm_bwd")
+    return dx1, dx2
+
+
+def pair_stats(x, out=None):
+    """fp64 (N, C/2, 2): per-(sample, channel pair) sum and sum of squares over the pixels of x (N,H,W,C) fp16 -- what a
+    convolution with `stats_out` emits for its own output."""
+    N, H, W, Cc = x.shape
+    if out is None:
+        out = torch.zeros(N, Cc // 2, 2, device=x.device, dtype=torch.float64)
+    L.check(L.lib().b2d_pair_stats(x.data_ptr(), x.stride(2), Cc, N, H * W, out.data_ptr(), _s()), "b2d_pair_stats")
+    return out
+
+
+def groupnorm_apply(x1, st1, gamma, beta, x2=None, st2=None, act=True, eps=1e-5, drop_p=0.0, seed=0, rows_per_sample=1,
+                    want_mask=False):
+    """One-pass GroupNorm32 (+SiLU, +dropout) with the statistics taken from the producers' pair sums.
+    Returns (y, mean, rstd, mask) -- mask (N, H, W, C/8) uint8 keep bits when want_mask and drop_p > 0, else None."""
+    L.require_cuda(x1)
+    if x1.dtype != F16 or (x2 is not None and x2.dtype != F16):
+        raise RuntimeError("groupnorm_apply: inputs must be fp16")
+    N, H, W, C1 = x1.shape
+    Ct = C1 + (x2.shape[3] if x2 is not None else 0)
+    a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed)
+    y = torch.empty(N, H, W, Ct, device=x1.device, dtype=F16)
+    mean = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
+    rstd = torch.empty(N, 32, device=x1.device, dtype=torch.float32)
+    mask = torch.empty(N, H, W, Ct // 8, device=x1.device, dtype=torch.uint8) if (want_mask and drop_p > 0.0) else None
+    with _timed("groupnorm_fwd", (N, H * W, Ct)):
+        L.check(L.lib().b2d_groupnorm_apply(C.byref(a), st1.data_ptr(), L.ptr(st2), int(rows_per_sample), y.data_ptr(),
+                                            mean.data_ptr(), rstd.data_ptr(), L.ptr(mask), _s()), "b2d_groupnorm_apply")
+    return y, mean, rstd, mask
+
+
+def groupnorm_bwd_apply(x1, gamma, beta, dyh, mean, rstd, ab, dgamma, dbeta, x2=None, eps=1e-5, add_a=None, add_b=None,
+                        add_a_full=False, colsum_out=None, overflow=None):
+    """Input-gradient pass of the GroupNorm backward given dyh / ab from the fused data-gradient epilogue."""
+    N, H, W, C1 = x1.shape
+    if any(t is not None and t.dtype != F16 for t in (x1, x2, dyh, add_a, add_b)):
+        raise RuntimeError("groupnorm_bwd_apply: x / dyh / add_a / add_b must be fp16")
+    a = _gn_args(x1, x2, gamma, beta, eps, True, 0.0, 0)
+    dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=F16)
+    dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=F16) if x2 is not None else None
+    Ct = C1 + (x2.shape[3] if x2 is not None else 0)
+    with _timed("groupnorm_bwd", (N, H * W, Ct)):
+        L.check(L.lib().b2d_groupnorm_bwd_apply(
+            C.byref(a), dyh.data_ptr(), mean.data_ptr(), rstd.data_ptr(), ab.data_ptr(), dx1.data_ptr(), C1,
+            L.ptr(dx2), (dx2.shape[3] if dx2 is not None else 0),
+            L.ptr(add_a), (add_a.stride(2) if add_a is not None else 0),
+            L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
+            L.ptr(colsum_out), (colsum_out.stride(0) if colsum_out is not None else 0),
+            dgamma.data_ptr(), dbeta.data_ptr(), L.ptr(overflow), _s()), "b2d_groupnorm_bwd_apply")
     return dx1, dx2
 
 

@@ -166,7 +166,7 @@ def test_gradient_all_reducer_single_rank_nccl_keeps_gradients_and_fills_missing
         torch.cuda.synchronize()
         got = {k: p.grad for k, p in model.named_parameters()}
         for k, w in want.items():
-            assert rel(got[k], w) <= 2e-3, k
+            assert rel(got[k], w) <= 5e-3, k      # two runs of one step differ by 16-bit re-rounding (atomic order in the sums)
         assert got["audio_encoder.skipped"] is not None and float(got["audio_encoder.skipped"].abs().sum()) == 0.0
     assert red.bytes_reduced > 0
     dist.destroy_process_group()
