@@ -3,11 +3,20 @@
 // single-tile variant for head dim 256 and tiny L.
 //
 // One CTA = 256 queries (two 128-row tiles) of one (sample, head); K/V tiles are streamed ONCE for both.
-// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = tcgen05 issuer, warps 2..5 = softmax group 0
-// (query tile 0), warps 6..9 = softmax group 1 (query tile 1).  TMEM: S0 | S1 | O0 | O1 | P0 | P1.  While one group
+// Warp roles (576 threads): warp 0 = TMA producer, warp 1 = tcgen05 issuer, warps 2..9 = softmax group 0
+// (query tile 0), warps 10..17 = softmax group 1 (query tile 1).  TMEM: S0 | S1 | O0 | O1 | P0 | P1.  While one group
 // runs exp2 on its S tile the tensor pipe computes the other tile's S = Q K^T and O += P V, so the MUFU and
 // the tensor pipe overlap instead of alternating (the single-tile kernel spent ~7.9k clk per 128x128 tile
 // against a ~1k clk MUFU floor: profiles/r1_attention_ncu.md).
+//
+// TWO threads per query row (round 2): a group is 8 warps, warp (qd, half) owns rows 32 qd .. 32 qd + 31 and the key
+// columns [half * BKV/2, (half + 1) * BKV/2) of the tile.  Head dim 64 is bound by the 16 ex2/clk/SM of the MUFU
+// unit (1024 clk per 128x128 tile vs 512 clk of MMA), and one warp per sub-partition issuing FFMA -> EX2 pairs reaches
+// only 9.5-10 clk per warp-ex2 against the unit's 8 (scripts/micro/mufu_rate.cu); with one thread per row each
+// sub-partition held two softmax warps whose load / max / pack phases left the unit idle ~1/3 of the time (clock64
+// trace, profiles/r2_attention_fwd.md).  Four warps per sub-partition with half the columns each keep it fed, and the
+// row fits 64 instead of 128 registers.  The two halves of a row exchange their tile maximum through shared memory
+// (one 64-thread named barrier per tile); sums stay per thread until the epilogue.
 //
 // Per KV tile j and query tile t:   s_full[t] (S ready) -> group t loads S into registers -> s_free[t]
 // (issuer may overwrite S_t with tile j+1) -> max / lazy O rescale / exp2 / P -> tensor memory -> p_full[t]
@@ -15,6 +24,7 @@
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
+#include <stdlib.h>
 
 namespace b2d {
 using namespace umma;
@@ -26,14 +36,28 @@ struct AttnFwd2Params {
   float scale_log2;
   __half* out; long long ldo;
   float* lse;
+  long long* trace;     // developer builds (-DFWD2_TRACE): clock64 stamps of CTA (0,0,0), [17 roles][64 steps][8]
 };
+
+#ifdef FWD2_TRACE
+#define FWD2_STAMP(role, j, k, dep)                                                                        \
+  do {                                                                                                     \
+    if (p.trace && blockIdx.x == 0 && blockIdx.y == 0 && blockIdx.z == 0 && (j) < 64 && lane == 0) {      \
+      long long _t;                                                                                        \
+      asm volatile("mov.u64 %0, %%clock64;" : "=l"(_t) : "r"(dep) : "memory");                             \
+      p.trace[((role) * 64 + (j)) * 8 + (k)] = _t;                                                         \
+    }                                                                                                      \
+  } while (0)
+#else
+#define FWD2_STAMP(role, j, k, dep) do { } while (0)
+#endif
 
 struct AttnFwd2Maps {
   CUtensorMap q;   // box (64, 128, 1)
   CUtensorMap kv;  // box (64, BKV, 1)
 };
 
-constexpr int ATT2_THREADS = 320;
+constexpr int ATT2_THREADS = 576;
 
 template <int D, int BKV>
 struct Fwd2Cfg {
@@ -44,7 +68,8 @@ struct Fwd2Cfg {
   static constexpr int PT_BYTES = 128 * BKV * 2;        // one P tile
   static constexpr int SMEM_DATA = 2 * QT_BYTES + ST * STAGE_BYTES;
   static constexpr int NBARS = 1 + 3 * ST + 8;
-  static constexpr int SMEM_TOTAL = SMEM_DATA + NBARS * 8 + 16 + 1024;
+  static constexpr int XCH_BYTES = 2 * 2 * 2 * 128 * 4;   // [group][tile parity][half][row] fp32: row-max exchange
+  static constexpr int SMEM_TOTAL = SMEM_DATA + NBARS * 8 + 16 + XCH_BYTES + 1024;
   static constexpr uint32_t S_COL = 0;                  // S_t at t * 128
   static constexpr uint32_t O_COL = 256;                // O_t at 256 + t * D
   // P_t as fp16 pairs (BKV / 2 columns), the tensor-memory A operand of O += P V: behind O for D = 64, in the
@@ -73,6 +98,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
   uint64_t* p_full = s_free + 2;           // [2]
   uint64_t* pv_done = p_full + 2;          // [2]
   uint32_t* tmem_slot = (uint32_t*)(pv_done + 2);
+  float* xch = (float*)(tmem_slot + 4);      // 16-byte aligned behind the barriers
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -88,7 +114,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
     mbar_init(q_full, 1);
     for (int s = 0; s < Cfg::ST; ++s) { mbar_init(&k_full[s], 1); mbar_init(&v_full[s], 1); mbar_init(&kv_empty[s], 1); }
     for (int t = 0; t < 2; ++t) {
-      mbar_init(&s_full[t], 1); mbar_init(&s_free[t], 128); mbar_init(&p_full[t], 128); mbar_init(&pv_done[t], 1);
+      mbar_init(&s_full[t], 1); mbar_init(&s_free[t], 256); mbar_init(&p_full[t], 256); mbar_init(&pv_done[t], 1);
     }
     fence_barrier_init();
     prefetch_tmap(&maps.q);
@@ -111,7 +137,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
           tma_load_3d(q_s + t * Cfg::QT_BYTES + b * (128 * 128), &maps.q, q_full, qc + b * 64, q0 + t * 128, n);
       for (int j = 0; j < n_kv; ++j) {
         const int s = j % Cfg::ST;
-        mbar_wait(&kv_empty[s], (uint32_t)(((j / Cfg::ST) & 1) ^ 1));
+        mbar_wait_sleep(&kv_empty[s], (uint32_t)(((j / Cfg::ST) & 1) ^ 1));
         uint8_t* k_dst = kv_s + s * Cfg::STAGE_BYTES;
         uint8_t* v_dst = k_dst + Cfg::K_BYTES;
         mbar_expect_tx(&k_full[s], Cfg::K_BYTES);
@@ -160,73 +186,100 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
       }
       __syncwarp();
     };
-    mbar_wait(q_full, 0);
-    mbar_wait(&k_full[0], 0);
+    mbar_wait_sleep(q_full, 0);
+    mbar_wait_sleep(&k_full[0], 0);
     tc_fence_after();
     issue_s(0, 0);
     issue_s(0, 1);
+    // (An event loop that served the two groups independently, whichever barrier completed first, was tried: no gain at
+    // head dim 64, -6 % at head dim 128 -- profiles/r2_attention_fwd.md.)
     for (int j = 0; j < n_kv; ++j) {
       const uint32_t par = (uint32_t)(j & 1);
       const bool more = j + 1 < n_kv;
-      if (more) mbar_wait(&k_full[(j + 1) % Cfg::ST], (uint32_t)(((j + 1) / Cfg::ST) & 1));
-      mbar_wait(&v_full[j % Cfg::ST], (uint32_t)((j / Cfg::ST) & 1));
+      if (more) mbar_wait_sleep(&k_full[(j + 1) % Cfg::ST], (uint32_t)(((j + 1) / Cfg::ST) & 1));
+      mbar_wait_sleep(&v_full[j % Cfg::ST], (uint32_t)((j / Cfg::ST) & 1));
 #pragma unroll
       for (int t = 0; t < 2; ++t) {
+        FWD2_STAMP(16, j, 4 * t + 0, 0u);
         if (more) {
-          mbar_wait(&s_free[t], par);
+          mbar_wait_sleep(&s_free[t], par);
           tc_fence_after();
+          FWD2_STAMP(16, j, 4 * t + 1, 0u);
           issue_s(j + 1, t);
         }
-        mbar_wait(&p_full[t], par);
+        FWD2_STAMP(16, j, 4 * t + 2, 0u);
+        mbar_wait_sleep(&p_full[t], par);
         tc_fence_after();
+        FWD2_STAMP(16, j, 4 * t + 3, 0u);
         issue_pv(j, t, t == 1);
       }
     }
   } else {
     // ---------------------------------------------------------------- softmax groups / epilogue
-    const int t = (warp - 2) >> 2;          // query tile of this group
+    constexpr int HC = BKV / 2;             // key columns of the tile owned by this thread
+    const int t = (warp - 2) >> 3;          // query tile of this group
+    const int g = (warp - 2) & 7;
     const int qd = warp & 3;                // TMEM lane quarter this warp may touch
+    const int half = g >> 2;                // which half of the tile's key columns
     const int row = qd * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
-    const uint32_t s_addr = lane_base + Cfg::S_COL + (uint32_t)t * 128u;
-    const uint32_t o_addr = lane_base + Cfg::O_COL + (uint32_t)(t * D);
-    const uint32_t p_taddr = lane_base + Cfg::P_COL + (uint32_t)t * Cfg::P_STRIDE;
+    const uint32_t s_addr = lane_base + Cfg::S_COL + (uint32_t)t * 128u + (uint32_t)(half * HC);
+    const uint32_t o_addr = lane_base + Cfg::O_COL + (uint32_t)(t * D) + (uint32_t)(half * (D / 2));
+    const uint32_t p_taddr = lane_base + Cfg::P_COL + (uint32_t)t * Cfg::P_STRIDE + (uint32_t)(half * (HC / 2));
+    const int pair_bar = 1 + t * 4 + qd;    // named barrier of the two warps that share these 32 rows
+    float* x_mine = xch + (t * 2 + half) * 128 + row;           // + (tile parity) * 512
+    float* x_peer = xch + (t * 2 + (half ^ 1)) * 128 + row;
     const float c = p.scale_log2;
     float m_used = -INFINITY;
-    float l_sum = 0.f;
+    float l_sum = 0.f;                      // this thread's half of the row sum
     for (int j = 0; j < n_kv; ++j) {
+      FWD2_STAMP(t * 8 + g, j, 0, 0u);
       mbar_wait(&s_full[t], (uint32_t)(j & 1));
       tc_fence_after();
-      uint32_t sr[BKV];                    // this thread's row of S, kept in registers (raw fp32 bits)
+      FWD2_STAMP(t * 8 + g, j, 1, 0u);
+      uint32_t sr[HC];                     // this thread's part of the row of S, kept in registers (raw fp32 bits)
 #pragma unroll
-      for (int c0 = 0; c0 < BKV; c0 += 32) tmem_ld32(s_addr + c0, sr + c0);
+      for (int c0 = 0; c0 < HC; c0 += 32) tmem_ld32(s_addr + c0, sr + c0);
       tmem_ld_wait();
       tc_fence_before();
       mbar_arrive(&s_free[t]);             // S_t may be overwritten by the next tile's Q K^T
-      const int kv_valid = p.L - j * BKV;  // keys of this tile that exist (>= BKV except on the last tile)
-      if (kv_valid < BKV) {
+      FWD2_STAMP(t * 8 + g, j, 2, sr[0]);
+      const int kv_valid = p.L - j * BKV - half * HC;  // keys of this part that exist (>= HC except on the last tile)
+      if (kv_valid < HC) {
 #pragma unroll
-        for (int i = 0; i < BKV; ++i) if (i >= kv_valid) sr[i] = 0xff800000u;   // -inf
+        for (int i = 0; i < HC; ++i) if (i >= kv_valid) sr[i] = 0xff800000u;   // -inf
       }
-      float mx0 = __uint_as_float(sr[0]), mx1 = __uint_as_float(sr[1]);
+      float mxa[8];                        // 8 independent chains
 #pragma unroll
-      for (int i = 2; i < BKV; i += 2) {
-        mx0 = fmaxf(mx0, __uint_as_float(sr[i]));
-        mx1 = fmaxf(mx1, __uint_as_float(sr[i + 1]));
+      for (int i = 0; i < 8; ++i) mxa[i] = __uint_as_float(sr[i]);
+#pragma unroll
+      for (int i = 8; i < HC; i += 8) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) mxa[u] = fmaxf(mxa[u], __uint_as_float(sr[i + u]));
       }
-      const float mx = fmaxf(mx0, mx1);
-      // previous O_t += P_t V must be complete before P_t is overwritten or O_t rescaled
+      float mx = fmaxf(fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3])),
+                       fmaxf(fmaxf(mxa[4], mxa[5]), fmaxf(mxa[6], mxa[7])));
+      // row maximum over both halves: exchange through shared memory (slot alternates with the tile parity, so one
+      // barrier per tile suffices: a slot is rewritten two tiles later, after the peer has passed the next barrier)
+      x_mine[(j & 1) * 512] = mx;
+      asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+      mx = fmaxf(mx, x_peer[(j & 1) * 512]);
+      FWD2_STAMP(t * 8 + g, j, 3, __float_as_uint(mx));
+      // previous O_t += P_t V must be complete before P_t is overwritten or O_t rescaled.  (Waiting only after the
+      // exponentials -- the MUFU work does not need it -- was tried and LOST 5 %: this wait is what staggers the two
+      // groups' exp2 phases; profiles/r2_attention_fwd.md.)
       if (j > 0) { mbar_wait(&pv_done[t], (uint32_t)((j - 1) & 1)); tc_fence_after(); }
+      FWD2_STAMP(t * 8 + g, j, 4, 0u);
       const bool grow = (mx - m_used) * c > 8.0f;   // lazy rescale: move the offset only for > 2^8 growth
       if (j == 0) {
         m_used = mx;
-      } else if (__any_sync(0xffffffffu, grow)) {
+      } else if (__any_sync(0xffffffffu, grow)) {   // both warps of the pair see the same 32 row maxima
         const float m_new = fmaxf(m_used, mx);
         const float f = fast_exp2((m_used - m_new) * c);
         m_used = m_new;
         l_sum *= f;
 #pragma unroll
-        for (int c0 = 0; c0 < D; c0 += 16) {
+        for (int c0 = 0; c0 < D / 2; c0 += 16) {    // this half's columns of O_t
           uint32_t r[16];
           tmem_ld16(o_addr + c0, r);
           tmem_ld_wait();
@@ -237,18 +290,20 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
         tmem_st_wait();
       }
       const float mc = m_used * c;
+      FWD2_STAMP(t * 8 + g, j, 5, 0u);
 #pragma unroll
-      for (int i = 0; i < BKV; ++i)        // exp2(-inf) = 0 for masked keys
+      for (int i = 0; i < HC; ++i)         // exp2(-inf) = 0 for masked keys
         sr[i] = __float_as_uint(fast_exp2(fmaf(__uint_as_float(sr[i]), c, -mc)));
-      float ls0 = 0.f, ls1 = 0.f, ls2 = 0.f, ls3 = 0.f;
+      FWD2_STAMP(t * 8 + g, j, 6, sr[0] ^ sr[HC - 1] ^ sr[HC / 2]);
+      float lsa[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-      for (int i = 0; i < BKV; i += 4) {
-        ls0 += __uint_as_float(sr[i]);     ls1 += __uint_as_float(sr[i + 1]);
-        ls2 += __uint_as_float(sr[i + 2]); ls3 += __uint_as_float(sr[i + 3]);
+      for (int i = 0; i < HC; i += 8) {
+#pragma unroll
+        for (int u = 0; u < 8; ++u) lsa[u] += __uint_as_float(sr[i + u]);
       }
-      l_sum += (ls0 + ls1) + (ls2 + ls3);
+      l_sum += ((lsa[0] + lsa[1]) + (lsa[2] + lsa[3])) + ((lsa[4] + lsa[5]) + (lsa[6] + lsa[7]));
 #pragma unroll
-      for (int c0 = 0; c0 < BKV / 2; c0 += 16) {       // P_t -> tensor memory, two fp16 per column
+      for (int c0 = 0; c0 < HC / 2; c0 += 16) {        // P_t -> tensor memory, two fp16 per column
         uint32_t pk[16];
 #pragma unroll
         for (int i = 0; i < 16; ++i)
@@ -258,32 +313,36 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
       tmem_st_wait();
       tc_fence_before();
       mbar_arrive(&p_full[t]);
+      FWD2_STAMP(t * 8 + g, j, 7, 0u);
     }
-    // epilogue: O / l -> fp16 global, lse
+    // epilogue: O / l -> fp16 global, lse.  Row sum = this thread's half + the peer's.
+    x_mine[(n_kv & 1) * 512] = l_sum;
+    asm volatile("bar.sync %0, 64;" :: "r"(pair_bar) : "memory");
+    l_sum += x_peer[(n_kv & 1) * 512];
     mbar_wait(&pv_done[t], (uint32_t)((n_kv - 1) & 1));
     tc_fence_after();
     const int qi = q0 + t * 128 + row;
     const bool valid = qi < p.L;
     const float inv_l = 1.0f / l_sum;
-    __half* op = p.out + ((long long)n * p.L + qi) * p.ldo + head * D;
+    __half* op = p.out + ((long long)n * p.L + qi) * p.ldo + head * D + half * (D / 2);
 #pragma unroll
-    for (int c0 = 0; c0 < D; c0 += 32) {
+    for (int c0 = 0; c0 < D / 2; c0 += 32) {
       uint32_t r[32];
       tmem_ld32(o_addr + c0, r);
       tmem_ld_wait();
       if (valid) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
+        for (int gg = 0; gg < 4; ++gg) {
           uint4 o;
-          o.x = pack_f16x2(__uint_as_float(r[8 * g + 0]) * inv_l, __uint_as_float(r[8 * g + 1]) * inv_l);
-          o.y = pack_f16x2(__uint_as_float(r[8 * g + 2]) * inv_l, __uint_as_float(r[8 * g + 3]) * inv_l);
-          o.z = pack_f16x2(__uint_as_float(r[8 * g + 4]) * inv_l, __uint_as_float(r[8 * g + 5]) * inv_l);
-          o.w = pack_f16x2(__uint_as_float(r[8 * g + 6]) * inv_l, __uint_as_float(r[8 * g + 7]) * inv_l);
-          *reinterpret_cast<uint4*>(op + c0 + 8 * g) = o;
+          o.x = pack_f16x2(__uint_as_float(r[8 * gg + 0]) * inv_l, __uint_as_float(r[8 * gg + 1]) * inv_l);
+          o.y = pack_f16x2(__uint_as_float(r[8 * gg + 2]) * inv_l, __uint_as_float(r[8 * gg + 3]) * inv_l);
+          o.z = pack_f16x2(__uint_as_float(r[8 * gg + 4]) * inv_l, __uint_as_float(r[8 * gg + 5]) * inv_l);
+          o.w = pack_f16x2(__uint_as_float(r[8 * gg + 6]) * inv_l, __uint_as_float(r[8 * gg + 7]) * inv_l);
+          *reinterpret_cast<uint4*>(op + c0 + 8 * gg) = o;
         }
       }
     }
-    if (valid && p.lse) p.lse[((long long)n * p.heads + head) * p.L + qi] = m_used * c + log2f(l_sum);
+    if (half == 0 && valid && p.lse) p.lse[((long long)n * p.heads + head) * p.L + qi] = m_used * c + log2f(l_sum);
   }
   tc_fence_before();
   __syncthreads();
@@ -324,6 +383,10 @@ int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int he
   else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }    // unet.py:359
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)ch);
   p.out = (__half*)out; p.ldo = ldo; p.lse = lse;
+  p.trace = nullptr;
+#ifdef FWD2_TRACE
+  { const char* e = getenv("B2D_FWD2_TRACE_PTR"); if (e) p.trace = (long long*)strtoull(e, nullptr, 0); }
+#endif
   if (ch == 64) return launch_attn_fwd2<64, 128>(qkv, ldqkv, N, 3 * C, p, stream);
   return launch_attn_fwd2<128, 64>(qkv, ldqkv, N, 3 * C, p, stream);
 }

@@ -86,7 +86,18 @@ class DenoiserEngine:
         self._stats = {}                      # data_ptr -> (pair statistics, tensor) of tensors a fused convolution produced
         self._fwd_arena, self._bwd_arena = _ZeroArena(), _ZeroArena()
         self._overflow = None                 # int32 device counter: saturated fp16 gradients seen by the backward
-        self.fuse_groupnorm = os.environ.get("B2D_GN_FUSE", "1") != "0"      # A/B switch for the fused epilogues
+        # A/B switch for the fused epilogues: 0 = two-kernel GroupNorm, 1 = fused statistics + fused backward reduce,
+        # 2 = fused statistics only (backward: two-kernel reduce + apply)
+        mode = os.environ.get("B2D_GN_FUSE", "1")
+        self.fuse_groupnorm = mode != "0"
+        self.fuse_groupnorm_bwd = mode == "1"
+        # The fused epilogues cost 30-90 us on the convolutions that are already bound by their epilogue (1x1 and
+        # 64-channel 3x3 layers: K = taps * Cin small, the tensor pipe 2 % busy) -- more than the GroupNorm pass they
+        # save; on the K >= 1152 / 2304 layers they are nearly free (profiles/r2_groupnorm_fused.md).  Below the
+        # threshold the statistics come from one pass over the tensor (b2d_pair_stats) and the backward reduce from the
+        # two-kernel path.  B2D_GN_FUSE_MINK="stats,gnb" overrides (0,0 = fuse everywhere).
+        mk = os.environ.get("B2D_GN_FUSE_MINK", "1152,2304").split(",")
+        self.fuse_min_k_stats, self.fuse_min_k_gnb = int(mk[0]), int(mk[1])
         self.seq_parallel = None              # parallel.SequenceParallelAttention, when one clip is split across GPUs
         self._step_seed = 0
         # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
@@ -166,7 +177,9 @@ class DenoiserEngine:
         address for `_gn_fwd`).  gnb: ops.GnBwdFuse (the output is the dL/dy of a GroupNorm)."""
         if not isinstance(wp, list):
             st = None
-            if stats and self.fuse_groupnorm and ops.gn_fusable(x.shape[1] // stride, x.shape[2] // stride, cout):
+            kk = k * k * (x.shape[3] + (x2.shape[3] if x2 is not None else 0))
+            if (stats and self.fuse_groupnorm and kk >= self.fuse_min_k_stats
+                    and ops.gn_fusable(x.shape[1] // stride, x.shape[2] // stride, cout)):
                 st = self._fwd_arena.zeros((x.shape[0], cout // 2, 2), torch.float64)
             out = ops.conv2d(x, wp, cout, k, stride, x2=x2, bias=bias, emb=emb, residual=residual, stats_out=st, gnb=gnb)
             if st is not None:
@@ -232,12 +245,14 @@ class DenoiserEngine:
                                                   seed=seed, want_mask=want_mask)
         return self._unfold(y, x), mean, rstd, mask
 
-    def _gnb(self, x, gn, mean, rstd, x2=None, act=True, mask=None, drop_p=0.0):
+    def _gnb(self, x, gn, mean, rstd, kk, x2=None, act=True, mask=None, drop_p=0.0):
         """ops.GnBwdFuse for the data-gradient convolution that produces dL/dy of act(GroupNorm([x | x2])), or None when
         the fused epilogue does not apply (dims=3 frame folding, planes the staging does not cover, dropout without
-        saved mask bits, A/B switch)."""
+        saved mask bits, a data-gradient convolution with a reduction length kk = taps * channels below the threshold
+        where the epilogue costs more than the reduce pass it replaces, A/B switch)."""
         ct = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
-        if (not self.fuse_groupnorm or self.T != 1 or not ops.gn_fusable(x.shape[1], x.shape[2], ct)
+        if (not self.fuse_groupnorm_bwd or self.T != 1 or kk < self.fuse_min_k_gnb
+                or not ops.gn_fusable(x.shape[1], x.shape[2], ct)
                 or (drop_p > 0.0 and mask is None)):
             return None
         ab = self._bwd_arena.zeros((x.shape[0], ct, 2), torch.float32)
@@ -618,7 +633,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     dyp = ops.nchw_to_pixel_major(dout, 64, scale=scale2)
     eng._wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
     bias_grad(dyp, conv_out.bias, 64)
-    gnb = eng._gnb(hd["h"], gn, hd["mean"], hd["rstd"], act=True)
+    gnb = eng._gnb(hd["h"], gn, hd["mean"], hd["rstd"], 9 * 64, act=True)
     d_hh = eng._conv(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1, gnb=gnb)
     if gnb is not None:
         dh, _ = eng._gn_bwd_fused(G, hd["h"], gn, gnb, d_hh)
@@ -636,7 +651,8 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         # conv2 (out_layers[3]) and the skip path share dout_
         eng._wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
         bias_grad(dout_, conv2.bias, also=rb.skip_connection.bias if has_skip_conv else None)
-        gnb2 = eng._gnb(t["h2"], gn2, t["mean2"], t["rstd2"], act=True, mask=t.get("mask2"), drop_p=t["drop_p"])
+        gnb2 = eng._gnb(t["h2"], gn2, t["mean2"], t["rstd2"], 9 * cout, act=True, mask=t.get("mask2"),
+                        drop_p=t["drop_p"])
         d_h3 = eng._conv(dout_, eng.w_dgrad(conv2), cout, 3, 1, gnb=gnb2)
         off = eng.emb_off[id(rb)]
         fused_cs = eng.T == 1                              # d emb_out (unet.py:266) and conv1 bias: sums of d_h2
@@ -650,7 +666,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
         eng._wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
         cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
-        gnb1 = eng._gnb(x, gn1, t["mean1"], t["rstd1"], x2=x2, act=True)
+        gnb1 = eng._gnb(x, gn1, t["mean1"], t["rstd1"], 9 * cout, x2=x2, act=True)
         d_h1 = eng._conv(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1, gnb=gnb1)
         if has_skip_conv:
             sc = rb.skip_connection
@@ -681,7 +697,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         dqkv = eng._unfold(dqkv, t["qkv"])
         ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
         bias_grad(dqkv, ab.qkv.bias)
-        gnb = eng._gnb(t["x"], gn_, t["mean"], t["rstd"], act=False)
+        gnb = eng._gnb(t["x"], gn_, t["mean"], t["rstd"], 3 * C_, act=False)
         d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1, gnb=gnb)
         if gnb is not None:
             dx, _ = eng._gn_bwd_fused(G, t["x"], gn_, gnb, d_hn, add_a=dout_, add_b=extra, want_colsum=True)

@@ -187,7 +187,8 @@ def conv2d(x, w_packed, cout, ksize=1, stride=1, x2=None, bias=None, emb=None, r
         a.gnb_mean, a.gnb_rstd = gnb.mean.data_ptr(), gnb.rstd.data_ptr()
         a.gnb_gamma, a.gnb_beta, a.gnb_act = gnb.gamma.data_ptr(), gnb.beta.data_ptr(), int(gnb.act)
         a.gnb_mask, a.gnb_keep_scale, a.gnb_ab = L.ptr(gnb.mask), float(gnb.keep_scale), gnb.ab.data_ptr()
-    with _timed("conv2d", (N, H, W, a.C1 + a.C2, cout, ksize, stride)):
+    epi = "gnb" if gnb is not None else ("stats" if stats_out is not None else "")
+    with _timed("conv2d", (N, H, W, a.C1 + a.C2, cout, ksize, stride) + ((epi,) if epi else ())):
         L.check(L.lib().b2d_conv2d(C.byref(a), _s()), "b2d_conv2d")
     return out if out is not None else out_nchw_f32
 
