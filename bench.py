@@ -160,7 +160,7 @@ class TrainStep:
         if os.environ.get("B2D_TORCH_ADAM") == "1":          # A/B runs only
             self.opt = torch.optim.Adam(model.parameters(), lr=1e-2, fused=True)
         else:
-            self.opt = P.Adam(model.parameters(), lr=1e-2)                            # train.py:102, one launch
+            self.opt = P.Adam(model.parameters(), lr=1e-2, skip_on_overflow=model)     # train.py:102, one launch
         self.reducer = GradientAllReducer(model) if world > 1 else None
         model.train()
 

@@ -200,6 +200,11 @@ typedef struct b2d_gn_args {
   int act;
   float drop_p;
   uint64_t seed;
+  /* backward calls only (may be NULL): int32 device counter, += 1 per thread that saw a gradient element with
+   * |value| >= 65504 (a saturated 16-bit gradient) or NaN -- the overflow check of the reference's low-precision
+   * trainer (fp16_util.py:236-237 check_overflow), kept on the device: b2d_grad_scale_finalize / b2d_adam_step_guarded
+   * consume it without a host synchronisation. */
+  int32_t* overflow;
 } b2d_gn_args;
 
 size_t b2d_groupnorm_workspace_bytes(int N, int Ctot);
@@ -230,15 +235,14 @@ int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, c
  * b2d_groupnorm_bwd_apply: the input-gradient pass given dyh = dy * act'(z) * mask (what the fused data-gradient
  *   epilogue stores) and ab[n][c] = (sum dyh, sum dyh * x) (fp32 [N][Ctot][2]):
  *     dx = rstd * (dyh*gamma - mean_g(dyh*gamma) - xhat * mean_g(dyh*gamma*xhat))  (+ add_a + add_b as above),
- *   and dgamma[c] += sum_n rstd*(ab1 - mean*ab0), dbeta[c] += sum_n ab0.  overflow (optional, int32, accumulated):
- *   number of threads that saw |dyh| or |dx| >= 65504, i.e. a saturated fp16 gradient (fp16_util.py:236-237). */
+ *   and dgamma[c] += sum_n rstd*(ab1 - mean*ab0), dbeta[c] += sum_n ab0.  a->overflow counts saturated gradients. */
 int b2d_pair_stats(const void* x, int64_t ld, int C, int N, int HW, double* st, void* stream);
 int b2d_groupnorm_apply(const b2d_gn_args* a, const double* st1, const double* st2, int rows_per_sample, void* y,
                         float* mean, float* rstd, uint8_t* mask_out, void* stream);
 int b2d_groupnorm_bwd_apply(const b2d_gn_args* a, const void* dyh, const float* mean, const float* rstd,
                             const float* ab, void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a,
                             int64_t lda, const void* add_b, int64_t ldb, int add_a_full, float* dx1_colsum,
-                            int64_t ld_colsum, float* dgamma, float* dbeta, int* overflow, void* stream);
+                            int64_t ld_colsum, float* dgamma, float* dbeta, void* stream);
 
 /* ------------------------------------------------------------------------
  * Layout / conditioning helpers (HBM bound).
@@ -268,6 +272,16 @@ int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C, int HW, i
  * max|x| * 2^k lies in [target/2, target), scale2[1] = 2^-k.  (The reference's own low-precision design is fp16
  * with dynamic loss scaling: fp16_util.py:148-233 MixedPrecisionTrainer.) */
 int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream);
+/* The same in two halves, so that ranks which must agree on the scale (one clip split across GPUs: their partial
+ * dK / dV are summed in fp16) can all-reduce(MAX) the maximum in between, and with the overflow state of
+ * fp16_util.py:148-233 (MixedPrecisionTrainer: lg_loss_scale -= 1 after an overflowed step, += 1e-3 after a clean one):
+ *   b2d_absmax:  out1[0] = max |x|   (fp32 bits; zeroed first)
+ *   b2d_grad_scale_finalize: scale2[0] holds max |x| on entry; on exit scale2 = (2^k, 2^-k) with k lowered by
+ *     ceil(backoff) bits.  state (int32[4], may be NULL): [0] overflow events counted during the PREVIOUS backward
+ *     (b2d_gn_args.overflow points here) -- consumed: > 0 raises the back-off by one bit and counts a skipped step,
+ *     0 lowers it by 1/1024 bit; [1] back-off in 1/1024 bits; [2] steps skipped so far; [3] copy of [0] for logging. */
+int b2d_absmax(const float* x, int64_t n, float* out1, void* stream);
+int b2d_grad_scale_finalize(float* scale2, float target, int32_t* state, void* stream);
 /* x[i] *= *scale  (unscale the fp32 parameter gradients). */
 int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream);
 /* fp32 convolution weights (state_dict layout, element strides s_o / s_i / s_k over Cout / Cin / the K = kh*kw
@@ -380,6 +394,11 @@ typedef struct B2dAdamChunk {
  * rounded once, as torch does: 1.f - 0.999f is 4.7e-5 off).  All arrays fp32, updated in place. */
 int b2d_adam_step(const B2dAdamChunk* chunks_dev, int n_chunks, double lr, double beta1, double beta2, float eps,
                   float weight_decay, double bias_correction1, double bias_correction2, void* stream);
+/* The same, but a no-op when *found_overflow != 0 (int32 device word, e.g. state[0] above): the skipped step of
+ * fp16_util.py:222-233 (`optimize_fp16`: "Found NaN, decreased lg_loss_scale") decided on the device. */
+int b2d_adam_step_guarded(const B2dAdamChunk* chunks_dev, int n_chunks, double lr, double beta1, double beta2, float eps,
+                          float weight_decay, double bias_correction1, double bias_correction2,
+                          const int32_t* found_overflow, void* stream);
 
 /* ------------------------------------------------------------------------
  * Input pipeline: TalkingFaceFrameDataset.__getitem__,

@@ -56,6 +56,7 @@ class GnArgs(C.Structure):
         ("N", c_int), ("HW", c_int),
         ("gamma", c_void_p), ("beta", c_void_p),
         ("eps", c_float), ("act", c_int), ("drop_p", c_float), ("seed", C.c_uint64),
+        ("overflow", c_void_p),
     ]
 
 
@@ -86,7 +87,7 @@ SIGNATURES = {
                                     c_void_p]),
     "b2d_groupnorm_bwd_apply": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int64,
                                         c_void_p, c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64,
-                                        c_void_p, c_void_p, c_void_p, c_void_p]),
+                                        c_void_p, c_void_p, c_void_p]),
     "b2d_attention_fwd": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p,
                                   c_void_p]),
     "b2d_pack_conv_weight": (c_int, [c_void_p, c_int64, c_int64, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int, c_int,
@@ -107,6 +108,8 @@ SIGNATURES = {
     "b2d_nchw_to_pixel_major": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "b2d_grad_scale": (c_int, [c_void_p, c_int64, c_float, c_void_p, c_void_p]),
     "b2d_scale_f32": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "b2d_absmax": (c_int, [c_void_p, c_int64, c_void_p, c_void_p]),
+    "b2d_grad_scale_finalize": (c_int, [c_void_p, c_float, c_void_p, c_void_p]),
     "b2d_w2v_layer0_fwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                    c_float, c_void_p, c_int, c_void_p, c_void_p, c_void_p]),
     "b2d_w2v_layer0_bwd": (c_int, [c_void_p, c_int64, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
@@ -133,6 +136,8 @@ SIGNATURES = {
                                        c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "b2d_adam_step": (c_int, [c_void_p, c_int, C.c_double, C.c_double, C.c_double, c_float, c_float, C.c_double, C.c_double,
                               c_void_p]),
+    "b2d_adam_step_guarded": (c_int, [c_void_p, c_int, C.c_double, C.c_double, C.c_double, c_float, c_float, C.c_double,
+                                      C.c_double, c_void_p, c_void_p]),
 }
 
 

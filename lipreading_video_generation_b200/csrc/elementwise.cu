@@ -422,13 +422,25 @@ absmax_kernel(const float* __restrict__ x, long long n, unsigned int* __restrict
     if (threadIdx.x == 0 && m == m) atomicMax(out_bits, __float_as_uint(m));   // non-negative floats order as uints
   }
 }
-__global__ void grad_scale_finalize_kernel(float* __restrict__ scale2, float target) {
+// state: [0] overflow events of the previous backward (consumed here), [1] back-off in 1/1024 bits, [2] skipped
+// steps, [3] last consumed count -- the device-side form of MixedPrecisionTrainer's lg_loss_scale update
+// (fp16_util.py:222-233: -1 after an overflow, +fp16_scale_growth = 1e-3 after a clean step).
+__global__ void grad_scale_finalize_kernel(float* __restrict__ scale2, float target, int* __restrict__ state) {
+  int backoff_bits = 0;
+  if (state != nullptr) {
+    const int ov = state[0];
+    state[3] = ov;
+    if (ov > 0) { state[1] += 1024; state[2] += 1; }
+    else if (state[1] > 0) state[1] -= 1;
+    state[0] = 0;
+    backoff_bits = (state[1] + 1023) >> 10;
+  }
   const float m = scale2[0];
   float s = 1.0f;
   if (m > 0.f && m < INFINITY) {
     int e;
     frexpf(target / m, &e);              // target/m = f * 2^e, f in [0.5, 1)  ->  2^(e-1) <= target/m
-    e = max(-60, min(60, e - 1));
+    e = max(-60, min(60, e - 1 - backoff_bits));
     s = ldexpf(1.0f, e);
   }
   scale2[0] = s;
@@ -519,15 +531,25 @@ extern "C" int b2d_nchw_to_pixel_major(const float* src, void* dst, int N, int C
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
-extern "C" int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream) {
-  B2D_REQUIRE(x && scale2 && n > 0 && target > 0.f, B2D_ERR_SHAPE, "grad_scale: bad arguments");
+extern "C" int b2d_absmax(const float* x, int64_t n, float* out1, void* stream) {
+  B2D_REQUIRE(x && out1 && n > 0, B2D_ERR_SHAPE, "absmax: bad arguments");
   cudaStream_t st = (cudaStream_t)stream;
-  B2D_CHECK_CUDA(cudaMemsetAsync(scale2, 0, 2 * sizeof(float), st));
-  absmax_kernel<<<ew_blocks(n), 256, 0, st>>>(x, n, (unsigned int*)scale2);
-  B2D_CHECK_LAUNCH();
-  grad_scale_finalize_kernel<<<1, 1, 0, st>>>(scale2, target);
+  B2D_CHECK_CUDA(cudaMemsetAsync(out1, 0, sizeof(float), st));
+  absmax_kernel<<<ew_blocks(n), 256, 0, st>>>(x, n, (unsigned int*)out1);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
+}
+extern "C" int b2d_grad_scale_finalize(float* scale2, float target, int32_t* state, void* stream) {
+  B2D_REQUIRE(scale2 && target > 0.f, B2D_ERR_SHAPE, "grad_scale_finalize: bad arguments");
+  grad_scale_finalize_kernel<<<1, 1, 0, (cudaStream_t)stream>>>(scale2, target, state);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_grad_scale(const float* x, int64_t n, float target, float* scale2, void* stream) {
+  B2D_REQUIRE(x && scale2 && n > 0 && target > 0.f, B2D_ERR_SHAPE, "grad_scale: bad arguments");
+  int rc = b2d_absmax(x, n, scale2, stream);
+  if (rc) return rc;
+  return b2d_grad_scale_finalize(scale2, target, nullptr, stream);
 }
 extern "C" int b2d_scale_f32(float* x, int64_t n, const float* scale, void* stream) {
   B2D_REQUIRE(x && scale && n >= 0, B2D_ERR_SHAPE, "scale_f32: bad arguments");

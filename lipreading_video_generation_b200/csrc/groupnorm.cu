@@ -242,6 +242,7 @@ struct GnBwdOut {
   const __half* add_b; long long ldb;
   int add_a_full;  // add_a spans all C1+C2 channels (also added to dx2)
   float* colsum; long long ldcs;  // optional: colsum[n][c] += sum over pixels of dx1[n, :, c] (c < C1), fp32
+  int* overflow;                  // optional: += 1 per thread that saw a saturated (|v| >= 65504) or NaN gradient element
 };
 
 // Per-sample column sums of the dx1 values a thread produced (cs[8], channels c..c+7 of source 1), folded into
@@ -303,6 +304,7 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
   const bool has_a = o.add_a && (first || o.add_a_full);
   const bool has_b = o.add_b && first;
   float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float amax = 0.f;
   const int step = gridDim.x * rows;
   for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 2 * step) {
     uint4 rx[2], rd[2], ra[2], rb[2];
@@ -324,6 +326,8 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
     float x[8], d[8];
     unpack8(rx[u], x);
     unpack8(rd[u], d);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(d[i]));
     if (drop_p > 0.f) {
       bool keep[8];
       dropout_keep8(seed, (unsigned long long)gp * Ctot + c, drop_p, keep);
@@ -346,6 +350,8 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
     if (has_b) { float t[8]; unpack8(rb[u], t);
 #pragma unroll
       for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fabsf(x[i]));
     if (first) {
       store8(o.dx1 + gp * o.ldd1 + c, x);
       if (CS) {
@@ -357,6 +363,7 @@ gn_bwd_apply_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot,
     }
     }
   }
+  if (o.overflow != nullptr && !(amax < 65504.f)) atomicAdd(o.overflow, 1);   // saturated (or NaN) 16-bit gradient seen
   if (CS) gn_colsum_flush(o, shc, cs, s.C1, c, n, first);
 }
 
@@ -615,6 +622,7 @@ gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, in
   const bool has_a = o.add_a && (first || o.add_a_full);
   const bool has_b = o.add_b && first;
   float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  float amax = 0.f;
   for (int pix0 = p0 + prow; pix0 < p1; pix0 += 2 * rows) {
     uint4 rd[2], ra[2], rb[2];
 #pragma unroll
@@ -656,6 +664,8 @@ gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, in
       if (has_b) { float t[8]; unpack8(rb[u], t);
 #pragma unroll
         for (int i = 0; i < 8; ++i) x[i] += t[i]; }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) amax = fmaxf(amax, fmaxf(fabsf(x[i]), fabsf(d[i])));
       if (first) {
         store8(o.dx1 + gp * o.ldd1 + c, x);
         if (CS) {
@@ -667,6 +677,7 @@ gn_bwd_fused_kernel(GnSrc s, const __half* __restrict__ dy, int HW, int Ctot, in
       }
     }
   }
+  if (o.overflow != nullptr && !(amax < 65504.f)) atomicAdd(o.overflow, 1);
   cluster_wait();                                       // after it no peer reads this CTA's `part`; `sh` is free for reuse
   if (CS) gn_colsum_flush(o, sh, cs, s.C1, c, n, first);
 }
@@ -797,7 +808,7 @@ template <bool CS>
 __global__ void __launch_bounds__(256, CS ? 2 : 3)
 gn_bwd_apply2_kernel(GnSrc s, const __half* __restrict__ dyh, int HW, int Ctot, const float* __restrict__ mean,
                      const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ ab,
-                     GnBwdOut o, int* __restrict__ overflow) {
+                     GnBwdOut o) {
   __shared__ float s1[32], s2[32];
   extern __shared__ float shc[];   // [C1] when o.colsum
   const int n = blockIdx.y;
@@ -879,7 +890,7 @@ gn_bwd_apply2_kernel(GnSrc s, const __half* __restrict__ dyh, int HW, int Ctot, 
       }
     }
   }
-  if (overflow != nullptr && !(amax < 65504.f)) atomicAdd(overflow, 1);   // saturated (or NaN) fp16 gradient seen
+  if (o.overflow != nullptr && !(amax < 65504.f)) atomicAdd(o.overflow, 1);   // saturated (or NaN) fp16 gradient seen
   if (CS) gn_colsum_flush(o, shc, cs, s.C1, c, n, first);
 }
 
@@ -1039,7 +1050,7 @@ extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const flo
   GnBwdOut o;
   o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
   o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
-  o.colsum = dx1_colsum; o.ldcs = ld_colsum;
+  o.colsum = dx1_colsum; o.ldcs = ld_colsum; o.overflow = a->overflow;
   int ppc = 0; size_t fsmem = 0;
   if (const int cl = gn_fused_plan(a->HW, Ctot, &ppc, &fsmem)) {
     gn_launch_dims(a->N, a->HW, Ctot, 1, &grid, &threads);
@@ -1104,8 +1115,7 @@ extern "C" int b2d_groupnorm_apply(const b2d_gn_args* a, const double* st1, cons
 extern "C" int b2d_groupnorm_bwd_apply(const b2d_gn_args* a, const void* dyh, const float* mean, const float* rstd,
                                        const float* ab, void* dx1, int64_t lddx1, void* dx2, int64_t lddx2,
                                        const void* add_a, int64_t lda, const void* add_b, int64_t ldb, int add_a_full,
-                                       float* dx1_colsum, int64_t ld_colsum, float* dgamma, float* dbeta, int* overflow,
-                                       void* stream) {
+                                       float* dx1_colsum, int64_t ld_colsum, float* dgamma, float* dbeta, void* stream) {
   int rc = gn_check(a, "groupnorm_bwd_apply");
   if (rc) return rc;
   const GnSrc s = make_src(a);
@@ -1117,15 +1127,14 @@ extern "C" int b2d_groupnorm_bwd_apply(const b2d_gn_args* a, const void* dyh, co
   GnBwdOut o;
   o.dx1 = (__half*)dx1; o.ldd1 = lddx1; o.dx2 = (__half*)dx2; o.ldd2 = lddx2;
   o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
-  o.colsum = dx1_colsum; o.ldcs = ld_colsum;
+  o.colsum = dx1_colsum; o.ldcs = ld_colsum; o.overflow = a->overflow;
   dim3 grid; int threads;
   gn_launch_dims(a->N, a->HW, Ctot, 8, &grid, &threads);
   if (dx1_colsum)
     gn_bwd_apply2_kernel<true><<<grid, threads, s.C1 * sizeof(float), st>>>(s, (const __half*)dyh, a->HW, Ctot, mean, rstd,
-                                                                           a->gamma, ab, o, overflow);
+                                                                           a->gamma, ab, o);
   else
-    gn_bwd_apply2_kernel<false><<<grid, threads, 0, st>>>(s, (const __half*)dyh, a->HW, Ctot, mean, rstd, a->gamma, ab, o,
-                                                          overflow);
+    gn_bwd_apply2_kernel<false><<<grid, threads, 0, st>>>(s, (const __half*)dyh, a->HW, Ctot, mean, rstd, a->gamma, ab, o);
   B2D_CHECK_LAUNCH();
   gn_param_grad2_kernel<<<(Ctot + 31) / 32, 256, 0, st>>>(ab, mean, rstd, a->N, Ctot, dgamma, dbeta);
   B2D_CHECK_LAUNCH();

@@ -26,7 +26,8 @@ constexpr int ADAM_THREADS = 512;
 
 // one CTA per chunk (a run of <= chunk_elems consecutive elements of one tensor); grid = number of chunks
 __global__ void __launch_bounds__(ADAM_THREADS)
-adam_multi_tensor_kernel(const B2dAdamChunk* __restrict__ chunks, AdamScalars s) {
+adam_multi_tensor_kernel(const B2dAdamChunk* __restrict__ chunks, AdamScalars s, const int* __restrict__ found_overflow) {
+  if (found_overflow != nullptr && *found_overflow != 0) return;      // skipped step (overflowed 16-bit gradients)
   const B2dAdamChunk c = chunks[blockIdx.x];
   float* __restrict__ p = c.param;
   const float* __restrict__ g = c.grad;
@@ -77,6 +78,13 @@ adam_multi_tensor_kernel(const B2dAdamChunk* __restrict__ chunks, AdamScalars s)
 
 extern "C" int b2d_adam_step(const B2dAdamChunk* chunks_dev, int n_chunks, double lr, double beta1_d, double beta2_d, float eps,
                              float weight_decay, double bias_correction1, double bias_correction2, void* stream) {
+  return b2d_adam_step_guarded(chunks_dev, n_chunks, lr, beta1_d, beta2_d, eps, weight_decay, bias_correction1,
+                               bias_correction2, nullptr, stream);
+}
+
+extern "C" int b2d_adam_step_guarded(const B2dAdamChunk* chunks_dev, int n_chunks, double lr, double beta1_d, double beta2_d,
+                                     float eps, float weight_decay, double bias_correction1, double bias_correction2,
+                                     const int32_t* found_overflow, void* stream) {
   using namespace b2d;
   if (n_chunks == 0) return B2D_OK;
   B2D_REQUIRE(chunks_dev != nullptr && n_chunks > 0, B2D_ERR_SHAPE, "adam_step: empty chunk table");
@@ -87,7 +95,7 @@ extern "C" int b2d_adam_step(const B2dAdamChunk* chunks_dev, int n_chunks, doubl
   s.inv_bc2_sqrt = (float)(1.0 / sqrt(bias_correction2));
   s.one_minus_beta1 = (float)(1.0 - (double)beta1_d); s.beta2 = (float)beta2_d; s.one_minus_beta2 = (float)(1.0 - beta2_d);
   s.eps = eps; s.weight_decay = weight_decay;
-  adam_multi_tensor_kernel<<<n_chunks, ADAM_THREADS, 0, (cudaStream_t)stream>>>(chunks_dev, s);
+  adam_multi_tensor_kernel<<<n_chunks, ADAM_THREADS, 0, (cudaStream_t)stream>>>(chunks_dev, s, found_overflow);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

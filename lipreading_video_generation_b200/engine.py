@@ -98,6 +98,14 @@ class DenoiserEngine:
         # two-kernel path.  B2D_GN_FUSE_MINK="stats,gnb" overrides (0,0 = fuse everywhere).
         mk = os.environ.get("B2D_GN_FUSE_MINK", "1152,2304").split(",")
         self.fuse_min_k_stats, self.fuse_min_k_gnb = int(mk[0]), int(mk[1])
+        # Deferred weight gradients: the tail of the backward -- the audio encoder's backward, ~1200 library launches of
+        # 3-10 us that leave most SMs idle -- runs AFTER the torso's; nothing depends on a weight gradient but the
+        # optimiser, so the last `defer_frac` of the torso's weight-gradient work is enqueued on a side stream when the
+        # torso backward ends and overlaps that tail.  B2D_DEFER_WGRAD=0 disables, a number sets the fraction.
+        dw = os.environ.get("B2D_DEFER_WGRAD", "0.45")
+        self.defer_frac = 0.0 if dw == "0" else float(dw)
+        self._wg_total = 0.0                  # weight-gradient work of one backward (previous step), MAC count
+        self._side = None
         self.seq_parallel = None              # parallel.SequenceParallelAttention, when one clip is split across GPUs
         self._step_seed = 0
         # ---- gradient layout: (param, flat offset, packed shape, unpack fn) in backward completion order
@@ -212,6 +220,11 @@ class DenoiserEngine:
                 ops.conv2d_wgrad(x[lo + 1:hi], dy[lo:hi - 1], gbuf[2], k, stride,
                                  x2=None if x2 is None else x2[lo + 1:hi])
 
+    def side_stream(self, device):
+        if self._side is None or self._side.device != device:
+            self._side = torch.cuda.Stream(device=device)
+        return self._side
+
     def _fold(self, t):
         """(B*T, H, W, C) -> (B, T*H, W, C): GroupNorm statistics and attention run over all T*H*W positions of a sample."""
         if t is None or self.T == 1:
@@ -281,11 +294,27 @@ class DenoiserEngine:
         dx1, dx2 = ops.groupnorm_bwd(self._fold(x), gn.weight.detach(), gn.bias.detach(), self._fold(dy), mean, rstd,
                                      G.g(gn.weight), G.g(gn.bias), x2=self._fold(x2), act=act, eps=gn.eps, drop_p=drop_p,
                                      seed=seed, add_a=self._fold(add_a), add_b=self._fold(add_b), add_a_full=add_a_full,
-                                     colsum_out=colsum_out)
+                                     colsum_out=colsum_out, overflow=self._overflow)
         dx1 = self._unfold(dx1, x)
         if want_colsum and colsum_out is not None:
             self._colsums = {dx1.data_ptr(): (colsum_out, dx1)}     # only the most recent one can be consumed next
         return dx1, self._unfold(dx2, x2) if x2 is not None else None
+
+    def overflow_report(self):
+        """(overflow events counted since the last backward started, back-off bits, steps skipped so far, events of the
+        last finished step) -- a host read of the int32[4] device state: call it outside the step loop or one step late."""
+        if self._overflow is None:
+            return (0, 0.0, 0, 0)
+        v = self._overflow.tolist()
+        return (v[0], v[1] / 1024.0, v[2], v[3])
+
+    def invalidate(self):
+        """Forget every cached operand copy (packed 16-bit weights, concatenated embedding weights): call after
+        mutating parameters behind autograd's back (`p.data.copy_()`, EMA updates, collectives on `.data`) when no
+        training forward precedes the next use."""
+        self._wcache.clear()
+        self._pack_table = None
+        self._weights_maybe_stale = False
 
     def emb_cat(self):
         ws = [rb.emb_layers[1].weight for rb in self.resblocks]
@@ -583,8 +612,10 @@ class _Grads:
         return v.reshape(co, ci)
 
 
-def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
-    """Hand-scheduled backward.  dout: fp32 (N,out_ch,S,S).  Returns (_Grads, d_audio_feat or None)."""
+def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None, defer=False):
+    """Hand-scheduled backward.  dout: fp32 (N,out_ch,S,S).  Returns (_Grads, d_audio_feat or None, finish) where
+    `finish` is None or a callable to run once the WHOLE backward pass has been enqueued (deferred weight gradients:
+    joins the side stream, unscales their slices, then fires the stage hooks)."""
     m = eng.model
     N, B, T = tape["N"], tape["B"], tape["T"]
     eng.T = T
@@ -601,8 +632,27 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     # fp16 gradient tensors: scale2 = [2^k, 2^-k] with max|dout| * 2^k in [64, 128); every gradient below is
     # carried times 2^k and each stage's slice of the flat fp32 buffer is unscaled as soon as the stage is done
     # (before the data-parallel reducer may all-reduce it: ranks choose different k).
-    scale2 = ops.grad_scale(dout)
+    # Ranks that share one clip (sequence-parallel attention) sum partial dK / dV in 16 bits: they must use the SAME
+    # scale, so the maximum is all-reduced (round-1 advisor finding: per-rank scales could differ by a factor 2 at a
+    # power-of-two boundary).  The overflow state lowers the scale after a step whose gradients saturated.
+    sp = eng.seq_parallel
+    scale2 = ops.grad_scale(dout, state=eng._overflow, reduce_max=sp.all_reduce_max if sp is not None else None)
     inv_scale = scale2[1:]
+    # ---- deferred weight gradients (see DenoiserEngine.__init__): decided per call from the work seen so far against
+    # the previous step's total; only when an encoder backward follows and no gradient accumulation is pending (the
+    # gradients are then handed over by the end-of-backward callback instead of through autograd, which would clone
+    # the packed views -- reading them -- as soon as this function returns)
+    defer_on = bool(defer) and eng.defer_frac > 0.0 and eng._wg_total > 0.0 and T == 1
+    deferred, seen = [], [0.0]
+
+    def wgrad(x, dy, gbuf, k, stride, x2=None, conv3d=True):
+        cin = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
+        seen[0] += float(dy.numel()) * cin * k * k
+        call = (eng._wgrad if conv3d else ops.conv2d_wgrad)
+        if defer_on and seen[0] > (1.0 - eng.defer_frac) * eng._wg_total:
+            deferred.append((call, x, dy, gbuf, k, stride, x2))
+        else:
+            call(x, dy, gbuf, k, stride, x2=x2)
 
     def done():
         nonlocal stage
@@ -610,7 +660,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         hi = G.stage_end[stage]
         if hi > lo:
             ops.scale_f32_(G.flat[lo:hi], inv_scale)
-        if on_stage_done is not None:
+        if on_stage_done is not None and not defer_on:
             on_stage_done(G, stage)
         stage += 1
 
@@ -631,7 +681,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     hd = tape["head"]
     gn, conv_out = m.out[0], m.out[2]
     dyp = ops.nchw_to_pixel_major(dout, 64, scale=scale2)
-    eng._wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
+    wgrad(hd["hh"], dyp, G.g(conv_out.weight), 3, 1)
     bias_grad(dyp, conv_out.bias, 64)
     gnb = eng._gnb(hd["h"], gn, hd["mean"], hd["rstd"], 9 * 64, act=True)
     d_hh = eng._conv(dyp, eng.w_dgrad(conv_out, cout_pad=64), conv_out.weight.shape[1], 3, 1, gnb=gnb)
@@ -649,7 +699,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         x, x2 = t["x"], t["x2"]
         has_skip_conv = not isinstance(rb.skip_connection, torch.nn.Identity)
         # conv2 (out_layers[3]) and the skip path share dout_
-        eng._wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
+        wgrad(t["h3"], dout_, G.g(conv2.weight), 3, 1)
         bias_grad(dout_, conv2.bias, also=rb.skip_connection.bias if has_skip_conv else None)
         gnb2 = eng._gnb(t["h2"], gn2, t["mean2"], t["rstd2"], 9 * cout, act=True, mask=t.get("mask2"),
                         drop_p=t["drop_p"])
@@ -664,13 +714,13 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
             if not fused_cs:
                 ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)
         ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
-        eng._wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
+        wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
         cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
         gnb1 = eng._gnb(x, gn1, t["mean1"], t["rstd1"], 9 * cout, x2=x2, act=True)
         d_h1 = eng._conv(d_h2, eng.w_dgrad(conv1), cin_tot, 3, 1, gnb=gnb1)
         if has_skip_conv:
             sc = rb.skip_connection
-            ops.conv2d_wgrad(x, dout_, G.g(sc.weight), 1, 1, x2=x2)
+            wgrad(x, dout_, G.g(sc.weight), 1, 1, x2=x2, conv3d=False)
             add_a = ops.conv2d(dout_, eng.w_dgrad(sc), cin_tot, 1, 1)
             full = True
         else:
@@ -686,7 +736,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         ab, t = ctx.mod, ctx.t
         C_ = ab.channels
         gn_ = ab.norm
-        ops.conv2d_wgrad(t["a"], dout_, G.g(ab.proj_out.weight), 1, 1)
+        wgrad(t["a"], dout_, G.g(ab.proj_out.weight), 1, 1, conv3d=False)
         bias_grad(dout_, ab.proj_out.bias)
         d_a = ops.conv2d(dout_, eng.w_dgrad(ab.proj_out), C_, 1, 1)
         rows = t.get("rows")                              # sequence-parallel shard: this rank's query rows
@@ -695,7 +745,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
         if rows is not None:
             eng.seq_parallel.all_reduce_sum(dqkv)         # dQ rows from their owner, dK / dV summed over the shards
         dqkv = eng._unfold(dqkv, t["qkv"])
-        ops.conv2d_wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1)
+        wgrad(t["hn"], dqkv, G.g(ab.qkv.weight), 1, 1, conv3d=False)
         bias_grad(dqkv, ab.qkv.bias)
         gnb = eng._gnb(t["x"], gn_, t["mean"], t["rstd"], 3 * C_, act=False)
         d_hn = ops.conv2d(dqkv, eng.w_dgrad(ab.qkv), C_, 1, 1, gnb=gnb)
@@ -708,14 +758,14 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
 
     def down_bwd(ctx, dout_, extra):
         layer, x = ctx.mod, ctx.t["x"]
-        eng._wgrad(x, dout_, G.g(layer.op.weight), 3, 2)
+        wgrad(x, dout_, G.g(layer.op.weight), 3, 2)
         bias_grad(dout_, layer.op.bias)
         z = ops.zero_insert2x(dout_)
         return eng._conv(z, eng.w_dgrad(layer.op), layer.channels, 3, 1, residual=extra)
 
     def up_bwd(ctx, dout_):
         layer, u = ctx.mod, ctx.t["u"]
-        eng._wgrad(u, dout_, G.g(layer.conv.weight), 3, 1)
+        wgrad(u, dout_, G.g(layer.conv.weight), 3, 1)
         bias_grad(dout_, layer.conv.bias)
         du = eng._conv(dout_, eng.w_dgrad(layer.conv), layer.channels, 3, 1)
         return ops.upsample2x_bwd(du)
@@ -753,7 +803,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
     # ---- input convolution
     conv_in = m.input_blocks[0][0]
     x0 = tape["x0"]
-    eng._wgrad(x0, dh, G.g(conv_in.weight), 3, 1)
+    wgrad(x0, dh, G.g(conv_in.weight), 3, 1)
     bias_grad(dh, conv_in.bias)
     d_feat = None
     if eng.is_audio:
@@ -785,7 +835,29 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None):
                                 relu_out=True)
         ops.scale_f32_(d_feat, inv_scale)
     done()
-    return G, d_feat
+    eng._wg_total = seen[0]
+    if not defer_on:
+        return G, d_feat, None
+    main = torch.cuda.current_stream(dev)
+    side = eng.side_stream(dev)
+    if deferred:
+        side.wait_stream(main)
+        with torch.cuda.stream(side):
+            for call, x, dy, gbuf, k, stride, x2 in deferred:
+                call(x, dy, gbuf, k, stride, x2=x2)
+
+    def finish():
+        # runs when autograd has enqueued everything downstream of the torso (the encoder's backward) on `main`
+        with torch.cuda.stream(main):
+            if deferred:
+                main.wait_stream(side)
+                for _, _, _, gbuf, _, _, _ in deferred:       # these slices were unscaled (as zeros) before they were filled
+                    ops.scale_f32_(gbuf.view(-1), inv_scale)
+                deferred.clear()                              # the tensors may be reused by work ordered after the join
+            if on_stage_done is not None:
+                for st in range(eng.n_stages):
+                    on_stage_done(G, st)
+    return G, d_feat, finish
 
 
 class _DenoiserFn(torch.autograd.Function):
@@ -795,6 +867,9 @@ class _DenoiserFn(torch.autograd.Function):
         out, tape = eng.forward(xt, cond, audio_feat, timesteps, train=True)
         ctx.model, ctx.tape = model, tape
         ctx.has_audio = audio_feat is not None
+        # where the gradient flows on to (the audio encoder): lets a data-parallel reducer read off the autograd graph
+        # which parameters this backward will reach
+        ctx.feat_grad_fn = audio_feat.grad_fn if (audio_feat is not None and audio_feat.requires_grad) else None
         return out
 
     @staticmethod
@@ -803,14 +878,37 @@ class _DenoiserFn(torch.autograd.Function):
         if tape is None:
             raise RuntimeError("denoiser backward called on a graph built without gradients")
         eng = model.engine()
+        begin = getattr(model, "_grad_begin_hook", None)
+        if begin is not None:
+            begin([ctx.feat_grad_fn])
         hook = getattr(model, "_grad_stage_hook", None)
-        G, d_feat = _engine_backward(eng, tape, dout, hook)
+        params = eng.torso_params()
+        # weight gradients may be deferred past the end of this function only if something follows it (the encoder's
+        # backward) and nobody reads the gradients before the end-of-backward callback: no accumulation into existing
+        # .grad tensors, and the gradients are assigned there rather than returned through autograd
+        defer = (ctx.feat_grad_fn is not None and all(p.grad is None for p in params)
+                 and not torch.is_grad_enabled())
+        G, d_feat, finish = _engine_backward(eng, tape, dout, hook, defer=defer)
         ctx.tape = None
         fin = getattr(model, "_grad_final_hook", None)
-        if fin is not None:
-            fin(G)
-        grads = tuple(G.unpacked(p) if p.requires_grad else None for p in eng.torso_params())
-        return (None, None, None, d_feat if ctx.has_audio else None, None) + grads
+        if finish is None:
+            if fin is not None:
+                fin(G)
+            grads = tuple(G.unpacked(p) if p.requires_grad else None for p in params)
+            return (None, None, None, d_feat if ctx.has_audio else None, None) + grads
+        end = getattr(model, "_grad_backward_end_hook", None)
+
+        def at_end():
+            if end is not None:
+                end()                 # data-parallel: the encoder's buckets first (fixed collective order on every rank)
+            finish()
+            if fin is not None:
+                fin(G)
+            for p in params:
+                if p.requires_grad:
+                    p.grad = G.unpacked(p)
+        torch.autograd.Variable._execution_engine.queue_callback(at_end)
+        return (None, None, None, d_feat if ctx.has_audio else None, None) + (None,) * len(params)
 
 
 def denoiser_apply(model, xt, cond, audio_feat, timesteps):

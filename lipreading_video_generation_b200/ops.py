@@ -232,7 +232,7 @@ def _gn_workspace(dev, N, Ct):
     return ws
 
 
-def _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed):
+def _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed, overflow=None):
     N = x1.shape[0]
     HW = x1.shape[1] * x1.shape[2]
     a = L.GnArgs()
@@ -243,6 +243,7 @@ def _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed):
         a.x2, a.ld2, a.C2 = None, 0, 0
     a.N, a.HW = N, HW
     a.gamma, a.beta, a.eps, a.act, a.drop_p, a.seed = gamma.data_ptr(), beta.data_ptr(), eps, int(act), drop_p, seed
+    a.overflow = L.ptr(overflow)
     return a
 
 
@@ -265,14 +266,14 @@ def groupnorm_fwd(x1, gamma, beta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed
 
 
 def groupnorm_bwd(x1, gamma, beta, dy, mean, rstd, dgamma, dbeta, x2=None, act=True, eps=1e-5, drop_p=0.0, seed=0,
-                  add_a=None, add_b=None, add_a_full=False, colsum_out=None):
+                  add_a=None, add_b=None, add_a_full=False, colsum_out=None, overflow=None):
     """Returns (dx1, dx2); dgamma/dbeta accumulated; add_a/add_b (fp16, any channel pitch) are added to dx1;
     colsum_out (fp32 (N, >= C1) view, accumulated): per-sample pixel sums of dx1."""
     N, H, W, C1 = x1.shape
     if any(t is not None and t.dtype != F16 for t in (x1, x2, dy, add_a, add_b)):
         raise RuntimeError("groupnorm_bwd: x / dy / add_a / add_b must be fp16")
     Ct = C1 + (x2.shape[3] if x2 is not None else 0)
-    a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed)
+    a = _gn_args(x1, x2, gamma, beta, eps, act, drop_p, seed, overflow)
     dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=F16)
     dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=F16) if x2 is not None else None
     ws = _gn_workspace(x1.device, N, Ct)
@@ -323,7 +324,7 @@ def groupnorm_bwd_apply(x1, gamma, beta, dyh, mean, rstd, ab, dgamma, dbeta, x2=
     N, H, W, C1 = x1.shape
     if any(t is not None and t.dtype != F16 for t in (x1, x2, dyh, add_a, add_b)):
         raise RuntimeError("groupnorm_bwd_apply: x / dyh / add_a / add_b must be fp16")
-    a = _gn_args(x1, x2, gamma, beta, eps, True, 0.0, 0)
+    a = _gn_args(x1, x2, gamma, beta, eps, True, 0.0, 0, overflow)
     dx1 = torch.empty(N, H, W, C1, device=x1.device, dtype=F16)
     dx2 = torch.empty(N, H, W, x2.shape[3], device=x1.device, dtype=F16) if x2 is not None else None
     Ct = C1 + (x2.shape[3] if x2 is not None else 0)
@@ -334,7 +335,7 @@ def groupnorm_bwd_apply(x1, gamma, beta, dyh, mean, rstd, ab, dgamma, dbeta, x2=
             L.ptr(add_a), (add_a.stride(2) if add_a is not None else 0),
             L.ptr(add_b), (add_b.stride(2) if add_b is not None else 0), int(add_a_full),
             L.ptr(colsum_out), (colsum_out.stride(0) if colsum_out is not None else 0),
-            dgamma.data_ptr(), dbeta.data_ptr(), L.ptr(overflow), _s()), "b2d_groupnorm_bwd_apply")
+            dgamma.data_ptr(), dbeta.data_ptr(), _s()), "b2d_groupnorm_bwd_apply")
     return dx1, dx2
 
 
@@ -436,10 +437,15 @@ def nchw_to_pixel_major(src, cpad, scale=None):
     return dst
 
 
-def grad_scale(x, target=GRAD_SCALE_TARGET):
-    """Device-chosen power-of-two loss scale for the fp16 gradient tensors: returns fp32 [scale, 1/scale]."""
+def grad_scale(x, target=GRAD_SCALE_TARGET, state=None, reduce_max=None):
+    """Device-chosen power-of-two loss scale for the fp16 gradient tensors: returns fp32 [scale, 1/scale].
+    state: int32[4] overflow / back-off state (b2d_grad_scale_finalize); reduce_max: callable applied to the 1-element
+    max|x| tensor between the two halves -- ranks that sum 16-bit partial gradients must agree on the scale."""
     s2 = torch.empty(2, device=x.device, dtype=torch.float32)
-    L.check(L.lib().b2d_grad_scale(x.data_ptr(), x.numel(), float(target), s2.data_ptr(), _s()), "b2d_grad_scale")
+    L.check(L.lib().b2d_absmax(x.data_ptr(), x.numel(), s2.data_ptr(), _s()), "b2d_absmax")
+    if reduce_max is not None:
+        reduce_max(s2[:1])
+    L.check(L.lib().b2d_grad_scale_finalize(s2.data_ptr(), float(target), L.ptr(state), _s()), "b2d_grad_scale_finalize")
     return s2
 
 

@@ -36,7 +36,7 @@ class Adam(torch.optim.Optimizer):
     contiguous CUDA tensors."""
 
     def __init__(self, params, lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0, amsgrad=False, *,
-                 maximize=False, foreach=None, capturable=False, differentiable=False, fused=None):
+                 maximize=False, foreach=None, capturable=False, differentiable=False, fused=None, skip_on_overflow=None):
         if amsgrad or maximize or capturable or differentiable:
             raise NotImplementedError("Adam: amsgrad / maximize / capturable / differentiable are not used by "
                                       "train.py:102 and are not provided")
@@ -46,6 +46,10 @@ class Adam(torch.optim.Optimizer):
                                       maximize=False, foreach=None, capturable=False, differentiable=False,
                                       fused=None))
         self._tables = {}          # group index -> (key, device table, pinned host table)
+        # skip_on_overflow: a model whose engine counts saturated 16-bit gradients on the device (or the int32 tensor
+        # itself): the update becomes a no-op for a step whose backward overflowed -- the reference's low-precision
+        # recipe (fp16_util.py:222-233), decided on the device without a host synchronisation
+        self._overflow_src = skip_on_overflow
 
     def _table(self, gi, ptrs, device):
         key = tuple(ptrs)
@@ -58,6 +62,13 @@ class Adam(torch.optim.Optimizer):
         # the previous pinned buffer may still be the source of an in-flight copy: keep it until the next rebuild
         self._tables[gi] = (key, dev, pinned, ent[2] if ent is not None else None)
         return dev
+
+    def _overflow_ptr(self, device):
+        src = self._overflow_src
+        if src is None:
+            return None
+        t = src if isinstance(src, torch.Tensor) else getattr(src.engine(), "_overflow", None)
+        return t.data_ptr() if (t is not None and t.device == device) else None
 
     @torch.no_grad()
     def step(self, closure=None):
@@ -99,9 +110,10 @@ class Adam(torch.optim.Optimizer):
                 with torch.cuda.device(device):
                     table = self._table((gi, si), ptrs, device)
                     n_chunks = table.numel() // _CHUNK_DTYPE.itemsize
-                    L.check(lib.b2d_adam_step(table.data_ptr(), n_chunks, float(group["lr"]), float(beta1),
-                                              float(beta2), float(group["eps"]), float(group["weight_decay"]),
-                                              1.0 - beta1 ** k, 1.0 - beta2 ** k, L.stream_ptr()), "b2d_adam_step")
+                    L.check(lib.b2d_adam_step_guarded(table.data_ptr(), n_chunks, float(group["lr"]), float(beta1),
+                                                      float(beta2), float(group["eps"]), float(group["weight_decay"]),
+                                                      1.0 - beta1 ** k, 1.0 - beta2 ** k, self._overflow_ptr(device),
+                                                      L.stream_ptr()), "b2d_adam_step_guarded")
             if touched:
                 torch._foreach_add_(steps, 1)
                 torch.autograd.graph.increment_version(touched)     # packed fp16 operand copies are keyed on _version

@@ -47,9 +47,10 @@ class GradientAllReducer:
     buffer (nothing is copied back).  A parameter that received no gradient on this rank (HF LayerDrop skips whole
     encoder layers per rank and step) contributes zeros: the collective's length never depends on which layers ran,
     which is what made the round-1 `torch.cat` of the present gradients unsafe.  Buckets are issued STRICTLY in index
-    order on every rank (NCCL matches collectives by issue order): forward pre-hooks on the modules that own the
-    parameters record which parameters take part in this step, so a bucket whose layer was skipped does not wait for
-    gradients that will never come; a bucket with an expected gradient still missing when backward ends is flushed by
+    order on every rank (NCCL matches collectives by issue order).  Which parameters will receive a gradient in this
+    backward is read off the autograd graph when the torso's backward starts (the AccumulateGrad nodes reachable from
+    the audio features' grad_fn -- exact whatever the encoder's Python code does), so a bucket whose layer was skipped
+    does not wait for gradients that will never come; whatever is still pending when backward ends is flushed by
     `finish()`, which then makes the compute stream wait for the side stream; it must run before `optimizer.step()`."""
 
     def __init__(self, model, group=None, bucket_mb: float = 25.0, force: bool = False):
@@ -65,6 +66,8 @@ class GradientAllReducer:
                              if id(p) not in self._torso_ids and p.requires_grad]
         model._grad_stage_hook = self._on_stage
         model._grad_final_hook = self._on_final
+        model._grad_begin_hook = self._on_begin
+        model._grad_backward_end_hook = self._on_backward_end
         self.bytes_reduced = 0
         # ---- fixed layout of the non-torso gradients
         self._flat = None
@@ -91,10 +94,7 @@ class GradientAllReducer:
         if self.active:
             for p in self.other_params:
                 self._handles.append(p.register_post_accumulate_grad_hook(self._on_param))
-            for mod in model.modules():
-                own = [p for p in mod.parameters(recurse=False) if id(p) in self._index]
-                if own:
-                    self._handles.append(mod.register_forward_pre_hook(self._make_expect(own)))
+        self._armed = False          # the expected set of this backward is known (set by _on_begin)
 
     def detach(self):
         for h in self._handles:
@@ -102,6 +102,8 @@ class GradientAllReducer:
         self._handles = []
         self.model._grad_stage_hook = None
         self.model._grad_final_hook = None
+        self.model._grad_begin_hook = None
+        self.model._grad_backward_end_hook = None
 
     def _stream(self, device):
         if self._comm is None and device.type == "cuda":
@@ -154,20 +156,35 @@ class GradientAllReducer:
                 self._views.append(self._flat[off:off + p.numel()].view(p.shape))
                 off += (p.numel() + 3) // 4 * 4
 
-    def _make_expect(self, own):
-        def pre_hook(module, args):
-            if torch.is_grad_enabled():
-                for p in own:
-                    if id(p) not in self._expected:
-                        self._expected.add(id(p))
-                        self._remaining[self._bucket_of[id(p)]] += 1
-        return pre_hook
+    def _on_begin(self, roots):
+        """Called when the torso's backward starts with the grad_fn(s) through which gradients will flow on into the
+        rest of the model: collects the parameters whose AccumulateGrad node is reachable, i.e. exactly those that
+        will get a gradient in this backward."""
+        if not self.active or not self.other_params:
+            return
+        self._expected.clear()
+        self._remaining = [0] * len(self._obuckets)
+        seen, stack = set(), [r for r in roots if r is not None]
+        while stack:
+            node = stack.pop()
+            if node in seen:
+                continue
+            seen.add(node)
+            var = getattr(node, "variable", None)           # AccumulateGrad
+            if var is not None and id(var) in self._index and id(var) not in self._expected:
+                self._expected.add(id(var))
+                self._remaining[self._bucket_of[id(var)]] += 1
+            for nxt, _ in node.next_functions:
+                if nxt is not None:
+                    stack.append(nxt)
+        self._armed = True
 
     def _on_param(self, p):
+        if not self._armed:          # backward without the torso hook (unknown expected set): everything goes in finish()
+            return
         b = self._bucket_of[id(p)]
         if b < self._next_other:
-            raise RuntimeError("GradientAllReducer: a gradient arrived after its bucket had been all-reduced -- the "
-                               "parameter is used outside the forward() of the module that owns it")
+            raise RuntimeError("GradientAllReducer: a gradient arrived after its bucket had been all-reduced")
         if id(p) in self._expected:
             self._expected.discard(id(p))
             self._remaining[b] -= 1
@@ -192,17 +209,34 @@ class GradientAllReducer:
             p.grad = self._views[i]
         self._next_other = b + 1
 
-    def finish(self):
-        """Flush the buckets whose parameters did not all receive a gradient this step, then make the compute stream
-        wait for every in-flight all-reduce.  Call between `loss.backward()` and `optimizer.step()`."""
-        if not self.active:
-            return
-        if self.other_params:
+    def _flush_other(self):
+        if self.other_params and self.active:
             for b in range(self._next_other, len(self._obuckets)):
                 self._launch_bucket(b)
             self._remaining = [0] * len(self._obuckets)
             self._expected.clear()
             self._next_other = 0
+            self._armed = False
+
+    def _on_backward_end(self):
+        """The engine deferred its stage hooks to the end of the backward pass (deferred weight gradients): issue the
+        remaining buckets of the other parameters FIRST, so that every rank issues [other buckets in index order, torso
+        buckets in stage order] whatever the timing of its hooks was."""
+        self._flush_other()
+
+    def finish(self):
+        """Flush the buckets whose parameters did not all receive a gradient this step, then make the compute stream
+        wait for every in-flight all-reduce.  Call between `loss.backward()` and `optimizer.step()`."""
+        if not self.active:
+            return
+        self._flush_other()
+        ov = getattr(self.model.engine(), "_overflow", None) if hasattr(self.model, "engine") else None
+        if ov is not None and ov.is_cuda and self.world > 1:
+            # a step is skipped on every rank or on none: MAX of the saturation counters (one 4-byte collective)
+            comm = self._stream(ov.device)
+            comm.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(comm):
+                dist.all_reduce(ov[:1], op=dist.ReduceOp.MAX, group=self.group)
         if self._comm is not None:
             torch.cuda.current_stream().wait_stream(self._comm)
 
@@ -263,6 +297,11 @@ class SequenceParallelAttention:
         if lse.shape[0] * lse.shape[1] != 1:
             raise RuntimeError("sequence-parallel lse gather expects one sample and one head")
         self._gather(lse.view(-1), rows)
+
+    def all_reduce_max(self, t):
+        """MAX over the ranks of a small fp32 tensor (the loss-scale maximum: every rank must pick the same scale)."""
+        if self.world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
 
     def all_reduce_sum(self, t):
         dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)

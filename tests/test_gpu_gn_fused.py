@@ -180,3 +180,33 @@ def test_groupnorm_backward_overflow_counter_flags_saturated_gradients():
     ovf = torch.zeros(1, device="cuda", dtype=torch.int32)
     ops.groupnorm_bwd_apply(x, gamma, beta, dyh, mean, rstd, ab, torch.zeros(64).cuda(), torch.zeros(64).cuda(), overflow=ovf)
     assert int(ovf.item()) >= 1
+
+
+def test_loss_scale_backs_off_after_an_overflowed_step_and_adam_skips_it():
+    """The device-side form of MixedPrecisionTrainer (fp16_util.py:148-233): the saturation counter of one backward
+    (state[0]) makes the optimiser step a no-op (b2d_adam_step_guarded) and lowers the next backward's loss scale by one
+    bit (b2d_grad_scale_finalize); clean steps raise it again by 1/1024 bit each.  No host synchronisation involved."""
+    import lipreading_video_generation_b200 as P
+    from lipreading_video_generation_b200 import ops
+    x = (torch.randn(4096, generator=gen(3)) * 1e-3).cuda()
+    clean = ops.grad_scale(x).tolist()
+    state = torch.tensor([7, 0, 0, 0], dtype=torch.int32, device="cuda")
+    after = ops.grad_scale(x, state=state).tolist()
+    assert after[0] == clean[0] / 2 and after[1] == clean[1] * 2
+    assert state.tolist() == [0, 1024, 1, 7]
+    again = ops.grad_scale(x, state=state).tolist()                   # a clean step: 1023/1024 bit still rounds up to 1
+    assert again[0] == clean[0] / 2 and state.tolist() == [0, 1023, 1, 0]
+    state[1] = 2
+    assert ops.grad_scale(x, state=state).tolist()[0] == clean[0] / 2 and state.tolist()[1] == 1
+    assert ops.grad_scale(x, state=state).tolist()[0] == clean[0] and state.tolist()[1] == 0
+    # guarded Adam
+    w = torch.nn.Parameter(torch.ones(1000, device="cuda"))
+    w.grad = torch.full((1000,), 0.5, device="cuda")
+    flag = torch.zeros(4, dtype=torch.int32, device="cuda")
+    opt = P.Adam([w], lr=1e-2, skip_on_overflow=flag)
+    flag[0] = 3
+    opt.step()
+    assert torch.equal(w.detach(), torch.ones(1000, device="cuda")), "an overflowed step must leave the weights untouched"
+    flag[0] = 0
+    opt.step()
+    assert (w.detach() < 1.0).all()

@@ -193,3 +193,46 @@ def test_wav2vec2_bf16_autocast_encoder_is_inside_the_16bit_bar_of_the_fp32_stoc
     assert got.shape == ref.shape == (256, 12, 768)
     assert rel(got, ref) <= BF16_TOL, rel(got, ref)
     assert rel(got.float().mean(dim=1), ref.mean(dim=1)) <= BF16_TOL
+
+
+def test_deferred_weight_gradients_equal_the_in_order_backward():
+    """The engine enqueues the last part of the torso's weight gradients on a side stream after the torso backward, so
+    that they overlap the audio encoder's backward, and hands the gradients over in an end-of-backward callback.  The
+    result must equal the in-order backward (first step: nothing is deferred because the work total is unknown)."""
+    import lipreading_video_generation_b200 as P
+
+    class Enc(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.scale = torch.nn.Parameter(torch.ones(768))
+
+        def forward(self, a):
+            return a["feats"] * self.scale
+
+    model = _dp_model()
+    model.audio_encoder = Enc().cuda()
+    eng = model.engine()
+    g = torch.Generator().manual_seed(21)
+    N, S = 2, 32
+    xt = torch.randn(N, 3, S, S, generator=g).cuda()
+    cond = (torch.rand(N, 3, S, S, generator=g) * 2 - 1).cuda()
+    feats = (torch.randn(N, 12, 768, generator=g) * 0.5).cuda()
+    eps = torch.randn(N, 3, S, S, generator=g).cuda()
+    t = torch.randint(0, 1000, (N,), generator=g).cuda()
+    crit = P.MSELoss()
+
+    def step():
+        model.zero_grad(set_to_none=True)
+        crit(model(xt, cond, {"feats": feats}, t), eps).backward()
+        torch.cuda.synchronize()
+        return {k: p.grad.detach().float().clone() for k, p in model.named_parameters()}
+    assert eng.defer_frac > 0.0 and eng._wg_total == 0.0
+    first = step()                                  # in order
+    assert eng._wg_total > 0.0
+    second = step()                                 # deferred tail
+    eng.defer_frac = 0.0
+    third = step()                                  # in order again
+    for k in first:
+        assert rel(second[k], first[k]) <= 5e-3, k
+        assert rel(third[k], first[k]) <= 5e-3, k
+    assert set(second) == set(first) and all(v is not None for v in second.values())
