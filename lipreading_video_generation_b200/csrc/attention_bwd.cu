@@ -487,12 +487,8 @@ static int launch_attn_bwd(const void* qkv, int64_t ldqkv, const void* d_o, int6
                            AttnBwdParams p, void* stream) {
   using CA = DkvCfg<D, DH, BQ>;
   using CB = DqCfg<D, BKV>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv_kernel<D, DH, BQ>, cudaFuncAttributeMaxDynamicSharedMemorySize, CA::SMEM_TOTAL));
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq_kernel<D, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, CB::SMEM_TOTAL));
-    attr_set = true;
-  }
+  B2D_SET_SMEM_ONCE((attn_bwd_dkv_kernel<D, DH, BQ>), CA::SMEM_TOTAL);
+  B2D_SET_SMEM_ONCE((attn_bwd_dq_kernel<D, BKV>), CB::SMEM_TOTAL);
   const int C = heads * D;
   const uint64_t dims[3] = {(uint64_t)(3 * C), (uint64_t)L, (uint64_t)N};
   const uint64_t str[2] = {(uint64_t)ldqkv * 2, (uint64_t)ldqkv * 2 * (uint64_t)L};

@@ -461,12 +461,8 @@ attn_bwd_dq2_kernel(const __grid_constant__ AttnBwd2Maps maps, const AttnBwd2Par
 int attention_bwd2_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
                             int new_order, const float* lse, const float* delta, void* dqkv, int64_t lddqkv,
                             void* stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dkv2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Dkv2Smem::TOTAL));
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_dq2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Dq2Smem::TOTAL));
-    attr_set = true;
-  }
+  B2D_SET_SMEM_ONCE((attn_bwd_dkv2_kernel), Dkv2Smem::TOTAL);
+  B2D_SET_SMEM_ONCE((attn_bwd_dq2_kernel), Dq2Smem::TOTAL);
   const int ch = 64, C = heads * ch;
   AttnBwd2Params p;
   p.L = L; p.heads = heads;

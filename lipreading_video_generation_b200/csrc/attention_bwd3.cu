@@ -20,8 +20,9 @@
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
+#include <stdlib.h>
 
-// Developer timeline: compile with -DB3_TRACE and set B2D_BWD3_TRACE=<file> to dump clock64() stamps of CTA (0,0,0):
+// Developer timeline: compile with -DB3_TRACE and set B2D_BWD3_TRACE_PTR=<device address of 1024 int64> to record clock64() stamps of CTA (0,0,0):
 // [(group*32 + step)*8 + k] for the compute groups, [512 + j*6 + k] for the tcgen05 issuer (scripts/dev_bwd3_trace.py).
 #ifdef B3_TRACE
 #define B3_TR(cond, idx) do { if (cond) p.trace[(idx)] = clock64(); } while (0)
@@ -385,11 +386,7 @@ dq_finalize_kernel(const float* __restrict__ acc, __half* __restrict__ dqkv, lon
 int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int64_t lddo, int N, int L, int heads,
                             int new_order, const float* lse, const float* delta, float* dq_acc, void* dqkv,
                             int64_t lddqkv, int q_row0, int q_rows, void* stream) {
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Bwd3Smem::TOTAL));
-    attr_set = true;
-  }
+  B2D_SET_SMEM_ONCE((attn_bwd_fused_kernel), Bwd3Smem::TOTAL);
   const int ch = 64, C = heads * ch;
   AttnBwd3Params p;
   p.L = L; p.heads = heads;
@@ -421,25 +418,17 @@ int attention_bwd3_dispatch(const void* qkv, int64_t ldqkv, const void* d_o, int
   if ((rc = make_tmap_f32_linear(&m.delta, delta, 2, vdims, vstr, vbox))) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   p.trace = nullptr;
-#ifdef B3_TRACE
-  const char* trace_path = getenv("B2D_BWD3_TRACE");
-  if (trace_path) { cudaMalloc(&p.trace, 1024 * 8); cudaMemset(p.trace, 0, 1024 * 8); }
+#ifdef B3_TRACE   // developer builds: the CALLER owns the 1024 x int64 device buffer (scripts/dev_bwd3_trace.py); the
+  {               // library allocates nothing and never synchronises, also when tracing
+    const char* e = getenv("B2D_BWD3_TRACE_PTR");
+    if (e) p.trace = (long long*)strtoull(e, nullptr, 0);
+  }
 #endif
   const long long rows = (long long)N * L;
   B2D_CHECK_CUDA(cudaMemsetAsync(dq_acc, 0, (size_t)rows * heads * 64 * sizeof(float), st));
   dim3 grid((unsigned)((L + 127) / 128), (unsigned)heads, (unsigned)N);
   attn_bwd_fused_kernel<<<grid, AB3_THREADS, Bwd3Smem::TOTAL, st>>>(m, p);
   B2D_CHECK_LAUNCH();
-#ifdef B3_TRACE
-  if (trace_path) {
-    static long long host[1024];
-    cudaDeviceSynchronize();
-    cudaMemcpy(host, p.trace, sizeof(host), cudaMemcpyDeviceToHost);
-    FILE* f = fopen(trace_path, "wb");
-    if (f) { fwrite(host, 1, sizeof(host), f); fclose(f); }
-    cudaFree(p.trace);
-  }
-#endif
   const long long groups = rows * heads * 8;
   const unsigned fin_blocks = (unsigned)((groups + 255) / 256 < 148 * 16 ? (groups + 255) / 256 : 148 * 16);
   dq_finalize_kernel<<<fin_blocks, 256, 0, st>>>(dq_acc, (__half*)dqkv, lddqkv, rows, heads, p.q_off, p.head_stride, p.scale);

@@ -271,11 +271,7 @@ attn_fwd_kernel(const __grid_constant__ AttnMaps maps, const AttnFwdParams p) {
 template <int D, int BKV>
 static int launch_attn_fwd(const AttnMaps& maps, const AttnFwdParams& p, int N, void* stream) {
   using Cfg = AttnCfg<D, BKV>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel<D, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_TOTAL));
-    attr_set = true;
-  }
+  B2D_SET_SMEM_ONCE((attn_fwd_kernel<D, BKV>), Cfg::SMEM_TOTAL);
   dim3 grid((unsigned)((p.L + 127) / 128), (unsigned)p.heads, (unsigned)N);
   attn_fwd_kernel<D, BKV><<<grid, ATT_THREADS, Cfg::SMEM_TOTAL, (cudaStream_t)stream>>>(maps, p);
   B2D_CHECK_LAUNCH();

@@ -352,11 +352,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
 template <int D, int BKV>
 static int launch_attn_fwd2(const void* qkv, int64_t ldqkv, int N, int C3, const AttnFwd2Params& p, void* stream) {
   using Cfg = Fwd2Cfg<D, BKV>;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd2_kernel<D, BKV>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_TOTAL));
-    attr_set = true;
-  }
+  B2D_SET_SMEM_ONCE((attn_fwd2_kernel<D, BKV>), Cfg::SMEM_TOTAL);
   AttnFwd2Maps maps;
   const uint64_t dims[3] = {(uint64_t)C3, (uint64_t)p.L, (uint64_t)N};
   const uint64_t str[2] = {(uint64_t)ldqkv * 2, (uint64_t)ldqkv * 2 * (uint64_t)p.L};

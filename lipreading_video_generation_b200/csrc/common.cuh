@@ -6,6 +6,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <stdarg.h>
+#include <mutex>
 #include "../../include/b2d.h"
 
 namespace b2d {
@@ -34,6 +35,21 @@ int set_err(int code, const char* fmt, ...);
 #define B2D_REQUIRE(cond, code, ...)                                           \
   do {                                                                         \
     if (!(cond)) return b2d::set_err(code, __VA_ARGS__);                       \
+  } while (0)
+
+// cudaFuncSetAttribute(MaxDynamicSharedMemorySize) exactly once per (kernel, device), race-free (lazily
+// initialised immutable kernel attributes guarded by std::call_once).  Use inside an int-returning entry point.
+#define B2D_SET_SMEM_ONCE(kernel, bytes)                                                              \
+  do {                                                                                                \
+    static std::once_flag _once[16];                                                                  \
+    static cudaError_t _err[16];                                                                      \
+    int _dev = 0;                                                                                     \
+    cudaGetDevice(&_dev);                                                                             \
+    _dev &= 15;                                                                                       \
+    std::call_once(_once[_dev], [&] {                                                                 \
+      _err[_dev] = cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)); \
+    });                                                                                               \
+    B2D_CHECK_CUDA(_err[_dev]);                                                                       \
   } while (0)
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }

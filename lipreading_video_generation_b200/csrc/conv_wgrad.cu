@@ -271,11 +271,7 @@ extern "C" int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream) {
   if (nsplit > p.pixel_tiles) nsplit = p.pixel_tiles;
   if (nsplit < 1) nsplit = 1;
   const size_t smem = (size_t)WG_STAGES * 4 * BLK + (2 * WG_STAGES + 1) * 8 + 16 + 1024;
-  static bool attr_set = false;
-  if (!attr_set) {
-    B2D_CHECK_CUDA(cudaFuncSetAttribute(conv_wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    attr_set = true;
-  }
+  B2D_SET_SMEM_ONCE((conv_wgrad_kernel), (int)smem);
   dim3 grid((unsigned)items, (unsigned)nsplit);
   conv_wgrad_kernel<<<grid, WG_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
   B2D_CHECK_LAUNCH();

@@ -182,9 +182,22 @@ class UNetModel(nn.Module):
     # -- engine plumbing -------------------------------------------------
     def engine(self):
         from .engine import DenoiserEngine
-        if self._engine is None:
+        if self._engine is None or self._engine.model is not self:
             self._engine = DenoiserEngine(self)
         return self._engine
+
+    def __deepcopy__(self, memo):
+        """`copy.deepcopy(model)` (an EMA copy): the engine -- operand caches and per-module tables keyed on THIS model's
+        modules -- is not copied; the copy builds its own on first use."""
+        import copy
+        eng, self._engine = self._engine, None
+        try:
+            new = self.__class__.__new__(self.__class__)
+            memo[id(self)] = new
+            new.__dict__ = copy.deepcopy(self.__dict__, memo)
+        finally:
+            self._engine = eng
+        return new
 
     def _torso(self, xt, cond, audio_feat, timesteps):
         from .engine import denoiser_apply

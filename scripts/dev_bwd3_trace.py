@@ -1,13 +1,17 @@
 """Developer timeline of the fused attention backward (CTA (0,0,0)): build csrc/attention_bwd3.cu with -DB3_TRACE
-(B2D_EXTRA_NVCC_FLAGS=-DB3_TRACE), then  B2D_BWD3_TRACE=gpurun_out/bwd3_trace.bin python scripts/dev_bwd3_trace.py run
-on the GPU box and  python scripts/dev_bwd3_trace.py show gpurun_out/bwd3_trace.bin  anywhere."""
+(B2D_EXTRA_NVCC_FLAGS=-DB3_TRACE), then  python scripts/dev_bwd3_trace.py run gpurun_out/bwd3_trace.bin  on the GPU box
+(the script owns the device buffer and hands its address to the library through B2D_BWD3_TRACE_PTR) and
+python scripts/dev_bwd3_trace.py show gpurun_out/bwd3_trace.bin  anywhere."""
 import struct
 import sys
 
 
-def run():
+def run(path):
+    import os
     import torch
     sys.path.insert(0, ".")
+    buf = torch.zeros(1024, dtype=torch.int64, device="cuda")
+    os.environ["B2D_BWD3_TRACE_PTR"] = str(buf.data_ptr())
     from lipreading_video_generation_b200 import ops
     g = torch.Generator(device="cuda").manual_seed(0)
     N, H, C = 32, 64, 64
@@ -17,6 +21,7 @@ def run():
     for _ in range(2):
         ops.attention_bwd(qkv, out, d_o, lse, 1)
     torch.cuda.synchronize()
+    open(path, "wb").write(struct.pack("1024q", *buf.cpu().tolist()))
 
 
 def show(path):
@@ -36,4 +41,4 @@ def show(path):
 
 
 if __name__ == "__main__":
-    run() if sys.argv[1] == "run" else show(sys.argv[2])
+    run(sys.argv[2]) if sys.argv[1] == "run" else show(sys.argv[2])
