@@ -120,32 +120,44 @@ class SampleStep:
     mode "ddpm": LinearNoiseScheduler.sample_prev_timestep over t = 999..0; mode "ddim": the 50-step eta = 0
     subsequence of the same schedule through scheduler.ddim_step."""
 
-    def __init__(self, model, S, device, mode="ddpm", ddim_steps=50):
+    def __init__(self, model, S, device, mode="ddpm", ddim_steps=50, graph=None):
         import lipreading_video_generation_b200 as P
         self.model, self.device, self.mode = model.eval(), device, mode
         self.sched = P.LinearNoiseScheduler(1000, 0.00085, 0.012)
         self.seq = [int(round(v)) for v in torch.linspace(999, 0, ddim_steps).tolist()]
         self.k = 0
         self.feats = None
+        # the model forward as one CUDA graph launch (sampling.GraphedDenoiser); B2D_SAMPLE_GRAPH=0 = eager launches
+        self.use_graph = (os.environ.get("B2D_SAMPLE_GRAPH", "1") != "0") if graph is None else graph
+        self.graphed = None
 
     def prepare(self, audio):
         with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
             self.feats = self.model.encode_audio({"input_values": audio}).float()
+
+    def _eps(self, xt, cond, i):
+        if self.use_graph:
+            import lipreading_video_generation_b200 as P
+            if self.graphed is None:
+                self.graphed = P.GraphedDenoiser(self.model, cond, self.feats)
+                self._cond_feats = (cond, self.feats)
+            elif self._cond_feats[0] is not cond or self._cond_feats[1] is not self.feats:
+                self.graphed.set_conditioning(cond, self.feats)
+                self._cond_feats = (cond, self.feats)
+            return self.graphed(xt, i)
+        t = torch.full((xt.shape[0],), i, device=self.device, dtype=torch.long)
+        return self.model(xt, cond, None, t, audio_features=self.feats)
 
     @torch.no_grad()
     def __call__(self, xt, cond):
         if self.mode == "ddpm":
             i = 999 - (self.k % 999)                # never t = 0 inside a timed region: every step draws noise
             self.k += 1
-            t = torch.full((xt.shape[0],), i, device=self.device, dtype=torch.long)
-            eps = self.model(xt, cond, None, t, audio_features=self.feats)
-            return self.sched.sample_prev_timestep(xt, eps, i)
+            return self.sched.sample_prev_timestep(xt, self._eps(xt, cond, i), i)
         k = self.k % len(self.seq)
         self.k += 1
         i, prev = self.seq[k], (self.seq[k + 1] if k + 1 < len(self.seq) else -1)
-        t = torch.full((xt.shape[0],), i, device=self.device, dtype=torch.long)
-        eps = self.model(xt, cond, None, t, audio_features=self.feats)
-        return self.sched.ddim_step(xt, eps, i, prev)
+        return self.sched.ddim_step(xt, self._eps(xt, cond, i), i, prev)
 
 
 class TrainStep:
@@ -325,6 +337,9 @@ def _attention_roofline(totals, steps, ms_step, sustained, which):
                    ms_per_step=t_ms / steps)
         if dom is None or rec["ms_per_step"] > dom["ms_per_step"]:
             dom = rec
+    if dom is None:                      # no attention launch was timed (e.g. a configuration without attention)
+        return {"bound": "tensor", "achieved": None, "peak": sustained, "unit": "TFLOP/s", "frac": None, "traffic": None,
+                "kernel": None, "peak_source": f"MEASURED_PEAKS.json bf16_tflops_sustained ({which})"}
     return {"bound": "tensor", "achieved": round(dom["tflops"], 1), "peak": sustained, "unit": "TFLOP/s",
             "frac": round(dom["tflops"] / sustained, 4), "traffic": None, "kernel": dom["kernel"],
             "ms_per_launch": round(dom["ms_per_launch"], 4), "share_of_step": round(dom["ms_per_step"] / ms_step, 3),
@@ -447,6 +462,19 @@ def measure_sample(steps, warmup, S, clips, frames, world, rank, local, device):
             _barrier(world)
         ms = e0.elapsed_time(e1) / steps
         launches = (L.lib().b2d_launch_count() - l0) // steps
+        kt_steps = steps
+        if step.graphed is not None:
+            # a replay executes the recorded forward's kernels without ABI calls: count them, and time the kernel
+            # classes on two eager (un-recorded, untimed-for-the-metric) steps -- events cannot be read out of a graph
+            launches += step.graphed.launches_per_replay
+            diag = SampleStep(model, S, device, mode=mode, graph=False)
+            diag.feats, kt_steps = step.feats, 2
+            xd = xt.clone()
+            xd, _ = diag(xd, cond)
+            with ops.KernelTimer({"attention_fwd", "conv2d", "groupnorm_fwd"}) as kt:
+                for _ in range(kt_steps):
+                    xd, _ = diag(xd, cond)
+            torch.cuda.synchronize()
         # end to end: conditioning + x_T from pinned host memory, wav2vec2 encoding, K steps, x0_pred back to the host
         _barrier(world)
         f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -462,14 +490,15 @@ def measure_sample(steps, warmup, S, clips, frames, world, rank, local, device):
         _barrier(world)
         ms_e2e = f0.elapsed_time(f1) / steps
         ms, ms_e2e = _max_over_ranks([ms, ms_e2e], world, device)
-        out[mode] = dict(ms=ms, ms_e2e=ms_e2e, launches=launches, host_ms=host_ms, kt=kt, clk=clk.summary(),
+        out[mode] = dict(ms=ms, ms_e2e=ms_e2e, launches=launches, host_ms=host_ms, kt=kt, kt_steps=kt_steps,
+                         clk=clk.summary(), graph=step.graphed is not None,
                          h2d=sum(t.numel() * t.element_size() for t in (hcond, haudio, hxt)) // steps,
                          d2h=hout.numel() * 4 // steps)
     burst, sustained, hbm, which = peaks()
     d, i = out["ddpm"], out["ddim"]
     by_class = {}
     for (name, meta), (t_ms, cnt) in d["kt"].totals().items():
-        by_class[name] = by_class.get(name, 0.0) + t_ms / steps
+        by_class[name] = by_class.get(name, 0.0) + t_ms / d["kt_steps"]
     fwd_tflop = FWD_GFLOP_PER_IMAGE[S] * n_img / 1000.0
     rec = {"value": round(n_img * world / (1000 * d["ms"] / 1000.0), 4), "unit": "frames/s (1000-step DDPM)",
            "steps": steps, "warmup": warmup, "ms_per_step": round(d["ms"], 3),
@@ -480,7 +509,8 @@ def measure_sample(steps, warmup, S, clips, frames, world, rank, local, device):
                    "h2d_bytes_per_step": d["h2d"], "d2h_bytes_per_step": d["d2h"], "ms_per_step": round(d["ms_e2e"], 3),
                    "frames_per_s_50_step_ddim": round(n_img * world / (50 * i["ms_e2e"] / 1000.0), 3)},
            "gpu_launches": int(d["launches"]), "host_enqueue_ms_per_step": round(d["host_ms"], 3),
-           "roofline": _attention_roofline(d["kt"].totals(), steps, d["ms"], sustained, which),
+           "model_forward": "one CUDA graph replay per step (sampling.GraphedDenoiser)" if d["graph"] else "eager launches",
+           "roofline": _attention_roofline(d["kt"].totals(), d["kt_steps"], d["ms"], sustained, which),
            "step_tflops_algorithmic": round(fwd_tflop / (d["ms"] / 1000.0), 1),
            "step_frac_of_sustained_peak": round(fwd_tflop / (d["ms"] / 1000.0) / sustained, 4),
            "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},

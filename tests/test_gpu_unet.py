@@ -238,3 +238,48 @@ def test_unet3d_single_frame_equals_centre_taps(golden):
         pred = model(x.cuda(), g["t"].cuda())
         ref = R.unet_forward(sd, g["oracle_cfg"], x, g["t"])
     assert rel(pred, ref) <= BF16_TOL
+
+
+def test_sampling_through_a_cuda_graph_equals_eager_sampling(golden):
+    """GraphedDenoiser: the model forward recorded once and replayed per step gives the eager trajectory (same x_T, same
+    injected z) at every step; one replay = the forward's kernels without their launch calls; update() re-records after
+    a parameter change."""
+    import lipreading_video_generation_b200 as P
+    from lipreading_video_generation_b200 import _lib as L
+    g = golden("unet_tiny.pt")
+    model = build_tiny(g).eval()
+    c = g["cfg"]
+    gg = torch.Generator().manual_seed(78)
+    N, S, T = 2, c["image_size"], 5
+    xT = torch.randn(N, 3, S, S, generator=gg).cuda()
+    zs = [torch.randn(N, 3, S, S, generator=gg).cuda() for _ in range(T)]
+    cond, audio = g["cond"].cuda(), {"feats": g["feats"].cuda()}
+    sched = P.LinearNoiseScheduler(T, 0.00085, 0.012)
+    eager, graphed = [], []
+    P.sample_images(model, sched, cond, audio, T, xt=xT, noises=zs, callback=lambda i, x, x0: eager.append(x.clone()))
+    P.sample_images(model, sched, cond, audio, T, xt=xT, noises=zs, graph=True,
+                    callback=lambda i, x, x0: graphed.append(x.clone()))
+    assert len(eager) == len(graphed) == T
+    for k in range(T):
+        # the GroupNorm pair statistics are summed by fp64 atomics: run-to-run differences are rounding noise
+        assert rel(graphed[k], eager[k]) <= 1e-3, (k, rel(graphed[k], eager[k]))
+    # a replay launches nothing through the ABI; the recording did
+    feats = model.encode_audio(audio)
+    gd = P.GraphedDenoiser(model, cond, feats)
+    assert gd.launches_per_replay > 20
+    t = torch.full((N,), 3, device="cuda", dtype=torch.long)
+    l0 = L.lib().b2d_launch_count()
+    e_graph = gd(xT, 3).clone()
+    assert L.lib().b2d_launch_count() == l0
+    with torch.no_grad():
+        e_eager = model(xT, cond, audio, t, audio_features=feats)
+    assert rel(e_graph, e_eager) <= 5e-3
+    # parameters change -> update() -> the replay follows the new weights
+    with torch.no_grad():
+        for p in model.out[2].parameters():
+            p.mul_(1.5)
+    gd.update()
+    with torch.no_grad():
+        e_eager2 = model(xT, cond, audio, t, audio_features=feats)
+    assert rel(e_eager2, e_eager) > 0.1
+    assert rel(gd(xT, 3), e_eager2) <= 5e-3
