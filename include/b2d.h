@@ -211,6 +211,16 @@ size_t b2d_groupnorm_workspace_bytes(int N, int Ctot);
 /* y: fp16 (N,HW,C1+C2) contiguous; mean, rstd: fp32 [N][32] (saved for the backward). */
 int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, float* rstd, void* workspace,
                       size_t workspace_bytes, void* stream);
+/* b2d_groupnorm_fwd without a caller workspace and without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (under CUDA graph capture, tight serving
+ * loops).  Same arguments, results and errors as b2d_groupnorm_fwd; the N * 64 doubles of scratch live in a
+ * file-scope `static __device__` array of B2D_GN_STATIC_MAX_N * 512 bytes (512 KiB per GPU that loads the library,
+ * held until exit), whose device address is taken with cudaGetSymbolAddress once per device.  N > B2D_GN_STATIC_MAX_N
+ * returns B2D_ERR_WORKSPACE.  Calls no cudaMalloc / cudaFree / allocating routine.  Every call shares the one array
+ * (cleared on `stream` before use): calls that overlap on the GPU -- different streams without an ordering between
+ * them -- race on it. */
+#define B2D_GN_STATIC_MAX_N 1024
+int b2d_groupnorm_fwd_static(const b2d_gn_args* a, void* y, float* mean, float* rstd, void* stream);
 /* dy: fp16 (N,HW,C1+C2) gradient w.r.t. y.  dx1 (N,HW,lddx1) / dx2 (N,HW,lddx2) receive the input
  * gradients; add_a / add_b (optional, fp16, channel pitch lda / ldb) are ADDED to dx1 so that the
  * residual / skip gradient accumulation is fused; with add_a_full != 0, add_a spans all C1+C2

@@ -97,6 +97,7 @@ SIGNATURES = {
                                   c_int, c_int, c_int, c_void_p, c_int64, c_void_p, c_void_p]),
     "b2d_groupnorm_workspace_bytes": (c_size_t, [c_int, c_int]),
     "b2d_groupnorm_fwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
+    "b2d_groupnorm_fwd_static": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p]),
     "b2d_groupnorm_bwd": (c_int, [C.POINTER(GnArgs), c_void_p, c_void_p, c_void_p, c_void_p, c_int64, c_void_p,
                                   c_int64, c_void_p, c_int64, c_void_p, c_int64, c_int, c_void_p, c_int64, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),

@@ -1032,6 +1032,40 @@ extern "C" int b2d_groupnorm_fwd(const b2d_gn_args* a, void* y, float* mean, flo
   return B2D_OK;
 }
 
+// ---- allocation-free variant (no counterpart in the reference) -------
+// The two-kernel GroupNorm forward needs N * 64 doubles of zeroed scratch (per-(sample, group) sum / sum of squares).
+// This variant keeps that scratch in a file-scope device array instead of a caller buffer, so a caller that may not
+// allocate (under CUDA graph capture, in a serving loop) can run it.  Every GPU that loads the library holds the
+// B2D_GN_STATIC_MAX_N * 512 bytes until exit.  All calls share the array: it is cleared on the stream before use, and
+// two calls that overlap on the GPU (different streams, no ordering) race on it.
+static __device__ __align__(256) unsigned char g_gn_static_scratch[(size_t)B2D_GN_STATIC_MAX_N * 64 * sizeof(double)];
+
+// The array's name in host code is a host-side stand-in, not a device address: the address a kernel can use comes from
+// cudaGetSymbolAddress, taken once per device with that device current.
+static int gn_static_scratch_ptr(void** out) {
+  static std::once_flag once[16];
+  static cudaError_t err[16];
+  static void* ptr[16];
+  int dev = 0;
+  B2D_CHECK_CUDA(cudaGetDevice(&dev));
+  B2D_REQUIRE(dev >= 0 && dev < 16, B2D_ERR_SHAPE, "groupnorm_fwd_static: device index %d not in [0, 16)", dev);
+  std::call_once(once[dev], [&] { err[dev] = cudaGetSymbolAddress(&ptr[dev], g_gn_static_scratch); });
+  B2D_CHECK_CUDA(err[dev]);
+  *out = ptr[dev];
+  return B2D_OK;
+}
+
+extern "C" int b2d_groupnorm_fwd_static(const b2d_gn_args* a, void* y, float* mean, float* rstd, void* stream) {
+  B2D_REQUIRE(a, B2D_ERR_SHAPE, "groupnorm_fwd_static: null arguments");
+  B2D_REQUIRE(a->N >= 1 && a->N <= B2D_GN_STATIC_MAX_N, B2D_ERR_WORKSPACE,
+              "groupnorm_fwd_static: N = %d samples exceeds the built-in scratch (B2D_GN_STATIC_MAX_N = %d); use "
+              "b2d_groupnorm_fwd with a caller workspace", a->N, B2D_GN_STATIC_MAX_N);
+  void* ws = nullptr;
+  int rc = gn_static_scratch_ptr(&ws);
+  if (rc) return rc;
+  return b2d_groupnorm_fwd(a, y, mean, rstd, ws, sizeof(g_gn_static_scratch), stream);
+}
+
 extern "C" int b2d_groupnorm_bwd(const b2d_gn_args* a, const void* dy, const float* mean, const float* rstd,
                                  void* dx1, int64_t lddx1, void* dx2, int64_t lddx2, const void* add_a, int64_t lda,
                                  const void* add_b, int64_t ldb, int add_a_full, float* dx1_colsum, int64_t ld_colsum,
