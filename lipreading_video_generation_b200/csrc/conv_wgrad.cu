@@ -195,6 +195,193 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
   if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// 3x3 stride-1 weight gradient from HALOED X tiles.
+//
+// The kernel above loads a shifted X box per tap: nine taps = nine copies of nearly the same pixels, and at 42 B/clk/SM
+// of L2 -> shared-memory bandwidth (all SMs streaming) that traffic, not the tensor pipe, bounds it (32 MAC/B with a
+// 128 x 128 tile, 21 MAC/B when Cout = 64).  Here a pixel tile's X is loaded ONCE with its halo, (rows + 2) x (Wo + 2)
+// pixels of 64 channels, and every tap is a shifted VIEW of that tile: an MN-major SWIZZLE_128B operand may start at any
+// 128-byte row, because the swizzle is a function of the absolute shared-memory address (scripts/micro/umma_shift.cu:
+// start addresses shifted by 0..16 rows and M = 128 operands made of two overlapping views are exact).  A K = 16
+// slice is 16 consecutive pixels of one image row, so its rows are contiguous in the haloed tile too.
+//
+//   MODE 1 (Cout == 64): CTA = one 64-channel block of X, all nine taps.  A (M = 128) = TWO taps' views of X -- the
+//     descriptor's LBO is the byte distance between the two views -- B (N = 64) = the dy block; five MMAs per slice,
+//     accumulator rows = (tap parity, ci), columns = co, 5 x 64 TMEM columns.  49 KB per 128 pixels for 4.7 M MACs
+//     (94 MAC/B, was 21).
+//   MODE 0 (Cout % 128 == 0): CTA = (kernel row, 128 output channels, 64 or 128 input channels): A (M = 128) = the two dy
+//     blocks, B = the view of tap (ky, kx) of an X tile with a COLUMN halo only (its rows are already those of ky),
+//     three MMAs per slice into three accumulators.  66 KB per 128 pixels for 6.3 M MACs (96 MAC/B, was 32).
+// (Nine taps of a 128 x 64 tile would need 576 TMEM columns, hence the kernel-row split in MODE 0.)
+struct HaloMaps {
+  CUtensorMap x, x2, dy;
+};
+
+struct HaloParams {
+  int C1, Ctot, Cout;
+  int R, tiles_per_img, pixel_tiles;
+  int pitch;             // Wo + 2: pixels per row of the haloed tile
+  int spr_shift;         // log2(Wo / 16): K = 16 slices per image row
+  int co_tiles, ci_tiles, nb;
+  uint32_t xblk_bytes;   // one haloed 64-channel X block in shared memory, rounded up to 1024 B
+  uint32_t stage_bytes, tx_bytes;
+  int stages;
+  float* dw;
+};
+
+constexpr int WGH_MAX_STAGES = 4;
+
+template <int MODE>
+__global__ void __launch_bounds__(WG_THREADS)
+conv_wgrad_halo_kernel(const __grid_constant__ HaloMaps maps, const HaloParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  uint64_t* full_bar = (uint64_t*)(smem + (size_t)p.stages * p.stage_bytes);
+  uint64_t* empty_bar = full_bar + WGH_MAX_STAGES;
+  uint64_t* acc_bar = empty_bar + WGH_MAX_STAGES;
+  uint32_t* tmem_slot = (uint32_t*)(acc_bar + 1);
+
+  int ky = 0, co0 = 0, ci0 = 0;
+  if (MODE == 0) {
+    int w = blockIdx.x;
+    ci0 = (w % p.ci_tiles) * p.nb * 64; w /= p.ci_tiles;
+    co0 = (w % p.co_tiles) * 128;
+    ky = w / p.co_tiles;
+  } else {
+    ci0 = (int)blockIdx.x * 64;
+  }
+  const int BN = MODE == 0 ? p.nb * 64 : 64;
+  const int split = blockIdx.y, nsplit = gridDim.y;
+  const int my_iters = (p.pixel_tiles - split + nsplit - 1) / nsplit;
+  // shared-memory offsets inside a stage
+  const uint32_t dy_off = MODE == 0 ? 0u : p.xblk_bytes;
+  const uint32_t x_off = MODE == 0 ? 2u * BLK : 0u;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
+    mbar_init(acc_bar, 1);
+    fence_barrier_init();
+  }
+  const uint32_t tmem_cols = (MODE == 0 && BN == 64) ? 256 : 512;
+  if (warp == 1) tmem_alloc(tmem_slot, tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      for (int it = 0; it < my_iters; ++it) {
+        const int tile = split + it * nsplit;
+        const int img = tile / p.tiles_per_img;
+        const int h0 = (tile - img * p.tiles_per_img) * p.R;
+        const int s = it % p.stages;
+        const uint32_t par = (uint32_t)((it / p.stages) & 1);
+        mbar_wait(&empty_bar[s], par ^ 1u);
+        uint8_t* base = smem + (size_t)s * p.stage_bytes;
+        mbar_expect_tx(&full_bar[s], p.tx_bytes);
+        if (MODE == 0) {
+          tma_load_4d(base, &maps.dy, &full_bar[s], co0, 0, h0, img);
+          tma_load_4d(base + BLK, &maps.dy, &full_bar[s], co0 + 64, 0, h0, img);
+          for (int j = 0; j < p.nb; ++j) {
+            const int c = ci0 + j * 64;
+            uint8_t* dst = base + x_off + (size_t)j * p.xblk_bytes;
+            if (c < p.C1) tma_load_4d(dst, &maps.x, &full_bar[s], c, -1, h0 + ky - 1, img);
+            else          tma_load_4d(dst, &maps.x2, &full_bar[s], c - p.C1, -1, h0 + ky - 1, img);
+          }
+        } else {
+          if (ci0 < p.C1) tma_load_4d(base, &maps.x, &full_bar[s], ci0, -1, h0 - 1, img);
+          else            tma_load_4d(base, &maps.x2, &full_bar[s], ci0 - p.C1, -1, h0 - 1, img);
+          tma_load_4d(base + dy_off, &maps.dy, &full_bar[s], 0, 0, h0, img);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    const uint32_t idesc = make_idesc(128, BN, 1, 1, FMT_F16, FMT_F16);  // both operands MN-major
+    const int spr_mask = (1 << p.spr_shift) - 1;
+    for (int it = 0; it < my_iters; ++it) {
+      const int s = it % p.stages;
+      const uint32_t par = (uint32_t)((it / p.stages) & 1);
+      mbar_wait(&full_bar[s], par);
+      tc_fence_after();
+      if (elect_one()) {
+        const uint32_t base = smem_u32(smem + (size_t)s * p.stage_bytes);
+        const uint32_t dy_addr = base + dy_off, x_addr = base + x_off;
+#pragma unroll 1
+        for (int j = 0; j < 8; ++j) {
+          const int r = j >> p.spr_shift, c0 = (j & spr_mask) << 4;
+          const uint32_t acc = (uint32_t)((it | j) != 0);
+          if (MODE == 0) {
+            const uint64_t a = make_sdesc_sw128(dy_addr + j * 2048, BLK, 1024);
+            const uint32_t xv = x_addr + (uint32_t)(r * p.pitch + c0) * 128u;
+#pragma unroll
+            for (int kx = 0; kx < 3; ++kx)
+              mma_f16_ss(tmem_base + (uint32_t)(kx * BN), a, make_sdesc_sw128(xv + kx * 128, p.xblk_bytes, 1024), idesc, acc);
+          } else {
+            const uint64_t b = make_sdesc_sw128(dy_addr + j * 2048, BLK, 1024);
+            const uint32_t xv = x_addr + (uint32_t)(r * p.pitch + c0) * 128u;
+            const uint32_t row = (uint32_t)p.pitch * 128u;
+            // views of taps t = 3 * ky + kx at xv + ky * row + kx * 128; pairs (0,1) (2,3) (4,5) (6,7) (8,8)
+            mma_f16_ss(tmem_base + 0,   make_sdesc_sw128(xv, 128, 1024), b, idesc, acc);
+            mma_f16_ss(tmem_base + 64,  make_sdesc_sw128(xv + 256, row - 256, 1024), b, idesc, acc);
+            mma_f16_ss(tmem_base + 128, make_sdesc_sw128(xv + row + 128, 128, 1024), b, idesc, acc);
+            mma_f16_ss(tmem_base + 192, make_sdesc_sw128(xv + 2 * row, 128, 1024), b, idesc, acc);
+            mma_f16_ss(tmem_base + 256, make_sdesc_sw128(xv + 2 * row + 256, 0, 1024), b, idesc, acc);
+          }
+        }
+        mma_commit(&empty_bar[s]);
+        if (it == my_iters - 1) mma_commit(acc_bar);
+      }
+      __syncwarp();
+    }
+  } else {
+    const int q = warp & 3;
+    const int row = q * 32 + lane;
+    if (my_iters > 0) {
+      mbar_wait(acc_bar, 0);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+      const long long Ktot = 9LL * p.Ctot;
+      if (MODE == 0) {
+        float* dst_row = p.dw + (long long)(co0 + row) * Ktot + (long long)(ky * 3) * p.Ctot + ci0;
+        for (int kx = 0; kx < 3; ++kx)
+          for (int c0 = 0; c0 < BN; c0 += 16) {
+            uint32_t r[16];
+            __syncwarp();
+            tmem_ld16(taddr + (uint32_t)(kx * BN + c0), r);
+            tmem_ld_wait();
+            float* dst = dst_row + (long long)kx * p.Ctot + c0;
+#pragma unroll
+            for (int j = 0; j < 16; ++j) atomicAdd(dst + j, __uint_as_float(r[j]));
+          }
+      } else {
+        // rows = (tap parity, ci): lanes hold consecutive ci -> each atomic instruction covers 128 contiguous bytes
+        for (int pr = 0; pr < 5; ++pr) {
+          const int tap = 2 * pr + (row >> 6);
+          const bool valid = tap < 9;
+          float* dst = p.dw + (long long)tap * p.Ctot + ci0 + (row & 63);
+          for (int c0 = 0; c0 < 64; c0 += 16) {
+            uint32_t r[16];
+            __syncwarp();
+            tmem_ld16(taddr + (uint32_t)(pr * 64 + c0), r);
+            tmem_ld_wait();
+            if (valid) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) atomicAdd(dst + (long long)(c0 + j) * Ktot, __uint_as_float(r[j]));
+            }
+          }
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) tmem_dealloc(tmem_base, tmem_cols);
+}
+
 static bool is_pow2w(int v) { return v > 0 && (v & (v - 1)) == 0; }
 
 static int make_map4(CUtensorMap* m, const void* base, int C, long long ld, int N, int H, int W, int phase_stride,
@@ -204,6 +391,70 @@ static int make_map4(CUtensorMap* m, const void* base, int C, long long ld, int 
                            (uint64_t)ld * 2 * W * H};
   const uint32_t box[4] = {64u, (uint32_t)Wo, (uint32_t)rows, (uint32_t)imgs};
   return make_tmap_16b(m, base, 4, dims, str, box);
+}
+
+static int make_map4_box(CUtensorMap* m, const void* base, int C, long long ld, int N, int H, int W, int box_w, int box_h) {
+  const uint64_t dims[4] = {(uint64_t)C, (uint64_t)W, (uint64_t)H, (uint64_t)N};
+  const uint64_t str[3] = {(uint64_t)ld * 2, (uint64_t)ld * 2 * W, (uint64_t)ld * 2 * W * H};
+  const uint32_t box[4] = {64u, (uint32_t)box_w, (uint32_t)box_h, 1u};
+  return make_tmap_16b(m, base, 4, dims, str, box);
+}
+
+// 3x3 stride-1, planes of >= 128 pixels, rows of >= 16: the haloed-tile kernels
+static int wgrad_halo(const b2d_wgrad_args* a, int C2, int Ho, int Wo, int R, void* stream) {
+  const int mode = a->Cout == 64 ? 1 : 0;
+  const int Rh = mode ? R + 2 : R;
+  HaloMaps maps;
+  memset(&maps, 0, sizeof(maps));
+  int rc = make_map4_box(&maps.x, a->x, a->C1, a->ldx, a->N, a->H, a->W, Wo + 2, Rh);
+  if (rc) return rc;
+  if (C2) { rc = make_map4_box(&maps.x2, a->x2, C2, a->ldx2, a->N, a->H, a->W, Wo + 2, Rh); if (rc) return rc; }
+  else maps.x2 = maps.x;
+  rc = make_map4_box(&maps.dy, a->dy, a->Cout, a->lddy, a->N, Ho, Wo, Wo, R);
+  if (rc) return rc;
+  HaloParams p;
+  memset(&p, 0, sizeof(p));
+  p.C1 = a->C1; p.Ctot = a->C1 + C2; p.Cout = a->Cout;
+  p.R = R; p.tiles_per_img = Ho / R; p.pixel_tiles = a->N * p.tiles_per_img;
+  p.pitch = Wo + 2;
+  p.spr_shift = 0;
+  while ((16 << p.spr_shift) < Wo) ++p.spr_shift;
+  const uint32_t xbox = (uint32_t)Rh * (uint32_t)(Wo + 2) * 128u;
+  p.xblk_bytes = (xbox + 1023u) & ~1023u;
+  int items;
+  if (mode == 0) {
+    p.nb = (a->C1 % 128 == 0 && C2 % 128 == 0) ? 2 : 1;     // a 128-wide ci tile must not straddle the two sources
+    p.co_tiles = a->Cout / 128;
+    p.ci_tiles = p.Ctot / (64 * p.nb);
+    p.stage_bytes = 2u * BLK + (uint32_t)p.nb * p.xblk_bytes;
+    p.tx_bytes = 2u * BLK + (uint32_t)p.nb * xbox;
+    items = 3 * p.co_tiles * p.ci_tiles;
+  } else {
+    p.nb = 1; p.co_tiles = 1; p.ci_tiles = p.Ctot / 64;
+    p.stage_bytes = p.xblk_bytes + (uint32_t)BLK;
+    p.tx_bytes = xbox + (uint32_t)BLK;
+    items = p.ci_tiles;
+  }
+  const size_t smem_max = 227 * 1024;
+  const size_t fixed = (2 * WGH_MAX_STAGES + 1) * 8 + 16 + 1024;
+  p.stages = (int)((smem_max - fixed) / p.stage_bytes);
+  if (p.stages > WGH_MAX_STAGES) p.stages = WGH_MAX_STAGES;
+  B2D_REQUIRE(p.stages >= 2, B2D_ERR_SHAPE, "wgrad: a %d-byte stage does not fit twice in shared memory", (int)p.stage_bytes);
+  p.dw = a->dw;
+  int nsplit = num_sms() / items;           // one CTA per SM (shared memory, TMEM): one wave
+  if (nsplit > p.pixel_tiles) nsplit = p.pixel_tiles;
+  if (nsplit < 1) nsplit = 1;
+  const size_t smem = (size_t)p.stages * p.stage_bytes + fixed;
+  dim3 grid((unsigned)items, (unsigned)nsplit);
+  if (mode == 0) {
+    B2D_SET_SMEM_ONCE((conv_wgrad_halo_kernel<0>), (int)smem_max);
+    conv_wgrad_halo_kernel<0><<<grid, WG_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
+  } else {
+    B2D_SET_SMEM_ONCE((conv_wgrad_halo_kernel<1>), (int)smem_max);
+    conv_wgrad_halo_kernel<1><<<grid, WG_THREADS, smem, (cudaStream_t)stream>>>(maps, p);
+  }
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
 }
 
 }  // namespace b2d
@@ -229,6 +480,9 @@ extern "C" int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream) {
   } else {
     B2D_REQUIRE(Ho % rows == 0, B2D_ERR_SHAPE, "wgrad: height %d not a multiple of %d", Ho, rows);
   }
+  static const bool halo_on = [] { const char* e = getenv("B2D_WGRAD_HALO"); return !(e && e[0] == '0'); }();
+  if (halo_on && a->ksize == 3 && a->stride == 1 && imgs == 1 && Wo >= 16 && (a->Cout == 64 || a->Cout % 128 == 0))
+    return wgrad_halo(a, C2, Ho, Wo, rows, stream);
   WgradMaps maps;
   memset(&maps, 0, sizeof(maps));
   int rc;

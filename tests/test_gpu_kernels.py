@@ -209,6 +209,37 @@ def test_conv2d_dgrad_and_wgrad_vs_autograd(N, H, C1, C2, Cout, k, stride):
     assert rel(dx.permute(0, 3, 1, 2), xr.grad) <= TOL16_KERNEL
 
 
+@pytest.mark.parametrize("N,H,C1,C2,Cout", [
+    # MODE 1 (Cout == 64: pairs of tap views form the M = 128 operand), rows of 16 / 32 / 64 / 128 pixels
+    (3, 16, 64, 0, 64), (2, 32, 128, 64, 64), (3, 64, 64, 0, 64), (1, 128, 64, 64, 64), (2, 64, 256, 0, 64),
+    # MODE 0 (kernel-row work items, column halo): 64- and 128-wide ci tiles, two co tiles, both sources
+    (3, 16, 64, 0, 128), (2, 32, 128, 128, 256), (2, 64, 128, 0, 128), (1, 128, 64, 0, 128), (2, 32, 192, 64, 128),
+    (5, 16, 256, 128, 256)])
+def test_conv2d_wgrad_3x3_from_haloed_tiles_every_tap_vs_autograd(N, H, C1, C2, Cout):
+    """3x3 stride-1 weight gradients come from ONE haloed X tile per pixel tile, each tap a shifted view of it
+    (conv_wgrad_halo_kernel): every tap separately against autograd -- a wrong view offset or a missing zero halo at
+    an image border shows up in one tap only; odd image counts give ragged split-K shares."""
+    from lipreading_video_generation_b200 import ops
+    g = gen(N * H + Cout + C1)
+    Ct = C1 + C2
+    x = torch.randn(N, H, H, Ct, generator=g).half()
+    dy = torch.randn(N, H, H, Cout, generator=g).half()
+    xr = x.float().permute(0, 3, 1, 2)
+    wr = torch.zeros(Cout, Ct, 3, 3, requires_grad=True)
+    F.conv2d(xr, wr, None, 1, 1).backward(dy.float().permute(0, 3, 1, 2))
+    x1 = x[..., :C1].contiguous().cuda()
+    x2 = x[..., C1:].contiguous().cuda() if C2 else None
+    dw = torch.zeros(Cout, 9 * Ct, device="cuda")
+    ops.conv2d_wgrad(x1, dy.cuda(), dw, 3, 1, x2=x2)
+    got = dw.view(Cout, 9, Ct).cpu()
+    want = wr.grad.permute(0, 2, 3, 1).reshape(Cout, 9, Ct)
+    for tap in range(9):
+        assert rel(got[:, tap], want[:, tap]) <= TOL16_KERNEL, (tap, rel(got[:, tap], want[:, tap]))
+    # accumulates into dw (the engine's flat gradient buffer is not cleared between micro-batches)
+    ops.conv2d_wgrad(x1, dy.cuda(), dw, 3, 1, x2=x2)
+    assert rel(dw.view(Cout, 9, Ct).cpu(), 2 * want) <= TOL16_KERNEL
+
+
 @pytest.mark.parametrize("N,HW,C1,C2,act", [(2, 1024, 64, 0, True), (3, 256, 256, 128, True), (2, 64, 256, 256, False),
                                             (1, 4096, 128, 64, True)])
 def test_groupnorm_forward_backward(N, HW, C1, C2, act):
