@@ -184,7 +184,9 @@ conv_wgrad_kernel(const __grid_constant__ WgradMaps maps, const WgradParams p) {
           if (valid) {
             float* dst = p.dw + (long long)co * Ktot + (long long)tap * p.Ctot + ci0 + c0;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) atomicAdd(dst + j, __uint_as_float(r[j]));
+            for (int j = 0; j < 16; j += 4)
+              red_add_f32x4(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                            __uint_as_float(r[j + 3]));
           }
         }
       }
@@ -355,7 +357,9 @@ conv_wgrad_halo_kernel(const __grid_constant__ HaloMaps maps, const HaloParams p
             tmem_ld_wait();
             float* dst = dst_row + (long long)kx * p.Ctot + c0;
 #pragma unroll
-            for (int j = 0; j < 16; ++j) atomicAdd(dst + j, __uint_as_float(r[j]));
+            for (int j = 0; j < 16; j += 4)
+              red_add_f32x4(dst + j, __uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
+                            __uint_as_float(r[j + 3]));
           }
       } else {
         // rows = (tap parity, ci): lanes hold consecutive ci -> each atomic instruction covers 128 contiguous bytes
@@ -463,6 +467,7 @@ using namespace b2d;
 
 extern "C" int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream) {
   B2D_REQUIRE(a && a->x && a->dy && a->dw, B2D_ERR_SHAPE, "wgrad: null argument");
+  B2D_REQUIRE(aligned16(a->dw), B2D_ERR_ALIGN, "wgrad: dw must be 16-byte aligned (vector accumulation)");
   B2D_REQUIRE(a->ksize == 1 || a->ksize == 3, B2D_ERR_SHAPE, "wgrad: ksize %d", a->ksize);
   B2D_REQUIRE(a->stride == 1 || (a->stride == 2 && a->ksize == 3), B2D_ERR_SHAPE, "wgrad: stride %d", a->stride);
   const int C2 = a->x2 ? a->C2 : 0;
