@@ -8,6 +8,8 @@ exchange per step; sampling needs no exchange at all (replicas only).
 """
 from __future__ import annotations
 
+import os
+
 import torch
 import torch.distributed as dist
 
@@ -53,8 +55,15 @@ class GradientAllReducer:
     does not wait for gradients that will never come; whatever is still pending when backward ends is flushed by
     `finish()`, which then makes the compute stream wait for the side stream; it must run before `optimizer.step()`."""
 
-    def __init__(self, model, group=None, bucket_mb: float = 25.0, force: bool = False):
+    def __init__(self, model, group=None, bucket_mb: float = 25.0, force: bool = False, overlap=None):
         self.model, self.group = model, group
+        # overlap=False (B2D_DP_OVERLAP=0): no collective is issued while backward runs; finish() all-reduces the two
+        # flat buffers with one call each.  NCCL's CTAs hold SMs while a collective is in flight, and a one-wave
+        # persistent kernel launched meanwhile runs its displaced CTAs as a second wave (measured in
+        # profiles/r2_parity_and_dp.md), so "overlapped" is not automatically the faster schedule.
+        if overlap is None:
+            overlap = os.environ.get("B2D_DP_OVERLAP", "1") != "0"
+        self.overlap = bool(overlap)
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         self.active = self.world > 1 or force          # force: run the whole path on one rank (tests)
         self.bucket_elems = int(bucket_mb * (1 << 20) / 4)
@@ -95,6 +104,7 @@ class GradientAllReducer:
             for p in self.other_params:
                 self._handles.append(p.register_post_accumulate_grad_hook(self._on_param))
         self._armed = False          # the expected set of this backward is known (set by _on_begin)
+        self._flushed = False        # this backward's remaining buckets have been issued (by the end-of-backward hook)
 
     def detach(self):
         for h in self._handles:
@@ -135,7 +145,7 @@ class GradientAllReducer:
         if not self.active:
             return
         if self._buckets is None:
-            self._buckets = plan_buckets(G.stage_end, self.bucket_elems)
+            self._buckets = plan_buckets(G.stage_end, self.bucket_elems if self.overlap else 1 << 62)
         if stage == 0:
             self._next = 0
         while self._next < len(self._buckets) and self._buckets[self._next][0] <= stage:
@@ -164,6 +174,7 @@ class GradientAllReducer:
             return
         self._expected.clear()
         self._remaining = [0] * len(self._obuckets)
+        self._flushed = False
         seen, stack = set(), [r for r in roots if r is not None]
         while stack:
             node = stack.pop()
@@ -180,7 +191,8 @@ class GradientAllReducer:
         self._armed = True
 
     def _on_param(self, p):
-        if not self._armed:          # backward without the torso hook (unknown expected set): everything goes in finish()
+        self._flushed = False
+        if not self._armed or not self.overlap:   # no torso hook (unknown expected set) / no overlap: all in finish()
             return
         b = self._bucket_of[id(p)]
         if b < self._next_other:
@@ -209,14 +221,33 @@ class GradientAllReducer:
             p.grad = self._views[i]
         self._next_other = b + 1
 
+    def _launch_all(self):
+        """Every non-torso gradient in ONE collective (no-overlap mode)."""
+        ps = self.other_params
+        self._ensure_flat(ps[0].device)
+        have = [(v, p.grad) for v, p in zip(self._views, ps) if p.grad is not None and p.grad.data_ptr() != v.data_ptr()]
+        for v, p in zip(self._views, ps):
+            if p.grad is None:
+                v.zero_()
+        if have:
+            with torch.no_grad():
+                torch._foreach_copy_([v for v, _ in have], [g for _, g in have])
+        self._reduce_async(self._flat[:self._other_total])
+        for v, p in zip(self._views, ps):
+            p.grad = v
+
     def _flush_other(self):
         if self.other_params and self.active:
-            for b in range(self._next_other, len(self._obuckets)):
-                self._launch_bucket(b)
+            if not self.overlap and self._next_other == 0:
+                self._launch_all()
+            else:
+                for b in range(self._next_other, len(self._obuckets)):
+                    self._launch_bucket(b)
             self._remaining = [0] * len(self._obuckets)
             self._expected.clear()
             self._next_other = 0
             self._armed = False
+            self._flushed = True
 
     def _on_backward_end(self):
         """The engine deferred its stage hooks to the end of the backward pass (deferred weight gradients): issue the
@@ -229,7 +260,8 @@ class GradientAllReducer:
         wait for every in-flight all-reduce.  Call between `loss.backward()` and `optimizer.step()`."""
         if not self.active:
             return
-        self._flush_other()
+        if not self._flushed:        # the end-of-backward hook already issued them when the engine deferred its stages
+            self._flush_other()
         ov = getattr(self.model.engine(), "_overflow", None) if hasattr(self.model, "engine") else None
         if ov is not None and ov.is_cuda and self.world > 1:
             # a step is skipped on every rank or on none: MAX of the saturation counters (one 4-byte collective)

@@ -103,6 +103,32 @@ def _worker(rank, world, port, q):
         red.finish()
         assert torch.allclose(m.audio_encoder.w.grad, torch.full((7,), sum(range(1, world + 1)) / world))
         assert float(m.audio_encoder.dropped.grad.abs().sum()) == 0.0
+        # the engine's end-of-backward hook issues the remaining buckets; finish() must not issue them a second time
+        # (the 378 MB of encoder gradients were all-reduced twice per step before this was checked)
+        (m.audio_encoder.w * float(rank + 1)).sum().backward()
+        b0 = red.bytes_reduced
+        m._grad_backward_end_hook()
+        red.finish()
+        assert red.bytes_reduced - b0 == 4 * (8 + 8)
+        # no-overlap mode: nothing is reduced while the stages finish; one collective per flat buffer at the end
+        red.detach()
+        red2 = GradientAllReducer(m, bucket_mb=0.5, overlap=False)
+        G.flat.copy_(base * (rank + 1))
+        for stage in range(eng.n_stages - 1):
+            m._grad_stage_hook(G, stage)
+            assert torch.equal(G.flat, base * (rank + 1)), "reduced before the last stage in no-overlap mode"
+        m._grad_stage_hook(G, eng.n_stages - 1)
+        m._grad_final_hook(G)
+        assert len(red2._buckets) == 1
+        assert torch.allclose(G.flat, base * (sum(range(1, world + 1)) / world))
+        m.audio_encoder.w.grad = None
+        m.audio_encoder.dropped.grad = None
+        (m.audio_encoder.w * float(rank + 1)).sum().backward()
+        assert red2.bytes_reduced == 4 * n, "a gradient hook issued a collective in no-overlap mode"
+        red2.finish()
+        assert red2.bytes_reduced == 4 * (n + 8 + 8)
+        assert torch.allclose(m.audio_encoder.w.grad, torch.full((7,), sum(range(1, world + 1)) / world))
+        assert float(m.audio_encoder.dropped.grad.abs().sum()) == 0.0
         dist.destroy_process_group()
         q.put((rank, "ok"))
     except Exception as e:  # noqa: BLE001
