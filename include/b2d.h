@@ -344,6 +344,17 @@ int b2d_short_attention_bwd(const void* q, const void* k, const void* v, int64_t
 int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, int HW, float* out, int64_t ldout, void* stream);
 /* out[c] += sum_r in[r*ld + c] */
 int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream);
+/* The same for n_descs jobs with one row count R in ONE launch (the ~80 bias gradients of a backward pass:
+ * out[c] += sum_r in[r][c] each).  descs_dev: device table; job d owns CTAs [block_begin[d], block_begin[d+1]) with
+ * ceil(C / 32) CTAs, block_begin ascending from 0, total_blocks = their sum.  Outputs are accumulated atomically, so two
+ * jobs may share an output. */
+typedef struct B2dReduceDesc {
+  const float* in;
+  float* out;
+  int64_t ld;
+  int32_t C, block_begin;
+} B2dReduceDesc;
+int b2d_reduce_rows_multi(const B2dReduceDesc* descs_dev, int n_descs, int R, int total_blocks, void* stream);
 /* timestep_embedding (utils.py:140-158): out[n] = [cos(t*f) | sin(t*f)], f = host-built table [dim/2]. */
 int b2d_timestep_embedding(const int64_t* t, int N, int dim, const float* freqs, float* out, void* stream);
 

@@ -40,10 +40,18 @@ struct AssembleParams {
 // values) is hoisted out of the pixel loop.  Cc <= 4 (the reference's conditioning image has 3 channels).
 __global__ void __launch_bounds__(256)
 assemble_input_kernel(AssembleParams p, __half* __restrict__ out) {
+  // Two roles (blockIdx.z): the vectors that hold x_t / cond_conv_in channels (9 of 32 at the train.py configuration)
+  // need loads and ~50 FMAs per pixel, the others (audio values, zero padding) are a pure store stream.  With one
+  // pixel per warp both paths ran one after the other in every warp, the store lanes idling behind the load
+  // latency of the others (0.51 ms for 537 MB); split by role every warp is uniform.
   const int V = p.Cpad >> 3;
-  const int v = threadIdx.x % V;
-  const int prow = threadIdx.x / V;
-  const int rows = blockDim.x / V;
+  const int vg = min(V, (p.Cin + p.Cim + 7) >> 3);
+  const int nv = blockIdx.z == 0 ? vg : V - vg;
+  if (nv == 0) return;
+  const int rows = blockDim.x / nv;
+  if ((int)threadIdx.x >= rows * nv) return;
+  const int v = (blockIdx.z == 0 ? 0 : vg) + threadIdx.x % nv;
+  const int prow = threadIdx.x / nv;
   const int n = blockIdx.y;
   const int HW = p.S * p.S;
   int kind[8];            // 0 zero, 1 x_t channel, 2 cond_conv_in output, 3 audio
@@ -386,6 +394,39 @@ reduce_rows_kernel(const float* __restrict__ in, int R, int C, long long ld, flo
   }
 }
 
+// The same for a table of (in, out, ld, C) jobs sharing one row count: the backward of a step makes ~80 bias gradients
+// of this kind, each a 2-6 CTA launch of ~6 us on an otherwise idle GPU.  CTA b serves the job d with
+// block_begin[d] <= b < block_begin[d + 1].
+__global__ void __launch_bounds__(256)
+reduce_rows_multi_kernel(const B2dReduceDesc* __restrict__ descs, int n_descs, int R) {
+  __shared__ float sh[8][33];
+  int lo = 0, hi = n_descs - 1;
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) >> 1;
+    if (descs[mid].block_begin <= (int)blockIdx.x) lo = mid; else hi = mid - 1;
+  }
+  const B2dReduceDesc d = descs[lo];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = ((int)blockIdx.x - d.block_begin) * 32 + tx;
+  float a = 0.f;
+  if (c < d.C) {
+    for (int r0 = ty; r0 < R; r0 += 32) {
+      float t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) t[u] = (r0 + 8 * u < R) ? __ldg(d.in + (long long)(r0 + 8 * u) * d.ld + c) : 0.f;
+      a += (t[0] + t[1]) + (t[2] + t[3]);
+    }
+  }
+  sh[ty][tx] = a;
+  __syncthreads();
+  if (ty == 0 && c < d.C) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sh[i][tx];
+    atomicAdd(d.out + c, t);        // two jobs of one table may share an output (a bias and its tied copy)
+  }
+}
+
 // ------------------------------------------------------------------ timestep embedding (utils.py:140-158)
 // freqs[k] = exp(-ln(max_period) * k / half) is built on the host with the reference's own torch ops
 // (bit-exact table); the kernel does the gather, the int->float cast, the product and cos | sin.
@@ -473,12 +514,11 @@ extern "C" int b2d_assemble_input(const float* xt, const float* cond, const floa
               "assemble_input: channels %d+%d+%d do not fit Cpad=%d", Cin, Cim, A, Cpad);
   AssembleParams p{xt, cond, wcond, audio, N, S, Cin, Cc, Hc, Wc, Cim, A, Cpad};
   B2D_REQUIRE(Cc <= 4 && Cpad / 8 <= 256 && N <= 65535, B2D_ERR_SHAPE, "assemble_input: Cc=%d (max 4), Cpad=%d, N=%d", Cc, Cpad, N);
-  const int V = Cpad / 8, rows = 256 / V;
-  long long chunks = ((long long)S * S + rows - 1) / rows;
-  const long long cap = ((long long)num_sms() * 8 + N - 1) / N;
+  long long chunks = ((long long)S * S + 7) / 8;
+  const long long cap = ((long long)num_sms() * 32) / (2LL * N);      // ~4 waves of 8 CTAs per SM over both roles
   if (chunks > cap) chunks = cap;
   if (chunks < 1) chunks = 1;
-  assemble_input_kernel<<<dim3((unsigned)chunks, (unsigned)N), V * rows, 0, (cudaStream_t)stream>>>(p, (__half*)out);
+  assemble_input_kernel<<<dim3((unsigned)chunks, (unsigned)N, 2u), 256, 0, (cudaStream_t)stream>>>(p, (__half*)out);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
@@ -565,7 +605,7 @@ extern "C" int b2d_colsum(const void* x, int64_t ld, int c_off, int C, int N, in
   const int V = C / 8;
   const int rows = 256 / V > 0 ? 256 / V : 1;
   long long chunks = ((long long)HW + rows - 1) / rows;
-  long long cap = ((long long)num_sms() * 8 + N - 1) / N;
+  long long cap = ((long long)num_sms() * 8) / N;   // rounded DOWN: 8 CTAs per SM are resident, a few more are a second wave
   if (chunks > cap) chunks = cap;
   if (chunks < 1) chunks = 1;
   dim3 grid((unsigned)chunks, (unsigned)N);
@@ -596,6 +636,14 @@ extern "C" int b2d_pack_conv_weights_multi(const B2dPackDesc* descs_dev, int n_d
 extern "C" int b2d_reduce_rows(const float* in, int R, int C, int64_t ld, float* out, void* stream) {
   B2D_REQUIRE(in && out && R > 0 && C > 0, B2D_ERR_SHAPE, "reduce_rows: bad arguments");
   reduce_rows_kernel<<<(C + 31) / 32, 256, 0, (cudaStream_t)stream>>>(in, R, C, ld, out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+extern "C" int b2d_reduce_rows_multi(const B2dReduceDesc* descs_dev, int n_descs, int R, int total_blocks, void* stream) {
+  if (n_descs == 0 || total_blocks == 0) return B2D_OK;
+  B2D_REQUIRE(descs_dev && n_descs > 0 && total_blocks > 0 && R > 0, B2D_ERR_SHAPE, "reduce_rows_multi: bad arguments");
+  B2D_REQUIRE((reinterpret_cast<uintptr_t>(descs_dev) & 7) == 0, B2D_ERR_ALIGN, "reduce_rows_multi: table must be 8-byte aligned");
+  reduce_rows_multi_kernel<<<total_blocks, 256, 0, (cudaStream_t)stream>>>(descs_dev, n_descs, R);
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }

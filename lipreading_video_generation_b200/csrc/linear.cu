@@ -17,6 +17,8 @@ struct GemmF32 {
   float* c; long long ldc;
   const float* bias; int relu_out; const float* dsilu_aux; int accumulate;
   int M, N, K;
+  int ksplit;   // > 1: gridDim.z CTAs share K, partial sums are added to c with atomics (c holds zeros or the value to
+                // accumulate onto); only for epilogues that are linear in the sum (no bias, no ReLU)
 };
 
 __device__ __forceinline__ float silu_grad(float z) {
@@ -32,7 +34,13 @@ gemm_f32_kernel(GemmF32 g) {
   const int tx = threadIdx.x & 15, ty = threadIdx.x >> 4;  // 16 x 16 threads, 2x2 outputs each
   const int m0 = blockIdx.y * 32, n0 = blockIdx.x * 32;
   float acc[2][2] = {{0.f, 0.f}, {0.f, 0.f}};
-  for (int k0 = 0; k0 < g.K; k0 += 32) {
+  int k_lo = 0, k_hi = g.K;
+  if (g.ksplit > 1) {
+    const int per = ((g.K + g.ksplit - 1) / g.ksplit + 31) & ~31;
+    k_lo = blockIdx.z * per;
+    k_hi = min(g.K, k_lo + per);
+  }
+  for (int k0 = k_lo; k0 < k_hi; k0 += 32) {
     // consecutive threads walk whichever index of the operand is contiguous in memory (the transposed operands of
     // the forward (w[n][k]) and of the weight gradient (dy[m][n] as A(n, m)) were read with a stride of a full row)
     const bool a_k_fast = g.sak == 1, b_n_fast = (g.sbn == 1) || !g.b;
@@ -42,7 +50,7 @@ gemm_f32_kernel(GemmF32 g) {
         const int mi = a_k_fast ? r : cidx, ki = a_k_fast ? cidx : r;
         const int m = m0 + mi, k = k0 + ki;
         float v = 0.f;
-        if (m < g.M && k < g.K) {
+        if (m < g.M && k < k_hi) {
           const long long off = (long long)m * g.sam + (long long)k * g.sak;
           v = g.a[off];
           if (g.amask) v = g.amask[off] > 0.f ? v : 0.f;
@@ -54,7 +62,7 @@ gemm_f32_kernel(GemmF32 g) {
         const int ki = b_n_fast ? r : cidx, ni = b_n_fast ? cidx : r;
         const int k = k0 + ki, n = n0 + ni;
         float v = 0.f;
-        if (k < g.K && n < g.N) {
+        if (k < k_hi && n < g.N) {
           v = g.b ? g.b[(long long)k * g.sbk + (long long)n * g.sbn] : 1.0f;
           if (g.act_b) v = silu_exact(v);
         }
@@ -82,14 +90,30 @@ gemm_f32_kernel(GemmF32 g) {
         if (g.relu_out) v = v > 0.f ? v : 0.f;
         const long long off = (long long)m * g.ldc + n;
         if (g.dsilu_aux) v *= silu_grad(g.dsilu_aux[off]);
-        g.c[off] = g.accumulate ? g.c[off] + v : v;
+        if (g.ksplit > 1) atomicAdd(&g.c[off], v);
+        else g.c[off] = g.accumulate ? g.c[off] + v : v;
       }
     }
 }
 
-static int launch_gemm(const GemmF32& g, void* stream) {
+static int launch_gemm(const GemmF32& g_in, void* stream) {
+  GemmF32 g = g_in;
   if (g.M <= 0 || g.N <= 0) return B2D_OK;
   dim3 grid((unsigned)((g.N + 31) / 32), (unsigned)((g.M + 31) / 32));
+  // a long K over a few output tiles (dx of the batched emb_layers: 256 x 256 outputs, K = 2816 -> 64 CTAs walking 88
+  // tiles each, 0.27 ms) is split over gridDim.z; needs an epilogue that is linear in the sum and a contiguous c
+  g.ksplit = 1;
+  const long long ctas = (long long)grid.x * grid.y;
+  if (!g.bias && !g.relu_out && g.K >= 512 && ctas * 2 <= num_sms() && g.ldc == g.N) {
+    int ks = (int)((2LL * num_sms() + ctas - 1) / ctas);
+    if (ks > g.K / 128) ks = g.K / 128;
+    if (ks > 1) {
+      g.ksplit = ks;
+      grid.z = (unsigned)ks;
+      if (!g.accumulate)
+        B2D_CHECK_CUDA(cudaMemsetAsync(g.c, 0, (size_t)g.M * g.N * sizeof(float), (cudaStream_t)stream));
+    }
+  }
   gemm_f32_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(g);
   B2D_CHECK_LAUNCH();
   return B2D_OK;

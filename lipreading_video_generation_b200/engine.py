@@ -654,11 +654,20 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None, defer=
         else:
             call(x, dy, gbuf, k, stride, x2=x2)
 
+    rr_jobs = []          # (per-sample column sums (N, C), bias gradient (C,)): summed over the samples in one launch
+
+    def flush_rr():
+        if rr_jobs:
+            ops.reduce_rows_multi(rr_jobs)
+            rr_jobs.clear()
+
     def done():
         nonlocal stage
         lo = G.stage_end[stage - 1] if stage > 0 else 0
         hi = G.stage_end[stage]
-        if hi > lo:
+        if not defer_on:
+            flush_rr()
+        if hi > lo and not defer_on:                      # deferred mode: ONE unscale of the whole buffer in finish()
             ops.scale_f32_(G.flat[lo:hi], inv_scale)
         if on_stage_done is not None and not defer_on:
             on_stage_done(G, stage)
@@ -673,9 +682,9 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None, defer=
         else:
             tmp = eng._bwd_arena.zeros((N, cout), torch.float32)
             ops.colsum(dy, tmp, 0, cout)
-        ops.reduce_rows(tmp, G.g(bias_param))
+        rr_jobs.append((tmp, G.g(bias_param)))            # one batched launch per stage (or per backward), see done()
         if also is not None:
-            ops.reduce_rows(tmp, G.g(also))
+            rr_jobs.append((tmp, G.g(also)))
 
     # ---- head: GroupNorm -> SiLU -> conv3x3 (Cout padded to 64 for the tensor-core tiles)
     hd = tape["head"]
@@ -713,7 +722,7 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None, defer=
                                   seed=t["seed"], colsum_out=d_emb_all[:, off:off + cout] if fused_cs else None)
             if not fused_cs:
                 ops.colsum(d_h2, d_emb_all[:, off:off + cout], 0, cout)
-        ops.reduce_rows(d_emb_all[:, off:off + cout], G.g(conv1.bias))
+        rr_jobs.append((d_emb_all[:, off:off + cout], G.g(conv1.bias)))
         wgrad(t["h1"], d_h2, G.g(conv1.weight), 3, 1)
         cin_tot = x.shape[3] + (x2.shape[3] if x2 is not None else 0)
         gnb1 = eng._gnb(x, gn1, t["mean1"], t["rstd1"], 9 * cout, x2=x2, act=True)
@@ -851,9 +860,11 @@ def _engine_backward(eng: DenoiserEngine, tape, dout, on_stage_done=None, defer=
         with torch.cuda.stream(main):
             if deferred:
                 main.wait_stream(side)
-                for _, _, _, gbuf, _, _, _ in deferred:       # these slices were unscaled (as zeros) before they were filled
-                    ops.scale_f32_(gbuf.view(-1), inv_scale)
                 deferred.clear()                              # the tensors may be reused by work ordered after the join
+            flush_rr()
+            # nothing has read the buffer yet (the stage hooks fire below, p.grad is assigned after this returns): one
+            # launch unscales all of it instead of one per stage and per deferred gradient (~85 launches of 3 us)
+            ops.scale_f32_(G.flat, inv_scale)
             if on_stage_done is not None:
                 for st in range(eng.n_stages):
                     on_stage_done(G, st)

@@ -531,6 +531,28 @@ def reduce_rows(inp, out):
     return out
 
 
+_REDUCE_DESC = np.dtype([("in", "<u8"), ("out", "<u8"), ("ld", "<i8"), ("C", "<i4"), ("block_begin", "<i4")])
+
+
+def reduce_rows_multi(jobs):
+    """out[c] += sum_r inp[r][c] for every (inp (R, C) fp32, out (C,)) in `jobs` (one R) with ONE launch."""
+    if not jobs:
+        return
+    R = jobs[0][0].shape[0]
+    tab = np.zeros(len(jobs), dtype=_REDUCE_DESC)
+    blocks = 0
+    for i, (inp, out) in enumerate(jobs):
+        if inp.shape[0] != R or inp.dtype != torch.float32 or out.dtype != torch.float32 or inp.stride(1) != 1:
+            raise RuntimeError("reduce_rows_multi: jobs must be fp32 (R, C) row-major views with one R")
+        tab[i] = (inp.data_ptr(), out.data_ptr(), inp.stride(0), inp.shape[1], blocks)
+        blocks += (inp.shape[1] + 31) // 32
+    dev = jobs[0][0].device
+    pinned = torch.from_numpy(tab.view("uint8").reshape(-1)).pin_memory()
+    table = pinned.to(dev, non_blocking=True)
+    L.check(L.lib().b2d_reduce_rows_multi(table.data_ptr(), len(jobs), R, blocks, _s()), "b2d_reduce_rows_multi")
+    table.record_stream(torch.cuda.current_stream(dev))
+
+
 def timestep_embedding(t, dim, freqs):
     N = t.shape[0]
     out = torch.empty(N, dim, device=t.device, dtype=torch.float32)

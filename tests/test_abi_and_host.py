@@ -200,7 +200,9 @@ def test_pos_conv_short_sequence_matches_stock_module(T):
     assert rel(y2, y1) <= 1e-5
     assert rel(x2.grad, x1.grad) <= 1e-5
     for (n1, p1), (_, p2) in zip(stock.named_parameters(), fast.named_parameters()):
-        assert rel(p2.grad, p1.grad) <= 1e-5, n1
+        # the weight-norm w = g v / ||v|| is evaluated with plain tensor ops (unet_audio._weight_normed) instead of
+        # torch._weight_norm: same formula, another fp32 summation order over the 64 x 4 x 128 weights
+        assert rel(p2.grad, p1.grad) <= 1e-4, n1
 
 
 def test_single_channel_conv1d_matches_stock_module():
