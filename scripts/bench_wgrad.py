@@ -12,6 +12,8 @@ SHAPES = [(64, 64, 0, 64, 7), (64, 256, 0, 64, 1), (64, 128, 64, 64, 1), (64, 64
           (32, 64, 0, 128, 1), (32, 128, 0, 128, 6), (32, 256, 128, 128, 1), (32, 128, 128, 128, 1), (32, 128, 64, 128, 1),
           (32, 256, 0, 256, 1), (16, 128, 0, 256, 1), (16, 256, 0, 256, 10), (16, 256, 256, 256, 2), (16, 256, 128, 256, 1)]
 N = int(os.environ.get("WG_N", "256"))
+if os.environ.get("WG_ONLY"):                     # comma-separated shape indices (profiling runs)
+    SHAPES = [SHAPES[int(i)] for i in os.environ["WG_ONLY"].split(",")]
 out, total = [], 0.0
 flush = torch.empty(256 << 20, device="cuda", dtype=torch.uint8)
 for H, C1, C2, Cout, cnt in SHAPES:
