@@ -10,8 +10,10 @@
 // B tiles (weights [Cout][K], K-major) use a 2-D TMA box.  Both land in 128B-swizzled smem,
 // consumed by tcgen05.mma (M=128, N=BN, K=16) with the fp32 accumulator in TMEM.
 //
-// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
-// warps 2..5 = epilogue (TMEM -> registers -> bias/emb/residual -> bf16 / fp32-NCHW global).
+// Warp roles (320 threads): warp 0 = TMA producer, warp 1 = TMEM owner + MMA issuer,
+// warps 2..9 = epilogue (TMEM -> registers -> bias/emb/residual -> bf16 / fp32-NCHW global): two warps per TMEM lane
+// quarter, one taking the even and one the odd 16-column chunks of the tile (the fused GroupNorm epilogues are ~2300
+// warp instructions per 128 x 64 tile: four warps per CTA left them latency bound, profiles/r2_groupnorm_fused.md).
 #include "common.cuh"
 #include "tmap.cuh"
 #include "umma.cuh"
@@ -71,7 +73,9 @@ struct ConvParams {
   float* gnb_ab;           // [N][Cout][2]
 };
 
-constexpr int CONV_THREADS = 192;
+constexpr int CONV_EPI_WARPS = 8;          // two per TMEM lane quarter: even / odd 16-column chunks of the tile
+constexpr int CONV_EPI_THREADS = CONV_EPI_WARPS * 32;
+constexpr int CONV_THREADS = 64 + CONV_EPI_THREADS;
 constexpr int EB_FLOATS = 512;              // images per tile x BN <= 512 (bias + emb staging)
 constexpr int SACC_FLOATS = 512;            // fused GroupNorm sums of one tile: images per tile x BN x 2 <= 512
 constexpr int A_TILE_BYTES = 128 * 128;  // 128 pixels x 64 bf16
@@ -98,7 +102,7 @@ __device__ __forceinline__ void warp_reduce_scatter32(float* v, int lane) {
 }
 
 template <int EPI>
-__global__ void __launch_bounds__(CONV_THREADS)
+__global__ void __launch_bounds__(CONV_THREADS, 2)
 conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
@@ -129,7 +133,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) { mbar_init(&full_bar[s], 1); mbar_init(&empty_bar[s], 1); }
     mbar_init(&acc_full[0], 1); mbar_init(&acc_full[1], 1);
-    mbar_init(&acc_empty[0], 128); mbar_init(&acc_empty[1], 128);
+    mbar_init(&acc_empty[0], CONV_EPI_THREADS); mbar_init(&acc_empty[1], CONV_EPI_THREADS);
     mbar_init(res_full, 1);
     fence_barrier_init();
     prefetch_tmap(&maps.a[0]);
@@ -213,14 +217,15 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       }
     }
   } else {
-    // ------------------------------------------------------------ epilogue (warps 2..5)
+    // ------------------------------------------------------------ epilogue (warps 2..9)
     // Per tile: (1) stage bias + emb for the tile's images in smem and issue ALL residual loads of this thread's
     // row into registers BEFORE waiting for the accumulator, so their HBM latency hides behind the tile's MMAs
     // (the first version loaded them 16 columns at a time after the wait: 62 % of its samples were long_sb);
     // (2) TMEM -> registers -> + (bias + emb) -> + residual -> fp16 / fp32-NCHW global.
     const int q = warp & 3;  // TMEM lane quarter this warp may access
+    const int chalf = (warp - 2) >> 2;      // this warp takes the 16-column chunks cc with (cc & 1) == chalf
     const int row = q * 32 + lane;
-    const int et = threadIdx.x - 64;        // 0..127 among the epilogue threads
+    const int et = threadIdx.x - 64;        // 0..255 among the epilogue threads
     const bool has_eb = (p.bias != nullptr) || (p.emb != nullptr);
     const int imgs_in_tile = p.HoWo >= 128 ? 1 : p.imgs;
     int lt = 0;
@@ -236,7 +241,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     const uint32_t eb_u32 = eb_base + (uint32_t)buf * (EB_FLOATS * 4u);
     if (EPI == EPI_GNB) {
       // per (image of the tile, channel): z = x * rg + bb with rg = rstd * gamma, bb = beta - mean * rg
-      for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
+      for (int idx = et; idx < imgs_in_tile * p.BN; idx += CONV_EPI_THREADS) {
         const int im = idx / p.BN, c = idx - im * p.BN;
         const int col = n0 + c, img = min(img_first + im, p.n_images - 1);
         const int g = col / p.gnb_cpg;
@@ -246,7 +251,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
         sts32f(eb_u32 + (uint32_t)idx * 8u + 4u, fmaf(-mu, rg, __ldg(p.gnb_beta + col)));
       }
     } else if (has_eb) {
-      for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
+      for (int idx = et; idx < imgs_in_tile * p.BN; idx += CONV_EPI_THREADS) {
         const int im = idx / p.BN, c = idx - im * p.BN;
         const int col = n0 + c, img = img_first + im;
         float v = 0.f;
@@ -288,9 +293,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
     if (res_vec) {
       const __half* rp = p.residual + pix * p.ldres + n0;
 #pragma unroll
-      for (int g = 0; g < 16; ++g) if (g * 8 < p.BN) rres[g] = ldg_nc_u4(rp + g * 8);
+      for (int g = 0; g < 16; ++g) if (g * 8 < p.BN && ((g >> 1) & 1) == chalf) rres[g] = ldg_nc_u4(rp + g * 8);
     }
-    named_bar_sync(1, 128);                            // eb staging visible to the four epilogue warps
+    named_bar_sync(1, CONV_EPI_THREADS);                            // eb staging visible to the four epilogue warps
     mbar_wait(&acc_full[buf], (uint32_t)((lt >> 1) & 1));
     tc_fence_after();
     const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)buf * p.tmem_cols;
@@ -307,7 +312,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
 #pragma unroll
       for (int cc = 0; cc < 8; ++cc) {
         const int c0 = cc * 16;
-        if (c0 < p.BN) {
+        if (c0 < p.BN && (cc & 1) == chalf) {
           uint32_t r[16];
           __syncwarp();
           tmem_ld16(taddr + (uint32_t)c0, r);
@@ -386,7 +391,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       tc_fence_before();
       mbar_arrive(&acc_empty[buf]);
       fence_proxy_async_smem();                        // staged tile visible to the TMA engine
-      named_bar_sync(2, 128);
+      named_bar_sync(2, CONV_EPI_THREADS);
       if (et == 0) {
         for (int b = 0; b < nblk; ++b) tma_store_4d(&maps.o, stage_out + b * A_TILE_BYTES, n0 + b * 64, 0, h0, img0);
         tma_store_commit();
@@ -394,7 +399,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       if (EPI == EPI_STATS) {
         // sacc[slot][BN] -> stats[img][(n0 + k) / 2][k & 1] (fp64), re-zeroed for the next tile (whose sums start
         // after its named barrier 1, which this thread reaches only after the stores below)
-        for (int idx = et; idx < imgs_in_tile * p.BN; idx += 128) {
+        for (int idx = et; idx < imgs_in_tile * p.BN; idx += CONV_EPI_THREADS) {
           const int im = idx / p.BN, k = idx - im * p.BN;
           const int img = img_first + im;
           const uint32_t sa = sacc_u32 + (uint32_t)idx * 4u;
@@ -405,7 +410,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
         }
       }
       if (EPI == EPI_GNB) {
-        for (int idx = et; idx < imgs_in_tile * p.BN * 2; idx += 128) {
+        for (int idx = et; idx < imgs_in_tile * p.BN * 2; idx += CONV_EPI_THREADS) {
           const int im = idx / (p.BN * 2), k = idx - im * p.BN * 2;
           const int img = img_first + im;
           const uint32_t sa = sacc_u32 + (uint32_t)idx * 4u;
@@ -420,7 +425,7 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
 #pragma unroll
     for (int cc = 0; cc < 8; ++cc) {
       const int c0 = cc * 16;
-      if (c0 < p.BN) {
+      if (c0 < p.BN && (cc & 1) == chalf) {
       uint32_t r[16];
       __syncwarp();
       tmem_ld16(taddr + (uint32_t)c0, r);

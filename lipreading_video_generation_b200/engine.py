@@ -91,12 +91,13 @@ class DenoiserEngine:
         mode = os.environ.get("B2D_GN_FUSE", "1")
         self.fuse_groupnorm = mode != "0"
         self.fuse_groupnorm_bwd = mode == "1"
-        # The fused epilogues cost 30-90 us on the convolutions that are already bound by their epilogue (1x1 and
-        # 64-channel 3x3 layers: K = taps * Cin small, the tensor pipe 2 % busy) -- more than the GroupNorm pass they
-        # save; on the K >= 1152 / 2304 layers they are nearly free (profiles/r2_groupnorm_fused.md).  Below the
-        # threshold the statistics come from one pass over the tensor (b2d_pair_stats) and the backward reduce from the
-        # two-kernel path.  B2D_GN_FUSE_MINK="stats,gnb" overrides (0,0 = fuse everywhere).
-        mk = os.environ.get("B2D_GN_FUSE_MINK", "1152,2304").split(",")
+        # The fused epilogues cost 30-90 us on the convolutions that are already bound by their epilogue or their L2
+        # traffic (1x1 and 64-channel 3x3 layers: K = taps * Cin small, the tensor pipe 2 % busy); on the K >= 1152
+        # layers they are nearly free (profiles/r2_groupnorm_fused.md).  With 8 epilogue warps per CTA the backward
+        # epilogue (which removes the reduce pass AND the second SiLU' / dropout evaluation of the two-kernel path) wins
+        # on every layer, the statistics epilogue only from K = 1152 on: below that the statistics come from one pass
+        # over the tensor (b2d_pair_stats).  B2D_GN_FUSE_MINK="stats,gnb" overrides (0,0 = fuse everywhere).
+        mk = os.environ.get("B2D_GN_FUSE_MINK", "1152,0").split(",")
         self.fuse_min_k_stats, self.fuse_min_k_gnb = int(mk[0]), int(mk[1])
         # Deferred weight gradients: the tail of the backward -- the audio encoder's backward, ~1200 library launches of
         # 3-10 us that leave most SMs idle -- runs AFTER the torso's; nothing depends on a weight gradient but the
