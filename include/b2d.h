@@ -329,6 +329,16 @@ int b2d_w2v_layer0_bwd(const float* audio, int64_t ld_audio, const float* w, con
                        const float* beta, int N, int S, int C, int K, int stride, float eps, const void* dout,
                        int dout_dtype, const float* mean, const float* rstd, float* dw, float* dbias, float* dgamma,
                        float* dbeta, void* stream);
+
+/* nn.LayerNorm over the last dimension as HF wav2vec2 calls it 26 times per forward (`Wav2Vec2EncoderLayer.layer_norm`
+ * / `.final_layer_norm`, `Wav2Vec2Encoder.layer_norm`, `Wav2Vec2FeatureProjection.layer_norm`; third-party, instantiated
+ * at unet_audio.py:14).  x: (R, C) contiguous, x_dtype 0 = fp32, 1 = bf16, 2 = fp16; C / 32 in {2, 4, 8, 16, 24, 32}.
+ *   fwd: y fp32 (R, C) = (x - mean) * rstd * gamma + beta; mean / rstd fp32 (R,) kept for the backward;
+ *   bwd: dx fp32 (R, C) written; dgamma / dbeta fp32 (C,) ACCUMULATED (+=). */
+int b2d_layernorm_fwd(const void* x, int x_dtype, const float* gamma, const float* beta, int R, int C, float eps,
+                      float* y, float* mean, float* rstd, void* stream);
+int b2d_layernorm_bwd(const void* x, int x_dtype, const float* gamma, const float* mean, const float* rstd,
+                      const float* dy, int R, int C, float* dx, float* dgamma, float* dbeta, void* stream);
 /* Self-attention over very short sequences (L <= 16 tokens, head dim D = 64): the attention function behind HF
  * transformers' `Wav2Vec2Attention` (the audio encoder of unet_audio.py:10-18 sees 12 frames per 4000-sample window).
  * q / k / v: (B, H, L, D) views with element strides (sb, sh, sl, 1); out, dout, dq, dk, dv: contiguous (B, L, H, D);

@@ -123,6 +123,9 @@ SIGNATURES = {
                                         c_void_p]),
     "b2d_colsum": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_void_p, c_int64, c_void_p]),
     "b2d_reduce_rows": (c_int, [c_void_p, c_int, c_int, c_int64, c_void_p, c_void_p]),
+    "b2d_layernorm_fwd": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p, c_void_p, c_void_p, c_void_p]),
+    "b2d_layernorm_bwd": (c_int, [c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p, c_void_p,
+                                  c_void_p, c_void_p]),
     "b2d_reduce_rows_multi": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
     "b2d_timestep_embedding": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b2d_linear_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),

@@ -270,3 +270,157 @@ extern "C" int b2d_w2v_layer0_bwd(const float* audio, int64_t ld_audio, const fl
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// LayerNorm over the last dimension for the encoder's 26 nn.LayerNorm calls per forward (HF `Wav2Vec2EncoderLayer`,
+// `Wav2Vec2Encoder`, `Wav2Vec2FeatureProjection`; third-party arithmetic, row N4): 3072 rows x 768 at the train64 batch.
+// torch serves the backward with `layer_norm_grad_input_kernel` + `GammaBetaBackwardCUDAKernelTemplate` -- 9 + 30 us per
+// call for 9 MB of traffic (profiles/r2_launch_list.md) -- because its two-stage gamma / beta reduction is built for
+// many more rows.  Here one warp owns a row (C / 32 values per lane in registers), walks several rows and keeps its
+// gamma / beta partial sums in registers across them; one shared-memory reduction per CTA, one atomic per column per CTA.
+namespace b2d {
+namespace {
+
+constexpr int LN_WARPS = 8;
+constexpr int LN_MAX_PER_LANE = 32;     // C <= 1024
+
+template <typename T> __device__ __forceinline__ float ln_ld(const T* p) { return (float)*p; }
+template <> __device__ __forceinline__ float ln_ld<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
+template <> __device__ __forceinline__ float ln_ld<__half>(const __half* p) { return __half2float(*p); }
+
+__device__ __forceinline__ float ln_warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+template <typename T, int CPL>   // CPL = C / 32
+__global__ void __launch_bounds__(LN_WARPS * 32)
+layernorm_fwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta, int R,
+                     float eps, float* __restrict__ y, float* __restrict__ mean, float* __restrict__ rstd) {
+  constexpr int C = CPL * 32;
+  const int lane = threadIdx.x & 31;
+  const int wid = blockIdx.x * LN_WARPS + (threadIdx.x >> 5), nw = gridDim.x * LN_WARPS;
+  float g[CPL], b[CPL];
+#pragma unroll
+  for (int i = 0; i < CPL; ++i) { g[i] = __ldg(gamma + lane + 32 * i); b[i] = __ldg(beta + lane + 32 * i); }
+  for (int r = wid; r < R; r += nw) {
+    float v[CPL];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) { v[i] = ln_ld(x + (long long)r * C + lane + 32 * i); s += v[i]; }
+    const float mu = ln_warp_sum(s) * (1.0f / C);
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) { const float d = v[i] - mu; q = fmaf(d, d, q); }
+    const float rs = rsqrtf(ln_warp_sum(q) * (1.0f / C) + eps);
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) y[(long long)r * C + lane + 32 * i] = fmaf((v[i] - mu) * rs, g[i], b[i]);
+    if (lane == 0) { mean[r] = mu; rstd[r] = rs; }
+  }
+}
+
+template <typename T, int CPL>
+__global__ void __launch_bounds__(LN_WARPS * 32)
+layernorm_bwd_kernel(const T* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ mean,
+                     const float* __restrict__ rstd, const float* __restrict__ dy, int R, float* __restrict__ dx,
+                     float* __restrict__ dgamma, float* __restrict__ dbeta) {
+  constexpr int C = CPL * 32;
+  __shared__ float sh[2][C];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int wid = blockIdx.x * LN_WARPS + warp, nw = gridDim.x * LN_WARPS;
+  for (int i = threadIdx.x; i < 2 * C; i += LN_WARPS * 32) (&sh[0][0])[i] = 0.f;
+  __syncthreads();
+  float g[CPL], ag[CPL], ab[CPL];
+#pragma unroll
+  for (int i = 0; i < CPL; ++i) { g[i] = __ldg(gamma + lane + 32 * i); ag[i] = 0.f; ab[i] = 0.f; }
+  for (int r = wid; r < R; r += nw) {
+    const float mu = __ldg(mean + r), rs = __ldg(rstd + r);
+    float xh[CPL], gy[CPL];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+      const long long o = (long long)r * C + lane + 32 * i;
+      const float d = __ldg(dy + o);
+      xh[i] = (ln_ld(x + o) - mu) * rs;
+      gy[i] = d * g[i];
+      s1 += gy[i];
+      s2 = fmaf(gy[i], xh[i], s2);
+      ab[i] += d;
+      ag[i] = fmaf(d, xh[i], ag[i]);
+    }
+    s1 = ln_warp_sum(s1) * (1.0f / C);
+    s2 = ln_warp_sum(s2) * (1.0f / C);
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) dx[(long long)r * C + lane + 32 * i] = rs * (gy[i] - s1 - xh[i] * s2);
+  }
+#pragma unroll
+  for (int i = 0; i < CPL; ++i) { atomicAdd(&sh[0][lane + 32 * i], ag[i]); atomicAdd(&sh[1][lane + 32 * i], ab[i]); }
+  __syncthreads();
+  for (int i = threadIdx.x; i < C; i += LN_WARPS * 32) { atomicAdd(dgamma + i, sh[0][i]); atomicAdd(dbeta + i, sh[1][i]); }
+}
+
+template <typename T>
+int launch_ln_fwd(int cpl, int blocks, cudaStream_t st, const void* x, const float* g, const float* b, int R, float eps,
+                  float* y, float* mean, float* rstd) {
+  switch (cpl) {
+#define B2D_LN_CASE(N) case N: layernorm_fwd_kernel<T, N><<<blocks, LN_WARPS * 32, 0, st>>>((const T*)x, g, b, R, eps, y, mean, rstd); break;
+    B2D_LN_CASE(2) B2D_LN_CASE(4) B2D_LN_CASE(8) B2D_LN_CASE(16) B2D_LN_CASE(24) B2D_LN_CASE(32)
+#undef B2D_LN_CASE
+    default: return 1;
+  }
+  return 0;
+}
+template <typename T>
+int launch_ln_bwd(int cpl, int blocks, cudaStream_t st, const void* x, const float* g, const float* mean, const float* rstd,
+                  const float* dy, int R, float* dx, float* dg, float* db) {
+  switch (cpl) {
+#define B2D_LN_CASE(N) case N: layernorm_bwd_kernel<T, N><<<blocks, LN_WARPS * 32, 0, st>>>((const T*)x, g, mean, rstd, dy, R, dx, dg, db); break;
+    B2D_LN_CASE(2) B2D_LN_CASE(4) B2D_LN_CASE(8) B2D_LN_CASE(16) B2D_LN_CASE(24) B2D_LN_CASE(32)
+#undef B2D_LN_CASE
+    default: return 1;
+  }
+  return 0;
+}
+
+int ln_blocks(int R) {
+  int b = (R + LN_WARPS * 4 - 1) / (LN_WARPS * 4);      // ~4 rows per warp: the gamma / beta partial sums amortise
+  const int cap = 2 * num_sms();
+  if (b > cap) b = cap;
+  return b < 1 ? 1 : b;
+}
+
+}  // namespace
+}  // namespace b2d
+
+extern "C" int b2d_layernorm_fwd(const void* x, int x_dtype, const float* gamma, const float* beta, int R, int C, float eps,
+                                 float* y, float* mean, float* rstd, void* stream) {
+  B2D_REQUIRE(x && gamma && beta && y && mean && rstd && R > 0, B2D_ERR_SHAPE, "layernorm_fwd: bad arguments");
+  B2D_REQUIRE(C % 32 == 0 && C <= 32 * b2d::LN_MAX_PER_LANE, B2D_ERR_SHAPE, "layernorm_fwd: C=%d", C);
+  const int blocks = b2d::ln_blocks(R);
+  cudaStream_t st = (cudaStream_t)stream;
+  int bad;
+  if (x_dtype == 0)      bad = b2d::launch_ln_fwd<float>(C / 32, blocks, st, x, gamma, beta, R, eps, y, mean, rstd);
+  else if (x_dtype == 1) bad = b2d::launch_ln_fwd<__nv_bfloat16>(C / 32, blocks, st, x, gamma, beta, R, eps, y, mean, rstd);
+  else if (x_dtype == 2) bad = b2d::launch_ln_fwd<__half>(C / 32, blocks, st, x, gamma, beta, R, eps, y, mean, rstd);
+  else bad = 1;
+  B2D_REQUIRE(!bad, B2D_ERR_SHAPE, "layernorm_fwd: unsupported C=%d (C / 32 in {2,4,8,16,24,32}) or dtype %d", C, x_dtype);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}
+
+extern "C" int b2d_layernorm_bwd(const void* x, int x_dtype, const float* gamma, const float* mean, const float* rstd,
+                                 const float* dy, int R, int C, float* dx, float* dgamma, float* dbeta, void* stream) {
+  B2D_REQUIRE(x && gamma && mean && rstd && dy && dx && dgamma && dbeta && R > 0, B2D_ERR_SHAPE, "layernorm_bwd: bad arguments");
+  B2D_REQUIRE(C % 32 == 0 && C <= 32 * b2d::LN_MAX_PER_LANE, B2D_ERR_SHAPE, "layernorm_bwd: C=%d", C);
+  const int blocks = b2d::ln_blocks(R);
+  cudaStream_t st = (cudaStream_t)stream;
+  int bad;
+  if (x_dtype == 0)      bad = b2d::launch_ln_bwd<float>(C / 32, blocks, st, x, gamma, mean, rstd, dy, R, dx, dgamma, dbeta);
+  else if (x_dtype == 1) bad = b2d::launch_ln_bwd<__nv_bfloat16>(C / 32, blocks, st, x, gamma, mean, rstd, dy, R, dx, dgamma, dbeta);
+  else if (x_dtype == 2) bad = b2d::launch_ln_bwd<__half>(C / 32, blocks, st, x, gamma, mean, rstd, dy, R, dx, dgamma, dbeta);
+  else bad = 1;
+  B2D_REQUIRE(!bad, B2D_ERR_SHAPE, "layernorm_bwd: unsupported C=%d (C / 32 in {2,4,8,16,24,32}) or dtype %d", C, x_dtype);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}

@@ -466,6 +466,29 @@ def colsum(x, out, c_off=0, C_=None):
 _W2V_DT = {torch.float32: 0, torch.bfloat16: 1, torch.float16: 2}
 
 
+def layernorm_fwd(x2, gamma, beta, eps):
+    """nn.LayerNorm over the last dim of x2 (R, C) fp32 / bf16 / fp16 -> (y fp32 (R, C), mean (R,), rstd (R,))."""
+    L.require_cuda(x2)
+    R, Cc = x2.shape
+    y = torch.empty(R, Cc, device=x2.device, dtype=torch.float32)
+    mean = torch.empty(R, device=x2.device, dtype=torch.float32)
+    rstd = torch.empty(R, device=x2.device, dtype=torch.float32)
+    L.check(L.lib().b2d_layernorm_fwd(x2.data_ptr(), _W2V_DT[x2.dtype], gamma.data_ptr(), beta.data_ptr(), R, Cc, eps,
+                                      y.data_ptr(), mean.data_ptr(), rstd.data_ptr(), _s()), "b2d_layernorm_fwd")
+    return y, mean, rstd
+
+
+def layernorm_bwd(x2, gamma, mean, rstd, dy):
+    """-> (dx fp32 (R, C), dgamma (C,), dbeta (C,))."""
+    R, Cc = x2.shape
+    dx = torch.empty(R, Cc, device=x2.device, dtype=torch.float32)
+    dgb = torch.zeros(2, Cc, device=x2.device, dtype=torch.float32)
+    L.check(L.lib().b2d_layernorm_bwd(x2.data_ptr(), _W2V_DT[x2.dtype], gamma.data_ptr(), mean.data_ptr(), rstd.data_ptr(),
+                                      dy.data_ptr(), R, Cc, dx.data_ptr(), dgb[0].data_ptr(), dgb[1].data_ptr(), _s()),
+            "b2d_layernorm_bwd")
+    return dx, dgb[0], dgb[1]
+
+
 def w2v_layer0_fwd(audio, w, bias, gamma, beta, stride, eps, out_dtype):
     """Fused first feature-extractor layer of wav2vec2 (conv k=10 -> per-channel GroupNorm -> erf GELU).
     audio (N,S) fp32, w (C,1,K) fp32 -> out (N,C,T) in out_dtype, mean (N,C), rstd (N,C)."""

@@ -185,6 +185,48 @@ def patch_short_attention(wav2vec2):
     return wav2vec2
 
 
+class _LayerNormFn(torch.autograd.Function):
+    """nn.LayerNorm (last dimension, affine) on csrc/wav2vec2_frontend.cu's kernels: fp32 arithmetic and fp32 output,
+    which is what the stock module gives for an fp32 input and, under autocast, for a 16-bit one."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias, eps):
+        from . import ops
+        x2 = x.reshape(-1, x.shape[-1]).contiguous()
+        y, mean, rstd = ops.layernorm_fwd(x2, weight, bias, eps)
+        ctx.save_for_backward(x2, weight, mean, rstd)
+        ctx.x_dtype = x.dtype
+        return y.view(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import ops
+        x2, weight, mean, rstd = ctx.saved_tensors
+        dx, dg, db = ops.layernorm_bwd(x2, weight, mean, rstd, dy.reshape(x2.shape).float().contiguous())
+        return dx.view(dy.shape).to(ctx.x_dtype), dg, db, None
+
+
+def _layer_norm_fused(self, x):
+    """Drop-in for `nn.LayerNorm.forward` on CUDA tensors; anything else takes the stock path."""
+    ok = (x.is_cuda and x.dim() >= 2 and len(self.normalized_shape) == 1 and self.elementwise_affine
+          and self.weight is not None and self.bias is not None and self.weight.dtype == torch.float32
+          and x.shape[-1] // 32 in (2, 4, 8, 16, 24, 32) and x.shape[-1] % 32 == 0 and x.numel() > 0
+          and (x.dtype == torch.float32 or (x.dtype in (torch.bfloat16, torch.float16) and torch.is_autocast_enabled("cuda"))))
+    if not ok:
+        return self._b2d_stock_forward(x)
+    return _LayerNormFn.apply(x, self.weight, self.bias, self.eps)
+
+
+def patch_layer_norms(wav2vec2):
+    """Route every affine nn.LayerNorm of the encoder through the fused kernels (row N4)."""
+    import types
+    for mod in wav2vec2.modules():
+        if type(mod) is nn.LayerNorm and not hasattr(mod, "_b2d_stock_forward"):
+            mod._b2d_stock_forward = mod.forward
+            mod.forward = types.MethodType(_layer_norm_fused, mod)
+    return wav2vec2
+
+
 def _mask_hidden_states_no_sync(self, hidden_states, mask_time_indices=None, attention_mask=None):
     """HF `Wav2Vec2Model._mask_hidden_states` (SpecAugment) without its four host<->device synchronisations per train
     step: the stock code uploads the numpy mask from pageable memory (`torch.tensor(mask, device=...)` -- a stream
@@ -264,6 +306,8 @@ class Wav2Vec2Encoder(nn.Module):
             patch_feature_layer0(self.wav2vec2)
             patch_short_attention(self.wav2vec2)
             patch_spec_augment(self.wav2vec2)
+            if os.environ.get("B2D_W2V_LAYERNORM", "1") != "0":
+                patch_layer_norms(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

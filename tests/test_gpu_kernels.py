@@ -501,6 +501,7 @@ def test_wav2vec2_with_short_attention_matches_stock_encoder():
     UA.patch_pos_conv(fast)
     UA.patch_feature_layer0(fast)
     UA.patch_short_attention(fast)
+    UA.patch_layer_norms(fast)
     assert fast.config._attn_implementation == UA.SHORT_ATTENTION_NAME and stock.config._attn_implementation == "sdpa"
     a = torch.randn(4, 4000, generator=gen(6)).cuda()
     n0 = UA._short_attention_calls[0]
@@ -513,6 +514,40 @@ def test_wav2vec2_with_short_attention_matches_stock_encoder():
         torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
     assert UA._short_attention_calls[0] == n0 + 3
     assert rel(yf, ys) <= 1e-4
+
+
+@pytest.mark.parametrize("shape,dtype", [((256, 12, 768), torch.float32), ((7, 3, 512), torch.float32),
+                                         ((5, 12, 768), torch.bfloat16), ((1, 1, 64), torch.float32), ((33, 1024), torch.float32)])
+def test_layernorm_kernels_match_torch_layer_norm(shape, dtype):
+    """The encoder's nn.LayerNorm calls (third-party arithmetic, row N4): y, dx, dgamma, dbeta against F.layer_norm in
+    float64 on the same (rounded) input; a 16-bit input under autocast gives an fp32 result like the stock module."""
+    import lipreading_video_generation_b200.unet_audio as UA
+    g = gen(sum(shape))
+    C_ = shape[-1]
+    x = (torch.randn(shape, generator=g) * 2 + 0.5).to(dtype)
+    w, b = 1 + 0.2 * torch.randn(C_, generator=g), 0.1 * torch.randn(C_, generator=g)
+    r = torch.randn(shape, generator=g)
+    ln = torch.nn.LayerNorm(C_).cuda()
+    with torch.no_grad():
+        ln.weight.copy_(w); ln.bias.copy_(b)
+    UA.patch_layer_norms(ln)
+    xg = x.cuda().requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.bfloat16, enabled=dtype != torch.float32):
+        y = ln(xg)
+    assert y.dtype == torch.float32
+    (y * r.cuda()).sum().backward()
+    x64 = x.double().requires_grad_(True)
+    w64, b64 = w.double().requires_grad_(True), b.double().requires_grad_(True)
+    y64 = F.layer_norm(x64, (C_,), w64, b64, ln.eps)
+    (y64 * r.double()).sum().backward()
+    assert rel(y, y64) <= 2e-6
+    assert xg.grad.dtype == dtype
+    assert rel(xg.grad, x64.grad) <= (2e-6 if dtype == torch.float32 else 5e-3)     # 16-bit: the gradient is rounded to it
+    assert rel(ln.weight.grad, w64.grad) <= 1e-5 and rel(ln.bias.grad, b64.grad) <= 1e-5
+    # an input the kernels are not built for (last dim not a multiple of 32) takes the stock path
+    ln2 = UA.patch_layer_norms(torch.nn.LayerNorm(48).cuda())
+    z = torch.randn(4, 48, device="cuda")
+    assert torch.equal(ln2(z), F.layer_norm(z, (48,), ln2.weight, ln2.bias, ln2.eps))
 
 
 # ----------------------------------------------------------------------------- Adam (row N3)
