@@ -424,3 +424,69 @@ extern "C" int b2d_layernorm_bwd(const void* x, int x_dtype, const float* gamma,
   B2D_CHECK_LAUNCH();
   return B2D_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Bias gradient of the encoder's 73 nn.Linear layers: out[c] = sum_r dy[r][c] over a 16-bit (R, C) gradient.  torch
+// serves it with `reduce_kernel<sum, bf16>` (15 us at 3072 x 768) plus a cast of the result to fp32 (4.6 us) -- twice the
+// time of the layer's dW GEMM (profiles/r2_launch_list.md).  CTA = 64 columns x a slice of rows; 8 row lanes per column
+// pair, fp32 accumulation, one atomic per column per CTA into the zeroed fp32 output.
+namespace b2d {
+namespace {
+
+template <typename T2>   // __nv_bfloat162 or __half2
+__device__ __forceinline__ float2 cs_ld2(const void* p);
+template <> __device__ __forceinline__ float2 cs_ld2<__nv_bfloat162>(const void* p) {
+  return __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(p));
+}
+template <> __device__ __forceinline__ float2 cs_ld2<__half2>(const void* p) {
+  return __half22float2(*reinterpret_cast<const __half2*>(p));
+}
+
+template <typename T2>
+__global__ void __launch_bounds__(256)
+colsum_rows16_kernel(const uint16_t* __restrict__ x, long long ld, int R, int C, int rows_per_cta, float* __restrict__ out) {
+  __shared__ float sh[8][65];
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  const int c = blockIdx.x * 64 + tx * 2;
+  const int r_lo = blockIdx.y * rows_per_cta, r_hi = min(R, r_lo + rows_per_cta);
+  float a0 = 0.f, a1 = 0.f;
+  if (c < C) {
+    for (int r = r_lo + ty; r < r_hi; r += 32) {
+      float2 v[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        v[u] = (r + 8 * u < r_hi) ? cs_ld2<T2>(x + (long long)(r + 8 * u) * ld + c) : make_float2(0.f, 0.f);
+      a0 += (v[0].x + v[1].x) + (v[2].x + v[3].x);
+      a1 += (v[0].y + v[1].y) + (v[2].y + v[3].y);
+    }
+  }
+  sh[ty][tx * 2] = a0; sh[ty][tx * 2 + 1] = a1;
+  __syncthreads();
+  if (threadIdx.x < 64 && blockIdx.x * 64 + (int)threadIdx.x < C) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sh[i][threadIdx.x];
+    atomicAdd(out + blockIdx.x * 64 + threadIdx.x, t);
+  }
+}
+
+}  // namespace
+}  // namespace b2d
+
+extern "C" int b2d_colsum_rows16(const void* x, int x_dtype, int64_t ld, int R, int C, float* out, void* stream) {
+  B2D_REQUIRE(x && out && R > 0 && C > 0 && C % 2 == 0 && ld % 2 == 0 && (reinterpret_cast<uintptr_t>(x) & 3) == 0,
+              B2D_ERR_SHAPE, "colsum_rows16: bad arguments (C=%d, ld=%lld must be even, x 4-byte aligned)", C, (long long)ld);
+  B2D_REQUIRE(x_dtype == 1 || x_dtype == 2, B2D_ERR_SHAPE, "colsum_rows16: dtype %d (1 = bf16, 2 = fp16)", x_dtype);
+  cudaStream_t st = (cudaStream_t)stream;
+  B2D_CHECK_CUDA(cudaMemsetAsync(out, 0, (size_t)C * sizeof(float), st));
+  const int gx = (C + 63) / 64;
+  int gy = (2 * b2d::num_sms() + gx - 1) / gx;
+  if (gy > (R + 31) / 32) gy = (R + 31) / 32;
+  if (gy < 1) gy = 1;
+  const int rows_per_cta = (R + gy - 1) / gy;
+  dim3 grid((unsigned)gx, (unsigned)gy);
+  if (x_dtype == 1) b2d::colsum_rows16_kernel<__nv_bfloat162><<<grid, 256, 0, st>>>((const uint16_t*)x, ld, R, C, rows_per_cta, out);
+  else              b2d::colsum_rows16_kernel<__half2><<<grid, 256, 0, st>>>((const uint16_t*)x, ld, R, C, rows_per_cta, out);
+  B2D_CHECK_LAUNCH();
+  return B2D_OK;
+}

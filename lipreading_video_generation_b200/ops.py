@@ -489,6 +489,16 @@ def layernorm_bwd(x2, gamma, mean, rstd, dy):
     return dx, dgb[0], dgb[1]
 
 
+def colsum_rows16(x2):
+    """fp32 (C,) column sums of a bf16 / fp16 (R, C) matrix (last dim contiguous)."""
+    L.require_cuda(x2)
+    R, Cc = x2.shape
+    out = torch.empty(Cc, device=x2.device, dtype=torch.float32)
+    L.check(L.lib().b2d_colsum_rows16(x2.data_ptr(), _W2V_DT[x2.dtype], x2.stride(0), R, Cc, out.data_ptr(), _s()),
+            "b2d_colsum_rows16")
+    return out
+
+
 def w2v_layer0_fwd(audio, w, bias, gamma, beta, stride, eps, out_dtype):
     """Fused first feature-extractor layer of wav2vec2 (conv k=10 -> per-channel GroupNorm -> erf GELU).
     audio (N,S) fp32, w (C,1,K) fp32 -> out (N,C,T) in out_dtype, mean (N,C), rstd (N,C)."""

@@ -227,6 +227,60 @@ def patch_layer_norms(wav2vec2):
     return wav2vec2
 
 
+class _LinearFn(torch.autograd.Function):
+    """nn.Linear as the stock module computes it (under autocast: in the autocast dtype, one library GEMM with the bias
+    in its epilogue), with the bias gradient from `b2d_colsum_rows16` in fp32 instead of torch's 16-bit `sum` + cast."""
+
+    @staticmethod
+    def forward(ctx, x, weight, bias):
+        dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+        xb, wb = x.to(dt), weight.to(dt)
+        with torch.autocast("cuda", enabled=False):
+            y = torch.nn.functional.linear(xb, wb, bias.to(dt))
+        ctx.save_for_backward(xb, wb)
+        ctx.dts = (x.dtype, weight.dtype, bias.dtype)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import ops
+        xb, wb = ctx.saved_tensors
+        dx = dw = db = None
+        dy2 = dy.reshape(-1, dy.shape[-1])
+        if dy2.dtype != xb.dtype:
+            dy2 = dy2.to(xb.dtype)
+        dy2 = dy2.contiguous()
+        with torch.autocast("cuda", enabled=False):
+            if ctx.needs_input_grad[0]:
+                dx = torch.mm(dy2, wb).view(xb.shape).to(ctx.dts[0])
+            if ctx.needs_input_grad[1]:
+                dw = torch.mm(dy2.t(), xb.reshape(-1, xb.shape[-1])).to(ctx.dts[1])
+        if ctx.needs_input_grad[2]:
+            db = ops.colsum_rows16(dy2).to(ctx.dts[2])
+        return dx, dw, db
+
+
+def _linear_fused(self, x):
+    """Drop-in for `nn.Linear.forward` in training on CUDA with a 16-bit compute dtype; anything else: stock path."""
+    dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
+    ok = (x.is_cuda and self.bias is not None and torch.is_grad_enabled() and self.weight.requires_grad
+          and dt in (torch.bfloat16, torch.float16) and x.dtype in (torch.float32, torch.bfloat16, torch.float16)
+          and self.out_features % 2 == 0 and x.numel() > 0)
+    if not ok:
+        return self._b2d_stock_forward(x)
+    return _LinearFn.apply(x, self.weight, self.bias)
+
+
+def patch_linears(wav2vec2):
+    """Route the encoder's nn.Linear layers through `_LinearFn` (bias gradient on this library's kernel; row N4)."""
+    import types
+    for mod in wav2vec2.modules():
+        if type(mod) is nn.Linear and not hasattr(mod, "_b2d_stock_forward"):
+            mod._b2d_stock_forward = mod.forward
+            mod.forward = types.MethodType(_linear_fused, mod)
+    return wav2vec2
+
+
 def _mask_hidden_states_no_sync(self, hidden_states, mask_time_indices=None, attention_mask=None):
     """HF `Wav2Vec2Model._mask_hidden_states` (SpecAugment) without its four host<->device synchronisations per train
     step: the stock code uploads the numpy mask from pageable memory (`torch.tensor(mask, device=...)` -- a stream
@@ -308,6 +362,8 @@ class Wav2Vec2Encoder(nn.Module):
             patch_spec_augment(self.wav2vec2)
             if os.environ.get("B2D_W2V_LAYERNORM", "1") != "0":
                 patch_layer_norms(self.wav2vec2)
+            if os.environ.get("B2D_W2V_LINEAR", "1") != "0":
+                patch_linears(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

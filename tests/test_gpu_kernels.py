@@ -550,6 +550,34 @@ def test_layernorm_kernels_match_torch_layer_norm(shape, dtype):
     assert torch.equal(ln2(z), F.layer_norm(z, (48,), ln2.weight, ln2.bias, ln2.eps))
 
 
+@pytest.mark.parametrize("R,Cin,Cout", [(3072, 768, 768), (3072, 768, 3072), (50, 512, 768), (7, 64, 34)])
+def test_encoder_linear_with_fp32_bias_gradient_matches_stock_autocast_linear(R, Cin, Cout):
+    """nn.Linear of the audio encoder under bf16 autocast through `_LinearFn` (row N4): same output and dx / dW as the
+    stock module (the same library GEMMs), bias gradient summed in fp32 by b2d_colsum_rows16 -- at least as close to
+    the float64 column sums as the stock 16-bit `sum`."""
+    import copy
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(R + Cout)
+    stock = torch.nn.Linear(Cin, Cout).cuda()
+    fast = UA.patch_linears(copy.deepcopy(stock))
+    x = torch.randn(R // 12 + 1, 12, Cin, device="cuda")[: max(1, R // 12)]
+    r = torch.randn(x.shape[0], 12, Cout, device="cuda")
+    x1, x2 = x.clone().requires_grad_(True), x.clone().requires_grad_(True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        y1, y2 = stock(x1), fast(x2)
+        (y1.float() * r).sum().backward()
+        (y2.float() * r).sum().backward()
+    assert y2.dtype == y1.dtype == torch.bfloat16 and torch.equal(y1, y2)
+    assert x2.grad.dtype == torch.float32 and rel(x2.grad, x1.grad) <= 1e-6
+    assert rel(fast.weight.grad, stock.weight.grad) <= 1e-6
+    want = r.to(torch.bfloat16).double().sum(dim=(0, 1))                 # dy as the layer sees it: rounded to bf16
+    e_fast, e_stock = rel(fast.bias.grad, want), rel(stock.bias.grad, want)
+    assert fast.bias.grad.dtype == torch.float32 and e_fast <= 1e-5 and e_fast <= e_stock + 1e-7, (e_fast, e_stock)
+    # fp32 (no autocast) and eval-mode calls take the stock path
+    with torch.no_grad():
+        assert torch.equal(fast(x), stock(x))
+
+
 # ----------------------------------------------------------------------------- Adam (row N3)
 @pytest.mark.parametrize("wd", [0.0, 0.01])
 def test_adam_multi_tensor_matches_torch_adam(wd):
