@@ -229,7 +229,8 @@ def patch_layer_norms(wav2vec2):
 
 class _LinearFn(torch.autograd.Function):
     """nn.Linear as the stock module computes it (under autocast: in the autocast dtype, one library GEMM with the bias
-    in its epilogue), with the bias gradient from `b2d_colsum_rows16` in fp32 instead of torch's 16-bit `sum` + cast."""
+    in its epilogue), with the bias gradient from `b2d_colsum_rows16` in fp32 instead of torch's 16-bit `sum` + cast and
+    dx / dW taken from the gradient GEMMs' fp32 accumulators instead of their 16-bit roundings + casts."""
 
     @staticmethod
     def forward(ctx, x, weight, bias):
@@ -251,10 +252,16 @@ class _LinearFn(torch.autograd.Function):
             dy2 = dy2.to(xb.dtype)
         dy2 = dy2.contiguous()
         with torch.autocast("cuda", enabled=False):
+            # fp32 consumers (the fp32 residual stream, the fp32 parameters) get the GEMM's fp32 accumulator directly:
+            # the stock path rounds it to 16 bits and casts it back with one more kernel per gradient
+            def mm(a, b, want):
+                if want == torch.float32 and a.dtype != torch.float32:
+                    return torch.mm(a, b, out_dtype=torch.float32)
+                return torch.mm(a, b).to(want)
             if ctx.needs_input_grad[0]:
-                dx = torch.mm(dy2, wb).view(xb.shape).to(ctx.dts[0])
+                dx = mm(dy2, wb, ctx.dts[0]).view(xb.shape)
             if ctx.needs_input_grad[1]:
-                dw = torch.mm(dy2.t(), xb.reshape(-1, xb.shape[-1])).to(ctx.dts[1])
+                dw = mm(dy2.t(), xb.reshape(-1, xb.shape[-1]), ctx.dts[1])
         if ctx.needs_input_grad[2]:
             db = ops.colsum_rows16(dy2).to(ctx.dts[2])
         return dx, dw, db
