@@ -332,6 +332,39 @@ def patch_spec_augment(wav2vec2):
         wav2vec2._mask_hidden_states = types.MethodType(_mask_hidden_states_no_sync, wav2vec2)
 
 
+def _feature_encoder_channels_last(self, input_values):
+    """Drop-in for `Wav2Vec2FeatureEncoder.forward` (third-party; row N4).  The stock layers 1..6 are nn.Conv1d on
+    (B, C, T) tensors: torch hands cuDNN contiguous NCW tensors, cuDNN's 16-bit kernels are NHWC, and every convolution
+    call is wrapped in `nchwToNhwc` / `nhwcToNchw` conversions -- 1.6 ms of conversions around 1.2 ms of convolution per
+    train64 step, forward + backward (profiles/r2_launch_list.md).  Here the activation is converted ONCE after layer 0
+    to a (B, C, 1, T) channels-last tensor (physically (B, T, C)) and the same library convolution is called as conv2d
+    with a 1 x k kernel: cuDNN runs its NHWC kernels on it directly, forward and backward, and the (B, C, T) view
+    returned at the end is the contiguous (B, T, C) tensor HF transposes it to."""
+    layers = list(self.conv_layers)
+    ok = (input_values.is_cuda and len(layers) > 1 and not getattr(self, "gradient_checkpointing", False)
+          and all(type(l).__name__ == "Wav2Vec2NoLayerNormConvLayer" and isinstance(l.conv, nn.Conv1d)
+                  and l.conv.padding[0] == 0 and l.conv.dilation[0] == 1 and l.conv.groups == 1
+                  and l.conv.padding_mode == "zeros" for l in layers[1:]))
+    if not ok:
+        return self._b2d_stock_forward(input_values)
+    h = layers[0](input_values[:, None])
+    h = h.unsqueeze(2).contiguous(memory_format=torch.channels_last)
+    for layer in layers[1:]:
+        conv = layer.conv
+        h = nn.functional.conv2d(h, conv.weight.unsqueeze(2), conv.bias, stride=(1, conv.stride[0]))
+        h = layer.activation(h)
+    return h.squeeze(2)
+
+
+def patch_feature_convs(wav2vec2):
+    import types
+    fe = wav2vec2.feature_extractor
+    if not hasattr(fe, "_b2d_stock_forward"):
+        fe._b2d_stock_forward = fe.forward
+        fe.forward = types.MethodType(_feature_encoder_channels_last, fe)
+    return wav2vec2
+
+
 def patch_pos_conv(wav2vec2):
     """Route the positional conv embedding of a HF Wav2Vec2Model through _pos_conv_short_sequence and the
     single-channel waveform conv through _conv1d_single_channel (same arithmetic, library GEMMs)."""
@@ -371,6 +404,8 @@ class Wav2Vec2Encoder(nn.Module):
                 patch_layer_norms(self.wav2vec2)
             if os.environ.get("B2D_W2V_LINEAR", "1") != "0":
                 patch_linears(self.wav2vec2)
+            if os.environ.get("B2D_W2V_CHANNELS_LAST", "1") != "0":
+                patch_feature_convs(self.wav2vec2)
 
     def forward(self, audio_input):
         return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state

@@ -502,6 +502,7 @@ def test_wav2vec2_with_short_attention_matches_stock_encoder():
     UA.patch_feature_layer0(fast)
     UA.patch_short_attention(fast)
     UA.patch_layer_norms(fast)
+    UA.patch_feature_convs(fast)
     assert fast.config._attn_implementation == UA.SHORT_ATTENTION_NAME and stock.config._attn_implementation == "sdpa"
     a = torch.randn(4, 4000, generator=gen(6)).cuda()
     n0 = UA._short_attention_calls[0]
@@ -581,6 +582,38 @@ def test_encoder_linear_with_fp32_bias_gradient_matches_stock_autocast_linear(R,
     # fp32 (no autocast) and eval-mode calls take the stock path
     with torch.no_grad():
         assert torch.equal(fast(x), stock(x))
+
+
+def test_wav2vec2_feature_convs_as_channels_last_conv2d_match_stock_conv1d():
+    """Feature-extractor layers 1..6 called as conv2d on a (B, C, 1, T) channels-last tensor (the same library
+    convolution without its layout conversions, row N4) against the stock Conv1d layers: features and every weight
+    gradient in fp32 (TF32 off) <= 1e-4, and the returned (B, C, T) view transposes to a contiguous (B, T, C)."""
+    import copy
+    from transformers import Wav2Vec2Config
+    from transformers.models.wav2vec2.modeling_wav2vec2 import Wav2Vec2FeatureEncoder
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(3)
+    stock = Wav2Vec2FeatureEncoder(Wav2Vec2Config(conv_dim=(64, 96, 64, 64, 64, 64, 64))).cuda()
+    fast = copy.deepcopy(stock)
+    holder = torch.nn.Module()
+    holder.feature_extractor = fast
+    UA.patch_feature_convs(holder)
+    a = torch.randn(5, 4000, generator=gen(8)).cuda()
+    old = torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32
+    torch.backends.cuda.matmul.allow_tf32 = torch.backends.cudnn.allow_tf32 = False
+    try:
+        y1, y2 = stock(a.clone()), fast(a.clone())
+        r = torch.randn(y1.shape, generator=gen(9)).cuda()
+        (y1 * r).sum().backward()
+        (y2 * r).sum().backward()
+    finally:
+        torch.backends.cuda.matmul.allow_tf32, torch.backends.cudnn.allow_tf32 = old
+    assert y1.shape == y2.shape == (5, 64, 12) and y2.transpose(1, 2).is_contiguous()
+    assert rel(y2, y1) <= 1e-4
+    for (n1, p1), (_, p2) in zip(stock.named_parameters(), fast.named_parameters()):
+        assert rel(p2.grad, p1.grad) <= 1e-4, n1
+    # CPU tensors and other layer types take the stock path
+    assert torch.equal(fast.cpu()(a.cpu()), stock.cpu()(a.cpu()))
 
 
 # ----------------------------------------------------------------------------- Adam (row N3)
