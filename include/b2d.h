@@ -342,6 +342,9 @@ int b2d_layernorm_bwd(const void* x, int x_dtype, const float* gamma, const floa
 /* Bias gradient of an nn.Linear of the same encoder: out[c] = sum_r x[r][c] for a 16-bit (R, C) gradient with row
  * stride ld (elements); x_dtype 1 = bf16, 2 = fp16; out fp32 (C,) is OVERWRITTEN (zeroed on the stream first). */
 int b2d_colsum_rows16(const void* x, int x_dtype, int64_t ld, int R, int C, float* out, void* stream);
+/* out (B, C, R) = in (B, R, C) transposed, 16-bit elements (bf16 / fp16 bit patterns), contiguous, 4-byte aligned: the
+ * layout change between the fused layer 0 ((N, C, T) rows) and the channels-last tensor of feature layers 1..6. */
+int b2d_transpose16(const void* in, void* out, int B, int R, int C, void* stream);
 /* Self-attention over very short sequences (L <= 16 tokens, head dim D = 64): the attention function behind HF
  * transformers' `Wav2Vec2Attention` (the audio encoder of unet_audio.py:10-18 sees 12 frames per 4000-sample window).
  * q / k / v: (B, H, L, D) views with element strides (sb, sh, sl, 1); out, dout, dq, dk, dv: contiguous (B, L, H, D);

@@ -499,6 +499,15 @@ def colsum_rows16(x2):
     return out
 
 
+def transpose16(x):
+    """(B, R, C) contiguous bf16 / fp16 -> (B, C, R) contiguous."""
+    L.require_cuda(x)
+    B, R, Cc = x.shape
+    out = torch.empty(B, Cc, R, device=x.device, dtype=x.dtype)
+    L.check(L.lib().b2d_transpose16(x.data_ptr(), out.data_ptr(), B, R, Cc, _s()), "b2d_transpose16")
+    return out
+
+
 def w2v_layer0_fwd(audio, w, bias, gamma, beta, stride, eps, out_dtype):
     """Fused first feature-extractor layer of wav2vec2 (conv k=10 -> per-channel GroupNorm -> erf GELU).
     audio (N,S) fp32, w (C,1,K) fp32 -> out (N,C,T) in out_dtype, mean (N,C), rstd (N,C)."""

@@ -332,6 +332,24 @@ def patch_spec_augment(wav2vec2):
         wav2vec2._mask_hidden_states = types.MethodType(_mask_hidden_states_no_sync, wav2vec2)
 
 
+class _ToChannelsLastFn(torch.autograd.Function):
+    """(B, C, T) contiguous -> the (B, C, 1, T) channels-last view of its (B, T, C) transpose, and back for the gradient,
+    on the tiled 16-bit transpose kernel (torch's strided copy: ~1 TB/s)."""
+
+    @staticmethod
+    def forward(ctx, h):
+        from . import ops
+        B, C, T = h.shape
+        return ops.transpose16(h.contiguous()).view(B, 1, T, C).permute(0, 3, 1, 2)
+
+    @staticmethod
+    def backward(ctx, dy):
+        from . import ops
+        B, C, _, T = dy.shape
+        d = dy.permute(0, 2, 3, 1).contiguous().view(B, T, C)          # a view when dy is channels-last, as it is here
+        return ops.transpose16(d)
+
+
 def _feature_encoder_channels_last(self, input_values):
     """Drop-in for `Wav2Vec2FeatureEncoder.forward` (third-party; row N4).  The stock layers 1..6 are nn.Conv1d on
     (B, C, T) tensors: torch hands cuDNN contiguous NCW tensors, cuDNN's 16-bit kernels are NHWC, and every convolution
@@ -348,7 +366,10 @@ def _feature_encoder_channels_last(self, input_values):
     if not ok:
         return self._b2d_stock_forward(input_values)
     h = layers[0](input_values[:, None])
-    h = h.unsqueeze(2).contiguous(memory_format=torch.channels_last)
+    if h.dtype in (torch.bfloat16, torch.float16):
+        h = _ToChannelsLastFn.apply(h)
+    else:
+        h = h.unsqueeze(2).contiguous(memory_format=torch.channels_last)
     for layer in layers[1:]:
         conv = layer.conv
         h = nn.functional.conv2d(h, conv.weight.unsqueeze(2), conv.bias, stride=(1, conv.stride[0]))

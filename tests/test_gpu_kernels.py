@@ -616,6 +616,47 @@ def test_wav2vec2_feature_convs_as_channels_last_conv2d_match_stock_conv1d():
     assert torch.equal(fast.cpu()(a.cpu()), stock.cpu()(a.cpu()))
 
 
+@pytest.mark.parametrize("B,R,Cc", [(3, 512, 799), (2, 799, 512), (1, 1, 1), (4, 65, 63), (2, 64, 128)])
+def test_transpose16_and_channels_last_bridge(B, R, Cc):
+    """b2d_transpose16 (odd and even sizes, ragged tiles) is an exact transpose; `_ToChannelsLastFn` gives the
+    channels-last view of it and transposes the gradient back."""
+    from lipreading_video_generation_b200 import ops
+    import lipreading_video_generation_b200.unet_audio as UA
+    x = torch.randn(B, R, Cc, generator=gen(R + Cc)).to(torch.bfloat16).cuda()
+    assert torch.equal(ops.transpose16(x), x.transpose(1, 2).contiguous())
+    xg = x.clone().requires_grad_(True)
+    y = UA._ToChannelsLastFn.apply(xg)
+    assert y.shape == (B, R, 1, Cc) and y.is_contiguous(memory_format=torch.channels_last)
+    assert torch.equal(y, x.unsqueeze(2))
+    g = torch.randn(B, R, 1, Cc, generator=gen(1)).to(torch.bfloat16).cuda().contiguous(memory_format=torch.channels_last)
+    y.backward(g)
+    assert torch.equal(xg.grad, g.squeeze(2))
+
+
+def test_wav2vec2_feature_extractor_under_autocast_with_all_patches_inside_the_16bit_bar():
+    """Fused layer 0 (bf16 out) -> tiled transpose -> channels-last convolutions, bf16 autocast, against the stock
+    feature extractor in fp32: features and weight gradients inside north_star's 2e-2."""
+    import copy
+    from transformers import Wav2Vec2Config, Wav2Vec2Model
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(4)
+    stock = Wav2Vec2Model(Wav2Vec2Config(num_hidden_layers=1)).cuda().train()
+    fast = copy.deepcopy(stock)
+    UA.patch_feature_layer0(fast)
+    UA.patch_feature_convs(fast)
+    a = torch.randn(6, 4000, generator=gen(10)).cuda()
+    y1 = stock.feature_extractor(a.clone())
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        y2 = fast.feature_extractor(a.clone())
+    assert y2.dtype == torch.bfloat16 and y2.transpose(1, 2).is_contiguous()
+    assert rel(y2, y1) <= 2e-2
+    r = torch.randn(y1.shape, generator=gen(11)).cuda()
+    (y1 * r).sum().backward()
+    (y2.float() * r).sum().backward()
+    for (n1, p1), (_, p2) in zip(stock.feature_extractor.named_parameters(), fast.feature_extractor.named_parameters()):
+        assert rel(p2.grad, p1.grad) <= 2e-2, (n1, rel(p2.grad, p1.grad))
+
+
 # ----------------------------------------------------------------------------- Adam (row N3)
 @pytest.mark.parametrize("wd", [0.0, 0.01])
 def test_adam_multi_tensor_matches_torch_adam(wd):
