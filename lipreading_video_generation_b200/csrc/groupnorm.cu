@@ -1138,7 +1138,10 @@ extern "C" int b2d_groupnorm_apply(const b2d_gn_args* a, const double* st1, cons
   B2D_REQUIRE(s.C1 % 2 == 0 && s.C2 % 2 == 0 && (Ctot / 32) % 2 == 0, B2D_ERR_SHAPE,
               "groupnorm_apply: groups of %d channels do not split into channel pairs", Ctot / 32);
   dim3 grid; int threads;
-  gn_launch_dims(a->N, a->HW, Ctot, 4, &grid, &threads);
+  // CTAs per SM's worth of grid: 2-3 measured best (scripts/bench_gn_fused.py: forward class 2.16 -> 2.0 ms, backward
+  // 5.17 -> 4.7 ms against 8): fewer, longer CTAs amortise the per-CTA moment / constant set-up
+  static const int bps_f = [] { const char* e = getenv("B2D_GN_BPS_F"); return e ? atoi(e) : 3; }();
+  gn_launch_dims(a->N, a->HW, Ctot, bps_f, &grid, &threads);
   gn_apply2_kernel<<<grid, threads, 0, (cudaStream_t)stream>>>(s, a->HW, Ctot, st1, st2, rows_per_sample, a->gamma, a->beta,
                                                                a->eps, a->act, a->drop_p, a->seed, (__half*)y, mean, rstd,
                                                                mask_out);
@@ -1163,7 +1166,8 @@ extern "C" int b2d_groupnorm_bwd_apply(const b2d_gn_args* a, const void* dyh, co
   o.add_a = (const __half*)add_a; o.lda = lda; o.add_b = (const __half*)add_b; o.ldb = ldb; o.add_a_full = add_a_full;
   o.colsum = dx1_colsum; o.ldcs = ld_colsum; o.overflow = a->overflow;
   dim3 grid; int threads;
-  gn_launch_dims(a->N, a->HW, Ctot, 8, &grid, &threads);
+  static const int bps_b = [] { const char* e = getenv("B2D_GN_BPS_B"); return e ? atoi(e) : 3; }();
+  gn_launch_dims(a->N, a->HW, Ctot, bps_b, &grid, &threads);
   if (dx1_colsum)
     gn_bwd_apply2_kernel<true><<<grid, threads, s.C1 * sizeof(float), st>>>(s, (const __half*)dyh, a->HW, Ctot, mean, rstd,
                                                                            a->gamma, ab, o);
