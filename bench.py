@@ -746,7 +746,7 @@ def main():
         out = {"metric": "sampler_frames_per_s", "n_gpus": world, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config, **rec}
         if rank == 0:
-            out["cpu_baseline"] = None if no_cpu else cpu_sampler_baseline(cores)
+            out["cpu_baseline"] = None if (no_cpu or world > 1) else cpu_sampler_baseline(cores)
             print(json.dumps(out))
         if world > 1:
             torch.distributed.destroy_process_group()
@@ -777,8 +777,11 @@ def main():
     if world > 1:
         torch.distributed.barrier()
     if rank == 0:
-        if no_cpu:
-            out["cpu_baseline"] = {"value": None, "unit": "clips/s", "cores": cores, "kind": "port", "sample": "skipped (B2D_BENCH_NO_CPU=1)"}
+        if no_cpu or world > 1:
+            # the CPU baseline is timed at N = 1 only (one process owns the host cores; under torchrun the other ranks
+            # spin in the barrier and OMP_NUM_THREADS is 1)
+            out["cpu_baseline"] = {"value": None, "unit": "clips/s", "cores": cores, "kind": "port",
+                                   "sample": "skipped (B2D_BENCH_NO_CPU=1)" if no_cpu else "timed at N = 1 only"}
         else:
             out["cpu_baseline"] = cpu_train_baseline(cores, frames)
             if "sample128" in extras:
