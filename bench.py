@@ -347,6 +347,19 @@ def _attention_roofline(totals, steps, ms_step, sustained, which):
                            f"10*L^2*ch*N bwd"}
 
 
+def _fill_traffic(rec, n_img):
+    """roofline.traffic: DRAM bytes per launch of the dominant kernel from one `ncu --set full` capture at this shape
+    (profiles/r2_traffic.json), null when no capture exists for it."""
+    try:
+        with open(os.path.join(ROOT, "profiles", "r2_traffic.json")) as f:
+            table = json.load(f)["kernels"]
+        hit = table.get(f'{rec["roofline"]["kernel"]}|N={n_img}')
+        if hit:
+            rec["roofline"]["traffic"] = hit["traffic_bytes_per_launch"]
+    except (OSError, KeyError, ValueError, TypeError):
+        pass
+
+
 def measure_train(steps, warmup, S, clips, frames, world, rank, local, device, verbose=False):
     """Returns the record of one train workload (all ranks run it; max over ranks)."""
     from lipreading_video_generation_b200 import _lib as L, ops
@@ -743,6 +756,7 @@ def main():
 
     if kind == "sample":
         rec = measure_sample(a.steps, a.warmup, S, clips, frames, world, rank, local, device)
+        _fill_traffic(rec, clips * frames)
         out = {"metric": "sampler_frames_per_s", "n_gpus": world, "higher_is_better": True, "scaling": "weak",
                "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config, **rec}
         if rank == 0:
@@ -753,12 +767,7 @@ def main():
         return
 
     rec = measure_train(a.steps, a.warmup, S, clips, frames, world, rank, local, device, verbose=True)
-    if rec["roofline"]["kernel"] == "attention_bwd L=4096 ch=64" and clips * frames == 256:
-        try:          # DRAM bytes per launch of the dominant kernel from one `ncu --set full` capture at this shape
-            with open(os.path.join(ROOT, "profiles", "r1_traffic.json")) as f:
-                rec["roofline"]["traffic"] = json.load(f)["traffic_bytes_per_launch"]
-        except (OSError, KeyError, ValueError):
-            pass
+    _fill_traffic(rec, clips * frames)
     out = {"metric": "denoiser_train_clips_per_s", "n_gpus": world, "higher_is_better": True, "scaling": "weak",
            "vs_baseline": None, "dtype": "f16", "data": "synthetic", "config": config, **rec}
     extras = {}
@@ -767,10 +776,12 @@ def main():
         c2, f2, s2, _ = WORKLOADS["sample128"]
         r = measure_sample(ks, 3, s2, c2, f2, world, rank, local, device)
         r["config"] = _config("sample128", c2, f2, s2, "sample", world)
+        _fill_traffic(r, c2 * f2)
         extras["sample128"] = r
         c3, f3, s3, _ = WORKLOADS["train128"]
         r = measure_train(max(3, min(a.steps, 3)), 3, s3, c3, f3, world, rank, local, device)
         r["config"] = _config("train128", c3, f3, s3, "train", world)
+        _fill_traffic(r, c3 * f3)
         extras["train128"] = r
         if rank == 0:
             extras["hbm_kernels"] = measure_hbm_kernels(device)
