@@ -35,7 +35,11 @@ struct AttnBwdMaps {
   CUtensorMap doT;     // box (64, BT, 1) on dO
 };
 
-constexpr int AB_THREADS = 192;
+// warps: 0 = TMA producer, 1 = tcgen05 issuer, 2..9 = compute: two warps per TMEM lane quarter, each one half of the
+// streamed tile's columns (round 2; one warp per quarter left the exp / pack phase ~2x longer than the tile's MMAs)
+constexpr int AB_CWARPS = 8;
+constexpr int AB_CTHREADS = AB_CWARPS * 32;
+constexpr int AB_THREADS = 64 + AB_CTHREADS;
 
 __device__ __forceinline__ void named_bar_sync(int id, int count) {
   asm volatile("bar.sync %0, %1;" :: "r"(id), "r"(count) : "memory");
@@ -92,13 +96,16 @@ attn_delta_kernel(const __half* __restrict__ o, long long ldo, const __half* __r
 // ------------------------------------------------------------------ kernel A: dK, dV
 template <int D, int DH, int BQ>
 struct DkvCfg {
-  static constexpr int ST = (D == 256) ? 1 : 2;
+  static constexpr int ST = (D == 256) ? 1 : (D == 128 ? 3 : 2);
+  // S^T | dP^T of step j + 1 are computed into a second pair of TMEM column blocks while the compute warps work on
+  // step j (round 2): needs two free stages and BQ <= 64 (columns [BQ, 128) and [128 + BQ, 256) are free then)
+  static constexpr bool PIPE = ST >= 2 && BQ <= 64;
   static constexpr int KV_BYTES = 128 * D * 2;
   static constexpr int QT_BYTES = BQ * D * 2;
   static constexpr int STAGE_BYTES = 2 * QT_BYTES;   // Q tile + dO tile
   static constexpr int PT_BYTES = 128 * BQ * 2;
   static constexpr int SMEM_DATA = 2 * KV_BYTES + ST * STAGE_BYTES + 2 * PT_BYTES;
-  static constexpr int SMEM_TOTAL = SMEM_DATA + 2 * 2 * BQ * 4 + (2 * ST + 4) * 8 + 16 + 1024;
+  static constexpr int SMEM_TOTAL = SMEM_DATA + 2 * 2 * BQ * 4 + (2 * ST + 5) * 8 + 16 + 1024;
   static constexpr uint32_t ST_COL = 0, DPT_COL = 128, DV_COL = 256, DK_COL = 256 + DH;
 };
 
@@ -119,8 +126,8 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
   uint64_t* kv_full = bars;
   uint64_t* full = bars + 1;
   uint64_t* empty = full + Cfg::ST;
-  uint64_t* s_full = empty + Cfg::ST;
-  uint64_t* p_ready = s_full + 1;
+  uint64_t* s_full = empty + Cfg::ST;      // [2]
+  uint64_t* p_ready = s_full + 2;
   uint64_t* acc_done = p_ready + 1;
   uint32_t* tmem_slot = (uint32_t*)(acc_done + 1);
 
@@ -135,7 +142,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
   if (threadIdx.x == 0) {
     mbar_init(kv_full, 1);
     for (int s = 0; s < Cfg::ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    mbar_init(s_full, 1); mbar_init(p_ready, 128); mbar_init(acc_done, 1);
+    mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, AB_CTHREADS); mbar_init(acc_done, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -173,30 +180,40 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
     const uint32_t k_addr = smem_u32(k_s), v_addr = smem_u32(v_s);
     const uint32_t pt_addr = smem_u32(pt_s), dst_addr = smem_u32(dst_s);
     mbar_wait(kv_full, 0);
-    for (int j = 0; j < n_q; ++j) {
+    auto issue_sdp = [&](int j) {             // S^T | dP^T of step j into column block (PIPE ? j & 1 : 0)
       const int s = j % Cfg::ST;
       mbar_wait(&full[s], (uint32_t)((j / Cfg::ST) & 1));
       tc_fence_after();
       const uint32_t q_addr = smem_u32(st_s + s * Cfg::STAGE_BYTES);
       const uint32_t do_addr = q_addr + Cfg::QT_BYTES;
+      const uint32_t buf = Cfg::PIPE ? (uint32_t)(j & 1) : 0u;
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BQ * 128) + (kk & 3) * 32;
-          mma_f16_ss(tmem_base + Cfg::ST_COL, make_sdesc_sw128(k_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::ST_COL + buf * BQ, make_sdesc_sw128(k_addr + ao, 16, 1024),
                       make_sdesc_sw128(q_addr + bo, 16, 1024), idesc_s, (uint32_t)(kk != 0));
         }
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BQ * 128) + (kk & 3) * 32;
-          mma_f16_ss(tmem_base + Cfg::DPT_COL, make_sdesc_sw128(v_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::DPT_COL + buf * BQ, make_sdesc_sw128(v_addr + ao, 16, 1024),
                       make_sdesc_sw128(do_addr + bo, 16, 1024), idesc_p, (uint32_t)(kk != 0));
         }
-        mma_commit(s_full);
+        mma_commit(&s_full[buf]);
       }
       __syncwarp();
+    };
+    if (Cfg::PIPE) issue_sdp(0);
+    for (int j = 0; j < n_q; ++j) {
+      const int s = j % Cfg::ST;
+      // the column block of step j + 1 was last read by the compute warps in step j - 1, whose p_ready this warp has
+      // waited for; the stage of step j + 1 is free since the dV / dK MMAs of step j + 1 - ST completed
+      if (Cfg::PIPE) { if (j + 1 < n_q) issue_sdp(j + 1); } else issue_sdp(j);
+      const uint32_t q_addr = smem_u32(st_s + s * Cfg::STAGE_BYTES);
+      const uint32_t do_addr = q_addr + Cfg::QT_BYTES;
       mbar_wait(p_ready, (uint32_t)(j & 1));
       tc_fence_after();
       if (elect_one()) {
@@ -220,8 +237,9 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
     }
   } else {
     const int qd = warp & 3;
+    const int chalf = (warp - 2) >> 2;         // which half of the step's BQ query columns this warp takes
     const int row = qd * 32 + lane;            // key index within the tile
-    const int ct = threadIdx.x - 64;           // 0..127 among compute threads
+    const int ct = threadIdx.x - 64;           // 0..255 among compute threads
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const float c = p.scale_log2;
     const float* lse_g = p.lse + ((long long)n * p.heads + head) * p.L;
@@ -234,15 +252,17 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
         ls[ct] = qi < p.L ? __ldg(lse_g + qi) : INFINITY;
         ds[ct] = qi < p.L ? __ldg(del_g + qi) : 0.f;
       }
-      named_bar_sync(1, 128);
-      mbar_wait(s_full, (uint32_t)(j & 1));
+      named_bar_sync(1, AB_CTHREADS);
+      const uint32_t buf = Cfg::PIPE ? (uint32_t)(j & 1) : 0u;
+      mbar_wait(&s_full[buf], (uint32_t)(Cfg::PIPE ? ((j >> 1) & 1) : (j & 1)));
       tc_fence_after();
       if (j > 0) mbar_wait(acc_done, (uint32_t)((j - 1) & 1));   // previous dV/dK MMAs have read P^T / dS^T
 #pragma unroll
-      for (int c0 = 0; c0 < BQ; c0 += 32) {
+      for (int cc = 0; cc < BQ / 2; cc += 32) {
+        const int c0 = chalf * (BQ / 2) + cc;
         uint32_t sr[32], dr[32];
-        tmem_ld32(lane_base + Cfg::ST_COL + c0, sr);
-        tmem_ld32(lane_base + Cfg::DPT_COL + c0, dr);
+        tmem_ld32(lane_base + Cfg::ST_COL + buf * BQ + c0, sr);
+        tmem_ld32(lane_base + Cfg::DPT_COL + buf * BQ + c0, dr);
         tmem_ld_wait();
         float pv[32], dv[32];
 #pragma unroll
@@ -275,7 +295,7 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
     const bool valid = ki < p.L;
     __half* base = p.dqkv + ((long long)n * p.L + ki) * p.lddqkv;
 #pragma unroll
-    for (int c0 = 0; c0 < DH; c0 += 16) {
+    for (int c0 = chalf * 16; c0 < DH; c0 += 32) {
       uint32_t a[16], b[16];
       tmem_ld16(lane_base + Cfg::DV_COL + c0, a);
       tmem_ld16(lane_base + Cfg::DK_COL + c0, b);
@@ -306,13 +326,14 @@ attn_bwd_dkv_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParam
 // ------------------------------------------------------------------ kernel B: dQ
 template <int D, int BKV>
 struct DqCfg {
-  static constexpr int ST = (D == 256) ? 1 : 2;
+  static constexpr int ST = (D == 256) ? 1 : (D == 128 ? 3 : 2);
+  static constexpr bool PIPE = ST >= 2 && BKV <= 64;   // S | dP of step j + 1 in a second pair of TMEM column blocks
   static constexpr int Q_BYTES = 128 * D * 2;
   static constexpr int T_BYTES = BKV * D * 2;
   static constexpr int STAGE_BYTES = 2 * T_BYTES;   // K tile + V tile
   static constexpr int DS_BYTES = 128 * BKV * 2;
   static constexpr int SMEM_DATA = 2 * Q_BYTES + ST * STAGE_BYTES + DS_BYTES;
-  static constexpr int SMEM_TOTAL = SMEM_DATA + (2 * ST + 4) * 8 + 16 + 1024;
+  static constexpr int SMEM_TOTAL = SMEM_DATA + (2 * ST + 5) * 8 + 16 + 1024;
   static constexpr uint32_t S_COL = 0, DP_COL = 128, DQ_COL = 256;
 };
 
@@ -330,8 +351,8 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
   uint64_t* q_full = bars;
   uint64_t* full = bars + 1;
   uint64_t* empty = full + Cfg::ST;
-  uint64_t* s_full = empty + Cfg::ST;
-  uint64_t* p_ready = s_full + 1;
+  uint64_t* s_full = empty + Cfg::ST;      // [2]
+  uint64_t* p_ready = s_full + 2;
   uint64_t* acc_done = p_ready + 1;
   uint32_t* tmem_slot = (uint32_t*)(acc_done + 1);
 
@@ -344,7 +365,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
   if (threadIdx.x == 0) {
     mbar_init(q_full, 1);
     for (int s = 0; s < Cfg::ST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    mbar_init(s_full, 1); mbar_init(p_ready, 128); mbar_init(acc_done, 1);
+    mbar_init(&s_full[0], 1); mbar_init(&s_full[1], 1); mbar_init(p_ready, AB_CTHREADS); mbar_init(acc_done, 1);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc(tmem_slot, 512);
@@ -380,30 +401,37 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
     const uint32_t idesc_g = make_idesc(128, D, 0, 1, FMT_F16, FMT_F16);    // dQ += dS K    (bf16 x fp16)
     const uint32_t q_addr = smem_u32(q_s), do_addr = smem_u32(do_s), ds_addr = smem_u32(ds_s);
     mbar_wait(q_full, 0);
-    for (int j = 0; j < n_kv; ++j) {
+    auto issue_sdp = [&](int j) {             // S | dP of step j into column block (PIPE ? j & 1 : 0)
       const int s = j % Cfg::ST;
       mbar_wait(&full[s], (uint32_t)((j / Cfg::ST) & 1));
       tc_fence_after();
       const uint32_t k_addr = smem_u32(st_s + s * Cfg::STAGE_BYTES);
       const uint32_t v_addr = k_addr + Cfg::T_BYTES;
+      const uint32_t buf = Cfg::PIPE ? (uint32_t)(j & 1) : 0u;
       if (elect_one()) {
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-          mma_f16_ss(tmem_base + Cfg::S_COL, make_sdesc_sw128(q_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::S_COL + buf * BKV, make_sdesc_sw128(q_addr + ao, 16, 1024),
                       make_sdesc_sw128(k_addr + bo, 16, 1024), idesc_s, (uint32_t)(kk != 0));
         }
 #pragma unroll
         for (int kk = 0; kk < D / 16; ++kk) {
           const uint32_t ao = (kk >> 2) * (128 * 128) + (kk & 3) * 32;
           const uint32_t bo = (kk >> 2) * (BKV * 128) + (kk & 3) * 32;
-          mma_f16_ss(tmem_base + Cfg::DP_COL, make_sdesc_sw128(do_addr + ao, 16, 1024),
+          mma_f16_ss(tmem_base + Cfg::DP_COL + buf * BKV, make_sdesc_sw128(do_addr + ao, 16, 1024),
                       make_sdesc_sw128(v_addr + bo, 16, 1024), idesc_p, (uint32_t)(kk != 0));
         }
-        mma_commit(s_full);
+        mma_commit(&s_full[buf]);
       }
       __syncwarp();
+    };
+    if (Cfg::PIPE) issue_sdp(0);
+    for (int j = 0; j < n_kv; ++j) {
+      const int s = j % Cfg::ST;
+      if (Cfg::PIPE) { if (j + 1 < n_kv) issue_sdp(j + 1); } else issue_sdp(j);
+      const uint32_t k_addr = smem_u32(st_s + s * Cfg::STAGE_BYTES);
       mbar_wait(p_ready, (uint32_t)(j & 1));
       tc_fence_after();
       if (elect_one()) {
@@ -420,6 +448,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
     }
   } else {
     const int qd = warp & 3;
+    const int chalf = (warp - 2) >> 2;         // which half of the step's BKV key columns this warp takes
     const int row = qd * 32 + lane;
     const uint32_t lane_base = tmem_base + ((uint32_t)(qd * 32) << 16);
     const float c = p.scale_log2;
@@ -429,14 +458,16 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
     const float lse_i = valid ? __ldg(p.lse + sidx) : INFINITY;
     const float del_i = valid ? __ldg(p.delta + sidx) : 0.f;
     for (int j = 0; j < n_kv; ++j) {
-      mbar_wait(s_full, (uint32_t)(j & 1));
+      const uint32_t buf = Cfg::PIPE ? (uint32_t)(j & 1) : 0u;
+      mbar_wait(&s_full[buf], (uint32_t)(Cfg::PIPE ? ((j >> 1) & 1) : (j & 1)));
       tc_fence_after();
       if (j > 0) mbar_wait(acc_done, (uint32_t)((j - 1) & 1));
 #pragma unroll
-      for (int c0 = 0; c0 < BKV; c0 += 32) {
+      for (int cc = 0; cc < BKV / 2; cc += 32) {
+        const int c0 = chalf * (BKV / 2) + cc;
         uint32_t sr[32], dr[32];
-        tmem_ld32(lane_base + Cfg::S_COL + c0, sr);
-        tmem_ld32(lane_base + Cfg::DP_COL + c0, dr);
+        tmem_ld32(lane_base + Cfg::S_COL + buf * BKV + c0, sr);
+        tmem_ld32(lane_base + Cfg::DP_COL + buf * BKV + c0, dr);
         tmem_ld_wait();
         float dv[32];
 #pragma unroll
@@ -462,7 +493,7 @@ attn_bwd_dq_kernel(const __grid_constant__ AttnBwdMaps maps, const AttnBwdParams
     __half* dst = p.dqkv + ((long long)n * p.L + qi) * p.lddqkv + qc;
     const float sc = p.scale;
 #pragma unroll
-    for (int c0 = 0; c0 < D; c0 += 16) {
+    for (int c0 = chalf * 16; c0 < D; c0 += 32) {
       uint32_t a[16];
       tmem_ld16(lane_base + Cfg::DQ_COL + c0, a);
       tmem_ld_wait();
