@@ -724,8 +724,8 @@ def main_reference(a, frames, config, cores, kind):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
-    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--steps", type=int, default=12)
+    ap.add_argument("--warmup", type=int, default=4)
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="train64", choices=list(WORKLOADS))
     ap.add_argument("--no-extras", action="store_true", help="train64 only: skip the sample128 / train128 / HBM-kernel extras")
