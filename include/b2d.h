@@ -185,6 +185,14 @@ int b2d_conv2d_wgrad(const b2d_wgrad_args* a, void* stream);
  * log2-domain log-sum-exp of the scaled logits (saved for the backward).  ch in {64,128,256}. */
 int b2d_attention_fwd(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
                       void* out, int64_t ldo, float* lse, void* stream);
+/* The same for small grids (the reference samples ONE frame at a time, test.py:54: a 128x128 frame is 64 CTAs of 256
+ * queries on 148 SMs): the key range is split over `splits` (1..8) CTAs per query block, each writes its normalised fp32
+ * output and log-sum-exp to ws (b2d_attention_fwd_splitkv_ws_floats floats, 16-byte aligned), a second kernel merges
+ * them.  ch in {64, 128}, L > 128.  Equal to b2d_attention_fwd up to the rounding of the 16-bit output. */
+int64_t b2d_attention_fwd_splitkv_ws_floats(int N, int L, int heads, int ch, int splits);
+int b2d_attention_fwd_splitkv(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
+                              int splits, float* ws, int64_t ws_floats, void* out, int64_t ldo, float* lse,
+                              void* stream);
 
 /* GroupNorm32(32, C) [+ SiLU] [+ dropout] on pixel-major fp16 (utils.py:54-56,130-137; call sites
  * unet.py:194-198 in_layers, :218-225 out_layers incl. nn.Dropout, :297 attention norm, :624-628 head).

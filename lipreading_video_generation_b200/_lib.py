@@ -128,6 +128,9 @@ SIGNATURES = {
                                   c_void_p, c_void_p]),
     "b2d_colsum_rows16": (c_int, [c_void_p, c_int, c_int64, c_int, c_int, c_void_p, c_void_p]),
     "b2d_transpose16": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p]),
+    "b2d_attention_fwd_splitkv_ws_floats": (c_int64, [c_int, c_int, c_int, c_int, c_int]),
+    "b2d_attention_fwd_splitkv": (c_int, [c_void_p, c_int64, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_int64,
+                                          c_void_p, c_int64, c_void_p, c_void_p]),
     "b2d_reduce_rows_multi": (c_int, [c_void_p, c_int, c_int, c_int, c_void_p]),
     "b2d_timestep_embedding": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "b2d_linear_fwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_void_p]),

@@ -279,7 +279,8 @@ static int launch_attn_fwd(const AttnMaps& maps, const AttnFwdParams& p, int N, 
 }
 
 int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order, void* out,
-                            int64_t ldo, float* lse, int q_row0, int q_rows, void* stream);   // attention_fwd2.cu
+                            int64_t ldo, float* lse, int q_row0, int q_rows, void* stream, int kv_splits = 1,
+                            float* ws = nullptr);   // attention_fwd2.cu
 
 }  // namespace b2d
 
@@ -329,4 +330,26 @@ extern "C" int b2d_attention_fwd_rows(const void* qkv, int64_t ldqkv, int N, int
               "attention_fwd_rows: rows [%d, +%d) must be 256-aligned inside L=%d", q_row0, q_rows, L);
   B2D_REQUIRE(ldo % 8 == 0 && aligned16(out), B2D_ERR_ALIGN, "attention_fwd_rows: output must be 16-byte aligned rows");
   return attention_fwd2_dispatch(qkv, ldqkv, N, L, heads, ch, new_order, out, ldo, lse, q_row0, q_rows, stream);
+}
+
+// Small grids (batch-1 sampling: one 128 x 128 frame = 64 CTAs of 256 queries on 148 SMs): the key range is split over
+// `splits` CTAs per query block, each writes its normalised fp32 output and log-sum-exp to `ws`, a second kernel merges
+// them.  Same result as b2d_attention_fwd up to the 16-bit rounding of the output.  ws: b2d_attention_fwd_splitkv_ws_floats.
+extern "C" int64_t b2d_attention_fwd_splitkv_ws_floats(int N, int L, int heads, int ch, int splits) {
+  if (splits < 1) splits = 1;
+  if (splits > 8) splits = 8;
+  return (int64_t)splits * N * L * heads * (ch + 1);
+}
+
+extern "C" int b2d_attention_fwd_splitkv(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order,
+                                         int splits, float* ws, int64_t ws_floats, void* out, int64_t ldo, float* lse,
+                                         void* stream) {
+  B2D_REQUIRE(qkv && out && ws, B2D_ERR_SHAPE, "attention_fwd_splitkv: null pointer");
+  B2D_REQUIRE(N > 0 && L > 128 && heads > 0 && N <= 65535 && heads <= 65535, B2D_ERR_SHAPE, "attention_fwd_splitkv: bad sizes");
+  B2D_REQUIRE(ch == 64 || ch == 128, B2D_ERR_SHAPE, "attention_fwd_splitkv: head dim %d not in {64,128}", ch);
+  B2D_REQUIRE(splits >= 1 && splits <= 8, B2D_ERR_SHAPE, "attention_fwd_splitkv: splits=%d not in [1, 8]", splits);
+  B2D_REQUIRE(ws_floats >= b2d_attention_fwd_splitkv_ws_floats(N, L, heads, ch, splits) && aligned16(ws), B2D_ERR_WORKSPACE,
+              "attention_fwd_splitkv: workspace of %lld floats too small or misaligned", (long long)ws_floats);
+  B2D_REQUIRE(ldo % 8 == 0 && aligned16(out), B2D_ERR_ALIGN, "attention_fwd_splitkv: output must be 16-byte aligned rows");
+  return attention_fwd2_dispatch(qkv, ldqkv, N, L, heads, ch, new_order, out, ldo, lse, 0, L, stream, splits, ws);
 }

@@ -36,6 +36,12 @@ struct AttnFwd2Params {
   float scale_log2;
   __half* out; long long ldo;
   float* lse;
+  // split-KV (small grids: batch-1 sampling): blockIdx.z = n * kv_splits + split, split s visits key tiles
+  // [s * kv_tiles_per_split, ...) and writes its normalised fp32 output / lse to part_o / part_lse; attn_combine_kernel
+  // merges the splits.  kv_splits == 1: the kernel writes out / lse itself.
+  int kv_splits, kv_tiles_per_split;
+  float* part_o;      // [split][n][L][heads * D]
+  float* part_lse;    // [split][n][heads][L]
   long long* trace;     // developer builds (-DFWD2_TRACE): clock64 stamps of CTA (0,0,0), [17 roles][64 steps][8]
 };
 
@@ -104,8 +110,10 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
   const int lane = threadIdx.x & 31;
   const int q0 = p.q_row0 + blockIdx.x * 256;
   const int head = blockIdx.y;
-  const int n = blockIdx.z;
-  const int n_kv = (p.L + BKV - 1) / BKV;
+  const int n = (int)blockIdx.z / p.kv_splits;
+  const int split = (int)blockIdx.z - n * p.kv_splits;
+  const int j0 = split * p.kv_tiles_per_split;                      // first key tile of this CTA
+  const int n_kv = min(p.kv_tiles_per_split, (p.L + BKV - 1) / BKV - j0);
   const int qc = p.q_off + head * p.head_stride;
   const int kc = p.k_off + head * p.head_stride;
   const int vc = p.v_off + head * p.head_stride;
@@ -142,10 +150,10 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
         uint8_t* v_dst = k_dst + Cfg::K_BYTES;
         mbar_expect_tx(&k_full[s], Cfg::K_BYTES);
 #pragma unroll
-        for (int b = 0; b < D / 64; ++b) tma_load_3d(k_dst + b * (BKV * 128), &maps.kv, &k_full[s], kc + b * 64, j * BKV, n);
+        for (int b = 0; b < D / 64; ++b) tma_load_3d(k_dst + b * (BKV * 128), &maps.kv, &k_full[s], kc + b * 64, (j0 + j) * BKV, n);
         mbar_expect_tx(&v_full[s], Cfg::K_BYTES);
 #pragma unroll
-        for (int b = 0; b < D / 64; ++b) tma_load_3d(v_dst + b * (BKV * 128), &maps.kv, &v_full[s], vc + b * 64, j * BKV, n);
+        for (int b = 0; b < D / 64; ++b) tma_load_3d(v_dst + b * (BKV * 128), &maps.kv, &v_full[s], vc + b * 64, (j0 + j) * BKV, n);
       }
     }
   } else if (warp == 1) {
@@ -244,7 +252,7 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
       tc_fence_before();
       mbar_arrive(&s_free[t]);             // S_t may be overwritten by the next tile's Q K^T
       FWD2_STAMP(t * 8 + g, j, 2, sr[0]);
-      const int kv_valid = p.L - j * BKV - half * HC;  // keys of this part that exist (>= HC except on the last tile)
+      const int kv_valid = p.L - (j0 + j) * BKV - half * HC;  // keys of this part that exist (>= HC except on the last tile)
       if (kv_valid < HC) {
 #pragma unroll
         for (int i = 0; i < HC; ++i) if (i >= kv_valid) sr[i] = 0xff800000u;   // -inf
@@ -324,6 +332,26 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
     const int qi = q0 + t * 128 + row;
     const bool valid = qi < p.L;
     const float inv_l = 1.0f / l_sum;
+    if (p.kv_splits > 1) {
+      const int n_img = (int)gridDim.z / p.kv_splits;
+      // this split's normalised output in fp32 + its log-sum-exp; merged by attn_combine_kernel
+      float* op = p.part_o + (((long long)split * n_img + n) * p.L + qi) * (p.heads * D) + head * D + half * (D / 2);
+#pragma unroll
+      for (int c0 = 0; c0 < D / 2; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(o_addr + c0, r);
+        tmem_ld_wait();
+        if (valid) {
+#pragma unroll
+          for (int gg = 0; gg < 8; ++gg)
+            *reinterpret_cast<float4*>(op + c0 + 4 * gg) =
+                make_float4(__uint_as_float(r[4 * gg]) * inv_l, __uint_as_float(r[4 * gg + 1]) * inv_l,
+                            __uint_as_float(r[4 * gg + 2]) * inv_l, __uint_as_float(r[4 * gg + 3]) * inv_l);
+        }
+      }
+      if (half == 0 && valid)
+        p.part_lse[(((long long)split * n_img + n) * p.heads + head) * p.L + qi] = m_used * c + log2f(l_sum);
+    } else {
     __half* op = p.out + ((long long)n * p.L + qi) * p.ldo + head * D + half * (D / 2);
 #pragma unroll
     for (int c0 = 0; c0 < D / 2; c0 += 32) {
@@ -343,10 +371,48 @@ attn_fwd2_kernel(const __grid_constant__ AttnFwd2Maps maps, const AttnFwd2Params
       }
     }
     if (half == 0 && valid && p.lse) p.lse[((long long)n * p.heads + head) * p.L + qi] = m_used * c + log2f(l_sum);
+    }
   }
   tc_fence_before();
   __syncthreads();
   if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// out[n, l, head, :] = sum_s w_s o_s,  w_s = 2^(lse_s - lse),  lse = log2 sum_s 2^lse_s  (one thread per 8 channels)
+__global__ void __launch_bounds__(256)
+attn_combine_kernel(const float* __restrict__ part_o, const float* __restrict__ part_lse, int splits, int N, int L, int heads,
+                    int D, __half* __restrict__ out, long long ldo, float* __restrict__ lse) {
+  const int G = D >> 3;
+  const long long total = (long long)N * L * heads * G;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  const int g = (int)(i % G);
+  const long long r = i / G;                 // (n, l, head)
+  const int head = (int)(r % heads);
+  const long long nl = r / heads;
+  const int n = (int)(nl / L), l = (int)(nl - (long long)n * L);
+  float ls[8];
+  float m = -INFINITY;
+  for (int s = 0; s < splits; ++s) {
+    ls[s] = part_lse[(((long long)s * N + n) * heads + head) * L + l];
+    m = fmaxf(m, ls[s]);
+  }
+  float tot = 0.f;
+  for (int s = 0; s < splits; ++s) { ls[s] = exp2f(ls[s] - m); tot += ls[s]; }
+  const float inv = 1.0f / tot;
+  float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  for (int s = 0; s < splits; ++s) {
+    const float* src = part_o + (((long long)s * N + n) * L + l) * (heads * D) + head * D + g * 8;
+    const float4 a = *reinterpret_cast<const float4*>(src), b = *reinterpret_cast<const float4*>(src + 4);
+    const float w = ls[s] * inv;
+    acc[0] = fmaf(w, a.x, acc[0]); acc[1] = fmaf(w, a.y, acc[1]); acc[2] = fmaf(w, a.z, acc[2]); acc[3] = fmaf(w, a.w, acc[3]);
+    acc[4] = fmaf(w, b.x, acc[4]); acc[5] = fmaf(w, b.y, acc[5]); acc[6] = fmaf(w, b.z, acc[6]); acc[7] = fmaf(w, b.w, acc[7]);
+  }
+  uint4 o;
+  o.x = pack_f16x2(acc[0], acc[1]); o.y = pack_f16x2(acc[2], acc[3]);
+  o.z = pack_f16x2(acc[4], acc[5]); o.w = pack_f16x2(acc[6], acc[7]);
+  *reinterpret_cast<uint4*>(out + ((long long)n * L + l) * ldo + head * D + g * 8) = o;
+  if (g == 0 && lse) lse[((long long)n * heads + head) * L + l] = m + log2f(tot);
 }
 
 template <int D, int BKV>
@@ -362,15 +428,23 @@ static int launch_attn_fwd2(const void* qkv, int64_t ldqkv, int N, int C3, const
   if (rc) return rc;
   rc = make_tmap_16b(&maps.kv, qkv, 3, dims, str, boxkv);
   if (rc) return rc;
-  dim3 grid((unsigned)((p.q_rows + 255) / 256), (unsigned)p.heads, (unsigned)N);
+  B2D_REQUIRE((long long)N * p.kv_splits <= 65535, B2D_ERR_SHAPE, "attention_fwd: N * splits = %lld exceeds 65535",
+              (long long)N * p.kv_splits);
+  dim3 grid((unsigned)((p.q_rows + 255) / 256), (unsigned)p.heads, (unsigned)(N * p.kv_splits));
   attn_fwd2_kernel<D, BKV><<<grid, ATT2_THREADS, Cfg::SMEM_TOTAL, (cudaStream_t)stream>>>(maps, p);
   B2D_CHECK_LAUNCH();
+  if (p.kv_splits > 1) {
+    const long long total = (long long)N * p.L * p.heads * (D / 8);
+    attn_combine_kernel<<<(unsigned)((total + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        p.part_o, p.part_lse, p.kv_splits, N, p.L, p.heads, D, p.out, p.ldo, p.lse);
+    B2D_CHECK_LAUNCH();
+  }
   return B2D_OK;
 }
 
 // called by b2d_attention_fwd (attention_fwd.cu) for ch in {64, 128} and L > 128
 int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int heads, int ch, int new_order, void* out,
-                            int64_t ldo, float* lse, int q_row0, int q_rows, void* stream) {
+                            int64_t ldo, float* lse, int q_row0, int q_rows, void* stream, int kv_splits, float* ws) {
   const int C = heads * ch;
   AttnFwd2Params p;
   p.L = L; p.heads = heads;
@@ -379,6 +453,17 @@ int attention_fwd2_dispatch(const void* qkv, int64_t ldqkv, int N, int L, int he
   else           { p.q_off = 0; p.k_off = ch; p.v_off = 2 * ch; p.head_stride = 3 * ch; }    // unet.py:359
   p.scale_log2 = 1.4426950408889634f / sqrtf((float)ch);
   p.out = (__half*)out; p.ldo = ldo; p.lse = lse;
+  {
+    const int bkv = ch == 64 ? 128 : 64;
+    const int tiles = (L + bkv - 1) / bkv;
+    if (kv_splits < 1 || !ws) kv_splits = 1;
+    if (kv_splits > 8) kv_splits = 8;
+    if (kv_splits > tiles) kv_splits = tiles;
+    p.kv_tiles_per_split = (tiles + kv_splits - 1) / kv_splits;
+    p.kv_splits = (tiles + p.kv_tiles_per_split - 1) / p.kv_tiles_per_split;     // no empty split
+    p.part_o = ws;
+    p.part_lse = ws ? ws + (size_t)p.kv_splits * N * L * heads * ch : nullptr;
+  }
   p.trace = nullptr;
 #ifdef FWD2_TRACE
   { const char* e = getenv("B2D_FWD2_TRACE_PTR"); if (e) p.trace = (long long*)strtoull(e, nullptr, 0); }

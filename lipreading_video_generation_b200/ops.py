@@ -339,9 +339,20 @@ def groupnorm_bwd_apply(x1, gamma, beta, dyh, mean, rstd, ab, dgamma, dbeta, x2=
     return dx1, dx2
 
 
-def attention_fwd(qkv, heads, new_order=False, rows=None):
+_SM_COUNT: dict = {}
+
+
+def _sm_count(dev):
+    i = dev.index if dev.index is not None else torch.cuda.current_device()
+    if i not in _SM_COUNT:
+        _SM_COUNT[i] = torch.cuda.get_device_properties(i).multi_processor_count
+    return _SM_COUNT[i]
+
+
+def attention_fwd(qkv, heads, new_order=False, rows=None, split=None):
     """qkv (N,H,W,3C) fp16 -> (out (N,H,W,C) fp16, lse (N,heads,L) fp32).  rows = (q_row0, q_rows): sequence-parallel
-    shard -- only those query rows of out / lse are written (the caller all-gathers `out`)."""
+    shard -- only those query rows of out / lse are written (the caller all-gathers `out`).  A grid that would leave
+    most SMs idle (batch-1 sampling) takes the split-KV variant unless split=False."""
     if qkv.dtype != F16:
         raise RuntimeError("attention_fwd: qkv must be fp16")
     N, H, W, C3 = qkv.shape
@@ -355,6 +366,20 @@ def attention_fwd(qkv, heads, new_order=False, rows=None):
                                                    int(rows[0]), int(rows[1]), out.data_ptr(), Cc, lse.data_ptr(), _s()),
                     "b2d_attention_fwd_rows")
         return out, lse
+    Lk = H * W
+    ctas = N * heads * ((Lk + 255) // 256)
+    sms = _sm_count(qkv.device)
+    if ch in (64, 128) and Lk > 128 and 2 * ctas <= sms and split is not False:
+        # small grid (batch-1 sampling): split the keys so that ~all SMs get a CTA
+        splits = max(1, min(8, sms // ctas, ((Lk + (127 if ch == 64 else 63)) // (128 if ch == 64 else 64)) // 2))
+        if splits > 1:
+            nws = int(L.lib().b2d_attention_fwd_splitkv_ws_floats(N, Lk, heads, ch, splits))
+            ws = torch.empty(nws, device=qkv.device, dtype=torch.float32)
+            with _timed("attention_fwd", (N, Lk, heads, ch)):
+                L.check(L.lib().b2d_attention_fwd_splitkv(qkv.data_ptr(), qkv.stride(2), N, Lk, heads, ch, int(new_order),
+                                                          splits, ws.data_ptr(), nws, out.data_ptr(), Cc, lse.data_ptr(),
+                                                          _s()), "b2d_attention_fwd_splitkv")
+            return out, lse
     with _timed("attention_fwd", (N, H * W, heads, ch)):
         L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), qkv.stride(2), N, H * W, heads, ch, int(new_order),
                                           out.data_ptr(), Cc, lse.data_ptr(), _s()), "b2d_attention_fwd")

@@ -657,6 +657,40 @@ def test_wav2vec2_feature_extractor_under_autocast_with_all_patches_inside_the_1
         assert rel(p2.grad, p1.grad) <= 2e-2, (n1, rel(p2.grad, p1.grad))
 
 
+@pytest.mark.parametrize("N,S,ch,splits", [(1, 64, 64, 2), (1, 64, 64, 8), (1, 128, 64, 2), (2, 32, 128, 4), (1, 12, 64, 2),
+                                           (3, 16, 64, 3), (1, 24, 128, 5)])
+def test_attention_forward_split_over_keys_equals_the_single_pass_kernel(N, S, ch, splits):
+    """b2d_attention_fwd_splitkv (small grids: the reference samples one frame at a time) against b2d_attention_fwd on
+    the same input: output within the rounding of the 16-bit result, log-sum-exp to 1e-5; ragged last key tile
+    (L = 144, 576), splits that do not divide the tile count, and the dispatch rule of ops.attention_fwd."""
+    import ctypes as C
+    from lipreading_video_generation_b200 import _lib as L, ops
+    g = gen(N * S + ch + splits)
+    qkv = (torch.randn(N, S, S, 3 * ch, generator=g) * 1.2).half().cuda()
+    Lk = S * S
+    ref = torch.empty(N, S, S, ch, device="cuda", dtype=torch.float16)
+    ref_lse = torch.empty(N, 1, Lk, device="cuda")
+    L.check(L.lib().b2d_attention_fwd(qkv.data_ptr(), 3 * ch, N, Lk, 1, ch, 0, ref.data_ptr(), ch, ref_lse.data_ptr(),
+                                      torch.cuda.current_stream().cuda_stream), "b2d_attention_fwd")
+    nws = int(L.lib().b2d_attention_fwd_splitkv_ws_floats(N, Lk, 1, ch, splits))
+    ws = torch.full((nws,), float("nan"), device="cuda")
+    out = torch.full_like(ref, float("nan"))
+    lse = torch.full_like(ref_lse, float("nan"))
+    L.check(L.lib().b2d_attention_fwd_splitkv(qkv.data_ptr(), 3 * ch, N, Lk, 1, ch, 0, splits, ws.data_ptr(), nws,
+                                              out.data_ptr(), ch, lse.data_ptr(), torch.cuda.current_stream().cuda_stream),
+            "b2d_attention_fwd_splitkv")
+    assert torch.isfinite(out).all() and torch.isfinite(lse).all()
+    assert rel(out, ref) <= 1e-3
+    assert torch.allclose(lse, ref_lse, atol=1e-4, rtol=1e-5)
+    # the public op picks the split variant by itself when the grid would leave most SMs idle, and agrees as well
+    o2, l2 = ops.attention_fwd(qkv, 1)
+    assert rel(o2, ref) <= 1e-3 and torch.allclose(l2, ref_lse, atol=1e-4, rtol=1e-5)
+    # too small a workspace is an error, not a fault
+    rc = L.lib().b2d_attention_fwd_splitkv(qkv.data_ptr(), 3 * ch, N, Lk, 1, ch, 0, splits, ws.data_ptr(), nws - 1,
+                                           out.data_ptr(), ch, lse.data_ptr(), torch.cuda.current_stream().cuda_stream)
+    assert rc == 4
+
+
 # ----------------------------------------------------------------------------- Adam (row N3)
 @pytest.mark.parametrize("wd", [0.0, 0.01])
 def test_adam_multi_tensor_matches_torch_adam(wd):
@@ -806,7 +840,7 @@ def test_attention_row_shards_reassemble_to_the_unsharded_result(ch, L):
     g = gen(11)
     qkv = (torch.randn(1, L // 32, 32, 3 * ch, generator=g) * 0.7).half().cuda()
     d_out = (torch.randn(1, L // 32, 32, ch, generator=g) * 0.5).half().cuda()
-    out, lse = ops.attention_fwd(qkv, 1)
+    out, lse = ops.attention_fwd(qkv, 1, split=False)       # the un-split kernel: the shards below are bit-identical to it
     dqkv = ops.attention_bwd(qkv, out, d_out, lse, 1)
     for world in (2, 4):
         per = L // world
