@@ -553,10 +553,11 @@ def measure_hbm_kernels(device):
         torch.cuda.synchronize()
         side = torch.cuda.Stream(device=device)
         graph = torch.cuda.CUDAGraph()
-        with torch.cuda.stream(side):
+        keep = []         # outputs stay alive through the capture: every launch writes its own buffers (a freed output
+        with torch.cuda.stream(side):          # would be handed to the next launch and stay in L2)
             with torch.cuda.graph(graph, stream=side):
                 for i in range(reps):
-                    fn(i)
+                    keep.append(fn(i))
         torch.cuda.synchronize()
         graph.replay()
         torch.cuda.synchronize()
@@ -565,6 +566,7 @@ def measure_hbm_kernels(device):
         graph.replay()
         e1.record()
         torch.cuda.synchronize()
+        del keep, graph
         return e0.elapsed_time(e1) / reps
     with torch.no_grad():
         n = 256
