@@ -148,22 +148,46 @@ assemble_input_bwd_kernel(AssembleParams p, const __half* __restrict__ dX, float
 #pragma unroll
   for (int j = 0; j < 8; ++j) { acc[j][0] = acc[j][1] = acc[j][2] = 0.f; }
   if (prow < rows) {
-    for (int pix = blockIdx.x * rows + prow; pix < p.S * p.S; pix += gridDim.x * rows) {
-      float d[8];
-      ld8(dX + ((long long)n * p.S * p.S + pix) * p.Cpad + v * 8, d);
-      const int h = pix / p.S, w = pix - h * p.S;
-      float cv[3] = {0.f, 0.f, 0.f};
-      if (p.Cim > 0) {
-        const int shh = nearest_src(h, p.Hc, p.S), sww = nearest_src(w, p.Wc, p.S);
-        for (int k = 0; k < p.Cc && k < 3; ++k) cv[k] = p.cond[((long long)n * p.Cc + k) * p.Hc * p.Wc + shh * p.Wc + sww];
+    // per-thread channel classes as multipliers (no per-element branches), four pixels in flight per thread (one
+    // dependent 16-byte load per iteration left the kernel at 1.4 TB/s: 0.30 ms for 403 MB)
+    float mc[8], ma[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int c = v * 8 + j;
+      mc[j] = (c >= p.Cin && c < p.Cin + p.Cim) ? 1.f : 0.f;
+      ma[j] = (c >= p.Cin + p.Cim) ? 1.f : 0.f;
+    }
+    const int HW = p.S * p.S, step = gridDim.x * rows;
+    const long long cplane = (long long)p.Hc * p.Wc;
+    const float* cbase = p.Cim > 0 ? p.cond + (long long)n * p.Cc * cplane : nullptr;
+    for (int pix0 = blockIdx.x * rows + prow; pix0 < HW; pix0 += 4 * step) {
+      uint4 raw[4];
+      float cv[4][3];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        const int pix = pix0 + u * step;
+        cv[u][0] = cv[u][1] = cv[u][2] = 0.f;
+        if (pix < HW) {
+          raw[u] = ldg_nc_u4(dX + ((long long)n * HW + pix) * p.Cpad + v * 8);
+          if (cbase) {
+            const int h = pix / p.S, w = pix - h * p.S;
+            const int so = nearest_src(h, p.Hc, p.S) * p.Wc + nearest_src(w, p.Wc, p.S);
+#pragma unroll
+            for (int k = 0; k < 3; ++k) if (k < p.Cc) cv[u][k] = __ldg(cbase + k * cplane + so);
+          }
+        }
       }
 #pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const int c = v * 8 + j;
-        if (c >= p.Cin && c < p.Cin + p.Cim) {
-          acc[j][0] = fmaf(d[j], cv[0], acc[j][0]); acc[j][1] = fmaf(d[j], cv[1], acc[j][1]); acc[j][2] = fmaf(d[j], cv[2], acc[j][2]);
-        } else if (c >= p.Cin + p.Cim) {
-          acc[j][0] += d[j];
+      for (int u = 0; u < 4; ++u) {
+        if (pix0 + u * step >= HW) continue;
+        float d[8];
+        unpack8(raw[u], d);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float dc = d[j] * mc[j];
+          acc[j][0] = fmaf(dc, cv[u][0], fmaf(d[j], ma[j], acc[j][0]));
+          acc[j][1] = fmaf(dc, cv[u][1], acc[j][1]);
+          acc[j][2] = fmaf(dc, cv[u][2], acc[j][2]);
         }
       }
     }
@@ -532,7 +556,7 @@ extern "C" int b2d_assemble_input_bwd(const void* dX, const float* cond, int N, 
   B2D_REQUIRE(V <= 256, B2D_ERR_SHAPE, "assemble_input_bwd: too many channels");
   const int rows = 256 / V;
   long long chunks = ((long long)S * S + rows - 1) / rows;
-  long long cap = ((long long)num_sms() * 4 + N - 1) / N;
+  long long cap = ((long long)num_sms() * 8) / N;      // 8 CTAs of 256 threads per SM are resident: one wave
   if (chunks > cap) chunks = cap;
   if (chunks < 1) chunks = 1;
   dim3 grid((unsigned)chunks, (unsigned)N);
