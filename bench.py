@@ -440,11 +440,19 @@ def measure_train(steps, warmup, S, clips, frames, world, rank, local, device, v
            "step_tflops_algorithmic": round(train_tflop / (ms / 1000.0), 1),
            "step_frac_of_sustained_peak": round(train_tflop / (ms / 1000.0) / sustained, 4),
            "kernel_class_ms_per_step": {k: round(v, 3) for k, v in sorted(by_class.items())},
-           "clocks": clk.summary(), "last_loss": losses_host[-1], "images_per_gpu": n_img}
+           "clocks": clk.summary(), "last_loss": losses_host[-1], "images_per_gpu": n_img,
+           # calls the patched HF encoder handed to the stock library path over the whole run, per patch site
+           # (unet_audio.stock_route_counts): {} = every patched piece ran on this library's kernels
+           "w2v_stock_routes": _stock_routes()}
     del step, model, x0, cond, audio
     gc.collect()
     torch.cuda.empty_cache()
     return rec
+
+
+def _stock_routes():
+    import lipreading_video_generation_b200.unet_audio as UA
+    return UA.stock_route_counts(reset=True)
 
 
 def measure_sample(steps, warmup, S, clips, frames, world, rank, local, device):

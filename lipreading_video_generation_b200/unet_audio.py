@@ -8,6 +8,9 @@ the conditioning assembly (nearest resize, 1x1 cond conv, broadcast, concat) and
 """
 from __future__ import annotations
 
+import collections as _collections
+import os as _os
+
 import torch
 import torch.nn as nn
 
@@ -15,6 +18,27 @@ from .unet import UNetModel
 
 
 POS_CONV_TOEPLITZ_MAX_T = 32
+
+# Every patched piece of the third-party encoder checks the shapes its kernel is built for and hands anything else
+# to the stock HF / library code.  Those hand-offs are COUNTED here per patch site (`stock_route_counts()`; bench.py
+# prints them, tests assert them zero at the train.py / test.py shapes) and, with B2D_W2V_STRICT=1, raise on CUDA
+# tensors instead: a step that silently ran on the library path must not pass for one that ran on these kernels.
+_STOCK_ROUTES = _collections.Counter()
+
+
+def stock_route_counts(reset=False):
+    """{patch site: calls handed to the stock library path since import / the last reset}."""
+    out = dict(_STOCK_ROUTES)
+    if reset:
+        _STOCK_ROUTES.clear()
+    return out
+
+
+def _route_to_stock(site, on_cuda):
+    _STOCK_ROUTES[site] += 1
+    if on_cuda and _os.environ.get("B2D_W2V_STRICT", "0") == "1":
+        raise RuntimeError(f"b2d: {site}: shape / dtype not served by the sm_100a kernel and B2D_W2V_STRICT=1 "
+                           "forbids the stock library path")
 
 
 def _weight_normed(conv):
@@ -46,6 +70,7 @@ def _pos_conv_short_sequence(mod, hidden_states):
     K, pad, G = conv.kernel_size[0], conv.padding[0], conv.groups
     if (T > POS_CONV_TOEPLITZ_MAX_T or conv.stride[0] != 1 or conv.dilation[0] != 1 or K % 2 != 0 or pad != K // 2
             or T - 1 > pad or pad + T > K or conv.padding_mode != "zeros"):
+        _route_to_stock("pos_conv", hidden_states.is_cuda)
         return mod._b2d_stock_forward(hidden_states)
     cg = C // G
     w = _weight_normed(conv)                                          # (C, C/G, K), weight-norm evaluated here
@@ -69,6 +94,7 @@ def _conv1d_single_channel(conv, x):
     the (k, C_out) weight it is one small GEMM."""
     if (conv.in_channels != 1 or conv.groups != 1 or conv.dilation[0] != 1 or conv.padding[0] != 0
             or x.dim() != 3):
+        _route_to_stock("conv1d_single_channel", x.is_cuda)
         return conv._b2d_stock_forward(x)
     cols = x[:, 0].unfold(-1, conv.kernel_size[0], conv.stride[0])           # (B, T_out, k) view
     y = torch.matmul(cols, conv.weight[:, 0, :].t())                          # (B, T_out, C_out)
@@ -111,6 +137,7 @@ def _feature_layer0_fused(self, hidden_states):
           and S >= 10 and 2 <= (S - 10) // conv.stride[0] + 1 <= W2V_LAYER0_MAX_STEPS and S * 4 <= 200 * 1024
           and conv.weight.dtype == torch.float32)
     if not ok:
+        _route_to_stock("feature_layer0", hidden_states.is_cuda)
         return self._b2d_stock_forward(hidden_states)
     out_dtype = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else torch.float32
     audio = hidden_states[:, 0].float().contiguous()
@@ -166,6 +193,7 @@ def _short_attention_interface(module, query, key, value, attention_mask, dropou
           and query.dtype == key.dtype == value.dtype and query.dtype in (torch.float32, torch.bfloat16, torch.float16)
           and query.stride() == key.stride() == value.stride() and query.stride(3) == 1)
     if not ok:
+        _route_to_stock("short_attention", query.is_cuda)
         from transformers.modeling_utils import ALL_ATTENTION_FUNCTIONS
         return ALL_ATTENTION_FUNCTIONS["sdpa"](module, query, key, value, attention_mask, dropout=dropout,
                                                scaling=scaling, **kwargs)
@@ -213,6 +241,7 @@ def _layer_norm_fused(self, x):
           and x.shape[-1] // 32 in (2, 4, 8, 16, 24, 32) and x.shape[-1] % 32 == 0 and x.numel() > 0
           and (x.dtype == torch.float32 or (x.dtype in (torch.bfloat16, torch.float16) and torch.is_autocast_enabled("cuda"))))
     if not ok:
+        _route_to_stock("layer_norm", x.is_cuda)
         return self._b2d_stock_forward(x)
     return _LayerNormFn.apply(x, self.weight, self.bias, self.eps)
 
@@ -274,6 +303,10 @@ def _linear_fused(self, x):
           and dt in (torch.bfloat16, torch.float16) and x.dtype in (torch.float32, torch.bfloat16, torch.float16)
           and self.out_features % 2 == 0 and x.numel() > 0)
     if not ok:
+        # eval / no-grad calls (the sampler) and fp32 runs are the stock module by design: the patch only replaces
+        # the 16-bit training backward.  Counted separately so that a training step can assert on "linear_train".
+        _route_to_stock("linear_train" if (x.is_cuda and torch.is_grad_enabled() and self.weight.requires_grad
+                                           and dt in (torch.bfloat16, torch.float16)) else "linear_eval_or_fp32", False)
         return self._b2d_stock_forward(x)
     return _LinearFn.apply(x, self.weight, self.bias)
 
@@ -299,6 +332,7 @@ def _mask_hidden_states_no_sync(self, hidden_states, mask_time_indices=None, att
     if not getattr(self.config, "apply_spec_augment", True):
         return hidden_states
     if not hidden_states.is_cuda:
+        _route_to_stock("spec_augment", False)
         return self._b2d_stock_mask_hidden_states(hidden_states, mask_time_indices=mask_time_indices,
                                                   attention_mask=attention_mask)
     batch_size, sequence_length, hidden_size = hidden_states.size()
@@ -364,6 +398,7 @@ def _feature_encoder_channels_last(self, input_values):
                   and l.conv.padding[0] == 0 and l.conv.dilation[0] == 1 and l.conv.groups == 1
                   and l.conv.padding_mode == "zeros" for l in layers[1:]))
     if not ok:
+        _route_to_stock("feature_convs", input_values.is_cuda)
         return self._b2d_stock_forward(input_values)
     h = layers[0](input_values[:, None])
     if h.dtype in (torch.bfloat16, torch.float16):

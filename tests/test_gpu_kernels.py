@@ -420,10 +420,39 @@ def test_w2v_layer0_fused_autocast_output_dtype_and_bar():
         assert rel(fused.get_parameter(name).grad, stock.get_parameter(name).grad) <= TOL16_KERNEL, name
 
 
-def test_w2v_layer0_unsupported_shapes_take_the_stock_path():
+def test_w2v_layer0_unsupported_shapes_take_the_stock_path_and_are_counted(monkeypatch):
+    import lipreading_video_generation_b200.unet_audio as UA
     stock, fused = _w2v_layer0_pair()
     a = torch.randn(1, 1, 6000, generator=gen(5)).cuda()       # 1199 steps > 800
+    UA.stock_route_counts(reset=True)
     assert torch.equal(fused(a), stock(a))
+    assert UA.stock_route_counts() == {"feature_layer0": 1}
+    monkeypatch.setenv("B2D_W2V_STRICT", "1")                  # strict mode: the hand-off is an error, not a route
+    with pytest.raises(RuntimeError, match="feature_layer0"):
+        fused(a)
+    UA.stock_route_counts(reset=True)
+
+
+def test_wav2vec2_training_step_at_the_train_py_shape_hands_nothing_to_the_stock_path(monkeypatch):
+    """the patches route shapes they are not built for to the stock HF code.  At train.py's shape
+    (4000-sample windows, bf16 autocast as bench.py runs the encoder) a forward + backward in train mode must take NO
+    such route on any patch site -- asserted through the public counter and, again, under B2D_W2V_STRICT=1."""
+    import lipreading_video_generation_b200.unet_audio as UA
+    monkeypatch.setenv("B2D_W2V_STRICT", "1")
+    torch.manual_seed(0)
+    enc = UA.Wav2Vec2Encoder(pretrained=False).cuda().train()
+    audio = torch.randn(32, 4000, generator=gen(9)).cuda()
+    UA.stock_route_counts(reset=True)
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        out = enc({"input_values": audio})
+    out.float().mean().backward()
+    torch.cuda.synchronize()
+    assert UA.stock_route_counts() == {}, UA.stock_route_counts()
+    # the sampler's no-grad call: only nn.Linear is the stock module (the patch replaces its training backward only)
+    enc.eval()
+    with torch.no_grad(), torch.autocast("cuda", dtype=torch.bfloat16):
+        enc({"input_values": audio})
+    assert set(UA.stock_route_counts(reset=True)) <= {"linear_eval_or_fp32"}
 
 
 # ----------------------------------------------------------------------------- short-sequence attention (wav2vec2 encoder)
