@@ -29,10 +29,13 @@ def _nchw(t):                         # pixel-major (N,H,W,C) -> the reference's
 @pytest.mark.parametrize("N,H,W,cin,cout,k,extras", [
     (3, 32, 32, 64, 128, 3, False), (5, 8, 8, 128, 64, 1, True), (2, 16, 16, 64, 256, 3, True),
     (2, 16, 16, 128, 192, 1, False), (1, 64, 64, 64, 64, 3, True)])
-def test_conv_epilogue_pair_statistics(N, H, W, cin, cout, k, extras):
+@pytest.mark.parametrize("halo", ["0", "1"])
+def test_conv_epilogue_pair_statistics(N, H, W, cin, cout, k, extras, halo, monkeypatch):
     """gn_stats_out of a convolution == pair sums of its own output (one-pass kernel and torch), incl. tiles that hold
-    several images with a ragged last tile (N = 5 at 8x8), two N tiles (256 channels), bias + emb + residual."""
+    several images with a ragged last tile (N = 5 at 8x8), two N tiles (256 channels), bias + emb + residual.
+    halo = "1": the opt-in haloed-patch variant of the 3x3 kernel (conv_gemm.cu) where the shape allows it."""
     from lipreading_video_generation_b200 import ops
+    monkeypatch.setenv("B2D_CONV_HALO", halo)
     g = gen(N * H + cout)
     x = torch.randn(N, H, W, cin, generator=g).half().cuda()
     w = (torch.randn(cout, cin, k, k, generator=g) / (cin * k * k) ** 0.5).cuda()
@@ -116,11 +119,13 @@ def test_groupnorm_apply_dropout_mask_bits_match_the_output():
 @pytest.mark.parametrize("N,H,W,C1,C2,cnext,k,act,drop", [
     (2, 32, 32, 64, 0, 64, 3, True, 0.0), (2, 16, 16, 128, 64, 128, 3, True, 0.0), (3, 16, 16, 256, 0, 768, 1, False, 0.0),
     (2, 32, 32, 128, 0, 128, 3, True, 0.1), (5, 8, 8, 64, 0, 64, 3, True, 0.1), (2, 16, 16, 256, 128, 256, 3, True, 0.0)])
-def test_groupnorm_backward_fused_into_the_data_gradient_convolution(N, H, W, C1, C2, cnext, k, act, drop):
+@pytest.mark.parametrize("halo", ["0", "1"])
+def test_groupnorm_backward_fused_into_the_data_gradient_convolution(N, H, W, C1, C2, cnext, k, act, drop, halo, monkeypatch):
     """y = dropout(act(GroupNorm([x1 | x2]))), o = conv(y): given dL/do, the data-gradient convolution with the gnb
     epilogue + b2d_groupnorm_bwd_apply must equal autograd of the same chain (fp32, same dropout mask): dx1, dx2 (with
-    the fused residual adds), dgamma, dbeta, and the column sums of dx1."""
+    the fused residual adds), dgamma, dbeta, and the column sums of dx1.  halo = "1": haloed-patch variant (3x3 only)."""
     from lipreading_video_generation_b200 import ops
+    monkeypatch.setenv("B2D_CONV_HALO", halo)
     g = gen(C1 + C2 + cnext + H)
     Ct = C1 + C2
     x1 = (torch.randn(N, H, W, C1, generator=g) + 0.2).half().cuda()

@@ -164,6 +164,49 @@ def test_conv2d_fprop(N, H, C1, C2, Cout, k, stride, extras):
     assert e <= TOL16_KERNEL, e
 
 
+@pytest.mark.parametrize("N,H,W,C1,C2,Cout,extras", [
+    (2, 16, 8, 64, 0, 64, False),        # one patch per image, weights resident
+    (1, 64, 64, 64, 0, 64, True),        # 32 patches, bias + emb + residual (fetched a tile ahead)
+    (40, 32, 32, 64, 0, 64, True),       # 320 tiles on 148 persistent CTAs: rings and staging slots wrap
+    (2, 32, 32, 64, 0, 192, False),      # three resident N tiles: grid rounded to a multiple of three
+    (3, 16, 16, 64, 0, 256, True),
+    (2, 32, 16, 128, 0, 128, True),      # streamed weights, BN = 128, non-square plane
+    (24, 32, 32, 128, 0, 128, False),    # streamed, 192 tiles
+    (2, 16, 16, 128, 64, 64, True),      # two sources, streamed, BN = 64
+    (3, 16, 16, 256, 128, 256, True),    # two sources, two N tiles of 128
+    (1, 32, 32, 192, 0, 128, False)])
+def test_conv2d_3x3_from_haloed_patches_vs_torch_and_the_per_tap_kernel(N, H, W, C1, C2, Cout, extras, monkeypatch):
+    """3x3 stride-1 convolutions on planes of 16k x 8m pixels load each 16 x 8 patch once with its halo and take the
+    nine taps as shifted shared-memory views (conv_gemm.cu, HALO variant).  Against torch's fp32 convolution of the same
+    16-bit operands, and against this library's per-tap kernel (B2D_CONV_HALO=0; the K order differs, so not bitwise)."""
+    from lipreading_video_generation_b200 import ops
+    g = gen(N + H + W + Cout)
+    x = torch.randn(N, H, W, C1, generator=g).half()
+    x2 = torch.randn(N, H, W, C2, generator=g).half() if C2 else None
+    w = torch.randn(Cout, C1 + C2, 3, 3, generator=g) / math.sqrt((C1 + C2) * 9)
+    bias = torch.randn(Cout, generator=g) if extras else None
+    emb = torch.randn(N, Cout, generator=g) if extras else None
+    res = torch.randn(N, H, W, Cout, generator=g).half() if extras else None
+    cu = lambda t: None if t is None else t.cuda()  # noqa: E731
+    wp = ops.pack_conv_weight(w.cuda())
+    run = lambda: ops.conv2d(cu(x), wp, Cout, 3, 1, x2=cu(x2), bias=cu(bias), emb=cu(emb), residual=cu(res))  # noqa: E731
+    monkeypatch.setenv("B2D_CONV_HALO", "1")
+    out = run()
+    again = run()
+    monkeypatch.setenv("B2D_CONV_HALO", "0")
+    per_tap = run()
+    torch.cuda.synchronize()
+    assert torch.equal(out, again), "same launch twice must give the same bits"
+    xin = x.float() if x2 is None else torch.cat([x.float(), x2.float()], 3)
+    ref = F.conv2d(xin.permute(0, 3, 1, 2), w.half().float(), bias, 1, 1)
+    if extras:
+        ref = ref + emb[:, :, None, None] + res.float().permute(0, 3, 1, 2)
+    assert rel(out.permute(0, 3, 1, 2), ref) <= TOL16_KERNEL
+    assert rel(out, per_tap) <= 1e-3
+    # every pixel of every patch, borders included: the worst single element, not only the norm
+    assert (out.float() - per_tap.float()).abs().max().item() <= 2e-2 * max(1.0, per_tap.float().abs().max().item())
+
+
 def test_conv2d_head_writes_fp32_nchw_and_small_cout():
     from lipreading_video_generation_b200 import ops
     g = gen(7)
