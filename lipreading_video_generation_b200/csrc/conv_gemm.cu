@@ -489,13 +489,9 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       if (p.BN > 64) { const uint2 hi = __ldg(reinterpret_cast<const uint2*>(mp + 8)); mbits.z = hi.x; mbits.w = hi.y; }
     }
     const bool fast_cols = (n0 + p.BN <= p.Cout);      // whole tile inside the logical channels: vector path
-    uint4 rres[16];                                    // residual row segment: up to 128 columns of fp16
+    // direct path (outputs that are not whole 64-channel blocks): residual segments by 16-byte loads inside the chunk
+    // loop (the staged path, which serves every other layer, fetches the residual tile by TMA)
     const bool res_vec = !p.tma_out && p.residual && valid && fast_cols && ((p.ldres & 7) == 0) && ((((uintptr_t)p.residual) & 15) == 0);
-    if (res_vec) {
-      const __half* rp = p.residual + pix * p.ldres + n0;
-#pragma unroll
-      for (int g = 0; g < 16; ++g) if (g * 8 < p.BN && ((g >> 1) % CSPLIT) == csel) rres[g] = ldg_nc_u4(rp + g * 8);
-    }
     named_bar_sync(1, EPI_THREADS);                                 // eb staging visible to the epilogue warps
     mbar_wait(&acc_full[buf], (uint32_t)((lt >> 1) & 1));
     tc_fence_after();
@@ -513,10 +509,12 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       const long long wpix = (long long)tile_m * 128 + q * 32;
       const bool wvalid = HALO ? true : wpix < p.total_pixels;
       const int wslot = (!HALO && wvalid) ? (int)(wpix / p.HoWo) - img_first : 0;
-#pragma unroll
-      for (int cc = 0; cc < 8; ++cc) {
+      // a real loop over this warp's chunks: unrolled eight-fold the three epilogue variants came to 30 k SASS
+      // instructions (480 KB of code), most of it never executed by a given warp
+#pragma unroll 1
+      for (int cc = csel; cc < 8; cc += CSPLIT) {
         const int c0 = cc * 16;
-        if (c0 < p.BN && (cc % CSPLIT) == csel) {
+        if (c0 < p.BN) {
           uint32_t r[16];
           __syncwarp();
           tmem_ld16(taddr + (uint32_t)c0, r);
@@ -626,10 +624,10 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       }
       continue;
     }
-#pragma unroll
-    for (int cc = 0; cc < 8; ++cc) {
+#pragma unroll 1
+    for (int cc = csel; cc < 8; cc += CSPLIT) {
       const int c0 = cc * 16;
-      if (c0 < p.BN && (cc % CSPLIT) == csel) {
+      if (c0 < p.BN) {
       uint32_t r[16];
       __syncwarp();
       tmem_ld16(taddr + (uint32_t)c0, r);
@@ -649,7 +647,8 @@ conv_gemm_kernel(const __grid_constant__ ConvMaps maps, const ConvParams p) {
       }
       if (p.residual) {
         if (res_vec) {
-          const uint4 u0 = rres[2 * cc], u1 = rres[2 * cc + 1];
+          const __half* rp = p.residual + pix * p.ldres + col0;
+          const uint4 u0 = ldg_nc_u4(rp), u1 = ldg_nc_u4(rp + 8);
           const uint32_t w[8] = {u0.x, u0.y, u0.z, u0.w, u1.x, u1.y, u1.z, u1.w};
 #pragma unroll
           for (int j = 0; j < 8; ++j) { float2 f = unpack_f16x2(w[j]); v[2 * j] += f.x; v[2 * j + 1] += f.y; }
