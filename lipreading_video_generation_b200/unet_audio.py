@@ -262,19 +262,25 @@ class _LinearFn(torch.autograd.Function):
     dx / dW taken from the gradient GEMMs' fp32 accumulators instead of their 16-bit roundings + casts."""
 
     @staticmethod
-    def forward(ctx, x, weight, bias):
+    def forward(ctx, x, weight, bias, w16=None, b16=None):
         dt = torch.get_autocast_dtype("cuda") if torch.is_autocast_enabled("cuda") else x.dtype
-        xb, wb = x.to(dt), weight.to(dt)
+        xb = x.to(dt)
+        # w16 / b16: this step's 16-bit copies from the encoder's cast cache (one multi-tensor copy per forward instead
+        # of two cast kernels per Linear); they are refreshed in place by the next forward, so they are kept as plain
+        # attributes -- autograd's version check is for tensors whose VALUES may have changed, these hold the same values
+        # until the optimiser has stepped
+        wb = weight.to(dt) if w16 is None else w16
         with torch.autocast("cuda", enabled=False):
-            y = torch.nn.functional.linear(xb, wb, bias.to(dt))
-        ctx.save_for_backward(xb, wb)
+            y = torch.nn.functional.linear(xb, wb, bias.to(dt) if b16 is None else b16)
+        ctx.save_for_backward(xb)
+        ctx.wb = wb
         ctx.dts = (x.dtype, weight.dtype, bias.dtype)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         from . import ops
-        xb, wb = ctx.saved_tensors
+        (xb,), wb = ctx.saved_tensors, ctx.wb
         dx = dw = db = None
         dy2 = dy.reshape(-1, dy.shape[-1])
         if dy2.dtype != xb.dtype:
@@ -293,7 +299,10 @@ class _LinearFn(torch.autograd.Function):
                 dw = mm(dy2.t(), xb.reshape(-1, xb.shape[-1]), ctx.dts[1])
         if ctx.needs_input_grad[2]:
             db = ops.colsum_rows16(dy2).to(ctx.dts[2])
-        return dx, dw, db
+        return dx, dw, db, None, None
+
+
+_CAST_CACHE_ACTIVE = [False]      # True while Wav2Vec2Encoder.forward runs with a refreshed cast cache
 
 
 def _linear_fused(self, x):
@@ -308,6 +317,9 @@ def _linear_fused(self, x):
         _route_to_stock("linear_train" if (x.is_cuda and torch.is_grad_enabled() and self.weight.requires_grad
                                            and dt in (torch.bfloat16, torch.float16)) else "linear_eval_or_fp32", False)
         return self._b2d_stock_forward(x)
+    w16 = getattr(self, "_b2d_w16", None) if _CAST_CACHE_ACTIVE[0] else None
+    if w16 is not None and w16.dtype == dt and w16.device == x.device:
+        return _LinearFn.apply(x, self.weight, self.bias, w16, self._b2d_b16)
     return _LinearFn.apply(x, self.weight, self.bias)
 
 
@@ -463,8 +475,49 @@ class Wav2Vec2Encoder(nn.Module):
             if os.environ.get("B2D_W2V_CHANNELS_LAST", "1") != "0":
                 patch_feature_convs(self.wav2vec2)
 
+        self._cast_cache = None
+        self._cast_cache_on = os.environ.get("B2D_W2V_CAST_CACHE", "1") != "0"
+
+    def _refresh_cast_cache(self, dt, device):
+        """16-bit copies of the patched Linear layers' weights and biases for this forward: views of one flat buffer,
+        refreshed by ONE multi-tensor copy (autocast casts each fp32 weight and bias with a kernel of its own on every
+        call: ~150 launches of 3-8 us per train step)."""
+        mods = [m for m in self.wav2vec2.modules()
+                if type(m) is nn.Linear and hasattr(m, "_b2d_stock_forward") and m.bias is not None]
+        key = (dt, device, tuple(id(m.weight) for m in mods))
+        if self._cast_cache is None or self._cast_cache[0] != key:
+            if not mods or any(m.weight.device != device or m.weight.dtype != torch.float32 for m in mods):
+                self._cast_cache = (key, None, None)
+            else:
+                src = [t for m in mods for t in (m.weight, m.bias)]
+                sizes = [(t.numel() + 7) // 8 * 8 for t in src]                  # 16-byte aligned views
+                flat = torch.empty(sum(sizes), dtype=dt, device=device)
+                dst, off = [], 0
+                for t, n in zip(src, sizes):
+                    dst.append(flat[off:off + t.numel()].view(t.shape))
+                    off += n
+                for i, m in enumerate(mods):
+                    m._b2d_w16, m._b2d_b16 = dst[2 * i], dst[2 * i + 1]
+                self._cast_cache = (key, src, dst)
+        _, src, dst = self._cast_cache
+        if src is None:
+            return False
+        with torch.no_grad():
+            torch._foreach_copy_(dst, src)
+        return True
+
     def forward(self, audio_input):
-        return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state
+        x = audio_input.get("input_values") if hasattr(audio_input, "get") else None      # dict or HF BatchFeature
+        use = (self._cast_cache_on and self.training and torch.is_grad_enabled() and x is not None and x.is_cuda
+               and torch.is_autocast_enabled("cuda") and hasattr(torch, "_foreach_copy_"))
+        if use:
+            use = self._refresh_cast_cache(torch.get_autocast_dtype("cuda"), x.device)
+        prev = _CAST_CACHE_ACTIVE[0]
+        _CAST_CACHE_ACTIVE[0] = bool(use)
+        try:
+            return self.wav2vec2(**audio_input, output_hidden_states=True).last_hidden_state
+        finally:
+            _CAST_CACHE_ACTIVE[0] = prev
 
 
 class AudioFeatureTransformer(nn.Module):

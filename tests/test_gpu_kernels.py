@@ -476,6 +476,47 @@ def test_w2v_layer0_unsupported_shapes_take_the_stock_path_and_are_counted(monke
     UA.stock_route_counts(reset=True)
 
 
+def test_wav2vec2_cast_cache_equals_per_call_casts():
+    """Wav2Vec2Encoder.forward refreshes 16-bit copies of the Linear weights / biases with one multi-tensor copy and the
+    patched Linear layers use them instead of casting per call: same rounding of the same values, so the output and
+    gradients of a training step must be the same with the cache on and off (same seeds for dropout, LayerDrop and
+    SpecAugment; output bit-identical), also for a second step after the weights have changed."""
+    import copy
+    import numpy as np
+    import lipreading_video_generation_b200.unet_audio as UA
+    torch.manual_seed(0)
+    enc_a = UA.Wav2Vec2Encoder(pretrained=False).cuda().train()
+    enc_b = copy.deepcopy(enc_a)
+    enc_b._cast_cache_on = False
+    assert enc_a._cast_cache_on
+    audio = torch.randn(8, 4000, generator=gen(3)).cuda()
+
+    def step(enc, seed):
+        torch.manual_seed(seed)
+        np.random.seed(seed)
+        UA._short_attention_calls[0] = 0          # the attention-dropout seeds count calls: same stream for both encoders
+        enc.zero_grad(set_to_none=True)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = enc({"input_values": audio})
+        out.float().square().mean().backward()
+        return out.detach().clone(), {k: p.grad.clone() for k, p in enc.named_parameters() if p.grad is not None}
+
+    for seed in (11, 12):
+        oa, ga = step(enc_a, seed)
+        ob, gb = step(enc_b, seed)
+        assert enc_a._cast_cache is not None and enc_a._cast_cache[1] is not None and enc_b._cast_cache is None
+        assert torch.equal(oa, ob)                              # the forward is deterministic: same bits
+        # the backward accumulates some gradients with atomics (bias / LayerNorm column sums), so two runs of the SAME
+        # encoder differ in the last bits and, through 16-bit roundings downstream, by ~1e-3: bound, not bit-compare
+        assert ga.keys() == gb.keys()
+        worst = max(rel(ga[k], gb[k]) for k in ga)
+        assert worst <= 1e-2, worst
+        with torch.no_grad():                                   # an optimiser step: the next forward must see the new weights
+            for pa, pb in zip(enc_a.parameters(), enc_b.parameters()):
+                pa.add_(0.01 * torch.sign(pa))
+                pb.copy_(pa)
+
+
 def test_wav2vec2_training_step_at_the_train_py_shape_hands_nothing_to_the_stock_path(monkeypatch):
     """the patches route shapes they are not built for to the stock HF code.  At train.py's shape
     (4000-sample windows, bf16 autocast as bench.py runs the encoder) a forward + backward in train mode must take NO
