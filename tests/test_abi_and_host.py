@@ -282,6 +282,27 @@ def test_short_attention_interface_falls_back_to_library_sdpa_on_cpu_tensors():
     assert UA._short_attention_calls[0] == n0
 
 
+def test_stock_route_counter_counts_cpu_hand_offs_and_strict_mode_leaves_cpu_tensors_alone(monkeypatch):
+    """Every patched encoder piece counts the calls it hands to the stock library path ("at least count and
+    expose the fallbacks").  On CPU tensors everything is a hand-off: the counter must name the patch sites, reset on
+    request, and B2D_W2V_STRICT=1 must not raise for CPU tensors (it guards the GPU product path only).  The cast cache
+    of Wav2Vec2Encoder stays off outside CUDA + autocast + training."""
+    import lipreading_video_generation_b200.unet_audio as UA
+    monkeypatch.setenv("B2D_W2V_STRICT", "1")
+    torch.manual_seed(0)
+    enc = UA.Wav2Vec2Encoder(pretrained=False).eval()
+    UA.stock_route_counts(reset=True)
+    with torch.no_grad():
+        out = enc({"input_values": torch.randn(2, 4000)})
+    assert out.shape == (2, 12, 768)
+    routes = UA.stock_route_counts()
+    for site in ("feature_layer0", "layer_norm", "short_attention", "feature_convs", "linear_eval_or_fp32"):
+        assert routes.get(site, 0) > 0, (site, routes)
+    assert routes["short_attention"] == 12 and routes["feature_convs"] == 1 and routes["feature_layer0"] == 1
+    assert UA.stock_route_counts(reset=True) == routes and UA.stock_route_counts() == {}
+    assert enc._cast_cache is None and UA._CAST_CACHE_ACTIVE == [False]
+
+
 # ----------------------------------------------------------------------------- Adam (row N3) host logic
 def test_adam_chunk_table_splits_tensors_into_runs_and_matches_the_c_struct():
     import ctypes as C
