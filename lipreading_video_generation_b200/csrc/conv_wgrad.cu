@@ -302,43 +302,53 @@ conv_wgrad_halo_kernel(const __grid_constant__ HaloMaps maps, const HaloParams p
       }
     }
   } else if (warp == 1) {
-    const uint32_t idesc = make_idesc(128, BN, 1, 1, FMT_F16, FMT_F16);  // both operands MN-major
-    const int spr_mask = (1 << p.spr_shift) - 1;
-    for (int it = 0; it < my_iters; ++it) {
-      const int s = it % p.stages;
-      const uint32_t par = (uint32_t)((it / p.stages) & 1);
-      mbar_wait(&full_bar[s], par);
-      tc_fence_after();
-      if (elect_one()) {
-        const uint32_t base = smem_u32(smem + (size_t)s * p.stage_bytes);
-        const uint32_t dy_addr = base + dy_off, x_addr = base + x_off;
-#pragma unroll 1
+    // One issuing thread, ring slot / phase by counting, descriptors by addition on the 32-bit words (hi = stride byte
+    // offset 1024 + version + swizzle mode, constant; lo = address >> 4 | LBO >> 4 << 16): the same finding as in
+    // conv_gemm.cu -- ~100 instructions of descriptor assembly per K = 16 slice cost more issue time than the slice's
+    // three to five MMAs take on the tensor pipe (162-270 clk).
+    if (lane == 0) {
+      const uint32_t idesc = make_idesc(128, BN, 1, 1, FMT_F16, FMT_F16);  // both operands MN-major
+      const int spr_mask = (1 << p.spr_shift) - 1;
+      const uint32_t hi = (uint32_t)(make_sdesc_sw128(0, 0, 1024) >> 32);
+      auto desc = [hi](uint32_t lo) { return ((uint64_t)hi << 32) | lo; };
+      const uint32_t ring = smem_u32(smem);
+      const uint32_t pitch16 = (uint32_t)p.pitch * 8u;                     // one pixel row of the haloed tile, in 16-byte units
+      const uint32_t lbo_blk = (uint32_t)(BLK >> 4) << 16, lbo_x = (p.xblk_bytes >> 4) << 16;
+      int s = 0;
+      uint32_t par = 0;
+      for (int it = 0; it < my_iters; ++it) {
+        mbar_wait(&full_bar[s], par);
+        tc_fence_after();
+        const uint32_t base = ring + (uint32_t)s * p.stage_bytes;
+        const uint32_t dy_lo = ((base + dy_off) >> 4) | lbo_blk;
+        const uint32_t x16 = (base + x_off) >> 4;
+#pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int r = j >> p.spr_shift, c0 = (j & spr_mask) << 4;
           const uint32_t acc = (uint32_t)((it | j) != 0);
+          const uint32_t xv = x16 + (uint32_t)r * pitch16 + (uint32_t)c0 * 8u;   // the slice's 16 pixels in the tile
           if (MODE == 0) {
-            const uint64_t a = make_sdesc_sw128(dy_addr + j * 2048, BLK, 1024);
-            const uint32_t xv = x_addr + (uint32_t)(r * p.pitch + c0) * 128u;
+            const uint64_t a = desc(dy_lo + (uint32_t)j * 128u);
 #pragma unroll
             for (int kx = 0; kx < 3; ++kx)
-              mma_f16_ss(tmem_base + (uint32_t)(kx * BN), a, make_sdesc_sw128(xv + kx * 128, p.xblk_bytes, 1024), idesc, acc);
+              mma_f16_ss(tmem_base + (uint32_t)(kx * BN), a, desc((xv + (uint32_t)kx * 8u) | lbo_x), idesc, acc);
           } else {
-            const uint64_t b = make_sdesc_sw128(dy_addr + j * 2048, BLK, 1024);
-            const uint32_t xv = x_addr + (uint32_t)(r * p.pitch + c0) * 128u;
-            const uint32_t row = (uint32_t)p.pitch * 128u;
-            // views of taps t = 3 * ky + kx at xv + ky * row + kx * 128; pairs (0,1) (2,3) (4,5) (6,7) (8,8)
-            mma_f16_ss(tmem_base + 0,   make_sdesc_sw128(xv, 128, 1024), b, idesc, acc);
-            mma_f16_ss(tmem_base + 64,  make_sdesc_sw128(xv + 256, row - 256, 1024), b, idesc, acc);
-            mma_f16_ss(tmem_base + 128, make_sdesc_sw128(xv + row + 128, 128, 1024), b, idesc, acc);
-            mma_f16_ss(tmem_base + 192, make_sdesc_sw128(xv + 2 * row, 128, 1024), b, idesc, acc);
-            mma_f16_ss(tmem_base + 256, make_sdesc_sw128(xv + 2 * row + 256, 0, 1024), b, idesc, acc);
+            const uint64_t b = desc(dy_lo + (uint32_t)j * 128u);
+            // views of taps t = 3 * ky + kx at xv + ky * row + kx * 128 B; pairs (0,1) (2,3) (4,5) (6,7) (8,8):
+            // LBO = byte distance between the pair's two views
+            mma_f16_ss(tmem_base + 0,   desc(xv | (8u << 16)), b, idesc, acc);
+            mma_f16_ss(tmem_base + 64,  desc((xv + 16u) | ((pitch16 - 16u) << 16)), b, idesc, acc);
+            mma_f16_ss(tmem_base + 128, desc((xv + pitch16 + 8u) | (8u << 16)), b, idesc, acc);
+            mma_f16_ss(tmem_base + 192, desc((xv + 2u * pitch16) | (8u << 16)), b, idesc, acc);
+            mma_f16_ss(tmem_base + 256, desc(xv + 2u * pitch16 + 16u), b, idesc, acc);
           }
         }
         mma_commit(&empty_bar[s]);
         if (it == my_iters - 1) mma_commit(acc_bar);
+        if (++s == p.stages) { s = 0; par ^= 1u; }
       }
-      __syncwarp();
     }
+    __syncwarp();
   } else {
     const int q = warp & 3;
     const int row = q * 32 + lane;
