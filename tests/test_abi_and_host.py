@@ -303,6 +303,26 @@ def test_stock_route_counter_counts_cpu_hand_offs_and_strict_mode_leaves_cpu_ten
     assert enc._cast_cache is None and UA._CAST_CACHE_ACTIVE == [False]
 
 
+def test_every_environment_switch_the_code_reads_is_documented():
+    """Each B2D_* variable read with getenv / os.environ in the package, the bench or the entry points appears in
+    INTEGRATION.md's switch table (or DESIGN.md): an undocumented switch is an undocumented code path."""
+    import glob
+    import os
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    pkg = os.path.join(root, "lipreading_video_generation_b200")
+    files = (glob.glob(os.path.join(pkg, "*.py")) + glob.glob(os.path.join(pkg, "csrc", "*.cu")) +
+             glob.glob(os.path.join(pkg, "csrc", "*.cuh")) + [os.path.join(root, "bench.py"), os.path.join(root, "__graft_entry__.py")])
+    pat = re.compile(r'(?:getenv\(\s*|environ\.get\(\s*|environ\[\s*|setdefault\(\s*)"(B2D_[A-Z0-9_]+)"')
+    read = set()
+    for f in files:
+        read |= set(pat.findall(open(f).read()))
+    assert len(read) >= 20, read                      # the pattern still matches how the code reads its switches
+    docs = open(os.path.join(root, "INTEGRATION.md")).read() + open(os.path.join(root, "DESIGN.md")).read()
+    missing = sorted(v for v in read if v not in docs)
+    assert not missing, missing
+
+
 # ----------------------------------------------------------------------------- Adam (row N3) host logic
 def test_adam_chunk_table_splits_tensors_into_runs_and_matches_the_c_struct():
     import ctypes as C
